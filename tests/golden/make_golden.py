@@ -1,0 +1,148 @@
+"""Generate the golden fixtures by RUNNING THE REFERENCE ITSELF (CPU, fp32).
+
+    python tests/golden/make_golden.py            # needs /root/reference (or $VFDEPTH_REF)
+
+Writes ``golden_fusion.npz`` and ``golden_warp.npz`` next to this file.  The
+fixtures hold the seeded inputs and what the reference's own classes
+(``VFNet``, ``ViewRendering``, ``Pose``, ``MultiCamLoss``) returned for them, at
+sizes small enough to commit.  ``tests/test_oracle_golden.py`` then pins
+``oracle/vfdepth_oracle.py`` to these bit for bit, and the GPU parity tests
+check the CUDA path against the same files.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_import  # noqa: E402
+from vfdepth_b200 import config as vcfg  # noqa: E402
+from vfdepth_b200.rig import make_rig  # noqa: E402
+
+FUSION_CFG = dict(model__voxel_size=[14, 12, 4], model__voxel_str_p=[-17.5, -15.0, -3.0],
+                  model__voxel_unit_size=[2.5, 2.5, 1.5], model__proj_d_bins=6, model__proj_d_str=2,
+                  model__proj_d_end=16, model__fusion_feat_in_dim=8, model__voxel_pre_dim=[4],
+                  training__height=64, training__width=96)
+WARP_CFG = dict(training__height=48, training__width=64, training__focal_length_scale=30)
+
+
+def fusion_cfg():
+    return vcfg.default_config('ddad', batch_size=2, **FUSION_CFG)
+
+
+def warp_cfg():
+    return vcfg.default_config('ddad', batch_size=2, **WARP_CFG)
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def make_fusion(ref, path):
+    cfg = fusion_cfg()
+    inputs, extras = make_rig(cfg, seed=4242, with_images=False)
+    C = cfg['model']['fusion_feat_in_dim']
+    lvl = cfg['model']['fusion_level'] + 1
+    out = {'feats_agg': _np(extras['feats_agg']), 'mask': _np(inputs['mask']),
+           'K': _np(inputs[('K', lvl)]), 'inv_K': _np(inputs[('inv_K', lvl)]),
+           'extrinsics': _np(inputs['extrinsics']), 'extrinsics_inv': _np(inputs['extrinsics_inv'])}
+    torch.manual_seed(7)
+    net = ref.VFNet(cfg, C, 16, model='depth')
+    net.reduce_dim = torch.nn.Identity()        # keep the raw ray samples (:262), skip the convs of :265
+    net.type_check(extras['feats_agg'][0, 0])
+    feats = extras['feats_agg'].clone().requires_grad_(True)
+    vox = net.backproject_into_voxel(feats, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'])
+    proj = net.project_voxel_into_image(vox, inputs[('inv_K', lvl)], inputs['extrinsics'])
+    gen = torch.Generator().manual_seed(99)
+    g_up = [torch.randn(p.shape, generator=gen) for p in proj]
+    loss = sum((p * g).sum() for p, g in zip(proj, g_up))
+    params = [net.conv_non_overlap[0].weight, net.conv_non_overlap[0].bias,
+              net.conv_overlap[0].weight, net.conv_overlap[0].bias]
+    grads = torch.autograd.grad(loss, [feats] + params)
+    out.update(w_no=_np(params[0]), b_no=_np(params[1]), w_ov=_np(params[2]), b_ov=_np(params[3]),
+               voxel_feat=_np(vox), proj=_np(torch.stack(proj, 1)), g_up=_np(torch.stack(g_up, 1)),
+               d_feats=_np(grads[0]), d_w_no=_np(grads[1]), d_b_no=_np(grads[2]), d_w_ov=_np(grads[3]),
+               d_b_ov=_np(grads[4]))
+    # per-camera coordinates / masks straight from the reference's own helpers
+    grids, valids = [], []
+    import torch.nn.functional as F
+    h, w = extras['feats_agg'].shape[-2:]
+    for c in range(6):
+        v_local = torch.matmul(inputs['extrinsics_inv'][:, c, :3, :], net.voxel_pts)
+        g = net.calculate_sample_pixel_coords(inputs[('K', lvl)][:, c], v_local, w, h)
+        m = F.interpolate(inputs['mask'][:, c], [h, w], mode='bilinear', align_corners=True)
+        grids.append(_np(g))
+        valids.append(_np(net.calculate_valid_mask(m, g, v_local)))
+    out['grids'] = np.stack(grids, 1)
+    out['valids'] = np.stack(valids, 1)
+    # pose model
+    netp = ref.VFNet(cfg, C, 16, model='pose')
+    netp.type_check(extras['feats_agg'][0, 0])
+    out['voxel_feat_pose'] = _np(netp.backproject_into_voxel(extras['feats_agg'], inputs['mask'],
+                                                             inputs[('K', lvl)], inputs['extrinsics_inv']))
+    np.savez_compressed(path, **out)
+    print('wrote', path, {k: v.shape for k, v in out.items()})
+
+
+def make_warp(ref, path):
+    cfg = warp_cfg()
+    inputs, extras = make_rig(cfg, seed=777, with_feats=False)
+    B = cfg['training']['batch_size']
+    out = {'mask': _np(inputs['mask']), 'K': _np(inputs[('K', 0)]), 'inv_K': _np(inputs[('inv_K', 0)]),
+           'extrinsics': _np(inputs['extrinsics']), 'extrinsics_inv': _np(inputs['extrinsics_inv'])}
+    for f in (0, -1, 1):
+        out['color_%d' % f] = _np(inputs[('color', f, 0)])
+    out['disp'] = _np(torch.stack(extras['disp'], 1))
+    out['depth'] = _np(torch.stack(extras['depth'], 1))
+    out['T_m1'] = _np(extras['cam_T_cam'][-1])
+    out['T_p1'] = _np(extras['cam_T_cam'][1])
+    vr = ref.ViewRendering(cfg, 'cpu')
+    pose = ref.Pose(cfg)
+    lossm = ref.MultiCamLoss(cfg, 'cpu')
+    depths = [d.clone().requires_grad_(True) for d in extras['depth']]
+    Ts = {f: extras['cam_T_cam'][f].clone().requires_grad_(True) for f in (-1, 1)}
+    outputs = {}
+    total = 0
+    noises, scal = [], []
+    for cam in range(6):
+        outputs[('cam', cam)] = {('depth', 0): depths[cam], ('disp', 0): extras['disp'][cam],
+                                 ('cam_T_cam', 0, -1): Ts[-1][:, cam], ('cam_T_cam', 0, 1): Ts[1][:, cam]}
+    for cam in range(6):
+        rel = pose.compute_relative_cam_poses(inputs, outputs, cam)
+        vr(inputs, outputs, cam, rel)
+        torch.manual_seed(1000 + cam)
+        noises.append(torch.randn(B, 2, cfg['training']['height'], cfg['training']['width']))
+        torch.manual_seed(1000 + cam)          # the loss module draws the same tensor from the global stream
+        cam_loss, ld = lossm(inputs, outputs, cam)
+        total = total + cam_loss
+        scal.append([ld['reproj_loss'], ld['spatio_loss'], ld['spatio_tempo_loss'], ld['smooth'], float(cam_loss)])
+    total = total / 6
+    grads = torch.autograd.grad(total, depths + [Ts[-1], Ts[1]])
+    out['noise'] = _np(torch.stack(noises, 1))
+    out['cam_scalars'] = np.asarray(scal, dtype=np.float64)
+    out['total'] = _np(total)
+    out['d_depth'] = _np(torch.stack(grads[:6], 1))
+    out['d_T_m1'] = _np(grads[6])
+    out['d_T_p1'] = _np(grads[7])
+    for cam in (0, 3):
+        tv = outputs[('cam', cam)]
+        for f in (-1, 1):
+            out['cam%d_color_%d' % (cam, f)] = _np(tv[('color', f, 0)])
+            out['cam%d_color_mask_%d' % (cam, f)] = _np(tv[('color_mask', f, 0)])
+        for f in (0, -1, 1):
+            out['cam%d_overlap_%d' % (cam, f)] = _np(tv[('overlap', f, 0)])
+            out['cam%d_overlap_mask_%d' % (cam, f)] = _np(tv[('overlap_mask', f, 0)])
+        out['cam%d_reproj_loss' % cam] = _np(tv[('reproj_loss', 0)])
+        out['cam%d_reproj_mask' % cam] = _np(tv[('reproj_mask', 0)])
+    np.savez_compressed(path, **out)
+    print('wrote', path, 'total loss', float(total))
+
+
+if __name__ == '__main__':
+    ref = ref_import.load()
+    make_fusion(ref, os.path.join(HERE, 'golden_fusion.npz'))
+    make_warp(ref, os.path.join(HERE, 'golden_warp.npz'))

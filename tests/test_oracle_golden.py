@@ -1,0 +1,69 @@
+"""CPU: pin oracle/vfdepth_oracle.py to the fixtures produced by running the reference itself
+(tests/golden/make_golden.py), bit for bit."""
+import torch
+
+from oracle import vfdepth_oracle as orc
+from tests import helpers as H
+
+
+def _mlp(g):
+    return dict(w_no=g['w_no'], b_no=g['b_no'], w_ov=g['w_ov'], b_ov=g['b_ov'])
+
+
+def test_fusion_forward_bit_exact():
+    g = H.load_npz('golden_fusion.npz')
+    cfg = H.fusion_cfg()
+    d = orc.backproject_into_voxel(cfg, g['feats_agg'], g['mask'], g['K'], g['extrinsics_inv'], 'depth',
+                                   _mlp(g), detail=True)
+    assert torch.equal(torch.stack(d['grids'], 1), g['grids'])
+    assert torch.equal(torch.stack(d['valids'], 1), g['valids'])
+    assert torch.equal(d['voxel_feat'], g['voxel_feat'])
+    proj = orc.project_voxel_into_image(cfg, d['voxel_feat'], g['inv_K'], g['extrinsics'])
+    assert torch.equal(torch.stack(proj, 1), g['proj'])
+    pose = orc.backproject_into_voxel(cfg, g['feats_agg'], g['mask'], g['K'], g['extrinsics_inv'], 'pose')
+    assert torch.equal(pose, g['voxel_feat_pose'])
+
+
+def test_fusion_backward_bit_exact():
+    g = H.load_npz('golden_fusion.npz')
+    cfg = H.fusion_cfg()
+    feats = g['feats_agg'].clone().requires_grad_(True)
+    mlp = {k: v.clone().requires_grad_(True) for k, v in _mlp(g).items()}
+    vox = orc.backproject_into_voxel(cfg, feats, g['mask'], g['K'], g['extrinsics_inv'], 'depth', mlp)
+    proj = orc.project_voxel_into_image(cfg, vox, g['inv_K'], g['extrinsics'])
+    loss = sum((p * g['g_up'][:, c]).sum() for c, p in enumerate(proj))
+    grads = torch.autograd.grad(loss, [feats, mlp['w_no'], mlp['b_no'], mlp['w_ov'], mlp['b_ov']])
+    for got, key in zip(grads, ['d_feats', 'd_w_no', 'd_b_no', 'd_w_ov', 'd_b_ov']):
+        assert torch.allclose(got, g[key], rtol=1e-6, atol=1e-7), key
+    assert torch.equal(grads[0], g['d_feats'])
+
+
+def test_warp_loss_bit_exact():
+    g = H.load_npz('golden_warp.npz')
+    cfg = H.warp_cfg()
+    inp = H.warp_inputs(g)
+    depths = [g['depth'][:, c].clone().requires_grad_(True) for c in range(6)]
+    Ts = {-1: g['T_m1'].clone().requires_grad_(True), 1: g['T_p1'].clone().requires_grad_(True)}
+    disps = [g['disp'][:, c] for c in range(6)]
+    noises = [g['noise'][:, c] for c in range(6)]
+    total, det = orc.warp_and_loss(cfg, inp, depths, disps, Ts, noises)
+    assert torch.equal(total.detach(), g['total'])
+    for cam in range(6):
+        got = [det[cam][k].item() for k in ('reproj_loss', 'spatio_loss', 'spatio_tempo_loss', 'smooth')]
+        assert got == g['cam_scalars'][cam, :4].tolist()
+    for cam in (0, 3):
+        v = det[cam]['view']
+        for f in (-1, 1):
+            assert torch.equal(v[('color', f)].detach(), g['cam%d_color_%d' % (cam, f)])
+            assert torch.equal(v[('color_mask', f)].detach(), g['cam%d_color_mask_%d' % (cam, f)])
+            assert torch.equal(v[('overlap_mask', f)].detach(), g['cam%d_overlap_mask_%d' % (cam, f)])
+        for f in (0, -1, 1):
+            assert torch.equal(v[('overlap', f)].detach(), g['cam%d_overlap_%d' % (cam, f)])
+        # compute_spatio_loss overwrites ('overlap_mask', 0) with ref_mask * overlap_mask (multi_cam_loss.py:28)
+        assert torch.equal(det[cam]['spatio_mask'], g['cam%d_overlap_mask_0' % cam])
+        assert torch.equal(det[cam]['reproj_mask'], g['cam%d_reproj_mask' % cam])
+        assert torch.equal(det[cam]['reproj_map'].detach(), g['cam%d_reproj_loss' % cam])
+    grads = torch.autograd.grad(total, depths + [Ts[-1], Ts[1]])
+    assert torch.equal(torch.stack(grads[:6], 1), g['d_depth'])
+    assert torch.allclose(grads[6], g['d_T_m1'], rtol=1e-6, atol=1e-9)
+    assert torch.allclose(grads[7], g['d_T_p1'], rtol=1e-6, atol=1e-9)
