@@ -1,0 +1,109 @@
+/* vfdepth_b200 -- C ABI of the B200 (sm_100a) implementation of VFDepth's volumetric-fusion and
+ * view-synthesis hot path.
+ *
+ * The reference (tronglh241/VFDepth) is pure PyTorch and has no FFI of its own; the boundary it offers is
+ * the Python method surface of VFNet / Projection / ViewRendering / the loss modules.  Each entry point
+ * below replaces the geometry core of one of those methods (file:line cited per function); the Python
+ * host layer in vfdepth_b200/ mirrors the reference signatures on top of this ABI (INTEGRATION.md shows the
+ * ctypes binding a maintainer adds to the reference).
+ *
+ * Conventions
+ *  - plain pointers + sizes, no torch types; all pointers are DEVICE pointers unless stated otherwise;
+ *  - every function returns 0 on success or a negative vfd_status; vfd_last_error(code) names it;
+ *  - nothing allocates, frees or retains device memory; scratch comes from the caller;
+ *  - everything is launched on the cudaStream_t passed in (as void*), nothing synchronises the device,
+ *    no global mutable state: entry points are re-entrant (autograd threads, DDP streams);
+ *  - fp32 everywhere (the reference's dtype); layouts are channel-last and stated per function.
+ */
+#ifndef VFDEPTH_B200_H_
+#define VFDEPTH_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VFD_VERSION 100 /* major*100 + minor */
+#define VFD_MAX_CAMS 8
+
+typedef enum vfd_status {
+    VFD_OK = 0,
+    VFD_ERR_NULL = -1,      /* a required pointer is NULL */
+    VFD_ERR_DESC = -2,      /* descriptor field out of range */
+    VFD_ERR_ALIGN = -3,     /* a pointer / leading dimension violates the stated alignment */
+    VFD_ERR_WORKSPACE = -4, /* workspace too small */
+    VFD_ERR_CUDA = -5,      /* cudaGetLastError() after launch was not cudaSuccess */
+    VFD_ERR_UNSUPPORTED = -6
+} vfd_status;
+
+int vfd_version(void);
+const char* vfd_last_error(int code);
+
+/* --------------------------------------------------------------------------------------------------
+ * Fusion geometry (network/volumetric_fusionnet.py).
+ * Voxel n = (z*Y + y)*X + x, x fastest (create_voxel_grid :67-80, flattened :24-29).
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct vfd_fusion_desc {
+    int32_t B;        /* rigs in the batch */
+    int32_t num_cams; /* 3 or 6 (preprocess_overlap :218-225); <= VFD_MAX_CAMS */
+    int32_t C;        /* feature channels (fusion_feat_in_dim); multiple of 4 */
+    int32_t h, w;     /* feature-map size = image size / 2^(fusion_level+1) (:32-34) */
+    int32_t X, Y, Z;  /* voxel_size */
+    int32_t D;        /* proj_d_bins */
+    int32_t Cv;       /* channels of the voxel volume the rays sample (voxel_pre_dim[-1]) */
+    int32_t ld_no;    /* row stride (floats) of x_no / pose rows, >= C+1, multiple of 4 */
+    int32_t ld_ov;    /* row stride (floats) of x_ov rows, >= 2*half_ov, multiple of 4 */
+    int32_t half_ov;  /* offset (floats) of the second camera group inside an x_ov row, >= C+1, multiple of 4 */
+    int32_t group[VFD_MAX_CAMS]; /* overlap group (0/1) of every camera: {0,1,1,0,0,1} for 6 cams (:222-223) */
+    float depth_div;      /* voxel_size[0]: the relative-depth channel is v.z / depth_div (:145) */
+    float vox_start[3];   /* voxel_str_p as fp32 (:256-258) */
+    float vox_length[3];  /* voxel_end_p - voxel_str_p, computed in double then cast (:257) */
+    const float* axis_x;  /* device, [X] = torch.linspace(str,end,X)  (:72) */
+    const float* axis_y;  /* device, [Y] */
+    const float* axis_z;  /* device, [Z] */
+    const float* bins;    /* device, [D] = torch.linspace(proj_d_str, proj_d_end, D)  (:39) */
+} vfd_fusion_desc;
+
+/* VFNet.backproject_into_voxel, model='depth' (:116-159) up to the inputs of the two 1x1 MLPs (:197-230):
+ *   feats      [B,cams,h,w,C]      channel-last feature maps (feats_agg of :124)
+ *   mask_small [B,cams,h,w]        self-occlusion mask already resized to h x w (:129)
+ *   K          [B,cams,4,4]        intrinsics at the feature scale (inputs['K', fusion_level+1])
+ *   Einv       [B,cams,4,4]        ego->camera (inputs['extrinsics_inv'])
+ *   x_no       [B,N,ld_no]         (sum_c feat_c) * [count==1]; cols C+1.. are written as 0
+ *   x_ov       [B,N,ld_ov]         [sum_{group 0} feat_c | pad | sum_{group 1} feat_c | pad]
+ *   count      [B,N]  uint8        number of cameras that see the voxel (:152)
+ *   grid  (optional) [B,cams,N,2]  normalised sampling coordinates (:166-181), bit-exact
+ *   valid (optional) [B,cams,N] u8 validity mask (:183-195), bit-exact
+ * feat_c = [bilinear(feats_c) ; v.z/depth_div] * valid_c  (:143-146). */
+int vfd_voxel_gather_depth_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                               const float* K, const float* Einv, float* x_no, float* x_ov, uint8_t* count,
+                               float* grid, uint8_t* valid, void* stream);
+
+/* backward of the above w.r.t. feats: d_feats [B,cams,h,w,C] is zero-filled here, then accumulated. */
+int vfd_voxel_gather_depth_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                               const float* Einv, const float* d_x_no, const float* d_x_ov, float* d_feats,
+                               void* stream);
+
+/* VFNet.backproject_into_voxel, model='pose' (:160-162):  avg [B,N,ld_no] = sum_c feat_c / (count + 1e-7) */
+int vfd_voxel_gather_pose_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                              const float* K, const float* Einv, float* avg, uint8_t* count, void* stream);
+int vfd_voxel_gather_pose_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                              const float* Einv, const float* d_avg, float* d_feats, void* stream);
+
+/* VFNet.project_voxel_into_image without reduce_dim (:245-262):
+ *   vol   [B,Z,Y,X,Cv]       channel-last voxel volume (voxel_feat of :240)
+ *   invK  [B,cams,4,4]       inputs['inv_K', fusion_level+1];   E [B,cams,4,4] camera->ego
+ *   out   [B,cams,h,w,Cv*D]  channel index = c*D + d (the .view of :262), channel-last
+ *   grid (optional) [B,cams,D,h,w,3]  normalised sampling coordinates (:251-260), bit-exact */
+int vfd_ray_sample_fwd(const vfd_fusion_desc* d, const float* vol, const float* invK, const float* E,
+                       float* out, float* grid, void* stream);
+/* d_vol [B,Z,Y,X,Cv] is zero-filled here, then accumulated. */
+int vfd_ray_sample_bwd(const vfd_fusion_desc* d, const float* invK, const float* E, const float* d_out,
+                       float* d_vol, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VFDEPTH_B200_H_ */

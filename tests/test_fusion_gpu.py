@@ -1,0 +1,190 @@
+"""GPU parity of the fusion kernels (voxel gather + ray sampling, forward and backward) through the drop-in
+``VFNet`` and the C ABI, against (1) the committed fixtures produced by running the reference itself and
+(2) the oracle on the same seeded rigs.
+
+Bars: normalised sampling coordinates, validity masks and camera counts BIT-EXACT; features, ray samples and
+gradients within 1e-4 of the tensor's scale (fp32; the north star's tolerance)."""
+import pytest
+import torch
+
+from oracle import vfdepth_oracle as orc
+from tests import helpers as H
+from vfdepth_b200 import config as vcfg
+from vfdepth_b200.rig import make_rig
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    return torch.device('cuda:0')
+
+
+def _net(cfg, C, feat_out, model, mlp=None, dev=None):
+    from vfdepth_b200.vfnet import VFNet
+    torch.manual_seed(3)
+    net = VFNet(cfg, C, feat_out, model=model)
+    if mlp is not None:
+        with torch.no_grad():
+            net.conv_non_overlap[0].weight.copy_(mlp['w_no'])
+            net.conv_non_overlap[0].bias.copy_(mlp['b_no'])
+            net.conv_overlap[0].weight.copy_(mlp['w_ov'])
+            net.conv_overlap[0].bias.copy_(mlp['b_ov'])
+    return net.to(dev)
+
+
+def _mlp(g):
+    return dict(w_no=g['w_no'], b_no=g['b_no'], w_ov=g['w_ov'], b_ov=g['b_ov'])
+
+
+def _ray_to_ref(rows, D):
+    """[B,cams,h,w,Cv*D] channel-last -> the reference's [B,cams,Cv*D,h,w]."""
+    return rows.permute(0, 1, 4, 2, 3)
+
+
+def test_golden_fusion_forward():
+    dev = _dev()
+    g = H.load_npz('golden_fusion.npz')
+    cfg = H.fusion_cfg()
+    net = _net(cfg, 8, 16, 'depth', _mlp(g), dev)
+    x_no, x_ov, count, grid, valid = net.gather_rows(g['feats_agg'].to(dev), g['mask'].to(dev), g['K'].to(dev),
+                                                     g['extrinsics_inv'].to(dev), detail=True)
+    # bit-exact: coordinates [B,6,N,1,2] and masks [B,6,1,N]
+    assert torch.equal(grid.cpu(), g['grids'].squeeze(3))
+    assert torch.equal(valid.cpu().bool(), g['valids'].squeeze(2))
+    assert torch.equal(count.cpu().long(), g['valids'].squeeze(2).sum(1))
+    vox = net.backproject_into_voxel(g['feats_agg'].to(dev), g['mask'].to(dev), g['K'].to(dev),
+                                     g['extrinsics_inv'].to(dev))
+    assert H.rel_err(vox.cpu(), g['voxel_feat']) < TOL
+    rows = net.ray_rows(vox, g['inv_K'].to(dev), g['extrinsics'].to(dev))
+    assert H.rel_err(_ray_to_ref(rows, cfg['model']['proj_d_bins']).cpu(), g['proj']) < TOL
+
+
+def test_golden_fusion_pose():
+    dev = _dev()
+    g = H.load_npz('golden_fusion.npz')
+    net = _net(H.fusion_cfg(), 8, 16, 'pose', None, dev)
+    vox = net.backproject_into_voxel(g['feats_agg'].to(dev), g['mask'].to(dev), g['K'].to(dev),
+                                     g['extrinsics_inv'].to(dev))
+    assert H.rel_err(vox.cpu(), g['voxel_feat_pose']) < TOL
+
+
+def test_golden_fusion_backward():
+    dev = _dev()
+    g = H.load_npz('golden_fusion.npz')
+    cfg = H.fusion_cfg()
+    net = _net(cfg, 8, 16, 'depth', _mlp(g), dev)
+    feats = g['feats_agg'].to(dev).requires_grad_(True)
+    vox = net.backproject_into_voxel(feats, g['mask'].to(dev), g['K'].to(dev), g['extrinsics_inv'].to(dev))
+    rows = net.ray_rows(vox, g['inv_K'].to(dev), g['extrinsics'].to(dev))
+    loss = (_ray_to_ref(rows, cfg['model']['proj_d_bins']) * g['g_up'].to(dev)).sum()
+    params = [net.conv_non_overlap[0].weight, net.conv_non_overlap[0].bias,
+              net.conv_overlap[0].weight, net.conv_overlap[0].bias]
+    grads = torch.autograd.grad(loss, [feats] + params)
+    for got, key in zip(grads, ['d_feats', 'd_w_no', 'd_b_no', 'd_w_ov', 'd_b_ov']):
+        assert H.rel_err(got.cpu(), g[key]) < TOL, key
+
+
+def test_golden_pose_backward():
+    """pose gather backward against torch autograd through the oracle on the golden inputs."""
+    dev = _dev()
+    g = H.load_npz('golden_fusion.npz')
+    cfg = H.fusion_cfg()
+    net = _net(cfg, 8, 16, 'pose', None, dev)
+    gen = torch.Generator().manual_seed(5)
+    up = torch.randn(g['voxel_feat_pose'].shape, generator=gen)
+    f_ref = g['feats_agg'].clone().requires_grad_(True)
+    ref = orc.backproject_into_voxel(cfg, f_ref, g['mask'], g['K'], g['extrinsics_inv'], 'pose')
+    d_ref, = torch.autograd.grad((ref * up).sum(), f_ref)
+    feats = g['feats_agg'].to(dev).requires_grad_(True)
+    vox = net.backproject_into_voxel(feats, g['mask'].to(dev), g['K'].to(dev), g['extrinsics_inv'].to(dev))
+    d_got, = torch.autograd.grad((vox * up.to(dev)).sum(), feats)
+    assert H.rel_err(d_got.cpu(), d_ref) < TOL
+
+
+@pytest.mark.parametrize('dataset,C,seed', [('ddad', 32, 101), ('nuscenes', 16, 102)])
+def test_oracle_full_grid(dataset, C, seed):
+    """full-size voxel grid / depth bins / feature map (channels reduced so the CPU oracle finishes in seconds):
+    coordinates and masks bit-exact, values and gradients within tolerance."""
+    dev = _dev()
+    cfg = vcfg.default_config(dataset, batch_size=1, model__fusion_feat_in_dim=C, model__voxel_pre_dim=[8])
+    inputs, extras = make_rig(cfg, seed=seed, with_images=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, C, 16, 'depth', None, dev)
+    mlp = dict(w_no=net.conv_non_overlap[0].weight.detach().cpu(), b_no=net.conv_non_overlap[0].bias.detach().cpu(),
+               w_ov=net.conv_overlap[0].weight.detach().cpu(), b_ov=net.conv_overlap[0].bias.detach().cpu())
+    f_ref = extras['feats_agg'].clone().requires_grad_(True)
+    d = orc.backproject_into_voxel(cfg, f_ref, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'], 'depth',
+                                   mlp, detail=True)
+    proj_ref, grids_ref = orc.project_voxel_into_image(cfg, d['voxel_feat'], inputs[('inv_K', lvl)],
+                                                       inputs['extrinsics'], detail=True)
+    gen = torch.Generator().manual_seed(seed)
+    up = torch.randn(torch.stack(proj_ref, 1).shape, generator=gen)
+    d_ref, = torch.autograd.grad((torch.stack(proj_ref, 1) * up).sum(), f_ref)
+
+    to = lambda t: t.to(dev)
+    feats = to(extras['feats_agg']).requires_grad_(True)
+    x_no, x_ov, count, grid, valid = net.gather_rows(feats, to(inputs['mask']), to(inputs[('K', lvl)]),
+                                                     to(inputs['extrinsics_inv']), detail=True)
+    assert torch.equal(grid.cpu(), torch.stack(d['grids'], 1).squeeze(3))
+    assert torch.equal(valid.cpu().bool(), torch.stack(d['valids'], 1).squeeze(2))
+    assert torch.equal(count.cpu().long(), d['count'].squeeze(1))
+    c1 = C + 1
+    assert H.rel_err(x_no[:, :, :c1].permute(0, 2, 1).cpu(), d['x_no']) < TOL
+    x_ov_ref = d['x_ov']
+    got_ov = torch.cat([x_ov[:, :, :c1], x_ov[:, :, net.geom.half_ov:net.geom.half_ov + c1]], 2).permute(0, 2, 1)
+    assert H.rel_err(got_ov.cpu(), x_ov_ref) < TOL
+    vox = net.backproject_into_voxel(feats, to(inputs['mask']), to(inputs[('K', lvl)]), to(inputs['extrinsics_inv']))
+    assert H.rel_err(vox.cpu(), d['voxel_feat']) < TOL
+    rows, rgrid = net.ray_rows(vox, to(inputs[('inv_K', lvl)]), to(inputs['extrinsics']), want_grid=True)
+    assert torch.equal(rgrid.cpu(), torch.stack(grids_ref, 1))
+    got = _ray_to_ref(rows, cfg['model']['proj_d_bins'])
+    assert H.rel_err(got.cpu(), torch.stack(proj_ref, 1)) < TOL
+    d_got, = torch.autograd.grad((got * to(up)).sum(), feats)
+    assert H.rel_err(d_got.cpu(), d_ref) < TOL
+
+
+def test_full_size_properties():
+    """BASELINE size (DDAD, C=256, Cv=64, B=2): size-independent properties instead of the slow CPU oracle --
+    linearity of both kernels in their feature input, zero rows exactly where count is 0 / >=3, and
+    <ray(v), u> == <v, ray^T(u)> (the backward is the exact adjoint of the forward)."""
+    dev = _dev()
+    cfg = vcfg.default_config('ddad', batch_size=2)
+    inputs, extras = make_rig(cfg, seed=7, with_images=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, 256, 128, 'depth', None, dev)
+    to = lambda t: t.to(dev)
+    args = (to(inputs['mask']), to(inputs[('K', lvl)]), to(inputs['extrinsics_inv']))
+    f1 = to(extras['feats_agg'])
+    f2 = torch.randn_like(f1)
+    a_no, a_ov, cnt = net.gather_rows(f1, *args)[:3]
+    b_no, b_ov, _ = net.gather_rows(f2, *args)[:3]
+    c_no, c_ov, _ = net.gather_rows(f1 + 2 * f2, *args)[:3]
+    C = 256
+    assert H.rel_err(c_no[..., :C], a_no[..., :C] + 2 * b_no[..., :C]) < TOL
+    assert H.rel_err(c_ov[..., :C], a_ov[..., :C] + 2 * b_ov[..., :C]) < TOL
+    assert float(a_no[cnt != 1].abs().max()) == 0.0
+    assert float(a_ov[cnt == 0].abs().max()) == 0.0
+    assert int((cnt == 1).sum()) > 0 and int((cnt == 2).sum()) > 0
+    # adjointness of the ray kernel
+    v = torch.randn(2, 64, net.n_voxels, device=dev).requires_grad_(True)
+    rows = net.ray_rows(v, to(inputs[('inv_K', lvl)]), to(inputs['extrinsics']))
+    u = torch.randn_like(rows)
+    lhs = (rows * u).sum()
+    gv, = torch.autograd.grad(lhs, v)
+    rhs = (gv * v).sum()
+    assert abs(float(lhs) - float(rhs)) / abs(float(lhs)) < 1e-3
+    # adjointness of the gather kernel
+    f = f1.clone().requires_grad_(True)
+    x_no, x_ov, _ = net.gather_rows(f, *args)[:3]
+    u1, u2 = torch.randn_like(x_no), torch.randn_like(x_ov)
+    ho = net.geom.half_ov
+    u1[..., C:] = 0          # the relative-depth column and the padding do not depend on the features
+    u2[..., C:ho] = 0
+    u2[..., ho + C:] = 0
+    lhs = (x_no * u1).sum() + (x_ov * u2).sum()
+    gf, = torch.autograd.grad(lhs, f)
+    rhs = (gf * f1).sum()
+    assert abs(float(lhs) - float(rhs)) / abs(float(lhs)) < 1e-3

@@ -1,0 +1,81 @@
+"""ctypes binding of libvfdepth_b200.so (the C ABI declared in include/vfdepth_b200.h).
+
+There is no fallback: if the library is missing it is built with nvcc, and if that fails, or a call returns a
+non-zero status, a RuntimeError is raised.  Nothing in this package computes the hot path any other way.
+"""
+import ctypes
+import os
+import threading
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, 'lib', 'libvfdepth_b200.so')
+VFD_MAX_CAMS = 8
+
+c_float_p = ctypes.c_void_p
+
+
+class FusionDesc(ctypes.Structure):
+    """struct vfd_fusion_desc"""
+    _fields_ = [
+        ('B', ctypes.c_int32), ('num_cams', ctypes.c_int32), ('C', ctypes.c_int32),
+        ('h', ctypes.c_int32), ('w', ctypes.c_int32),
+        ('X', ctypes.c_int32), ('Y', ctypes.c_int32), ('Z', ctypes.c_int32),
+        ('D', ctypes.c_int32), ('Cv', ctypes.c_int32),
+        ('ld_no', ctypes.c_int32), ('ld_ov', ctypes.c_int32), ('half_ov', ctypes.c_int32),
+        ('group', ctypes.c_int32 * VFD_MAX_CAMS),
+        ('depth_div', ctypes.c_float),
+        ('vox_start', ctypes.c_float * 3), ('vox_length', ctypes.c_float * 3),
+        ('axis_x', ctypes.c_void_p), ('axis_y', ctypes.c_void_p), ('axis_z', ctypes.c_void_p),
+        ('bins', ctypes.c_void_p),
+    ]
+
+
+class WarpDesc(ctypes.Structure):
+    """struct vfd_warp_desc"""
+    _fields_ = [
+        ('B', ctypes.c_int32), ('num_cams', ctypes.c_int32), ('H', ctypes.c_int32), ('W', ctypes.c_int32),
+        ('n_frames', ctypes.c_int32), ('n_nbr', ctypes.c_int32),
+        ('spatio', ctypes.c_int32), ('spatio_temporal', ctypes.c_int32), ('intensity_align', ctypes.c_int32),
+        ('nbr', (ctypes.c_int32 * 2) * VFD_MAX_CAMS),
+    ]
+
+
+_lock = threading.Lock()
+_lib = None
+launches = 0   # number of kernel-launching ABI calls made by this process (bench.py reports it)
+
+
+def load():
+    """-> ctypes.CDLL; builds the library first if it is not there."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.isfile(LIB_PATH):
+            from . import build as _build
+            _build.build()
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.vfd_version.restype = ctypes.c_int
+        lib.vfd_last_error.restype = ctypes.c_char_p
+        lib.vfd_last_error.argtypes = [ctypes.c_int]
+        _lib = lib
+    return _lib
+
+
+def check(code, what):
+    if code != 0:
+        raise RuntimeError('%s failed: %s (status %d)' % (what, load().vfd_last_error(code).decode(), code))
+
+
+def ptr(t):
+    """device pointer of a torch tensor (None -> NULL)."""
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def call(name, *args):
+    global launches
+    fn = getattr(load(), name)
+    launches += 1
+    check(fn(*args), name)

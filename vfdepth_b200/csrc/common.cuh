@@ -1,0 +1,73 @@
+// Shared device helpers for the vfdepth_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vfdepth_b200.h"
+#include "vfd_coords.h"
+
+#define VFD_WARP 32
+
+#define VFD_CHECK_LAUNCH()                                   \
+    do {                                                     \
+        if (cudaGetLastError() != cudaSuccess) return VFD_ERR_CUDA; \
+    } while (0)
+
+namespace vfd {
+
+__device__ __forceinline__ float4 ldg_f4(const float* p) {
+    return __ldg(reinterpret_cast<const float4*>(p));
+}
+
+// streaming (write-once) 128-bit store: do not keep the line in L1
+__device__ __forceinline__ void st_stream_f4(float* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+// streaming read-once 128-bit load
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+// 128-bit vector reduction into global memory (sm_90+): one L2 atomic transaction for 4 channels
+__device__ __forceinline__ void red_add_f4(float* p, float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ void red_add_f2(float* p, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+
+__device__ __forceinline__ void red_add_f1(float* p, float a) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
+
+__device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+
+__device__ __forceinline__ void f4_fma(float4& acc, float w, const float4& v) {
+    acc.x = fmaf(w, v.x, acc.x);
+    acc.y = fmaf(w, v.y, acc.y);
+    acc.z = fmaf(w, v.z, acc.z);
+    acc.w = fmaf(w, v.w, acc.w);
+}
+
+__device__ __forceinline__ void f4_add(float4& acc, const float4& v) {
+    acc.x += v.x;
+    acc.y += v.y;
+    acc.z += v.z;
+    acc.w += v.w;
+}
+
+__device__ __forceinline__ float4 f4_scale(float s, const float4& v) {
+    return make_float4(s * v.x, s * v.y, s * v.z, s * v.w);
+}
+
+}  // namespace vfd

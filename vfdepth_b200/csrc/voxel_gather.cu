@@ -1,0 +1,377 @@
+// Voxel gather: VFNet.backproject_into_voxel (network/volumetric_fusionnet.py:116-164) forward and backward.
+//
+// Mapping.  One warp owns 32 consecutive voxels (x fastest) of one rig.
+//   phase 1  lane <-> voxel: project the voxel into every camera with the exact fp32 operation order of
+//            the reference (vfd_coords.h), decide validity, keep (texel index, 2 weights, relative depth) per
+//            camera in shared memory and the camera bit-mask in a register.
+//   phase 2  lane <-> 4 channels: for each of the 32 voxels the warp reads the 4 bilinear corners of every
+//            VALID camera as contiguous channel-last rows (C floats = 1 KB at C=256, 512 B per LDG.128 warp
+//            instruction), accumulates the two overlap-group sums in registers and streams the finished rows
+//            out with 128-bit stores.  The per-camera [B,257,N] tensors of the reference are never formed.
+// The feature maps of one rig (23.6 MB at DDAD size) stay L2-resident while its 200 000 voxels are processed
+// (blockIdx.y = rig), so HBM traffic is the 617 MB/rig (depth) or 206 MB/rig (pose) of output rows.
+#include "common.cuh"
+
+namespace vfd {
+
+constexpr int kGatherWarps = 8;
+
+struct GatherArgs {
+    vfd_fusion_desc d;
+    const float* feats;
+    const float* mask_small;
+    const float* K;
+    const float* Einv;
+    float* x_no;      // depth: x_no, pose: avg
+    float* x_ov;
+    uint8_t* count;
+    float* grid;
+    uint8_t* valid;
+    // backward
+    const float* d_x_no;
+    const float* d_x_ov;
+    float* d_feats;
+};
+
+struct CamSlot {   // one (voxel, camera) projection, kept in shared memory between the two phases
+    int idx;       // iy0 * w + ix0
+    float wx, wy;  // fractional parts
+    float zrel;    // v.z / depth_div
+};
+
+// phase 1: returns the camera bit-mask of this lane's voxel and fills slot[c][lane]
+__device__ __forceinline__ unsigned project_voxel(const GatherArgs& a, const float* s_mat, int b, long n, int lane,
+                                                  bool in_range, CamSlot (*slot)[VFD_WARP]) {
+    const vfd_fusion_desc& d = a.d;
+    const int N = d.X * d.Y * d.Z;
+    unsigned vmask = 0;
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (in_range) {
+        int xi = (int)(n % d.X), yi = (int)((n / d.X) % d.Y), zi = (int)(n / ((long)d.X * d.Y));
+        x = __ldg(d.axis_x + xi);
+        y = __ldg(d.axis_y + yi);
+        z = __ldg(d.axis_z + zi);
+    }
+    for (int c = 0; c < d.num_cams; ++c) {
+        const float* Einv = s_mat + c * 32;
+        const float* K = Einv + 16;
+        float v[3], g[2];
+        vfd_voxel_to_pixel(Einv, K, x, y, z, d.w, d.h, v, g);
+        bool inb = vfd_in_bounds2(g[0], g[1]);
+        float ix = vfd_unnormalize(g[0], d.w), iy = vfd_unnormalize(g[1], d.h);
+        bool ok = false;
+        CamSlot s = {0, 0.f, 0.f, 0.f};
+        if (in_range && inb && v[2] > 0.f) {
+            // nearest-neighbour self-occlusion lookup: ATen uses nearbyint (half-to-even) -> rintf
+            float fx = rintf(ix), fy = rintf(iy);
+            if (fx >= 0.f && fx <= (float)(d.w - 1) && fy >= 0.f && fy <= (float)(d.h - 1)) {
+                float m = __ldg(a.mask_small + ((size_t)(b * d.num_cams + c) * d.h + (int)fy) * d.w + (int)fx);
+                ok = m > 0.5f;
+            }
+            float x0 = floorf(ix), y0 = floorf(iy);
+            s.idx = (int)y0 * d.w + (int)x0;
+            s.wx = ix - x0;
+            s.wy = iy - y0;
+            s.zrel = VFD_DIV(v[2], d.depth_div);
+        }
+        if (in_range) {
+            size_t o = (size_t)(b * d.num_cams + c) * N + n;
+            if (a.grid) reinterpret_cast<float2*>(a.grid)[o] = make_float2(g[0], g[1]);
+            if (a.valid) a.valid[o] = ok ? 1 : 0;
+        }
+        slot[c][lane] = s;
+        vmask |= (ok ? 1u : 0u) << c;
+    }
+    return vmask;
+}
+
+__device__ __forceinline__ void load_mats(const GatherArgs& a, int b, float* s_mat) {
+    // per camera 32 floats: Einv 4x4 (16) then K 4x4 (16)
+    const int n = a.d.num_cams * 32;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        int c = i >> 5, r = i & 31;
+        const float* src = (r < 16 ? a.Einv : a.K) + (size_t)(b * a.d.num_cams + c) * 16 + (r & 15);
+        s_mat[i] = __ldg(src);
+    }
+}
+
+// bilinear corner walk shared by forward (gather) and backward (scatter)
+struct Corners {
+    int off[4];
+    float wgt[4];
+};
+__device__ __forceinline__ Corners make_corners(const CamSlot& s, int w, int h, int C) {
+    Corners q;
+    int x0 = s.idx % w, y0 = s.idx / w;
+    bool x1 = (x0 + 1) < w, y1 = (y0 + 1) < h;
+    float ex = 1.f - s.wx, ey = 1.f - s.wy;
+    q.off[0] = s.idx * C;            q.wgt[0] = ex * ey;
+    q.off[1] = (s.idx + 1) * C;      q.wgt[1] = x1 ? s.wx * ey : 0.f;
+    q.off[2] = (s.idx + w) * C;      q.wgt[2] = y1 ? ex * s.wy : 0.f;
+    q.off[3] = (s.idx + w + 1) * C;  q.wgt[3] = (x1 && y1) ? s.wx * s.wy : 0.f;
+    if (!x1) { q.off[1] = q.off[0]; q.off[3] = q.off[0]; }
+    if (!y1) { q.off[2] = q.off[0]; q.off[3] = q.off[0]; }
+    return q;
+}
+
+template <int MODE /*0 depth, 1 pose*/, int ITERS>
+__global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_fwd_kernel(const GatherArgs a) {
+    const vfd_fusion_desc& d = a.d;
+    __shared__ float s_mat[VFD_MAX_CAMS * 32];
+    __shared__ CamSlot s_slot[kGatherWarps][VFD_MAX_CAMS][VFD_WARP];
+    const int b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int N = d.X * d.Y * d.Z;
+    load_mats(a, b, s_mat);
+    __syncthreads();
+    const long n0 = ((long)blockIdx.x * kGatherWarps + warp) * VFD_WARP;
+    if (n0 >= N) return;
+    const long n = n0 + lane;
+    unsigned vmask = project_voxel(a, s_mat, b, n, lane, n < N, s_slot[warp]);
+    if (n < N && a.count) a.count[(size_t)b * N + n] = (uint8_t)__popc(vmask);
+    __syncwarp();
+
+    const int C = d.C, hw = d.h * d.w;
+    const int jmax = min(VFD_WARP, (int)(N - n0));
+    for (int j = 0; j < jmax; ++j) {
+        unsigned m = __shfl_sync(0xffffffffu, vmask, j);
+        const int cnt = __popc(m);
+        float4 acc0[ITERS], acc1[ITERS];
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it) { acc0[it] = f4_zero(); acc1[it] = f4_zero(); }
+        float z0 = 0.f, z1 = 0.f;
+        while (m) {
+            const int c = __ffs(m) - 1;
+            m &= m - 1;
+            const CamSlot s = s_slot[warp][c][j];
+            const Corners q = make_corners(s, d.w, d.h, C);
+            const float* base = a.feats + (size_t)(b * d.num_cams + c) * hw * C;
+            const bool g1 = (MODE == 0) && d.group[c];
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int k = it * 128 + lane * 4;
+                if (k < C) {
+                    float4 v0 = ldg_f4(base + q.off[0] + k), v1 = ldg_f4(base + q.off[1] + k);
+                    float4 v2 = ldg_f4(base + q.off[2] + k), v3 = ldg_f4(base + q.off[3] + k);
+                    float4 r = f4_scale(q.wgt[0], v0);
+                    f4_fma(r, q.wgt[1], v1);
+                    f4_fma(r, q.wgt[2], v2);
+                    f4_fma(r, q.wgt[3], v3);
+                    if (g1) f4_add(acc1[it], r); else f4_add(acc0[it], r);
+                }
+            }
+            if (g1) z1 += s.zrel; else z0 += s.zrel;
+        }
+        const size_t row = (size_t)b * N + n0 + j;
+        if (MODE == 0) {
+            float* rno = a.x_no + row * d.ld_no;
+            float* rov = a.x_ov + row * d.ld_ov;
+            const float keep = (cnt == 1) ? 1.f : 0.f;
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int k = it * 128 + lane * 4;
+                if (k < C) {
+                    float4 s = acc0[it];
+                    f4_add(s, acc1[it]);
+                    st_stream_f4(rno + k, f4_scale(keep, s));
+                    st_stream_f4(rov + k, acc0[it]);
+                    st_stream_f4(rov + d.half_ov + k, acc1[it]);
+                }
+            }
+            // tail columns: relative depth at column C, then zero padding
+            for (int k = C + lane * 4; k < d.ld_no; k += 128)
+                st_stream_f4(rno + k, make_float4(k == C ? keep * (z0 + z1) : 0.f, 0.f, 0.f, 0.f));
+            for (int k = C + lane * 4; k < d.half_ov; k += 128)
+                st_stream_f4(rov + k, make_float4(k == C ? z0 : 0.f, 0.f, 0.f, 0.f));
+            for (int k = d.half_ov + C + lane * 4; k < d.ld_ov; k += 128)
+                st_stream_f4(rov + k, make_float4(k == d.half_ov + C ? z1 : 0.f, 0.f, 0.f, 0.f));
+        } else {
+            float* ravg = a.x_no + row * d.ld_no;
+            const float den = VFD_ADD((float)cnt, 1e-7f);  // count + 1e-7 (:162)
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int k = it * 128 + lane * 4;
+                if (k < C) {
+                    float4 s = acc0[it];
+                    st_stream_f4(ravg + k, make_float4(VFD_DIV(s.x, den), VFD_DIV(s.y, den), VFD_DIV(s.z, den),
+                                                       VFD_DIV(s.w, den)));
+                }
+            }
+            for (int k = C + lane * 4; k < d.ld_no; k += 128)
+                st_stream_f4(ravg + k, make_float4(k == C ? VFD_DIV(z0, den) : 0.f, 0.f, 0.f, 0.f));
+        }
+    }
+}
+
+// Backward: d_feats[b,c,texel,:] += w_corner * g(voxel, c) for the 4 corners, with 128-bit vector reductions
+// (red.global.add.v4.f32).  g = [count==1] * d_x_no + d_x_ov[group(c)]  (depth) or d_avg / (count+1e-7) (pose).
+template <int MODE, int ITERS>
+__global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_bwd_kernel(const GatherArgs a) {
+    const vfd_fusion_desc& d = a.d;
+    __shared__ float s_mat[VFD_MAX_CAMS * 32];
+    __shared__ CamSlot s_slot[kGatherWarps][VFD_MAX_CAMS][VFD_WARP];
+    const int b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int N = d.X * d.Y * d.Z;
+    load_mats(a, b, s_mat);
+    __syncthreads();
+    const long n0 = ((long)blockIdx.x * kGatherWarps + warp) * VFD_WARP;
+    if (n0 >= N) return;
+    const long n = n0 + lane;
+    unsigned vmask = project_voxel(a, s_mat, b, n, lane, n < N, s_slot[warp]);
+    __syncwarp();
+
+    const int C = d.C, hw = d.h * d.w;
+    const int jmax = min(VFD_WARP, (int)(N - n0));
+    for (int j = 0; j < jmax; ++j) {
+        unsigned m = __shfl_sync(0xffffffffu, vmask, j);
+        if (!m) continue;
+        const int cnt = __popc(m);
+        const size_t row = (size_t)b * N + n0 + j;
+        float4 gno[ITERS];
+        if (MODE == 0) {
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int k = it * 128 + lane * 4;
+                gno[it] = (cnt == 1 && k < C) ? ld_stream_f4(a.d_x_no + row * d.ld_no + k) : f4_zero();
+            }
+        } else {
+            const float den = VFD_ADD((float)cnt, 1e-7f);
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int k = it * 128 + lane * 4;
+                float4 g = (k < C) ? ld_stream_f4(a.d_x_no + row * d.ld_no + k) : f4_zero();
+                gno[it] = make_float4(g.x / den, g.y / den, g.z / den, g.w / den);
+            }
+        }
+        while (m) {
+            const int c = __ffs(m) - 1;
+            m &= m - 1;
+            const CamSlot s = s_slot[warp][c][j];
+            const Corners q = make_corners(s, d.w, d.h, C);
+            float* base = a.d_feats + (size_t)(b * d.num_cams + c) * hw * C;
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int k = it * 128 + lane * 4;
+                if (k < C) {
+                    float4 g = gno[it];
+                    if (MODE == 0) {
+                        float4 o = ld_stream_f4(a.d_x_ov + row * d.ld_ov + (d.group[c] ? d.half_ov : 0) + k);
+                        f4_add(g, o);
+                    }
+                    if (g.x == 0.f && g.y == 0.f && g.z == 0.f && g.w == 0.f) continue;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t)
+                        if (q.wgt[t] != 0.f) red_add_f4(base + q.off[t] + k, f4_scale(q.wgt[t], g));
+                }
+            }
+        }
+    }
+}
+
+static int check_desc(const vfd_fusion_desc* d) {
+    if (!d) return VFD_ERR_NULL;
+    if (d->B < 1 || d->num_cams < 1 || d->num_cams > VFD_MAX_CAMS || d->C < 4 || d->h < 2 || d->w < 2 ||
+        d->X < 1 || d->Y < 1 || d->Z < 1)
+        return VFD_ERR_DESC;
+    if (d->C % 4 || d->C > 512) return VFD_ERR_UNSUPPORTED;
+    if (!d->axis_x || !d->axis_y || !d->axis_z) return VFD_ERR_NULL;
+    if ((long)d->h * d->w * d->C >= (1L << 31)) return VFD_ERR_DESC;
+    return VFD_OK;
+}
+
+static int check_rows(const vfd_fusion_desc* d, bool depth) {
+    if (d->ld_no < d->C + 1 || d->ld_no % 4) return VFD_ERR_ALIGN;
+    if (depth && (d->half_ov < d->C + 1 || d->half_ov % 4 || d->ld_ov < d->half_ov + d->C + 1 || d->ld_ov % 4))
+        return VFD_ERR_ALIGN;
+    return VFD_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int MODE>
+static int launch(const GatherArgs& a, bool bwd, cudaStream_t st) {
+    const vfd_fusion_desc& d = a.d;
+    const long N = (long)d.X * d.Y * d.Z;
+    dim3 grid((unsigned)((N + kGatherWarps * VFD_WARP - 1) / (kGatherWarps * VFD_WARP)), d.B);
+    dim3 block(kGatherWarps * VFD_WARP);
+    const int iters = (d.C + 127) / 128;
+#define VFD_GATHER_CASE(I)                                                            \
+    case I:                                                                           \
+        if (bwd) voxel_gather_bwd_kernel<MODE, I><<<grid, block, 0, st>>>(a);         \
+        else voxel_gather_fwd_kernel<MODE, I><<<grid, block, 0, st>>>(a);             \
+        break;
+    switch (iters) {
+        VFD_GATHER_CASE(1)
+        VFD_GATHER_CASE(2)
+        VFD_GATHER_CASE(3)
+        VFD_GATHER_CASE(4)
+        default: return VFD_ERR_UNSUPPORTED;
+    }
+#undef VFD_GATHER_CASE
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+}  // namespace vfd
+
+using namespace vfd;
+
+extern "C" int vfd_voxel_gather_depth_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                                          const float* K, const float* Einv, float* x_no, float* x_ov,
+                                          uint8_t* count, float* grid, uint8_t* valid, void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, true))) return rc;
+    if (!feats || !mask_small || !K || !Einv || !x_no || !x_ov) return VFD_ERR_NULL;
+    if (!aligned16(feats) || !aligned16(x_no) || !aligned16(x_ov) || (grid && !aligned16(grid))) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv;
+    a.x_no = x_no; a.x_ov = x_ov; a.count = count; a.grid = grid; a.valid = valid;
+    return launch<0>(a, false, (cudaStream_t)stream);
+}
+
+extern "C" int vfd_voxel_gather_pose_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                                         const float* K, const float* Einv, float* avg, uint8_t* count,
+                                         void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, false))) return rc;
+    if (!feats || !mask_small || !K || !Einv || !avg) return VFD_ERR_NULL;
+    if (!aligned16(feats) || !aligned16(avg)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.x_no = avg; a.count = count;
+    return launch<1>(a, false, (cudaStream_t)stream);
+}
+
+static int bwd_common(const vfd_fusion_desc* d, GatherArgs& a, float* d_feats, cudaStream_t st) {
+    const size_t bytes = (size_t)d->B * d->num_cams * d->h * d->w * d->C * sizeof(float);
+    if (cudaMemsetAsync(d_feats, 0, bytes, st) != cudaSuccess) return VFD_ERR_CUDA;
+    a.d_feats = d_feats;
+    return VFD_OK;
+}
+
+extern "C" int vfd_voxel_gather_depth_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                                          const float* Einv, const float* d_x_no, const float* d_x_ov,
+                                          float* d_feats, void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, true))) return rc;
+    if (!mask_small || !K || !Einv || !d_x_no || !d_x_ov || !d_feats) return VFD_ERR_NULL;
+    if (!aligned16(d_feats) || !aligned16(d_x_no) || !aligned16(d_x_ov)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.d_x_no = d_x_no; a.d_x_ov = d_x_ov;
+    if ((rc = bwd_common(d, a, d_feats, (cudaStream_t)stream))) return rc;
+    return launch<0>(a, true, (cudaStream_t)stream);
+}
+
+extern "C" int vfd_voxel_gather_pose_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                                         const float* Einv, const float* d_avg, float* d_feats, void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, false))) return rc;
+    if (!mask_small || !K || !Einv || !d_avg || !d_feats) return VFD_ERR_NULL;
+    if (!aligned16(d_feats) || !aligned16(d_avg)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.d_x_no = d_avg;
+    if ((rc = bwd_common(d, a, d_feats, (cudaStream_t)stream))) return rc;
+    return launch<1>(a, true, (cudaStream_t)stream);
+}

@@ -1,0 +1,173 @@
+"""VFNet -- drop-in for /root/reference/network/volumetric_fusionnet.py:11-343 on top of the CUDA kernels.
+
+Same constructor, same ``forward(inputs, feats_agg)``, same sub-methods and the same state-dict keys
+(``conv_overlap.0.*``, ``conv_non_overlap.0.*``, ``reduce_dim.0.*``, ``reduce_dim.3.*``) so published
+checkpoints load.  What changes is underneath:
+
+* the per-camera loops of ``backproject_into_voxel`` (:124-149) and ``project_voxel_into_image`` (:243-262)
+  are one kernel launch each (vfdepth_b200/csrc/voxel_gather.cu, ray_sample.cu);
+* everything is channel-last: the gather writes the two MLP inputs as rows ``[B,N,257(+pad)]`` so the 1x1
+  ``Conv1d`` of :197-230 is a plain GEMM (``F.linear`` with the Conv1d's own weight) whose output IS the
+  channel-last voxel volume the ray kernel reads, and the ray kernel emits ``[B*6,h,w,Cv*D]`` which is handed
+  to ``reduce_dim`` as a channels_last NCHW tensor with channel = c*D + d (:262).
+
+The learnable parts (the two MLPs and ``reduce_dim``) stay in PyTorch / cuBLAS / cuDNN.
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import config as vcfg
+from . import ops
+from .rig import axis_angle_to_matrix
+
+
+def _act():
+    return nn.LeakyReLU(0.1, inplace=True)
+
+
+def _conv1x1_block(cin, cout):
+    # the reference's conv1d() factory (network/blocks.py:64-83) with kernel_size=1: (conv, identity, act)
+    return nn.Sequential(nn.Conv1d(cin, cout, kernel_size=1, padding=0, bias=True, padding_mode='reflect'),
+                         nn.Identity(), _act())
+
+
+def _conv3x3_layers(cin, cout, stride):
+    # the reference's conv2d() factory (network/blocks.py:41-61): (conv, identity, act)
+    return [nn.Conv2d(cin, cout, kernel_size=3, stride=stride, padding=1, bias=True, padding_mode='reflect'),
+            nn.Identity(), _act()]
+
+
+class VFNet(nn.Module):
+    """Surround-view volumetric fusion (reference: VFNet, volumetric_fusionnet.py:11)."""
+
+    def __init__(self, cfg, feat_in_dim, feat_out_dim, model='depth'):
+        super().__init__()
+        vcfg.flatten_into(self, cfg)          # the reference's read_config (:62-65)
+        self.eps = 1e-8
+        self.model = model
+        self.voxel_end_p = [self.voxel_str_p[i] + self.voxel_unit_size[i] * (self.voxel_size[i] - 1)
+                            for i in range(3)]
+        self.x_dim, self.y_dim, self.z_dim = self.voxel_size
+        self.n_voxels = self.x_dim * self.y_dim * self.z_dim
+        self.img_h = self.height // (2 ** (self.fusion_level + 1))
+        self.img_w = self.width // (2 ** (self.fusion_level + 1))
+        self.num_pix = self.img_h * self.img_w
+        self.feat_in_dim = feat_in_dim
+
+        if model == 'depth':
+            self.v_dim_o = [(feat_in_dim + 1) * 2] + list(self.voxel_pre_dim)
+            self.v_dim_no = [feat_in_dim + 1] + list(self.voxel_pre_dim)
+            self.conv_overlap = _conv1x1_block(self.v_dim_o[0], self.v_dim_o[1])
+            self.conv_non_overlap = _conv1x1_block(self.v_dim_no[0], self.v_dim_no[1])
+            encoder_dims = self.proj_d_bins * self.v_dim_o[-1]
+            stride = 1
+            cv = self.v_dim_o[-1]
+        else:
+            encoder_dims = (feat_in_dim + 1) * self.z_dim
+            stride = 2
+            cv = feat_in_dim + 1
+        self.reduce_dim = nn.Sequential(*_conv3x3_layers(encoder_dims, 256, stride),
+                                        *_conv3x3_layers(256, feat_out_dim, stride))
+        self.geom = ops.FusionGeometry(self.batch_size, self.num_cams, feat_in_dim, self.img_h, self.img_w,
+                                       self.voxel_size, self.voxel_str_p, self.voxel_unit_size, self.proj_d_bins,
+                                       self.proj_d_str, self.proj_d_end, cv)
+        self.last_count = None      # [B,N] uint8 camera count of the last gather (:152), for inspection
+
+    # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def _channel_last(feats_agg):
+        """[B,cams,C,h,w] -> contiguous [B,cams,h,w,C]; free when the producer already emits channels_last."""
+        return feats_agg.permute(0, 1, 3, 4, 2).contiguous()
+
+    def _mask_small(self, input_mask):
+        # the resize of :129 stays in torch so the thresholded values are the reference's
+        B, ncam = input_mask.shape[:2]
+        m = F.interpolate(input_mask.reshape(B * ncam, 1, *input_mask.shape[-2:]).float(),
+                          [self.img_h, self.img_w], mode='bilinear', align_corners=True)
+        return m.view(B, ncam, self.img_h, self.img_w).contiguous()
+
+    def _mlp(self, rows, block, out_mask):
+        """1x1 Conv1d + LeakyReLU(0.1) of :197-230 on channel-last rows [B,N,ld] (zero-padded columns)."""
+        conv = block[0]
+        wgt = conv.weight.squeeze(-1)
+        return F.leaky_relu(F.linear(rows, wgt, conv.bias), 0.1) * out_mask
+
+    def gather_rows(self, feats_agg, input_mask, intrinsics, extrinsics_inv, detail=False):
+        """The geometry core of ``backproject_into_voxel``: the kernel's raw channel-last outputs."""
+        feats_cl = self._channel_last(feats_agg)
+        mask_small = self._mask_small(input_mask)
+        K = intrinsics.float().contiguous()
+        Einv = extrinsics_inv.float().contiguous()
+        if self.model == 'depth':
+            return ops.voxel_gather_depth(feats_cl, mask_small, K, Einv, self.geom, detail)
+        return ops.voxel_gather_pose(feats_cl, mask_small, K, Einv, self.geom)
+
+    def backproject_into_voxel(self, feats_agg, input_mask, intrinsics, extrinsics_inv):
+        """-> voxel_feat [B,C',N] (a permuted view of channel-last rows [B,N,C']).  Reference :116-164."""
+        g = self.geom
+        if self.model == 'depth':
+            x_no, x_ov, count = self.gather_rows(feats_agg, input_mask, intrinsics, extrinsics_inv)[:3]
+            self.last_count = count
+            c1 = self.feat_in_dim + 1
+            w_no = F.pad(self.conv_non_overlap[0].weight.squeeze(-1), (0, g.ld_no - c1))
+            w_ov = self.conv_overlap[0].weight.squeeze(-1)
+            w_ov = torch.cat([F.pad(w_ov[:, :c1], (0, g.half_ov - c1)),
+                              F.pad(w_ov[:, c1:], (0, g.ld_ov - g.half_ov - c1))], 1)
+            cnt = count.unsqueeze(-1)
+            y_no = F.leaky_relu(F.linear(x_no, w_no, self.conv_non_overlap[0].bias), 0.1) * (cnt == 1).float()
+            y_ov = F.leaky_relu(F.linear(x_ov, w_ov, self.conv_overlap[0].bias), 0.1) * (cnt == 2).float()
+            rows = y_no + y_ov                                   # [B,N,Cv] == channel-last voxel volume
+            return rows.permute(0, 2, 1)
+        avg, count = self.gather_rows(feats_agg, input_mask, intrinsics, extrinsics_inv)
+        self.last_count = count
+        return avg[:, :, :self.feat_in_dim + 1].permute(0, 2, 1)
+
+    def ray_rows(self, voxel_feat, inv_K, extrinsics, want_grid=False):
+        """The geometry core of ``project_voxel_into_image``: [B,cams,h,w,Cv*D] channel-last ray samples."""
+        B, cv, _ = voxel_feat.shape
+        vol = voxel_feat.permute(0, 2, 1).contiguous().view(B, self.z_dim, self.y_dim, self.x_dim, cv)
+        return ops.ray_sample(vol, inv_K.float().contiguous(), extrinsics.float().contiguous(), self.geom, want_grid)
+
+    def project_voxel_into_image(self, voxel_feat, inv_K, extrinsics):
+        """-> list over cameras of [B,feat_out,h,w].  Reference :232-267."""
+        rows = self.ray_rows(voxel_feat, inv_K, extrinsics)
+        B, ncam = rows.shape[:2]
+        x = rows.view(B * ncam, self.img_h, self.img_w, -1).permute(0, 3, 1, 2)   # channels_last NCHW
+        y = self.reduce_dim(x)
+        y = y.view(B, ncam, *y.shape[1:])
+        return [y[:, c] for c in range(ncam)]
+
+    def augment_extrinsics(self, ext):
+        """random rotation of every camera's extrinsics (:269-287), aug_depth only."""
+        with torch.no_grad():
+            b, cam = ext.shape[:2]
+            angle = torch.rand(b, cam, 3)
+            for i in range(3):
+                angle[:, :, i] = (angle[:, :, i] - 0.5) * self.aug_angle[i]
+            tform = torch.eye(4).repeat(b, cam, 1, 1)
+            tform[:, :, :3, :3] = axis_angle_to_matrix(angle)
+            return tform.to(device=ext.device, dtype=ext.dtype) @ ext
+
+    def forward(self, inputs, feats_agg):
+        """Reference :289-343."""
+        lvl = self.fusion_level + 1
+        mask, K, inv_K = inputs['mask'], inputs['K', lvl], inputs['inv_K', lvl]
+        extrinsics, extrinsics_inv = inputs['extrinsics'], inputs['extrinsics_inv']
+        fusion_dict = {('cam', cam): {} for cam in range(self.num_cams)}
+        voxel_feat = self.backproject_into_voxel(feats_agg, mask, K, extrinsics_inv)
+        if self.model == 'depth':
+            feats = self.project_voxel_into_image(voxel_feat, inv_K, extrinsics)
+            fusion_dict['proj_feat'] = torch.stack(feats, 1).flatten(0, 1)
+            if self.aug_depth:
+                inputs['extrinsics_aug'] = self.augment_extrinsics(extrinsics)
+                feats = self.project_voxel_into_image(voxel_feat, inv_K, inputs['extrinsics_aug'])
+                fusion_dict['proj_feat_aug'] = torch.stack(feats, 1).flatten(0, 1)
+            if getattr(self, 'syn_visualize', False):
+                raise NotImplementedError('synthesis visualisation sweep (:320-336) is outside the hot path')
+            return fusion_dict
+        if self.model == 'pose':
+            b, c, _ = voxel_feat.shape
+            bev = voxel_feat.reshape(b, c * self.z_dim, self.y_dim, self.x_dim)
+            return self.reduce_dim(bev)
+        raise ValueError(self.model)
