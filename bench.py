@@ -1,0 +1,368 @@
+"""bench.py -- rigs/second of the VFDepth fusion (+ view-synthesis) hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 ... bench.py --gpus N ...
+
+One step = one pass of the hot path, forward AND backward, over one batch of synthetic DDAD-shaped rigs
+(BASELINE.json configs[1]: 8 rigs of 6 cameras, 384x640 images -> 48x80x256 feature maps, 100x100x20 voxels,
+50 depth bins): VFNet.backproject_into_voxel (voxel gather kernel + the two 1x1 MLPs, which stay cuBLAS) ->
+project_voxel_into_image without reduce_dim (ray-sampling kernel) -> backward of both with a resident upstream
+gradient; then, when built, the 6-camera x 3-frame view-synthesis warp + SSIM/L1 loss forward+backward.
+Every rank owns whole rigs (weak scaling, no data-path collective); value = rigs all ranks processed / max-over-
+ranks device time.  The JSON line also carries the roofline of the dominant kernel, the CPU baseline (the oracle =
+the reference's own torch ops on the host cores) and the end-to-end number with host buffers.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'vfnet_fusion_warp_fwd_bwd_rigs_per_sec'
+UNIT = 'rigs/s'
+BATCH = 8                 # rigs per GPU per step (configs[1])
+DATASET = 'ddad'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--batch', type=int, default=BATCH)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-warp', action='store_true', help='time the fusion half only')
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    return rank, world, local
+
+
+def measured_peak():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.isfile(p):
+        with open(p) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '200'], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(',')]
+            if len(f) < 6 or not f[0].isdigit():
+                continue
+            sm.append(int(f[0]))
+            mx = int(f[1])
+            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), f[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------
+# workload
+# --------------------------------------------------------------------------------------------------
+class FusionWorkload:
+    """BATCH synthetic DDAD-shaped rigs on one device + the drop-in VFNet (random-init MLP weights)."""
+
+    def __init__(self, batch, dev, seed):
+        from vfdepth_b200 import config as vcfg
+        from vfdepth_b200.rig import make_rig
+        from vfdepth_b200.vfnet import VFNet
+        self.cfg = vcfg.default_config(DATASET, batch_size=batch)
+        self.dev, self.B = dev, batch
+        inputs, _ = make_rig(self.cfg, seed=seed, with_feats=False, with_images=False)
+        m = self.cfg['model']
+        self.lvl = m['fusion_level'] + 1
+        torch.manual_seed(seed)
+        self.net = VFNet(self.cfg, m['fusion_feat_in_dim'], 128, 'depth').to(dev)
+        g = self.net.geom
+        self.g = g
+        gen = torch.Generator().manual_seed(seed)
+        # host (pinned) copies: what a data loader / the encoder hand-off would hold
+        pin = lambda t: t.contiguous().pin_memory()
+        # channel-last feature maps, as a channels_last 1x1 conv emits them; logical shape [B,6,C,h,w]
+        self.h_feats = pin(torch.randn((batch, g.num_cams, g.h, g.w, g.C), generator=gen))
+        self.h_small = {k: pin(inputs[k]) for k in ('mask', 'extrinsics', 'extrinsics_inv')}
+        self.h_small['K'] = pin(inputs[('K', self.lvl)])
+        self.h_small['inv_K'] = pin(inputs[('inv_K', self.lvl)])
+        self.d_feats_host = torch.empty_like(self.h_feats).pin_memory()
+        self.h_scalar = torch.zeros(1).pin_memory()
+        # resident copies
+        self.feats = self.h_feats.to(dev)
+        self.small = {k: v.to(dev) for k, v in self.h_small.items()}
+        # upstream gradient of the ray samples: produced on the device by reduce_dim's backward in training
+        self.g_up = torch.randn((batch, g.num_cams, g.h, g.w, g.Cv * g.D), device=dev)
+
+    def step(self, feats, small):
+        """fusion forward + backward through the drop-in API; returns (ray rows, d_feats)."""
+        f = feats.permute(0, 1, 4, 2, 3).requires_grad_(True)        # [B,6,C,h,w] view, channels_last strides
+        vox = self.net.backproject_into_voxel(f, small['mask'], small['K'], small['extrinsics_inv'])
+        rows = self.net.ray_rows(vox, small['inv_K'], small['extrinsics'])
+        for p in self.net.parameters():
+            p.grad = None
+        torch.autograd.backward(rows, self.g_up)
+        return rows, f.grad
+
+    def step_resident(self):
+        return self.step(self.feats, self.small)
+
+    def step_e2e(self):
+        feats = self.h_feats.to(self.dev, non_blocking=True)
+        small = {k: v.to(self.dev, non_blocking=True) for k, v in self.h_small.items()}
+        rows, d_feats = self.step(feats, small)
+        self.d_feats_host.copy_(d_feats.permute(0, 1, 3, 4, 2), non_blocking=True)
+        self.h_scalar.copy_(rows[0, 0, 0, 0, :1], non_blocking=True)
+
+    def h2d_bytes(self):
+        return self.h_feats.numel() * 4 + sum(v.numel() * 4 for v in self.h_small.values())
+
+    def d2h_bytes(self):
+        return self.d_feats_host.numel() * 4 + 4
+
+    def algorithmic_bytes(self):
+        """per launch, SURVEY.md 8d: unique inputs read once + required outputs written once (fp32)."""
+        g, B = self.g, self.B
+        feats = B * g.num_cams * g.h * g.w * g.C * 4
+        msk = B * g.num_cams * g.h * g.w * 4
+        rows = B * g.N * 3 * (g.C + 1) * 4
+        vol = B * g.N * g.Cv * 4
+        ray = B * g.num_cams * g.h * g.w * g.Cv * g.D * 4
+        return {'vfd_voxel_gather_depth_fwd': feats + msk + rows, 'vfd_voxel_gather_depth_bwd': feats + msk + rows,
+                'vfd_ray_sample_fwd': vol + ray, 'vfd_ray_sample_bwd': vol + ray}
+
+
+def timed(fn, steps, world):
+    """K steps bracketed by barrier + synchronize on both sides, CUDA events on the launching stream."""
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the reference's own torch path (the oracle) on the host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_fusion_pass(steps, warmup, seed=1234):
+    """fusion forward+backward of ONE rig per step through the oracle (bit-identical to the reference on CPU,
+    tests/test_oracle_golden.py).  -> (rigs/s, cores, seconds per rig)."""
+    from oracle import vfdepth_oracle as orc
+    from vfdepth_b200 import config as vcfg
+    from vfdepth_b200.rig import make_rig
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = vcfg.default_config(DATASET, batch_size=1)
+    inputs, extras = make_rig(cfg, seed=seed, with_images=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    C, Cv = cfg['model']['fusion_feat_in_dim'], cfg['model']['voxel_pre_dim'][-1]
+    gen = torch.Generator().manual_seed(seed)
+    mlp = dict(w_no=torch.randn((Cv, C + 1, 1), generator=gen) * 0.05, b_no=torch.zeros(Cv),
+               w_ov=torch.randn((Cv, 2 * (C + 1), 1), generator=gen) * 0.05, b_ov=torch.zeros(Cv))
+    h, w = orc.feature_hw(cfg)
+    g_up = torch.randn((1, Cv * cfg['model']['proj_d_bins'], h, w), generator=gen)
+
+    def one():
+        f = extras['feats_agg'].clone().requires_grad_(True)
+        p = {k: v.clone().requires_grad_(True) for k, v in mlp.items()}
+        vox = orc.backproject_into_voxel(cfg, f, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'],
+                                         'depth', p)
+        proj = orc.project_voxel_into_image(cfg, vox, inputs[('inv_K', lvl)], inputs['extrinsics'])
+        torch.autograd.backward(proj, [g_up] * len(proj))
+        return f.grad
+
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    return steps / dt, cores, dt / steps
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    steps, warmup = max(1, args.steps), max(1, min(args.warmup, 2))
+    steps = min(steps, 6)               # ~5-15 s per rig on a many-core host: keep the arm within minutes
+    rps, cores, sec = cpu_fusion_pass(steps, warmup)
+    sample = 'fusion fwd+bwd (gather + 1x1 MLPs + ray sampling, no reduce_dim) of 1 DDAD rig per step, %d steps' % steps
+    line = {'impl': 'reference', 'metric': METRIC, 'value': rps, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
+            'warmup': warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': 'configs[1]: VFNet fusion fwd+bwd, DDAD-shaped rigs (6x384x640), reference torch '
+                                   'path on the host cores', 'rigs_per_step': 1},
+            'cpu_baseline': {'value': rps, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': rps, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: vfdepth_b200 has no CPU path')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    torch.backends.cuda.matmul.allow_tf32 = False      # the reference's setting (train.py:25)
+    from vfdepth_b200 import _lib
+    wl = FusionWorkload(args.batch, dev, seed=1234 + 1000 * rank)
+    warp = None
+    if not args.no_warp:
+        try:
+            from vfdepth_b200.bench_warp import WarpWorkload
+            warp = WarpWorkload(args.batch, dev, seed=1234 + 1000 * rank)
+        except ImportError:
+            warp = None
+
+    def step():
+        wl.step_resident()
+        if warp is not None:
+            warp.step_resident()
+
+    def step_e2e():
+        wl.step_e2e()
+        if warp is not None:
+            warp.step_e2e()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = _lib.launches
+    ms = timed(step, args.steps, world)
+    launches = _lib.launches - n0
+    rigs = args.batch * world * args.steps
+    value = rigs / (ms * 1e-3)
+
+    # per-kernel device time inside a second timed pass (events around every ABI call on the launch stream)
+    _lib.start_event_trace()
+    for _ in range(args.steps):
+        step()
+    trace = _lib.stop_event_trace()
+
+    e2e = None
+    if not args.no_e2e:
+        for _ in range(2):
+            step_e2e()
+        ms_e2e = timed(step_e2e, args.steps, world)
+        h2d = wl.h2d_bytes() + (warp.h2d_bytes() if warp else 0)
+        d2h = wl.d2h_bytes() + (warp.d2h_bytes() if warp else 0)
+        e2e = {'value': rigs / (ms_e2e * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+               'ms_per_step': ms_e2e / args.steps}
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank == 0:
+        peak, how = measured_peak()
+        alg = wl.algorithmic_bytes()
+        if warp is not None:
+            alg.update(warp.algorithmic_bytes())
+        kernels = {}
+        for name, (n, tot) in trace.items():
+            per = tot / max(n, 1)
+            k = {'launches_per_step': n / args.steps, 'ms_per_launch': per, 'ms_per_step': tot / args.steps}
+            if name in alg:
+                k['algorithmic_mb'] = alg[name] / 1e6
+                k['gbs'] = alg[name] / per / 1e6
+                k['frac_of_hbm_peak'] = k['gbs'] / peak
+            kernels[name] = k
+        ours_ms = sum(k['ms_per_step'] for k in kernels.values())
+        dom = max(kernels, key=lambda n: kernels[n]['ms_per_step'])
+        roof = {'bound': 'hbm', 'kernel': dom, 'achieved': kernels[dom].get('gbs'), 'peak': peak, 'unit': 'GB/s',
+                'frac': kernels[dom].get('frac_of_hbm_peak'), 'traffic': None, 'peak_source': how,
+                'algorithmic_bytes_per_launch': alg.get(dom), 'ms_per_launch': kernels[dom]['ms_per_launch']}
+        tpath = os.path.join(ROOT, 'profiles', 'traffic.json')
+        if os.path.isfile(tpath):
+            with open(tpath) as f:
+                roof['traffic'] = json.load(f).get(dom)
+        line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+                'warmup': max(3, args.warmup), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
+                'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                'config': {'workload': 'configs[1]: VFNet fusion fwd+bwd (voxel gather + 1x1 MLPs + ray sampling, no '
+                                       'reduce_dim)%s, %d DDAD-shaped rigs (6x384x640) per GPU per step'
+                                       % (' + 6-cam x 3-frame warp + SSIM/L1 loss fwd+bwd' if warp else '', args.batch),
+                           'rigs_per_step_per_gpu': args.batch, 'l2': 'inputs and outputs larger than L2 '
+                           '(189 MB feature maps, 4.9 GB gather rows, 2.4 GB ray samples per step)',
+                           'sharding': 'whole rigs per rank, no data-path collective',
+                           'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms},
+                'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof, 'kernels': kernels}
+        if world == 1 and not args.no_cpu_baseline:
+            rps, cores, sec = cpu_fusion_pass(2, 1)
+            line['cpu_baseline'] = {'value': rps, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                                    'sample': 'fusion fwd+bwd of 1 DDAD rig per step through the oracle (reference '
+                                              'torch ops), 1 warm-up + 2 timed, %.1f s per rig' % sec}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

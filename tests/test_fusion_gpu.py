@@ -104,12 +104,12 @@ def test_golden_pose_backward():
     assert H.rel_err(d_got.cpu(), d_ref) < TOL
 
 
-@pytest.mark.parametrize('dataset,C,seed', [('ddad', 32, 101), ('nuscenes', 16, 102)])
-def test_oracle_full_grid(dataset, C, seed):
+@pytest.mark.parametrize('dataset,C,Cv,seed', [('ddad', 32, 8, 101), ('nuscenes', 16, 8, 102), ('ddad', 8, 64, 103)])
+def test_oracle_full_grid(dataset, C, Cv, seed):
     """full-size voxel grid / depth bins / feature map (channels reduced so the CPU oracle finishes in seconds):
     coordinates and masks bit-exact, values and gradients within tolerance."""
     dev = _dev()
-    cfg = vcfg.default_config(dataset, batch_size=1, model__fusion_feat_in_dim=C, model__voxel_pre_dim=[8])
+    cfg = vcfg.default_config(dataset, batch_size=1, model__fusion_feat_in_dim=C, model__voxel_pre_dim=[Cv])
     inputs, extras = make_rig(cfg, seed=seed, with_images=False)
     lvl = cfg['model']['fusion_level'] + 1
     net = _net(cfg, C, 16, 'depth', None, dev)

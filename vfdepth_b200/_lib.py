@@ -74,8 +74,35 @@ def ptr(t):
     return ctypes.c_void_p(0 if t is None else t.data_ptr())
 
 
+_events = None   # when a dict: name -> [(start, end) CUDA events] recorded around every ABI call (bench.py)
+
+
+def start_event_trace():
+    """Record a CUDA-event pair on the current stream around every ABI call until ``stop_event_trace``."""
+    global _events
+    _events = {}
+
+
+def stop_event_trace():
+    """-> {name: (launch count, total ms)}; synchronises the device."""
+    global _events
+    import torch
+    ev, _events = _events, None
+    torch.cuda.synchronize()
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in (ev or {}).items()}
+
+
 def call(name, *args):
     global launches
     fn = getattr(load(), name)
     launches += 1
-    check(fn(*args), name)
+    if _events is None:
+        check(fn(*args), name)
+        return
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rc = fn(*args)
+    e1.record()
+    _events.setdefault(name, []).append((e0, e1))
+    check(rc, name)

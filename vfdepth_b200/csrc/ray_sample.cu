@@ -194,6 +194,151 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_kernel(con
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Vectorised variant for CV channels with CV % 4 == 0 and CV/4 a divisor of 32 (CV = 64 in both reference configs).
+//   lane = (sub-warp q, l): the CV/4 lanes of a sub-warp hold 4 channels each of ONE depth bin, so a warp
+//   interpolates 32/(CV/4) bins per iteration with LDG.128 (256 B contiguous per corner at CV=64) -- 4x fewer
+//   issued instructions than the generic kernel, which ncu showed to be issue-bound (profiles/).
+//   The [channel][D] shared tile is exactly the output run out[pixel][c*D+d], so it leaves the SM as ONE bulk
+//   asynchronous copy (cp.async.bulk, the TMA engine) per pixel, overlapped with the next pixel's coordinates.
+// Warps walk pixels with a grid stride so the tile, the slots and the mbarrier are set up once.
+// ---------------------------------------------------------------------------------------------
+template <int CV>
+struct VecCfg {
+    static constexpr int kLanes = CV / 4;            // lanes per depth bin
+    static constexpr int kBins = VFD_WARP / kLanes;  // bins per warp iteration
+};
+
+template <int CV>
+__device__ __forceinline__ void vec_smem_carve(int D, int warp, float*& tile, RaySlot*& slot, uint64_t*& bar) {
+    float* tiles = reinterpret_cast<float*>(vfd_ray_smem);
+    RaySlot* slots = reinterpret_cast<RaySlot*>(tiles + (size_t)kRayWarps * CV * D);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(slots + (size_t)kRayWarps * D + (((size_t)kRayWarps * D) & 1));
+    tile = tiles + (size_t)warp * CV * D;
+    slot = slots + (size_t)warp * D;
+    bar = bars + warp;
+}
+
+template <int CV>
+static size_t vec_smem_bytes(int D) {
+    return (size_t)kRayWarps * CV * D * sizeof(float) + ((size_t)kRayWarps * D + 1) * sizeof(RaySlot) +
+           kRayWarps * sizeof(uint64_t) + 16;
+}
+
+__device__ __forceinline__ void corner_weights(const RaySlot& s, float* w) {
+    const float ex = 1.f - s.fx, ey = 1.f - s.fy, ez = 1.f - s.fz;
+    const float a = ex * ey, b = s.fx * ey, c = ex * s.fy, d = s.fx * s.fy;
+    w[0] = a * ez; w[1] = b * ez; w[2] = c * ez; w[3] = d * ez;
+    w[4] = a * s.fz; w[5] = b * s.fz; w[6] = c * s.fz; w[7] = d * s.fz;
+}
+
+template <int CV>
+__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel(const RayArgs a) {
+    using Cfg = VecCfg<CV>;
+    const vfd_fusion_desc& d = a.d;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = lane / Cfg::kLanes, l = lane % Cfg::kLanes;
+    const int P = d.h * d.w, D = d.D;
+    const long ntasks = (long)d.B * d.num_cams * P;
+    float* tile;
+    RaySlot* slot;
+    uint64_t* bar;
+    vec_smem_carve<CV>(D, warp, tile, slot, bar);
+    const int XC = d.X * CV, YXC = d.Y * XC;
+    for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
+        const int p = (int)(task % P), bc = (int)(task / P), c = bc % d.num_cams, b = bc / d.num_cams;
+        ray_phase1(a, b, c, p, lane, slot);
+        if (lane == 0) bulk_wait_read0();   // the previous pixel's tile has left shared memory
+        __syncwarp();
+        const float* vol = a.vol + (size_t)b * d.X * d.Y * d.Z * CV + 4 * l;
+        for (int d0 = 0; d0 < D; d0 += Cfg::kBins) {
+            const int dd = d0 + q;
+            if (dd < D) {
+                const RaySlot s = slot[dd];
+                float4 r = f4_zero();
+                if (s.corners) {
+                    float w[8];
+                    corner_weights(s, w);
+                    const float* p0 = vol + (long)s.base * CV;
+                    if (s.corners == 0xFFu) {
+                        float4 v[8];
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) v[t] = ldg_f4(p0 + (t & 1) * CV + ((t >> 1) & 1) * XC + (t >> 2) * YXC);
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) f4_fma(r, w[t], v[t]);
+                    } else {
+#pragma unroll
+                        for (int t = 0; t < 8; ++t)
+                            if (s.corners & (1u << t))
+                                f4_fma(r, w[t], ldg_f4(p0 + (t & 1) * CV + ((t >> 1) & 1) * XC + (t >> 2) * YXC));
+                    }
+                }
+                float* t0 = tile + (4 * l) * D + dd;
+                t0[0] = r.x; t0[D] = r.y; t0[2 * D] = r.z; t0[3 * D] = r.w;
+            }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            bulk_store_s2g(a.out + (size_t)task * CV * D, tile, (uint32_t)(CV * D * sizeof(float)));
+            bulk_commit();
+        }
+    }
+    if (lane == 0) bulk_wait_read0();
+}
+
+template <int CV>
+__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_vec_kernel(const RayArgs a) {
+    using Cfg = VecCfg<CV>;
+    const vfd_fusion_desc& d = a.d;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = lane / Cfg::kLanes, l = lane % Cfg::kLanes;
+    const int P = d.h * d.w, D = d.D;
+    const long ntasks = (long)d.B * d.num_cams * P;
+    float* tile;
+    RaySlot* slot;
+    uint64_t* bar;
+    vec_smem_carve<CV>(D, warp, tile, slot, bar);
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    const int XC = d.X * CV, YXC = d.Y * XC;
+    const uint32_t bytes = (uint32_t)(CV * D * sizeof(float));
+    uint32_t phase = 0;
+    for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
+        const int p = (int)(task % P), bc = (int)(task / P), c = bc % d.num_cams, b = bc / d.num_cams;
+        if (lane == 0) {   // the pixel's upstream-gradient run arrives as one bulk copy while phase 1 runs
+            mbar_expect_tx(bar, bytes);
+            bulk_load_g2s(tile, a.d_out + (size_t)task * CV * D, bytes, bar);
+        }
+        ray_phase1(a, b, c, p, lane, slot);
+        __syncwarp();
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        float* dvol = a.d_vol + (size_t)b * d.X * d.Y * d.Z * CV + 4 * l;
+        for (int d0 = 0; d0 < D; d0 += Cfg::kBins) {
+            const int dd = d0 + q;
+            if (dd < D) {
+                const RaySlot s = slot[dd];
+                if (s.corners) {
+                    const float* t0 = tile + (4 * l) * D + dd;
+                    const float4 g = make_float4(t0[0], t0[D], t0[2 * D], t0[3 * D]);
+                    float w[8];
+                    corner_weights(s, w);
+                    float* p0 = dvol + (long)s.base * CV;
+#pragma unroll
+                    for (int t = 0; t < 8; ++t)
+                        if (s.corners & (1u << t))
+                            red_add_f4(p0 + (t & 1) * CV + ((t >> 1) & 1) * XC + (t >> 2) * YXC, f4_scale(w[t], g));
+                }
+            }
+        }
+        __syncwarp();   // every lane is done with the tile before the next bulk load overwrites it
+    }
+}
+
 static int check_ray_desc(const vfd_fusion_desc* d) {
     if (!d) return VFD_ERR_NULL;
     if (d->B < 1 || d->num_cams < 1 || d->num_cams > VFD_MAX_CAMS || d->h < 1 || d->w < 1 || d->X < 1 ||
@@ -204,6 +349,10 @@ static int check_ray_desc(const vfd_fusion_desc* d) {
     if (ray_smem_bytes(d->D) > 200 * 1024) return VFD_ERR_UNSUPPORTED;
     return VFD_OK;
 }
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+// persistent-style grid for the vectorised kernels: 148 SMs x 2 resident CTAs x 4 waves of work items
+constexpr long kVecGrid = 148 * 2 * 4;
 
 }  // namespace vfd
 
@@ -216,11 +365,22 @@ extern "C" int vfd_ray_sample_fwd(const vfd_fusion_desc* d, const float* vol, co
     if (!vol || !invK || !E || !out) return VFD_ERR_NULL;
     RayArgs a = {};
     a.d = *d; a.vol = vol; a.invK = invK; a.E = E; a.out = out; a.grid = grid;
+    const long tasks = (long)d->B * d->num_cams * d->h * d->w;
+    if (d->Cv == 64 && vec_smem_bytes<64>(d->D) <= 110 * 1024 && aligned16(out) && aligned16(vol)) {
+        const size_t smem = vec_smem_bytes<64>(d->D);
+        if (cudaFuncSetAttribute(ray_sample_fwd_vec_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem) != cudaSuccess)
+            return VFD_ERR_CUDA;
+        const long blocks = (tasks + kRayWarps - 1) / kRayWarps;
+        ray_sample_fwd_vec_kernel<64><<<(unsigned)(blocks < kVecGrid ? blocks : kVecGrid), kRayWarps * VFD_WARP, smem,
+                                        (cudaStream_t)stream>>>(a);
+        VFD_CHECK_LAUNCH();
+        return VFD_OK;
+    }
     const size_t smem = ray_smem_bytes(d->D);
     if (cudaFuncSetAttribute(ray_sample_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
         cudaSuccess)
         return VFD_ERR_CUDA;
-    const long tasks = (long)d->B * d->num_cams * d->h * d->w;
     ray_sample_fwd_kernel<<<(unsigned)((tasks + kRayWarps - 1) / kRayWarps), kRayWarps * VFD_WARP, smem,
                             (cudaStream_t)stream>>>(a);
     VFD_CHECK_LAUNCH();
@@ -236,11 +396,22 @@ extern "C" int vfd_ray_sample_bwd(const vfd_fusion_desc* d, const float* invK, c
     a.d = *d; a.invK = invK; a.E = E; a.d_out = d_out; a.d_vol = d_vol;
     const size_t bytes = (size_t)d->B * d->X * d->Y * d->Z * d->Cv * sizeof(float);
     if (cudaMemsetAsync(d_vol, 0, bytes, (cudaStream_t)stream) != cudaSuccess) return VFD_ERR_CUDA;
+    const long tasks = (long)d->B * d->num_cams * d->h * d->w;
+    if (d->Cv == 64 && vec_smem_bytes<64>(d->D) <= 110 * 1024 && aligned16(d_out) && aligned16(d_vol)) {
+        const size_t smem = vec_smem_bytes<64>(d->D);
+        if (cudaFuncSetAttribute(ray_sample_bwd_vec_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem) != cudaSuccess)
+            return VFD_ERR_CUDA;
+        const long blocks = (tasks + kRayWarps - 1) / kRayWarps;
+        ray_sample_bwd_vec_kernel<64><<<(unsigned)(blocks < kVecGrid ? blocks : kVecGrid), kRayWarps * VFD_WARP, smem,
+                                        (cudaStream_t)stream>>>(a);
+        VFD_CHECK_LAUNCH();
+        return VFD_OK;
+    }
     const size_t smem = ray_smem_bytes(d->D);
     if (cudaFuncSetAttribute(ray_sample_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
         cudaSuccess)
         return VFD_ERR_CUDA;
-    const long tasks = (long)d->B * d->num_cams * d->h * d->w;
     ray_sample_bwd_kernel<<<(unsigned)((tasks + kRayWarps - 1) / kRayWarps), kRayWarps * VFD_WARP, smem,
                             (cudaStream_t)stream>>>(a);
     VFD_CHECK_LAUNCH();
