@@ -135,7 +135,7 @@ class FusionWorkload:
         self.feats = self.h_feats.to(dev)
         self.small = {k: v.to(dev) for k, v in self.h_small.items()}
         # upstream gradient of the ray samples: produced on the device by reduce_dim's backward in training
-        self.g_up = torch.randn((batch, g.num_cams, g.h, g.w, g.Cv * g.D), device=dev)
+        self.g_up = torch.randn((batch, g.num_cams, g.h, g.w, g.D, g.Cv), device=dev)
 
     def step(self, feats, small):
         """fusion forward + backward through the drop-in API; returns (ray rows, d_feats)."""
@@ -155,7 +155,7 @@ class FusionWorkload:
         small = {k: v.to(self.dev, non_blocking=True) for k, v in self.h_small.items()}
         rows, d_feats = self.step(feats, small)
         self.d_feats_host.copy_(d_feats.permute(0, 1, 3, 4, 2), non_blocking=True)
-        self.h_scalar.copy_(rows[0, 0, 0, 0, :1], non_blocking=True)
+        self.h_scalar.copy_(rows[0, 0, 0, 0, 0, :1], non_blocking=True)
 
     def h2d_bytes(self):
         return self.h_feats.numel() * 4 + sum(v.numel() * 4 for v in self.h_small.values())

@@ -95,7 +95,9 @@ int vfd_voxel_gather_pose_bwd(const vfd_fusion_desc* d, const float* mask_small,
 /* VFNet.project_voxel_into_image without reduce_dim (:245-262):
  *   vol   [B,Z,Y,X,Cv]       channel-last voxel volume (voxel_feat of :240)
  *   invK  [B,cams,4,4]       inputs['inv_K', fusion_level+1];   E [B,cams,4,4] camera->ego
- *   out   [B,cams,h,w,Cv*D]  channel index = c*D + d (the .view of :262), channel-last
+ *   out   [B,cams,h,w,D,Cv]  channel-last samples, c fastest.  The reference's channel order c*D + d (the .view
+ *                            of :262) is a fixed permutation of reduce_dim's INPUT channels; the host layer applies
+ *                            it to reduce_dim.0.weight instead of transposing the samples
  *   grid (optional) [B,cams,D,h,w,3]  normalised sampling coordinates (:251-260), bit-exact */
 int vfd_ray_sample_fwd(const vfd_fusion_desc* d, const float* vol, const float* invK, const float* E,
                        float* out, float* grid, void* stream);

@@ -40,8 +40,9 @@ def _mlp(g):
 
 
 def _ray_to_ref(rows, D):
-    """[B,cams,h,w,Cv*D] channel-last -> the reference's [B,cams,Cv*D,h,w]."""
-    return rows.permute(0, 1, 4, 2, 3)
+    """samples [B,cams,h,w,D,Cv] -> the reference's [B,cams,Cv*D,h,w] with channel = c*D + d (:262)."""
+    B, n, h, w, D, cv = rows.shape
+    return rows.permute(0, 1, 5, 4, 2, 3).reshape(B, n, cv * D, h, w)
 
 
 def test_golden_fusion_forward():
@@ -188,3 +189,18 @@ def test_full_size_properties():
     gf, = torch.autograd.grad(lhs, f)
     rhs = (gf * f1).sum()
     assert abs(float(lhs) - float(rhs)) / abs(float(lhs)) < 1e-3
+
+
+def test_reduce_dim_handoff_matches_reference_channel_order():
+    """project_voxel_into_image feeds reduce_dim with d-major samples and a permuted weight; the result must equal
+    reduce_dim applied to the reference's [B, Cv*D (c*D+d), h, w] tensor (volumetric_fusionnet.py:262-265)."""
+    dev = _dev()
+    g = H.load_npz('golden_fusion.npz')
+    cfg = H.fusion_cfg()
+    net = _net(cfg, 8, 16, 'depth', _mlp(g), dev)
+    vox = g['voxel_feat'].to(dev)
+    outs = net.project_voxel_into_image(vox, g['inv_K'].to(dev), g['extrinsics'].to(dev))
+    ref_in = g['proj'].to(dev)                      # the reference's own ray samples, reference channel order
+    for c in range(6):
+        ref = net.reduce_dim(ref_in[:, c])
+        assert H.rel_err(outs[c].detach().cpu(), ref.detach().cpu()) < TOL

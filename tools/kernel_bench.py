@@ -56,7 +56,7 @@ def main():
     count = torch.empty(B, N, dtype=torch.uint8, device=dev)
     d_feats = torch.empty_like(feats)
     vol = torch.randn(B, g.Z, g.Y, g.X, g.Cv, device=dev)
-    out = torch.empty(B, 6, g.h, g.w, g.Cv * g.D, device=dev)
+    out = torch.empty(B, 6, g.h, g.w, g.D, g.Cv, device=dev)
     d_vol = torch.empty_like(vol)
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     p = _lib.ptr

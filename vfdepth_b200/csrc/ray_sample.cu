@@ -1,21 +1,28 @@
 // Ray sampling: VFNet.project_voxel_into_image without reduce_dim (network/volumetric_fusionnet.py:232-262),
 // forward and backward.
 //
+// Layout.  Samples leave the kernel as out[b, cam, v, u, d, c] (channel-last, c fastest): the 64 channels of one
+// (pixel, depth bin) sample are one contiguous 256 B run, written by one half-warp with 128-bit stores and read
+// back the same way by the backward.  The reference's channel order c*D + d (:262) is a fixed permutation of
+// reduce_dim's input channels; the host layer applies it to reduce_dim.0.weight (29 MB, once per step) instead
+// of transposing 295 MB of samples per rig.
+//
 // Mapping.  One warp owns one feature-map pixel of one camera (its whole ray of D depth bins).
 //   phase 1  lane <-> depth bin: the bin's 3-D point in ego space with the reference's exact fp32 operation
 //            order (vfd_coords.h), un-normalised as ATen does, floor + 3 fractions + an 8-bit corner mask,
-//            kept in shared memory.
-//   phase 2  lane <-> channel (32 channels = one 128 B line of the channel-last volume per corner): walk the
-//            D bins, trilinear-interpolate, park the result in a [channel][D+1] shared tile (conflict-free
-//            both ways), then stream the tile out as the contiguous run out[pixel][c*D + d] with 128-bit
-//            stores.  The reference layout channel = c*D + d (:262) is produced directly, channel-last.
+//            kept in shared memory (20 B per bin).
+//   phase 2  vectorised kernel (Cv % 4 == 0, Cv/4 divides 32; Cv = 64 in both reference configs): the Cv/4 lanes
+//            of a sub-warp hold 4 channels each of ONE bin, so a warp interpolates 32/(Cv/4) bins per iteration
+//            with LDG.128 (256 B contiguous per corner).  Generic kernel (any Cv): lane <-> channel.
 // The volume of one rig (51.2 MB at DDAD size) is L2-resident; consecutive bins of a ray and neighbouring
-// pixels share voxel cells, so most corner lines hit in L1.
+// pixels share voxel cells, so most corner lines hit in L1.  Warps walk pixels with a grid stride.
 #include "common.cuh"
 
 namespace vfd {
 
 constexpr int kRayWarps = 8;
+// persistent-style grid: 148 SMs x resident CTAs x a few waves of work items
+constexpr long kRayGrid = 148 * 8 * 2;
 
 struct RayArgs {
     vfd_fusion_desc d;
@@ -72,159 +79,6 @@ __device__ __forceinline__ void ray_phase1(const RayArgs& a, int b, int c, int p
     }
 }
 
-__device__ __forceinline__ float corner_weight(const RaySlot& s, int t) {
-    const float wx = (t & 1) ? s.fx : 1.f - s.fx;
-    const float wy = (t & 2) ? s.fy : 1.f - s.fy;
-    const float wz = (t & 4) ? s.fz : 1.f - s.fz;
-    return wx * wy * wz;
-}
-
-extern __shared__ __align__(16) unsigned char vfd_ray_smem[];
-
-__device__ __forceinline__ void ray_smem_carve(int D, int warp, RaySlot*& slot, float*& tile) {
-    RaySlot* slots = reinterpret_cast<RaySlot*>(vfd_ray_smem);
-    float* tiles = reinterpret_cast<float*>(slots + kRayWarps * D);
-    slot = slots + warp * D;
-    tile = tiles + (size_t)warp * VFD_WARP * (D + 1);
-}
-
-static size_t ray_smem_bytes(int D) {
-    return (size_t)kRayWarps * D * sizeof(RaySlot) + (size_t)kRayWarps * VFD_WARP * (D + 1) * sizeof(float);
-}
-
-__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_kernel(const RayArgs a) {
-    const vfd_fusion_desc& d = a.d;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int P = d.h * d.w, D = d.D, Cv = d.Cv;
-    const long task = (long)blockIdx.x * kRayWarps + warp;  // (b*cams + c)*P + p
-    if (task >= (long)d.B * d.num_cams * P) return;
-    const int p = (int)(task % P), bc = (int)(task / P), c = bc % d.num_cams, b = bc / d.num_cams;
-    RaySlot* slot;
-    float* tile;
-    ray_smem_carve(D, warp, slot, tile);
-    ray_phase1(a, b, c, p, lane, slot);
-    __syncwarp();
-    const float* vol = a.vol + (size_t)b * d.X * d.Y * d.Z * Cv;
-    const int XC = d.X * Cv, YXC = d.Y * XC;
-    float* orow = a.out + (size_t)task * Cv * D;
-    for (int cg = 0; cg < Cv; cg += VFD_WARP) {
-        const int ch = cg + lane;
-        const int nch = min(VFD_WARP, Cv - cg);
-        for (int dd = 0; dd < D; ++dd) {
-            const RaySlot s = slot[dd];
-            float val = 0.f;
-            if (s.corners && ch < Cv) {
-                const float* p0 = vol + (long)s.base * Cv + ch;
-#pragma unroll
-                for (int t = 0; t < 8; ++t)
-                    if (s.corners & (1u << t))
-                        val = fmaf(corner_weight(s, t), __ldg(p0 + (t & 1) * Cv + ((t >> 1) & 1) * XC + (t >> 2) * YXC), val);
-            }
-            tile[lane * (D + 1) + dd] = val;
-        }
-        __syncwarp();
-        // the group's outputs are the contiguous run orow[cg*D .. cg*D + nch*D)
-        float* run = orow + (size_t)cg * D;
-        const int len = nch * D;
-        if (((reinterpret_cast<uintptr_t>(run) & 15) == 0) && (len % 4 == 0)) {
-            for (int e = lane * 4; e < len; e += VFD_WARP * 4) {
-                float4 v;
-                v.x = tile[((e + 0) / D) * (D + 1) + (e + 0) % D];
-                v.y = tile[((e + 1) / D) * (D + 1) + (e + 1) % D];
-                v.z = tile[((e + 2) / D) * (D + 1) + (e + 2) % D];
-                v.w = tile[((e + 3) / D) * (D + 1) + (e + 3) % D];
-                st_stream_f4(run + e, v);
-            }
-        } else {
-            for (int e = lane; e < len; e += VFD_WARP) run[e] = tile[(e / D) * (D + 1) + e % D];
-        }
-        __syncwarp();
-    }
-}
-
-// Backward: d_vol[corner, ch] += w_corner * d_out[pixel][ch*D + d]; the run of one channel group is first
-// brought into the shared tile with coalesced 128-bit loads, then scattered bin by bin (one 128 B reduction per
-// corner per warp instruction).
-__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_kernel(const RayArgs a) {
-    const vfd_fusion_desc& d = a.d;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int P = d.h * d.w, D = d.D, Cv = d.Cv;
-    const long task = (long)blockIdx.x * kRayWarps + warp;
-    if (task >= (long)d.B * d.num_cams * P) return;
-    const int p = (int)(task % P), bc = (int)(task / P), c = bc % d.num_cams, b = bc / d.num_cams;
-    RaySlot* slot;
-    float* tile;
-    ray_smem_carve(D, warp, slot, tile);
-    RayArgs a2 = a;
-    a2.grid = nullptr;
-    ray_phase1(a2, b, c, p, lane, slot);
-    __syncwarp();
-    float* dvol = a.d_vol + (size_t)b * d.X * d.Y * d.Z * Cv;
-    const int XC = d.X * Cv, YXC = d.Y * XC;
-    const float* grow = a.d_out + (size_t)task * Cv * D;
-    for (int cg = 0; cg < Cv; cg += VFD_WARP) {
-        const int ch = cg + lane;
-        const int nch = min(VFD_WARP, Cv - cg);
-        const float* run = grow + (size_t)cg * D;
-        const int len = nch * D;
-        if (((reinterpret_cast<uintptr_t>(run) & 15) == 0) && (len % 4 == 0)) {
-            for (int e = lane * 4; e < len; e += VFD_WARP * 4) {
-                const float4 v = ld_stream_f4(run + e);
-                tile[((e + 0) / D) * (D + 1) + (e + 0) % D] = v.x;
-                tile[((e + 1) / D) * (D + 1) + (e + 1) % D] = v.y;
-                tile[((e + 2) / D) * (D + 1) + (e + 2) % D] = v.z;
-                tile[((e + 3) / D) * (D + 1) + (e + 3) % D] = v.w;
-            }
-        } else {
-            for (int e = lane; e < len; e += VFD_WARP) tile[(e / D) * (D + 1) + e % D] = __ldg(run + e);
-        }
-        __syncwarp();
-        for (int dd = 0; dd < D; ++dd) {
-            const RaySlot s = slot[dd];
-            if (!s.corners || ch >= Cv) continue;
-            const float g = tile[lane * (D + 1) + dd];
-            if (g == 0.f) continue;
-            float* p0 = dvol + (long)s.base * Cv + ch;
-#pragma unroll
-            for (int t = 0; t < 8; ++t)
-                if (s.corners & (1u << t))
-                    red_add_f1(p0 + (t & 1) * Cv + ((t >> 1) & 1) * XC + (t >> 2) * YXC, corner_weight(s, t) * g);
-        }
-        __syncwarp();
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Vectorised variant for CV channels with CV % 4 == 0 and CV/4 a divisor of 32 (CV = 64 in both reference configs).
-//   lane = (sub-warp q, l): the CV/4 lanes of a sub-warp hold 4 channels each of ONE depth bin, so a warp
-//   interpolates 32/(CV/4) bins per iteration with LDG.128 (256 B contiguous per corner at CV=64) -- 4x fewer
-//   issued instructions than the generic kernel, which ncu showed to be issue-bound (profiles/).
-//   The [channel][D] shared tile is exactly the output run out[pixel][c*D+d], so it leaves the SM as ONE bulk
-//   asynchronous copy (cp.async.bulk, the TMA engine) per pixel, overlapped with the next pixel's coordinates.
-// Warps walk pixels with a grid stride so the tile, the slots and the mbarrier are set up once.
-// ---------------------------------------------------------------------------------------------
-template <int CV>
-struct VecCfg {
-    static constexpr int kLanes = CV / 4;            // lanes per depth bin
-    static constexpr int kBins = VFD_WARP / kLanes;  // bins per warp iteration
-};
-
-template <int CV>
-__device__ __forceinline__ void vec_smem_carve(int D, int warp, float*& tile, RaySlot*& slot, uint64_t*& bar) {
-    float* tiles = reinterpret_cast<float*>(vfd_ray_smem);
-    RaySlot* slots = reinterpret_cast<RaySlot*>(tiles + (size_t)kRayWarps * CV * D);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(slots + (size_t)kRayWarps * D + (((size_t)kRayWarps * D) & 1));
-    tile = tiles + (size_t)warp * CV * D;
-    slot = slots + (size_t)warp * D;
-    bar = bars + warp;
-}
-
-template <int CV>
-static size_t vec_smem_bytes(int D) {
-    return (size_t)kRayWarps * CV * D * sizeof(float) + ((size_t)kRayWarps * D + 1) * sizeof(RaySlot) +
-           kRayWarps * sizeof(uint64_t) + 16;
-}
-
 __device__ __forceinline__ void corner_weights(const RaySlot& s, float* w) {
     const float ex = 1.f - s.fx, ey = 1.f - s.fy, ez = 1.f - s.fz;
     const float a = ex * ey, b = s.fx * ey, c = ex * s.fy, d = s.fx * s.fy;
@@ -232,26 +86,107 @@ __device__ __forceinline__ void corner_weights(const RaySlot& s, float* w) {
     w[4] = a * s.fz; w[5] = b * s.fz; w[6] = c * s.fz; w[7] = d * s.fz;
 }
 
-template <int CV>
-__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel(const RayArgs a) {
-    using Cfg = VecCfg<CV>;
+extern __shared__ __align__(16) unsigned char vfd_ray_smem[];
+
+static size_t ray_smem_bytes(int D) { return (size_t)kRayWarps * D * sizeof(RaySlot); }
+
+struct Task {
+    int b, c, p;
+};
+__device__ __forceinline__ Task decode_task(long task, int P, int cams) {
+    Task t;
+    t.p = (int)(task % P);
+    const int bc = (int)(task / P);
+    t.c = bc % cams;
+    t.b = bc / cams;
+    return t;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// generic kernels: lane <-> channel (any Cv)
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_kernel(const RayArgs a) {
     const vfd_fusion_desc& d = a.d;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int q = lane / Cfg::kLanes, l = lane % Cfg::kLanes;
+    const int P = d.h * d.w, D = d.D, Cv = d.Cv;
+    const long ntasks = (long)d.B * d.num_cams * P;
+    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * D;
+    const int XC = d.X * Cv, YXC = d.Y * XC;
+    for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
+        const Task t = decode_task(task, P, d.num_cams);
+        ray_phase1(a, t.b, t.c, t.p, lane, slot);
+        __syncwarp();
+        const float* vol = a.vol + (size_t)t.b * d.X * d.Y * d.Z * Cv;
+        float* orow = a.out + (size_t)task * D * Cv;
+        for (int dd = 0; dd < D; ++dd) {
+            const RaySlot s = slot[dd];
+            float w[8];
+            corner_weights(s, w);
+            for (int ch = lane; ch < Cv; ch += VFD_WARP) {
+                float val = 0.f;
+                const float* p0 = vol + (long)s.base * Cv + ch;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (s.corners & (1u << k))
+                        val = fmaf(w[k], __ldg(p0 + (k & 1) * Cv + ((k >> 1) & 1) * XC + (k >> 2) * YXC), val);
+                orow[dd * Cv + ch] = val;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_kernel(const RayArgs a) {
+    const vfd_fusion_desc& d = a.d;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int P = d.h * d.w, D = d.D, Cv = d.Cv;
+    const long ntasks = (long)d.B * d.num_cams * P;
+    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * D;
+    const int XC = d.X * Cv, YXC = d.Y * XC;
+    for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
+        const Task t = decode_task(task, P, d.num_cams);
+        ray_phase1(a, t.b, t.c, t.p, lane, slot);
+        __syncwarp();
+        float* dvol = a.d_vol + (size_t)t.b * d.X * d.Y * d.Z * Cv;
+        const float* grow = a.d_out + (size_t)task * D * Cv;
+        for (int dd = 0; dd < D; ++dd) {
+            const RaySlot s = slot[dd];
+            if (!s.corners) continue;
+            float w[8];
+            corner_weights(s, w);
+            for (int ch = lane; ch < Cv; ch += VFD_WARP) {
+                const float g = __ldg(grow + dd * Cv + ch);
+                float* p0 = dvol + (long)s.base * Cv + ch;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (s.corners & (1u << k))
+                        red_add_f1(p0 + (k & 1) * Cv + ((k >> 1) & 1) * XC + (k >> 2) * YXC, w[k] * g);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// vectorised kernels: sub-warp of CV/4 lanes <-> one depth bin, lane <-> 4 channels
+// ------------------------------------------------------------------------------------------------------------
+template <int CV>
+__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel(const RayArgs a) {
+    constexpr int kLanes = CV / 4, kBins = VFD_WARP / kLanes;
+    const vfd_fusion_desc& d = a.d;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = lane / kLanes, l = lane % kLanes;
     const int P = d.h * d.w, D = d.D;
     const long ntasks = (long)d.B * d.num_cams * P;
-    float* tile;
-    RaySlot* slot;
-    uint64_t* bar;
-    vec_smem_carve<CV>(D, warp, tile, slot, bar);
+    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * D;
     const int XC = d.X * CV, YXC = d.Y * XC;
     for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
-        const int p = (int)(task % P), bc = (int)(task / P), c = bc % d.num_cams, b = bc / d.num_cams;
-        ray_phase1(a, b, c, p, lane, slot);
-        if (lane == 0) bulk_wait_read0();   // the previous pixel's tile has left shared memory
+        const Task t = decode_task(task, P, d.num_cams);
+        ray_phase1(a, t.b, t.c, t.p, lane, slot);
         __syncwarp();
-        const float* vol = a.vol + (size_t)b * d.X * d.Y * d.Z * CV + 4 * l;
-        for (int d0 = 0; d0 < D; d0 += Cfg::kBins) {
+        const float* vol = a.vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
+        float* orow = a.out + (size_t)task * D * CV + 4 * l;
+        for (int d0 = 0; d0 < D; d0 += kBins) {
             const int dd = d0 + q;
             if (dd < D) {
                 const RaySlot s = slot[dd];
@@ -263,79 +198,56 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
                     if (s.corners == 0xFFu) {
                         float4 v[8];
 #pragma unroll
-                        for (int t = 0; t < 8; ++t) v[t] = ldg_f4(p0 + (t & 1) * CV + ((t >> 1) & 1) * XC + (t >> 2) * YXC);
+                        for (int k = 0; k < 8; ++k) v[k] = ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC);
 #pragma unroll
-                        for (int t = 0; t < 8; ++t) f4_fma(r, w[t], v[t]);
+                        for (int k = 0; k < 8; ++k) f4_fma(r, w[k], v[k]);
                     } else {
 #pragma unroll
-                        for (int t = 0; t < 8; ++t)
-                            if (s.corners & (1u << t))
-                                f4_fma(r, w[t], ldg_f4(p0 + (t & 1) * CV + ((t >> 1) & 1) * XC + (t >> 2) * YXC));
+                        for (int k = 0; k < 8; ++k)
+                            if (s.corners & (1u << k))
+                                f4_fma(r, w[k], ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC));
                     }
                 }
-                float* t0 = tile + (4 * l) * D + dd;
-                t0[0] = r.x; t0[D] = r.y; t0[2 * D] = r.z; t0[3 * D] = r.w;
+                st_stream_f4(orow + dd * CV, r);
             }
         }
-        fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) {
-            bulk_store_s2g(a.out + (size_t)task * CV * D, tile, (uint32_t)(CV * D * sizeof(float)));
-            bulk_commit();
-        }
     }
-    if (lane == 0) bulk_wait_read0();
 }
 
 template <int CV>
 __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_vec_kernel(const RayArgs a) {
-    using Cfg = VecCfg<CV>;
+    constexpr int kLanes = CV / 4, kBins = VFD_WARP / kLanes;
     const vfd_fusion_desc& d = a.d;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int q = lane / Cfg::kLanes, l = lane % Cfg::kLanes;
+    const int q = lane / kLanes, l = lane % kLanes;
     const int P = d.h * d.w, D = d.D;
     const long ntasks = (long)d.B * d.num_cams * P;
-    float* tile;
-    RaySlot* slot;
-    uint64_t* bar;
-    vec_smem_carve<CV>(D, warp, tile, slot, bar);
-    if (lane == 0) {
-        mbar_init(bar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncwarp();
+    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * D;
     const int XC = d.X * CV, YXC = d.Y * XC;
-    const uint32_t bytes = (uint32_t)(CV * D * sizeof(float));
-    uint32_t phase = 0;
     for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
-        const int p = (int)(task % P), bc = (int)(task / P), c = bc % d.num_cams, b = bc / d.num_cams;
-        if (lane == 0) {   // the pixel's upstream-gradient run arrives as one bulk copy while phase 1 runs
-            mbar_expect_tx(bar, bytes);
-            bulk_load_g2s(tile, a.d_out + (size_t)task * CV * D, bytes, bar);
-        }
-        ray_phase1(a, b, c, p, lane, slot);
+        const Task t = decode_task(task, P, d.num_cams);
+        ray_phase1(a, t.b, t.c, t.p, lane, slot);
         __syncwarp();
-        mbar_wait(bar, phase);
-        phase ^= 1;
-        float* dvol = a.d_vol + (size_t)b * d.X * d.Y * d.Z * CV + 4 * l;
-        for (int d0 = 0; d0 < D; d0 += Cfg::kBins) {
+        float* dvol = a.d_vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
+        const float* grow = a.d_out + (size_t)task * D * CV + 4 * l;
+        for (int d0 = 0; d0 < D; d0 += kBins) {
             const int dd = d0 + q;
             if (dd < D) {
                 const RaySlot s = slot[dd];
                 if (s.corners) {
-                    const float* t0 = tile + (4 * l) * D + dd;
-                    const float4 g = make_float4(t0[0], t0[D], t0[2 * D], t0[3 * D]);
+                    const float4 g = ld_stream_f4(grow + dd * CV);
                     float w[8];
                     corner_weights(s, w);
                     float* p0 = dvol + (long)s.base * CV;
 #pragma unroll
-                    for (int t = 0; t < 8; ++t)
-                        if (s.corners & (1u << t))
-                            red_add_f4(p0 + (t & 1) * CV + ((t >> 1) & 1) * XC + (t >> 2) * YXC, f4_scale(w[t], g));
+                    for (int k = 0; k < 8; ++k)
+                        if (s.corners & (1u << k))
+                            red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, f4_scale(w[k], g));
                 }
             }
         }
-        __syncwarp();   // every lane is done with the tile before the next bulk load overwrites it
+        __syncwarp();
     }
 }
 
@@ -346,13 +258,35 @@ static int check_ray_desc(const vfd_fusion_desc* d) {
         return VFD_ERR_DESC;
     if (!d->bins) return VFD_ERR_NULL;
     if ((long)d->X * d->Y * d->Z * d->Cv >= (1L << 31)) return VFD_ERR_DESC;
-    if (ray_smem_bytes(d->D) > 200 * 1024) return VFD_ERR_UNSUPPORTED;
+    if (ray_smem_bytes(d->D) > 48 * 1024) return VFD_ERR_UNSUPPORTED;
     return VFD_OK;
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
-// persistent-style grid for the vectorised kernels: 148 SMs x 2 resident CTAs x 4 waves of work items
-constexpr long kVecGrid = 148 * 2 * 4;
+
+static int launch_ray(const RayArgs& a, bool bwd, cudaStream_t st) {
+    const vfd_fusion_desc& d = a.d;
+    const long tasks = (long)d.B * d.num_cams * d.h * d.w;
+    const long blocks = (tasks + kRayWarps - 1) / kRayWarps;
+    const unsigned grid = (unsigned)(blocks < kRayGrid ? blocks : kRayGrid);
+    const size_t smem = ray_smem_bytes(d.D);
+    const bool vec_ok = bwd ? (aligned16(a.d_out) && aligned16(a.d_vol)) : (aligned16(a.out) && aligned16(a.vol));
+#define VFD_RAY_VEC(CVAL)                                                                                   \
+    if (d.Cv == CVAL && vec_ok) {                                                                           \
+        if (bwd) ray_sample_bwd_vec_kernel<CVAL><<<grid, kRayWarps * VFD_WARP, smem, st>>>(a);              \
+        else ray_sample_fwd_vec_kernel<CVAL><<<grid, kRayWarps * VFD_WARP, smem, st>>>(a);                  \
+        VFD_CHECK_LAUNCH();                                                                                 \
+        return VFD_OK;                                                                                      \
+    }
+    VFD_RAY_VEC(64)
+    VFD_RAY_VEC(32)
+    VFD_RAY_VEC(128)
+#undef VFD_RAY_VEC
+    if (bwd) ray_sample_bwd_kernel<<<grid, kRayWarps * VFD_WARP, smem, st>>>(a);
+    else ray_sample_fwd_kernel<<<grid, kRayWarps * VFD_WARP, smem, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
 
 }  // namespace vfd
 
@@ -365,26 +299,7 @@ extern "C" int vfd_ray_sample_fwd(const vfd_fusion_desc* d, const float* vol, co
     if (!vol || !invK || !E || !out) return VFD_ERR_NULL;
     RayArgs a = {};
     a.d = *d; a.vol = vol; a.invK = invK; a.E = E; a.out = out; a.grid = grid;
-    const long tasks = (long)d->B * d->num_cams * d->h * d->w;
-    if (d->Cv == 64 && vec_smem_bytes<64>(d->D) <= 110 * 1024 && aligned16(out) && aligned16(vol)) {
-        const size_t smem = vec_smem_bytes<64>(d->D);
-        if (cudaFuncSetAttribute(ray_sample_fwd_vec_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smem) != cudaSuccess)
-            return VFD_ERR_CUDA;
-        const long blocks = (tasks + kRayWarps - 1) / kRayWarps;
-        ray_sample_fwd_vec_kernel<64><<<(unsigned)(blocks < kVecGrid ? blocks : kVecGrid), kRayWarps * VFD_WARP, smem,
-                                        (cudaStream_t)stream>>>(a);
-        VFD_CHECK_LAUNCH();
-        return VFD_OK;
-    }
-    const size_t smem = ray_smem_bytes(d->D);
-    if (cudaFuncSetAttribute(ray_sample_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
-        cudaSuccess)
-        return VFD_ERR_CUDA;
-    ray_sample_fwd_kernel<<<(unsigned)((tasks + kRayWarps - 1) / kRayWarps), kRayWarps * VFD_WARP, smem,
-                            (cudaStream_t)stream>>>(a);
-    VFD_CHECK_LAUNCH();
-    return VFD_OK;
+    return launch_ray(a, false, (cudaStream_t)stream);
 }
 
 extern "C" int vfd_ray_sample_bwd(const vfd_fusion_desc* d, const float* invK, const float* E, const float* d_out,
@@ -396,24 +311,5 @@ extern "C" int vfd_ray_sample_bwd(const vfd_fusion_desc* d, const float* invK, c
     a.d = *d; a.invK = invK; a.E = E; a.d_out = d_out; a.d_vol = d_vol;
     const size_t bytes = (size_t)d->B * d->X * d->Y * d->Z * d->Cv * sizeof(float);
     if (cudaMemsetAsync(d_vol, 0, bytes, (cudaStream_t)stream) != cudaSuccess) return VFD_ERR_CUDA;
-    const long tasks = (long)d->B * d->num_cams * d->h * d->w;
-    if (d->Cv == 64 && vec_smem_bytes<64>(d->D) <= 110 * 1024 && aligned16(d_out) && aligned16(d_vol)) {
-        const size_t smem = vec_smem_bytes<64>(d->D);
-        if (cudaFuncSetAttribute(ray_sample_bwd_vec_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smem) != cudaSuccess)
-            return VFD_ERR_CUDA;
-        const long blocks = (tasks + kRayWarps - 1) / kRayWarps;
-        ray_sample_bwd_vec_kernel<64><<<(unsigned)(blocks < kVecGrid ? blocks : kVecGrid), kRayWarps * VFD_WARP, smem,
-                                        (cudaStream_t)stream>>>(a);
-        VFD_CHECK_LAUNCH();
-        return VFD_OK;
-    }
-    const size_t smem = ray_smem_bytes(d->D);
-    if (cudaFuncSetAttribute(ray_sample_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
-        cudaSuccess)
-        return VFD_ERR_CUDA;
-    ray_sample_bwd_kernel<<<(unsigned)((tasks + kRayWarps - 1) / kRayWarps), kRayWarps * VFD_WARP, smem,
-                            (cudaStream_t)stream>>>(a);
-    VFD_CHECK_LAUNCH();
-    return VFD_OK;
+    return launch_ray(a, true, (cudaStream_t)stream);
 }

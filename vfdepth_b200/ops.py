@@ -180,7 +180,7 @@ class _RaySample(torch.autograd.Function):
         _chk(E, 'extrinsics', (B, g.num_cams, 4, 4))
         dev = vol.device
         d = g.desc(dev, B)
-        out = torch.empty((B, g.num_cams, g.h, g.w, g.Cv * g.D), device=dev, dtype=torch.float32)
+        out = torch.empty((B, g.num_cams, g.h, g.w, g.D, g.Cv), device=dev, dtype=torch.float32)
         grid = torch.empty((B, g.num_cams, g.D, g.h, g.w, 3), device=dev) if want_grid else None
         _lib.call('vfd_ray_sample_fwd', ctypes.byref(d), _lib.ptr(vol), _lib.ptr(invK), _lib.ptr(E), _lib.ptr(out),
                   _lib.ptr(grid), _stream())
@@ -216,5 +216,5 @@ def voxel_gather_pose(feats_cl, mask_small, K, Einv, geom):
 
 
 def ray_sample(vol_cl, invK, E, geom, want_grid=False):
-    """vol_cl [B,Z,Y,X,Cv] -> [B,cams,h,w,Cv*D] (channel = c*D + d), (+ grid [B,cams,D,h,w,3])."""
+    """vol_cl [B,Z,Y,X,Cv] -> samples [B,cams,h,w,D,Cv] (c fastest), (+ grid [B,cams,D,h,w,3])."""
     return _RaySample.apply(vol_cl, invK, E, geom, want_grid)

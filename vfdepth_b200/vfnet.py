@@ -8,8 +8,10 @@ checkpoints load.  What changes is underneath:
   are one kernel launch each (vfdepth_b200/csrc/voxel_gather.cu, ray_sample.cu);
 * everything is channel-last: the gather writes the two MLP inputs as rows ``[B,N,257(+pad)]`` so the 1x1
   ``Conv1d`` of :197-230 is a plain GEMM (``F.linear`` with the Conv1d's own weight) whose output IS the
-  channel-last voxel volume the ray kernel reads, and the ray kernel emits ``[B*6,h,w,Cv*D]`` which is handed
-  to ``reduce_dim`` as a channels_last NCHW tensor with channel = c*D + d (:262).
+  channel-last voxel volume the ray kernel reads, and the ray kernel emits samples ``[B*6,h,w,D,Cv]`` (one
+  contiguous 256 B run per sample) which are handed to ``reduce_dim`` as a channels_last NCHW tensor with channel
+  = d*Cv + c; the reference's order c*D + d (:262) is restored by permuting the INPUT channels of
+  ``reduce_dim.0.weight`` on the fly (the parameter itself keeps the reference's shape and meaning).
 
 The learnable parts (the two MLPs and ``reduce_dim``) stay in PyTorch / cuBLAS / cuDNN.
 """
@@ -124,7 +126,7 @@ class VFNet(nn.Module):
         return avg[:, :, :self.feat_in_dim + 1].permute(0, 2, 1)
 
     def ray_rows(self, voxel_feat, inv_K, extrinsics, want_grid=False):
-        """The geometry core of ``project_voxel_into_image``: [B,cams,h,w,Cv*D] channel-last ray samples."""
+        """The geometry core of ``project_voxel_into_image``: ray samples [B,cams,h,w,D,Cv], c fastest."""
         B, cv, _ = voxel_feat.shape
         vol = voxel_feat.permute(0, 2, 1).contiguous().view(B, self.z_dim, self.y_dim, self.x_dim, cv)
         return ops.ray_sample(vol, inv_K.float().contiguous(), extrinsics.float().contiguous(), self.geom, want_grid)
@@ -132,9 +134,15 @@ class VFNet(nn.Module):
     def project_voxel_into_image(self, voxel_feat, inv_K, extrinsics):
         """-> list over cameras of [B,feat_out,h,w].  Reference :232-267."""
         rows = self.ray_rows(voxel_feat, inv_K, extrinsics)
-        B, ncam = rows.shape[:2]
-        x = rows.view(B * ncam, self.img_h, self.img_w, -1).permute(0, 3, 1, 2)   # channels_last NCHW
-        y = self.reduce_dim(x)
+        B, ncam, _, _, D, cv = rows.shape
+        x = rows.view(B * ncam, self.img_h, self.img_w, D * cv).permute(0, 3, 1, 2)   # channels_last NCHW
+        conv0 = self.reduce_dim[0]
+        # input channel c*D+d of the reference (:262) is channel d*cv+c here: permute the weight, not the samples
+        w0 = conv0.weight.view(conv0.out_channels, cv, D, 3, 3).permute(0, 2, 1, 3, 4)
+        w0 = w0.reshape(conv0.out_channels, D * cv, 3, 3)
+        y = F.conv2d(F.pad(x, (1, 1, 1, 1), mode='reflect'), w0, conv0.bias, stride=conv0.stride)
+        for layer in list(self.reduce_dim)[1:]:
+            y = layer(y)
         y = y.view(B, ncam, *y.shape[1:])
         return [y[:, c] for c in range(ncam)]
 
