@@ -16,6 +16,8 @@
 //            with LDG.128 (256 B contiguous per corner).  Generic kernel (any Cv): lane <-> channel.
 // The volume of one rig (51.2 MB at DDAD size) is L2-resident; consecutive bins of a ray and neighbouring
 // pixels share voxel cells, so most corner lines hit in L1.  Warps walk pixels with a grid stride.
+#include <limits.h>
+
 #include "common.cuh"
 
 namespace vfd {
@@ -168,47 +170,123 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_kernel(con
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// vectorised kernels: sub-warp of CV/4 lanes <-> one depth bin, lane <-> 4 channels
+// vectorised kernels (CV % 4 == 0, CV/4 divides 32): COLUMN WALK.
+//   One warp owns one image column u of one camera and kBins = 32/(CV/4) consecutive depth bins; the CV/4 lanes of
+//   a sub-warp hold 4 channels each and walk the h pixels of the column top to bottom at a fixed bin.
+//   Consecutive pixels of a column at the same depth differ by depth/f metres in ego height (0.1 .. 1.1 m) against
+//   1.5 m voxels, so runs of pixels share the same 2x2x2 voxel cell:
+//     forward   the 8 corner rows (8 x LDG.128) stay in registers while the cell does not change;
+//     backward  the 8 corner contributions are accumulated in registers and leave as 8 vector reductions
+//               (red.global.add.v4.f32) only when the cell changes -- ncu showed the one-reduction-per-sample
+//               version saturating the L2 atomic units (profiles/).
+//   Slots (cell index, fractions, corner mask) of the kBins x h samples are computed lane-parallel first.
 // ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ RaySlot make_slot(const vfd_fusion_desc& d, const float* Em, const float* iK, int u, int v,
+                                             float dep, float* g /*3, out*/) {
+    float ray[3];
+    vfd_pixel_ray(iK, (float)u, (float)v, ray);
+    vfd_ray_point_to_grid(Em, ray, dep, d.vox_start, d.vox_length, g);
+    const float ix = vfd_unnormalize(g[0], d.X), iy = vfd_unnormalize(g[1], d.Y), iz = vfd_unnormalize(g[2], d.Z);
+    const float x0 = floorf(ix), y0 = floorf(iy), z0 = floorf(iz);
+    RaySlot s;
+    s.corners = 0;
+    s.base = 0;
+    s.fx = ix - x0; s.fy = iy - y0; s.fz = iz - z0;
+    if (x0 >= -1.f && x0 <= (float)(d.X - 1) && y0 >= -1.f && y0 <= (float)(d.Y - 1) && z0 >= -1.f &&
+        z0 <= (float)(d.Z - 1)) {
+        const int xi = (int)x0, yi = (int)y0, zi = (int)z0;
+        s.base = (zi * d.Y + yi) * d.X + xi;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const int xx = xi + (t & 1), yy = yi + ((t >> 1) & 1), zz = zi + (t >> 2);
+            if (xx >= 0 && xx < d.X && yy >= 0 && yy < d.Y && zz >= 0 && zz < d.Z) s.corners |= 1u << t;
+        }
+    }
+    return s;
+}
+
+struct ColTask {
+    int b, c, u, d0;
+};
+template <int KBINS>
+__device__ __forceinline__ ColTask decode_col(long task, const vfd_fusion_desc& d) {
+    const int nd = (d.D + KBINS - 1) / KBINS;
+    ColTask t;
+    t.d0 = (int)(task % nd) * KBINS;
+    long r = task / nd;
+    t.u = (int)(r % d.w);
+    r /= d.w;
+    t.c = (int)(r % d.num_cams);
+    t.b = (int)(r / d.num_cams);
+    return t;
+}
+
+template <int KBINS>
+__device__ __forceinline__ void col_phase1(const RayArgs& a, const ColTask& t, int lane, RaySlot* slot) {
+    const vfd_fusion_desc& d = a.d;
+    const float* invK = a.invK + (size_t)(t.b * d.num_cams + t.c) * 16;
+    const float* E = a.E + (size_t)(t.b * d.num_cams + t.c) * 16;
+    float Em[12], iK[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) { Em[i] = __ldg(E + i); iK[i] = __ldg(invK + i); }
+    for (int idx = lane; idx < KBINS * d.h; idx += VFD_WARP) {
+        const int q = idx / d.h, v = idx % d.h, dd = t.d0 + q;
+        RaySlot s;
+        s.corners = 0; s.base = 0; s.fx = s.fy = s.fz = 0.f;
+        if (dd < d.D) {
+            float g[3];
+            s = make_slot(d, Em, iK, t.u, v, __ldg(d.bins + dd), g);
+            if (a.grid) {
+                float* go = a.grid + ((((size_t)(t.b * d.num_cams + t.c) * d.D + dd) * d.h + v) * d.w + t.u) * 3;
+                go[0] = g[0]; go[1] = g[1]; go[2] = g[2];
+            }
+        }
+        slot[idx] = s;
+    }
+}
+
 template <int CV>
 __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel(const RayArgs a) {
     constexpr int kLanes = CV / 4, kBins = VFD_WARP / kLanes;
     const vfd_fusion_desc& d = a.d;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = lane / kLanes, l = lane % kLanes;
-    const int P = d.h * d.w, D = d.D;
-    const long ntasks = (long)d.B * d.num_cams * P;
-    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * D;
+    const int H = d.h, W = d.w, D = d.D;
+    const long ntasks = (long)d.B * d.num_cams * W * ((D + kBins - 1) / kBins);
+    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * kBins * H;
     const int XC = d.X * CV, YXC = d.Y * XC;
     for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
-        const Task t = decode_task(task, P, d.num_cams);
-        ray_phase1(a, t.b, t.c, t.p, lane, slot);
+        const ColTask t = decode_col<kBins>(task, d);
+        col_phase1<kBins>(a, t, lane, slot);
         __syncwarp();
-        const float* vol = a.vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
-        float* orow = a.out + (size_t)task * D * CV + 4 * l;
-        for (int d0 = 0; d0 < D; d0 += kBins) {
-            const int dd = d0 + q;
-            if (dd < D) {
-                const RaySlot s = slot[dd];
+        const int dd = t.d0 + q;
+        if (dd < D) {
+            const float* vol = a.vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
+            float* o = a.out + ((((size_t)(t.b * d.num_cams + t.c) * H) * W + t.u) * D + dd) * CV + 4 * l;
+            const size_t ostride = (size_t)W * D * CV;
+            int cur_base = INT_MIN;
+            float4 vv[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) vv[k] = f4_zero();
+            for (int v = 0; v < H; ++v) {
+                const RaySlot s = slot[q * H + v];
                 float4 r = f4_zero();
                 if (s.corners) {
-                    float w[8];
-                    corner_weights(s, w);
-                    const float* p0 = vol + (long)s.base * CV;
-                    if (s.corners == 0xFFu) {
-                        float4 v[8];
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) v[k] = ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC);
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) f4_fma(r, w[k], v[k]);
-                    } else {
+                    if (s.base != cur_base) {
+                        cur_base = s.base;
+                        const float* p0 = vol + (long)s.base * CV;
 #pragma unroll
                         for (int k = 0; k < 8; ++k)
-                            if (s.corners & (1u << k))
-                                f4_fma(r, w[k], ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC));
+                            vv[k] = (s.corners & (1u << k))
+                                        ? ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC)
+                                        : f4_zero();
                     }
+                    float w[8];
+                    corner_weights(s, w);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) f4_fma(r, w[k], vv[k]);
                 }
-                st_stream_f4(orow + dd * CV, r);
+                st_stream_f4(o + v * ostride, r);
             }
         }
         __syncwarp();
@@ -221,30 +299,55 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_vec_kernel
     const vfd_fusion_desc& d = a.d;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = lane / kLanes, l = lane % kLanes;
-    const int P = d.h * d.w, D = d.D;
-    const long ntasks = (long)d.B * d.num_cams * P;
-    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * D;
+    const int H = d.h, W = d.w, D = d.D;
+    const long ntasks = (long)d.B * d.num_cams * W * ((D + kBins - 1) / kBins);
+    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * kBins * H;
     const int XC = d.X * CV, YXC = d.Y * XC;
     for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
-        const Task t = decode_task(task, P, d.num_cams);
-        ray_phase1(a, t.b, t.c, t.p, lane, slot);
+        const ColTask t = decode_col<kBins>(task, d);
+        col_phase1<kBins>(a, t, lane, slot);
         __syncwarp();
-        float* dvol = a.d_vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
-        const float* grow = a.d_out + (size_t)task * D * CV + 4 * l;
-        for (int d0 = 0; d0 < D; d0 += kBins) {
-            const int dd = d0 + q;
-            if (dd < D) {
-                const RaySlot s = slot[dd];
+        const int dd = t.d0 + q;
+        if (dd < D) {
+            float* dvol = a.d_vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
+            const float* gp = a.d_out + ((((size_t)(t.b * d.num_cams + t.c) * H) * W + t.u) * D + dd) * CV + 4 * l;
+            const size_t gstride = (size_t)W * D * CV;
+            int cur_base = INT_MIN;
+            unsigned cur_corners = 0;
+            float4 acc[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
+            float4 g = ld_stream_f4(gp);
+            for (int v = 0; v < H; ++v) {
+                const RaySlot s = slot[q * H + v];
+                const float4 gn = (v + 1 < H) ? ld_stream_f4(gp + (v + 1) * gstride) : f4_zero();   // prefetch
                 if (s.corners) {
-                    const float4 g = ld_stream_f4(grow + dd * CV);
+                    if (s.base != cur_base) {
+                        if (cur_corners) {
+                            float* p0 = dvol + (long)cur_base * CV;
+#pragma unroll
+                            for (int k = 0; k < 8; ++k)
+                                if (cur_corners & (1u << k))
+                                    red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
+                        }
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
+                        cur_base = s.base;
+                        cur_corners = s.corners;
+                    }
                     float w[8];
                     corner_weights(s, w);
-                    float* p0 = dvol + (long)s.base * CV;
 #pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        if (s.corners & (1u << k))
-                            red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, f4_scale(w[k], g));
+                    for (int k = 0; k < 8; ++k) f4_fma(acc[k], w[k], g);
                 }
+                g = gn;
+            }
+            if (cur_corners) {
+                float* p0 = dvol + (long)cur_base * CV;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (cur_corners & (1u << k))
+                        red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
             }
         }
         __syncwarp();
@@ -273,10 +376,17 @@ static int launch_ray(const RayArgs& a, bool bwd, cudaStream_t st) {
     const bool vec_ok = bwd ? (aligned16(a.d_out) && aligned16(a.d_vol)) : (aligned16(a.out) && aligned16(a.vol));
 #define VFD_RAY_VEC(CVAL)                                                                                   \
     if (d.Cv == CVAL && vec_ok) {                                                                           \
-        if (bwd) ray_sample_bwd_vec_kernel<CVAL><<<grid, kRayWarps * VFD_WARP, smem, st>>>(a);              \
-        else ray_sample_fwd_vec_kernel<CVAL><<<grid, kRayWarps * VFD_WARP, smem, st>>>(a);                  \
-        VFD_CHECK_LAUNCH();                                                                                 \
-        return VFD_OK;                                                                                      \
+        constexpr int kb = VFD_WARP / (CVAL / 4);                                                           \
+        const size_t vsmem = (size_t)kRayWarps * kb * d.h * sizeof(RaySlot);                                \
+        const long vtasks = (long)d.B * d.num_cams * d.w * ((d.D + kb - 1) / kb);                           \
+        const long vblocks = (vtasks + kRayWarps - 1) / kRayWarps;                                          \
+        const unsigned vgrid = (unsigned)(vblocks < kRayGrid ? vblocks : kRayGrid);                         \
+        if (vsmem <= 48 * 1024) {                                                                           \
+            if (bwd) ray_sample_bwd_vec_kernel<CVAL><<<vgrid, kRayWarps * VFD_WARP, vsmem, st>>>(a);        \
+            else ray_sample_fwd_vec_kernel<CVAL><<<vgrid, kRayWarps * VFD_WARP, vsmem, st>>>(a);            \
+            VFD_CHECK_LAUNCH();                                                                             \
+            return VFD_OK;                                                                                  \
+        }                                                                                                   \
     }
     VFD_RAY_VEC(64)
     VFD_RAY_VEC(32)
