@@ -105,6 +105,71 @@ int vfd_ray_sample_fwd(const vfd_fusion_desc* d, const float* vol, const float* 
 int vfd_ray_sample_bwd(const vfd_fusion_desc* d, const float* invK, const float* E, const float* d_out,
                        float* d_vol, void* stream);
 
+/* --------------------------------------------------------------------------------------------------
+ * View synthesis + photometric loss (models/geometry/geometry_util.py:33-82, view_rendering.py:30-82,118-198,
+ * models/losses/loss_util.py:6-25,43-78, single_cam_loss.py:17-55, multi_cam_loss.py:16-59,94-138), scale 0.
+ *
+ * For a target camera `cam` there are NW = n_src + (1+n_src)*VFD_WARP_NBR warps of a source image into its view:
+ *   j <  n_src                       temporal: frame 1+j of the SAME camera          (view_rendering.py:133-157)
+ *   j =  n_src + fi*VFD_WARP_NBR+k   frame fi (0 = current) of NEIGHBOUR nbr[cam][k]  (:160-198), summed over k
+ * "frame fi" indexes desc.color[]: fi = 0 is frame 0, fi >= 1 is frame_ids[fi].
+ * ------------------------------------------------------------------------------------------------ */
+#define VFD_WARP_SRC 2 /* max source frames besides frame 0 */
+#define VFD_WARP_NBR 2 /* neighbours per camera (utils/misc.py:10) */
+#define VFD_WARP_MAXW (VFD_WARP_SRC + (1 + VFD_WARP_SRC) * VFD_WARP_NBR)
+
+typedef struct vfd_warp_desc {
+    int32_t B, num_cams, H, W;
+    int32_t n_src;           /* len(frame_ids) - 1: 1 or 2 */
+    int32_t cam0, n_call;    /* this call processes target cameras [cam0, cam0 + n_call) */
+    int32_t intensity_align; /* training.intensity_align (view_rendering.py:148) */
+    int32_t nbr[VFD_MAX_CAMS][VFD_WARP_NBR]; /* rel_cam_list: neighbour camera or -1 (skipped, :167-168) */
+    const float* color[1 + VFD_WARP_SRC];    /* device, per frame [B,cams,3,H,W]: inputs['color', f, 0] */
+    const float* mask;                       /* device [B,cams,H,W]: inputs['mask'] */
+    const float* K;                          /* device [B,cams,4,4]: inputs['K', 0] */
+    const float* invK;                       /* device [B,cams,4,4]: inputs['inv_K', 0] */
+} vfd_warp_desc;
+
+/* optional materialised views of one call (any pointer may be NULL); [B,n_call,...] */
+typedef struct vfd_warp_views {
+    float* color;        /* [B,n_call,n_src,3,H,W]    ('color', f, 0)       view_rendering.py:156 */
+    float* color_mask;   /* [B,n_call,n_src,H,W]      ('color_mask', f, 0)  :157 */
+    float* overlap;      /* [B,n_call,1+n_src,3,H,W]  ('overlap', f, 0)     :197 */
+    float* overlap_mask; /* [B,n_call,1+n_src,H,W]    ('overlap_mask', f, 0) :198 (before multi_cam_loss.py:28) */
+    float* reproj_loss;  /* [B,n_call,H,W]            ('reproj_loss', 0)    single_cam_loss.py:53 */
+    float* reproj_mask;  /* [B,n_call,H,W]            ('reproj_mask', 0)    :54 */
+    float* grid;         /* [B,n_call,NW,H,W,2]  normalised sampling coordinates (geometry_util.py:62-77), bit-exact */
+} vfd_warp_views;
+
+/* Pass 1 -- intensity-alignment statistics (view_rendering.py:30-59) of every warp.
+ *   depth  [B,n_call,H,W]        target depth (('depth', 0) of each camera)
+ *   T      [B,n_call,NW,4,4]     target->source transforms (cam_T_cam / rel_pose_dict, pose.py:66-96)
+ *   stats  [B,n_call,NW,8] f64   scratch, zero-filled here: {count, sum ref*m, sum warp*m, sum warp, sum warp^2,
+ *                                sum ref, sum ref^2, -}
+ *   params [B,n_call,NW,8] f32   out: {w_mean, w_std+1e-8, s_std, s_mean, apply, -, -, -}; apply = 0 when
+ *                                intensity_align is off or the batch-wide early exit of :50-53 fires for warp j */
+int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const float* T, double* stats, float* params,
+                   void* stream);
+
+/* Pass 2 -- warp again, normalise, SSIM+L1 maps, min over frames, auto-mask, masked sums.
+ *   noise  [B,n_call,n_src,H,W]  the torch.randn of single_cam_loss.py:45-46 (drawn by the caller)
+ *   sums   [n_call,8] f64        zero-filled here: {sum reproj*auto, sum auto, sum spatial*m, sum m,
+ *                                sum spatio-temporal*m, sum m, -, -} over the whole local batch (loss_util.py:21-25)
+ *   views  optional materialised images (NULL for the fused path) */
+int vfd_warp_loss_fwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
+                      const float* noise, double* sums, const vfd_warp_views* views, void* stream);
+
+size_t vfd_warp_bwd_workspace_bytes(const vfd_warp_desc* d);
+
+/* Backward of pass 2 w.r.t. depth and T (statistics are constants, view_rendering.py:45).
+ *   d_num   [n_call,3] f32   dL/d(sum reproj*auto), dL/d(sum spatial*m), dL/d(sum spatio-temporal*m)
+ *   d_depth [B,n_call,H,W]   written (every pixel exactly once, no atomics)
+ *   d_T     [B,n_call,NW,4,4] written; per-block partial sums go through `ws` and are reduced in a fixed
+ *                            order (deterministic) */
+int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
+                      const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
+                      size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,14 +30,26 @@ class FusionDesc(ctypes.Structure):
     ]
 
 
+VFD_WARP_SRC = 2
+VFD_WARP_NBR = 2
+
+
 class WarpDesc(ctypes.Structure):
     """struct vfd_warp_desc"""
     _fields_ = [
         ('B', ctypes.c_int32), ('num_cams', ctypes.c_int32), ('H', ctypes.c_int32), ('W', ctypes.c_int32),
-        ('n_frames', ctypes.c_int32), ('n_nbr', ctypes.c_int32),
-        ('spatio', ctypes.c_int32), ('spatio_temporal', ctypes.c_int32), ('intensity_align', ctypes.c_int32),
-        ('nbr', (ctypes.c_int32 * 2) * VFD_MAX_CAMS),
+        ('n_src', ctypes.c_int32), ('cam0', ctypes.c_int32), ('n_call', ctypes.c_int32),
+        ('intensity_align', ctypes.c_int32),
+        ('nbr', (ctypes.c_int32 * VFD_WARP_NBR) * VFD_MAX_CAMS),
+        ('color', ctypes.c_void_p * (1 + VFD_WARP_SRC)),
+        ('mask', ctypes.c_void_p), ('K', ctypes.c_void_p), ('invK', ctypes.c_void_p),
     ]
+
+
+class WarpViews(ctypes.Structure):
+    """struct vfd_warp_views"""
+    _fields_ = [(n, ctypes.c_void_p) for n in ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss',
+                                               'reproj_mask', 'grid')]
 
 
 _lock = threading.Lock()
@@ -60,6 +72,7 @@ def load():
         lib.vfd_version.restype = ctypes.c_int
         lib.vfd_last_error.restype = ctypes.c_char_p
         lib.vfd_last_error.argtypes = [ctypes.c_int]
+        lib.vfd_warp_bwd_workspace_bytes.restype = ctypes.c_size_t
         _lib = lib
     return _lib
 

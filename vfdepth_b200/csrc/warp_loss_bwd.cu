@@ -1,0 +1,287 @@
+// Pass 2 of the view-synthesis path, backward: d loss / d depth (per pixel) and d loss / d T (4x4 per warp).
+// Nothing was saved by the forward except the statistics: the CTA re-warps a (32+4) x (8+4) region, re-evaluates the
+// loss decisions (min over frames, auto-mask, masks) on the (32+2) x (8+2) ring around its tile, turns them into
+// SSIM derivative coefficients in shared memory, gathers those over each interior pixel's 3x3 neighbourhood
+// (reflection padding handled by tap multiplicity), and pushes the result through normalisation, the bilinear
+// sampler and the projection.  Every d_depth pixel is written exactly once; d_T goes through per-CTA partial sums
+// that a second kernel adds in a fixed order -- the whole backward is deterministic.
+//   autograd of: view_rendering.py:58-82, geometry_util.py:52-77, loss_util.py:21-25,43-78,
+//                single_cam_loss.py:17-55, multi_cam_loss.py:16-59
+#include "warp_tile.cuh"
+
+namespace vfd {
+
+struct LossBwdArgs {
+    vfd_warp_desc d;
+    const float* depth;
+    const float* T;
+    const float* params;
+    const float* noise;
+    const float* d_num;   // [n_call,3]
+    float* d_depth;
+    float* d_T;
+    float* partial;       // [B*n_call][tiles][kMaxW*12]
+};
+
+extern __shared__ __align__(16) float vfd_warp_smem[];
+
+// coefficient planes over the 1-halo ring (R1 pixels): 3 sets (reproj, spatial, spatio-temporal) x 3 channels x (a,b,c),
+// the set's upstream weight (for the L1 term) and the frame each min selected
+struct Coef {
+    static constexpr int RW = kTileW + 2, RH = kTileH + 2, R = RW * RH;
+    static constexpr int kAbc = 0;                 // [3 sets][3 ch][3][R]
+    static constexpr int kWgt = kAbc + 27 * R;     // [3][R]
+    static constexpr int kSel = kWgt + 3 * R;      // [R] (int bits: sel_reproj | sel_st << 1)
+    static constexpr int kFloats = kSel + R;
+};
+
+// how many of pixel p's 3 horizontal (or vertical) window taps land on q, with reflection padding of 1
+__device__ __forceinline__ int tap_mult(int p, int q, int n) {
+    int m = 0;
+#pragma unroll
+    for (int dlt = -1; dlt <= 1; ++dlt) m += (reflect1(p + dlt, n) == q) ? 1 : 0;
+    return m;
+}
+
+__device__ __forceinline__ float pick5(const float (*v)[3], int k, int c) {
+    float r = v[0][c];
+#pragma unroll
+    for (int i = 1; i < kNPred; ++i) r = (k == i) ? v[i][c] : r;
+    return r;
+}
+
+__global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossBwdArgs a) {
+    using Rg = Region<2>;
+    const vfd_warp_desc& d = a.d;
+    __shared__ WarpCtx ctx;
+    __shared__ float s_dP[kTileThreads / 32][kMaxW * 12];
+    float* sm = vfd_warp_smem;
+    float* cf = sm + Rg::kFloats;
+    const int b = blockIdx.z / d.n_call, ci = blockIdx.z % d.n_call, cam = d.cam0 + ci;
+    const int W = d.W, H = d.H, HW = H * W, n_src = d.n_src;
+    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH, ox = tx0 - 2, oy = ty0 - 2;
+    warp_ctx_init(ctx, d, a.T, a.params, b, ci);
+    __syncthreads();
+    const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
+    const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
+    fill_region<2>(ctx, d, b, ci, ox, oy, depth, sm);
+    __syncthreads();
+
+    // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
+    const float w_set[3] = {__ldg(a.d_num + ci * 3 + 0), __ldg(a.d_num + ci * 3 + 1), __ldg(a.d_num + ci * 3 + 2)};
+    for (int r = threadIdx.x; r < Coef::R; r += kTileThreads) {
+        const int x = tx0 - 1 + r % Coef::RW, y = ty0 - 1 + r / Coef::RW;
+        if (x < 0 || x >= W || y < 0 || y >= H) continue;
+        const int p = y * W + x;
+        float nz[VFD_WARP_SRC] = {0.f, 0.f};
+        for (int k = 0; k < n_src; ++k) nz[k] = __ldg(a.noise + ((size_t)(b * d.n_call + ci) * n_src + k) * HW + p);
+        SsimGrad g[kNPred];
+        const PixelLoss o = pixel_loss<2, true>(sm, d, x, y, ox, oy, __ldg(rmaskp + p), nz, g);
+        const float wr = w_set[0] * o.automask, ws = w_set[1] * o.sp_mask, wt = w_set[2] * o.st_mask;
+        const bool s1 = o.sel_reproj == 1, t1 = o.sel_st == 1;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float ra = s1 ? g[1].a[c] : g[0].a[c], rb = s1 ? g[1].b[c] : g[0].b[c], rc = s1 ? g[1].c[c] : g[0].c[c];
+            const float ta = t1 ? g[VFD_WARP_SRC + 2].a[c] : g[VFD_WARP_SRC + 1].a[c];
+            const float tb = t1 ? g[VFD_WARP_SRC + 2].b[c] : g[VFD_WARP_SRC + 1].b[c];
+            const float tc = t1 ? g[VFD_WARP_SRC + 2].c[c] : g[VFD_WARP_SRC + 1].c[c];
+            float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
+            q[0] = wr * ra; q[Coef::R] = wr * rb; q[2 * Coef::R] = wr * rc;
+            q += 9 * Coef::R;
+            q[0] = ws * g[VFD_WARP_SRC].a[c]; q[Coef::R] = ws * g[VFD_WARP_SRC].b[c]; q[2 * Coef::R] = ws * g[VFD_WARP_SRC].c[c];
+            q += 9 * Coef::R;
+            q[0] = wt * ta; q[Coef::R] = wt * tb; q[2 * Coef::R] = wt * tc;
+        }
+        cf[Coef::kWgt + r] = wr;
+        cf[Coef::kWgt + Coef::R + r] = ws;
+        cf[Coef::kWgt + 2 * Coef::R + r] = wt;
+        reinterpret_cast<int*>(cf)[Coef::kSel + r] = (s1 ? 1 : 0) | (t1 ? 2 : 0);
+    }
+    __syncthreads();
+
+    // ---- phase C: gather the coefficients at the interior pixel, then back through normalise / sampler / projection ----
+    const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
+    const bool live = x < W && y < H;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    float dpred[kNPred][3];
+#pragma unroll
+    for (int k = 0; k < kNPred; ++k) dpred[k][0] = dpred[k][1] = dpred[k][2] = 0.f;
+    float X[3] = {0.f, 0.f, 0.f}, ray[3] = {0.f, 0.f, 0.f};
+    if (live) {
+        float SA[kNPred][3], SB[kNPred][3], SC[kNPred][3];
+#pragma unroll
+        for (int k = 0; k < kNPred; ++k)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) SA[k][c] = SB[k][c] = SC[k][c] = 0.f;
+        for (int dy = -1; dy <= 1; ++dy) {
+            const int py = y + dy;
+            if (py < 0 || py >= H) continue;
+            const int my = tap_mult(py, y, H);
+            for (int dx = -1; dx <= 1; ++dx) {
+                const int px = x + dx;
+                if (px < 0 || px >= W) continue;
+                const float mult = (float)(my * tap_mult(px, x, W));
+                const int r = (py - (ty0 - 1)) * Coef::RW + (px - (tx0 - 1));
+                const int sel = reinterpret_cast<const int*>(cf)[Coef::kSel + r];
+                const int kr = sel & 1, kt = VFD_WARP_SRC + 1 + (sel >> 1);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
+                    const float ra = mult * q[0], rb = mult * q[Coef::R], rc = mult * q[2 * Coef::R];
+                    q += 9 * Coef::R;
+                    const float sa = mult * q[0], sb = mult * q[Coef::R], sc = mult * q[2 * Coef::R];
+                    q += 9 * Coef::R;
+                    const float ta = mult * q[0], tb = mult * q[Coef::R], tc = mult * q[2 * Coef::R];
+#pragma unroll
+                    for (int k = 0; k < VFD_WARP_SRC; ++k)
+                        if (kr == k) { SA[k][c] += ra; SB[k][c] += rb; SC[k][c] += rc; }
+                    SA[VFD_WARP_SRC][c] += sa; SB[VFD_WARP_SRC][c] += sb; SC[VFD_WARP_SRC][c] += sc;
+#pragma unroll
+                    for (int k = VFD_WARP_SRC + 1; k < kNPred; ++k)
+                        if (kt == k) { SA[k][c] += ta; SB[k][c] += tb; SC[k][c] += tc; }
+                }
+            }
+        }
+        const int ctr2 = (y - oy) * Rg::RW + (x - ox);
+        const int r0 = (y - (ty0 - 1)) * Coef::RW + (x - (tx0 - 1));
+        const int sel0 = reinterpret_cast<const int*>(cf)[Coef::kSel + r0];
+        const float wl[3] = {cf[Coef::kWgt + r0], cf[Coef::kWgt + Coef::R + r0], cf[Coef::kWgt + 2 * Coef::R + r0]};
+#pragma unroll
+        for (int k = 0; k < kNPred; ++k) {
+            // which set's L1 term reaches pred k at this pixel
+            float w1;
+            if (k < VFD_WARP_SRC) w1 = ((sel0 & 1) == k) ? wl[0] : 0.f;
+            else if (k == VFD_WARP_SRC) w1 = wl[1];
+            else w1 = ((sel0 >> 1) == k - VFD_WARP_SRC - 1) ? wl[2] : 0.f;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float xv = sm[Rg::kPred + (k * 3 + c) * Rg::R + ctr2], yv = sm[Rg::kTgt + c * Rg::R + ctr2];
+                const float df = xv - yv;
+                const float sgn = df > 0.f ? 1.f : (df < 0.f ? -1.f : 0.f);
+                dpred[k][c] = (SA[k][c] + 2.f * xv * SB[k][c] + yv * SC[k][c]) * (1.f / 9.f) + (0.15f / 3.f) * w1 * sgn;
+            }
+        }
+        vfd_pixel_ray(ctx.invK, (float)x, (float)y, ray);
+        const float dep = __ldg(depth + y * W + x);
+        X[0] = VFD_MUL(dep, ray[0]); X[1] = VFD_MUL(dep, ray[1]); X[2] = VFD_MUL(dep, ray[2]);
+    }
+    float gdepth = 0.f;
+    for (int j = 0; j < ctx.NW; ++j) {
+        float dP[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) dP[i] = 0.f;
+        if (live && ctx.active[j]) {
+            const int k = j < n_src ? j : VFD_WARP_SRC + (j - n_src) / VFD_WARP_NBR;
+            const WarpSample s = warp_sample<true>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
+            if (!s.nan) {
+                const float ng = warp_normalise_grad(ctx.prm[j], s.m);
+                float gix = 0.f, giy = 0.f;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float dw = pick5(dpred, k, c) * ng;
+                    gix = fmaf(dw, s.dvx[c], gix);
+                    giy = fmaf(dw, s.dvy[c], giy);
+                }
+                // ix == cam.x / den, iy == cam.y / den  (normalise then un-normalise cancel exactly in the derivative)
+                const float inv = 1.f / s.den;
+                const float dc0 = gix * inv, dc1 = giy * inv;
+                const float dc2 = -(gix * s.cam[0] + giy * s.cam[1]) * inv * inv;
+                const float* P = ctx.P[j];
+                gdepth += dc0 * (P[0] * ray[0] + P[1] * ray[1] + P[2] * ray[2]) +
+                          dc1 * (P[4] * ray[0] + P[5] * ray[1] + P[6] * ray[2]) +
+                          dc2 * (P[8] * ray[0] + P[9] * ray[1] + P[10] * ray[2]);
+                const float dc[3] = {dc0, dc1, dc2};
+#pragma unroll
+                for (int rr = 0; rr < 3; ++rr) {
+                    dP[rr * 4 + 0] = dc[rr] * X[0];
+                    dP[rr * 4 + 1] = dc[rr] * X[1];
+                    dP[rr * 4 + 2] = dc[rr] * X[2];
+                    dP[rr * 4 + 3] = dc[rr];
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+            float v = dP[i];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) s_dP[wid][j * 12 + i] = v;
+        }
+    }
+    if (live) a.d_depth[(size_t)(b * d.n_call + ci) * HW + y * W + x] = gdepth;
+    __syncthreads();
+    const int ntile = gridDim.x * gridDim.y, tile = blockIdx.y * gridDim.x + blockIdx.x;
+    float* part = a.partial + ((size_t)blockIdx.z * ntile + tile) * (kMaxW * 12);
+    for (int i = threadIdx.x; i < ctx.NW * 12; i += kTileThreads) {
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < kTileThreads / 32; ++w) v += s_dP[w][i];
+        part[i] = v;
+    }
+}
+
+// d_T[b,ci,j] = K_src^T[:, :3] @ (sum over tiles of dP), tiles added in index order with fp64 accumulators.
+__global__ void __launch_bounds__(128) warp_dT_reduce_kernel(const LossBwdArgs a, int ntile) {
+    const vfd_warp_desc& d = a.d;
+    __shared__ double s_sum[kMaxW * 12];
+    const int bc = blockIdx.x, b = bc / d.n_call, ci = bc % d.n_call, cam = d.cam0 + ci;
+    const int NW = warp_count(d);
+    const float* part = a.partial + (size_t)bc * ntile * (kMaxW * 12);
+    for (int i = threadIdx.x; i < NW * 12; i += blockDim.x) {
+        double s = 0.0;
+        for (int t = 0; t < ntile; ++t) s += (double)part[(size_t)t * (kMaxW * 12) + i];
+        s_sum[i] = s;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < NW * 16; i += blockDim.x) {
+        const int j = i / 16, k = (i % 16) / 4, c = i % 4;
+        int fi, src;
+        warp_source(d, cam, j, &fi, &src);
+        float v = 0.f;
+        if (src >= 0) {
+            const float* K = d.K + (size_t)(b * d.num_cams + src) * 16;
+            double s = 0.0;
+            for (int r = 0; r < 3; ++r) s += (double)__ldg(K + r * 4 + k) * s_sum[j * 12 + r * 4 + c];
+            v = (float)s;
+        }
+        a.d_T[((size_t)bc * NW + j) * 16 + i % 16] = v;
+    }
+}
+
+int check_warp_desc(const vfd_warp_desc* d);   // warp_stats.cu
+
+static size_t bwd_smem_bytes() { return (Region<2>::kFloats + Coef::kFloats) * sizeof(float); }
+
+}  // namespace vfd
+
+using namespace vfd;
+
+extern "C" size_t vfd_warp_bwd_workspace_bytes(const vfd_warp_desc* d) {
+    if (check_warp_desc(d)) return 0;
+    const size_t tiles = (size_t)((d->W + kTileW - 1) / kTileW) * ((d->H + kTileH - 1) / kTileH);
+    return (size_t)d->B * d->n_call * tiles * kMaxW * 12 * sizeof(float);
+}
+
+extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
+                                 const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
+                                 size_t ws_bytes, void* stream) {
+    int rc = check_warp_desc(d);
+    if (rc) return rc;
+    if (!depth || !T || !params || !noise || !d_num || !d_depth || !d_T || !ws) return VFD_ERR_NULL;
+    if (ws_bytes < vfd_warp_bwd_workspace_bytes(d)) return VFD_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    LossBwdArgs a = {};
+    a.d = *d; a.depth = depth; a.T = T; a.params = params; a.noise = noise; a.d_num = d_num;
+    a.d_depth = d_depth; a.d_T = d_T; a.partial = (float*)ws;
+    const size_t smem = bwd_smem_bytes();
+    // > 48 KB of dynamic shared memory needs the opt-in; setting it is idempotent and per device, so it is simply
+    // repeated on every call (no global state to keep in step with the current device)
+    if (cudaFuncSetAttribute(warp_loss_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return VFD_ERR_CUDA;
+    dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);
+    warp_loss_bwd_kernel<<<grid, kTileThreads, smem, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    warp_dT_reduce_kernel<<<d->B * d->n_call, 128, 0, st>>>(a, (int)(grid.x * grid.y));
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}

@@ -1,0 +1,170 @@
+// Pass 1 of the view-synthesis path: intensity-alignment statistics of every warp
+// (models/geometry/view_rendering.py:30-59: get_mean_std + the early exit of get_norm_image_single).
+//
+// Per (rig, target camera, warp j):  count of pixels with ref_mask*warp_mask != 0, the masked sums of the target
+// and of the warped image, and the UNMASKED sums / sums of squares the reference's variance runs over (:36).
+// Per-thread partial sums are fp32 over a handful of pixels; everything above that (warp, CTA, grid) is fp64, so the
+// one-pass variance  (S2 - 2 m S1 + n m^2) / n  is as accurate as the reference's two-pass form.
+#include "warp_common.cuh"
+
+namespace vfd {
+
+constexpr int kStatThreads = 256;
+constexpr int kStatPx = 8;   // pixels per thread
+
+struct StatsArgs {
+    vfd_warp_desc d;
+    const float* depth;
+    const float* T;
+    double* stats;
+    float* params;
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArgs a) {
+    const vfd_warp_desc& d = a.d;
+    __shared__ WarpCtx ctx;
+    __shared__ double sacc[kMaxW][8];
+    const int b = blockIdx.z, ci = blockIdx.y, cam = d.cam0 + ci;
+    const int W = d.W, H = d.H, HW = H * W;
+    warp_ctx_init(ctx, d, a.T, nullptr, b, ci);
+    for (int i = threadIdx.x; i < kMaxW * 8; i += kStatThreads) (&sacc[0][0])[i] = 0.0;
+    __syncthreads();
+    const int NW = ctx.NW;
+    const int lane = threadIdx.x & 31;
+    const int p0 = blockIdx.x * kStatThreads * kStatPx + threadIdx.x;
+    const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
+    const float* ref = d.color[0] + (size_t)(b * d.num_cams + cam) * 3 * HW;
+    const float* rmask = d.mask + (size_t)(b * d.num_cams + cam) * HW;
+
+    // target image: unmasked sum and sum of squares (shared by all warps of this camera)
+    {
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < kStatPx; ++k) {
+            const int p = p0 + k * kStatThreads;
+            if (p < HW) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float r = __ldg(ref + c * HW + p);
+                    s1 += r;
+                    s2 = fmaf(r, r, s2);
+                }
+            }
+        }
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        if (lane == 0) {
+            atomicAdd(&sacc[0][5], (double)s1);
+            atomicAdd(&sacc[0][6], (double)s2);
+        }
+    }
+    for (int j = 0; j < NW; ++j) {
+        if (!ctx.active[j]) continue;
+        float cnt = 0.f, srm = 0.f, swm = 0.f, sw1 = 0.f, sw2 = 0.f;
+#pragma unroll 2
+        for (int k = 0; k < kStatPx; ++k) {
+            const int p = p0 + k * kStatThreads;
+            if (p >= HW) break;
+            const int u = p % W, v = p / W;
+            float X[3];
+            vfd_backproject(ctx.invK, (float)u, (float)v, __ldg(depth + p), X);
+            const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
+            const bool m = (__ldg(rmask + p) * s.m) != 0.f;   // (src_mask * warp_mask).bool()  (:46)
+            const float w3 = s.v[0] + s.v[1] + s.v[2];
+            sw1 += w3;
+            sw2 += s.v[0] * s.v[0] + s.v[1] * s.v[1] + s.v[2] * s.v[2];
+            if (m) {
+                cnt += 1.f;
+                swm += w3;
+                srm += __ldg(ref + p) + __ldg(ref + HW + p) + __ldg(ref + 2 * HW + p);
+            }
+        }
+        cnt = warp_sum(cnt); srm = warp_sum(srm); swm = warp_sum(swm); sw1 = warp_sum(sw1); sw2 = warp_sum(sw2);
+        if (lane == 0) {
+            atomicAdd(&sacc[j][0], (double)cnt);
+            atomicAdd(&sacc[j][1], (double)srm);
+            atomicAdd(&sacc[j][2], (double)swm);
+            atomicAdd(&sacc[j][3], (double)sw1);
+            atomicAdd(&sacc[j][4], (double)sw2);
+        }
+    }
+    __syncthreads();
+    double* out = a.stats + (size_t)(b * d.n_call + ci) * NW * 8;
+    for (int i = threadIdx.x; i < NW * 8; i += kStatThreads) {
+        const int j = i >> 3, q = i & 7;
+        // the target-image sums were accumulated in row 0; every warp row gets a copy
+        const double v = (q == 5 || q == 6) ? sacc[0][q] : sacc[j][q];
+        if (v != 0.0) atomicAdd(out + i, v);
+    }
+}
+
+// One thread per (target camera, warp): the batch-wide "any sample without overlap" test of :50-53, then the
+// per-sample normalisation parameters.
+__global__ void warp_stats_finalize_kernel(const StatsArgs a) {
+    const vfd_warp_desc& d = a.d;
+    const int NW = warp_count(d);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.n_call * NW) return;
+    const int ci = t / NW, j = t % NW;
+    bool apply = d.intensity_align != 0;
+    for (int b = 0; b < d.B && apply; ++b)
+        if (a.stats[((size_t)(b * d.n_call + ci) * NW + j) * 8] == 0.0) apply = false;
+    const double n = 3.0 * d.H * d.W;
+    for (int b = 0; b < d.B; ++b) {
+        const double* s = a.stats + ((size_t)(b * d.n_call + ci) * NW + j) * 8;
+        float* p = a.params + ((size_t)(b * d.n_call + ci) * NW + j) * 8;
+        const double msum = 3.0 * s[0] + 1e-8;           // mask repeated over 3 channels (:47-48)
+        const double s_mean = (double)(float)(s[1] / msum), w_mean = (double)(float)(s[2] / msum);
+        const double s_var = (s[6] - 2.0 * s_mean * s[5] + n * s_mean * s_mean) / n;
+        const double w_var = (s[4] - 2.0 * w_mean * s[3] + n * w_mean * w_mean) / n;
+        const float s_std = (float)sqrt(fmax(s_var, 0.0) + 1e-16), w_std = (float)sqrt(fmax(w_var, 0.0) + 1e-16);
+        p[0] = (float)w_mean;
+        p[1] = w_std + 1e-8f;
+        p[2] = s_std;
+        p[3] = (float)s_mean;
+        p[4] = apply ? 1.f : 0.f;
+        p[5] = p[6] = p[7] = 0.f;
+    }
+}
+
+int check_warp_desc(const vfd_warp_desc* d) {
+    if (!d) return VFD_ERR_NULL;
+    if (d->B < 1 || d->num_cams < 1 || d->num_cams > VFD_MAX_CAMS || d->H < 2 || d->W < 2) return VFD_ERR_DESC;
+    if (d->n_src < 1 || d->n_src > VFD_WARP_SRC) return VFD_ERR_UNSUPPORTED;
+    if (d->cam0 < 0 || d->n_call < 1 || d->cam0 + d->n_call > d->num_cams) return VFD_ERR_DESC;
+    if ((long)d->H * d->W >= (1L << 30)) return VFD_ERR_DESC;
+    for (int f = 0; f <= d->n_src; ++f)
+        if (!d->color[f]) return VFD_ERR_NULL;
+    if (!d->mask || !d->K || !d->invK) return VFD_ERR_NULL;
+    return VFD_OK;
+}
+
+}  // namespace vfd
+
+using namespace vfd;
+
+extern "C" int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const float* T, double* stats,
+                              float* params, void* stream) {
+    int rc = check_warp_desc(d);
+    if (rc) return rc;
+    if (!depth || !T || !stats || !params) return VFD_ERR_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int NW = d->n_src + (1 + d->n_src) * VFD_WARP_NBR;
+    if (cudaMemsetAsync(stats, 0, (size_t)d->B * d->n_call * NW * 8 * sizeof(double), st) != cudaSuccess)
+        return VFD_ERR_CUDA;
+    StatsArgs a = {*d, depth, T, stats, params};
+    const int HW = d->H * d->W, per = kStatThreads * kStatPx;
+    dim3 grid((HW + per - 1) / per, d->n_call, d->B);
+    warp_stats_kernel<<<grid, kStatThreads, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    const int nt = d->n_call * NW;
+    warp_stats_finalize_kernel<<<(nt + 63) / 64, 64, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}

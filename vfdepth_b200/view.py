@@ -1,0 +1,307 @@
+"""View synthesis + photometric loss on the CUDA kernels: the host-side mirror of
+/root/reference/models/geometry/view_rendering.py (ViewRendering), models/geometry/pose.py:66-96 (relative camera
+poses) and models/losses/{single_cam,multi_cam}_loss.py + loss_util.py (MultiCamLoss), at scale 0.
+
+Three kernels replace the ~1 000 ATen launches per rig of the reference (csrc/warp_stats.cu, warp_loss_fwd.cu,
+warp_loss_bwd.cu): pass 1 warps every source image and reduces the intensity-alignment statistics, pass 2 warps
+again and goes straight to the masked loss sums, the backward re-warps and writes d_depth / d_T.  No warped image
+reaches HBM unless ``materialize`` asks for the ``('color', f, 0)`` / ``('overlap', f, 0)`` views (logger, tests).
+
+There is no CPU path: tensors must be CUDA fp32, the library must load, non-zero status codes raise.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from . import config as vcfg
+from .ops import _chk, _stream
+
+NBR = _lib.VFD_WARP_NBR
+
+
+def num_warps(n_src):
+    return n_src + (1 + n_src) * NBR
+
+
+class WarpInputs:
+    """The rig-level tensors every warp call reads, validated once: colour frames, mask, K, inv_K (scale 0)."""
+
+    def __init__(self, cfg, inputs):
+        t, d = cfg['training'], cfg['data']
+        self.frame_ids = list(t['frame_ids'])
+        self.n_src = len(self.frame_ids) - 1
+        if self.frame_ids[0] != 0 or not 1 <= self.n_src <= _lib.VFD_WARP_SRC:
+            raise NotImplementedError('frame_ids must be [0, f1] or [0, f1, f2]')
+        self.num_cams = d['num_cams']
+        self.H, self.W = t['height'], t['width']
+        self.intensity_align = bool(t.get('intensity_align', True))
+        self.rel = {c: [n for n in d['rel_cam_list'][c]][:NBR] for c in range(self.num_cams)}
+        color0 = inputs[('color', 0, 0)]
+        self.B = color0.shape[0]
+        shp = (self.B, self.num_cams, 3, self.H, self.W)
+        self.color = [_chk(inputs[('color', f, 0)], "inputs['color', %d, 0]" % f, shp) for f in self.frame_ids]
+        mask = inputs['mask']
+        if mask.dtype != torch.float32:
+            mask = mask.float()
+        self.mask = _chk(mask.reshape(self.B, self.num_cams, self.H, self.W), "inputs['mask']")
+        self.K = _chk(inputs[('K', 0)].float().contiguous(), "inputs['K', 0]", (self.B, self.num_cams, 4, 4))
+        self.invK = _chk(inputs[('inv_K', 0)].float().contiguous(), "inputs['inv_K', 0]", (self.B, self.num_cams, 4, 4))
+        self.device = color0.device
+
+    def desc(self, cam0, n_call):
+        d = _lib.WarpDesc()
+        d.B, d.num_cams, d.H, d.W = self.B, self.num_cams, self.H, self.W
+        d.n_src, d.cam0, d.n_call = self.n_src, cam0, n_call
+        d.intensity_align = 1 if self.intensity_align else 0
+        for c in range(_lib.VFD_MAX_CAMS):
+            for k in range(NBR):
+                nb = self.rel.get(c, [])
+                d.nbr[c][k] = nb[k] if k < len(nb) and nb[k] < self.num_cams else -1
+        for i, t in enumerate(self.color):
+            d.color[i] = t.data_ptr()
+        d.mask, d.K, d.invK = self.mask.data_ptr(), self.K.data_ptr(), self.invK.data_ptr()
+        return d
+
+
+def warp_stats(wi, depth, T, cam0=0):
+    """pass 1 -> params [B,n_call,NW,8] (constants for autograd: view_rendering.py:45 runs under no_grad)."""
+    n_call = depth.shape[1]
+    NW = num_warps(wi.n_src)
+    _chk(depth, 'depth', (wi.B, n_call, wi.H, wi.W))
+    _chk(T, 'T', (wi.B, n_call, NW, 4, 4))
+    stats = torch.empty((wi.B, n_call, NW, 8), device=wi.device, dtype=torch.float64)
+    params = torch.empty((wi.B, n_call, NW, 8), device=wi.device, dtype=torch.float32)
+    d = wi.desc(cam0, n_call)
+    _lib.call('vfd_warp_stats', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(stats), _lib.ptr(params),
+              _stream())
+    return params
+
+
+VIEW_KEYS = ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss', 'reproj_mask', 'grid')
+
+
+def _alloc_views(wi, n_call, want):
+    n, H, W, B = wi.n_src, wi.H, wi.W, wi.B
+    shapes = {'color': (B, n_call, n, 3, H, W), 'color_mask': (B, n_call, n, H, W),
+              'overlap': (B, n_call, 1 + n, 3, H, W), 'overlap_mask': (B, n_call, 1 + n, H, W),
+              'reproj_loss': (B, n_call, H, W), 'reproj_mask': (B, n_call, H, W),
+              'grid': (B, n_call, num_warps(n), H, W, 2)}
+    out = {k: torch.empty(shapes[k], device=wi.device, dtype=torch.float32) for k in want}
+    v = _lib.WarpViews()
+    for k, t in out.items():
+        setattr(v, k, t.data_ptr())
+    return v, out
+
+
+class _WarpLoss(torch.autograd.Function):
+    """(depth, T) -> masked-loss numerators [n_call,3] (differentiable) and denominators [n_call,3]."""
+
+    @staticmethod
+    def forward(ctx, depth, T, wi, params, noise, cam0, views_struct):
+        n_call = depth.shape[1]
+        _chk(depth, 'depth', (wi.B, n_call, wi.H, wi.W))
+        _chk(T, 'T', (wi.B, n_call, num_warps(wi.n_src), 4, 4))
+        _chk(noise, 'noise', (wi.B, n_call, wi.n_src, wi.H, wi.W))
+        sums = torch.empty((n_call, 8), device=wi.device, dtype=torch.float64)
+        d = wi.desc(cam0, n_call)
+        vptr = ctypes.byref(views_struct) if views_struct is not None else None
+        _lib.call('vfd_warp_loss_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
+                  _lib.ptr(noise), _lib.ptr(sums), vptr, _stream())
+        ctx.wi, ctx.cam0 = wi, cam0
+        ctx.save_for_backward(depth, T, params, noise)
+        s = sums.float()
+        num, den = s[:, 0:6:2].contiguous(), s[:, 1:6:2].contiguous()
+        ctx.mark_non_differentiable(den)
+        return num, den
+
+    @staticmethod
+    def backward(ctx, d_num, _):
+        depth, T, params, noise = ctx.saved_tensors
+        wi = ctx.wi
+        n_call = depth.shape[1]
+        d = wi.desc(ctx.cam0, n_call)
+        d_num = d_num.float().contiguous()
+        d_depth = torch.empty_like(depth)
+        d_T = torch.empty_like(T)
+        nbytes = _lib.load().vfd_warp_bwd_workspace_bytes(ctypes.byref(d))
+        ws = torch.empty((max(nbytes, 4) // 4,), device=wi.device, dtype=torch.float32)
+        _lib.call('vfd_warp_loss_bwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
+                  _lib.ptr(noise), _lib.ptr(d_num), _lib.ptr(d_depth), _lib.ptr(d_T), _lib.ptr(ws),
+                  ctypes.c_size_t(nbytes), _stream())
+        return d_depth, d_T, None, None, None, None, None
+
+
+def warp_loss_sums(wi, depth, T, noise, cam0=0, params=None, want_views=()):
+    """-> (num [n_call,3], den [n_call,3], views dict).  Columns: reprojection, spatial, spatio-temporal
+    (single_cam_loss.py:55, multi_cam_loss.py:29, :59 are num / (den + 1e-8))."""
+    depth = depth.contiguous()
+    T = T.contiguous()
+    if params is None:
+        params = warp_stats(wi, depth.detach(), T.detach(), cam0)
+    vstruct, views = (None, {})
+    if want_views:
+        vstruct, views = _alloc_views(wi, depth.shape[1], tuple(want_views))
+    num, den = _WarpLoss.apply(depth, T, wi, params, noise, cam0, vstruct)
+    return num, den, views
+
+
+# --------------------------------------------------------------------------------------------------
+# pose plumbing (models/geometry/pose.py:66-96): 4x4 products on [B,4,4] -- stays torch, differentiable
+# --------------------------------------------------------------------------------------------------
+def rig_transforms(wi, inputs, cam_T_cam):
+    """cam_T_cam {f: [B,cams,4,4]} -> T [B,cams,NW,4,4] in the kernel's warp order (include/vfdepth_b200.h):
+    temporal warps first, then for every frame the two neighbours' relative poses ext_inv[nbr] @ ext[cam] (@ T_f)."""
+    E, Einv = inputs['extrinsics'].float(), inputs['extrinsics_inv'].float()
+    B, ncam = wi.B, wi.num_cams
+    eye = torch.eye(4, device=E.device, dtype=E.dtype).expand(B, ncam, 4, 4)
+    cols = [cam_T_cam[f] for f in wi.frame_ids[1:]]
+    rel0 = []
+    for k in range(NBR):
+        idx = [wi.rel[c][k] if k < len(wi.rel[c]) and wi.rel[c][k] < ncam else c for c in range(ncam)]
+        rel0.append(torch.matmul(Einv[:, idx], E))                      # pose.py:81
+    for fi, f in enumerate(wi.frame_ids):
+        for k in range(NBR):
+            cols.append(rel0[k] if fi == 0 else torch.matmul(rel0[k], cam_T_cam[f]))   # pose.py:95
+    del eye
+    return torch.stack(cols, 2)
+
+
+def camera_transforms(wi, target_view, rel_pose_dict, cam):
+    """one camera: T [B,1,NW,4,4] from ('cam_T_cam', 0, f) and the reference's rel_pose_dict."""
+    cols = [target_view[('cam_T_cam', 0, f)] for f in wi.frame_ids[1:]]
+    eye = torch.eye(4, device=wi.device).expand(wi.B, 4, 4)
+    for f in wi.frame_ids:
+        for k in range(NBR):
+            nb = wi.rel[cam][k] if k < len(wi.rel[cam]) else -1
+            cols.append(rel_pose_dict[(f, nb)] if (f, nb) in rel_pose_dict else eye)
+    return torch.stack(cols, 1).unsqueeze(1).float()
+
+
+def smooth_loss(color, disp):
+    """single_cam_loss.py:57-65 + loss_util.py:28-40 (weight 0.001; stays torch)."""
+    mean_disp = disp.mean(2, True).mean(3, True)
+    nd = disp / (mean_disp + 1e-8)
+    grx = (color[:, :, :, :-1] - color[:, :, :, 1:]).abs().mean(1, True)
+    gry = (color[:, :, :-1, :] - color[:, :, 1:, :]).abs().mean(1, True)
+    gdx = (nd[:, :, :, :-1] - nd[:, :, :, 1:]).abs() * (-1.0 * grx).exp()
+    gdy = (nd[:, :, :-1, :] - nd[:, :, 1:, :]).abs() * (-1.0 * gry).exp()
+    return gdx.mean() + gdy.mean()
+
+
+def combine_losses(cfg, num, den, smooth):
+    """per-camera total of multi_cam_loss.py:118-137 from the kernel's sums. num/den [n,3], smooth [n] -> [n]"""
+    L = cfg['loss']
+    terms = num / (den + 1e-8)
+    cam = terms[:, 0] + L['disparity_smoothness'] * smooth
+    cam = cam + (L['spatio_coeff'] * terms[:, 1] + L['spatio_tempo_coeff'] * terms[:, 2])
+    return cam / len(cfg['training']['scales']), terms
+
+
+def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises, want_views=()):
+    """The view-synthesis half of a training step for a whole rig batch in three launches
+    (models/vfdepth.py:290-313: loop over cameras, mean over cameras).
+    depths / disps / noises: list over cameras of [B,1,H,W] / [B,1,H,W] / [B,n_src,H,W]; cam_T_cam {f: [B,cams,4,4]}.
+    -> (total loss, dict(terms [cams,3], cam_loss [cams], views))."""
+    wi = WarpInputs(cfg, inputs)
+    depth = torch.cat(depths, 1)
+    noise = torch.stack(noises, 1)
+    T = rig_transforms(wi, inputs, cam_T_cam)
+    num, den, views = warp_loss_sums(wi, depth, T, noise, 0, None, want_views)
+    color0 = inputs[('color', 0, 0)]
+    sm = torch.stack([smooth_loss(color0[:, c], disps[c]) for c in range(wi.num_cams)])
+    cam_loss, terms = combine_losses(cfg, num, den, sm)
+    return cam_loss.sum() / wi.num_cams, dict(terms=terms, cam_loss=cam_loss, smooth=sm, views=views, T=T)
+
+
+# --------------------------------------------------------------------------------------------------
+# drop-in modules with the reference's constructor / forward signatures
+# --------------------------------------------------------------------------------------------------
+_CTX = '_vfd_warp'      # private key in outputs[('cam', cam)] that hands pass-1 results to the loss module
+
+
+class ViewRendering(torch.nn.Module):
+    """Drop-in for models/geometry/view_rendering.py:8 (``ViewRendering(cfg, rank)``;
+    ``forward(inputs, outputs, cam, rel_pose_dict)`` mutating ``outputs[('cam', cam)]``).
+
+    ``forward`` runs pass 1 (statistics) for the camera and leaves the warp context for ``MultiCamLoss``; the
+    reference's image keys ``('color', f, s)``, ``('color_mask', f, s)``, ``('overlap', f, s)``,
+    ``('overlap_mask', f, s)`` are written only when ``materialize`` is true (the reference's logger reads them at
+    checkpoints only, utils/logger.py:120-170) -- they are non-differentiable copies; gradients flow through the
+    fused loss."""
+
+    def __init__(self, cfg, rank, materialize=False):
+        super().__init__()
+        vcfg.flatten_into(self, cfg)
+        self.cfg, self.rank, self.materialize = cfg, rank, materialize
+        if getattr(self, 'aug_depth', False):
+            raise NotImplementedError('aug_depth (view_rendering.py:201-241) is outside the hot path')
+        if list(self.scales) != [0]:
+            raise NotImplementedError('only scales == [0] (all reference configs)')
+
+    def forward(self, inputs, outputs, cam, rel_pose_dict):
+        wi = inputs.get(_CTX)
+        if wi is None or wi.color[0].data_ptr() != inputs[('color', 0, 0)].data_ptr():
+            wi = inputs[_CTX] = WarpInputs(self.cfg, inputs)
+        tv = outputs[('cam', cam)]
+        depth = tv[('depth', 0)].reshape(wi.B, 1, wi.H, wi.W)
+        T = camera_transforms(wi, tv, rel_pose_dict, cam)
+        params = warp_stats(wi, depth.detach().contiguous(), T.detach().contiguous(), cam)
+        tv[_CTX] = dict(wi=wi, depth=depth, T=T, params=params)
+        if self.materialize:
+            self.render(inputs, outputs, cam)
+
+    @torch.no_grad()
+    def render(self, inputs, outputs, cam):
+        """write the reference's image keys for camera ``cam`` (on demand)."""
+        tv = outputs[('cam', cam)]
+        c = tv[_CTX]
+        wi = c['wi']
+        noise = torch.zeros((wi.B, 1, wi.n_src, wi.H, wi.W), device=wi.device)
+        _, _, v = warp_loss_sums(wi, c['depth'].detach(), c['T'].detach(), noise, cam, c['params'],
+                                 ('color', 'color_mask', 'overlap', 'overlap_mask'))
+        for k, f in enumerate(wi.frame_ids[1:]):
+            tv[('color', f, 0)] = v['color'][:, 0, k]
+            tv[('color_mask', f, 0)] = v['color_mask'][:, 0, k:k + 1]
+        for k, f in enumerate(wi.frame_ids):
+            tv[('overlap', f, 0)] = v['overlap'][:, 0, k]
+            tv[('overlap_mask', f, 0)] = v['overlap_mask'][:, 0, k:k + 1]
+
+
+class MultiCamLoss(torch.nn.Module):
+    """Drop-in for models/losses/multi_cam_loss.py:9 (``MultiCamLoss(cfg, rank)``; ``forward(inputs, outputs, cam)``
+    -> ``(cam_loss, loss_dict)``), pose_model == 'fusion' (no pose-consistency term, multi_cam_loss.py:113)."""
+
+    def __init__(self, cfg, rank):
+        super().__init__()
+        self.cfg, self.rank = cfg, rank
+        for k, v in cfg['loss'].items():
+            setattr(self, k, v)
+        self.scales, self.frame_ids = cfg['training']['scales'], cfg['training']['frame_ids']
+        self.pose_model = cfg['model'].get('pose_model', 'fusion')
+        if self.pose_model == 'fsm':
+            raise NotImplementedError('FSM pose-consistency loss (multi_cam_loss.py:61-92) is outside the hot path')
+
+    def forward(self, inputs, outputs, cam):
+        tv = outputs[('cam', cam)]
+        c = tv[_CTX]
+        wi = c['wi']
+        # the reference draws the tie-break noise on the CPU and ships it (single_cam_loss.py:45-46)
+        noise = torch.randn((wi.B, wi.n_src, wi.H, wi.W)).to(wi.device).unsqueeze(1)
+        num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['params'], ('reproj_loss', 'reproj_mask'))
+        tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
+        tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
+        sm = smooth_loss(inputs[('color', 0, 0)][:, cam], tv[('disp', 0)])
+        cam_loss, terms = combine_losses(self.cfg, num, den, sm.reshape(1))
+        t = terms[0].detach().cpu()
+        loss_dict = {'reproj_loss': float(t[0]), 'spatio_loss': float(t[1]), 'spatio_tempo_loss': float(t[2]),
+                     'smooth': float(sm.detach())}
+        depth_log = tv[('depth', 0)].detach()           # base_loss.py:29-33
+        loss_dict['depth/mean'], loss_dict['depth/max'], loss_dict['depth/min'] = \
+            depth_log.mean(), depth_log.max(), depth_log.min()
+        if cam == 0:
+            pose_t = tv[('cam_T_cam', 0, -1)].detach() if ('cam_T_cam', 0, -1) in tv else None
+            if pose_t is not None:
+                for i, n in enumerate(('pose/tx', 'pose/ty', 'pose/tz')):
+                    loss_dict[n] = pose_t[:, i, 3].abs().mean()
+        return cam_loss[0], loss_dict
