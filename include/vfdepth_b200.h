@@ -139,6 +139,8 @@ typedef struct vfd_warp_views {
     float* reproj_loss;  /* [B,n_call,H,W]            ('reproj_loss', 0)    single_cam_loss.py:53 */
     float* reproj_mask;  /* [B,n_call,H,W]            ('reproj_mask', 0)    :54 */
     float* grid;         /* [B,n_call,NW,H,W,2]  normalised sampling coordinates (geometry_util.py:62-77), bit-exact */
+    float* selection;    /* [B,n_call,H,W]  which frame won the two torch.min over frames: (reprojection index)
+                            + 2 * (spatio-temporal index)  (single_cam_loss.py:30, multi_cam_loss.py:56) */
 } vfd_warp_views;
 
 /* Pass 1 -- intensity-alignment statistics (view_rendering.py:30-59) of every warp.

@@ -357,10 +357,14 @@ def edge_smooth_loss(rgb, disp):
     return gdx.mean() + gdy.mean()
 
 
-def multi_cam_loss(cfg, inputs, view, disp, cam, noise):
+def multi_cam_loss(cfg, inputs, view, disp, cam, noise, decisions=None):
     """One camera of MultiCamLoss.forward (multi_cam_loss.py:94-138, scale 0, pose_model='fusion').
     ``noise`` [B,2,H,W] is the CPU-drawn ``torch.randn`` of single_cam_loss.py:45-46, passed in so
-    that every implementation sees the same draw.  -> (cam_loss, detail dict)."""
+    that every implementation sees the same draw.  -> (cam_loss, detail dict).
+
+    ``decisions`` (tests only) pins the three per-pixel hard decisions to given values instead of taking them from
+    this run's own fp32 comparisons: dict(reproj_mask [B,1,H,W] float = auto-mask * ref_mask, sel_reproj / sel_st
+    [B,1,H,W] long = the frame each torch.min picked).  Everything else is computed exactly as without it."""
     t, L = cfg['training'], cfg['loss']
     target = inputs[('color', 0, 0)][:, cam]
     ref_mask = inputs['mask'][:, cam]
@@ -368,11 +372,15 @@ def multi_cam_loss(cfg, inputs, view, disp, cam, noise):
     # single_cam_loss.py:17-55
     reproj_all = torch.cat([photometric_loss(view[('color', f)], target) for f in fr], 1)
     reproj, _ = torch.min(reproj_all, dim=1, keepdim=True)
+    if decisions is not None:
+        reproj = torch.gather(reproj_all, 1, decisions['sel_reproj'])
     ident_all = torch.cat([photometric_loss(inputs[('color', f, 0)][:, cam], target) for f in fr], 1)
     ident_all = ident_all + 0.00001 * noise
     ident, _ = torch.min(ident_all, dim=1, keepdim=True)
     idx = torch.argmin(torch.cat([reproj, ident], dim=1), dim=1, keepdim=True)
     auto = (idx == 0).float() * ref_mask
+    if decisions is not None:
+        auto = decisions['reproj_mask'].to(reproj.dtype)
     reproj_loss = masked_loss(reproj, auto)
     smooth = edge_smooth_loss(target, disp)
     # multi_cam_loss.py:16-29
@@ -383,6 +391,8 @@ def multi_cam_loss(cfg, inputs, view, disp, cam, noise):
     st_maps = torch.cat([photometric_loss(view[('overlap', f)], target) for f in fr], 1)
     st_masks = torch.cat([ref_mask * view[('overlap_mask', f)] * auto for f in fr], 1)
     st_map, _ = torch.min(st_maps, dim=1, keepdim=True)
+    if decisions is not None:
+        st_map = torch.gather(st_maps, 1, decisions['sel_st'])
     st_mask, _ = torch.max(st_masks.float(), dim=1, keepdim=True)
     spatio_tempo = masked_loss(st_map, st_mask)
     # accumulation order of multi_cam_loss.py:118-121
@@ -394,10 +404,16 @@ def multi_cam_loss(cfg, inputs, view, disp, cam, noise):
     cam_loss /= len(t['scales'])
     detail = dict(reproj_loss=reproj_loss, smooth=smooth, spatio_loss=spatio, spatio_tempo_loss=spatio_tempo,
                   reproj_mask=auto, reproj_map=auto * reproj, spatio_mask=sp_mask, spatio_tempo_mask=st_mask)
+    # decisions and their margins (how far each comparison is from flipping), for the parity tests
+    with torch.no_grad():
+        big = torch.full_like(reproj, 1e30)
+        gap = lambda x: (x[:, 0:1] - x[:, 1:2]).abs() if x.shape[1] > 1 else big
+        detail.update(sel_reproj=torch.argmin(reproj_all, 1, keepdim=True), sel_st=torch.argmin(st_maps, 1, keepdim=True),
+                      margin_auto=(reproj - ident).abs(), margin_reproj=gap(reproj_all), margin_st=gap(st_maps))
     return cam_loss, detail
 
 
-def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises):
+def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises, decisions=None):
     """The view-synthesis half of a training step for a whole rig batch:
     models/vfdepth.py:290-313 (loop over cameras, mean over cameras).
     depths/disps/noises: list over cameras; cam_T_cam {f: [B,6,4,4]}."""
@@ -406,7 +422,8 @@ def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises):
     for cam in range(cfg['data']['num_cams']):
         T = {f: cam_T_cam[f][:, cam] for f in cfg['training']['frame_ids'][1:]}
         view = view_rendering(cfg, inputs, depths[cam], T, cam)
-        loss, det = multi_cam_loss(cfg, inputs, view, disps[cam], cam, noises[cam])
+        loss, det = multi_cam_loss(cfg, inputs, view, disps[cam], cam, noises[cam],
+                                   None if decisions is None else decisions[cam])
         det['view'] = view
         details.append(det)
         total = total + loss

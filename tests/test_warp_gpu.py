@@ -1,0 +1,266 @@
+"""GPU parity of the view-synthesis warp + SSIM/L1 photometric loss kernels (forward and backward) through the
+C ABI, against (1) the committed fixture produced by running the reference itself and (2) the oracle.
+
+Bars.  Sampling coordinates and warp masks: BIT-EXACT.  Warped / normalised images, loss maps, loss terms, totals:
+1e-4 of the tensor's scale (fp32; the north star's tolerance).  The loss takes three hard decisions per pixel
+(auto-mask argmin, and two min-over-frames); SSIM in fp32 amplifies a 1-ulp difference of the warped image to ~5e-5
+of the loss map, so a handful of pixels whose decision margin is below that flip between ANY two fp32
+implementations (the reference on CPU vs the reference on CUDA included).  The tests therefore require: decisions
+identical except at pixels whose oracle margin is < 1e-3 and those are < 2e-4 of all pixels; per-pixel gradients
+within tolerance everywhere outside the 5x5 footprint of a flipped pixel; and, in a configuration with no decisions
+(one source frame, auto-mask forced on), every gradient including d_T within tolerance -- where the oracle run in
+fp64 arbitrates when the fp32 oracle itself is further than 1e-4 from it."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import vfdepth_oracle as orc
+from tests import helpers as H
+from vfdepth_b200 import config as vcfg
+from vfdepth_b200.rig import make_rig
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    return torch.device('cuda:0')
+
+
+def _golden():
+    g = H.load_npz('golden_warp.npz')
+    cfg = H.warp_cfg()
+    return cfg, H.warp_inputs(g), dict(depth=[g['depth'][:, c] for c in range(6)], disp=[g['disp'][:, c] for c in range(6)],
+                                       noise=[g['noise'][:, c] for c in range(6)],
+                                       cam_T_cam={-1: g['T_m1'], 1: g['T_p1']}), g
+
+
+def _rig(height, width, batch, seed, **over):
+    cfg = vcfg.default_config('ddad', batch_size=batch, training__height=height, training__width=width,
+                              training__focal_length_scale=300 * width / 640, **over)
+    inp, ex = make_rig(cfg, seed=seed, with_feats=False)
+    return cfg, inp, ex
+
+
+def _run_gpu(cfg, inp, ex, dev, views=()):
+    from vfdepth_b200 import view
+    to = lambda t: t.to(dev)
+    inp_d = {k: to(v) for k, v in inp.items()}
+    depths = [to(d).requires_grad_(True) for d in ex['depth']]
+    Ts = {f: to(t).requires_grad_(True) for f, t in ex['cam_T_cam'].items()}
+    total, det = view.warp_and_loss(cfg, inp_d, depths, [to(d) for d in ex['disp']], Ts, [to(n) for n in ex['noise']],
+                                    want_views=views)
+    fr = cfg['training']['frame_ids'][1:]
+    grads = torch.autograd.grad(total, depths + [Ts[f] for f in fr])
+    return total.detach().cpu(), det, [g.cpu() for g in grads]
+
+
+def _run_oracle(cfg, inp, ex, dtype=torch.float32, decisions=None):
+    cv = lambda t: t.to(dtype) if t.is_floating_point() else t
+    inp = {k: cv(v) for k, v in inp.items()}
+    depths = [cv(d).clone().requires_grad_(True) for d in ex['depth']]
+    Ts = {f: cv(t).clone().requires_grad_(True) for f, t in ex['cam_T_cam'].items()}
+    total, det = orc.warp_and_loss(cfg, inp, depths, [cv(d) for d in ex['disp']], Ts, [cv(n) for n in ex['noise']],
+                                   decisions)
+    fr = cfg['training']['frame_ids'][1:]
+    grads = torch.autograd.grad(total, depths + [Ts[f] for f in fr])
+    return total.detach(), det, list(grads)
+
+
+def _gpu_decisions(det, cfg):
+    """the kernel's own per-pixel decisions, in the form oracle.multi_cam_loss(decisions=...) pins them"""
+    n_src = len(cfg['training']['frame_ids']) - 1
+    out = []
+    for cam in range(cfg['data']['num_cams']):
+        auto, sr, st = _decisions(det, cam, n_src)
+        out.append(dict(reproj_mask=auto, sel_reproj=sr, sel_st=st))
+    return out
+
+
+def _decisions(det, cam, n_src):
+    """(auto-mask, reprojection argmin, spatio-temporal argmin) of one camera from GPU views or oracle details."""
+    if isinstance(det, dict):       # GPU: det['views']
+        v = det['views']
+        sel = v['selection'][:, cam:cam + 1].cpu().long()
+        return v['reproj_mask'][:, cam:cam + 1].cpu().float(), sel % 2, sel // 2
+    r = det[cam]
+    z = torch.zeros_like(r['sel_reproj'])
+    return r['reproj_mask'].float(), (r['sel_reproj'] if n_src > 1 else z), (r['sel_st'] if n_src > 1 else z)
+
+
+def _flip_footprint(det_a, det_ref, cfg):
+    """-> (bool [B,cams,H,W] pixels within the 5x5 footprint of a decision on which ``det_a`` and the fp32 oracle
+    differ, number of flipped pixels, largest fp32-oracle margin among the flipped decisions)."""
+    ncam = cfg['data']['num_cams']
+    n_src = len(cfg['training']['frame_ids']) - 1
+    flips, worst = [], 0.0
+    for cam in range(ncam):
+        r = det_ref[cam]
+        da, dr = _decisions(det_a, cam, n_src), _decisions(det_ref, cam, n_src)
+        fl = torch.zeros_like(dr[0], dtype=torch.bool)
+        for x, y, m in zip(da, dr, (r['margin_auto'], r['margin_reproj'], r['margin_st'])):
+            f = x != y
+            if f.any():
+                worst = max(worst, float(m.float()[f].max()))
+            fl |= f
+        flips.append(fl)
+    flips = torch.cat(flips, 1)
+    foot = F.max_pool2d(flips.float(), 5, 1, 2) > 0
+    return foot, int(flips.sum()), worst
+
+
+def _arbitrated(got, ref32, ref64, keep=None):
+    """error of ``got`` against the fp64 oracle, and the bar: 1e-4, or twice the fp32 oracle's own error if larger."""
+    scale = ref64.abs().max().clamp_min(1e-30)
+    e_got, e_ref = (got.double() - ref64).abs() / scale, (ref32.double() - ref64).abs() / scale
+    if keep is not None:
+        e_got, e_ref = e_got[keep], e_ref[keep]
+    return float(e_got.max()), max(TOL, 2 * float(e_ref.max()))
+
+
+def _check_views(cfg, det_gpu, det_ref, cams, tol=TOL):
+    v = det_gpu['views']
+    fr = cfg['training']['frame_ids']
+    for cam in cams:
+        rv = det_ref[cam]['view']
+        for k, f in enumerate(fr[1:]):
+            assert H.rel_err(v['color'][:, cam, k].cpu(), rv[('color', f)].detach()) < tol
+            assert torch.equal(v['color_mask'][:, cam, k:k + 1].cpu(), rv[('color_mask', f)])
+        for k, f in enumerate(fr):
+            assert H.rel_err(v['overlap'][:, cam, k].cpu(), rv[('overlap', f)].detach()) < tol
+            assert torch.equal(v['overlap_mask'][:, cam, k:k + 1].cpu(), rv[('overlap_mask', f)])
+
+
+ALL_VIEWS = ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss', 'reproj_mask', 'grid', 'selection')
+
+
+def test_golden_warp_forward():
+    """images and masks against what the reference's own ViewRendering / MultiCamLoss produced (48x64, B=2)."""
+    dev = _dev()
+    cfg, inp, ex, g = _golden()
+    total, det, _ = _run_gpu(cfg, inp, ex, dev, ALL_VIEWS)
+    v = det['views']
+    for cam in (0, 3):
+        for k, f in enumerate((-1, 1)):
+            assert H.rel_err(v['color'][:, cam, k].cpu(), g['cam%d_color_%d' % (cam, f)]) < TOL
+            assert torch.equal(v['color_mask'][:, cam, k:k + 1].cpu(), g['cam%d_color_mask_%d' % (cam, f)])
+        for k, f in enumerate((0, -1, 1)):
+            assert H.rel_err(v['overlap'][:, cam, k].cpu(), g['cam%d_overlap_%d' % (cam, f)]) < TOL
+        for k, f in enumerate((-1, 1)):
+            assert torch.equal(v['overlap_mask'][:, cam, 1 + k:2 + k].cpu(), g['cam%d_overlap_mask_%d' % (cam, f)])
+        # compute_spatio_loss overwrote ('overlap_mask', 0) with ref_mask * overlap_mask (multi_cam_loss.py:28)
+        assert torch.equal((v['overlap_mask'][:, cam, 0:1].cpu() * inp['mask'][:, cam]), g['cam%d_overlap_mask_0' % cam])
+        # auto-mask: identical except for fp32 near-ties (at most a few pixels of 6144)
+        assert int((v['reproj_mask'][:, cam:cam + 1].cpu() != g['cam%d_reproj_mask' % cam]).sum()) <= 3
+    # tiny images: one flipped pixel of 6144 moves a term by ~1e-4, so the loss bars are looser here than at full size
+    ref_terms = g['cam_scalars'][:, :3].float()
+    assert float(((det['terms'].cpu() - ref_terms).abs() / ref_terms.abs()).max()) < 2e-3
+    assert abs(float(total) - float(g['total'])) / float(g['total']) < 3e-4
+
+
+def test_sampling_grid_bit_exact():
+    """every warp's normalised sampling coordinate equals Projection.forward's (geometry_util.py:52-82) bit for bit"""
+    dev = _dev()
+    cfg, inp, ex = _rig(96, 160, 2, seed=41)
+    _, det, _ = _run_gpu(cfg, inp, ex, dev, ('grid',))
+    grid = det['views']['grid'].cpu()
+    T = det['T'].detach().cpu()
+    rel = cfg['data']['rel_cam_list']
+    for cam in range(6):
+        srcs = [cam, cam] + [rel[cam][k] for _ in range(3) for k in range(2)]
+        for j, src in enumerate(srcs):
+            ref = orc.reproject_grid(ex['depth'][cam], T[:, cam, j], inp[('inv_K', 0)][:, cam], inp[('K', 0)][:, src])
+            assert torch.equal(grid[:, cam, j], ref), (cam, j)
+
+
+def _terms(det_ref):
+    return torch.tensor([[float(det_ref[c][k]) for k in ('reproj_loss', 'spatio_loss', 'spatio_tempo_loss')]
+                         for c in range(6)], dtype=torch.float64)
+
+
+def _standard_case(dev, height, width, batch, seed):
+    """The reference's own configuration (3 frames, spatio + spatio-temporal, intensity alignment).
+    1. against the plain fp32 oracle: images within tolerance, masks bit-exact, the three per-pixel decisions identical
+       except at near-ties (few, and each with a tiny oracle margin);
+    2. against the oracle PINNED to the kernel's decisions (fp32 and fp64): loss map, loss terms, total and every
+       gradient (6 depth maps, 2 x [B,6,4,4] poses) within tolerance at every pixel -- no exclusions."""
+    cfg, inp, ex = _rig(height, width, batch, seed)
+    total, det, grads = _run_gpu(cfg, inp, ex, dev, ALL_VIEWS)
+    t32, d32, g32 = _run_oracle(cfg, inp, ex)
+    _check_views(cfg, det, d32, range(6))
+    npix = batch * 6 * height * width
+    _, nflip, worst = _flip_footprint(det, d32, cfg)
+    assert nflip <= max(3, 2e-4 * npix), nflip
+    assert worst < 1e-3, worst                      # only near-ties flip
+    dec = _gpu_decisions(det, cfg)
+    p32 = _run_oracle(cfg, inp, ex, torch.float32, dec)
+    p64 = _run_oracle(cfg, inp, ex, torch.float64, dec)
+    assert abs(float(total) - float(p64[0])) / float(p64[0]) < TOL
+    e, bar = _arbitrated(det['terms'].cpu(), _terms(p32[1]), _terms(p64[1]))
+    assert e <= bar, ('terms', e, bar)
+    for cam in range(6):
+        e, bar = _arbitrated(det['views']['reproj_loss'][:, cam:cam + 1].cpu(), p32[1][cam]['reproj_map'].detach(),
+                             p64[1][cam]['reproj_map'].detach())
+        assert e <= 2 * bar, ('reproj_map', cam, e, bar)     # SSIM amplifies 1 ulp of the image to ~5e-5 of the map
+    for i in range(len(grads)):
+        e, bar = _arbitrated(grads[i], p32[2][i], p64[2][i])
+        assert e <= bar, ('gradient', i, e, bar)
+    return nflip, npix
+
+
+def test_oracle_midsize_standard_config():
+    _standard_case(_dev(), 96, 160, 2, seed=99)
+
+
+def test_full_size_standard_config():
+    """BASELINE configs[2] size: 6 cameras x 3 frames at 384x640."""
+    _standard_case(_dev(), 384, 640, 1, seed=123)
+
+
+def test_gradients_without_decisions():
+    """one source frame (no min over frames) and the auto-mask forced on by a huge tie-break noise: no decision can
+    flip, so EVERY gradient -- d_depth at every pixel and d_T through the pose chain -- must meet the bar."""
+    dev = _dev()
+    cfg, inp, ex = _rig(96, 160, 2, seed=7, training__frame_ids=[0, -1])
+    ex['noise'] = [torch.full((2, 1, 96, 160), 1e9) for _ in range(6)]
+    total, det, grads = _run_gpu(cfg, inp, ex, dev, ALL_VIEWS)
+    t32, d32, g32 = _run_oracle(cfg, inp, ex)
+    t64, d64, g64 = _run_oracle(cfg, inp, ex, torch.float64)
+    _, nflip, _ = _flip_footprint(det, d32, cfg)
+    assert nflip == 0
+    assert abs(float(total) - float(t32)) / float(t32) < TOL
+    for i in range(7):
+        e, bar = _arbitrated(grads[i], g32[i], g64[i])
+        assert e <= bar, (i, e, bar)
+
+
+def test_backward_is_deterministic():
+    dev = _dev()
+    cfg, inp, ex = _rig(96, 160, 2, seed=3)
+    a = _run_gpu(cfg, inp, ex, dev)
+    b = _run_gpu(cfg, inp, ex, dev)
+    assert torch.equal(a[0], b[0])
+    for x, y in zip(a[2], b[2]):
+        assert torch.equal(x, y)
+
+
+def test_no_intensity_align_and_early_exit():
+    """intensity_align off, and the batch-wide early exit of view_rendering.py:50-53 (a sample whose warp has no
+    overlap -> the WHOLE batch keeps the raw, unmasked warp for that warp index)."""
+    dev = _dev()
+    cfg, inp, ex = _rig(64, 96, 2, seed=11, training__intensity_align=False)
+    total, det, _ = _run_gpu(cfg, inp, ex, dev, ALL_VIEWS)
+    t32, d32, _ = _run_oracle(cfg, inp, ex)
+    _check_views(cfg, det, d32, range(6))
+    assert abs(float(total) - float(t32)) / float(t32) < 3e-4
+    cfg, inp, ex = _rig(64, 96, 2, seed=12)
+    # throw camera 2 of sample 1 far away at frame -1: its temporal warp and the spatio-temporal warps INTO its
+    # neighbours' views land out of bounds -> zero overlap for that sample only
+    ex['cam_T_cam'][-1][1, 2, :3, 3] += torch.tensor([500.0, 0.0, 0.0])
+    total, det, _ = _run_gpu(cfg, inp, ex, dev, ALL_VIEWS)
+    t32, d32, _ = _run_oracle(cfg, inp, ex)
+    assert float(det['views']['color_mask'][1, 2, 0].sum()) == 0.0      # the exit really fires
+    _check_views(cfg, det, d32, range(6))
+    assert abs(float(total) - float(t32)) / float(t32) < 3e-4

@@ -1,5 +1,3 @@
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest.log 2>&1; echo "pytest rc=$?" > gpurun_out/rc.log
-python tools/kernel_bench.py > gpurun_out/kb.log 2>&1; echo "kb rc=$?" >> gpurun_out/rc.log
-python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.log
-python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu1.log 2>&1; echo "ncu1 rc=$?" >> gpurun_out/rc.log
-python tools/kernel_bench.py --iters 1 --warmup 0 --only gather_fwd,gather_bwd,ray_fwd,ray_bwd > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:'voxel_gather|ray_sample' -c 6 -o gpurun_out/prof_r1a python tools/kernel_bench.py --iters 1 --warmup 0 --only gather_fwd,gather_bwd,ray_fwd,ray_bwd > gpurun_out/ncu2.log 2>&1; echo "ncu2 rc=$?" >> gpurun_out/rc.log
+python -m pytest tests/test_warp_gpu.py -x -q > gpurun_out/pytest_warp.log 2>&1; echo "pytest_warp rc=$?" > gpurun_out/rc.log
+python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/rc.log
+python bench.py --steps 5 --no-cpu-baseline > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.log

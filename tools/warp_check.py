@@ -65,6 +65,11 @@ def main():
     tot_ref, det_ref = orc.warp_and_loss(cfg, inp, d_ref, disps, T_ref, noises)
     g_ref = torch.autograd.grad(tot_ref, d_ref + [T_ref[f] for f in sorted(T_ref)])
     total, det, grads = run(cfg, inp, depths, disps, Ts, noises, dev)
+    from vfdepth_b200 import _lib
+    _lib.start_event_trace()
+    for _ in range(3):
+        run(cfg, inp, depths, disps, Ts, noises, dev)
+    print('kernel ms (3 runs):', _lib.stop_event_trace())
     print('total', float(total), float(tot_ref), 'rel', abs(float(total) - float(tot_ref)) / abs(float(tot_ref)))
     for cam in range(6):
         r = det_ref[cam]

@@ -49,7 +49,7 @@ class WarpDesc(ctypes.Structure):
 class WarpViews(ctypes.Structure):
     """struct vfd_warp_views"""
     _fields_ = [(n, ctypes.c_void_p) for n in ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss',
-                                               'reproj_mask', 'grid')]
+                                               'reproj_mask', 'grid', 'selection')]
 
 
 _lock = threading.Lock()

@@ -1,0 +1,62 @@
+"""Workload of bench.py's view-synthesis half: 6 cameras x 3 frames warp + SSIM/L1 photometric loss, forward and
+backward to the 6 depth maps and the 12 cam_T_cam (BASELINE.json configs[2]), on synthetic DDAD-shaped rigs."""
+import torch
+
+from . import config as vcfg
+from . import view
+from .rig import make_rig
+
+
+class WarpWorkload:
+    def __init__(self, batch, dev, seed, dataset='ddad'):
+        self.cfg = vcfg.default_config(dataset, batch_size=batch)
+        self.dev, self.B = dev, batch
+        inputs, ex = make_rig(self.cfg, seed=seed, with_feats=False)
+        t = self.cfg['training']
+        self.H, self.W, self.frames = t['height'], t['width'], t['frame_ids']
+        pin = lambda x: x.contiguous().pin_memory()
+        keys = [('color', f, 0) for f in self.frames] + ['mask', ('K', 0), ('inv_K', 0), 'extrinsics', 'extrinsics_inv']
+        self.h_inputs = {k: pin(inputs[k]) for k in keys}
+        self.h_depth = pin(torch.cat(ex['depth'], 1))                 # [B,6,H,W]
+        self.h_disp = pin(torch.cat(ex['disp'], 1))
+        self.h_noise = pin(torch.stack(ex['noise'], 1))               # [B,6,2,H,W]
+        self.h_T = {f: pin(ex['cam_T_cam'][f]) for f in self.frames[1:]}
+        self.h_out = torch.empty((batch, 6, self.H, self.W)).pin_memory()
+        self.h_loss = torch.zeros(1).pin_memory()
+        self.inputs = {k: v.to(dev) for k, v in self.h_inputs.items()}
+        self.depth, self.disp, self.noise = self.h_depth.to(dev), self.h_disp.to(dev), self.h_noise.to(dev)
+        self.T = {f: v.to(dev) for f, v in self.h_T.items()}
+
+    def step(self, inputs, depth, disp, noise, T):
+        n = self.cfg['data']['num_cams']
+        depths = [depth[:, c:c + 1].detach().requires_grad_(True) for c in range(n)]
+        Ts = {f: t.detach().requires_grad_(True) for f, t in T.items()}
+        total, _ = view.warp_and_loss(self.cfg, inputs, depths, [disp[:, c:c + 1] for c in range(n)], Ts,
+                                      [noise[:, c] for c in range(n)])
+        grads = torch.autograd.grad(total, depths + list(Ts.values()))
+        return total, grads
+
+    def step_resident(self):
+        return self.step(self.inputs, self.depth, self.disp, self.noise, self.T)
+
+    def step_e2e(self):
+        nb = dict(non_blocking=True)
+        inputs = {k: v.to(self.dev, **nb) for k, v in self.h_inputs.items()}
+        total, grads = self.step(inputs, self.h_depth.to(self.dev, **nb), self.h_disp.to(self.dev, **nb),
+                                 self.h_noise.to(self.dev, **nb), {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
+        self.h_out.copy_(torch.cat(grads[:6], 1), non_blocking=True)
+        self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
+
+    def h2d_bytes(self):
+        ts = list(self.h_inputs.values()) + [self.h_depth, self.h_disp, self.h_noise] + list(self.h_T.values())
+        return sum(t.numel() * t.element_size() for t in ts)
+
+    def d2h_bytes(self):
+        return self.h_out.numel() * 4 + 4
+
+    def algorithmic_bytes(self):
+        """per launch: unique inputs read once + required outputs written once."""
+        px = self.B * 6 * self.H * self.W * 4
+        imgs, depth, mask, noise = 3 * 3 * px, px, px, 2 * px
+        return {'vfd_warp_stats': imgs + depth + mask, 'vfd_warp_loss_fwd': imgs + depth + mask + noise,
+                'vfd_warp_loss_bwd': imgs + depth + mask + noise + px}

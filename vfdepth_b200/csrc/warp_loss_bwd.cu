@@ -187,9 +187,15 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossB
                 const float dc0 = gix * inv, dc1 = giy * inv;
                 const float dc2 = -(gix * s.cam[0] + giy * s.cam[1]) * inv * inv;
                 const float* P = ctx.P[j];
-                gdepth += dc0 * (P[0] * ray[0] + P[1] * ray[1] + P[2] * ray[2]) +
-                          dc1 * (P[4] * ray[0] + P[5] * ray[1] + P[6] * ray[2]) +
-                          dc2 * (P[8] * ray[0] + P[9] * ray[1] + P[10] * ray[2]);
+                // d(ix)/d(depth) = (a0 * den - cam.x * a2) / den^2 with a = P[:, :3] @ ray, cam = depth * a + P[:, 3].
+                // The depth-proportional parts cancel EXACTLY in that numerator (a pure rotation moves no pixel when
+                // depth changes); written as below the fp32 result keeps ~7 digits even when depth*|a| >> |t|, where
+                // the chain-rule form loses 2-3 of them.
+                const float a0 = P[0] * ray[0] + P[1] * ray[1] + P[2] * ray[2];
+                const float a1 = P[4] * ray[0] + P[5] * ray[1] + P[6] * ray[2];
+                const float a2 = P[8] * ray[0] + P[9] * ray[1] + P[10] * ray[2];
+                const float t2 = P[11] + 1e-7f;
+                gdepth += (gix * (a0 * t2 - P[3] * a2) + giy * (a1 * t2 - P[7] * a2)) * inv * inv;
                 const float dc[3] = {dc0, dc1, dc2};
 #pragma unroll
                 for (int rr = 0; rr < 3; ++rr) {

@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_fwd_kernel(const LossF
             }
             if (v.reproj_loss) v.reproj_loss[bc * HW + p] = acc[0];
             if (v.reproj_mask) v.reproj_mask[bc * HW + p] = o.automask;
+            if (v.selection) v.selection[bc * HW + p] = (float)(o.sel_reproj + 2 * o.sel_st);
             if (v.grid) {
                 float X[3];
                 vfd_backproject(ctx.invK, (float)x, (float)y, __ldg(depth + p), X);

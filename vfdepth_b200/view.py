@@ -78,7 +78,7 @@ def warp_stats(wi, depth, T, cam0=0):
     return params
 
 
-VIEW_KEYS = ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss', 'reproj_mask', 'grid')
+VIEW_KEYS = ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss', 'reproj_mask', 'grid', 'selection')
 
 
 def _alloc_views(wi, n_call, want):
@@ -86,7 +86,7 @@ def _alloc_views(wi, n_call, want):
     shapes = {'color': (B, n_call, n, 3, H, W), 'color_mask': (B, n_call, n, H, W),
               'overlap': (B, n_call, 1 + n, 3, H, W), 'overlap_mask': (B, n_call, 1 + n, H, W),
               'reproj_loss': (B, n_call, H, W), 'reproj_mask': (B, n_call, H, W),
-              'grid': (B, n_call, num_warps(n), H, W, 2)}
+              'grid': (B, n_call, num_warps(n), H, W, 2), 'selection': (B, n_call, H, W)}
     out = {k: torch.empty(shapes[k], device=wi.device, dtype=torch.float32) for k in want}
     v = _lib.WarpViews()
     for k, t in out.items():
