@@ -1,0 +1,113 @@
+"""CPU: the C-ABI library builds, loads, exports every symbol include/vfdepth_b200.h declares, agrees with the ctypes
+structs on layout, and rejects bad arguments with the documented status codes BEFORE touching the device (no compute
+calls are made here -- there is no GPU in the build container)."""
+import ctypes
+import os
+import re
+import subprocess
+import tempfile
+
+import pytest
+
+from vfdepth_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, 'include', 'vfdepth_b200.h')
+
+
+def _declared():
+    with open(HEADER) as f:
+        return sorted(set(re.findall(r'\b(vfd_[a-z0-9_]+)\s*\(', f.read())))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    names = _declared()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(lib, n), n
+    assert lib.vfd_version() == 100
+
+
+def test_header_is_plain_c_and_structs_match_ctypes():
+    """the header must compile as C (no C++/torch types in the boundary) and the struct layouts must be the ones the
+    ctypes mirror assumes."""
+    src = r'''
+#include <stdio.h>
+#include <stddef.h>
+#include "vfdepth_b200.h"
+int main(void) {
+  printf("%zu %zu %zu ", sizeof(vfd_fusion_desc), sizeof(vfd_warp_desc), sizeof(vfd_warp_views));
+  printf("%zu %zu %zu ", offsetof(vfd_fusion_desc, group), offsetof(vfd_fusion_desc, depth_div), offsetof(vfd_fusion_desc, axis_x));
+  printf("%zu %zu %zu\n", offsetof(vfd_warp_desc, nbr), offsetof(vfd_warp_desc, color), offsetof(vfd_warp_desc, invK));
+  return 0; }
+'''
+    d = tempfile.mkdtemp(prefix='vfd_abi_')
+    c, exe = os.path.join(d, 't.c'), os.path.join(d, 't')
+    with open(c, 'w') as f:
+        f.write(src)
+    subprocess.check_call(['gcc', '-std=c99', '-Wall', '-Werror', '-I', os.path.join(ROOT, 'include'), c, '-o', exe])
+    got = [int(x) for x in subprocess.check_output([exe]).split()]
+    F, W, V = _lib.FusionDesc, _lib.WarpDesc, _lib.WarpViews
+    want = [ctypes.sizeof(F), ctypes.sizeof(W), ctypes.sizeof(V), F.group.offset, F.depth_div.offset, F.axis_x.offset,
+            W.nbr.offset, W.color.offset, W.invK.offset]
+    assert got == want
+
+
+def test_error_strings():
+    lib = _lib.load()
+    assert lib.vfd_last_error(0) == b'ok'
+    for code in range(-6, 0):
+        assert lib.vfd_last_error(code) not in (b'ok', b'unknown vfd_status')
+    assert lib.vfd_last_error(-99) == b'unknown vfd_status'
+
+
+def test_bad_arguments_are_rejected_before_any_launch():
+    lib = _lib.load()
+    null = ctypes.c_void_p(0)
+    # NULL descriptor
+    assert lib.vfd_voxel_gather_depth_fwd(null, null, null, null, null, null, null, null, null, null, null) == -1
+    assert lib.vfd_ray_sample_fwd(null, null, null, null, null, null, null) == -1
+    assert lib.vfd_warp_stats(null, null, null, null, null, null) == -1
+    # descriptor out of range
+    d = _lib.FusionDesc()
+    assert lib.vfd_voxel_gather_depth_fwd(ctypes.byref(d), null, null, null, null, null, null, null, null, null, null) == -2
+    w = _lib.WarpDesc()
+    assert lib.vfd_warp_loss_fwd(ctypes.byref(w), null, null, null, null, null, null, null) == -2
+    # unsupported channel count (not a multiple of 4)
+    d.B, d.num_cams, d.C, d.h, d.w, d.X, d.Y, d.Z, d.D, d.Cv = 1, 6, 6, 4, 4, 2, 2, 2, 2, 4
+    assert lib.vfd_voxel_gather_depth_fwd(ctypes.byref(d), null, null, null, null, null, null, null, null, null, null) == -6
+    # valid sizes but NULL data pointers
+    w.B, w.num_cams, w.H, w.W, w.n_src, w.cam0, w.n_call = 1, 6, 8, 8, 2, 0, 6
+    assert lib.vfd_warp_stats(ctypes.byref(w), null, null, null, null, null) == -1
+    with pytest.raises(RuntimeError, match='NULL'):
+        _lib.check(-1, 'vfd_test')
+
+
+def test_host_layer_refuses_cpu_tensors():
+    """no CPU fallback: the host layer raises instead of computing anything off the device."""
+    import torch
+    from vfdepth_b200 import config as vcfg
+    from vfdepth_b200.vfnet import VFNet
+    cfg = vcfg.default_config('ddad', batch_size=1, model__voxel_size=[4, 4, 2], model__fusion_feat_in_dim=8,
+                              model__voxel_pre_dim=[4], training__height=32, training__width=32)
+    net = VFNet(cfg, 8, 8, 'depth')
+    feats = torch.zeros(1, 6, 8, 4, 4)
+    mask = torch.ones(1, 6, 1, 32, 32)
+    eye = torch.eye(4).expand(1, 6, 4, 4)
+    with pytest.raises(ValueError, match='CUDA'):
+        net.backproject_into_voxel(feats, mask, eye, eye)
+
+
+def test_state_dict_keys_match_reference():
+    """published checkpoints must load: SURVEY.md section 5 lists the VFNet keys of the reference."""
+    from vfdepth_b200 import config as vcfg
+    from vfdepth_b200.vfnet import VFNet
+    cfg = vcfg.default_config('ddad', batch_size=1, model__voxel_size=[4, 4, 2], model__fusion_feat_in_dim=8,
+                              model__voxel_pre_dim=[4], training__height=32, training__width=32)
+    keys = set(VFNet(cfg, 8, 8, 'depth').state_dict().keys())
+    assert keys == {'conv_overlap.0.weight', 'conv_overlap.0.bias', 'conv_non_overlap.0.weight',
+                    'conv_non_overlap.0.bias', 'reduce_dim.0.weight', 'reduce_dim.0.bias', 'reduce_dim.3.weight',
+                    'reduce_dim.3.bias'}
+    assert set(VFNet(cfg, 8, 8, 'pose').state_dict().keys()) == {'reduce_dim.0.weight', 'reduce_dim.0.bias',
+                                                                 'reduce_dim.3.weight', 'reduce_dim.3.bias'}
