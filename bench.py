@@ -30,6 +30,9 @@ if ROOT not in sys.path:
 METRIC = 'vfnet_fusion_warp_fwd_bwd_rigs_per_sec'
 UNIT = 'rigs/s'
 BATCH = 8                 # rigs per GPU per step (configs[1])
+WORKLOAD = ('configs[1]: VFNet fusion fwd+bwd (voxel gather + 1x1 MLPs + ray sampling, no reduce_dim)%s, %d DDAD-shaped '
+            'rigs (6x384x640) per GPU per step')
+WARP_PART = ' + configs[2]: 6-cam x 3-frame view-synthesis warp + SSIM/L1 photometric loss fwd+bwd'
 DATASET = 'ddad'
 
 
@@ -171,7 +174,13 @@ class FusionWorkload:
         rows = B * g.N * 3 * (g.C + 1) * 4
         vol = B * g.N * g.Cv * 4
         ray = B * g.num_cams * g.h * g.w * g.Cv * g.D * 4
-        return {'vfd_voxel_gather_depth_fwd': feats + msk + rows, 'vfd_voxel_gather_depth_bwd': feats + msk + rows,
+        # backward: only the gradient rows that can reach a camera are needed -- d_x_no where count == 1 and one half
+        # of d_x_ov per camera group that sees the voxel (count >= 2 -> both halves, adjacent cameras are in different
+        # groups): 2 * (C+1) floats for every voxel seen by at least one camera, none for the rest.
+        cnt = self.net.last_count
+        seen = int((cnt > 0).sum()) if cnt is not None else B * g.N
+        rows_bwd = seen * 2 * (g.C + 1) * 4
+        return {'vfd_voxel_gather_depth_fwd': feats + msk + rows, 'vfd_voxel_gather_depth_bwd': feats + msk + rows_bwd,
                 'vfd_ray_sample_fwd': vol + ray, 'vfd_ray_sample_bwd': vol + ray}
 
 
@@ -199,16 +208,17 @@ def timed(fn, steps, world):
 # --------------------------------------------------------------------------------------------------
 # CPU baseline / reference arm: the reference's own torch path (the oracle) on the host cores
 # --------------------------------------------------------------------------------------------------
-def cpu_fusion_pass(steps, warmup, seed=1234):
-    """fusion forward+backward of ONE rig per step through the oracle (bit-identical to the reference on CPU,
-    tests/test_oracle_golden.py).  -> (rigs/s, cores, seconds per rig)."""
+def cpu_step_pass(steps, warmup, seed=1234, with_warp=True):
+    """One rig per step through the oracle (bit-identical to the reference on CPU, tests/test_oracle_golden.py):
+    fusion forward+backward (gather + 1x1 MLPs + ray sampling) and, with ``with_warp``, the 6-camera x 3-frame warp +
+    SSIM/L1 loss forward+backward.  -> (rigs/s, cores, seconds per rig)."""
     from oracle import vfdepth_oracle as orc
     from vfdepth_b200 import config as vcfg
     from vfdepth_b200.rig import make_rig
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     cfg = vcfg.default_config(DATASET, batch_size=1)
-    inputs, extras = make_rig(cfg, seed=seed, with_images=False)
+    inputs, extras = make_rig(cfg, seed=seed, with_images=with_warp)
     lvl = cfg['model']['fusion_level'] + 1
     C, Cv = cfg['model']['fusion_feat_in_dim'], cfg['model']['voxel_pre_dim'][-1]
     gen = torch.Generator().manual_seed(seed)
@@ -224,6 +234,11 @@ def cpu_fusion_pass(steps, warmup, seed=1234):
                                          'depth', p)
         proj = orc.project_voxel_into_image(cfg, vox, inputs[('inv_K', lvl)], inputs['extrinsics'])
         torch.autograd.backward(proj, [g_up] * len(proj))
+        if with_warp:
+            depths = [d.clone().requires_grad_(True) for d in extras['depth']]
+            Ts = {k: v.clone().requires_grad_(True) for k, v in extras['cam_T_cam'].items()}
+            total, _ = orc.warp_and_loss(cfg, inputs, depths, extras['disp'], Ts, extras['noise'])
+            torch.autograd.grad(total, depths + list(Ts.values()))
         return f.grad
 
     for _ in range(warmup):
@@ -241,13 +256,14 @@ def run_reference(args):
         return
     steps, warmup = max(1, args.steps), max(1, min(args.warmup, 2))
     steps = min(steps, 6)               # ~5-15 s per rig on a many-core host: keep the arm within minutes
-    rps, cores, sec = cpu_fusion_pass(steps, warmup)
-    sample = 'fusion fwd+bwd (gather + 1x1 MLPs + ray sampling, no reduce_dim) of 1 DDAD rig per step, %d steps' % steps
+    rps, cores, sec = cpu_step_pass(steps, warmup, with_warp=not args.no_warp)
+    sample = ('fusion fwd+bwd (gather + 1x1 MLPs + ray sampling, no reduce_dim)%s of 1 DDAD rig per step, %d steps, '
+              'reference torch ops on %d host threads' % ('' if args.no_warp else ' + 6-cam x 3-frame warp + SSIM/L1 loss fwd+bwd', steps, cores))
     line = {'impl': 'reference', 'metric': METRIC, 'value': rps, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
             'warmup': warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': 'configs[1]: VFNet fusion fwd+bwd, DDAD-shaped rigs (6x384x640), reference torch '
-                                   'path on the host cores', 'rigs_per_step': 1},
+            'config': {'workload': WORKLOAD % ('' if args.no_warp else WARP_PART, 1) + '; reference torch path on the host cores',
+                       'rigs_per_step_per_gpu': 1},
             'cpu_baseline': {'value': rps, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
             'e2e': {'value': rps, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
@@ -338,19 +354,17 @@ def run_ours(args):
         line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
                 'warmup': max(3, args.warmup), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
                 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-                'config': {'workload': 'configs[1]: VFNet fusion fwd+bwd (voxel gather + 1x1 MLPs + ray sampling, no '
-                                       'reduce_dim)%s, %d DDAD-shaped rigs (6x384x640) per GPU per step'
-                                       % (' + 6-cam x 3-frame warp + SSIM/L1 loss fwd+bwd' if warp else '', args.batch),
+                'config': {'workload': WORKLOAD % (WARP_PART if warp else '', args.batch),
                            'rigs_per_step_per_gpu': args.batch, 'l2': 'inputs and outputs larger than L2 '
                            '(189 MB feature maps, 4.9 GB gather rows, 2.4 GB ray samples per step)',
                            'sharding': 'whole rigs per rank, no data-path collective',
                            'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms},
                 'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof, 'kernels': kernels}
         if world == 1 and not args.no_cpu_baseline:
-            rps, cores, sec = cpu_fusion_pass(2, 1)
+            rps, cores, sec = cpu_step_pass(2, 1, with_warp=warp is not None)
             line['cpu_baseline'] = {'value': rps, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                                    'sample': 'fusion fwd+bwd of 1 DDAD rig per step through the oracle (reference '
-                                              'torch ops), 1 warm-up + 2 timed, %.1f s per rig' % sec}
+                                    'sample': 'the same step (fusion%s fwd+bwd) of 1 DDAD rig through the oracle (reference '
+                                              'torch ops), 1 warm-up + 2 timed, %.1f s per rig' % (' + warp/loss' if warp is not None else '', sec)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
