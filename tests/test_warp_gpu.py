@@ -264,3 +264,47 @@ def test_no_intensity_align_and_early_exit():
     assert float(det['views']['color_mask'][1, 2, 0].sum()) == 0.0      # the exit really fires
     _check_views(cfg, det, d32, range(6))
     assert abs(float(total) - float(t32)) / float(t32) < 3e-4
+
+
+def test_dropin_modules_per_camera():
+    """ViewRendering / MultiCamLoss with the reference's call pattern (models/vfdepth.py:290-313: per camera,
+    outputs dict mutated in place) give the rig-level result, write the reference's keys, and back-propagate."""
+    dev = _dev()
+    from vfdepth_b200 import view
+    cfg, inp, ex = _rig(64, 96, 2, seed=21)
+    to = lambda t: t.to(dev)
+    inputs = {k: to(v) for k, v in inp.items()}
+    depths = [to(d).requires_grad_(True) for d in ex['depth']]
+    Ts = {f: to(t).requires_grad_(True) for f, t in ex['cam_T_cam'].items()}
+    outputs = {('cam', c): {('depth', 0): depths[c], ('disp', 0): to(ex['disp'][c]),
+                            ('cam_T_cam', 0, -1): Ts[-1][:, c], ('cam_T_cam', 0, 1): Ts[1][:, c]} for c in range(6)}
+    vr = view.ViewRendering(cfg, dev, materialize=True)
+    lossm = view.MultiCamLoss(cfg, dev)
+    total, noises = 0, []
+    for cam in range(6):
+        rel = orc.relative_cam_poses(cfg, inputs, {-1: Ts[-1][:, cam], 1: Ts[1][:, cam]}, cam)
+        vr(inputs, outputs, cam, rel)
+        torch.manual_seed(1000 + cam)
+        noises.append(torch.randn(2, 2, 64, 96))
+        torch.manual_seed(1000 + cam)           # the module draws the same tensor from the global CPU stream
+        cam_loss, ld = lossm(inputs, outputs, cam)
+        assert set(ld) >= {'reproj_loss', 'spatio_loss', 'spatio_tempo_loss', 'smooth', 'depth/mean'}
+        total = total + cam_loss
+    total = total / 6
+    g_mod = torch.autograd.grad(total, depths + [Ts[-1], Ts[1]])
+    ex2 = dict(ex, noise=noises)
+    t_rig, det, g_rig = _run_gpu(cfg, inp, ex2, dev, ALL_VIEWS)
+    assert abs(float(total) - float(t_rig)) / float(t_rig) < 1e-6
+    for a, b in zip(g_mod, g_rig):
+        assert H.rel_err(a.cpu(), b) < 1e-5
+    v = det['views']
+    for cam in (0, 4):
+        tv = outputs[('cam', cam)]
+        for k, f in enumerate((-1, 1)):
+            assert torch.equal(tv[('color', f, 0)], v['color'][:, cam, k])
+            assert torch.equal(tv[('color_mask', f, 0)], v['color_mask'][:, cam, k:k + 1])
+        for k, f in enumerate((0, -1, 1)):
+            assert torch.equal(tv[('overlap', f, 0)], v['overlap'][:, cam, k])
+            assert torch.equal(tv[('overlap_mask', f, 0)], v['overlap_mask'][:, cam, k:k + 1])
+        assert torch.equal(tv[('reproj_mask', 0)], v['reproj_mask'][:, cam:cam + 1])
+        assert tv[('reproj_loss', 0)].shape == (2, 1, 64, 96)
