@@ -148,18 +148,20 @@ typedef struct vfd_warp_views {
  *   T      [B,n_call,NW,4,4]     target->source transforms (cam_T_cam / rel_pose_dict, pose.py:66-96)
  *   stats  [B,n_call,NW,8] f64   scratch, zero-filled here: {count, sum ref*m, sum warp*m, sum warp, sum warp^2,
  *                                sum ref, sum ref^2, -}
- *   params [B,n_call,NW,8] f32   out: {w_mean, w_std+1e-8, s_std, s_mean, apply, -, -, -}; apply = 0 when
- *                                intensity_align is off or the batch-wide early exit of :50-53 fires for warp j */
+ *   params [B,n_call,NW,8] f32   out: {w_mean, w_std+1e-8, s_std, s_mean, apply, 1/(w_std+1e-8), -, -}; apply = 0
+ *                                when intensity_align is off or the batch-wide early exit of :50-53 fires for warp j
+ *   raw    [B,n_call,NW,H,W,4]   out: the un-normalised warp (r, g, b) and warp mask of every source image
+ *                                (get_virtual_image, :61-82); 16-byte aligned.  The loss passes read it back. */
 int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const float* T, double* stats, float* params,
-                   void* stream);
+                   float* raw, void* stream);
 
-/* Pass 2 -- warp again, normalise, SSIM+L1 maps, min over frames, auto-mask, masked sums.
+/* Pass 2 -- normalise the raw warps, SSIM+L1 maps, min over frames, auto-mask, masked sums.
  *   noise  [B,n_call,n_src,H,W]  the torch.randn of single_cam_loss.py:45-46 (drawn by the caller)
  *   sums   [n_call,8] f64        zero-filled here: {sum reproj*auto, sum auto, sum spatial*m, sum m,
  *                                sum spatio-temporal*m, sum m, -, -} over the whole local batch (loss_util.py:21-25)
  *   views  optional materialised images (NULL for the fused path) */
 int vfd_warp_loss_fwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
-                      const float* noise, double* sums, const vfd_warp_views* views, void* stream);
+                      const float* raw, const float* noise, double* sums, const vfd_warp_views* views, void* stream);
 
 size_t vfd_warp_bwd_workspace_bytes(const vfd_warp_desc* d);
 
@@ -169,7 +171,7 @@ size_t vfd_warp_bwd_workspace_bytes(const vfd_warp_desc* d);
  *   d_T     [B,n_call,NW,4,4] written; per-block partial sums go through `ws` and are reduced in a fixed
  *                            order (deterministic) */
 int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
-                      const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
+                      const float* raw, const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
                       size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus

@@ -68,18 +68,18 @@ def test_bad_arguments_are_rejected_before_any_launch():
     # NULL descriptor
     assert lib.vfd_voxel_gather_depth_fwd(null, null, null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_ray_sample_fwd(null, null, null, null, null, null, null) == -1
-    assert lib.vfd_warp_stats(null, null, null, null, null, null) == -1
+    assert lib.vfd_warp_stats(null, null, null, null, null, null, null) == -1
     # descriptor out of range
     d = _lib.FusionDesc()
     assert lib.vfd_voxel_gather_depth_fwd(ctypes.byref(d), null, null, null, null, null, null, null, null, null, null) == -2
     w = _lib.WarpDesc()
-    assert lib.vfd_warp_loss_fwd(ctypes.byref(w), null, null, null, null, null, null, null) == -2
+    assert lib.vfd_warp_loss_fwd(ctypes.byref(w), null, null, null, null, null, null, null, null) == -2
     # unsupported channel count (not a multiple of 4)
     d.B, d.num_cams, d.C, d.h, d.w, d.X, d.Y, d.Z, d.D, d.Cv = 1, 6, 6, 4, 4, 2, 2, 2, 2, 4
     assert lib.vfd_voxel_gather_depth_fwd(ctypes.byref(d), null, null, null, null, null, null, null, null, null, null) == -6
     # valid sizes but NULL data pointers
     w.B, w.num_cams, w.H, w.W, w.n_src, w.cam0, w.n_call = 1, 6, 8, 8, 2, 0, 6
-    assert lib.vfd_warp_stats(ctypes.byref(w), null, null, null, null, null) == -1
+    assert lib.vfd_warp_stats(ctypes.byref(w), null, null, null, null, null, null) == -1
     with pytest.raises(RuntimeError, match='NULL'):
         _lib.check(-1, 'vfd_test')
 

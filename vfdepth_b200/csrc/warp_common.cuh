@@ -145,18 +145,4 @@ __device__ __forceinline__ WarpSample warp_sample(const float* P, const float* _
     return s;
 }
 
-// normalised prediction of warp j (view_rendering.py:58-59): ((w - w_mean) / (w_std + 1e-8) * s_std + s_mean) * mask,
-// or the raw warp when apply == 0 (intensity_align off, or the batch-wide early exit of :50-53)
-__device__ __forceinline__ float warp_normalise(const float* prm, float w, float m) {
-    if (prm[4] == 0.f) return w;
-    float r = VFD_DIV(VFD_SUB(w, prm[0]), prm[1]);
-    r = VFD_ADD(VFD_MUL(r, prm[2]), prm[3]);
-    return VFD_MUL(r, m);
-}
-// d pred / d w
-__device__ __forceinline__ float warp_normalise_grad(const float* prm, float m) {
-    if (prm[4] == 0.f) return 1.f;
-    return m * prm[2] / prm[1];
-}
-
 }  // namespace vfd

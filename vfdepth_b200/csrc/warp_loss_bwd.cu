@@ -1,6 +1,6 @@
 // Pass 2 of the view-synthesis path, backward: d loss / d depth (per pixel) and d loss / d T (4x4 per warp).
-// Nothing was saved by the forward except the statistics: the CTA re-warps a (32+4) x (8+4) region, re-evaluates the
-// loss decisions (min over frames, auto-mask, masks) on the (32+2) x (8+2) ring around its tile, turns them into
+// The forward saved nothing but the statistics and pass 1's raw warps: the CTA rebuilds the normalised images of a
+// (32+4) x (8+4) region from them, re-evaluates the loss decisions (min over frames, auto-mask, masks) on the (32+2) x (8+2) ring around its tile, turns them into
 // SSIM derivative coefficients in shared memory, gathers those over each interior pixel's 3x3 neighbourhood
 // (reflection padding handled by tap multiplicity), and pushes the result through normalisation, the bilinear
 // sampler and the projection.  Every d_depth pixel is written exactly once; d_T goes through per-CTA partial sums
@@ -16,6 +16,7 @@ struct LossBwdArgs {
     const float* depth;
     const float* T;
     const float* params;
+    const float4* raw;
     const float* noise;
     const float* d_num;   // [n_call,3]
     float* d_depth;
@@ -43,6 +44,8 @@ __device__ __forceinline__ int tap_mult(int p, int q, int n) {
     return m;
 }
 
+constexpr int kNPred = VFD_WARP_SRC + 1 + VFD_WARP_SRC;   // differentiable images: 2 temporal, overlap_0, 2 spatio-temporal
+
 __device__ __forceinline__ float pick5(const float (*v)[3], int k, int c) {
     float r = v[0][c];
 #pragma unroll
@@ -64,7 +67,7 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossB
     __syncthreads();
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
-    fill_region<2>(ctx, d, b, ci, ox, oy, depth, sm);
+    fill_region<2>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW, sm);
     __syncthreads();
 
     // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
@@ -75,22 +78,22 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossB
         const int p = y * W + x;
         float nz[VFD_WARP_SRC] = {0.f, 0.f};
         for (int k = 0; k < n_src; ++k) nz[k] = __ldg(a.noise + ((size_t)(b * d.n_call + ci) * n_src + k) * HW + p);
-        SsimGrad g[kNPred];
+        SsimGrad2 g[3];
         const PixelLoss o = pixel_loss<2, true>(sm, d, x, y, ox, oy, __ldg(rmaskp + p), nz, g);
         const float wr = w_set[0] * o.automask, ws = w_set[1] * o.sp_mask, wt = w_set[2] * o.st_mask;
         const bool s1 = o.sel_reproj == 1, t1 = o.sel_st == 1;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const float ra = s1 ? g[1].a[c] : g[0].a[c], rb = s1 ? g[1].b[c] : g[0].b[c], rc = s1 ? g[1].c[c] : g[0].c[c];
-            const float ta = t1 ? g[VFD_WARP_SRC + 2].a[c] : g[VFD_WARP_SRC + 1].a[c];
-            const float tb = t1 ? g[VFD_WARP_SRC + 2].b[c] : g[VFD_WARP_SRC + 1].b[c];
-            const float tc = t1 ? g[VFD_WARP_SRC + 2].c[c] : g[VFD_WARP_SRC + 1].c[c];
             float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
-            q[0] = wr * ra; q[Coef::R] = wr * rb; q[2 * Coef::R] = wr * rc;
+            q[0] = wr * (s1 ? g[0].a[c].y : g[0].a[c].x);
+            q[Coef::R] = wr * (s1 ? g[0].b[c].y : g[0].b[c].x);
+            q[2 * Coef::R] = wr * (s1 ? g[0].c[c].y : g[0].c[c].x);
             q += 9 * Coef::R;
-            q[0] = ws * g[VFD_WARP_SRC].a[c]; q[Coef::R] = ws * g[VFD_WARP_SRC].b[c]; q[2 * Coef::R] = ws * g[VFD_WARP_SRC].c[c];
+            q[0] = ws * g[2].a[c].x; q[Coef::R] = ws * g[2].b[c].x; q[2 * Coef::R] = ws * g[2].c[c].x;
             q += 9 * Coef::R;
-            q[0] = wt * ta; q[Coef::R] = wt * tb; q[2 * Coef::R] = wt * tc;
+            q[0] = wt * (t1 ? g[1].a[c].y : g[1].a[c].x);
+            q[Coef::R] = wt * (t1 ? g[1].b[c].y : g[1].b[c].x);
+            q[2 * Coef::R] = wt * (t1 ? g[1].c[c].y : g[1].c[c].x);
         }
         cf[Coef::kWgt + r] = wr;
         cf[Coef::kWgt + Coef::R + r] = ws;
@@ -155,7 +158,10 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossB
             else w1 = ((sel0 >> 1) == k - VFD_WARP_SRC - 1) ? wl[2] : 0.f;
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-                const float xv = sm[Rg::kPred + (k * 3 + c) * Rg::R + ctr2], yv = sm[Rg::kTgt + c * Rg::R + ctr2];
+                // image k of the tile: 0,1 = pair 0 (.x,.y); 2 = pair 2.x; 3,4 = pair 1 (.x,.y); target = pair 3.y
+                const float2* ic = reinterpret_cast<const float2*>(sm + Rg::kImg) + c * kPairs * Rg::R + ctr2;
+                const float2 pr = ic[(k < VFD_WARP_SRC ? 0 : (k == VFD_WARP_SRC ? 2 : 1)) * Rg::R];
+                const float xv = (k == 1 || k == VFD_WARP_SRC + 2) ? pr.y : pr.x, yv = ic[3 * Rg::R].y;
                 const float df = xv - yv;
                 const float sgn = df > 0.f ? 1.f : (df < 0.f ? -1.f : 0.f);
                 dpred[k][c] = (SA[k][c] + 2.f * xv * SB[k][c] + yv * SC[k][c]) * (1.f / 9.f) + (0.15f / 3.f) * w1 * sgn;
@@ -269,15 +275,16 @@ extern "C" size_t vfd_warp_bwd_workspace_bytes(const vfd_warp_desc* d) {
 }
 
 extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
-                                 const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
+                                 const float* raw, const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
                                  size_t ws_bytes, void* stream) {
     int rc = check_warp_desc(d);
     if (rc) return rc;
-    if (!depth || !T || !params || !noise || !d_num || !d_depth || !d_T || !ws) return VFD_ERR_NULL;
+    if (!depth || !T || !params || !raw || !noise || !d_num || !d_depth || !d_T || !ws) return VFD_ERR_NULL;
+    if (reinterpret_cast<uintptr_t>(raw) & 15) return VFD_ERR_ALIGN;
     if (ws_bytes < vfd_warp_bwd_workspace_bytes(d)) return VFD_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     LossBwdArgs a = {};
-    a.d = *d; a.depth = depth; a.T = T; a.params = params; a.noise = noise; a.d_num = d_num;
+    a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise; a.d_num = d_num;
     a.d_depth = d_depth; a.d_T = d_T; a.partial = (float*)ws;
     const size_t smem = bwd_smem_bytes();
     // > 48 KB of dynamic shared memory needs the opt-in; setting it is idempotent and per device, so it is simply

@@ -1,6 +1,6 @@
-// Pass 2 of the view-synthesis path, forward: warp (again) + intensity alignment + SSIM/L1 maps + min over frames +
-// auto-mask + masked sums in ONE kernel -- no warped image, grid or loss map ever goes to HBM unless the caller asks
-// for the materialised views (logger / parity tests).
+// Pass 2 of the view-synthesis path, forward: intensity alignment of the raw warps pass 1 left + SSIM/L1 maps + min
+// over frames + auto-mask + masked sums in ONE kernel -- no normalised image, overlap sum or loss map goes to HBM
+// unless the caller asks for the materialised views (logger / parity tests).
 //   models/geometry/view_rendering.py:118-198, models/losses/single_cam_loss.py:17-55, multi_cam_loss.py:16-59,
 //   loss_util.py:6-25, 43-78.
 // Grid: (tiles_x, tiles_y, B * n_call); CTA = 32 x 8 pixel tile with a 1-pixel halo (the 3x3 SSIM window).
@@ -13,6 +13,7 @@ struct LossFwdArgs {
     const float* depth;
     const float* T;
     const float* params;
+    const float4* raw;
     const float* noise;
     double* sums;
     vfd_warp_views views;
@@ -34,7 +35,7 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_fwd_kernel(const LossF
     if (threadIdx.x < 8) sacc[threadIdx.x] = 0.0;
     __syncthreads();
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
-    fill_region<1>(ctx, d, b, ci, ox, oy, depth, sm);
+    fill_region<1>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW, sm);
     __syncthreads();
 
     const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
@@ -42,7 +43,7 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_fwd_kernel(const LossF
     if (x < W && y < H) {
         const int p = y * W + x;
         const float rmask = __ldg(d.mask + (size_t)(b * d.num_cams + cam) * HW + p);
-        float nz[VFD_WARP_SRC];
+        float nz[VFD_WARP_SRC] = {0.f, 0.f};
         for (int k = 0; k < n_src; ++k) nz[k] = __ldg(a.noise + ((size_t)(b * d.n_call + ci) * n_src + k) * HW + p);
         const PixelLoss o = pixel_loss<1, false>(sm, d, x, y, ox, oy, rmask, nz, nullptr);
         acc[0] = VFD_MUL(o.reproj, o.automask); acc[1] = o.automask;
@@ -52,19 +53,24 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_fwd_kernel(const LossF
             const vfd_warp_views& v = a.views;
             const size_t bc = (size_t)(b * d.n_call + ci);
             const int ctr = (y - oy) * Rg::RW + (x - ox);
-            for (int k = 0; k < n_src; ++k) {
-                if (v.color)
-                    for (int c = 0; c < 3; ++c)
-                        v.color[((bc * n_src + k) * 3 + c) * HW + p] = sm[Rg::kPred + (k * 3 + c) * Rg::R + ctr];
+            const float2* img = reinterpret_cast<const float2*>(sm + Rg::kImg) + ctr;
+            for (int c = 0; c < 3; ++c) {
+                const float2 tp = img[(c * kPairs + 0) * Rg::R], st = img[(c * kPairs + 1) * Rg::R];
+                const float2 sp = img[(c * kPairs + 2) * Rg::R];
+                if (v.color) {
+                    v.color[((bc * n_src + 0) * 3 + c) * HW + p] = tp.x;
+                    if (n_src > 1) v.color[((bc * n_src + 1) * 3 + c) * HW + p] = tp.y;
+                }
+                if (v.overlap) {
+                    v.overlap[((bc * (1 + n_src) + 0) * 3 + c) * HW + p] = sp.x;
+                    v.overlap[((bc * (1 + n_src) + 1) * 3 + c) * HW + p] = st.x;
+                    if (n_src > 1) v.overlap[((bc * (1 + n_src) + 2) * 3 + c) * HW + p] = st.y;
+                }
+            }
+            for (int k = 0; k < n_src; ++k)
                 if (v.color_mask) v.color_mask[(bc * n_src + k) * HW + p] = sm[Rg::kCmask + k * Rg::R + ctr];
-            }
-            for (int f = 0; f <= n_src; ++f) {
-                if (v.overlap)
-                    for (int c = 0; c < 3; ++c)
-                        v.overlap[((bc * (1 + n_src) + f) * 3 + c) * HW + p] =
-                            sm[Rg::kPred + ((VFD_WARP_SRC + f) * 3 + c) * Rg::R + ctr];
+            for (int f = 0; f <= n_src; ++f)
                 if (v.overlap_mask) v.overlap_mask[(bc * (1 + n_src) + f) * HW + p] = sm[Rg::kOmask + f * Rg::R + ctr];
-            }
             if (v.reproj_loss) v.reproj_loss[bc * HW + p] = acc[0];
             if (v.reproj_mask) v.reproj_mask[bc * HW + p] = o.automask;
             if (v.selection) v.selection[bc * HW + p] = (float)(o.sel_reproj + 2 * o.sel_st);
@@ -98,14 +104,15 @@ int check_warp_desc(const vfd_warp_desc* d);   // warp_stats.cu
 using namespace vfd;
 
 extern "C" int vfd_warp_loss_fwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
-                                 const float* noise, double* sums, const vfd_warp_views* views, void* stream) {
+                                 const float* raw, const float* noise, double* sums, const vfd_warp_views* views, void* stream) {
     int rc = check_warp_desc(d);
     if (rc) return rc;
-    if (!depth || !T || !params || !noise || !sums) return VFD_ERR_NULL;
+    if (!depth || !T || !params || !raw || !noise || !sums) return VFD_ERR_NULL;
+    if (reinterpret_cast<uintptr_t>(raw) & 15) return VFD_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(sums, 0, (size_t)d->n_call * 8 * sizeof(double), st) != cudaSuccess) return VFD_ERR_CUDA;
     LossFwdArgs a = {};
-    a.d = *d; a.depth = depth; a.T = T; a.params = params; a.noise = noise; a.sums = sums;
+    a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise; a.sums = sums;
     if (views) { a.views = *views; a.has_views = 1; }
     const size_t smem = Region<1>::kFloats * sizeof(float);
     dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);

@@ -1,16 +1,81 @@
-// SSIM + L1 photometric loss at one pixel from shared-memory tiles (models/losses/loss_util.py:43-78), forward value
-// and the derivative coefficients the backward pass gathers.
+// SSIM + L1 photometric loss at one pixel from shared-memory tiles (models/losses/loss_util.py:43-78) for all eight
+// images of a camera at once, on Blackwell's packed fp32 pipe.
 //
-// The 3x3 means are summed tap by tap in row-major order and divided by 9 -- the order ATen's avg_pool2d uses -- with
-// unfused multiplies and adds, so E[x^2] - mu^2 (a difference of two nearly equal numbers) carries the same rounding
-// as the reference instead of an independent 3e-8 error on a 0.25-sized quantity.
+// The eight images are kept as four float2 pairs per channel:
+//   pair 0 = (color_-1, color_+1)   temporal warps                      single_cam_loss.py:23-30
+//   pair 1 = (overlap_-1, overlap_+1) spatio-temporal                   multi_cam_loss.py:38-56
+//   pair 2 = (overlap_0, frame -1)  spatial warp | identity image       multi_cam_loss.py:21-26, single_cam_loss.py:33-43
+//   pair 3 = (frame +1, target)     identity image | the target itself
+// so one LDS.64 fetches a tap of two images and add/mul.f32x2 (sm_100 packed fp32: two IEEE round-to-nearest results
+// per instruction, bit-identical to the scalar ops) update two window sums.
+//
+// Rounding.  The 3x3 means are summed tap by tap in row-major order and divided by 9 -- the order ATen's avg_pool2d
+// uses -- with un-fused multiplies and adds, so E[x^2] - mu^2 (a difference of two nearly equal numbers) carries the
+// same rounding as the reference instead of an independent 3e-8 error on a 0.25-sized quantity.  x / 9 and x / 3 are
+// computed as q = x*r; q += fma(-9, q, x) * r, which is the correctly rounded quotient for every fp32 x (checked
+// exhaustively over all 2^23 mantissas, tools/check_div_const.py).  Only the final ssim = num / den uses a fast
+// reciprocal: it is 1-2 ulp (1e-7) on a quantity whose fp32 noise floor is 5e-5.
 #pragma once
 #include "warp_common.cuh"
 
 namespace vfd {
 
+// ---- packed fp32 (PTX ISA 8.6+, sm_100+) ----
+__device__ __forceinline__ unsigned long long f2_bits(float2 a) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+    return r;
+}
+__device__ __forceinline__ float2 bits_f2(unsigned long long r) {
+    float2 a;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(r));
+    return a;
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return bits_f2(r);
+}
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return bits_f2(r);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return bits_f2(r);
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)), "l"(f2_bits(c)));
+    return bits_f2(r);
+}
+__device__ __forceinline__ float2 splat2(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float fast_rcp(float x) {   // MUFU.RCP, ~1 ulp
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// correctly rounded x / K for K = 9 or 3 (Markstein: r = RN(1/K), one residual correction)
+template <int K>
+__device__ __forceinline__ float2 div_const2(float2 x) {
+    const float r = 1.0f / (float)K;
+    float2 q = mul2(x, splat2(r));
+    const float2 rem = fma2(splat2(-(float)K), q, x);
+    return fma2(rem, splat2(r), q);
+}
+template <int K>
+__device__ __forceinline__ float div_const(float x) {
+    const float r = 1.0f / (float)K;
+    const float q = __fmul_rn(x, r);
+    return __fmaf_rn(__fmaf_rn(-(float)K, q, x), r, q);
+}
+
 constexpr float kC1 = (float)(0.01 * 0.01);   // python: 0.01**2 in double, cast to fp32 when it meets the tensor
 constexpr float kC2 = (float)(0.03 * 0.03);
+constexpr int kPairs = 4;                      // float2 image pairs per channel (see the table above)
 
 // reflection padding of 1 (ReflectionPad2d(1), loss_util.py:47-49)
 __device__ __forceinline__ int reflect1(int i, int n) { return i < 0 ? -i : (i >= n ? 2 * (n - 1) - i : i); }
@@ -25,76 +90,82 @@ __device__ __forceinline__ void tap_indices(int x, int y, int W, int H, int ox, 
     }
 }
 
-struct TargetStats {   // per channel: mean and E[t^2] of the target window
-    float mu[3], sq[3];
+// derivative coefficients of one image pair: d L / d (window mean of x, of x^2, of x*y), per channel
+struct SsimGrad2 {
+    float2 a[3], b[3], c[3];
 };
 
-__device__ __forceinline__ TargetStats target_stats(const float* tgt, int plane, const int* idx) {
-    TargetStats t;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        float s = 0.f, s2 = 0.f;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) {
-            const float v = tgt[c * plane + idx[k]];
-            s = VFD_ADD(s, v);
-            s2 = VFD_ADD(s2, VFD_MUL(v, v));
-        }
-        t.mu[c] = VFD_DIV(s, 9.f);
-        t.sq[c] = VFD_DIV(s2, 9.f);
-    }
-    return t;
-}
-
-struct SsimGrad {   // d loss / d (window mean of x, of x^2, of x*y) per channel, before the upstream weight
-    float a[3], b[3], c[3];
-};
-
-// 0.85 * mean_c clamp((1 - ssim_c) / 2, 0, 1) + 0.15 * mean_c |t_c - p_c|     (loss_util.py:70-78)
-// pred / tgt: 3 channel planes of `plane` floats; idx: taps; ctr: tile-local index of the pixel itself
+// Photometric loss 0.85 * mean_c clamp((1 - ssim_c) / 2, 0, 1) + 0.15 * mean_c |t_c - p_c| of the 7 images against
+// the target (loss_util.py:70-78).  img: float2 planes [3 channels][kPairs][plane].  L[q] = losses of pair q
+// (L[3].y, target against itself, is meaningless).  g (GRAD): coefficients for pairs 0..2.
 template <bool GRAD>
-__device__ __forceinline__ float photometric(const float* pred, const float* tgt, int plane, const int* idx, int ctr,
-                                             const TargetStats& ts, SsimGrad* g) {
-    float ssum = 0.f, lsum = 0.f;
+__device__ __forceinline__ void photometric8(const float2* __restrict__ img, int plane, const int* idx, float2* L,
+                                             SsimGrad2* g) {
+    float2 ssum[kPairs], lsum[kPairs];
+#pragma unroll
+    for (int q = 0; q < kPairs; ++q) ssum[q] = lsum[q] = splat2(0.f);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        const float* pp = pred + c * plane;
-        const float* tp = tgt + c * plane;
-        float sx = 0.f, sxx = 0.f, sxy = 0.f;
+        const float2* pc = img + c * kPairs * plane;
+        float2 sx[kPairs], sxx[kPairs], sxy[kPairs], xc[kPairs];
+#pragma unroll
+        for (int q = 0; q < kPairs; ++q) sx[q] = sxx[q] = sxy[q] = splat2(0.f);
 #pragma unroll
         for (int k = 0; k < 9; ++k) {
-            const float xv = pp[idx[k]], yv = tp[idx[k]];
-            sx = VFD_ADD(sx, xv);
-            sxx = VFD_ADD(sxx, VFD_MUL(xv, xv));
-            sxy = VFD_ADD(sxy, VFD_MUL(xv, yv));
+            float2 x[kPairs];
+#pragma unroll
+            for (int q = 0; q < kPairs; ++q) x[q] = pc[q * plane + idx[k]];
+            const float2 yy = splat2(x[3].y);
+#pragma unroll
+            for (int q = 0; q < kPairs; ++q) {
+                sx[q] = add2(sx[q], x[q]);
+                sxx[q] = add2(sxx[q], mul2(x[q], x[q]));
+                sxy[q] = add2(sxy[q], mul2(x[q], yy));
+                if (k == 4) xc[q] = x[q];
+            }
         }
-        const float mu_x = VFD_DIV(sx, 9.f), mu_y = ts.mu[c];
-        const float musq_x = VFD_MUL(mu_x, mu_x), musq_y = VFD_MUL(mu_y, mu_y), mu_xy = VFD_MUL(mu_x, mu_y);
-        const float sig_x = VFD_SUB(VFD_DIV(sxx, 9.f), musq_x);
-        const float sig_y = VFD_SUB(ts.sq[c], musq_y);
-        const float sig_xy = VFD_SUB(VFD_DIV(sxy, 9.f), mu_xy);
-        const float n1 = VFD_ADD(VFD_MUL(2.f, mu_xy), kC1), n2 = VFD_ADD(VFD_MUL(2.f, sig_xy), kC2);
-        const float d1 = VFD_ADD(VFD_ADD(musq_x, musq_y), kC1), d2 = VFD_ADD(VFD_ADD(sig_x, sig_y), kC2);
-        const float den = VFD_ADD(VFD_MUL(d1, d2), 1e-8f);
-        const float ssim = VFD_DIV(VFD_MUL(n1, n2), den);
-        const float raw = VFD_DIV(VFD_SUB(1.f, ssim), 2.f);
-        const float l = fminf(fmaxf(raw, 0.f), 1.f);
-        ssum = VFD_ADD(ssum, l);
-        lsum = VFD_ADD(lsum, fabsf(VFD_SUB(tp[ctr], pp[ctr])));
-        if (GRAD) {
-            // d l / d ssim = -1/2 inside the clamp (torch: gradient passes where 0 <= raw <= 1), then * 0.85 / 3
-            const float gs = (raw >= 0.f && raw <= 1.f) ? (-0.5f * 0.85f / 3.f) : 0.f;
-            const float inv = 1.f / den;
-            // n2 = 2 (sxy - mu_x mu_y) + C2 ; d2 = (sxx - mu_x^2) + sig_y + C2
-            const float dn_dmu = 2.f * mu_y * n2 - 2.f * mu_y * n1;
-            const float dd_dmu = 2.f * mu_x * d2 - 2.f * mu_x * d1;
-            g->a[c] = gs * (dn_dmu - ssim * dd_dmu) * inv;
-            g->b[c] = gs * (-ssim * d1) * inv;
-            g->c[c] = gs * (2.f * n1) * inv;
+        const float mu_y = div_const<9>(sx[3].y), e_yy = div_const<9>(sxx[3].y);
+        const float musq_y = __fmul_rn(mu_y, mu_y), sig_y = __fsub_rn(e_yy, musq_y);
+        const float2 yc = splat2(xc[3].y);
+#pragma unroll
+        for (int q = 0; q < kPairs; ++q) {
+            const float2 mu = div_const2<9>(sx[q]);
+            const float2 musq = mul2(mu, mu), mu_xy = mul2(mu, splat2(mu_y));
+            const float2 sig_x = sub2(div_const2<9>(sxx[q]), musq);
+            const float2 sig_xy = sub2(div_const2<9>(sxy[q]), mu_xy);
+            // 2*v + C: 2*v is exact, so the fused form rounds once exactly like mul-then-add
+            const float2 n1 = fma2(splat2(2.f), mu_xy, splat2(kC1)), n2 = fma2(splat2(2.f), sig_xy, splat2(kC2));
+            const float2 d1 = add2(add2(musq, splat2(musq_y)), splat2(kC1));
+            const float2 d2 = add2(add2(sig_x, splat2(sig_y)), splat2(kC2));
+            const float2 den = add2(mul2(d1, d2), splat2(1e-8f));
+            const float2 num = mul2(n1, n2);
+            const float2 inv = make_float2(fast_rcp(den.x), fast_rcp(den.y));
+            const float2 ssim = mul2(num, inv);
+            const float2 raw = mul2(sub2(splat2(1.f), ssim), splat2(0.5f));
+            const float2 l = make_float2(fminf(fmaxf(raw.x, 0.f), 1.f), fminf(fmaxf(raw.y, 0.f), 1.f));
+            ssum[q] = add2(ssum[q], l);
+            const float2 df = sub2(yc, xc[q]);
+            lsum[q] = add2(lsum[q], make_float2(fabsf(df.x), fabsf(df.y)));
+            if (GRAD && q < 3) {
+                // d l / d ssim = -1/2 inside the clamp (torch: gradient passes where 0 <= raw <= 1), then * 0.85 / 3
+                const float gk = -0.5f * 0.85f / 3.f;
+                const float2 gs = make_float2((raw.x >= 0.f && raw.x <= 1.f) ? gk : 0.f,
+                                              (raw.y >= 0.f && raw.y <= 1.f) ? gk : 0.f);
+                const float2 gi = mul2(gs, inv);
+                // n2 = 2 (sxy - mu_x mu_y) + C2 ; d2 = (sxx - mu_x^2) + sig_y + C2
+                const float2 dn = mul2(splat2(2.f * mu_y), sub2(n2, n1));
+                const float2 dd = mul2(mul2(splat2(2.f), mu), sub2(d2, d1));
+                g[q].a[c] = mul2(gi, sub2(dn, mul2(ssim, dd)));
+                g[q].b[c] = mul2(gi, mul2(ssim, mul2(splat2(-1.f), d1)));
+                g[q].c[c] = mul2(gi, mul2(splat2(2.f), n1));
+            }
         }
     }
-    const float s_mean = VFD_DIV(ssum, 3.f), l_mean = VFD_DIV(lsum, 3.f);
-    return VFD_ADD(VFD_MUL(0.85f, s_mean), VFD_MUL(0.15f, l_mean));
+#pragma unroll
+    for (int q = 0; q < kPairs; ++q) {
+        const float2 s_mean = div_const2<3>(ssum[q]), l_mean = div_const2<3>(lsum[q]);
+        L[q] = add2(mul2(splat2(0.85f), s_mean), mul2(splat2(0.15f), l_mean));
+    }
 }
 
 }  // namespace vfd

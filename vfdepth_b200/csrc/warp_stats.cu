@@ -3,6 +3,8 @@
 //
 // Per (rig, target camera, warp j):  count of pixels with ref_mask*warp_mask != 0, the masked sums of the target
 // and of the warped image, and the UNMASKED sums / sums of squares the reference's variance runs over (:36).
+// The raw warps (r, g, b, mask) are also written out, one float4 per pixel and warp, so that the loss kernels
+// normalise and compare them without projecting and sampling again.
 // Per-thread partial sums are fp32 over a handful of pixels; everything above that (warp, CTA, grid) is fp64, so the
 // one-pass variance  (S2 - 2 m S1 + n m^2) / n  is as accurate as the reference's two-pass form.
 #include "warp_common.cuh"
@@ -18,6 +20,7 @@ struct StatsArgs {
     const float* T;
     double* stats;
     float* params;
+    float4* raw;   // [B,n_call,NW,H*W] (r, g, b, warp mask) of every warp: read back by the loss kernels
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -66,6 +69,7 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
     }
     for (int j = 0; j < NW; ++j) {
         if (!ctx.active[j]) continue;
+        float4* raw = a.raw + ((size_t)(b * d.n_call + ci) * NW + j) * HW;
         float cnt = 0.f, srm = 0.f, swm = 0.f, sw1 = 0.f, sw2 = 0.f;
 #pragma unroll 2
         for (int k = 0; k < kStatPx; ++k) {
@@ -75,6 +79,7 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
             float X[3];
             vfd_backproject(ctx.invK, (float)u, (float)v, __ldg(depth + p), X);
             const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
+            raw[p] = make_float4(s.v[0], s.v[1], s.v[2], s.m);
             const bool m = (__ldg(rmask + p) * s.m) != 0.f;   // (src_mask * warp_mask).bool()  (:46)
             const float w3 = s.v[0] + s.v[1] + s.v[2];
             sw1 += w3;
@@ -129,7 +134,8 @@ __global__ void warp_stats_finalize_kernel(const StatsArgs a) {
         p[2] = s_std;
         p[3] = (float)s_mean;
         p[4] = apply ? 1.f : 0.f;
-        p[5] = p[6] = p[7] = 0.f;
+        p[5] = 1.0f / p[1];
+        p[6] = p[7] = 0.f;
     }
 }
 
@@ -150,15 +156,16 @@ int check_warp_desc(const vfd_warp_desc* d) {
 using namespace vfd;
 
 extern "C" int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const float* T, double* stats,
-                              float* params, void* stream) {
+                              float* params, float* raw, void* stream) {
     int rc = check_warp_desc(d);
     if (rc) return rc;
-    if (!depth || !T || !stats || !params) return VFD_ERR_NULL;
+    if (!depth || !T || !stats || !params || !raw) return VFD_ERR_NULL;
+    if (reinterpret_cast<uintptr_t>(raw) & 15) return VFD_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     const int NW = d->n_src + (1 + d->n_src) * VFD_WARP_NBR;
     if (cudaMemsetAsync(stats, 0, (size_t)d->B * d->n_call * NW * 8 * sizeof(double), st) != cudaSuccess)
         return VFD_ERR_CUDA;
-    StatsArgs a = {*d, depth, T, stats, params};
+    StatsArgs a = {*d, depth, T, stats, params, reinterpret_cast<float4*>(raw)};
     const int HW = d->H * d->W, per = kStatThreads * kStatPx;
     dim3 grid((HW + per - 1) / per, d->n_call, d->B);
     warp_stats_kernel<<<grid, kStatThreads, 0, st>>>(a);

@@ -1,77 +1,90 @@
-// Shared-memory tile of the fused warp + photometric-loss kernels: every pixel of a (32+2h) x (8+2h) region of one
-// target camera is warped NW times ONCE, normalised, and the per-frame predictions the loss consumes are kept as
-// channel planes:
-//   pred[k]   k < VFD_WARP_SRC: temporal warp of frame 1+k (('color', f, 0));  k = VFD_WARP_SRC + fi: sum over the
-//             neighbours of the warps of frame fi (('overlap', f, 0), view_rendering.py:193-198)
-//   tgt       the target image, idn[k] the un-warped source frames of the same camera (identity reprojection,
-//             single_cam_loss.py:33-43), omask[fi] the summed neighbour masks, cmask[k] the temporal warp masks.
+// Shared-memory tile of the fused photometric-loss kernels.  Pass 1 (warp_stats.cu) left the raw warp of every
+// source image as one float4 (r, g, b, warp mask) per pixel; here a (32+2h) x (8+2h) region of one target camera is
+// normalised (intensity alignment, view_rendering.py:58-59), the two neighbours of each frame are summed
+// (view_rendering.py:193-198) and the eight images the loss compares are laid out as float2 pairs for the packed SSIM
+// of warp_ssim.cuh:  img[channel][pair][pixel], pairs as listed there.
 #pragma once
 #include "warp_ssim.cuh"
 
 namespace vfd {
 
 constexpr int kTileW = 32, kTileH = 8, kTileThreads = kTileW * kTileH;
-constexpr int kNPred = VFD_WARP_SRC + 1 + VFD_WARP_SRC;   // 5
 
 template <int HALO>
 struct Region {
     static constexpr int RW = kTileW + 2 * HALO, RH = kTileH + 2 * HALO, R = RW * RH;
-    static constexpr int kPred = 0;                          // [kNPred][3][R]
-    static constexpr int kTgt = kPred + kNPred * 3 * R;      // [3][R]
-    static constexpr int kIdn = kTgt + 3 * R;                // [VFD_WARP_SRC][3][R]
-    static constexpr int kOmask = kIdn + VFD_WARP_SRC * 3 * R;   // [1+VFD_WARP_SRC][R]
-    static constexpr int kCmask = kOmask + (1 + VFD_WARP_SRC) * R;   // [VFD_WARP_SRC][R]
+    static constexpr int kImg = 0;                                   // float2 [3][kPairs][R]
+    static constexpr int kOmask = kImg + 2 * 3 * kPairs * R;         // float  [1+VFD_WARP_SRC][R] summed neighbour masks
+    static constexpr int kCmask = kOmask + (1 + VFD_WARP_SRC) * R;   // float  [VFD_WARP_SRC][R]   temporal warp masks
     static constexpr int kFloats = kCmask + VFD_WARP_SRC * R;
 };
 
-// Phase A: warp every in-image pixel of the region and fill the planes.  Caller synchronises afterwards.
+// normalised prediction of warp j from its raw sample (view_rendering.py:58-59), in the reference's operation order
+//   ((w - w_mean) / (w_std + 1e-8)) * s_std + s_mean, then * mask
+// prm = {w_mean, w_std+1e-8, s_std, s_mean, apply, RN(1 / (w_std+1e-8))}.  The quotient is formed as q = t*r;
+// q += fma(-den, q, t) * r (Markstein), which is the correctly rounded t / den without a division instruction.
+// apply == 0 (alignment off, or the batch-wide early exit of :50-53): the raw, un-masked warp.
+__device__ __forceinline__ float warp_normalise(const float* prm, float w, float m) {
+    if (prm[4] == 0.f) return w;
+    const float t = VFD_SUB(w, prm[0]);
+    float q = VFD_MUL(t, prm[5]);
+    q = VFD_FMA(VFD_FMA(-prm[1], q, t), prm[5], q);
+    return VFD_MUL(VFD_ADD(VFD_MUL(q, prm[2]), prm[3]), m);
+}
+// d pred / d w
+__device__ __forceinline__ float warp_normalise_grad(const float* prm, float m) {
+    return prm[4] == 0.f ? 1.f : m * prm[2] * prm[5];
+}
+
+// where warp j's normalised image and mask go in the tile: float offset of its (pair, component) inside one
+// channel's block of pairs, and its mask plane
+__device__ __forceinline__ void warp_slot(int j, int n_src, int R, int omask0, int cmask0, int* img_off, int* msk_off) {
+    if (j < n_src) {                 // temporal warp of frame 1+j -> pair 0, component j
+        *img_off = j;
+        *msk_off = cmask0 + j * R;
+    } else {
+        const int fi = (j - n_src) / VFD_WARP_NBR;          // 0: spatial -> pair 2.x; 1, 2: spatio-temporal -> pair 1.x/.y
+        *img_off = fi == 0 ? 2 * R * 2 : 1 * R * 2 + (fi - 1);
+        *msk_off = omask0 + fi * R;
+    }
+}
+
+// Phase A.  Caller synchronises afterwards.  Pixels of the region outside the image are never read.
 template <int HALO>
 __device__ __forceinline__ void fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
-                                            const float* __restrict__ depth, float* sm) {
+                                            const float4* __restrict__ raw, float* sm) {
     using Rg = Region<HALO>;
     const int W = d.W, H = d.H, HW = H * W, cam = d.cam0 + ci, NW = ctx.NW, n_src = d.n_src;
     const float* ref = d.color[0] + (size_t)(b * d.num_cams + cam) * 3 * HW;
+    const float* src0 = d.color[1] + (size_t)(b * d.num_cams + cam) * 3 * HW;
+    const float* src1 = d.color[n_src] + (size_t)(b * d.num_cams + cam) * 3 * HW;   // == src0 when n_src == 1 (unused)
+    float2* img = reinterpret_cast<float2*>(sm + Rg::kImg);
+    constexpr int kChan = kPairs * Rg::R * 2;      // floats per channel block
     for (int r = threadIdx.x; r < Rg::R; r += kTileThreads) {
         const int x = ox + r % Rg::RW, y = oy + r / Rg::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
-        float X[3];
-        vfd_backproject(ctx.invK, (float)x, (float)y, __ldg(depth + p), X);
-        float ov[1 + VFD_WARP_SRC][3], om[1 + VFD_WARP_SRC];
+        // this thread owns pixel r of every plane: zero the accumulated ones, place the un-warped images
 #pragma unroll
-        for (int f = 0; f <= VFD_WARP_SRC; ++f) { ov[f][0] = ov[f][1] = ov[f][2] = 0.f; om[f] = 0.f; }
+        for (int c = 0; c < 3; ++c) {
+            float2* pc = img + c * kPairs * Rg::R + r;
+            pc[0 * Rg::R] = make_float2(0.f, 0.f);
+            pc[1 * Rg::R] = make_float2(0.f, 0.f);
+            pc[2 * Rg::R] = make_float2(0.f, __ldg(src0 + c * HW + p));
+            pc[3 * Rg::R] = make_float2(__ldg(src1 + c * HW + p), __ldg(ref + c * HW + p));
+        }
+#pragma unroll
+        for (int f = 0; f < 1 + 2 * VFD_WARP_SRC; ++f) sm[Rg::kOmask + f * Rg::R + r] = 0.f;   // omask + cmask planes
         for (int j = 0; j < NW; ++j) {
             if (!ctx.active[j]) continue;
-            const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
-            float n[3];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) n[c] = warp_normalise(ctx.prm[j], s.v[c], s.m);
-            if (j < n_src) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) sm[Rg::kPred + (j * 3 + c) * Rg::R + r] = n[c];
-                sm[Rg::kCmask + j * Rg::R + r] = s.m;
-            } else {
-                const int fi = (j - n_src) / VFD_WARP_NBR;
-#pragma unroll
-                for (int f = 0; f <= VFD_WARP_SRC; ++f)
-                    if (f == fi) {
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) ov[f][c] = VFD_ADD(ov[f][c], n[c]);
-                        om[f] = VFD_ADD(om[f], s.m);
-                    }
-            }
-        }
-        for (int f = 0; f <= n_src; ++f) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) sm[Rg::kPred + ((VFD_WARP_SRC + f) * 3 + c) * Rg::R + r] = ov[f][c];
-            sm[Rg::kOmask + f * Rg::R + r] = om[f];
-        }
-#pragma unroll
-        for (int c = 0; c < 3; ++c) sm[Rg::kTgt + c * Rg::R + r] = __ldg(ref + c * HW + p);
-        for (int k = 0; k < n_src; ++k) {
-            const float* src = d.color[1 + k] + (size_t)(b * d.num_cams + cam) * 3 * HW;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) sm[Rg::kIdn + (k * 3 + c) * Rg::R + r] = __ldg(src + c * HW + p);
+            const float4 w = __ldg(raw + (size_t)j * HW + p);
+            int io, mo;
+            warp_slot(j, n_src, Rg::R, Rg::kOmask, Rg::kCmask, &io, &mo);
+            float* dst = sm + Rg::kImg + io + 2 * r;
+            dst[0] = VFD_ADD(dst[0], warp_normalise(ctx.prm[j], w.x, w.w));
+            dst[kChan] = VFD_ADD(dst[kChan], warp_normalise(ctx.prm[j], w.y, w.w));
+            dst[2 * kChan] = VFD_ADD(dst[2 * kChan], warp_normalise(ctx.prm[j], w.z, w.w));
+            sm[mo + r] = VFD_ADD(sm[mo + r], w.w);
         }
     }
 }
@@ -84,42 +97,32 @@ struct PixelLoss {
     int sel_reproj, sel_st;          // which frame won each min (gradient routing)
 };
 
+// g (GRAD): SSIM derivative coefficients of pairs 0..2 (see warp_ssim.cuh)
 template <int HALO, bool GRAD>
 __device__ __forceinline__ PixelLoss pixel_loss(const float* sm, const vfd_warp_desc& d, int x, int y, int ox, int oy,
-                                                float rmask, const float* noise /*[n_src]*/, SsimGrad* g /*[kNPred]*/) {
+                                                float rmask, const float* noise /*[VFD_WARP_SRC]*/, SsimGrad2* g) {
     using Rg = Region<HALO>;
-    const int n_src = d.n_src;
+    const bool two = d.n_src > 1;
     int idx[9];
     tap_indices(x, y, d.W, d.H, ox, oy, Rg::RW, idx);
     const int ctr = (y - oy) * Rg::RW + (x - ox);
-    const float* tgt = sm + Rg::kTgt;
-    const TargetStats ts = target_stats(tgt, Rg::R, idx);
+    float2 L[kPairs];
+    photometric8<GRAD>(reinterpret_cast<const float2*>(sm + Rg::kImg), Rg::R, idx, L, g);
     PixelLoss o;
-    float ident = 0.f;
-    o.reproj = 0.f; o.sel_reproj = 0; o.st = 0.f; o.sel_st = 0; o.st_mask = 0.f;
-#pragma unroll
-    for (int k = 0; k < VFD_WARP_SRC; ++k) {
-        if (k >= n_src) break;
-        const float l = photometric<GRAD>(sm + Rg::kPred + k * 3 * Rg::R, tgt, Rg::R, idx, ctr, ts, GRAD ? g + k : nullptr);
-        if (k == 0 || l < o.reproj) { o.reproj = l; o.sel_reproj = k; }
-        float li = photometric<false>(sm + Rg::kIdn + k * 3 * Rg::R, tgt, Rg::R, idx, ctr, ts, nullptr);
-        li = VFD_ADD(li, VFD_MUL(0.00001f, noise[k]));
-        if (k == 0 || li < ident) ident = li;
-    }
+    // temporal reprojection: torch.min over frames keeps the first minimum on a tie
+    o.sel_reproj = (two && L[0].y < L[0].x) ? 1 : 0;
+    o.reproj = o.sel_reproj ? L[0].y : L[0].x;
+    // identity reprojection + tie-break noise (single_cam_loss.py:44-47)
+    float ident = VFD_ADD(L[2].y, VFD_MUL(0.00001f, noise[0]));
+    if (two) ident = fminf(ident, VFD_ADD(L[3].x, VFD_MUL(0.00001f, noise[1])));
     // argmin over cat([reproj, identity]) == 0: the first minimum wins a tie (loss_util.py:15-17)
     o.automask = VFD_MUL((o.reproj <= ident) ? 1.f : 0.f, rmask);
     o.sp_mask = VFD_MUL(rmask, sm[Rg::kOmask + ctr]);
-    o.spatial = photometric<GRAD>(sm + Rg::kPred + VFD_WARP_SRC * 3 * Rg::R, tgt, Rg::R, idx, ctr, ts,
-                                  GRAD ? g + VFD_WARP_SRC : nullptr);
-#pragma unroll
-    for (int k = 0; k < VFD_WARP_SRC; ++k) {
-        if (k >= n_src) break;
-        const float l = photometric<GRAD>(sm + Rg::kPred + (VFD_WARP_SRC + 1 + k) * 3 * Rg::R, tgt, Rg::R, idx, ctr, ts,
-                                          GRAD ? g + VFD_WARP_SRC + 1 + k : nullptr);
-        if (k == 0 || l < o.st) { o.st = l; o.sel_st = k; }
-        const float m = VFD_MUL(VFD_MUL(rmask, sm[Rg::kOmask + (1 + k) * Rg::R + ctr]), o.automask);
-        o.st_mask = (k == 0) ? m : fmaxf(o.st_mask, m);
-    }
+    o.spatial = L[2].x;
+    o.sel_st = (two && L[1].y < L[1].x) ? 1 : 0;
+    o.st = o.sel_st ? L[1].y : L[1].x;
+    o.st_mask = VFD_MUL(VFD_MUL(rmask, sm[Rg::kOmask + Rg::R + ctr]), o.automask);
+    if (two) o.st_mask = fmaxf(o.st_mask, VFD_MUL(VFD_MUL(rmask, sm[Rg::kOmask + 2 * Rg::R + ctr]), o.automask));
     return o;
 }
 

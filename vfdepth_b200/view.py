@@ -65,17 +65,19 @@ class WarpInputs:
 
 
 def warp_stats(wi, depth, T, cam0=0):
-    """pass 1 -> params [B,n_call,NW,8] (constants for autograd: view_rendering.py:45 runs under no_grad)."""
+    """pass 1 -> (params [B,n_call,NW,8], raw [B,n_call,NW,H,W,4]): the intensity-alignment constants (autograd
+    constants: view_rendering.py:45 runs under no_grad) and the raw warps (r, g, b, mask) the loss passes read back."""
     n_call = depth.shape[1]
     NW = num_warps(wi.n_src)
     _chk(depth, 'depth', (wi.B, n_call, wi.H, wi.W))
     _chk(T, 'T', (wi.B, n_call, NW, 4, 4))
     stats = torch.empty((wi.B, n_call, NW, 8), device=wi.device, dtype=torch.float64)
     params = torch.empty((wi.B, n_call, NW, 8), device=wi.device, dtype=torch.float32)
+    raw = torch.empty((wi.B, n_call, NW, wi.H, wi.W, 4), device=wi.device, dtype=torch.float32)
     d = wi.desc(cam0, n_call)
     _lib.call('vfd_warp_stats', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(stats), _lib.ptr(params),
-              _stream())
-    return params
+              _lib.ptr(raw), _stream())
+    return params, raw
 
 
 VIEW_KEYS = ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss', 'reproj_mask', 'grid', 'selection')
@@ -98,7 +100,7 @@ class _WarpLoss(torch.autograd.Function):
     """(depth, T) -> masked-loss numerators [n_call,3] (differentiable) and denominators [n_call,3]."""
 
     @staticmethod
-    def forward(ctx, depth, T, wi, params, noise, cam0, views_struct):
+    def forward(ctx, depth, T, wi, params, raw, noise, cam0, views_struct):
         n_call = depth.shape[1]
         _chk(depth, 'depth', (wi.B, n_call, wi.H, wi.W))
         _chk(T, 'T', (wi.B, n_call, num_warps(wi.n_src), 4, 4))
@@ -107,9 +109,9 @@ class _WarpLoss(torch.autograd.Function):
         d = wi.desc(cam0, n_call)
         vptr = ctypes.byref(views_struct) if views_struct is not None else None
         _lib.call('vfd_warp_loss_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
-                  _lib.ptr(noise), _lib.ptr(sums), vptr, _stream())
+                  _lib.ptr(raw), _lib.ptr(noise), _lib.ptr(sums), vptr, _stream())
         ctx.wi, ctx.cam0 = wi, cam0
-        ctx.save_for_backward(depth, T, params, noise)
+        ctx.save_for_backward(depth, T, params, raw, noise)
         s = sums.float()
         num, den = s[:, 0:6:2].contiguous(), s[:, 1:6:2].contiguous()
         ctx.mark_non_differentiable(den)
@@ -117,7 +119,7 @@ class _WarpLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, d_num, _):
-        depth, T, params, noise = ctx.saved_tensors
+        depth, T, params, raw, noise = ctx.saved_tensors
         wi = ctx.wi
         n_call = depth.shape[1]
         d = wi.desc(ctx.cam0, n_call)
@@ -127,22 +129,21 @@ class _WarpLoss(torch.autograd.Function):
         nbytes = _lib.load().vfd_warp_bwd_workspace_bytes(ctypes.byref(d))
         ws = torch.empty((max(nbytes, 4) // 4,), device=wi.device, dtype=torch.float32)
         _lib.call('vfd_warp_loss_bwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
-                  _lib.ptr(noise), _lib.ptr(d_num), _lib.ptr(d_depth), _lib.ptr(d_T), _lib.ptr(ws),
+                  _lib.ptr(raw), _lib.ptr(noise), _lib.ptr(d_num), _lib.ptr(d_depth), _lib.ptr(d_T), _lib.ptr(ws),
                   ctypes.c_size_t(nbytes), _stream())
-        return d_depth, d_T, None, None, None, None, None
+        return d_depth, d_T, None, None, None, None, None, None
 
 
-def warp_loss_sums(wi, depth, T, noise, cam0=0, params=None, want_views=()):
+def warp_loss_sums(wi, depth, T, noise, cam0=0, stats=None, want_views=()):
     """-> (num [n_call,3], den [n_call,3], views dict).  Columns: reprojection, spatial, spatio-temporal
     (single_cam_loss.py:55, multi_cam_loss.py:29, :59 are num / (den + 1e-8))."""
     depth = depth.contiguous()
     T = T.contiguous()
-    if params is None:
-        params = warp_stats(wi, depth.detach(), T.detach(), cam0)
+    params, raw = stats if stats is not None else warp_stats(wi, depth.detach(), T.detach(), cam0)
     vstruct, views = (None, {})
     if want_views:
         vstruct, views = _alloc_views(wi, depth.shape[1], tuple(want_views))
-    num, den = _WarpLoss.apply(depth, T, wi, params, noise, cam0, vstruct)
+    num, den = _WarpLoss.apply(depth, T, wi, params, raw, noise, cam0, vstruct)
     return num, den, views
 
 
@@ -246,8 +247,8 @@ class ViewRendering(torch.nn.Module):
         tv = outputs[('cam', cam)]
         depth = tv[('depth', 0)].reshape(wi.B, 1, wi.H, wi.W)
         T = camera_transforms(wi, tv, rel_pose_dict, cam)
-        params = warp_stats(wi, depth.detach().contiguous(), T.detach().contiguous(), cam)
-        tv[_CTX] = dict(wi=wi, depth=depth, T=T, params=params)
+        stats = warp_stats(wi, depth.detach().contiguous(), T.detach().contiguous(), cam)
+        tv[_CTX] = dict(wi=wi, depth=depth, T=T, stats=stats)
         if self.materialize:
             self.render(inputs, outputs, cam)
 
@@ -258,7 +259,7 @@ class ViewRendering(torch.nn.Module):
         c = tv[_CTX]
         wi = c['wi']
         noise = torch.zeros((wi.B, 1, wi.n_src, wi.H, wi.W), device=wi.device)
-        _, _, v = warp_loss_sums(wi, c['depth'].detach(), c['T'].detach(), noise, cam, c['params'],
+        _, _, v = warp_loss_sums(wi, c['depth'].detach(), c['T'].detach(), noise, cam, c['stats'],
                                  ('color', 'color_mask', 'overlap', 'overlap_mask'))
         for k, f in enumerate(wi.frame_ids[1:]):
             tv[('color', f, 0)] = v['color'][:, 0, k]
@@ -288,7 +289,7 @@ class MultiCamLoss(torch.nn.Module):
         wi = c['wi']
         # the reference draws the tie-break noise on the CPU and ships it (single_cam_loss.py:45-46)
         noise = torch.randn((wi.B, wi.n_src, wi.H, wi.W)).to(wi.device).unsqueeze(1)
-        num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['params'], ('reproj_loss', 'reproj_mask'))
+        num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['stats'], ('reproj_loss', 'reproj_mask'))
         tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
         tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
         sm = smooth_loss(inputs[('color', 0, 0)][:, cam], tv[('disp', 0)])
