@@ -1,2 +1,8 @@
-python -m pytest tests/test_warp_gpu.py -x -q > gpurun_out/pytest_warp.log 2>&1; echo "pytest_warp rc=$?" > gpurun_out/rc.log
-python bench.py --steps 5 --no-cpu-baseline --no-e2e > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.log
+# one gpurun call: GPU tests, smoke, bench, kernel bench, then ncu launch list
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest_gpu rc=$?" > gpurun_out/rc.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/rc.log
+python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.log
+python tools/kernel_bench.py > gpurun_out/kernel_bench.log 2>&1; echo "kbench rc=$?" >> gpurun_out/rc.log
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launch.log 2>&1; echo "ncu rc=$?" >> gpurun_out/rc.log
+cat gpurun_out/rc.log; tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/bench.log
