@@ -86,6 +86,29 @@ int vfd_voxel_gather_depth_bwd(const vfd_fusion_desc* d, const float* mask_small
                                const float* Einv, const float* d_x_no, const float* d_x_ov, float* d_feats,
                                void* stream);
 
+/* Which voxels feed which MLP (preprocess_non_overlap :197-207 keeps count==1, preprocess_overlap :209-230 keeps
+ * count==2; the rest of the volume is zero).  Gives every count-1 voxel a row in a compact x_no matrix and every
+ * count-2 voxel a row in a compact x_ov matrix, in voxel order (b major, then n) -- deterministic.
+ *   count   [B,N] u8      cameras that see the voxel (:152), bit-exact
+ *   slot    [B,N] i32     row of the voxel in ITS compact matrix, -1 when count is 0 or >= 3
+ *   idx_no  [>= B*N] i64  out: idx_no[r] = b*N+n of compact x_no row r  (first totals[0] entries are written)
+ *   idx_ov  [>= B*N] i64  same for x_ov (first totals[1] entries)
+ *   totals  [2] i32       device: number of count-1 and count-2 voxels; the caller reads it back to size the MLP GEMMs
+ *   ws                    scratch of vfd_voxel_classify_workspace_bytes(d) bytes, 8-byte aligned */
+size_t vfd_voxel_classify_workspace_bytes(const vfd_fusion_desc* d);
+int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_small, const float* K, const float* Einv,
+                       uint8_t* count, int32_t* slot, int64_t* idx_no, int64_t* idx_ov, int32_t* totals, void* ws,
+                       size_t ws_bytes, void* stream);
+
+/* vfd_voxel_gather_depth_fwd / _bwd on compact rows: x_no [totals[0], ld_no] and x_ov [totals[1], ld_ov] hold one
+ * row per voxel that reaches the corresponding MLP (row = slot[b,n]); voxels with slot < 0 are skipped entirely. */
+int vfd_voxel_gather_depth_compact_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                                       const float* K, const float* Einv, const int32_t* slot, float* x_no,
+                                       float* x_ov, void* stream);
+int vfd_voxel_gather_depth_compact_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                                       const float* Einv, const int32_t* slot, const float* d_x_no,
+                                       const float* d_x_ov, float* d_feats, void* stream);
+
 /* VFNet.backproject_into_voxel, model='pose' (:160-162):  avg [B,N,ld_no] = sum_c feat_c / (count + 1e-7) */
 int vfd_voxel_gather_pose_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
                               const float* K, const float* Einv, float* avg, uint8_t* count, void* stream);

@@ -204,3 +204,47 @@ def test_reduce_dim_handoff_matches_reference_channel_order():
     for c in range(6):
         ref = net.reduce_dim(ref_in[:, c])
         assert H.rel_err(outs[c].detach().cpu(), ref.detach().cpu()) < TOL
+
+
+@pytest.mark.parametrize('B', [1, 3])
+def test_compact_rows_equal_dense_rows(B):
+    """vfd_voxel_classify + the compact gather: counts bit-equal to the dense kernel's, slots number the count-1 /
+    count-2 voxels in voxel order, every compact row is BIT-IDENTICAL to the dense row of its voxel, and the
+    compact backward equals the dense backward fed with the scattered gradient rows."""
+    from vfdepth_b200 import ops
+    dev = _dev()
+    cfg = vcfg.default_config('ddad', batch_size=B, model__fusion_feat_in_dim=32, model__voxel_pre_dim=[8])
+    inputs, extras = make_rig(cfg, seed=31, with_images=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, 32, 16, 'depth', None, dev)
+    to = lambda t: t.to(dev)
+    feats = to(extras['feats_agg'])
+    x_no, x_ov, count = net.gather_rows(feats, to(inputs['mask']), to(inputs[('K', lvl)]),
+                                        to(inputs['extrinsics_inv']))[:3]
+    g = net.geom
+    feats_cl = net._channel_last(feats)
+    mask_small = net._mask_small(to(inputs['mask']))
+    K, Einv = to(inputs[('K', lvl)]).contiguous(), to(inputs['extrinsics_inv']).contiguous()
+    cnt2, slot, idx_no, idx_ov = ops.voxel_classify(mask_small, K, Einv, g)
+    assert torch.equal(cnt2, count)
+    flat = count.flatten()
+    assert torch.equal(idx_no, (flat == 1).nonzero().flatten())
+    assert torch.equal(idx_ov, (flat == 2).nonzero().flatten())
+    s = slot.flatten().long()
+    assert torch.equal(s[idx_no], torch.arange(idx_no.numel(), device=dev))
+    assert torch.equal(s[idx_ov], torch.arange(idx_ov.numel(), device=dev))
+    assert bool((s[(flat != 1) & (flat != 2)] == -1).all())
+    assert idx_no.numel() > 0 and idx_ov.numel() > 0
+    f = feats_cl.clone().requires_grad_(True)
+    c_no, c_ov = ops.voxel_gather_depth_compact(f, mask_small, K, Einv, slot, idx_no.numel(), idx_ov.numel(), g)
+    assert torch.equal(c_no, x_no.flatten(0, 1)[idx_no])
+    assert torch.equal(c_ov, x_ov.flatten(0, 1)[idx_ov])
+    # backward: same gradient rows through both paths
+    u_no, u_ov = torch.randn_like(c_no), torch.randn_like(c_ov)
+    d_c, = torch.autograd.grad((c_no * u_no).sum() + (c_ov * u_ov).sum(), f)
+    f2 = feats_cl.clone().requires_grad_(True)
+    d_no, d_ov, _ = ops.voxel_gather_depth(f2, mask_small, K, Einv, g)
+    U_no = torch.zeros_like(d_no).flatten(0, 1).index_copy(0, idx_no, u_no).view_as(d_no)
+    U_ov = torch.zeros_like(d_ov).flatten(0, 1).index_copy(0, idx_ov, u_ov).view_as(d_ov)
+    d_d, = torch.autograd.grad((d_no * U_no).sum() + (d_ov * U_ov).sum(), f2)
+    assert H.rel_err(d_c, d_d) < 1e-5      # atomics: summation order differs

@@ -39,11 +39,18 @@ class WarpWorkload:
     def step_resident(self):
         return self.step(self.inputs, self.depth, self.disp, self.noise, self.T)
 
-    def step_e2e(self):
+    def upload(self):
+        """host (pinned) -> device copies of one step's inputs, on the current stream."""
         nb = dict(non_blocking=True)
         inputs = {k: v.to(self.dev, **nb) for k, v in self.h_inputs.items()}
-        total, grads = self.step(inputs, self.h_depth.to(self.dev, **nb), self.h_disp.to(self.dev, **nb),
-                                 self.h_noise.to(self.dev, **nb), {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
+        return (inputs, self.h_depth.to(self.dev, **nb), self.h_disp.to(self.dev, **nb),
+                self.h_noise.to(self.dev, **nb), {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
+
+    def compute(self, staged):
+        return self.step(*staged)
+
+    def download(self, result):
+        total, grads = result
         self.h_out.copy_(torch.cat(grads[:6], 1), non_blocking=True)
         self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
 

@@ -31,6 +31,8 @@ struct GatherArgs {
     const float* d_x_no;
     const float* d_x_ov;
     float* d_feats;
+    // compact rows (only voxels with count 1 / 2 own a row); NULL = dense rows, one per voxel
+    const int32_t* slot;
 };
 
 struct CamSlot {   // one (voxel, camera) projection, kept in shared memory between the two phases
@@ -128,6 +130,8 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_fwd_kerne
     const long n = n0 + lane;
     unsigned vmask = project_voxel(a, s_mat, b, n, lane, n < N, s_slot[warp]);
     if (n < N && a.count) a.count[(size_t)b * N + n] = (uint8_t)__popc(vmask);
+    int my_slot = -1;
+    if (MODE == 0 && a.slot && n < N) my_slot = __ldg(a.slot + (size_t)b * N + n);
     __syncwarp();
 
     const int C = d.C, hw = d.h * d.w;
@@ -135,6 +139,8 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_fwd_kerne
     for (int j = 0; j < jmax; ++j) {
         unsigned m = __shfl_sync(0xffffffffu, vmask, j);
         const int cnt = __popc(m);
+        const int sl = __shfl_sync(0xffffffffu, my_slot, j);
+        if (MODE == 0 && a.slot && sl < 0) continue;   // compact rows: count 0 or >= 3 feeds neither MLP
         float4 acc0[ITERS], acc1[ITERS];
 #pragma unroll
         for (int it = 0; it < ITERS; ++it) { acc0[it] = f4_zero(); acc1[it] = f4_zero(); }
@@ -161,8 +167,10 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_fwd_kerne
             }
             if (g1) z1 += s.zrel; else z0 += s.zrel;
         }
-        const size_t row = (size_t)b * N + n0 + j;
+        const size_t row = a.slot ? (size_t)sl : (size_t)b * N + n0 + j;
         if (MODE == 0) {
+            // dense: both rows of every voxel; compact: the x_no row of a count-1 voxel, the x_ov row of a count-2 one
+            const bool wr_no = !a.slot || cnt == 1, wr_ov = !a.slot || cnt == 2;
             float* rno = a.x_no + row * d.ld_no;
             float* rov = a.x_ov + row * d.ld_ov;
             const float keep = (cnt == 1) ? 1.f : 0.f;
@@ -172,18 +180,23 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_fwd_kerne
                 if (k < C) {
                     float4 s = acc0[it];
                     f4_add(s, acc1[it]);
-                    st_stream_f4(rno + k, f4_scale(keep, s));
-                    st_stream_f4(rov + k, acc0[it]);
-                    st_stream_f4(rov + d.half_ov + k, acc1[it]);
+                    if (wr_no) st_stream_f4(rno + k, f4_scale(keep, s));
+                    if (wr_ov) {
+                        st_stream_f4(rov + k, acc0[it]);
+                        st_stream_f4(rov + d.half_ov + k, acc1[it]);
+                    }
                 }
             }
             // tail columns: relative depth at column C, then zero padding
-            for (int k = C + lane * 4; k < d.ld_no; k += 128)
-                st_stream_f4(rno + k, make_float4(k == C ? keep * (z0 + z1) : 0.f, 0.f, 0.f, 0.f));
-            for (int k = C + lane * 4; k < d.half_ov; k += 128)
-                st_stream_f4(rov + k, make_float4(k == C ? z0 : 0.f, 0.f, 0.f, 0.f));
-            for (int k = d.half_ov + C + lane * 4; k < d.ld_ov; k += 128)
-                st_stream_f4(rov + k, make_float4(k == d.half_ov + C ? z1 : 0.f, 0.f, 0.f, 0.f));
+            if (wr_no)
+                for (int k = C + lane * 4; k < d.ld_no; k += 128)
+                    st_stream_f4(rno + k, make_float4(k == C ? keep * (z0 + z1) : 0.f, 0.f, 0.f, 0.f));
+            if (wr_ov) {
+                for (int k = C + lane * 4; k < d.half_ov; k += 128)
+                    st_stream_f4(rov + k, make_float4(k == C ? z0 : 0.f, 0.f, 0.f, 0.f));
+                for (int k = d.half_ov + C + lane * 4; k < d.ld_ov; k += 128)
+                    st_stream_f4(rov + k, make_float4(k == d.half_ov + C ? z1 : 0.f, 0.f, 0.f, 0.f));
+            }
         } else {
             float* ravg = a.x_no + row * d.ld_no;
             const float den = VFD_ADD((float)cnt, 1e-7f);  // count + 1e-7 (:162)
@@ -217,15 +230,19 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_bwd_kerne
     if (n0 >= N) return;
     const long n = n0 + lane;
     unsigned vmask = project_voxel(a, s_mat, b, n, lane, n < N, s_slot[warp]);
+    int my_slot = -1;
+    if (MODE == 0 && a.slot && n < N) my_slot = __ldg(a.slot + (size_t)b * N + n);
     __syncwarp();
 
     const int C = d.C, hw = d.h * d.w;
     const int jmax = min(VFD_WARP, (int)(N - n0));
     for (int j = 0; j < jmax; ++j) {
         unsigned m = __shfl_sync(0xffffffffu, vmask, j);
+        const int sl = __shfl_sync(0xffffffffu, my_slot, j);
         if (!m) continue;
+        if (MODE == 0 && a.slot && sl < 0) continue;
         const int cnt = __popc(m);
-        const size_t row = (size_t)b * N + n0 + j;
+        const size_t row = a.slot ? (size_t)sl : (size_t)b * N + n0 + j;
         float4 gno[ITERS];
         if (MODE == 0) {
 #pragma unroll
@@ -253,7 +270,7 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_bwd_kerne
                 const int k = it * 128 + lane * 4;
                 if (k < C) {
                     float4 g = gno[it];
-                    if (MODE == 0) {
+                    if (MODE == 0 && (!a.slot || cnt == 2)) {
                         float4 o = ld_stream_f4(a.d_x_ov + row * d.ld_ov + (d.group[c] ? d.half_ov : 0) + k);
                         f4_add(g, o);
                     }
@@ -264,6 +281,121 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_bwd_kerne
                 }
             }
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Classification: which voxels feed which MLP.  preprocess_non_overlap (:197-207) multiplies its input AND its
+// output by [count==1], preprocess_overlap (:209-230) by [count==2]; a voxel seen by 0 or >=3 cameras feeds
+// neither.  Three small launches give every count-1 / count-2 voxel a row ("slot") in a compact matrix, in voxel
+// order (deterministic): count + per-block totals, an exclusive scan of the block totals, slots + index lists.
+// ---------------------------------------------------------------------------------------------------------
+struct ClassifyArgs {
+    vfd_fusion_desc d;
+    const float* mask_small;
+    const float* K;
+    const float* Einv;
+    uint8_t* count;
+    int32_t* slot;
+    int64_t* idx_no;
+    int64_t* idx_ov;
+    int32_t* totals;
+    int2* block_tot;   // [B * blocks_per_rig]
+};
+
+__global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_count_kernel(const ClassifyArgs c) {
+    const vfd_fusion_desc& d = c.d;
+    __shared__ float s_mat[VFD_MAX_CAMS * 32];
+    __shared__ int s_n1[kGatherWarps], s_n2[kGatherWarps];
+    const int b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int N = d.X * d.Y * d.Z;
+    GatherArgs a = {};
+    a.d = d; a.mask_small = c.mask_small; a.K = c.K; a.Einv = c.Einv;
+    load_mats(a, b, s_mat);
+    __syncthreads();
+    const long n = ((long)blockIdx.x * kGatherWarps + warp) * VFD_WARP + lane;
+    int cnt = 0;
+    if (n < N) {
+        const int xi = (int)(n % d.X), yi = (int)((n / d.X) % d.Y), zi = (int)(n / ((long)d.X * d.Y));
+        const float x = __ldg(d.axis_x + xi), y = __ldg(d.axis_y + yi), z = __ldg(d.axis_z + zi);
+        for (int cam = 0; cam < d.num_cams; ++cam) {
+            const float* Einv = s_mat + cam * 32;
+            float v[3], g[2];
+            vfd_voxel_to_pixel(Einv, Einv + 16, x, y, z, d.w, d.h, v, g);
+            if (vfd_in_bounds2(g[0], g[1]) && v[2] > 0.f) {
+                const float fx = rintf(vfd_unnormalize(g[0], d.w)), fy = rintf(vfd_unnormalize(g[1], d.h));
+                if (fx >= 0.f && fx <= (float)(d.w - 1) && fy >= 0.f && fy <= (float)(d.h - 1))
+                    cnt += __ldg(c.mask_small + ((size_t)(b * d.num_cams + cam) * d.h + (int)fy) * d.w + (int)fx) > 0.5f;
+            }
+        }
+        c.count[(size_t)b * N + n] = (uint8_t)cnt;
+    }
+    const unsigned b1 = __ballot_sync(0xffffffffu, cnt == 1), b2 = __ballot_sync(0xffffffffu, cnt == 2);
+    if (lane == 0) { s_n1[warp] = __popc(b1); s_n2[warp] = __popc(b2); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t1 = 0, t2 = 0;
+        for (int i = 0; i < kGatherWarps; ++i) { t1 += s_n1[i]; t2 += s_n2[i]; }
+        c.block_tot[(size_t)b * gridDim.x + blockIdx.x] = make_int2(t1, t2);
+    }
+}
+
+// single CTA: exclusive scan of the per-block totals (in place), grand totals to totals[0..1]
+__global__ void __launch_bounds__(1024) voxel_scan_kernel(int2* block_tot, int n, int32_t* totals) {
+    __shared__ int2 s_warp[32];
+    __shared__ int2 s_carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = make_int2(0, 0);
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int2 v = i < n ? block_tot[i] : make_int2(0, 0);
+        int2 inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int ux = __shfl_up_sync(0xffffffffu, inc.x, o), uy = __shfl_up_sync(0xffffffffu, inc.y, o);
+            if (lane >= o) { inc.x += ux; inc.y += uy; }
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int2 w = s_warp[lane], winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int ux = __shfl_up_sync(0xffffffffu, winc.x, o), uy = __shfl_up_sync(0xffffffffu, winc.y, o);
+                if (lane >= o) { winc.x += ux; winc.y += uy; }
+            }
+            s_warp[lane] = make_int2(winc.x - w.x, winc.y - w.y);   // exclusive warp offsets
+        }
+        __syncthreads();
+        const int2 carry = s_carry, wo = s_warp[warp];
+        if (i < n) block_tot[i] = make_int2(carry.x + wo.x + inc.x - v.x, carry.y + wo.y + inc.y - v.y);
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = make_int2(carry.x + wo.x + inc.x, carry.y + wo.y + inc.y);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { totals[0] = s_carry.x; totals[1] = s_carry.y; }
+}
+
+__global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_slot_kernel(const ClassifyArgs c) {
+    const vfd_fusion_desc& d = c.d;
+    __shared__ int s_n1[kGatherWarps], s_n2[kGatherWarps];
+    const int b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int N = d.X * d.Y * d.Z;
+    const long n = ((long)blockIdx.x * kGatherWarps + warp) * VFD_WARP + lane;
+    const int cnt = n < N ? c.count[(size_t)b * N + n] : 0;
+    const unsigned b1 = __ballot_sync(0xffffffffu, cnt == 1), b2 = __ballot_sync(0xffffffffu, cnt == 2);
+    if (lane == 0) { s_n1[warp] = __popc(b1); s_n2[warp] = __popc(b2); }
+    __syncthreads();
+    int2 off = c.block_tot[(size_t)b * gridDim.x + blockIdx.x];
+    for (int i = 0; i < warp; ++i) { off.x += s_n1[i]; off.y += s_n2[i]; }
+    const unsigned below = (1u << lane) - 1u;
+    if (n < N) {
+        const size_t row = (size_t)b * N + n;
+        int sl = -1;
+        if (cnt == 1) { sl = off.x + __popc(b1 & below); c.idx_no[sl] = (int64_t)row; }
+        if (cnt == 2) { sl = off.y + __popc(b2 & below); c.idx_ov[sl] = (int64_t)row; }
+        c.slot[row] = sl;
     }
 }
 
@@ -374,4 +506,63 @@ extern "C" int vfd_voxel_gather_pose_bwd(const vfd_fusion_desc* d, const float* 
     a.d = *d; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.d_x_no = d_avg;
     if ((rc = bwd_common(d, a, d_feats, (cudaStream_t)stream))) return rc;
     return launch<1>(a, true, (cudaStream_t)stream);
+}
+
+extern "C" size_t vfd_voxel_classify_workspace_bytes(const vfd_fusion_desc* d) {
+    if (!d || d->B < 1) return 0;
+    const long N = (long)d->X * d->Y * d->Z;
+    const long blocks = (N + kGatherWarps * VFD_WARP - 1) / (kGatherWarps * VFD_WARP);
+    return (size_t)d->B * blocks * sizeof(int2);
+}
+
+extern "C" int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                                  const float* Einv, uint8_t* count, int32_t* slot, int64_t* idx_no,
+                                  int64_t* idx_ov, int32_t* totals, void* ws, size_t ws_bytes, void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if (!mask_small || !K || !Einv || !count || !slot || !idx_no || !idx_ov || !totals || !ws) return VFD_ERR_NULL;
+    if (ws_bytes < vfd_voxel_classify_workspace_bytes(d)) return VFD_ERR_WORKSPACE;
+    if (reinterpret_cast<uintptr_t>(ws) & 7) return VFD_ERR_ALIGN;
+    const long N = (long)d->X * d->Y * d->Z;
+    if ((long)d->B * N >= (1L << 31)) return VFD_ERR_DESC;
+    ClassifyArgs c = {};
+    c.d = *d; c.mask_small = mask_small; c.K = K; c.Einv = Einv; c.count = count; c.slot = slot;
+    c.idx_no = idx_no; c.idx_ov = idx_ov; c.totals = totals; c.block_tot = static_cast<int2*>(ws);
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid((unsigned)((N + kGatherWarps * VFD_WARP - 1) / (kGatherWarps * VFD_WARP)), d->B);
+    voxel_count_kernel<<<grid, kGatherWarps * VFD_WARP, 0, st>>>(c);
+    voxel_scan_kernel<<<1, 1024, 0, st>>>(c.block_tot, (int)(grid.x * grid.y), totals);
+    voxel_slot_kernel<<<grid, kGatherWarps * VFD_WARP, 0, st>>>(c);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+extern "C" int vfd_voxel_gather_depth_compact_fwd(const vfd_fusion_desc* d, const float* feats,
+                                                  const float* mask_small, const float* K, const float* Einv,
+                                                  const int32_t* slot, float* x_no, float* x_ov, void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, true))) return rc;
+    if (!feats || !mask_small || !K || !Einv || !slot || !x_no || !x_ov) return VFD_ERR_NULL;
+    if (!aligned16(feats) || !aligned16(x_no) || !aligned16(x_ov)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv;
+    a.x_no = x_no; a.x_ov = x_ov; a.slot = slot;
+    return launch<0>(a, false, (cudaStream_t)stream);
+}
+
+extern "C" int vfd_voxel_gather_depth_compact_bwd(const vfd_fusion_desc* d, const float* mask_small,
+                                                  const float* K, const float* Einv, const int32_t* slot,
+                                                  const float* d_x_no, const float* d_x_ov, float* d_feats,
+                                                  void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, true))) return rc;
+    if (!mask_small || !K || !Einv || !slot || !d_x_no || !d_x_ov || !d_feats) return VFD_ERR_NULL;
+    if (!aligned16(d_feats) || !aligned16(d_x_no) || !aligned16(d_x_ov)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.d_x_no = d_x_no; a.d_x_ov = d_x_ov;
+    a.slot = slot;
+    if ((rc = bwd_common(d, a, d_feats, (cudaStream_t)stream))) return rc;
+    return launch<0>(a, true, (cudaStream_t)stream);
 }

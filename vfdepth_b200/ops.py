@@ -205,6 +205,73 @@ class _RaySample(torch.autograd.Function):
         return d_vol, None, None, None, None
 
 
+def voxel_classify(mask_small, K, Einv, geom):
+    """-> count [B,N] u8, slot [B,N] i32, idx_no [M1] i64, idx_ov [M2] i64 (only count-1 / count-2
+    voxels reach an MLP).  Reads the two totals back to the host (one 8-byte copy) because they size the GEMMs."""
+    g = geom
+    B = mask_small.shape[0]
+    _chk(mask_small, 'mask_small', (B, g.num_cams, g.h, g.w))
+    _chk(K, 'K', (B, g.num_cams, 4, 4))
+    _chk(Einv, 'Einv', (B, g.num_cams, 4, 4))
+    dev = mask_small.device
+    d = g.desc(dev, B)
+    count = torch.empty((B, g.N), device=dev, dtype=torch.uint8)
+    slot = torch.empty((B, g.N), device=dev, dtype=torch.int32)
+    idx_no = torch.empty((B * g.N,), device=dev, dtype=torch.int64)
+    idx_ov = torch.empty((B * g.N,), device=dev, dtype=torch.int64)
+    totals = torch.empty((2,), device=dev, dtype=torch.int32)
+    nbytes = _lib.load().vfd_voxel_classify_workspace_bytes(ctypes.byref(d))
+    ws = torch.empty((max(nbytes, 8) // 8,), device=dev, dtype=torch.int64)
+    _lib.call('vfd_voxel_classify', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv),
+              _lib.ptr(count), _lib.ptr(slot), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(ws),
+              ctypes.c_size_t(ws.numel() * 8), _stream())
+    m1, m2 = totals.tolist()
+    return count, slot, idx_no[:m1], idx_ov[:m2]
+
+
+class _VoxelGatherDepthCompact(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, feats, mask_small, K, Einv, slot, m1, m2, geom):
+        B = feats.shape[0]
+        g = geom
+        _chk(feats, 'feats', (B, g.num_cams, g.h, g.w, g.C))
+        _chk(mask_small, 'mask_small', (B, g.num_cams, g.h, g.w))
+        _chk(K, 'K', (B, g.num_cams, 4, 4))
+        _chk(Einv, 'Einv', (B, g.num_cams, 4, 4))
+        if slot.dtype != torch.int32 or tuple(slot.shape) != (B, g.N) or not slot.is_cuda or not slot.is_contiguous():
+            raise ValueError('slot must be a contiguous CUDA int32 tensor [B,N]')
+        dev = feats.device
+        d = g.desc(dev, B)
+        # at least one (never read) row so the pointers stay valid when a class is empty
+        x_no = torch.empty((max(m1, 1), g.ld_no), device=dev, dtype=torch.float32)
+        x_ov = torch.empty((max(m2, 1), g.ld_ov), device=dev, dtype=torch.float32)
+        _lib.call('vfd_voxel_gather_depth_compact_fwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small),
+                  _lib.ptr(K), _lib.ptr(Einv), _lib.ptr(slot), _lib.ptr(x_no), _lib.ptr(x_ov), _stream())
+        ctx.geom, ctx.m = g, (m1, m2)
+        ctx.save_for_backward(mask_small, K, Einv, slot)
+        return x_no[:m1], x_ov[:m2]
+
+    @staticmethod
+    def backward(ctx, d_no, d_ov):
+        mask_small, K, Einv, slot = ctx.saved_tensors
+        g = ctx.geom
+        m1, m2 = ctx.m
+        B = mask_small.shape[0]
+        dev = mask_small.device
+        d = g.desc(dev, B)
+        d_no = torch.zeros((max(m1, 1), g.ld_no), device=dev) if d_no is None or m1 == 0 else d_no.contiguous()
+        d_ov = torch.zeros((max(m2, 1), g.ld_ov), device=dev) if d_ov is None or m2 == 0 else d_ov.contiguous()
+        d_feats = torch.empty((B, g.num_cams, g.h, g.w, g.C), device=dev, dtype=torch.float32)
+        _lib.call('vfd_voxel_gather_depth_compact_bwd', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K),
+                  _lib.ptr(Einv), _lib.ptr(slot), _lib.ptr(d_no), _lib.ptr(d_ov), _lib.ptr(d_feats), _stream())
+        return d_feats, None, None, None, None, None, None, None
+
+
+def voxel_gather_depth_compact(feats_cl, mask_small, K, Einv, slot, m1, m2, geom):
+    """feats_cl [B,cams,h,w,C] -> x_no [m1,ld_no] (count-1 voxels), x_ov [m2,ld_ov] (count-2 voxels)."""
+    return _VoxelGatherDepthCompact.apply(feats_cl, mask_small, K, Einv, slot, m1, m2, geom)
+
+
 def voxel_gather_depth(feats_cl, mask_small, K, Einv, geom, detail=False):
     """feats_cl [B,cams,h,w,C] -> x_no [B,N,ld_no], x_ov [B,N,ld_ov], count [B,N] (+ grid, valid with ``detail``)."""
     return _VoxelGatherDepth.apply(feats_cl, mask_small, K, Einv, geom, detail)

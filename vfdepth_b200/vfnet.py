@@ -109,18 +109,27 @@ class VFNet(nn.Module):
         """-> voxel_feat [B,C',N] (a permuted view of channel-last rows [B,N,C']).  Reference :116-164."""
         g = self.geom
         if self.model == 'depth':
-            x_no, x_ov, count = self.gather_rows(feats_agg, input_mask, intrinsics, extrinsics_inv)[:3]
+            # only voxels seen by exactly 1 / exactly 2 cameras reach an MLP (:200-206, :227-229): classify first,
+            # gather compact GEMM rows for those, scatter the MLP outputs into the (otherwise zero) volume
+            feats_cl = self._channel_last(feats_agg)
+            mask_small = self._mask_small(input_mask)
+            K = intrinsics.float().contiguous()
+            Einv = extrinsics_inv.float().contiguous()
+            count, slot, idx_no, idx_ov = ops.voxel_classify(mask_small, K, Einv, g)
             self.last_count = count
+            x_no, x_ov = ops.voxel_gather_depth_compact(feats_cl, mask_small, K, Einv, slot, idx_no.numel(),
+                                                        idx_ov.numel(), g)
             c1 = self.feat_in_dim + 1
             w_no = F.pad(self.conv_non_overlap[0].weight.squeeze(-1), (0, g.ld_no - c1))
             w_ov = self.conv_overlap[0].weight.squeeze(-1)
             w_ov = torch.cat([F.pad(w_ov[:, :c1], (0, g.half_ov - c1)),
                               F.pad(w_ov[:, c1:], (0, g.ld_ov - g.half_ov - c1))], 1)
-            cnt = count.unsqueeze(-1)
-            y_no = F.leaky_relu(F.linear(x_no, w_no, self.conv_non_overlap[0].bias), 0.1) * (cnt == 1).float()
-            y_ov = F.leaky_relu(F.linear(x_ov, w_ov, self.conv_overlap[0].bias), 0.1) * (cnt == 2).float()
-            rows = y_no + y_ov                                   # [B,N,Cv] == channel-last voxel volume
-            return rows.permute(0, 2, 1)
+            y_no = F.leaky_relu(F.linear(x_no, w_no, self.conv_non_overlap[0].bias), 0.1)
+            y_ov = F.leaky_relu(F.linear(x_ov, w_ov, self.conv_overlap[0].bias), 0.1)
+            B = feats_cl.shape[0]
+            rows = torch.zeros((B * g.N, y_no.shape[1]), device=feats_cl.device, dtype=torch.float32)
+            rows = rows.index_copy(0, idx_no, y_no).index_copy(0, idx_ov, y_ov)
+            return rows.view(B, g.N, -1).permute(0, 2, 1)     # [B,N,Cv] == channel-last voxel volume
         avg, count = self.gather_rows(feats_agg, input_mask, intrinsics, extrinsics_inv)
         self.last_count = count
         return avg[:, :, :self.feat_in_dim + 1].permute(0, 2, 1)
