@@ -189,6 +189,9 @@ class FusionWorkload:
         classify = msk + B * g.N * (1 + 4) + (m1 + m2) * 8
         return {'vfd_voxel_gather_depth_compact_fwd': feats + msk + rows,
                 'vfd_voxel_gather_depth_compact_bwd': feats + msk + rows, 'vfd_voxel_classify': classify,
+                # fused gather + MLPs: the rows never reach HBM.  fwd: features in, volume out;
+                # bwd: features + volume + its gradient in, feature gradient out
+                'vfd_voxel_fuse_fwd': feats + msk + vol, 'vfd_voxel_fuse_bwd': 2 * feats + msk + 2 * vol,
                 'vfd_ray_sample_fwd': vol + ray, 'vfd_ray_sample_bwd': vol + ray}
 
 

@@ -109,6 +109,32 @@ int vfd_voxel_gather_depth_compact_bwd(const vfd_fusion_desc* d, const float* ma
                                        const float* Einv, const int32_t* slot, const float* d_x_no,
                                        const float* d_x_ov, float* d_feats, void* stream);
 
+/* Fused gather + both 1x1 MLPs: VFNet.backproject_into_voxel, model='depth', :116-159 INCLUDING
+ * preprocess_non_overlap (:197-207) and preprocess_overlap (:209-230).  The GEMM rows never reach HBM.
+ *   idx_no/idx_ov/totals  from vfd_voxel_classify (totals stay on the device: no host round trip)
+ *   w_no [Cv][C+1], b_no [Cv]       conv_non_overlap.0.{weight,bias}   (Conv1d weight with the k=1 axis squeezed)
+ *   w_ov [Cv][2(C+1)], b_ov [Cv]    conv_overlap.0.{weight,bias}
+ *   vol  [B,N,Cv]                   channel-last voxel volume (voxel_feat of :158 transposed); zero-filled here, rows
+ *                                   of count-1 / count-2 voxels = LeakyReLU_0.1(x W^T + b)
+ * Cv even, <= 64.  The products run as error-compensated 3xTF32 on the tensor cores (fp32-level accuracy). */
+int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small, const float* K,
+                       const float* Einv, const int64_t* idx_no, const int64_t* idx_ov, const int32_t* totals,
+                       const float* w_no, const float* b_no, const float* w_ov, const float* b_ov, float* vol,
+                       void* stream);
+
+/* Backward of vfd_voxel_fuse_fwd w.r.t. the feature maps and the four MLP parameters.
+ *   vol    [B,N,Cv]  the forward output (the sign of the pre-activation is read from it)
+ *   d_vol  [B,N,Cv]  upstream gradient
+ *   d_feats [B,cams,h,w,C]  zero-filled here, then accumulated (L2 atomics)
+ *   d_w_no [Cv][C+1], d_b_no [Cv], d_w_ov [Cv][2(C+1)], d_b_ov [Cv]  written; per-CTA partial sums go through `ws`
+ *                    (vfd_voxel_fuse_bwd_workspace_bytes) and are reduced in a fixed order (deterministic) */
+size_t vfd_voxel_fuse_bwd_workspace_bytes(const vfd_fusion_desc* d);
+int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small, const float* K,
+                       const float* Einv, const int64_t* idx_no, const int64_t* idx_ov, const int32_t* totals,
+                       const float* w_no, const float* w_ov, const float* vol, const float* d_vol, float* d_feats,
+                       float* d_w_no, float* d_b_no, float* d_w_ov, float* d_b_ov, void* ws, size_t ws_bytes,
+                       void* stream);
+
 /* VFNet.backproject_into_voxel, model='pose' (:160-162):  avg [B,N,ld_no] = sum_c feat_c / (count + 1e-7) */
 int vfd_voxel_gather_pose_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
                               const float* K, const float* Einv, float* avg, uint8_t* count, void* stream);

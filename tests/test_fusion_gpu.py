@@ -248,3 +248,65 @@ def test_compact_rows_equal_dense_rows(B):
     U_ov = torch.zeros_like(d_ov).flatten(0, 1).index_copy(0, idx_ov, u_ov).view_as(d_ov)
     d_d, = torch.autograd.grad((d_no * U_no).sum() + (d_ov * U_ov).sum(), f2)
     assert H.rel_err(d_c, d_d) < 1e-5      # atomics: summation order differs
+
+
+@pytest.mark.parametrize('dataset,B,C,Cv', [('ddad', 2, 256, 64), ('nuscenes', 1, 64, 32), ('ddad', 1, 20, 12)])
+def test_fused_mlp_matches_fp32_gemm_path(dataset, B, C, Cv):
+    """SURVEY.md 8f-1 at BASELINE size: the fused gather + MLP kernels (3xTF32 tensor-core products) against the dense
+    gather rows + fp32 cuBLAS GEMMs -- volume, feature gradient and the four parameter gradients within 1e-4 of each
+    tensor's scale; parameter gradients bit-identical between two runs.
+
+    LeakyReLU has a kink: where a pre-activation is ~0 two fp32 implementations may take different slopes, which
+    changes that element's gradient by a factor 10 however small the value.  As for the loss decisions
+    (tests/test_warp_gpu.py) the test requires the slope pattern to agree except where |pre-activation| < 1e-4 (and on
+    fewer than 1e-5 of the elements) and compares gradients with the reference PINNED to the kernel's pattern."""
+    import torch.nn.functional as F
+    dev = _dev()
+    cfg = vcfg.default_config(dataset, batch_size=B, model__fusion_feat_in_dim=C, model__voxel_pre_dim=[Cv])
+    inputs, extras = make_rig(cfg, seed=41, with_images=False, with_feats=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, C, 16, 'depth', None, dev)
+    with torch.no_grad():      # biases away from zero so the LeakyReLU sign pattern is non-trivial
+        net.conv_non_overlap[0].bias.normal_(0, 0.5)
+        net.conv_overlap[0].bias.normal_(0, 0.5)
+    to = lambda t: t.to(dev)
+    g = net.geom
+    torch.manual_seed(5)
+    feats0 = torch.randn(B, 6, C, g.h, g.w, device=dev)
+    up = torch.randn(B, Cv, g.N, device=dev)
+    args = (to(inputs['mask']), to(inputs[('K', lvl)]), to(inputs['extrinsics_inv']))
+    params = [net.conv_non_overlap[0].weight, net.conv_non_overlap[0].bias,
+              net.conv_overlap[0].weight, net.conv_overlap[0].bias]
+    res = {}
+    for name in ('fused', 'fused2'):
+        f = feats0.clone().requires_grad_(True)
+        vox = net.backproject_into_voxel(f, *args)
+        grads = torch.autograd.grad((vox * up).sum(), [f] + params)
+        res[name] = [vox.detach()] + [x.detach() for x in grads]
+    assert torch.equal(res['fused'][0], res['fused2'][0])
+    for a, b in zip(res['fused'][2:], res['fused2'][2:]):
+        assert torch.equal(a, b)
+    cnt = net.last_count
+    vol = res['fused'][0].permute(0, 2, 1)                      # [B,N,Cv]
+    assert float(vol[(cnt != 1) & (cnt != 2)].abs().max()) == 0.0
+
+    # reference: dense gather rows -> fp32 GEMMs (torch), slopes pinned to the kernel's
+    f = feats0.clone().requires_grad_(True)
+    x_no, x_ov, count = net.gather_rows(f, *args)[:3]
+    assert torch.equal(count, cnt)
+    c1 = C + 1
+    w_no = F.pad(params[0].squeeze(-1), (0, g.ld_no - c1))
+    w_ov = params[2].squeeze(-1)
+    w_ov = torch.cat([F.pad(w_ov[:, :c1], (0, g.half_ov - c1)), F.pad(w_ov[:, c1:], (0, g.ld_ov - g.half_ov - c1))], 1)
+    c = count.unsqueeze(-1)
+    z = F.linear(x_no, w_no, params[1]) * (c == 1).float() + F.linear(x_ov, w_ov, params[3]) * (c == 2).float()
+    assert H.rel_err(vol, F.leaky_relu(z.detach(), 0.1)) < TOL
+    active = ((c == 1) | (c == 2)).expand_as(z)
+    flip = ((z.detach() > 0) != (vol > 0)) & active
+    assert int(flip.sum()) <= max(1, int(1e-5 * int(active.sum())))
+    if int(flip.sum()):
+        assert float(z.detach()[flip].abs().max()) < 1e-4
+    y = z * torch.where(vol > 0, 1.0, 0.1)
+    ref = torch.autograd.grad((y.permute(0, 2, 1) * up).sum(), [f] + params)
+    for n, a, b in zip(['d_feats', 'd_w_no', 'd_b_no', 'd_w_ov', 'd_b_ov'], res['fused'][1:], ref):
+        assert H.rel_err(a, b) < TOL, (n, H.rel_err(a, b))

@@ -10,7 +10,7 @@
 //            out with 128-bit stores.  The per-camera [B,257,N] tensors of the reference are never formed.
 // The feature maps of one rig (23.6 MB at DDAD size) stay L2-resident while its 200 000 voxels are processed
 // (blockIdx.y = rig), so HBM traffic is the 617 MB/rig (depth) or 206 MB/rig (pose) of output rows.
-#include "common.cuh"
+#include "gather_common.cuh"
 
 namespace vfd {
 
@@ -35,12 +35,6 @@ struct GatherArgs {
     const int32_t* slot;
 };
 
-struct CamSlot {   // one (voxel, camera) projection, kept in shared memory between the two phases
-    int idx;       // iy0 * w + ix0
-    float wx, wy;  // fractional parts
-    float zrel;    // v.z / depth_div
-};
-
 // phase 1: returns the camera bit-mask of this lane's voxel and fills slot[c][lane]
 __device__ __forceinline__ unsigned project_voxel(const GatherArgs& a, const float* s_mat, int b, long n, int lane,
                                                   bool in_range, CamSlot (*slot)[VFD_WARP]) {
@@ -56,26 +50,10 @@ __device__ __forceinline__ unsigned project_voxel(const GatherArgs& a, const flo
     }
     for (int c = 0; c < d.num_cams; ++c) {
         const float* Einv = s_mat + c * 32;
-        const float* K = Einv + 16;
-        float v[3], g[2];
-        vfd_voxel_to_pixel(Einv, K, x, y, z, d.w, d.h, v, g);
-        bool inb = vfd_in_bounds2(g[0], g[1]);
-        float ix = vfd_unnormalize(g[0], d.w), iy = vfd_unnormalize(g[1], d.h);
-        bool ok = false;
-        CamSlot s = {0, 0.f, 0.f, 0.f};
-        if (in_range && inb && v[2] > 0.f) {
-            // nearest-neighbour self-occlusion lookup: ATen uses nearbyint (half-to-even) -> rintf
-            float fx = rintf(ix), fy = rintf(iy);
-            if (fx >= 0.f && fx <= (float)(d.w - 1) && fy >= 0.f && fy <= (float)(d.h - 1)) {
-                float m = __ldg(a.mask_small + ((size_t)(b * d.num_cams + c) * d.h + (int)fy) * d.w + (int)fx);
-                ok = m > 0.5f;
-            }
-            float x0 = floorf(ix), y0 = floorf(iy);
-            s.idx = (int)y0 * d.w + (int)x0;
-            s.wx = ix - x0;
-            s.wy = iy - y0;
-            s.zrel = VFD_DIV(v[2], d.depth_div);
-        }
+        float g[2];
+        CamSlot s;
+        const bool ok = project_cam(d, a.mask_small + (size_t)(b * d.num_cams + c) * d.h * d.w, Einv, Einv + 16, x, y,
+                                    z, s, g) && in_range;
         if (in_range) {
             size_t o = (size_t)(b * d.num_cams + c) * N + n;
             if (a.grid) reinterpret_cast<float2*>(a.grid)[o] = make_float2(g[0], g[1]);
@@ -95,25 +73,6 @@ __device__ __forceinline__ void load_mats(const GatherArgs& a, int b, float* s_m
         const float* src = (r < 16 ? a.Einv : a.K) + (size_t)(b * a.d.num_cams + c) * 16 + (r & 15);
         s_mat[i] = __ldg(src);
     }
-}
-
-// bilinear corner walk shared by forward (gather) and backward (scatter)
-struct Corners {
-    int off[4];
-    float wgt[4];
-};
-__device__ __forceinline__ Corners make_corners(const CamSlot& s, int w, int h, int C) {
-    Corners q;
-    int x0 = s.idx % w, y0 = s.idx / w;
-    bool x1 = (x0 + 1) < w, y1 = (y0 + 1) < h;
-    float ex = 1.f - s.wx, ey = 1.f - s.wy;
-    q.off[0] = s.idx * C;            q.wgt[0] = ex * ey;
-    q.off[1] = (s.idx + 1) * C;      q.wgt[1] = x1 ? s.wx * ey : 0.f;
-    q.off[2] = (s.idx + w) * C;      q.wgt[2] = y1 ? ex * s.wy : 0.f;
-    q.off[3] = (s.idx + w + 1) * C;  q.wgt[3] = (x1 && y1) ? s.wx * s.wy : 0.f;
-    if (!x1) { q.off[1] = q.off[0]; q.off[3] = q.off[0]; }
-    if (!y1) { q.off[2] = q.off[0]; q.off[3] = q.off[0]; }
-    return q;
 }
 
 template <int MODE /*0 depth, 1 pose*/, int ITERS>

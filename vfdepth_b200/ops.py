@@ -205,9 +205,10 @@ class _RaySample(torch.autograd.Function):
         return d_vol, None, None, None, None
 
 
-def voxel_classify(mask_small, K, Einv, geom):
+def voxel_classify(mask_small, K, Einv, geom, sizes=True):
     """-> count [B,N] u8, slot [B,N] i32, idx_no [M1] i64, idx_ov [M2] i64 (only count-1 / count-2
-    voxels reach an MLP).  Reads the two totals back to the host (one 8-byte copy) because they size the GEMMs."""
+    voxels reach an MLP).  With ``sizes`` the two totals are read back to the host (one 8-byte copy) to slice the
+    lists; without, the full-capacity lists and the device-side totals [2] are returned (no synchronisation)."""
     g = geom
     B = mask_small.shape[0]
     _chk(mask_small, 'mask_small', (B, g.num_cams, g.h, g.w))
@@ -225,6 +226,8 @@ def voxel_classify(mask_small, K, Einv, geom):
     _lib.call('vfd_voxel_classify', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv),
               _lib.ptr(count), _lib.ptr(slot), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(ws),
               ctypes.c_size_t(ws.numel() * 8), _stream())
+    if not sizes:
+        return count, slot, idx_no, idx_ov, totals
     m1, m2 = totals.tolist()
     return count, slot, idx_no[:m1], idx_ov[:m2]
 
@@ -270,6 +273,58 @@ class _VoxelGatherDepthCompact(torch.autograd.Function):
 def voxel_gather_depth_compact(feats_cl, mask_small, K, Einv, slot, m1, m2, geom):
     """feats_cl [B,cams,h,w,C] -> x_no [m1,ld_no] (count-1 voxels), x_ov [m2,ld_ov] (count-2 voxels)."""
     return _VoxelGatherDepthCompact.apply(feats_cl, mask_small, K, Einv, slot, m1, m2, geom)
+
+
+class _VoxelFuse(torch.autograd.Function):
+    """gather + both 1x1 MLPs in one kernel (vfd_voxel_fuse_fwd); backward in vfd_voxel_fuse_bwd."""
+
+    @staticmethod
+    def forward(ctx, feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, geom):
+        B = feats.shape[0]
+        g = geom
+        c1 = g.C + 1
+        _chk(feats, 'feats', (B, g.num_cams, g.h, g.w, g.C))
+        _chk(mask_small, 'mask_small', (B, g.num_cams, g.h, g.w))
+        _chk(K, 'K', (B, g.num_cams, 4, 4))
+        _chk(Einv, 'Einv', (B, g.num_cams, 4, 4))
+        w_no, b_no, w_ov, b_ov = (t.detach().contiguous() for t in (w_no, b_no, w_ov, b_ov))
+        _chk(w_no, 'w_no', (g.Cv, c1))
+        _chk(b_no, 'b_no', (g.Cv,))
+        _chk(w_ov, 'w_ov', (g.Cv, 2 * c1))
+        _chk(b_ov, 'b_ov', (g.Cv,))
+        dev = feats.device
+        d = g.desc(dev, B)
+        vol = torch.empty((B, g.N, g.Cv), device=dev, dtype=torch.float32)
+        _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
+                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(w_no), _lib.ptr(b_no),
+                  _lib.ptr(w_ov), _lib.ptr(b_ov), _lib.ptr(vol), _stream())
+        ctx.geom = g
+        ctx.save_for_backward(feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, vol)
+        return vol
+
+    @staticmethod
+    def backward(ctx, d_vol):
+        feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, vol = ctx.saved_tensors
+        g = ctx.geom
+        B = feats.shape[0]
+        dev = feats.device
+        d = g.desc(dev, B)
+        d_vol = d_vol.contiguous()
+        d_feats = torch.empty_like(feats)
+        d_w_no, d_b_no = torch.empty_like(w_no), torch.empty_like(b_no)
+        d_w_ov, d_b_ov = torch.empty_like(w_ov), torch.empty_like(b_ov)
+        nbytes = _lib.load().vfd_voxel_fuse_bwd_workspace_bytes(ctypes.byref(d))
+        ws = torch.empty((max(nbytes, 16) // 4,), device=dev, dtype=torch.float32)
+        _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
+                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(w_no), _lib.ptr(w_ov),
+                  _lib.ptr(vol), _lib.ptr(d_vol), _lib.ptr(d_feats), _lib.ptr(d_w_no), _lib.ptr(d_b_no),
+                  _lib.ptr(d_w_ov), _lib.ptr(d_b_ov), _lib.ptr(ws), ctypes.c_size_t(ws.numel() * 4), _stream())
+        return d_feats, d_w_no, d_b_no, d_w_ov, d_b_ov, None, None, None, None, None, None, None
+
+
+def voxel_fuse(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, geom):
+    """feats_cl [B,cams,h,w,C] + MLP parameters -> channel-last voxel volume [B,N,Cv]."""
+    return _VoxelFuse.apply(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, geom)
 
 
 def voxel_gather_depth(feats_cl, mask_small, K, Einv, geom, detail=False):

@@ -75,6 +75,7 @@ class VFNet(nn.Module):
                                        self.voxel_size, self.voxel_str_p, self.voxel_unit_size, self.proj_d_bins,
                                        self.proj_d_str, self.proj_d_end, cv)
         self.last_count = None      # [B,N] uint8 camera count of the last gather (:152), for inspection
+        self.fused_mlp = True       # gather + MLPs in one kernel (else: compact gather rows + cuBLAS GEMMs)
 
     # ------------------------------------------------------------------------------------------
     @staticmethod
@@ -115,6 +116,14 @@ class VFNet(nn.Module):
             mask_small = self._mask_small(input_mask)
             K = intrinsics.float().contiguous()
             Einv = extrinsics_inv.float().contiguous()
+            if self.fused_mlp and g.C <= 256 and g.Cv <= 64 and g.Cv % 4 == 0:
+                # gather + both MLPs in one kernel, no host round trip, rows never reach HBM
+                count, _, idx_no, idx_ov, totals = ops.voxel_classify(mask_small, K, Einv, g, sizes=False)
+                self.last_count = count
+                vol = ops.voxel_fuse(feats_cl, self.conv_non_overlap[0].weight.squeeze(-1),
+                                     self.conv_non_overlap[0].bias, self.conv_overlap[0].weight.squeeze(-1),
+                                     self.conv_overlap[0].bias, mask_small, K, Einv, idx_no, idx_ov, totals, g)
+                return vol.permute(0, 2, 1)
             count, slot, idx_no, idx_ov = ops.voxel_classify(mask_small, K, Einv, g)
             self.last_count = count
             x_no, x_ov = ops.voxel_gather_depth_compact(feats_cl, mask_small, K, Einv, slot, idx_no.numel(),
