@@ -81,11 +81,41 @@ def main():
         'ray_bwd': (lambda: _lib.call('vfd_ray_sample_bwd', ctypes.byref(d), p(iK), p(E), p(out), p(d_vol), st),
                     vol.numel() * 4 + out.numel() * 4),
     }
+    # compact lists + fused gather/MLP kernels
+    cnt8, slot, idx_no, idx_ov, totals = ops.voxel_classify(mask_small, K, Einv, g, sizes=False)
+    m1, m2 = totals.tolist()
+    w_no, b_no = torch.randn(g.Cv, c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
+    w_ov, b_ov = torch.randn(g.Cv, 2 * c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
+    fvol = torch.empty(B, N, g.Cv, device=dev)
+    gvol = torch.randn(B, N, g.Cv, device=dev)
+    dw_no, db_no, dw_ov, db_ov = (torch.empty_like(t) for t in (w_no, b_no, w_ov, b_ov))
+    nws = _lib.load().vfd_voxel_fuse_bwd_workspace_bytes(ctypes.byref(d))
+    ws = torch.empty(nws // 4, device=dev)
+    cx_no = torch.empty(max(m1, 1), g.ld_no, device=dev)
+    cx_ov = torch.empty(max(m2, 1), g.ld_ov, device=dev)
+    rows_b = (m1 + 2 * m2) * c1 * 4
+    vol_b = B * N * g.Cv * 4
+    kernels.update({
+        'compact_fwd': (lambda: _lib.call('vfd_voxel_gather_depth_compact_fwd', ctypes.byref(d), p(feats), p(mask_small),
+                                          p(K), p(Einv), p(slot), p(cx_no), p(cx_ov), st), feat_b + rows_b),
+        'compact_bwd': (lambda: _lib.call('vfd_voxel_gather_depth_compact_bwd', ctypes.byref(d), p(mask_small), p(K),
+                                          p(Einv), p(slot), p(cx_no), p(cx_ov), p(d_feats), st), feat_b + rows_b),
+        'fuse_fwd': (lambda: _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), p(feats), p(mask_small), p(K), p(Einv),
+                                       p(idx_no), p(idx_ov), p(totals), p(w_no), p(b_no), p(w_ov), p(b_ov), p(fvol), st),
+                     feat_b + vol_b),
+        'fuse_bwd': (lambda: _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), p(feats), p(mask_small), p(K), p(Einv),
+                                       p(idx_no), p(idx_ov), p(totals), p(w_no), p(w_ov), p(fvol), p(gvol), p(d_feats),
+                                       p(dw_no), p(db_no), p(dw_ov), p(db_ov), p(ws), ctypes.c_size_t(nws), st),
+                     2 * feat_b + 2 * vol_b),
+    })
+    print('count-1 voxels %d, count-2 voxels %d of %d' % (m1, m2, B * N), flush=True)
     only = [k for k in args.only.split(',') if k]
     peak, how = peak_gbs()
     # make x_no / x_ov / out hold realistic upstream gradients for the backward kernels
     kernels['gather_fwd'][0]()
     kernels['ray_fwd'][0]()
+    kernels['compact_fwd'][0]()
+    kernels['fuse_fwd'][0]()
     torch.cuda.synchronize()
     for name, (fn, nbytes) in kernels.items():
         if only and name not in only:

@@ -9,9 +9,14 @@
 // into the channel-last voxel volume -- the GEMM rows never exist in HBM.  Algorithmic HBM bytes: 23.6 MB of feature
 // maps + 51.2 MB of volume per rig instead of 640 MB.
 //
-// The product runs on the tensor cores through mma.sync.m16n8k8 TF32 with the error-compensated 3xTF32 split
+// Both directions run as three passes over the lists, one per (C+1) x Cv weight block:
+//   pass 0: count-1 voxels x W_no;  pass 1: count-2 voxels, camera group 0 x W_ov[:, :C+1];  pass 2: group 1 x W_ov[:, C+1:]
+// (forward pass 1 parks its raw accumulators in the volume, pass 2 adds its own, the bias and the LeakyReLU).
+//
+// The products run on the tensor cores through mma.sync.m16n8k8 TF32 with the error-compensated 3xTF32 split
 // (x = hi + lo, x*w ~ hi*hi + hi*lo + lo*hi, fp32 accumulate), which keeps the result within fp32 round-off of the
-// reference's fp32 GEMM (tests: 1e-4 of the tensor's scale; measured ~1e-6).
+// reference's fp32 GEMM (tests: 1e-4 of the tensor's scale; measured ~3e-6).  The weight block is split once per pass
+// into TF32 hi/lo planes in shared memory.
 //
 // Persistent grid (one CTA per SM, 16 warps); the list lengths are read from device memory (vfd_voxel_classify's
 // totals), so nothing here needs a host round trip.
@@ -22,7 +27,9 @@ namespace vfd {
 constexpr int kFuseRows = 64;       // voxels per tile
 constexpr int kFuseWarps = 16;
 constexpr int kFuseThreads = kFuseWarps * VFD_WARP;
-constexpr int kWS = 72;             // shared-memory row stride of the [k][n] weight (8k+n banks: conflict-free B fragments)
+constexpr int kRowsPerWarp = kFuseRows / kFuseWarps;
+constexpr int kWS = 72;             // row stride of [k][n] planes (8k+n banks: conflict-free B fragments)
+constexpr int kMaxEnt = 2;          // cameras of one group that can see a listed voxel (count <= 2)
 
 struct FuseArgs {
     vfd_fusion_desc d;
@@ -41,59 +48,45 @@ struct FuseArgs {
     // backward
     const float* d_vol;  // [B*N][Cv]
     float* d_feats;      // [B,cams,h,w,C]
-    float* partial;      // [gridDim.x][3][Cv][KP+... ] per-CTA weight-gradient partial sums
+    float* partial;      // [gridDim.x][3][Cv*(C+2)] per-CTA weight-gradient partial sums
     int KP;              // round_up(C+1, 8)
     int NT;              // ceil(Cv / 8)
 };
 
-struct FuseSmem {
-    float* W[2];     // [KP][kWS] each
-    float* A;        // [kFuseRows][AS]
-    CamSlot* slot;   // [VFD_MAX_CAMS][kFuseRows]
-    unsigned* vmask; // [kFuseRows]
-    long long* row;  // [kFuseRows]  b*N+n or -1
+// per-tile bookkeeping shared by forward and backward: for every row of the tile the (at most two) cameras of the
+// current pass that see the voxel, with their bilinear corners precomputed
+struct TileMeta {
+    long long* row;   // [64]     b*N+n, -1 past the end of the list
+    int* cnt;         // [64]     entries of this row in this pass
+    int4* off;        // [2][64]  corner offsets (floats) inside the camera's feature map
+    float4* wgt;      // [2][64]  corner weights
+    int2* meta;       // [2][64]  {b*num_cams + c, bits of zrel}
 };
+constexpr size_t kMetaBytes = kFuseRows * (8 + 4 + kMaxEnt * (16 + 16 + 8));
 
-__host__ __device__ inline size_t fuse_fwd_smem_bytes(int KP) {
-    return (size_t)2 * KP * kWS * 4 + (size_t)kFuseRows * (KP + 4) * 4 + sizeof(CamSlot) * VFD_MAX_CAMS * kFuseRows +
-           kFuseRows * 4 + kFuseRows * 8;
-}
-
-__device__ __forceinline__ FuseSmem carve_fwd(unsigned char* base, int KP) {
-    FuseSmem s;
-    s.row = reinterpret_cast<long long*>(base);
+__device__ __forceinline__ TileMeta carve_meta(unsigned char* base) {
+    TileMeta m;
+    m.row = reinterpret_cast<long long*>(base);
     base += kFuseRows * 8;
-    s.W[0] = reinterpret_cast<float*>(base);
-    base += (size_t)KP * kWS * 4;
-    s.W[1] = reinterpret_cast<float*>(base);
-    base += (size_t)KP * kWS * 4;
-    s.A = reinterpret_cast<float*>(base);
-    base += (size_t)kFuseRows * (KP + 4) * 4;
-    s.slot = reinterpret_cast<CamSlot*>(base);
-    base += sizeof(CamSlot) * VFD_MAX_CAMS * kFuseRows;
-    s.vmask = reinterpret_cast<unsigned*>(base);
-    return s;
+    m.off = reinterpret_cast<int4*>(base);
+    base += kMaxEnt * kFuseRows * 16;
+    m.wgt = reinterpret_cast<float4*>(base);
+    base += kMaxEnt * kFuseRows * 16;
+    m.meta = reinterpret_cast<int2*>(base);
+    base += kMaxEnt * kFuseRows * 8;
+    m.cnt = reinterpret_cast<int*>(base);
+    return m;
 }
 
-// sW[k][n] = w[n][koff + k] for k < C1, n < Cv; zero elsewhere (k < KP, n < kWS)
-__device__ __forceinline__ void load_weight_kn(float* sW, const float* w, int ld, int koff, int C1, int Cv, int KP) {
-    for (int i = threadIdx.x; i < KP * kWS; i += blockDim.x) sW[i] = 0.f;
-    __syncthreads();
-    for (int i = threadIdx.x; i < Cv * C1; i += blockDim.x) {
-        const int n = i / C1, k = i - n * C1;
-        sW[k * kWS + n] = __ldg(w + (size_t)n * ld + koff + k);
-    }
-}
-
-// threads r < kFuseRows: project list entry base+r into every camera
-__device__ __forceinline__ void project_tile(const FuseArgs& a, const FuseSmem& s, const int64_t* idx, int base,
-                                             int M) {
+// threads r < 64: project list entry base+r into the cameras in `want`, keep the valid ones
+__device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& tm, const int64_t* idx, int base, int M,
+                                             unsigned want) {
     const vfd_fusion_desc& d = a.d;
     const int r = threadIdx.x;
     if (r >= kFuseRows) return;
     const long N = (long)d.X * d.Y * d.Z;
     long long row = -1;
-    unsigned vm = 0;
+    int n_ent = 0;
     if (base + r < M) {
         row = idx[base + r];
         const int b = (int)(row / N);
@@ -101,117 +94,140 @@ __device__ __forceinline__ void project_tile(const FuseArgs& a, const FuseSmem& 
         const int xi = (int)(n % d.X), yi = (int)((n / d.X) % d.Y), zi = (int)(n / ((long)d.X * d.Y));
         const float x = __ldg(d.axis_x + xi), y = __ldg(d.axis_y + yi), z = __ldg(d.axis_z + zi);
         for (int c = 0; c < d.num_cams; ++c) {
-            const size_t bc = (size_t)b * d.num_cams + c;
+            if (!((want >> c) & 1u)) continue;
+            const int bc = b * d.num_cams + c;
             float g[2];
             CamSlot cs;
-            const bool ok = project_cam(d, a.mask_small + bc * d.h * d.w, a.Einv + bc * 16, a.K + bc * 16, x, y, z, cs, g);
-            s.slot[c * kFuseRows + r] = cs;
-            vm |= (ok ? 1u : 0u) << c;
-        }
-    }
-    s.row[r] = row;
-    s.vmask[r] = vm;
-}
-
-// warp-cooperative gather of one row: A[r][0..C) = sum over cameras in `m` of the bilinear sample, A[r][C] = sum zrel,
-// A[r][C+1..KP) = 0
-__device__ __forceinline__ void gather_row(const FuseArgs& a, const FuseSmem& s, int r, unsigned m, int lane, int AS) {
-    const vfd_fusion_desc& d = a.d;
-    const int C = d.C, hw = d.h * d.w;
-    float* arow = s.A + (size_t)r * AS;
-    const long long row = s.row[r];
-    const long N = (long)d.X * d.Y * d.Z;
-    const int b = row >= 0 ? (int)(row / N) : 0;
-    float zsum = 0.f;
-    for (int k0 = 0; k0 < C; k0 += 128) {
-        const int k = k0 + lane * 4;
-        float4 acc = f4_zero();
-        unsigned mm = m;
-        while (mm) {
-            const int c = __ffs(mm) - 1;
-            mm &= mm - 1;
-            const CamSlot cs = s.slot[c * kFuseRows + r];
-            if (k0 == 0) zsum += cs.zrel;
-            if (k < C) {
-                const Corners q = make_corners(cs, d.w, d.h, C);
-                const float* base = a.feats + ((size_t)b * d.num_cams + c) * hw * C;
-                const float4 v0 = ldg_f4(base + q.off[0] + k), v1 = ldg_f4(base + q.off[1] + k);
-                const float4 v2 = ldg_f4(base + q.off[2] + k), v3 = ldg_f4(base + q.off[3] + k);
-                float4 t = f4_scale(q.wgt[0], v0);
-                f4_fma(t, q.wgt[1], v1);
-                f4_fma(t, q.wgt[2], v2);
-                f4_fma(t, q.wgt[3], v3);
-                f4_add(acc, t);
+            const bool ok = project_cam(d, a.mask_small + (size_t)bc * d.h * d.w, a.Einv + (size_t)bc * 16,
+                                        a.K + (size_t)bc * 16, x, y, z, cs, g);
+            if (ok && n_ent < kMaxEnt) {
+                const Corners q = make_corners(cs, d.w, d.h, d.C);
+                tm.off[n_ent * kFuseRows + r] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
+                tm.wgt[n_ent * kFuseRows + r] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
+                tm.meta[n_ent * kFuseRows + r] = make_int2(bc, __float_as_int(cs.zrel));
+                ++n_ent;
             }
         }
-        if (k < C) *reinterpret_cast<float4*>(arow + k) = acc;
     }
+    tm.row[r] = row;
+    tm.cnt[r] = n_ent;
+}
+
+// warp-cooperative gather of one row into shared memory: arow[0..C) = sum over the row's entries of the bilinear
+// sample, arow[C] = sum of the relative depths, arow[C+1..KP) = 0.  NCH = ceil(C / 128) chunks of 4 floats per lane.
+template <int NCH>
+__device__ __forceinline__ void gather_row(const FuseArgs& a, const TileMeta& tm, int r, int lane, float* arow) {
+    const int C = a.d.C;
+    const size_t map = (size_t)a.d.h * a.d.w * C;
+    const int cnt = tm.cnt[r];
+    float4 acc[NCH];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) acc[i] = f4_zero();
+    float zsum = 0.f;
+    for (int e = 0; e < cnt; ++e) {
+        const int4 off = tm.off[e * kFuseRows + r];
+        const float4 wg = tm.wgt[e * kFuseRows + r];
+        const int2 me = tm.meta[e * kFuseRows + r];
+        const float* base = a.feats + (size_t)me.x * map + lane * 4;
+        zsum += __int_as_float(me.y);
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+            if (i * 128 + lane * 4 < C) {
+                const float4 v0 = ldg_f4(base + off.x + i * 128), v1 = ldg_f4(base + off.y + i * 128);
+                const float4 v2 = ldg_f4(base + off.z + i * 128), v3 = ldg_f4(base + off.w + i * 128);
+                float4 t = f4_scale(wg.x, v0);
+                f4_fma(t, wg.y, v1);
+                f4_fma(t, wg.z, v2);
+                f4_fma(t, wg.w, v3);
+                f4_add(acc[i], t);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+        if (i * 128 + lane * 4 < C) *reinterpret_cast<float4*>(arow + i * 128 + lane * 4) = acc[i];
     for (int k = C + lane; k < a.KP; k += VFD_WARP) arow[k] = (k == C) ? zsum : 0.f;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Forward
+// ---------------------------------------------------------------------------------------------------------
+__host__ __device__ inline size_t fuse_fwd_smem_bytes(int KP) {
+    const size_t a_tile = (size_t)kFuseRows * (KP + 4) * 4, partials = (size_t)3 * kFuseRows * kWS * 4;
+    return kMetaBytes + (size_t)2 * KP * kWS * 4 + (a_tile > partials ? a_tile : partials);
+}
+
+template <int NCH>
 __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const FuseArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const vfd_fusion_desc& d = a.d;
     const int KP = a.KP, AS = KP + 4, NT = a.NT, C1 = d.C + 1, Cv = d.Cv;
-    const FuseSmem s = carve_fwd(smem_raw, KP);
+    const TileMeta tm = carve_meta(smem_raw);
+    uint32_t* Whi = reinterpret_cast<uint32_t*>(smem_raw + kMetaBytes);   // [KP][kWS] tf32 hi plane, [k][n]
+    uint32_t* Wlo = Whi + (size_t)KP * kWS;
+    float* sA = reinterpret_cast<float*>(Wlo + (size_t)KP * kWS);         // [64][AS]; later the K-split partials
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int wm = warp & 3, wn = warp >> 2;
+    const int wm = warp & 3, wk = warp >> 2;      // 16-row block, quarter of the K range
     const int M1 = a.totals[0], M2 = a.totals[1];
     const int T1 = (M1 + kFuseRows - 1) / kFuseRows, T2 = (M2 + kFuseRows - 1) / kFuseRows;
     unsigned gmask[2] = {0u, 0u};
     for (int c = 0; c < d.num_cams; ++c) gmask[d.group[c] ? 1 : 0] |= 1u << c;
+    const int nk = KP / 8, kq = (nk + 3) / 4;
+    const int ks0 = wk * kq, ks1 = min(nk, ks0 + kq);
 
-    int cur = -1;
-    for (int tile = blockIdx.x; tile < T1 + T2; tile += gridDim.x) {
-        const int type = tile < T1 ? 0 : 1;
-        const int base = (type ? tile - T1 : tile) * kFuseRows;
-        const int M = type ? M2 : M1;
-        const int64_t* idx = type ? a.idx_ov : a.idx_no;
-        if (type != cur) {
-            __syncthreads();
-            if (type == 0) {
-                load_weight_kn(s.W[0], a.w_no, C1, 0, C1, Cv, KP);
-            } else {
-                load_weight_kn(s.W[0], a.w_ov, 2 * C1, 0, C1, Cv, KP);
-                load_weight_kn(s.W[1], a.w_ov, 2 * C1, C1, C1, Cv, KP);
-            }
-            cur = type;
-        }
-        project_tile(a, s, idx, base, M);
+    for (int pass = 0; pass < 3; ++pass) {
+        const int M = pass ? M2 : M1, T = pass ? T2 : T1;
+        const int64_t* idx = pass ? a.idx_ov : a.idx_no;
+        const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
+        const float* bias = pass ? a.b_ov : a.b_no;
         __syncthreads();
-
-        float acc[2][4];
+        {   // weight block [k][n] = w[n][koff + k], split into TF32 hi / lo planes, zero padded
+            const float* w = pass ? a.w_ov : a.w_no;
+            const int ld = pass ? 2 * C1 : C1, koff = pass == 2 ? C1 : 0;
+            for (int i = threadIdx.x; i < KP * kWS; i += blockDim.x) { Whi[i] = 0u; Wlo[i] = 0u; }
+            __syncthreads();
+            for (int i = threadIdx.x; i < Cv * C1; i += blockDim.x) {
+                const int n = i / C1, k = i - n * C1;
+                uint32_t hi, lo;
+                split_tf32(__ldg(w + (size_t)n * ld + koff + k), hi, lo);
+                Whi[k * kWS + n] = hi;
+                Wlo[k * kWS + n] = lo;
+            }
+        }
+        for (int tile = blockIdx.x; tile < T; tile += gridDim.x) {
+            project_tile(a, tm, idx, tile * kFuseRows, M, want);
+            __syncthreads();
 #pragma unroll
-        for (int j = 0; j < 2; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[j][i] = 0.f;
-
-        for (int half = 0; half <= type; ++half) {
-            // gather: 4 rows per warp
-#pragma unroll 2
-            for (int rr = 0; rr < kFuseRows / kFuseWarps; ++rr) {
-                const int r = warp * (kFuseRows / kFuseWarps) + rr;
-                const unsigned m = s.vmask[r] & (type ? gmask[half] : 0xffffffffu);
-                gather_row(a, s, r, m, lane, AS);
+            for (int rr = 0; rr < kRowsPerWarp; ++rr) {
+                const int r = warp * kRowsPerWarp + rr;
+                gather_row<NCH>(a, tm, r, lane, sA + (size_t)r * AS);
             }
             __syncthreads();
-            // [64 x KP] x [KP x Cv] on the tensor cores, 3xTF32
-            const float* A0 = s.A + (size_t)(wm * 16 + g) * AS + t;
-            const float* A1 = A0 + 8 * AS;
-            const float* Wb = s.W[half] + t * kWS + wn * 16 + g;
-            if (wn * 2 < NT) {
-                for (int ks = 0; ks < KP; ks += 8) {
-                    uint32_t ah[4], al[4];
-                    split_tf32(A0[ks], ah[0], al[0]);
-                    split_tf32(A1[ks], ah[1], al[1]);
-                    split_tf32(A0[ks + 4], ah[2], al[2]);
-                    split_tf32(A1[ks + 4], ah[3], al[3]);
+
+            // [16 rows x (this warp's K quarter)] x [K x Cv]: 3xTF32 on the tensor cores
+            float acc[8][4];
 #pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        if (wn * 2 + j < NT) {
-                            uint32_t bh0, bl0, bh1, bl1;
-                            split_tf32(Wb[ks * kWS + j * 8], bh0, bl0);
-                            split_tf32(Wb[(ks + 4) * kWS + j * 8], bh1, bl1);
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[j][i] = 0.f;
+            {
+                const float* A0 = sA + (size_t)(wm * 16 + g) * AS + t;
+                const float* A1 = A0 + 8 * AS;
+                const uint32_t* Bh = Whi + t * kWS + g;
+                const uint32_t* Bl = Wlo + t * kWS + g;
+                for (int ks = ks0; ks < ks1; ++ks) {
+                    uint32_t ah[4], al[4];
+                    split_tf32(A0[ks * 8], ah[0], al[0]);
+                    split_tf32(A1[ks * 8], ah[1], al[1]);
+                    split_tf32(A0[ks * 8 + 4], ah[2], al[2]);
+                    split_tf32(A1[ks * 8 + 4], ah[3], al[3]);
+                    const uint32_t* bh = Bh + ks * 8 * kWS;
+                    const uint32_t* bl = Bl + ks * 8 * kWS;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (j < NT) {
+                            const uint32_t bh0 = bh[j * 8], bh1 = bh[4 * kWS + j * 8];
+                            const uint32_t bl0 = bl[j * 8], bl1 = bl[4 * kWS + j * 8];
                             mma_tf32(acc[j], al, bh0, bh1);
                             mma_tf32(acc[j], ah, bl0, bl1);
                             mma_tf32(acc[j], ah, bh0, bh1);
@@ -219,33 +235,60 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
                     }
                 }
             }
-            __syncthreads();
-        }
-        // epilogue: + bias, LeakyReLU(0.1), scatter the rows into the volume
-        const float* bias = type ? a.b_ov : a.b_no;
-        const long long row0 = s.row[wm * 16 + g], row1 = s.row[wm * 16 + g + 8];
+            __syncthreads();     // all warps are done with the A tile: reuse it for the K-split partial sums
+            float* P = sA;       // [3][64][kWS]
+            if (wk > 0) {
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int col = (wn * 2 + j) * 8 + 2 * t;
-            if (wn * 2 + j < NT && col < Cv) {
-                const float b0 = __ldg(bias + col), b1 = __ldg(bias + col + 1);
-                float y0 = acc[j][0] + b0, y1 = acc[j][1] + b1, y2 = acc[j][2] + b0, y3 = acc[j][3] + b1;
-                y0 = y0 > 0.f ? y0 : 0.1f * y0;
-                y1 = y1 > 0.f ? y1 : 0.1f * y1;
-                y2 = y2 > 0.f ? y2 : 0.1f * y2;
-                y3 = y3 > 0.f ? y3 : 0.1f * y3;
-                if (row0 >= 0) *reinterpret_cast<float2*>(a.vol + (size_t)row0 * Cv + col) = make_float2(y0, y1);
-                if (row1 >= 0) *reinterpret_cast<float2*>(a.vol + (size_t)row1 * Cv + col) = make_float2(y2, y3);
+                for (int j = 0; j < 8; ++j) {
+                    if (j < NT) {
+                        float* p0 = P + ((size_t)(wk - 1) * kFuseRows + wm * 16 + g) * kWS + j * 8 + 2 * t;
+                        *reinterpret_cast<float2*>(p0) = make_float2(acc[j][0], acc[j][1]);
+                        *reinterpret_cast<float2*>(p0 + 8 * kWS) = make_float2(acc[j][2], acc[j][3]);
+                    }
+                }
             }
+            __syncthreads();
+            if (wk == 0) {
+                const long long row0 = tm.row[wm * 16 + g], row1 = tm.row[wm * 16 + g + 8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int col = j * 8 + 2 * t;
+                    if (j < NT && col < Cv) {
+                        float y0 = acc[j][0], y1 = acc[j][1], y2 = acc[j][2], y3 = acc[j][3];
+#pragma unroll
+                        for (int q = 0; q < 3; ++q) {
+                            const float* p0 = P + ((size_t)q * kFuseRows + wm * 16 + g) * kWS + col;
+                            const float2 u = *reinterpret_cast<const float2*>(p0);
+                            const float2 v = *reinterpret_cast<const float2*>(p0 + 8 * kWS);
+                            y0 += u.x; y1 += u.y; y2 += v.x; y3 += v.y;
+                        }
+                        float* o0 = a.vol + (size_t)row0 * Cv + col;
+                        float* o1 = a.vol + (size_t)row1 * Cv + col;
+                        if (pass == 2) {   // add the group-0 half parked by pass 1
+                            if (row0 >= 0) { const float2 u = *reinterpret_cast<const float2*>(o0); y0 += u.x; y1 += u.y; }
+                            if (row1 >= 0) { const float2 v = *reinterpret_cast<const float2*>(o1); y2 += v.x; y3 += v.y; }
+                        }
+                        if (pass != 1) {
+                            const float b0 = __ldg(bias + col), b1 = __ldg(bias + col + 1);
+                            y0 += b0; y1 += b1; y2 += b0; y3 += b1;
+                            y0 = y0 > 0.f ? y0 : 0.1f * y0;
+                            y1 = y1 > 0.f ? y1 : 0.1f * y1;
+                            y2 = y2 > 0.f ? y2 : 0.1f * y2;
+                            y3 = y3 > 0.f ? y3 : 0.1f * y3;
+                        }
+                        if (row0 >= 0) *reinterpret_cast<float2*>(o0) = make_float2(y0, y1);
+                        if (row1 >= 0) *reinterpret_cast<float2*>(o1) = make_float2(y2, y3);
+                    }
+                }
+            }
+            __syncthreads();   // the metadata and the A tile are rewritten by the next tile
         }
-        __syncthreads();   // s.row / s.vmask are rewritten by the next tile's projection
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Backward.  Three passes over the compact lists, one per weight block (W_no, W_ov[:, :C+1], W_ov[:, C+1:]); a tile of
-// 64 voxels per step:
-//   dZ  = d_vol[rows] * LeakyReLU'(vol[rows])                         (y > 0 <=> pre-activation > 0)
+// Backward.  Per pass (weight block) and per tile of 64 voxels:
+//   dZ  = d_vol[rows] * LeakyReLU'(vol[rows])       (y > 0 <=> pre-activation > 0), split into TF32 hi/lo planes
 //   A   = the gathered feature rows, recomputed (L2-resident feature maps)  [64 x (C+1)]
 //   dW += A^T dZ    tensor cores, accumulators stay in registers for the whole pass (one 16-row block per warp);
 //                   the relative-depth column and db are two SIMT dot products
@@ -253,44 +296,25 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
 // Per-CTA weight-gradient partials are written to the workspace and summed in CTA order by a second kernel, so dW / db
 // are deterministic; d_feats is accumulated with L2 atomics like vfd_voxel_gather_depth_bwd.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int kZS = 72;   // row stride of the dZ tile
+constexpr int kZS = 72;   // row stride of the dZ planes
 
 __host__ __device__ inline int fuse_sn(int KP) { return (KP - 8 + 31) / 32 * 32 + 8; }   // stride = 8 (mod 32)
 
 __host__ __device__ inline size_t fuse_bwd_smem_bytes(int KP, int NT) {
     const int SN = fuse_sn(KP);
-    return (size_t)kFuseRows * 8 + (size_t)NT * 8 * SN * 4 + (size_t)kFuseRows * SN * 4 + (size_t)kFuseRows * kZS * 4 +
-           sizeof(CamSlot) * VFD_MAX_CAMS * kFuseRows + kFuseRows * 4;
+    return kMetaBytes + (size_t)NT * 8 * SN * 4 + (size_t)kFuseRows * SN * 4 + (size_t)2 * kFuseRows * kZS * 4;
 }
 
-struct FuseBwdSmem {
-    FuseSmem g;      // A (stride SN), slot, vmask, row;  g.W[0] = natural-layout weight [NT*8][SN]
-    float* Z;        // [kFuseRows][kZS]
-};
-
-__device__ __forceinline__ FuseBwdSmem carve_bwd(unsigned char* base, int KP, int NT) {
-    const int SN = fuse_sn(KP);
-    FuseBwdSmem s;
-    s.g.row = reinterpret_cast<long long*>(base);
-    base += kFuseRows * 8;
-    s.g.W[0] = reinterpret_cast<float*>(base);
-    s.g.W[1] = nullptr;
-    base += (size_t)NT * 8 * SN * 4;
-    s.g.A = reinterpret_cast<float*>(base);
-    base += (size_t)kFuseRows * SN * 4;
-    s.Z = reinterpret_cast<float*>(base);
-    base += (size_t)kFuseRows * kZS * 4;
-    s.g.slot = reinterpret_cast<CamSlot*>(base);
-    base += sizeof(CamSlot) * VFD_MAX_CAMS * kFuseRows;
-    s.g.vmask = reinterpret_cast<unsigned*>(base);
-    return s;
-}
-
+template <int NCH>
 __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const FuseArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const vfd_fusion_desc& d = a.d;
     const int KP = a.KP, SN = fuse_sn(KP), NT = a.NT, C = d.C, C1 = C + 1, Cv = d.Cv;
-    const FuseBwdSmem s = carve_bwd(smem_raw, KP, NT);
+    const TileMeta tm = carve_meta(smem_raw);
+    float* sW = reinterpret_cast<float*>(smem_raw + kMetaBytes);          // [NT*8][SN] natural layout [out][in]
+    float* sA = sW + (size_t)NT * 8 * SN;                                 // [64][SN]: A, then dA
+    uint32_t* Zhi = reinterpret_cast<uint32_t*>(sA + (size_t)kFuseRows * SN);   // [64][kZS]
+    uint32_t* Zlo = Zhi + kFuseRows * kZS;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     const int wm = warp & 3, wn = warp >> 2;
     const int M1 = a.totals[0], M2 = a.totals[1];
@@ -301,19 +325,19 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
     const int NA = (C + 7) / 8;            // 8-column blocks of dA
     const int NAW = (NA + 3) / 4;          // ... per warp column group (<= 8)
     const size_t pstride = (size_t)Cv * (C1 + 1);     // one (CTA, pass) partial: [Cv][C1] weights then [Cv] bias
+    const size_t map = (size_t)d.h * d.w * C;
 
     for (int pass = 0; pass < 3; ++pass) {
         const int M = pass ? M2 : M1, T = pass ? T2 : T1;
         const int64_t* idx = pass ? a.idx_ov : a.idx_no;
         const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
-        // natural-layout weight block [out][in], zero padded
         __syncthreads();
-        {
+        {   // natural-layout weight block [out][in], zero padded
             const float* w = pass ? a.w_ov : a.w_no;
             const int ld = pass ? 2 * C1 : C1, koff = pass == 2 ? C1 : 0;
             for (int i = threadIdx.x; i < NT * 8 * SN; i += blockDim.x) {
                 const int o = i / SN, k = i - o * SN;
-                s.g.W[0][i] = (o < Cv && k < C1) ? __ldg(w + (size_t)o * ld + koff + k) : 0.f;
+                sW[i] = (o < Cv && k < C1) ? __ldg(w + (size_t)o * ld + koff + k) : 0.f;
             }
         }
         float accw[8][4];
@@ -324,13 +348,12 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
         float db = 0.f, dwz = 0.f;           // threads o < Cv: bias gradient and the relative-depth column of dW
 
         for (int tile = blockIdx.x; tile < T; tile += gridDim.x) {
-            const int base = tile * kFuseRows;
-            project_tile(a, s.g, idx, base, M);
+            project_tile(a, tm, idx, tile * kFuseRows, M, want);
             __syncthreads();
-            // dZ tile
+            // dZ tile, split once
             for (int i = threadIdx.x; i < kFuseRows * (kZS / 4); i += blockDim.x) {
                 const int r = i / (kZS / 4), q = (i - r * (kZS / 4)) * 4;
-                const long long row = s.g.row[r];
+                const long long row = tm.row[r];
                 float4 z = f4_zero();
                 if (row >= 0 && q < Cv) {
                     const float4 gy = ld_stream_f4(a.d_vol + (size_t)row * Cv + q);
@@ -340,20 +363,27 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
                     z.z = y.z > 0.f ? gy.z : 0.1f * gy.z;
                     z.w = y.w > 0.f ? gy.w : 0.1f * gy.w;
                 }
-                *reinterpret_cast<float4*>(s.Z + r * kZS + q) = z;
+                uint4 hi, lo;
+                split_tf32(z.x, hi.x, lo.x);
+                split_tf32(z.y, hi.y, lo.y);
+                split_tf32(z.z, hi.z, lo.z);
+                split_tf32(z.w, hi.w, lo.w);
+                *reinterpret_cast<uint4*>(Zhi + r * kZS + q) = hi;
+                *reinterpret_cast<uint4*>(Zlo + r * kZS + q) = lo;
             }
             // recompute the gathered rows
-#pragma unroll 2
-            for (int rr = 0; rr < kFuseRows / kFuseWarps; ++rr) {
-                const int r = warp * (kFuseRows / kFuseWarps) + rr;
-                gather_row(a, s.g, r, s.g.vmask[r] & want, lane, SN);
+#pragma unroll
+            for (int rr = 0; rr < kRowsPerWarp; ++rr) {
+                const int r = warp * kRowsPerWarp + rr;
+                gather_row<NCH>(a, tm, r, lane, sA + (size_t)r * SN);
             }
             __syncthreads();
 
             // dW^T block [16 in x Cv out] += A^T [16 x 64] dZ [64 x Cv]
             if (warp < MT) {
-                const float* At = s.g.A + t * SN + warp * 16 + g;
-                const float* Zb = s.Z + t * kZS + g;
+                const float* At = sA + t * SN + warp * 16 + g;
+                const uint32_t* Bh = Zhi + t * kZS + g;
+                const uint32_t* Bl = Zlo + t * kZS + g;
 #pragma unroll 2
                 for (int ks = 0; ks < kFuseRows; ks += 8) {
                     uint32_t ah[4], al[4];
@@ -364,9 +394,8 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         if (j < NT) {
-                            uint32_t bh0, bl0, bh1, bl1;
-                            split_tf32(Zb[ks * kZS + j * 8], bh0, bl0);
-                            split_tf32(Zb[(ks + 4) * kZS + j * 8], bh1, bl1);
+                            const uint32_t bh0 = Bh[ks * kZS + j * 8], bh1 = Bh[(ks + 4) * kZS + j * 8];
+                            const uint32_t bl0 = Bl[ks * kZS + j * 8], bl1 = Bl[(ks + 4) * kZS + j * 8];
                             mma_tf32(accw[j], al, bh0, bh1);
                             mma_tf32(accw[j], ah, bl0, bl1);
                             mma_tf32(accw[j], ah, bh0, bh1);
@@ -378,9 +407,9 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
                 const int o = threadIdx.x;
                 float sb = 0.f, sz = 0.f;
                 for (int r = 0; r < kFuseRows; ++r) {
-                    const float z = s.Z[r * kZS + o];
+                    const float z = __uint_as_float(Zhi[r * kZS + o]) + __uint_as_float(Zlo[r * kZS + o]);
                     sb += z;
-                    sz = fmaf(z, s.g.A[r * SN + C], sz);
+                    sz = fmaf(z, sA[r * SN + C], sz);
                 }
                 db += sb;
                 dwz += sz;
@@ -393,15 +422,15 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
 #pragma unroll
                 for (int i = 0; i < 4; ++i) acca[j][i] = 0.f;
             {
-                const float* Z0 = s.Z + (wm * 16 + g) * kZS + t;
-                const float* Z1 = Z0 + 8 * kZS;
-                const float* Wb = s.g.W[0] + t * SN + wn * NAW * 8 + g;
+                const uint32_t* Z0h = Zhi + (wm * 16 + g) * kZS + t;
+                const uint32_t* Z0l = Zlo + (wm * 16 + g) * kZS + t;
+                const float* Wb = sW + t * SN + wn * NAW * 8 + g;
                 for (int ks = 0; ks < NT * 8; ks += 8) {
                     uint32_t ah[4], al[4];
-                    split_tf32(Z0[ks], ah[0], al[0]);
-                    split_tf32(Z1[ks], ah[1], al[1]);
-                    split_tf32(Z0[ks + 4], ah[2], al[2]);
-                    split_tf32(Z1[ks + 4], ah[3], al[3]);
+                    ah[0] = Z0h[ks];            al[0] = Z0l[ks];
+                    ah[1] = Z0h[ks + 8 * kZS];  al[1] = Z0l[ks + 8 * kZS];
+                    ah[2] = Z0h[ks + 4];        al[2] = Z0l[ks + 4];
+                    ah[3] = Z0h[ks + 4 + 8 * kZS];  al[3] = Z0l[ks + 4 + 8 * kZS];
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         if (j < NAW && wn * NAW + j < NA) {
@@ -420,32 +449,29 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
             for (int j = 0; j < 8; ++j) {
                 if (j < NAW && wn * NAW + j < NA) {
                     const int col = (wn * NAW + j) * 8 + 2 * t;
-                    float* r0 = s.g.A + (size_t)(wm * 16 + g) * SN + col;
+                    float* r0 = sA + (size_t)(wm * 16 + g) * SN + col;
                     *reinterpret_cast<float2*>(r0) = make_float2(acca[j][0], acca[j][1]);
                     *reinterpret_cast<float2*>(r0 + 8 * SN) = make_float2(acca[j][2], acca[j][3]);
                 }
             }
             __syncthreads();
             // bilinear scatter of the dA rows
-            {
-                const long N = (long)d.X * d.Y * d.Z;
-                const int hw = d.h * d.w;
-                for (int rr = 0; rr < kFuseRows / kFuseWarps; ++rr) {
-                    const int r = warp * (kFuseRows / kFuseWarps) + rr;
-                    const long long row = s.g.row[r];
-                    if (row < 0) continue;
-                    const int b = (int)(row / N);
-                    unsigned mm = s.g.vmask[r] & want;
-                    while (mm) {
-                        const int c = __ffs(mm) - 1;
-                        mm &= mm - 1;
-                        const Corners q = make_corners(s.g.slot[c * kFuseRows + r], d.w, d.h, C);
-                        float* fb = a.d_feats + ((size_t)b * d.num_cams + c) * hw * C;
-                        for (int k = lane * 4; k < C; k += 128) {
-                            const float4 gv = *reinterpret_cast<const float4*>(s.g.A + (size_t)r * SN + k);
 #pragma unroll
-                            for (int u = 0; u < 4; ++u)
-                                if (q.wgt[u] != 0.f) red_add_f4(fb + q.off[u] + k, f4_scale(q.wgt[u], gv));
+            for (int rr = 0; rr < kRowsPerWarp; ++rr) {
+                const int r = warp * kRowsPerWarp + rr;
+                const int cnt = tm.cnt[r];
+                for (int e = 0; e < cnt; ++e) {
+                    const int4 off = tm.off[e * kFuseRows + r];
+                    const float4 wg = tm.wgt[e * kFuseRows + r];
+                    float* fb = a.d_feats + (size_t)tm.meta[e * kFuseRows + r].x * map + lane * 4;
+#pragma unroll
+                    for (int i = 0; i < NCH; ++i) {
+                        if (i * 128 + lane * 4 < C) {
+                            const float4 gv = *reinterpret_cast<const float4*>(sA + (size_t)r * SN + i * 128 + lane * 4);
+                            if (wg.x != 0.f) red_add_f4(fb + off.x + i * 128, f4_scale(wg.x, gv));
+                            if (wg.y != 0.f) red_add_f4(fb + off.y + i * 128, f4_scale(wg.y, gv));
+                            if (wg.z != 0.f) red_add_f4(fb + off.z + i * 128, f4_scale(wg.z, gv));
+                            if (wg.w != 0.f) red_add_f4(fb + off.w + i * 128, f4_scale(wg.w, gv));
                         }
                     }
                 }
@@ -514,6 +540,15 @@ static int sm_count() {
     return n;
 }
 
+template <typename Kern>
+static int launch_fuse(Kern kern, const FuseArgs& a, size_t smem, int sms, cudaStream_t st) {
+    if (smem > 227 * 1024) return VFD_ERR_UNSUPPORTED;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return VFD_ERR_CUDA;
+    kern<<<sms, kFuseThreads, smem, st>>>(a);
+    return VFD_OK;
+}
+
 }  // namespace vfd
 
 using namespace vfd;
@@ -537,14 +572,12 @@ extern "C" int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, 
     cudaStream_t st = (cudaStream_t)stream;
     const size_t vol_bytes = (size_t)d->B * d->X * d->Y * d->Z * d->Cv * sizeof(float);
     if (cudaMemsetAsync(vol, 0, vol_bytes, st) != cudaSuccess) return VFD_ERR_CUDA;
-    const size_t smem = fuse_fwd_smem_bytes(a.KP);
-    if (smem > 227 * 1024) return VFD_ERR_UNSUPPORTED;
-    if (cudaFuncSetAttribute(voxel_fuse_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
-        cudaSuccess)
-        return VFD_ERR_CUDA;
     const int sms = sm_count();
     if (sms <= 0) return VFD_ERR_CUDA;
-    voxel_fuse_fwd_kernel<<<sms, kFuseThreads, smem, st>>>(a);
+    const size_t smem = fuse_fwd_smem_bytes(a.KP);
+    rc = d->C > 128 ? launch_fuse(voxel_fuse_fwd_kernel<2>, a, smem, sms, st)
+                    : launch_fuse(voxel_fuse_fwd_kernel<1>, a, smem, sms, st);
+    if (rc) return rc;
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
@@ -582,11 +615,9 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
     const size_t fbytes = (size_t)d->B * d->num_cams * d->h * d->w * d->C * sizeof(float);
     if (cudaMemsetAsync(d_feats, 0, fbytes, st) != cudaSuccess) return VFD_ERR_CUDA;
     const size_t smem = fuse_bwd_smem_bytes(a.KP, a.NT);
-    if (smem > 227 * 1024) return VFD_ERR_UNSUPPORTED;
-    if (cudaFuncSetAttribute(voxel_fuse_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
-        cudaSuccess)
-        return VFD_ERR_CUDA;
-    voxel_fuse_bwd_kernel<<<sms, kFuseThreads, smem, st>>>(a);
+    rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2>, a, smem, sms, st)
+                    : launch_fuse(voxel_fuse_bwd_kernel<1>, a, smem, sms, st);
+    if (rc) return rc;
     const int total = 3 * d->Cv * (d->C + 2);
     voxel_fuse_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(a.partial, sms, d->Cv, d->C + 1, d_w_no, d_b_no,
                                                                   d_w_ov, d_b_ov);
