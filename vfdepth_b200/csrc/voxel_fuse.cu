@@ -61,8 +61,9 @@ struct TileMeta {
     int4* off;        // [2][64]  corner offsets (floats) inside the camera's feature map
     float4* wgt;      // [2][64]  corner weights
     int2* meta;       // [2][64]  {b*num_cams + c, bits of zrel}
+    unsigned char* ok;  // [8][64]  validity of (camera, row) while the entries are being numbered
 };
-constexpr size_t kMetaBytes = kFuseRows * (8 + 4 + kMaxEnt * (16 + 16 + 8));
+constexpr size_t kMetaBytes = kFuseRows * (8 + 4 + kMaxEnt * (16 + 16 + 8) + VFD_MAX_CAMS);
 
 __device__ __forceinline__ TileMeta carve_meta(unsigned char* base) {
     TileMeta m;
@@ -75,42 +76,55 @@ __device__ __forceinline__ TileMeta carve_meta(unsigned char* base) {
     m.meta = reinterpret_cast<int2*>(base);
     base += kMaxEnt * kFuseRows * 8;
     m.cnt = reinterpret_cast<int*>(base);
+    base += kFuseRows * 4;
+    m.ok = base;
     return m;
 }
 
-// threads r < 64: project list entry base+r into the cameras in `want`, keep the valid ones
+// All 512 threads: thread (camera c = tid / 64, row r = tid % 64) projects list entry base+r into camera c; the valid
+// cameras in `want` become the row's entries in camera order.  Contains one __syncthreads; the caller adds another
+// before the entries are read.
 __device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& tm, const int64_t* idx, int base, int M,
                                              unsigned want) {
     const vfd_fusion_desc& d = a.d;
-    const int r = threadIdx.x;
-    if (r >= kFuseRows) return;
+    const int r = threadIdx.x & (kFuseRows - 1), c = threadIdx.x >> 6;
     const long N = (long)d.X * d.Y * d.Z;
-    long long row = -1;
-    int n_ent = 0;
-    if (base + r < M) {
-        row = idx[base + r];
+    const long long row = (base + r < M) ? idx[base + r] : -1;
+    bool ok = false;
+    Corners q;
+    int bc = 0;
+    float zrel = 0.f;
+    if (row >= 0 && c < d.num_cams && ((want >> c) & 1u)) {
         const int b = (int)(row / N);
         const long n = row - (long)b * N;
         const int xi = (int)(n % d.X), yi = (int)((n / d.X) % d.Y), zi = (int)(n / ((long)d.X * d.Y));
         const float x = __ldg(d.axis_x + xi), y = __ldg(d.axis_y + yi), z = __ldg(d.axis_z + zi);
-        for (int c = 0; c < d.num_cams; ++c) {
-            if (!((want >> c) & 1u)) continue;
-            const int bc = b * d.num_cams + c;
-            float g[2];
-            CamSlot cs;
-            const bool ok = project_cam(d, a.mask_small + (size_t)bc * d.h * d.w, a.Einv + (size_t)bc * 16,
-                                        a.K + (size_t)bc * 16, x, y, z, cs, g);
-            if (ok && n_ent < kMaxEnt) {
-                const Corners q = make_corners(cs, d.w, d.h, d.C);
-                tm.off[n_ent * kFuseRows + r] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
-                tm.wgt[n_ent * kFuseRows + r] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
-                tm.meta[n_ent * kFuseRows + r] = make_int2(bc, __float_as_int(cs.zrel));
-                ++n_ent;
-            }
-        }
+        bc = b * d.num_cams + c;
+        float g[2];
+        CamSlot cs;
+        ok = project_cam(d, a.mask_small + (size_t)bc * d.h * d.w, a.Einv + (size_t)bc * 16, a.K + (size_t)bc * 16, x, y,
+                         z, cs, g);
+        q = make_corners(cs, d.w, d.h, d.C);
+        zrel = cs.zrel;
     }
-    tm.row[r] = row;
-    tm.cnt[r] = n_ent;
+    tm.ok[c * kFuseRows + r] = ok ? 1 : 0;
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int cc = 0; cc < VFD_MAX_CAMS; ++cc) {
+        const int f = tm.ok[cc * kFuseRows + r];
+        total += f;
+        before += (cc < c) ? f : 0;
+    }
+    if (ok && before < kMaxEnt) {
+        tm.off[before * kFuseRows + r] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
+        tm.wgt[before * kFuseRows + r] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
+        tm.meta[before * kFuseRows + r] = make_int2(bc, __float_as_int(zrel));
+    }
+    if (c == 0) {
+        tm.row[r] = row;
+        tm.cnt[r] = min(total, kMaxEnt);
+    }
 }
 
 // warp-cooperative gather of one row into shared memory: arow[0..C) = sum over the row's entries of the bilinear
@@ -153,7 +167,7 @@ __device__ __forceinline__ void gather_row(const FuseArgs& a, const TileMeta& tm
 // Forward
 // ---------------------------------------------------------------------------------------------------------
 __host__ __device__ inline size_t fuse_fwd_smem_bytes(int KP) {
-    const size_t a_tile = (size_t)kFuseRows * (KP + 4) * 4, partials = (size_t)3 * kFuseRows * kWS * 4;
+    const size_t a_tile = (size_t)kFuseRows * (KP + 4) * 4, partials = (size_t)4 * kFuseRows * kWS * 4;
     return kMetaBytes + (size_t)2 * KP * kWS * 4 + (a_tile > partials ? a_tile : partials);
 }
 
@@ -224,61 +238,57 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
                     const uint32_t* bh = Bh + ks * 8 * kWS;
                     const uint32_t* bl = Bl + ks * 8 * kWS;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (j < NT) {
-                            const uint32_t bh0 = bh[j * 8], bh1 = bh[4 * kWS + j * 8];
-                            const uint32_t bl0 = bl[j * 8], bl1 = bl[4 * kWS + j * 8];
-                            mma_tf32(acc[j], al, bh0, bh1);
-                            mma_tf32(acc[j], ah, bl0, bl1);
-                            mma_tf32(acc[j], ah, bh0, bh1);
+                    for (int jg = 0; jg < 8; jg += 4) {
+                        if (jg < NT) {      // four independent accumulators per round: no back-to-back dependent MMAs
+                            uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                bh0[j] = bh[(jg + j) * 8];
+                                bh1[j] = bh[4 * kWS + (jg + j) * 8];
+                                bl0[j] = bl[(jg + j) * 8];
+                                bl1[j] = bl[4 * kWS + (jg + j) * 8];
+                            }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(acc[jg + j], al, bh0[j], bh1[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(acc[jg + j], ah, bl0[j], bl1[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(acc[jg + j], ah, bh0[j], bh1[j]);
                         }
                     }
                 }
             }
             __syncthreads();     // all warps are done with the A tile: reuse it for the K-split partial sums
-            float* P = sA;       // [3][64][kWS]
-            if (wk > 0) {
+            float* P = sA;       // [4][64][kWS]
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    if (j < NT) {
-                        float* p0 = P + ((size_t)(wk - 1) * kFuseRows + wm * 16 + g) * kWS + j * 8 + 2 * t;
-                        *reinterpret_cast<float2*>(p0) = make_float2(acc[j][0], acc[j][1]);
-                        *reinterpret_cast<float2*>(p0 + 8 * kWS) = make_float2(acc[j][2], acc[j][3]);
-                    }
+            for (int j = 0; j < 8; ++j) {
+                if (j < NT) {
+                    float* p0 = P + ((size_t)wk * kFuseRows + wm * 16 + g) * kWS + j * 8 + 2 * t;
+                    *reinterpret_cast<float2*>(p0) = make_float2(acc[j][0], acc[j][1]);
+                    *reinterpret_cast<float2*>(p0 + 8 * kWS) = make_float2(acc[j][2], acc[j][3]);
                 }
             }
             __syncthreads();
-            if (wk == 0) {
-                const long long row0 = tm.row[wm * 16 + g], row1 = tm.row[wm * 16 + g + 8];
+            {   // all threads: sum the four K quarters, finish the row and write it (one 16-byte store per quad)
+                const int nq = Cv / 4;
+                for (int i = threadIdx.x; i < kFuseRows * nq; i += blockDim.x) {
+                    const int r = i / nq, q = (i - r * nq) * 4;
+                    const long long row = tm.row[r];
+                    if (row < 0) continue;
+                    float4 y = *reinterpret_cast<const float4*>(P + (size_t)r * kWS + q);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int col = j * 8 + 2 * t;
-                    if (j < NT && col < Cv) {
-                        float y0 = acc[j][0], y1 = acc[j][1], y2 = acc[j][2], y3 = acc[j][3];
-#pragma unroll
-                        for (int q = 0; q < 3; ++q) {
-                            const float* p0 = P + ((size_t)q * kFuseRows + wm * 16 + g) * kWS + col;
-                            const float2 u = *reinterpret_cast<const float2*>(p0);
-                            const float2 v = *reinterpret_cast<const float2*>(p0 + 8 * kWS);
-                            y0 += u.x; y1 += u.y; y2 += v.x; y3 += v.y;
-                        }
-                        float* o0 = a.vol + (size_t)row0 * Cv + col;
-                        float* o1 = a.vol + (size_t)row1 * Cv + col;
-                        if (pass == 2) {   // add the group-0 half parked by pass 1
-                            if (row0 >= 0) { const float2 u = *reinterpret_cast<const float2*>(o0); y0 += u.x; y1 += u.y; }
-                            if (row1 >= 0) { const float2 v = *reinterpret_cast<const float2*>(o1); y2 += v.x; y3 += v.y; }
-                        }
-                        if (pass != 1) {
-                            const float b0 = __ldg(bias + col), b1 = __ldg(bias + col + 1);
-                            y0 += b0; y1 += b1; y2 += b0; y3 += b1;
-                            y0 = y0 > 0.f ? y0 : 0.1f * y0;
-                            y1 = y1 > 0.f ? y1 : 0.1f * y1;
-                            y2 = y2 > 0.f ? y2 : 0.1f * y2;
-                            y3 = y3 > 0.f ? y3 : 0.1f * y3;
-                        }
-                        if (row0 >= 0) *reinterpret_cast<float2*>(o0) = make_float2(y0, y1);
-                        if (row1 >= 0) *reinterpret_cast<float2*>(o1) = make_float2(y2, y3);
+                    for (int u = 1; u < 4; ++u)
+                        f4_add(y, *reinterpret_cast<const float4*>(P + ((size_t)u * kFuseRows + r) * kWS + q));
+                    float* o = a.vol + (size_t)row * Cv + q;
+                    if (pass == 2) f4_add(y, *reinterpret_cast<const float4*>(o));   // the group-0 half parked by pass 1
+                    if (pass != 1) {
+                        f4_add(y, ldg_f4(bias + q));
+                        y.x = y.x > 0.f ? y.x : 0.1f * y.x;
+                        y.y = y.y > 0.f ? y.y : 0.1f * y.y;
+                        y.z = y.z > 0.f ? y.z : 0.1f * y.z;
+                        y.w = y.w > 0.f ? y.w : 0.1f * y.w;
                     }
+                    *reinterpret_cast<float4*>(o) = y;
                 }
             }
             __syncthreads();   // the metadata and the A tile are rewritten by the next tile
@@ -392,13 +402,22 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
                     split_tf32(At[(ks + 4) * SN], ah[2], al[2]);
                     split_tf32(At[(ks + 4) * SN + 8], ah[3], al[3]);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (j < NT) {
-                            const uint32_t bh0 = Bh[ks * kZS + j * 8], bh1 = Bh[(ks + 4) * kZS + j * 8];
-                            const uint32_t bl0 = Bl[ks * kZS + j * 8], bl1 = Bl[(ks + 4) * kZS + j * 8];
-                            mma_tf32(accw[j], al, bh0, bh1);
-                            mma_tf32(accw[j], ah, bl0, bl1);
-                            mma_tf32(accw[j], ah, bh0, bh1);
+                    for (int jg = 0; jg < 8; jg += 4) {
+                        if (jg < NT) {
+                            uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                bh0[j] = Bh[ks * kZS + (jg + j) * 8];
+                                bh1[j] = Bh[(ks + 4) * kZS + (jg + j) * 8];
+                                bl0[j] = Bl[ks * kZS + (jg + j) * 8];
+                                bl1[j] = Bl[(ks + 4) * kZS + (jg + j) * 8];
+                            }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(accw[jg + j], al, bh0[j], bh1[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(accw[jg + j], ah, bl0[j], bl1[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(accw[jg + j], ah, bh0[j], bh1[j]);
                         }
                     }
                 }
@@ -432,14 +451,20 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
                     ah[2] = Z0h[ks + 4];        al[2] = Z0l[ks + 4];
                     ah[3] = Z0h[ks + 4 + 8 * kZS];  al[3] = Z0l[ks + 4 + 8 * kZS];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (j < NAW && wn * NAW + j < NA) {
-                            uint32_t bh0, bl0, bh1, bl1;
-                            split_tf32(Wb[ks * SN + j * 8], bh0, bl0);
-                            split_tf32(Wb[(ks + 4) * SN + j * 8], bh1, bl1);
-                            mma_tf32(acca[j], al, bh0, bh1);
-                            mma_tf32(acca[j], ah, bl0, bl1);
-                            mma_tf32(acca[j], ah, bh0, bh1);
+                    for (int jg = 0; jg < 8; jg += 4) {
+                        if (jg < NAW) {      // columns past NA read zero-padded / unused weight columns: harmless
+                            uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                split_tf32(Wb[ks * SN + (jg + j) * 8], bh0[j], bl0[j]);
+                                split_tf32(Wb[(ks + 4) * SN + (jg + j) * 8], bh1[j], bl1[j]);
+                            }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(acca[jg + j], al, bh0[j], bh1[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(acca[jg + j], ah, bl0[j], bl1[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) mma_tf32(acca[jg + j], ah, bh0[j], bh1[j]);
                         }
                     }
                 }
@@ -562,7 +587,7 @@ extern "C" int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, 
     if (!feats || !mask_small || !K || !Einv || !idx_no || !idx_ov || !totals || !w_no || !b_no || !w_ov || !b_ov ||
         !vol)
         return VFD_ERR_NULL;
-    if ((reinterpret_cast<uintptr_t>(feats) & 15) || (reinterpret_cast<uintptr_t>(vol) & 7)) return VFD_ERR_ALIGN;
+    if ((reinterpret_cast<uintptr_t>(feats) & 15) || (reinterpret_cast<uintptr_t>(vol) & 15)) return VFD_ERR_ALIGN;
     FuseArgs a = {};
     a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv;
     a.idx_no = idx_no; a.idx_ov = idx_ov; a.totals = totals;
