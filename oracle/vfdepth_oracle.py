@@ -122,7 +122,8 @@ def overlap_groups(num_cams):
     raise NotImplementedError
 
 
-def backproject_into_voxel(cfg, feats_agg, input_mask, K, E_inv, model='depth', mlp=None, detail=False):
+def backproject_into_voxel(cfg, feats_agg, input_mask, K, E_inv, model='depth', mlp=None, detail=False,
+                           slopes_from=None):
     """-> voxel_feat [B,64,N] (depth; needs ``mlp`` = dict(w_no,b_no,w_ov,b_ov)) or [B,C+1,N] (pose).
 
     With ``detail`` also returns the intermediates the parity tests compare: per-camera grids, valid masks,
@@ -142,8 +143,14 @@ def backproject_into_voxel(cfg, feats_agg, input_mask, K, E_inv, model='depth', 
         x_ov = torch.cat([sum(feats[i] for i in ga), sum(feats[i] for i in gb)], dim=1)
         ov_mask = (count == 2)
         if mlp is not None:
-            y_no = F.leaky_relu(F.conv1d(x_no, mlp['w_no'], mlp['b_no']), 0.1) * no_mask.float()
-            y_ov = F.leaky_relu(F.conv1d(x_ov, mlp['w_ov'], mlp['b_ov']), 0.1) * ov_mask.float()
+            z_no, z_ov = F.conv1d(x_no, mlp['w_no'], mlp['b_no']), F.conv1d(x_ov, mlp['w_ov'], mlp['b_ov'])
+            if slopes_from is None:
+                y_no, y_ov = F.leaky_relu(z_no, 0.1) * no_mask.float(), F.leaky_relu(z_ov, 0.1) * ov_mask.float()
+            else:
+                # test aid: LeakyReLU with the slope pattern PINNED to another implementation's output [B,Cv,N] (same
+                # values except where a pre-activation is ~0 and two fp32 implementations pick different slopes)
+                slope = torch.where(slopes_from > 0, 1.0, 0.1)
+                y_no, y_ov = z_no * slope * no_mask.float(), z_ov * slope * ov_mask.float()
             voxel_feat = y_no + y_ov
         else:
             voxel_feat = None

@@ -57,15 +57,13 @@ __device__ __forceinline__ Corners make_corners(const CamSlot& s, int w, int h, 
 }
 
 // ---- legacy-path tensor-core helpers (mma.sync m16n8k8 tf32, fp32 accumulate) for the fused 1x1 MLPs ----
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
-// x = hi + lo with hi, lo both TF32: three products hi*hi + hi*lo + lo*hi recover fp32 accuracy ("3xTF32")
+// x = hi + lo (+ a remainder below 2^-20 |x|) with hi, lo both exactly representable in TF32 (13 low mantissa bits
+// zero): three products hi*hi + hi*lo + lo*hi recover fp32-level accuracy ("3xTF32").  Truncation instead of
+// cvt.rna.tf32 (which sm_100a emulates with ~6 instructions): hi carries 10 explicit mantissa bits of x, lo the next
+// 10, and x - hi is exact in fp32.
 __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
-    hi = to_tf32(x);
-    lo = to_tf32(x - __uint_as_float(hi));
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi)) & 0xffffe000u;
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm(
