@@ -53,41 +53,53 @@ struct FuseArgs {
     int NT;              // ceil(Cv / 8)
 };
 
-// per-tile bookkeeping shared by forward and backward: for every row of the tile the (at most two) cameras of the
-// current pass that see the voxel, with their bilinear corners precomputed
-struct TileMeta {
-    long long* row;   // [64]     b*N+n, -1 past the end of the list
-    int* cnt;         // [64]     entries of this row in this pass
-    int4* off;        // [2][64]  corner offsets (floats) inside the camera's feature map
-    float4* wgt;      // [2][64]  corner weights
-    int2* meta;       // [2][64]  {b*num_cams + c, bits of zrel}
-    unsigned char* ok;  // [8][64]  validity of (camera, row) while the entries are being numbered
+// a group of warps that works on one tile: the whole CTA (barrier 0) or half of it (named barriers 1, 2)
+struct Group {
+    int tid, size, bar;
 };
-constexpr size_t kMetaBytes = kFuseRows * (8 + 4 + kMaxEnt * (16 + 16 + 8) + VFD_MAX_CAMS);
+__device__ __forceinline__ void group_sync(const Group& G) {
+    asm volatile("bar.sync %0, %1;" ::"r"(G.bar), "r"(G.size) : "memory");
+}
 
+// per-tile bookkeeping shared by forward and backward: for every row of the tile the (at most two) cameras of the
+// current pass that see the voxel, with their bilinear corners precomputed.  ROWS rows per tile.
+struct TileMeta {
+    long long* row;   // [ROWS]     b*N+n, -1 past the end of the list
+    int* cnt;         // [ROWS]     entries of this row in this pass
+    int4* off;        // [2][ROWS]  corner offsets (floats) inside the camera's feature map
+    float4* wgt;      // [2][ROWS]  corner weights
+    int2* meta;       // [2][ROWS]  {b*num_cams + c, bits of zrel}
+    unsigned char* ok;  // [8][ROWS]  validity of (camera, row) while the entries are being numbered
+};
+__host__ __device__ constexpr size_t meta_bytes(int rows) {
+    return (size_t)rows * (8 + 4 + kMaxEnt * (16 + 16 + 8) + VFD_MAX_CAMS);
+}
+
+template <int ROWS>
 __device__ __forceinline__ TileMeta carve_meta(unsigned char* base) {
     TileMeta m;
     m.row = reinterpret_cast<long long*>(base);
-    base += kFuseRows * 8;
+    base += ROWS * 8;
     m.off = reinterpret_cast<int4*>(base);
-    base += kMaxEnt * kFuseRows * 16;
+    base += kMaxEnt * ROWS * 16;
     m.wgt = reinterpret_cast<float4*>(base);
-    base += kMaxEnt * kFuseRows * 16;
+    base += kMaxEnt * ROWS * 16;
     m.meta = reinterpret_cast<int2*>(base);
-    base += kMaxEnt * kFuseRows * 8;
+    base += kMaxEnt * ROWS * 8;
     m.cnt = reinterpret_cast<int*>(base);
-    base += kFuseRows * 4;
+    base += ROWS * 4;
     m.ok = base;
     return m;
 }
 
-// All 512 threads: thread (camera c = tid / 64, row r = tid % 64) projects list entry base+r into camera c; the valid
-// cameras in `want` become the row's entries in camera order.  Contains one __syncthreads; the caller adds another
-// before the entries are read.
-__device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& tm, const int64_t* idx, int base, int M,
-                                             unsigned want) {
+// All ROWS*8 threads of the group: thread (camera c = tid / ROWS, row r = tid % ROWS) projects list entry base+r into
+// camera c; the valid cameras in `want` become the row's entries in camera order.  Contains one group barrier; the
+// caller adds another before the entries are read.
+template <int ROWS>
+__device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& tm, const Group& G, const int64_t* idx,
+                                             int base, int M, unsigned want) {
     const vfd_fusion_desc& d = a.d;
-    const int r = threadIdx.x & (kFuseRows - 1), c = threadIdx.x >> 6;
+    const int r = G.tid & (ROWS - 1), c = G.tid / ROWS;
     const long N = (long)d.X * d.Y * d.Z;
     const long long row = (base + r < M) ? idx[base + r] : -1;
     bool ok = false;
@@ -107,19 +119,19 @@ __device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& 
         q = make_corners(cs, d.w, d.h, d.C);
         zrel = cs.zrel;
     }
-    tm.ok[c * kFuseRows + r] = ok ? 1 : 0;
-    __syncthreads();
+    tm.ok[c * ROWS + r] = ok ? 1 : 0;
+    group_sync(G);
     int before = 0, total = 0;
 #pragma unroll
     for (int cc = 0; cc < VFD_MAX_CAMS; ++cc) {
-        const int f = tm.ok[cc * kFuseRows + r];
+        const int f = tm.ok[cc * ROWS + r];
         total += f;
         before += (cc < c) ? f : 0;
     }
     if (ok && before < kMaxEnt) {
-        tm.off[before * kFuseRows + r] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
-        tm.wgt[before * kFuseRows + r] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
-        tm.meta[before * kFuseRows + r] = make_int2(bc, __float_as_int(zrel));
+        tm.off[before * ROWS + r] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
+        tm.wgt[before * ROWS + r] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
+        tm.meta[before * ROWS + r] = make_int2(bc, __float_as_int(zrel));
     }
     if (c == 0) {
         tm.row[r] = row;
@@ -129,7 +141,7 @@ __device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& 
 
 // warp-cooperative gather of one row into shared memory: arow[0..C) = sum over the row's entries of the bilinear
 // sample, arow[C] = sum of the relative depths, arow[C+1..KP) = 0.  NCH = ceil(C / 128) chunks of 4 floats per lane.
-template <int NCH>
+template <int NCH, int ROWS>
 __device__ __forceinline__ void gather_row(const FuseArgs& a, const TileMeta& tm, int r, int lane, float* arow) {
     const int C = a.d.C;
     const size_t map = (size_t)a.d.h * a.d.w * C;
@@ -139,9 +151,9 @@ __device__ __forceinline__ void gather_row(const FuseArgs& a, const TileMeta& tm
     for (int i = 0; i < NCH; ++i) acc[i] = f4_zero();
     float zsum = 0.f;
     for (int e = 0; e < cnt; ++e) {
-        const int4 off = tm.off[e * kFuseRows + r];
-        const float4 wg = tm.wgt[e * kFuseRows + r];
-        const int2 me = tm.meta[e * kFuseRows + r];
+        const int4 off = tm.off[e * ROWS + r];
+        const float4 wg = tm.wgt[e * ROWS + r];
+        const int2 me = tm.meta[e * ROWS + r];
         const float* base = a.feats + (size_t)me.x * map + lane * 4;
         zsum += __int_as_float(me.y);
 #pragma unroll
@@ -164,11 +176,20 @@ __device__ __forceinline__ void gather_row(const FuseArgs& a, const TileMeta& tm
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Forward
+// Forward.  The CTA's 16 warps form two groups of 8 that share the weight planes but otherwise run independently
+// (named barriers), each on its own 32-voxel tiles: while one group waits for its L2 gathers the other keeps the tensor
+// pipe busy.  Inside a group: 2 row blocks of 16 x 4 quarters of the K range, partial sums reduced through shared memory.
 // ---------------------------------------------------------------------------------------------------------
+constexpr int kFwdRows = 32;
+constexpr int kFwdGroups = 2;
+constexpr int kFwdGroupThreads = kFuseThreads / kFwdGroups;
+
+__host__ __device__ inline size_t fuse_fwd_group_bytes(int KP) {
+    const size_t a_tile = (size_t)kFwdRows * (KP + 4) * 4, partials = (size_t)4 * kFwdRows * kWS * 4;
+    return meta_bytes(kFwdRows) + (a_tile > partials ? a_tile : partials);
+}
 __host__ __device__ inline size_t fuse_fwd_smem_bytes(int KP) {
-    const size_t a_tile = (size_t)kFuseRows * (KP + 4) * 4, partials = (size_t)4 * kFuseRows * kWS * 4;
-    return kMetaBytes + (size_t)2 * KP * kWS * 4 + (a_tile > partials ? a_tile : partials);
+    return (size_t)2 * KP * kWS * 4 + kFwdGroups * fuse_fwd_group_bytes(KP);
 }
 
 template <int NCH>
@@ -176,14 +197,17 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const vfd_fusion_desc& d = a.d;
     const int KP = a.KP, AS = KP + 4, NT = a.NT, C1 = d.C + 1, Cv = d.Cv;
-    const TileMeta tm = carve_meta(smem_raw);
-    uint32_t* Whi = reinterpret_cast<uint32_t*>(smem_raw + kMetaBytes);   // [KP][kWS] tf32 hi plane, [k][n]
+    uint32_t* Whi = reinterpret_cast<uint32_t*>(smem_raw);                // [KP][kWS] tf32 hi plane, [k][n]
     uint32_t* Wlo = Whi + (size_t)KP * kWS;
-    float* sA = reinterpret_cast<float*>(Wlo + (size_t)KP * kWS);         // [64][AS]; later the K-split partials
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int wm = warp & 3, wk = warp >> 2;      // 16-row block, quarter of the K range
+    const int grp = threadIdx.x / kFwdGroupThreads;
+    const Group G = {(int)threadIdx.x - grp * kFwdGroupThreads, kFwdGroupThreads, 1 + grp};
+    unsigned char* gbase = smem_raw + (size_t)2 * KP * kWS * 4 + (size_t)grp * fuse_fwd_group_bytes(KP);
+    const TileMeta tm = carve_meta<kFwdRows>(gbase);
+    float* sA = reinterpret_cast<float*>(gbase + meta_bytes(kFwdRows));   // [32][AS]; later the K-split partials
+    const int warp = G.tid >> 5, lane = G.tid & 31, g = lane >> 2, t = lane & 3;
+    const int wm = warp & 1, wk = warp >> 1;      // 16-row block, quarter of the K range
     const int M1 = a.totals[0], M2 = a.totals[1];
-    const int T1 = (M1 + kFuseRows - 1) / kFuseRows, T2 = (M2 + kFuseRows - 1) / kFuseRows;
+    const int T1 = (M1 + kFwdRows - 1) / kFwdRows, T2 = (M2 + kFwdRows - 1) / kFwdRows;
     unsigned gmask[2] = {0u, 0u};
     for (int c = 0; c < d.num_cams; ++c) gmask[d.group[c] ? 1 : 0] |= 1u << c;
     const int nk = KP / 8, kq = (nk + 3) / 4;
@@ -208,15 +232,16 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
                 Wlo[k * kWS + n] = lo;
             }
         }
-        for (int tile = blockIdx.x; tile < T; tile += gridDim.x) {
-            project_tile(a, tm, idx, tile * kFuseRows, M, want);
-            __syncthreads();
+        __syncthreads();
+        for (int tile = blockIdx.x * kFwdGroups + grp; tile < T; tile += gridDim.x * kFwdGroups) {
+            project_tile<kFwdRows>(a, tm, G, idx, tile * kFwdRows, M, want);
+            group_sync(G);
 #pragma unroll
-            for (int rr = 0; rr < kRowsPerWarp; ++rr) {
-                const int r = warp * kRowsPerWarp + rr;
-                gather_row<NCH>(a, tm, r, lane, sA + (size_t)r * AS);
+            for (int rr = 0; rr < 4; ++rr) {
+                const int r = warp * 4 + rr;
+                gather_row<NCH, kFwdRows>(a, tm, r, lane, sA + (size_t)r * AS);
             }
-            __syncthreads();
+            group_sync(G);
 
             // [16 rows x (this warp's K quarter)] x [K x Cv]: 3xTF32 on the tensor cores
             float acc[8][4];
@@ -258,27 +283,27 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
                     }
                 }
             }
-            __syncthreads();     // all warps are done with the A tile: reuse it for the K-split partial sums
-            float* P = sA;       // [4][64][kWS]
+            group_sync(G);       // the group is done with the A tile: reuse it for the K-split partial sums
+            float* P = sA;       // [4][32][kWS]
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 if (j < NT) {
-                    float* p0 = P + ((size_t)wk * kFuseRows + wm * 16 + g) * kWS + j * 8 + 2 * t;
+                    float* p0 = P + ((size_t)wk * kFwdRows + wm * 16 + g) * kWS + j * 8 + 2 * t;
                     *reinterpret_cast<float2*>(p0) = make_float2(acc[j][0], acc[j][1]);
                     *reinterpret_cast<float2*>(p0 + 8 * kWS) = make_float2(acc[j][2], acc[j][3]);
                 }
             }
-            __syncthreads();
-            {   // all threads: sum the four K quarters, finish the row and write it (one 16-byte store per quad)
+            group_sync(G);
+            {   // sum the four K quarters, finish the row and write it (one 16-byte store per quad)
                 const int nq = Cv / 4;
-                for (int i = threadIdx.x; i < kFuseRows * nq; i += blockDim.x) {
+                for (int i = G.tid; i < kFwdRows * nq; i += G.size) {
                     const int r = i / nq, q = (i - r * nq) * 4;
                     const long long row = tm.row[r];
                     if (row < 0) continue;
                     float4 y = *reinterpret_cast<const float4*>(P + (size_t)r * kWS + q);
 #pragma unroll
                     for (int u = 1; u < 4; ++u)
-                        f4_add(y, *reinterpret_cast<const float4*>(P + ((size_t)u * kFuseRows + r) * kWS + q));
+                        f4_add(y, *reinterpret_cast<const float4*>(P + ((size_t)u * kFwdRows + r) * kWS + q));
                     float* o = a.vol + (size_t)row * Cv + q;
                     if (pass == 2) f4_add(y, *reinterpret_cast<const float4*>(o));   // the group-0 half parked by pass 1
                     if (pass != 1) {
@@ -291,7 +316,7 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
                     *reinterpret_cast<float4*>(o) = y;
                 }
             }
-            __syncthreads();   // the metadata and the A tile are rewritten by the next tile
+            group_sync(G);     // the metadata and the A tile are rewritten by the next tile
         }
     }
 }
@@ -312,7 +337,7 @@ __host__ __device__ inline int fuse_sn(int KP) { return (KP - 8 + 31) / 32 * 32 
 
 __host__ __device__ inline size_t fuse_bwd_smem_bytes(int KP, int NT) {
     const int SN = fuse_sn(KP);
-    return kMetaBytes + (size_t)NT * 8 * SN * 4 + (size_t)kFuseRows * SN * 4 + (size_t)2 * kFuseRows * kZS * 4;
+    return meta_bytes(kFuseRows) + (size_t)NT * 8 * SN * 4 + (size_t)kFuseRows * SN * 4 + (size_t)2 * kFuseRows * kZS * 4;
 }
 
 template <int NCH>
@@ -320,8 +345,9 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const vfd_fusion_desc& d = a.d;
     const int KP = a.KP, SN = fuse_sn(KP), NT = a.NT, C = d.C, C1 = C + 1, Cv = d.Cv;
-    const TileMeta tm = carve_meta(smem_raw);
-    float* sW = reinterpret_cast<float*>(smem_raw + kMetaBytes);          // [NT*8][SN] natural layout [out][in]
+    const TileMeta tm = carve_meta<kFuseRows>(smem_raw);
+    const Group G = {(int)threadIdx.x, kFuseThreads, 0};
+    float* sW = reinterpret_cast<float*>(smem_raw + meta_bytes(kFuseRows));          // [NT*8][SN] natural layout [out][in]
     float* sA = sW + (size_t)NT * 8 * SN;                                 // [64][SN]: A, then dA
     uint32_t* Zhi = reinterpret_cast<uint32_t*>(sA + (size_t)kFuseRows * SN);   // [64][kZS]
     uint32_t* Zlo = Zhi + kFuseRows * kZS;
@@ -358,7 +384,7 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
         float db = 0.f, dwz = 0.f;           // threads o < Cv: bias gradient and the relative-depth column of dW
 
         for (int tile = blockIdx.x; tile < T; tile += gridDim.x) {
-            project_tile(a, tm, idx, tile * kFuseRows, M, want);
+            project_tile<kFuseRows>(a, tm, G, idx, tile * kFuseRows, M, want);
             __syncthreads();
             // dZ tile, split once
             for (int i = threadIdx.x; i < kFuseRows * (kZS / 4); i += blockDim.x) {
@@ -385,7 +411,7 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
 #pragma unroll
             for (int rr = 0; rr < kRowsPerWarp; ++rr) {
                 const int r = warp * kRowsPerWarp + rr;
-                gather_row<NCH>(a, tm, r, lane, sA + (size_t)r * SN);
+                gather_row<NCH, kFuseRows>(a, tm, r, lane, sA + (size_t)r * SN);
             }
             __syncthreads();
 
