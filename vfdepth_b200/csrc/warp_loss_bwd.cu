@@ -53,7 +53,7 @@ __device__ __forceinline__ float pick5(const float (*v)[3], int k, int c) {
     return r;
 }
 
-__global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossBwdArgs a) {
+__global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const LossBwdArgs a) {
     using Rg = Region<2>;
     const vfd_warp_desc& d = a.d;
     __shared__ WarpCtx ctx;
@@ -212,12 +212,22 @@ __global__ void __launch_bounds__(kTileThreads) warp_loss_bwd_kernel(const LossB
                 }
             }
         }
+        {   // warp sum of the 12 values as a reduce-scatter butterfly (16 shuffles instead of 60, fixed order):
+            // after the steps over lane bits 4..1 lane l holds element l >> 1 summed over half the warp
+            float v[16];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) {
-            float v = dP[i];
+            for (int i = 0; i < 16; ++i) v[i] = i < 12 ? dP[i] : 0.f;
 #pragma unroll
-            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0) s_dP[wid][j * 12 + i] = v;
+            for (int n = 8; n >= 1; n >>= 1) {
+                const bool up = (lane & (2 * n)) != 0;
+#pragma unroll
+                for (int i = 0; i < n; ++i) {
+                    const float keep = up ? v[i + n] : v[i], send = up ? v[i] : v[i + n];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2 * n);
+                }
+            }
+            v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+            if (!(lane & 1) && (lane >> 1) < 12) s_dP[wid][j * 12 + (lane >> 1)] = v[0];
         }
     }
     if (live) a.d_depth[(size_t)(b * d.n_call + ci) * HW + y * W + x] = gdepth;

@@ -50,43 +50,82 @@ __device__ __forceinline__ void warp_slot(int j, int n_src, int R, int omask0, i
 }
 
 // Phase A.  Caller synchronises afterwards.  Pixels of the region outside the image are never read.
-template <int HALO>
-__device__ __forceinline__ void fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
-                                            const float4* __restrict__ raw, float* sm) {
+// NSRC (= n_src, 1 or 2) is a template parameter so that the warp -> plane mapping is static: all raw warps and the
+// un-warped images of a pixel are loaded in one batch (8 x 16 B + 9 x 4 B in flight per thread), combined in registers
+// in the reference's order (neighbour k = 0, then 1, view_rendering.py:193-198) and written once.
+template <int HALO, int NSRC>
+__device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
+                                              const float4* __restrict__ raw, float* sm) {
     using Rg = Region<HALO>;
-    const int W = d.W, H = d.H, HW = H * W, cam = d.cam0 + ci, NW = ctx.NW, n_src = d.n_src;
+    constexpr int NWc = NSRC + (1 + NSRC) * VFD_WARP_NBR;
+    const int W = d.W, H = d.H, HW = H * W, cam = d.cam0 + ci;
     const float* ref = d.color[0] + (size_t)(b * d.num_cams + cam) * 3 * HW;
     const float* src0 = d.color[1] + (size_t)(b * d.num_cams + cam) * 3 * HW;
-    const float* src1 = d.color[n_src] + (size_t)(b * d.num_cams + cam) * 3 * HW;   // == src0 when n_src == 1 (unused)
+    const float* src1 = d.color[NSRC] + (size_t)(b * d.num_cams + cam) * 3 * HW;   // == src0 when NSRC == 1 (unused)
     float2* img = reinterpret_cast<float2*>(sm + Rg::kImg);
-    constexpr int kChan = kPairs * Rg::R * 2;      // floats per channel block
+    bool act[NWc];
+#pragma unroll
+    for (int j = 0; j < NWc; ++j) act[j] = ctx.active[j] != 0;
     for (int r = threadIdx.x; r < Rg::R; r += kTileThreads) {
         const int x = ox + r % Rg::RW, y = oy + r / Rg::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
-        // this thread owns pixel r of every plane: zero the accumulated ones, place the un-warped images
+        float4 w[NWc];
+#pragma unroll
+        for (int j = 0; j < NWc; ++j) w[j] = act[j] ? __ldg(raw + (size_t)j * HW + p) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float vr[3], v0[3], v1[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            vr[c] = __ldg(ref + c * HW + p);
+            v0[c] = __ldg(src0 + c * HW + p);
+            v1[c] = __ldg(src1 + c * HW + p);
+        }
+        // temporal warps -> pair 0 (.x = frame 1, .y = frame 2); their masks -> cmask planes
+        float tw[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}, cm[2] = {0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < NSRC; ++j) {
+            if (act[j]) {
+                tw[j][0] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].x, w[j].w));
+                tw[j][1] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].y, w[j].w));
+                tw[j][2] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].z, w[j].w));
+                cm[j] = VFD_ADD(0.f, w[j].w);
+            }
+        }
+        // neighbour warps of frame fi, summed over the two neighbours: fi = 0 -> pair 2.x, fi = 1, 2 -> pair 1.x / .y
+        float ov[3][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}, om[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int fi = 0; fi <= NSRC; ++fi) {
+#pragma unroll
+            for (int k = 0; k < VFD_WARP_NBR; ++k) {
+                const int j = NSRC + fi * VFD_WARP_NBR + k;
+                if (act[j]) {
+                    ov[fi][0] = VFD_ADD(ov[fi][0], warp_normalise(ctx.prm[j], w[j].x, w[j].w));
+                    ov[fi][1] = VFD_ADD(ov[fi][1], warp_normalise(ctx.prm[j], w[j].y, w[j].w));
+                    ov[fi][2] = VFD_ADD(ov[fi][2], warp_normalise(ctx.prm[j], w[j].z, w[j].w));
+                    om[fi] = VFD_ADD(om[fi], w[j].w);
+                }
+            }
+        }
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             float2* pc = img + c * kPairs * Rg::R + r;
-            pc[0 * Rg::R] = make_float2(0.f, 0.f);
-            pc[1 * Rg::R] = make_float2(0.f, 0.f);
-            pc[2 * Rg::R] = make_float2(0.f, __ldg(src0 + c * HW + p));
-            pc[3 * Rg::R] = make_float2(__ldg(src1 + c * HW + p), __ldg(ref + c * HW + p));
+            pc[0 * Rg::R] = make_float2(tw[0][c], tw[1][c]);
+            pc[1 * Rg::R] = make_float2(ov[1][c], ov[2][c]);
+            pc[2 * Rg::R] = make_float2(ov[0][c], v0[c]);
+            pc[3 * Rg::R] = make_float2(v1[c], vr[c]);
         }
 #pragma unroll
-        for (int f = 0; f < 1 + 2 * VFD_WARP_SRC; ++f) sm[Rg::kOmask + f * Rg::R + r] = 0.f;   // omask + cmask planes
-        for (int j = 0; j < NW; ++j) {
-            if (!ctx.active[j]) continue;
-            const float4 w = __ldg(raw + (size_t)j * HW + p);
-            int io, mo;
-            warp_slot(j, n_src, Rg::R, Rg::kOmask, Rg::kCmask, &io, &mo);
-            float* dst = sm + Rg::kImg + io + 2 * r;
-            dst[0] = VFD_ADD(dst[0], warp_normalise(ctx.prm[j], w.x, w.w));
-            dst[kChan] = VFD_ADD(dst[kChan], warp_normalise(ctx.prm[j], w.y, w.w));
-            dst[2 * kChan] = VFD_ADD(dst[2 * kChan], warp_normalise(ctx.prm[j], w.z, w.w));
-            sm[mo + r] = VFD_ADD(sm[mo + r], w.w);
-        }
+        for (int f = 0; f < 1 + VFD_WARP_SRC; ++f) sm[Rg::kOmask + f * Rg::R + r] = om[f];
+#pragma unroll
+        for (int f = 0; f < VFD_WARP_SRC; ++f) sm[Rg::kCmask + f * Rg::R + r] = cm[f];
     }
+}
+
+template <int HALO>
+__device__ __forceinline__ void fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
+                                            const float4* __restrict__ raw, float* sm) {
+    if (d.n_src == 2) fill_region_n<HALO, 2>(ctx, d, b, ci, ox, oy, raw, sm);
+    else fill_region_n<HALO, 1>(ctx, d, b, ci, ox, oy, raw, sm);
 }
 
 // Everything the loss decides at one pixel (single_cam_loss.py:17-55, multi_cam_loss.py:16-59).
