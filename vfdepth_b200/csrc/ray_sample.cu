@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
 }
 
 template <int CV>
-__global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_vec_kernel(const RayArgs a) {
+__global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_kernel(const RayArgs a) {
     constexpr int kLanes = CV / 4, kBins = VFD_WARP / kLanes;
     const vfd_fusion_desc& d = a.d;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -317,30 +317,43 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_bwd_vec_kernel
             float4 acc[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
-            float4 g = ld_stream_f4(gp);
-            for (int v = 0; v < H; ++v) {
-                const RaySlot s = slot[q * H + v];
-                const float4 gn = (v + 1 < H) ? ld_stream_f4(gp + (v + 1) * gstride) : f4_zero();   // prefetch
-                if (s.corners) {
-                    if (s.base != cur_base) {
-                        if (cur_corners) {
-                            float* p0 = dvol + (long)cur_base * CV;
+            // the gradient column is read once, straight from HBM: keep kPf rows per lane in flight (next chunk is
+            // requested before the current one is consumed)
+            constexpr int kPf = 4;
+            float4 g[kPf], gn[kPf];
 #pragma unroll
-                            for (int k = 0; k < 8; ++k)
-                                if (cur_corners & (1u << k))
-                                    red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
+            for (int i = 0; i < kPf; ++i) g[i] = (i < H) ? ld_stream_f4(gp + i * gstride) : f4_zero();
+            for (int v0 = 0; v0 < H; v0 += kPf) {
+#pragma unroll
+                for (int i = 0; i < kPf; ++i)
+                    gn[i] = (v0 + kPf + i < H) ? ld_stream_f4(gp + (size_t)(v0 + kPf + i) * gstride) : f4_zero();
+#pragma unroll
+                for (int i = 0; i < kPf; ++i) {
+                    const int v = v0 + i;
+                    if (v >= H) break;
+                    const RaySlot s = slot[q * H + v];
+                    if (s.corners) {
+                        if (s.base != cur_base) {
+                            if (cur_corners) {
+                                float* p0 = dvol + (long)cur_base * CV;
+#pragma unroll
+                                for (int k = 0; k < 8; ++k)
+                                    if (cur_corners & (1u << k))
+                                        red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
+                            }
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
+                            cur_base = s.base;
+                            cur_corners = s.corners;
                         }
+                        float w[8];
+                        corner_weights(s, w);
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
-                        cur_base = s.base;
-                        cur_corners = s.corners;
+                        for (int k = 0; k < 8; ++k) f4_fma(acc[k], w[k], g[i]);
                     }
-                    float w[8];
-                    corner_weights(s, w);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) f4_fma(acc[k], w[k], g);
                 }
-                g = gn;
+#pragma unroll
+                for (int i = 0; i < kPf; ++i) g[i] = gn[i];
             }
             if (cur_corners) {
                 float* p0 = dvol + (long)cur_base * CV;
