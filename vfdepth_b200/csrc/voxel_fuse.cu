@@ -139,40 +139,70 @@ __device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& 
     }
 }
 
-// warp-cooperative gather of one row into shared memory: arow[0..C) = sum over the row's entries of the bilinear
-// sample, arow[C] = sum of the relative depths, arow[C+1..KP) = 0.  NCH = ceil(C / 128) chunks of 4 floats per lane.
-template <int NCH, int ROWS>
-__device__ __forceinline__ void gather_row(const FuseArgs& a, const TileMeta& tm, int r, int lane, float* arow) {
+// warp-cooperative gather of NR consecutive rows into shared memory: arow[0..C) = sum over the row's entries of the
+// bilinear sample, arow[C] = sum of the relative depths, arow[C+1..KP) = 0.  NCH = ceil(C / 128) chunks of 4 floats per
+// lane.  The corner rows of all NR voxels (first entry each) are requested before any is consumed: NR * NCH * 4 128-bit
+// loads in flight per lane; a second entry (two cameras of one group, rare) is added afterwards.
+template <int NCH, int ROWS, int NR>
+__device__ __forceinline__ void gather_rows(const FuseArgs& a, const TileMeta& tm, int r0, int lane, float* arow0,
+                                            int stride) {
     const int C = a.d.C;
     const size_t map = (size_t)a.d.h * a.d.w * C;
-    const int cnt = tm.cnt[r];
-    float4 acc[NCH];
+    int cnt[NR];
+    float4 wg[NR], v[NR][NCH][4];
+    float zsum[NR];
 #pragma unroll
-    for (int i = 0; i < NCH; ++i) acc[i] = f4_zero();
-    float zsum = 0.f;
-    for (int e = 0; e < cnt; ++e) {
-        const int4 off = tm.off[e * ROWS + r];
-        const float4 wg = tm.wgt[e * ROWS + r];
-        const int2 me = tm.meta[e * ROWS + r];
+    for (int n = 0; n < NR; ++n) {
+        const int r = r0 + n;
+        cnt[n] = tm.cnt[r];
+        const int4 off = tm.off[r];
+        wg[n] = tm.wgt[r];
+        const int2 me = tm.meta[r];
         const float* base = a.feats + (size_t)me.x * map + lane * 4;
-        zsum += __int_as_float(me.y);
+        zsum[n] = cnt[n] > 0 ? __int_as_float(me.y) : 0.f;
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
-            if (i * 128 + lane * 4 < C) {
-                const float4 v0 = ldg_f4(base + off.x + i * 128), v1 = ldg_f4(base + off.y + i * 128);
-                const float4 v2 = ldg_f4(base + off.z + i * 128), v3 = ldg_f4(base + off.w + i * 128);
-                float4 t = f4_scale(wg.x, v0);
-                f4_fma(t, wg.y, v1);
-                f4_fma(t, wg.z, v2);
-                f4_fma(t, wg.w, v3);
-                f4_add(acc[i], t);
-            }
+            const bool on = cnt[n] > 0 && i * 128 + lane * 4 < C;
+            v[n][i][0] = on ? ldg_f4(base + off.x + i * 128) : f4_zero();
+            v[n][i][1] = on ? ldg_f4(base + off.y + i * 128) : f4_zero();
+            v[n][i][2] = on ? ldg_f4(base + off.z + i * 128) : f4_zero();
+            v[n][i][3] = on ? ldg_f4(base + off.w + i * 128) : f4_zero();
         }
     }
 #pragma unroll
-    for (int i = 0; i < NCH; ++i)
-        if (i * 128 + lane * 4 < C) *reinterpret_cast<float4*>(arow + i * 128 + lane * 4) = acc[i];
-    for (int k = C + lane; k < a.KP; k += VFD_WARP) arow[k] = (k == C) ? zsum : 0.f;
+    for (int n = 0; n < NR; ++n) {
+        const int r = r0 + n;
+        float* arow = arow0 + (size_t)n * stride;
+        float4 acc[NCH];
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+            acc[i] = f4_scale(wg[n].x, v[n][i][0]);
+            f4_fma(acc[i], wg[n].y, v[n][i][1]);
+            f4_fma(acc[i], wg[n].z, v[n][i][2]);
+            f4_fma(acc[i], wg[n].w, v[n][i][3]);
+        }
+        for (int e = 1; e < cnt[n]; ++e) {
+            const int4 off = tm.off[e * ROWS + r];
+            const float4 w2 = tm.wgt[e * ROWS + r];
+            const int2 me = tm.meta[e * ROWS + r];
+            const float* base = a.feats + (size_t)me.x * map + lane * 4;
+            zsum[n] += __int_as_float(me.y);
+#pragma unroll
+            for (int i = 0; i < NCH; ++i) {
+                if (i * 128 + lane * 4 < C) {
+                    float4 t = f4_scale(w2.x, ldg_f4(base + off.x + i * 128));
+                    f4_fma(t, w2.y, ldg_f4(base + off.y + i * 128));
+                    f4_fma(t, w2.z, ldg_f4(base + off.z + i * 128));
+                    f4_fma(t, w2.w, ldg_f4(base + off.w + i * 128));
+                    f4_add(acc[i], t);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NCH; ++i)
+            if (i * 128 + lane * 4 < C) *reinterpret_cast<float4*>(arow + i * 128 + lane * 4) = acc[i];
+        for (int k = C + lane; k < a.KP; k += VFD_WARP) arow[k] = (k == C) ? zsum[n] : 0.f;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -237,10 +267,8 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
             project_tile<kFwdRows>(a, tm, G, idx, tile * kFwdRows, M, want);
             group_sync(G);
 #pragma unroll
-            for (int rr = 0; rr < 4; ++rr) {
-                const int r = warp * 4 + rr;
-                gather_row<NCH, kFwdRows>(a, tm, r, lane, sA + (size_t)r * AS);
-            }
+            for (int rr = 0; rr < 4; rr += 2)
+                gather_rows<NCH, kFwdRows, 2>(a, tm, warp * 4 + rr, lane, sA + (size_t)(warp * 4 + rr) * AS, AS);
             group_sync(G);
 
             // [16 rows x (this warp's K quarter)] x [K x Cv]: 3xTF32 on the tensor cores
@@ -409,10 +437,9 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
             }
             // recompute the gathered rows
 #pragma unroll
-            for (int rr = 0; rr < kRowsPerWarp; ++rr) {
-                const int r = warp * kRowsPerWarp + rr;
-                gather_row<NCH, kFuseRows>(a, tm, r, lane, sA + (size_t)r * SN);
-            }
+            for (int rr = 0; rr < kRowsPerWarp; rr += 2)
+                gather_rows<NCH, kFuseRows, 2>(a, tm, warp * kRowsPerWarp + rr, lane,
+                                               sA + (size_t)(warp * kRowsPerWarp + rr) * SN, SN);
             __syncthreads();
 
             // dW^T block [16 in x Cv out] += A^T [16 x 64] dZ [64 x Cv]
