@@ -1,0 +1,46 @@
+"""Read an .ncu-rep (ncu --set full) and write a per-kernel summary CSV + profiles/traffic.json (DRAM bytes per launch,
+keyed by the C-ABI entry point that launches the kernel; bench.py reports it as roofline.traffic)."""
+import csv
+import io
+import json
+import subprocess
+import sys
+
+KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+        'launch__registers_per_thread', 'smsp__issue_active.avg.pct_of_peak_sustained_active',
+        'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active', 'l1tex__t_sector_hit_rate.pct',
+        'lts__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed']
+ABI = {'voxel_fuse_fwd_kernel': 'vfd_voxel_fuse_fwd', 'voxel_fuse_bwd_kernel': 'vfd_voxel_fuse_bwd',
+       'ray_sample_fwd_vec_kernel': 'vfd_ray_sample_fwd', 'ray_sample_bwd_vec_kernel': 'vfd_ray_sample_bwd',
+       'warp_stats_kernel': 'vfd_warp_stats', 'warp_loss_fwd_kernel': 'vfd_warp_loss_fwd',
+       'warp_loss_bwd_kernel': 'vfd_warp_loss_bwd', 'voxel_count_kernel': 'vfd_voxel_classify',
+       'voxel_gather_fwd_kernel': 'vfd_voxel_gather_depth_fwd', 'voxel_gather_bwd_kernel': 'vfd_voxel_gather_depth_bwd'}
+UNIT = {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}
+
+
+def main(rep, out_csv, out_json):
+    raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units = rows[0], rows[1]
+    col = {h: i for i, h in enumerate(hdr)}
+    name_i = col['Kernel Name']
+    traffic = {}
+    with open(out_csv, 'w', newline='') as f:
+        w = csv.writer(f)
+        w.writerow(['Kernel Name'] + KEYS)
+        w.writerow([''] + [units[col[k]] for k in KEYS])
+        for r in rows[2:]:
+            w.writerow([r[name_i]] + [r[col[k]] for k in KEYS])
+            for frag, abi in ABI.items():
+                if frag in r[name_i]:
+                    b = sum(float(r[col[k]].replace(',', '')) * UNIT[units[col[k]]]
+                            for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
+                    traffic.setdefault(abi, []).append(b)
+    with open(out_json, 'w') as f:
+        json.dump({k: sum(v) / len(v) for k, v in traffic.items()}, f, indent=1, sort_keys=True)
+    print(open(out_csv).read())
+
+
+if __name__ == '__main__':
+    main(*sys.argv[1:4])
