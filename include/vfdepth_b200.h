@@ -223,6 +223,22 @@ int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T
                       const float* raw, const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
                       size_t ws_bytes, void* stream);
 
+/* --------------------------------------------------------------------------------------------------
+ * Edge-aware disparity smoothness (models/losses/single_cam_loss.py:57-65, loss_util.py:28-40), scale 0, all cameras
+ * of the batch at once.
+ *   color   [B,cams,3,H,W]  inputs['color', 0, 0]
+ *   disp    [B,cams,H,W]    ('disp', 0) of every camera
+ *   img_sum [B*cams] f64    out: sum of disp per image (the mean of single_cam_loss.py:63), kept for the backward
+ *   sums    [cams][2] f64   out: sum over the batch of |d nd / dx| * exp(-|d rgb / dx|) and of the y term; the loss of
+ *                           camera c is sums[c][0] / (B*H*(W-1)) + sums[c][1] / (B*(H-1)*W)   (the two .mean() of :40)
+ * Both buffers are zero-filled here. */
+int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* color, const float* disp, double* img_sum,
+                        double* sums, void* stream);
+/* backward w.r.t. disp:  d_smooth [cams] upstream gradient of the per-camera loss, gdot [B*cams] f64 scratch
+ * (zero-filled here), d_disp [B,cams,H,W] written. */
+int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* color, const float* disp, const double* img_sum,
+                        const float* d_smooth, double* gdot, float* d_disp, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

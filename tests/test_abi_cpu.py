@@ -75,6 +75,9 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.vfd_voxel_fuse_fwd(*([null] * 14)) == -1
     assert lib.vfd_voxel_fuse_bwd(*([null] * 18), ctypes.c_size_t(0), null) == -1
     assert lib.vfd_voxel_fuse_bwd_workspace_bytes(null) == 0
+    assert lib.vfd_smooth_loss_fwd(1, 6, 8, 8, null, null, null, null, null) == -1
+    assert lib.vfd_smooth_loss_fwd(1, 6, 1, 8, null, null, null, null, null) == -2
+    assert lib.vfd_smooth_loss_bwd(1, 6, 8, 8, null, null, null, null, null, null, null) == -1
     assert lib.vfd_warp_stats(null, null, null, null, null, null, null) == -1
     # descriptor out of range
     d = _lib.FusionDesc()

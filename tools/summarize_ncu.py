@@ -14,7 +14,7 @@ KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
 ABI = {'voxel_fuse_fwd_kernel': 'vfd_voxel_fuse_fwd', 'voxel_fuse_bwd_kernel': 'vfd_voxel_fuse_bwd',
        'ray_sample_fwd_vec_kernel': 'vfd_ray_sample_fwd', 'ray_sample_bwd_vec_kernel': 'vfd_ray_sample_bwd',
        'warp_stats_kernel': 'vfd_warp_stats', 'warp_loss_fwd_kernel': 'vfd_warp_loss_fwd',
-       'warp_loss_bwd_kernel': 'vfd_warp_loss_bwd', 'voxel_count_kernel': 'vfd_voxel_classify',
+       'warp_loss_bwd_kernel': 'vfd_warp_loss_bwd', 'voxel_count_kernel': 'vfd_voxel_classify', 'smooth_loss_kernel': 'vfd_smooth_loss_fwd',
        'voxel_gather_fwd_kernel': 'vfd_voxel_gather_depth_fwd', 'voxel_gather_bwd_kernel': 'vfd_voxel_gather_depth_bwd'}
 UNIT = {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}
 

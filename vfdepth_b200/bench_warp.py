@@ -66,4 +66,5 @@ class WarpWorkload:
         px = self.B * 6 * self.H * self.W * 4
         imgs, depth, mask, noise = 3 * 3 * px, px, px, 2 * px
         return {'vfd_warp_stats': imgs + depth + mask, 'vfd_warp_loss_fwd': imgs + depth + mask + noise,
-                'vfd_warp_loss_bwd': imgs + depth + mask + noise + px}
+                'vfd_warp_loss_bwd': imgs + depth + mask + noise + px,
+                'vfd_smooth_loss_fwd': 3 * px + px}

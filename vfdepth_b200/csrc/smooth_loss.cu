@@ -1,0 +1,172 @@
+// Edge-aware disparity smoothness for all cameras of a rig batch in two launches per direction
+// (models/losses/single_cam_loss.py:57-65 compute_smooth_loss + loss_util.py:28-40 compute_edg_smooth_loss, scale 0):
+//   nd   = disp / (mean_HW(disp) + 1e-8)                                   per (rig, camera) image
+//   gx   = |nd[x] - nd[x+1]| * exp(-mean_c |rgb[x] - rgb[x+1]|),  gy likewise along y
+//   loss = mean(gx) + mean(gy)                                              means over the whole local batch of one camera
+// The reference spends ~25 elementwise / reduction launches per camera on it; here the image means are one reduction
+// launch and the loss one stencil launch (fp32 per thread, fp64 across threads); the backward to disp (the only
+// differentiable input) is a stencil launch that also accumulates sum_i g_i * disp_i per image for the mean's chain
+// rule, and a finishing launch.
+#include "common.cuh"
+
+namespace vfd {
+
+constexpr int kSmoothThreads = 256;
+
+struct SmoothArgs {
+    int B, cams, H, W;
+    const float* color;    // [B,cams,3,H,W]
+    const float* disp;     // [B,cams,H,W]
+    double* img_sum;       // [B*cams]   sum of disp per image
+    double* sums;          // [cams][2]  sum gx, sum gy over the batch
+    // backward
+    const float* d_smooth; // [cams]
+    double* gdot;          // [B*cams]   sum_i g_i * disp_i
+    float* d_disp;         // [B,cams,H,W]
+};
+
+__device__ __forceinline__ double block_sum(double v, double* s_red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) s_red[wid] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (threadIdx.x == 0)
+        for (int i = 0; i < kSmoothThreads / 32; ++i) t += s_red[i];
+    return t;   // valid in thread 0
+}
+
+__global__ void __launch_bounds__(kSmoothThreads) smooth_mean_kernel(const SmoothArgs a) {
+    __shared__ double s_red[kSmoothThreads / 32];
+    const int bc = blockIdx.y, HW = a.H * a.W;
+    const float* d = a.disp + (size_t)bc * HW;
+    double acc = 0.0;
+    for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads) acc += (double)__ldg(d + p);
+    const double t = block_sum(acc, s_red);
+    if (threadIdx.x == 0) atomicAdd(a.img_sum + bc, t);
+}
+
+// edge weight exp(-mean_c |rgb[p] - rgb[q]|)
+__device__ __forceinline__ float edge_weight(const float* col, int HW, int p, int q) {
+    const float d0 = fabsf(__ldg(col + p) - __ldg(col + q));
+    const float d1 = fabsf(__ldg(col + HW + p) - __ldg(col + HW + q));
+    const float d2 = fabsf(__ldg(col + 2 * HW + p) - __ldg(col + 2 * HW + q));
+    return expf(-((d0 + d1 + d2) / 3.0f));
+}
+
+__device__ __forceinline__ float image_scale(const SmoothArgs& a, int bc) {
+    const float mean = (float)(a.img_sum[bc] / (double)(a.H * a.W));
+    return mean + 1e-8f;
+}
+
+__global__ void __launch_bounds__(kSmoothThreads) smooth_loss_kernel(const SmoothArgs a) {
+    __shared__ double s_red[kSmoothThreads / 32];
+    const int bc = blockIdx.y, cam = bc % a.cams, HW = a.H * a.W, W = a.W, H = a.H;
+    const float* d = a.disp + (size_t)bc * HW;
+    const float* col = a.color + (size_t)bc * 3 * HW;
+    const float den = image_scale(a, bc);
+    float sx = 0.f, sy = 0.f;
+    for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads) {
+        const int x = p % W, y = p / W;
+        const float n0 = __ldg(d + p) / den;
+        if (x + 1 < W) sx += fabsf(n0 - __ldg(d + p + 1) / den) * edge_weight(col, HW, p, p + 1);
+        if (y + 1 < H) sy += fabsf(n0 - __ldg(d + p + W) / den) * edge_weight(col, HW, p, p + W);
+    }
+    const double tx = block_sum((double)sx, s_red);
+    const double ty = block_sum((double)sy, s_red);
+    if (threadIdx.x == 0) {
+        atomicAdd(a.sums + cam * 2 + 0, tx);
+        atomicAdd(a.sums + cam * 2 + 1, ty);
+    }
+}
+
+__device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
+
+// g_i = d loss / d nd_i (written to d_disp), and sum_i g_i * disp_i per image
+__global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const SmoothArgs a) {
+    __shared__ double s_red[kSmoothThreads / 32];
+    const int bc = blockIdx.y, cam = bc % a.cams, HW = a.H * a.W, W = a.W, H = a.H;
+    const float* d = a.disp + (size_t)bc * HW;
+    const float* col = a.color + (size_t)bc * 3 * HW;
+    float* g = a.d_disp + (size_t)bc * HW;
+    const float den = image_scale(a, bc);
+    const float up = __ldg(a.d_smooth + cam);
+    const float ux = up / (float)((double)a.B * H * (W - 1)), uy = up / (float)((double)a.B * (H - 1) * W);
+    double acc = 0.0;
+    for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads) {
+        const int x = p % W, y = p / W;
+        const float dp = __ldg(d + p), n0 = dp / den;
+        float gi = 0.f;
+        if (x + 1 < W) gi += ux * sgn(n0 - __ldg(d + p + 1) / den) * edge_weight(col, HW, p, p + 1);
+        if (x > 0) gi -= ux * sgn(__ldg(d + p - 1) / den - n0) * edge_weight(col, HW, p - 1, p);
+        if (y + 1 < H) gi += uy * sgn(n0 - __ldg(d + p + W) / den) * edge_weight(col, HW, p, p + W);
+        if (y > 0) gi -= uy * sgn(__ldg(d + p - W) / den - n0) * edge_weight(col, HW, p - W, p);
+        g[p] = gi;
+        acc += (double)gi * (double)dp;
+    }
+    const double t = block_sum(acc, s_red);
+    if (threadIdx.x == 0) atomicAdd(a.gdot + bc, t);
+}
+
+// d_disp_j = g_j / den - (sum_i g_i disp_i) / (den^2 * HW)      (nd = disp / den, den = mean + 1e-8)
+__global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_finish_kernel(const SmoothArgs a) {
+    const int bc = blockIdx.y, HW = a.H * a.W;
+    float* g = a.d_disp + (size_t)bc * HW;
+    const float den = image_scale(a, bc);
+    const float shift = (float)(a.gdot[bc] / ((double)den * (double)den * (double)HW));
+    for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads)
+        g[p] = g[p] / den - shift;
+}
+
+static int check_smooth(int B, int cams, int H, int W) {
+    if (B < 1 || cams < 1 || H < 2 || W < 2) return VFD_ERR_DESC;
+    if ((long)H * W >= (1L << 30)) return VFD_ERR_DESC;
+    return VFD_OK;
+}
+
+static dim3 smooth_grid(int B, int cams, int H, int W) {
+    int bx = (H * W + kSmoothThreads * 4 - 1) / (kSmoothThreads * 4);
+    if (bx > 256) bx = 256;
+    return dim3(bx, B * cams);
+}
+
+}  // namespace vfd
+
+using namespace vfd;
+
+extern "C" int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* color, const float* disp,
+                                   double* img_sum, double* sums, void* stream) {
+    int rc = check_smooth(B, cams, H, W);
+    if (rc) return rc;
+    if (!color || !disp || !img_sum || !sums) return VFD_ERR_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(img_sum, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
+    if (cudaMemsetAsync(sums, 0, sizeof(double) * cams * 2, st) != cudaSuccess) return VFD_ERR_CUDA;
+    SmoothArgs a = {};
+    a.B = B; a.cams = cams; a.H = H; a.W = W; a.color = color; a.disp = disp; a.img_sum = img_sum; a.sums = sums;
+    const dim3 grid = smooth_grid(B, cams, H, W);
+    smooth_mean_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    smooth_loss_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+extern "C" int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* color, const float* disp,
+                                   const double* img_sum, const float* d_smooth, double* gdot, float* d_disp,
+                                   void* stream) {
+    int rc = check_smooth(B, cams, H, W);
+    if (rc) return rc;
+    if (!color || !disp || !img_sum || !d_smooth || !gdot || !d_disp) return VFD_ERR_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(gdot, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
+    SmoothArgs a = {};
+    a.B = B; a.cams = cams; a.H = H; a.W = W; a.color = color; a.disp = disp;
+    a.img_sum = const_cast<double*>(img_sum); a.d_smooth = d_smooth; a.gdot = gdot; a.d_disp = d_disp;
+    const dim3 grid = smooth_grid(B, cams, H, W);
+    smooth_bwd_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    smooth_bwd_finish_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}

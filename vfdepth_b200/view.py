@@ -179,15 +179,38 @@ def camera_transforms(wi, target_view, rel_pose_dict, cam):
     return torch.stack(cols, 1).unsqueeze(1).float()
 
 
+class _SmoothLoss(torch.autograd.Function):
+    """vfd_smooth_loss_fwd / _bwd: edge-aware smoothness of every camera of the batch, gradient to disp."""
+
+    @staticmethod
+    def forward(ctx, color, disp):
+        B, n, _, H, W = color.shape
+        _chk(color, 'color', (B, n, 3, H, W))
+        _chk(disp, 'disp', (B, n, H, W))
+        dev = color.device
+        img_sum = torch.empty((B * n,), device=dev, dtype=torch.float64)
+        sums = torch.empty((n, 2), device=dev, dtype=torch.float64)
+        _lib.call('vfd_smooth_loss_fwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum), _lib.ptr(sums),
+                  _stream())
+        ctx.save_for_backward(color, disp, img_sum)
+        out = sums[:, 0] / float(B * H * (W - 1)) + sums[:, 1] / float(B * (H - 1) * W)
+        return out.float()
+
+    @staticmethod
+    def backward(ctx, d_smooth):
+        color, disp, img_sum = ctx.saved_tensors
+        B, n, _, H, W = color.shape
+        gdot = torch.empty((B * n,), device=color.device, dtype=torch.float64)
+        d_disp = torch.empty_like(disp)
+        _lib.call('vfd_smooth_loss_bwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum),
+                  _lib.ptr(d_smooth.float().contiguous()), _lib.ptr(gdot), _lib.ptr(d_disp), _stream())
+        return None, d_disp
+
+
 def smooth_loss(color, disp):
-    """single_cam_loss.py:57-65 + loss_util.py:28-40 (weight 0.001; stays torch)."""
-    mean_disp = disp.mean(2, True).mean(3, True)
-    nd = disp / (mean_disp + 1e-8)
-    grx = (color[:, :, :, :-1] - color[:, :, :, 1:]).abs().mean(1, True)
-    gry = (color[:, :, :-1, :] - color[:, :, 1:, :]).abs().mean(1, True)
-    gdx = (nd[:, :, :, :-1] - nd[:, :, :, 1:]).abs() * (-1.0 * grx).exp()
-    gdy = (nd[:, :, :-1, :] - nd[:, :, 1:, :]).abs() * (-1.0 * gry).exp()
-    return gdx.mean() + gdy.mean()
+    """single_cam_loss.py:57-65 + loss_util.py:28-40 for all cameras at once.
+    color [B,cams,3,H,W], disp [B,cams,H,W] -> per-camera loss [cams]."""
+    return _SmoothLoss.apply(color.contiguous(), disp.contiguous())
 
 
 def combine_losses(cfg, num, den, smooth):
@@ -210,7 +233,7 @@ def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises, want_views=()):
     T = rig_transforms(wi, inputs, cam_T_cam)
     num, den, views = warp_loss_sums(wi, depth, T, noise, 0, None, want_views)
     color0 = inputs[('color', 0, 0)]
-    sm = torch.stack([smooth_loss(color0[:, c], disps[c]) for c in range(wi.num_cams)])
+    sm = smooth_loss(color0, torch.cat(disps, 1))
     cam_loss, terms = combine_losses(cfg, num, den, sm)
     return cam_loss.sum() / wi.num_cams, dict(terms=terms, cam_loss=cam_loss, smooth=sm, views=views, T=T)
 
@@ -292,7 +315,7 @@ class MultiCamLoss(torch.nn.Module):
         num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['stats'], ('reproj_loss', 'reproj_mask'))
         tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
         tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
-        sm = smooth_loss(inputs[('color', 0, 0)][:, cam], tv[('disp', 0)])
+        sm = smooth_loss(inputs[('color', 0, 0)][:, cam:cam + 1], tv[('disp', 0)])[0]
         cam_loss, terms = combine_losses(self.cfg, num, den, sm.reshape(1))
         t = terms[0].detach().cpu()
         loss_dict = {'reproj_loss': float(t[0]), 'spatio_loss': float(t[1]), 'spatio_tempo_loss': float(t[2]),
