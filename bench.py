@@ -186,12 +186,13 @@ class FusionWorkload:
         m1 = int((cnt == 1).sum()) if cnt is not None else B * g.N
         m2 = int((cnt == 2).sum()) if cnt is not None else B * g.N
         rows = (m1 + 2 * m2) * (g.C + 1) * 4
-        classify = msk + B * g.N * (1 + 4) + (m1 + m2) * 8
+        table = (m1 + 2 * m2) * 40          # corner table: 40 bytes per (voxel, camera) entry, written once, read per pass
+        classify = msk + B * g.N * (1 + 4) + (m1 + m2) * 8 + table + m1 * 8
         return {'vfd_voxel_gather_depth_compact_fwd': feats + msk + rows,
                 'vfd_voxel_gather_depth_compact_bwd': feats + msk + rows, 'vfd_voxel_classify': classify,
                 # fused gather + MLPs: the rows never reach HBM.  fwd: features in, volume out;
                 # bwd: features + volume + its gradient in, feature gradient out
-                'vfd_voxel_fuse_fwd': feats + msk + vol, 'vfd_voxel_fuse_bwd': 2 * feats + msk + 2 * vol,
+                'vfd_voxel_fuse_fwd': feats + table + vol, 'vfd_voxel_fuse_bwd': 2 * feats + table + 2 * vol,
                 'vfd_ray_sample_fwd': vol + ray, 'vfd_ray_sample_bwd': vol + ray}
 
 

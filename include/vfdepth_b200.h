@@ -94,11 +94,15 @@ int vfd_voxel_gather_depth_bwd(const vfd_fusion_desc* d, const float* mask_small
  *   idx_no  [>= B*N] i64  out: idx_no[r] = b*N+n of compact x_no row r  (first totals[0] entries are written)
  *   idx_ov  [>= B*N] i64  same for x_ov (first totals[1] entries)
  *   totals  [2] i32       device: number of count-1 and count-2 voxels; the caller reads it back to size the MLP GEMMs
+ *   table   (optional)    vfd_voxel_table_bytes(d) bytes, 16-byte aligned: for every listed voxel the bilinear corner
+ *                         offsets / weights, camera and relative depth of the one or two cameras that see it, so that
+ *                         vfd_voxel_fuse_fwd / _bwd do not project again; NULL = not written
  *   ws                    scratch of vfd_voxel_classify_workspace_bytes(d) bytes, 8-byte aligned */
 size_t vfd_voxel_classify_workspace_bytes(const vfd_fusion_desc* d);
+size_t vfd_voxel_table_bytes(const vfd_fusion_desc* d);
 int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_small, const float* K, const float* Einv,
-                       uint8_t* count, int32_t* slot, int64_t* idx_no, int64_t* idx_ov, int32_t* totals, void* ws,
-                       size_t ws_bytes, void* stream);
+                       uint8_t* count, int32_t* slot, int64_t* idx_no, int64_t* idx_ov, int32_t* totals, void* table,
+                       void* ws, size_t ws_bytes, void* stream);
 
 /* vfd_voxel_gather_depth_fwd / _bwd on compact rows: x_no [totals[0], ld_no] and x_ov [totals[1], ld_ov] hold one
  * row per voxel that reaches the corresponding MLP (row = slot[b,n]); voxels with slot < 0 are skipped entirely. */
@@ -111,7 +115,7 @@ int vfd_voxel_gather_depth_compact_bwd(const vfd_fusion_desc* d, const float* ma
 
 /* Fused gather + both 1x1 MLPs: VFNet.backproject_into_voxel, model='depth', :116-159 INCLUDING
  * preprocess_non_overlap (:197-207) and preprocess_overlap (:209-230).  The GEMM rows never reach HBM.
- *   idx_no/idx_ov/totals  from vfd_voxel_classify (totals stay on the device: no host round trip)
+ *   idx_no/idx_ov/totals/table  from vfd_voxel_classify (totals stay on the device: no host round trip)
  *   w_no [Cv][C+1], b_no [Cv]       conv_non_overlap.0.{weight,bias}   (Conv1d weight with the k=1 axis squeezed)
  *   w_ov [Cv][2(C+1)], b_ov [Cv]    conv_overlap.0.{weight,bias}
  *   vol  [B,N,Cv]                   channel-last voxel volume (voxel_feat of :158 transposed); zero-filled here, rows
@@ -119,8 +123,8 @@ int vfd_voxel_gather_depth_compact_bwd(const vfd_fusion_desc* d, const float* ma
  * Cv even, <= 64.  The products run as error-compensated 3xTF32 on the tensor cores (fp32-level accuracy). */
 int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small, const float* K,
                        const float* Einv, const int64_t* idx_no, const int64_t* idx_ov, const int32_t* totals,
-                       const float* w_no, const float* b_no, const float* w_ov, const float* b_ov, float* vol,
-                       void* stream);
+                       const void* table, const float* w_no, const float* b_no, const float* w_ov, const float* b_ov,
+                       float* vol, void* stream);
 
 /* Backward of vfd_voxel_fuse_fwd w.r.t. the feature maps and the four MLP parameters.
  *   vol    [B,N,Cv]  the forward output (the sign of the pre-activation is read from it)
@@ -131,7 +135,8 @@ int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, const float
 size_t vfd_voxel_fuse_bwd_workspace_bytes(const vfd_fusion_desc* d);
 int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small, const float* K,
                        const float* Einv, const int64_t* idx_no, const int64_t* idx_ov, const int32_t* totals,
-                       const float* w_no, const float* w_ov, const float* vol, const float* d_vol, float* d_feats,
+                       const void* table, const float* w_no, const float* w_ov, const float* vol, const float* d_vol,
+                       float* d_feats,
                        float* d_w_no, float* d_b_no, float* d_w_ov, float* d_b_ov, void* ws, size_t ws_bytes,
                        void* stream);
 

@@ -68,12 +68,13 @@ def test_bad_arguments_are_rejected_before_any_launch():
     # NULL descriptor
     assert lib.vfd_voxel_gather_depth_fwd(null, null, null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_ray_sample_fwd(null, null, null, null, null, null, null) == -1
-    assert lib.vfd_voxel_classify(null, null, null, null, null, null, null, null, null, null, ctypes.c_size_t(0), null) == -1
+    assert lib.vfd_voxel_classify(null, null, null, null, null, null, null, null, null, null, null, ctypes.c_size_t(0), null) == -1
     assert lib.vfd_voxel_gather_depth_compact_fwd(null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_gather_depth_compact_bwd(null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_classify_workspace_bytes(null) == 0
-    assert lib.vfd_voxel_fuse_fwd(*([null] * 14)) == -1
-    assert lib.vfd_voxel_fuse_bwd(*([null] * 18), ctypes.c_size_t(0), null) == -1
+    assert lib.vfd_voxel_fuse_fwd(*([null] * 15)) == -1
+    assert lib.vfd_voxel_fuse_bwd(*([null] * 19), ctypes.c_size_t(0), null) == -1
+    assert lib.vfd_voxel_table_bytes(null) == 0
     assert lib.vfd_voxel_fuse_bwd_workspace_bytes(null) == 0
     assert lib.vfd_smooth_loss_fwd(1, 6, 8, 8, null, null, null, null, null) == -1
     assert lib.vfd_smooth_loss_fwd(1, 6, 1, 8, null, null, null, null, null) == -2

@@ -319,3 +319,42 @@ def test_fused_mlp_matches_fp32_gemm_path(dataset, B, C, Cv):
     ref = torch.autograd.grad((y.permute(0, 2, 1) * up).sum(), [f] + params)
     for n, a, b in zip(['d_feats', 'd_w_no', 'd_b_no', 'd_w_ov', 'd_b_ov'], res['fused'][1:], ref):
         assert H.rel_err(a, b) < TOL, (n, H.rel_err(a, b))
+
+
+@pytest.mark.parametrize('keep', [0, 1, 6])
+def test_fused_mlp_degenerate_lists(keep):
+    """edge cases of the compact lists: no camera sees anything (both lists empty), a single camera (no count-2
+    voxels), and a ragged last tile (list lengths not multiples of 32/64): the fused path still equals the fp32 GEMM
+    path and voxels outside the lists stay exactly zero."""
+    dev = _dev()
+    cfg = vcfg.default_config('ddad', batch_size=2, model__voxel_size=[23, 17, 5], model__voxel_str_p=[-23.0, -17.0, -3.0],
+                              model__voxel_unit_size=[2.0, 2.0, 1.5], model__fusion_feat_in_dim=24,
+                              model__voxel_pre_dim=[16], training__height=96, training__width=160)
+    inputs, extras = make_rig(cfg, seed=77, with_images=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, 24, 16, 'depth', None, dev)
+    to = lambda t: t.to(dev)
+    mask = inputs['mask'].clone()
+    mask[:, keep:] = 0                       # cameras >= keep see nothing
+    args = (to(mask), to(inputs[('K', lvl)]), to(inputs['extrinsics_inv']))
+    params = [net.conv_non_overlap[0].weight, net.conv_non_overlap[0].bias,
+              net.conv_overlap[0].weight, net.conv_overlap[0].bias]
+    res = {}
+    for fused in (True, False):
+        net.fused_mlp = fused
+        f = to(extras['feats_agg']).requires_grad_(True)
+        vox = net.backproject_into_voxel(f, *args)
+        grads = torch.autograd.grad(vox.square().sum(), [f] + params, allow_unused=True)
+        res[fused] = [vox.detach()] + [torch.zeros_like(p) if g is None else g for g, p in zip(grads, [f] + params)]
+    cnt = net.last_count
+    if keep == 0:
+        assert int(cnt.max()) == 0 and float(res[True][0].abs().max()) == 0.0
+    if keep == 1:
+        assert int(cnt.max()) == 1
+    for a, b in zip(res[True], res[False]):
+        scale = float(b.abs().max())
+        assert float((a - b).abs().max()) <= TOL * max(scale, 1e-30) + (0.0 if scale > 0 else 0.0)
+    vol = res[True][0].permute(0, 2, 1)
+    outside = (cnt != 1) & (cnt != 2)
+    if bool(outside.any()):
+        assert float(vol[outside].abs().max()) == 0.0

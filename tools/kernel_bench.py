@@ -82,7 +82,7 @@ def main():
                     vol.numel() * 4 + out.numel() * 4),
     }
     # compact lists + fused gather/MLP kernels
-    cnt8, slot, idx_no, idx_ov, totals = ops.voxel_classify(mask_small, K, Einv, g, sizes=False)
+    cnt8, slot, idx_no, idx_ov, totals, table = ops.voxel_classify(mask_small, K, Einv, g, sizes=False, table=True)
     m1, m2 = totals.tolist()
     w_no, b_no = torch.randn(g.Cv, c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
     w_ov, b_ov = torch.randn(g.Cv, 2 * c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
@@ -101,10 +101,10 @@ def main():
         'compact_bwd': (lambda: _lib.call('vfd_voxel_gather_depth_compact_bwd', ctypes.byref(d), p(mask_small), p(K),
                                           p(Einv), p(slot), p(cx_no), p(cx_ov), p(d_feats), st), feat_b + rows_b),
         'fuse_fwd': (lambda: _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), p(feats), p(mask_small), p(K), p(Einv),
-                                       p(idx_no), p(idx_ov), p(totals), p(w_no), p(b_no), p(w_ov), p(b_ov), p(fvol), st),
+                                       p(idx_no), p(idx_ov), p(totals), p(table), p(w_no), p(b_no), p(w_ov), p(b_ov), p(fvol), st),
                      feat_b + vol_b),
         'fuse_bwd': (lambda: _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), p(feats), p(mask_small), p(K), p(Einv),
-                                       p(idx_no), p(idx_ov), p(totals), p(w_no), p(w_ov), p(fvol), p(gvol), p(d_feats),
+                                       p(idx_no), p(idx_ov), p(totals), p(table), p(w_no), p(w_ov), p(fvol), p(gvol), p(d_feats),
                                        p(dw_no), p(db_no), p(dw_ov), p(db_ov), p(ws), ctypes.c_size_t(nws), st),
                      2 * feat_b + 2 * vol_b),
     })

@@ -75,6 +75,7 @@ def load():
         lib.vfd_warp_bwd_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_classify_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_fuse_bwd_workspace_bytes.restype = ctypes.c_size_t
+        lib.vfd_voxel_table_bytes.restype = ctypes.c_size_t
         _lib = lib
     return _lib
 

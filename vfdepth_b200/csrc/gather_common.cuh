@@ -56,6 +56,24 @@ __device__ __forceinline__ Corners make_corners(const CamSlot& s, int w, int h, 
     return q;
 }
 
+// Per-voxel corner table written by vfd_voxel_classify for the voxels that reach an MLP (camera count 1 or 2): up to two
+// entries per voxel row (b*N+n), in camera order, each = the four bilinear corner offsets (floats inside the camera's
+// feature map), the four corner weights and {b*num_cams + c, bits of v.z / depth_div}; meta.x = -1 marks an unused
+// entry.  The fused gather + MLP kernels read it instead of re-projecting in every pass.
+struct CornerTable {
+    int4* off;     // [2][rows]
+    float4* wgt;   // [2][rows]
+    int2* meta;    // [2][rows]
+};
+__host__ __device__ inline size_t corner_table_bytes(size_t rows) { return rows * 2 * (16 + 16 + 8); }
+__host__ __device__ inline CornerTable carve_table(void* p, size_t rows) {
+    CornerTable t;
+    t.off = reinterpret_cast<int4*>(p);
+    t.wgt = reinterpret_cast<float4*>(t.off + 2 * rows);
+    t.meta = reinterpret_cast<int2*>(t.wgt + 2 * rows);
+    return t;
+}
+
 // ---- legacy-path tensor-core helpers (mma.sync m16n8k8 tf32, fp32 accumulate) for the fused 1x1 MLPs ----
 // x = hi + lo (+ a remainder below 2^-20 |x|) with hi, lo both exactly representable in TF32 (13 low mantissa bits
 // zero): three products hi*hi + hi*lo + lo*hi recover fp32-level accuracy ("3xTF32").  Truncation instead of

@@ -49,6 +49,7 @@ struct FuseArgs {
     const float* d_vol;  // [B*N][Cv]
     float* d_feats;      // [B,cams,h,w,C]
     float* partial;      // [gridDim.x][3][Cv*(C+2)] per-CTA weight-gradient partial sums
+    const void* table;   // corner table of vfd_voxel_classify (gather_common.cuh), B*N rows
     int KP;              // round_up(C+1, 8)
     int NT;              // ceil(Cv / 8)
 };
@@ -92,50 +93,63 @@ __device__ __forceinline__ TileMeta carve_meta(unsigned char* base) {
     return m;
 }
 
-// All ROWS*8 threads of the group: thread (camera c = tid / ROWS, row r = tid % ROWS) projects list entry base+r into
-// camera c; the valid cameras in `want` become the row's entries in camera order.  Contains one group barrier; the
-// caller adds another before the entries are read.
+// One thread's share of a tile's metadata, loaded from the corner table of vfd_voxel_classify one tile ahead of its
+// use (the index -> table chain of two dependent global loads is hidden behind the previous tile's work).
+// Thread (part = tid / ROWS, row r = tid % ROWS): parts 0..3 carry the corner offsets / weights of entry 0 / 1, part 4
+// the two meta words, the row id and the entry count; parts 5..7 idle.
+struct TilePf {
+    long long row;
+    int2 m0, m1;
+    uint4 piece;
+};
+
+__device__ __forceinline__ bool entry_wanted(int2 m, unsigned want, int num_cams) {
+    return m.x >= 0 && ((want >> (m.x % num_cams)) & 1u);
+}
+
 template <int ROWS>
-__device__ __forceinline__ void project_tile(const FuseArgs& a, const TileMeta& tm, const Group& G, const int64_t* idx,
-                                             int base, int M, unsigned want) {
-    const vfd_fusion_desc& d = a.d;
-    const int r = G.tid & (ROWS - 1), c = G.tid / ROWS;
-    const long N = (long)d.X * d.Y * d.Z;
-    const long long row = (base + r < M) ? idx[base + r] : -1;
-    bool ok = false;
-    Corners q;
-    int bc = 0;
-    float zrel = 0.f;
-    if (row >= 0 && c < d.num_cams && ((want >> c) & 1u)) {
-        const int b = (int)(row / N);
-        const long n = row - (long)b * N;
-        const int xi = (int)(n % d.X), yi = (int)((n / d.X) % d.Y), zi = (int)(n / ((long)d.X * d.Y));
-        const float x = __ldg(d.axis_x + xi), y = __ldg(d.axis_y + yi), z = __ldg(d.axis_z + zi);
-        bc = b * d.num_cams + c;
-        float g[2];
-        CamSlot cs;
-        ok = project_cam(d, a.mask_small + (size_t)bc * d.h * d.w, a.Einv + (size_t)bc * 16, a.K + (size_t)bc * 16, x, y,
-                         z, cs, g);
-        q = make_corners(cs, d.w, d.h, d.C);
-        zrel = cs.zrel;
+__device__ __forceinline__ TilePf prefetch_tile(const FuseArgs& a, const CornerTable& tb, size_t rows_total,
+                                                const Group& G, const int64_t* idx, int base, int M, unsigned want,
+                                                bool tile_ok) {
+    TilePf p;
+    p.row = -1;
+    p.m0 = p.m1 = make_int2(-1, 0);
+    p.piece = make_uint4(0u, 0u, 0u, 0u);
+    const int r = G.tid & (ROWS - 1), part = G.tid / ROWS;
+    if (tile_ok && part < 5 && base + r < M) {
+        p.row = idx[base + r];
+        p.m0 = __ldg(tb.meta + p.row);
+        p.m1 = __ldg(tb.meta + rows_total + p.row);
+        if (part < 4) {
+            const int e = part >> 1;
+            if (entry_wanted(e ? p.m1 : p.m0, want, a.d.num_cams)) {
+                const uint4* src = (part & 1) ? reinterpret_cast<const uint4*>(tb.wgt) : reinterpret_cast<const uint4*>(tb.off);
+                p.piece = __ldg(src + e * rows_total + p.row);
+            }
+        }
     }
-    tm.ok[c * ROWS + r] = ok ? 1 : 0;
-    group_sync(G);
-    int before = 0, total = 0;
-#pragma unroll
-    for (int cc = 0; cc < VFD_MAX_CAMS; ++cc) {
-        const int f = tm.ok[cc * ROWS + r];
-        total += f;
-        before += (cc < c) ? f : 0;
-    }
-    if (ok && before < kMaxEnt) {
-        tm.off[before * ROWS + r] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
-        tm.wgt[before * ROWS + r] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
-        tm.meta[before * ROWS + r] = make_int2(bc, __float_as_int(zrel));
-    }
-    if (c == 0) {
-        tm.row[r] = row;
-        tm.cnt[r] = min(total, kMaxEnt);
+    return p;
+}
+
+// write the prefetched share into the tile metadata: the wanted entries of a row, in camera order.  The caller
+// synchronises the group before the metadata is read.
+template <int ROWS>
+__device__ __forceinline__ void commit_tile(const TileMeta& tm, const Group& G, const TilePf& p, unsigned want,
+                                            int num_cams) {
+    const int r = G.tid & (ROWS - 1), part = G.tid / ROWS;
+    const bool w0 = entry_wanted(p.m0, want, num_cams), w1 = entry_wanted(p.m1, want, num_cams);
+    if (part < 4) {
+        const int e = part >> 1;
+        const int dest = e ? (w0 ? 1 : 0) : 0;
+        if (e ? w1 : w0) {
+            uint4* dst = (part & 1) ? reinterpret_cast<uint4*>(tm.wgt) : reinterpret_cast<uint4*>(tm.off);
+            dst[dest * ROWS + r] = p.piece;
+        }
+    } else if (part == 4) {
+        if (w0) tm.meta[r] = p.m0;
+        if (w1) tm.meta[(w0 ? 1 : 0) * ROWS + r] = p.m1;
+        tm.row[r] = p.row;
+        tm.cnt[r] = (w0 ? 1 : 0) + (w1 ? 1 : 0);
     }
 }
 
@@ -242,6 +256,8 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
     for (int c = 0; c < d.num_cams; ++c) gmask[d.group[c] ? 1 : 0] |= 1u << c;
     const int nk = KP / 8, kq = (nk + 3) / 4;
     const int ks0 = wk * kq, ks1 = min(nk, ks0 + kq);
+    const size_t rows_total = (size_t)d.B * d.X * d.Y * d.Z;
+    const CornerTable tb = carve_table(const_cast<void*>(a.table), rows_total);
 
     for (int pass = 0; pass < 3; ++pass) {
         const int M = pass ? M2 : M1, T = pass ? T2 : T1;
@@ -263,8 +279,12 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
             }
         }
         __syncthreads();
-        for (int tile = blockIdx.x * kFwdGroups + grp; tile < T; tile += gridDim.x * kFwdGroups) {
-            project_tile<kFwdRows>(a, tm, G, idx, tile * kFwdRows, M, want);
+        const int tstep = gridDim.x * kFwdGroups;
+        int tile = blockIdx.x * kFwdGroups + grp;
+        TilePf pf = prefetch_tile<kFwdRows>(a, tb, rows_total, G, idx, tile * kFwdRows, M, want, tile < T);
+        for (; tile < T; tile += tstep) {
+            commit_tile<kFwdRows>(tm, G, pf, want, d.num_cams);
+            pf = prefetch_tile<kFwdRows>(a, tb, rows_total, G, idx, (tile + tstep) * kFwdRows, M, want, tile + tstep < T);
             group_sync(G);
 #pragma unroll
             for (int rr = 0; rr < 4; rr += 2)
@@ -390,6 +410,8 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
     const int NAW = (NA + 3) / 4;          // ... per warp column group (<= 8)
     const size_t pstride = (size_t)Cv * (C1 + 1);     // one (CTA, pass) partial: [Cv][C1] weights then [Cv] bias
     const size_t map = (size_t)d.h * d.w * C;
+    const size_t rows_total = (size_t)d.B * d.X * d.Y * d.Z;
+    const CornerTable tb = carve_table(const_cast<void*>(a.table), rows_total);
 
     for (int pass = 0; pass < 3; ++pass) {
         const int M = pass ? M2 : M1, T = pass ? T2 : T1;
@@ -411,8 +433,12 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
             for (int i = 0; i < 4; ++i) accw[j][i] = 0.f;
         float db = 0.f, dwz = 0.f;           // threads o < Cv: bias gradient and the relative-depth column of dW
 
-        for (int tile = blockIdx.x; tile < T; tile += gridDim.x) {
-            project_tile<kFuseRows>(a, tm, G, idx, tile * kFuseRows, M, want);
+        int tile = blockIdx.x;
+        TilePf pf = prefetch_tile<kFuseRows>(a, tb, rows_total, G, idx, tile * kFuseRows, M, want, tile < T);
+        for (; tile < T; tile += gridDim.x) {
+            commit_tile<kFuseRows>(tm, G, pf, want, d.num_cams);
+            pf = prefetch_tile<kFuseRows>(a, tb, rows_total, G, idx, (tile + (int)gridDim.x) * kFuseRows, M, want,
+                                          tile + (int)gridDim.x < T);
             __syncthreads();
             // dZ tile, split once
             for (int i = threadIdx.x; i < kFuseRows * (kZS / 4); i += blockDim.x) {
@@ -633,18 +659,18 @@ using namespace vfd;
 
 extern "C" int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
                                   const float* K, const float* Einv, const int64_t* idx_no, const int64_t* idx_ov,
-                                  const int32_t* totals, const float* w_no, const float* b_no, const float* w_ov,
-                                  const float* b_ov, float* vol, void* stream) {
+                                  const int32_t* totals, const void* table, const float* w_no, const float* b_no,
+                                  const float* w_ov, const float* b_ov, float* vol, void* stream) {
     int rc = check_fuse(d);
     if (rc) return rc;
-    if (!feats || !mask_small || !K || !Einv || !idx_no || !idx_ov || !totals || !w_no || !b_no || !w_ov || !b_ov ||
-        !vol)
+    if (!feats || !mask_small || !K || !Einv || !idx_no || !idx_ov || !totals || !table || !w_no || !b_no || !w_ov ||
+        !b_ov || !vol)
         return VFD_ERR_NULL;
     if ((reinterpret_cast<uintptr_t>(feats) & 15) || (reinterpret_cast<uintptr_t>(vol) & 15)) return VFD_ERR_ALIGN;
     FuseArgs a = {};
     a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv;
     a.idx_no = idx_no; a.idx_ov = idx_ov; a.totals = totals;
-    a.w_no = w_no; a.b_no = b_no; a.w_ov = w_ov; a.b_ov = b_ov; a.vol = vol;
+    a.w_no = w_no; a.b_no = b_no; a.w_ov = w_ov; a.b_ov = b_ov; a.vol = vol; a.table = table;
     a.KP = (d->C + 1 + 7) / 8 * 8;
     a.NT = (d->Cv + 7) / 8;
     cudaStream_t st = (cudaStream_t)stream;
@@ -668,12 +694,12 @@ extern "C" size_t vfd_voxel_fuse_bwd_workspace_bytes(const vfd_fusion_desc* d) {
 
 extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
                                   const float* K, const float* Einv, const int64_t* idx_no, const int64_t* idx_ov,
-                                  const int32_t* totals, const float* w_no, const float* w_ov, const float* vol,
-                                  const float* d_vol, float* d_feats, float* d_w_no, float* d_b_no, float* d_w_ov,
+                                  const int32_t* totals, const void* table, const float* w_no, const float* w_ov,
+                                  const float* vol, const float* d_vol, float* d_feats, float* d_w_no, float* d_b_no, float* d_w_ov,
                                   float* d_b_ov, void* ws, size_t ws_bytes, void* stream) {
     int rc = check_fuse(d);
     if (rc) return rc;
-    if (!feats || !mask_small || !K || !Einv || !idx_no || !idx_ov || !totals || !w_no || !w_ov || !vol || !d_vol ||
+    if (!feats || !mask_small || !K || !Einv || !idx_no || !idx_ov || !totals || !table || !w_no || !w_ov || !vol || !d_vol ||
         !d_feats || !d_w_no || !d_b_no || !d_w_ov || !d_b_ov || !ws)
         return VFD_ERR_NULL;
     if ((reinterpret_cast<uintptr_t>(feats) & 15) || (reinterpret_cast<uintptr_t>(d_feats) & 15) ||
@@ -685,7 +711,7 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
     if (ws_bytes < (size_t)sms * 3 * d->Cv * (d->C + 2) * sizeof(float)) return VFD_ERR_WORKSPACE;
     FuseArgs a = {};
     a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv;
-    a.idx_no = idx_no; a.idx_ov = idx_ov; a.totals = totals; a.w_no = w_no; a.w_ov = w_ov;
+    a.idx_no = idx_no; a.idx_ov = idx_ov; a.totals = totals; a.w_no = w_no; a.w_ov = w_ov; a.table = table;
     a.vol = const_cast<float*>(vol); a.d_vol = d_vol; a.d_feats = d_feats; a.partial = static_cast<float*>(ws);
     a.KP = (d->C + 1 + 7) / 8 * 8;
     a.NT = (d->Cv + 7) / 8;

@@ -260,6 +260,7 @@ struct ClassifyArgs {
     int64_t* idx_ov;
     int32_t* totals;
     int2* block_tot;   // [B * blocks_per_rig]
+    void* table;       // optional corner table (gather_common.cuh), B*N rows
 };
 
 __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_count_kernel(const ClassifyArgs c) {
@@ -277,17 +278,36 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_count_kernel(con
     if (n < N) {
         const int xi = (int)(n % d.X), yi = (int)((n / d.X) % d.Y), zi = (int)(n / ((long)d.X * d.Y));
         const float x = __ldg(d.axis_x + xi), y = __ldg(d.axis_y + yi), z = __ldg(d.axis_z + zi);
+        CamSlot ent[2];
+        int ecam[2] = {-1, -1};
         for (int cam = 0; cam < d.num_cams; ++cam) {
             const float* Einv = s_mat + cam * 32;
-            float v[3], g[2];
-            vfd_voxel_to_pixel(Einv, Einv + 16, x, y, z, d.w, d.h, v, g);
-            if (vfd_in_bounds2(g[0], g[1]) && v[2] > 0.f) {
-                const float fx = rintf(vfd_unnormalize(g[0], d.w)), fy = rintf(vfd_unnormalize(g[1], d.h));
-                if (fx >= 0.f && fx <= (float)(d.w - 1) && fy >= 0.f && fy <= (float)(d.h - 1))
-                    cnt += __ldg(c.mask_small + ((size_t)(b * d.num_cams + cam) * d.h + (int)fy) * d.w + (int)fx) > 0.5f;
+            float g[2];
+            CamSlot cs;
+            if (project_cam(d, c.mask_small + (size_t)(b * d.num_cams + cam) * d.h * d.w, Einv, Einv + 16, x, y, z, cs,
+                            g)) {
+                if (cnt == 0) { ent[0] = cs; ecam[0] = cam; }
+                if (cnt == 1) { ent[1] = cs; ecam[1] = cam; }
+                ++cnt;
             }
         }
-        c.count[(size_t)b * N + n] = (uint8_t)cnt;
+        const size_t row = (size_t)b * N + n;
+        c.count[row] = (uint8_t)cnt;
+        if (c.table && (cnt == 1 || cnt == 2)) {
+            const size_t rows = (size_t)d.B * N;
+            const CornerTable t = carve_table(c.table, rows);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                if (e < cnt) {
+                    const Corners q = make_corners(ent[e], d.w, d.h, d.C);
+                    t.off[e * rows + row] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
+                    t.wgt[e * rows + row] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
+                    t.meta[e * rows + row] = make_int2(b * d.num_cams + ecam[e], __float_as_int(ent[e].zrel));
+                } else {
+                    t.meta[e * rows + row] = make_int2(-1, 0);
+                }
+            }
+        }
     }
     const unsigned b1 = __ballot_sync(0xffffffffu, cnt == 1), b2 = __ballot_sync(0xffffffffu, cnt == 2);
     if (lane == 0) { s_n1[warp] = __popc(b1); s_n2[warp] = __popc(b2); }
@@ -474,9 +494,15 @@ extern "C" size_t vfd_voxel_classify_workspace_bytes(const vfd_fusion_desc* d) {
     return (size_t)d->B * blocks * sizeof(int2);
 }
 
+extern "C" size_t vfd_voxel_table_bytes(const vfd_fusion_desc* d) {
+    if (!d || d->B < 1) return 0;
+    return corner_table_bytes((size_t)d->B * d->X * d->Y * d->Z);
+}
+
 extern "C" int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_small, const float* K,
                                   const float* Einv, uint8_t* count, int32_t* slot, int64_t* idx_no,
-                                  int64_t* idx_ov, int32_t* totals, void* ws, size_t ws_bytes, void* stream) {
+                                  int64_t* idx_ov, int32_t* totals, void* table, void* ws, size_t ws_bytes,
+                                  void* stream) {
     int rc = check_desc(d);
     if (rc) return rc;
     if (!mask_small || !K || !Einv || !count || !slot || !idx_no || !idx_ov || !totals || !ws) return VFD_ERR_NULL;
@@ -487,6 +513,8 @@ extern "C" int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_sm
     ClassifyArgs c = {};
     c.d = *d; c.mask_small = mask_small; c.K = K; c.Einv = Einv; c.count = count; c.slot = slot;
     c.idx_no = idx_no; c.idx_ov = idx_ov; c.totals = totals; c.block_tot = static_cast<int2*>(ws);
+    if (table && (reinterpret_cast<uintptr_t>(table) & 15)) return VFD_ERR_ALIGN;
+    c.table = table;
     cudaStream_t st = (cudaStream_t)stream;
     dim3 grid((unsigned)((N + kGatherWarps * VFD_WARP - 1) / (kGatherWarps * VFD_WARP)), d->B);
     voxel_count_kernel<<<grid, kGatherWarps * VFD_WARP, 0, st>>>(c);

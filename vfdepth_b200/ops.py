@@ -205,7 +205,7 @@ class _RaySample(torch.autograd.Function):
         return d_vol, None, None, None, None
 
 
-def voxel_classify(mask_small, K, Einv, geom, sizes=True):
+def voxel_classify(mask_small, K, Einv, geom, sizes=True, table=False):
     """-> count [B,N] u8, slot [B,N] i32, idx_no [M1] i64, idx_ov [M2] i64 (only count-1 / count-2
     voxels reach an MLP).  With ``sizes`` the two totals are read back to the host (one 8-byte copy) to slice the
     lists; without, the full-capacity lists and the device-side totals [2] are returned (no synchronisation)."""
@@ -223,9 +223,15 @@ def voxel_classify(mask_small, K, Einv, geom, sizes=True):
     totals = torch.empty((2,), device=dev, dtype=torch.int32)
     nbytes = _lib.load().vfd_voxel_classify_workspace_bytes(ctypes.byref(d))
     ws = torch.empty((max(nbytes, 8) // 8,), device=dev, dtype=torch.int64)
+    tab = None
+    if table:   # per-voxel corner table for the fused kernels (80 bytes per voxel of the grid)
+        tab = torch.empty((_lib.load().vfd_voxel_table_bytes(ctypes.byref(d)) // 16,), device=dev,
+                          dtype=torch.complex128)
     _lib.call('vfd_voxel_classify', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv),
-              _lib.ptr(count), _lib.ptr(slot), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(ws),
-              ctypes.c_size_t(ws.numel() * 8), _stream())
+              _lib.ptr(count), _lib.ptr(slot), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(tab),
+              _lib.ptr(ws), ctypes.c_size_t(ws.numel() * 8), _stream())
+    if table:
+        return count, slot, idx_no, idx_ov, totals, tab
     if not sizes:
         return count, slot, idx_no, idx_ov, totals
     m1, m2 = totals.tolist()
@@ -279,7 +285,7 @@ class _VoxelFuse(torch.autograd.Function):
     """gather + both 1x1 MLPs in one kernel (vfd_voxel_fuse_fwd); backward in vfd_voxel_fuse_bwd."""
 
     @staticmethod
-    def forward(ctx, feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, geom):
+    def forward(ctx, feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, geom):
         B = feats.shape[0]
         g = geom
         c1 = g.C + 1
@@ -296,15 +302,15 @@ class _VoxelFuse(torch.autograd.Function):
         d = g.desc(dev, B)
         vol = torch.empty((B, g.N, g.Cv), device=dev, dtype=torch.float32)
         _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
-                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(w_no), _lib.ptr(b_no),
-                  _lib.ptr(w_ov), _lib.ptr(b_ov), _lib.ptr(vol), _stream())
+                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(table), _lib.ptr(w_no),
+                  _lib.ptr(b_no), _lib.ptr(w_ov), _lib.ptr(b_ov), _lib.ptr(vol), _stream())
         ctx.geom = g
-        ctx.save_for_backward(feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, vol)
+        ctx.save_for_backward(feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, vol)
         return vol
 
     @staticmethod
     def backward(ctx, d_vol):
-        feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, vol = ctx.saved_tensors
+        feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, vol = ctx.saved_tensors
         g = ctx.geom
         B = feats.shape[0]
         dev = feats.device
@@ -316,15 +322,15 @@ class _VoxelFuse(torch.autograd.Function):
         nbytes = _lib.load().vfd_voxel_fuse_bwd_workspace_bytes(ctypes.byref(d))
         ws = torch.empty((max(nbytes, 16) // 4,), device=dev, dtype=torch.float32)
         _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
-                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(w_no), _lib.ptr(w_ov),
-                  _lib.ptr(vol), _lib.ptr(d_vol), _lib.ptr(d_feats), _lib.ptr(d_w_no), _lib.ptr(d_b_no),
+                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(table), _lib.ptr(w_no),
+                  _lib.ptr(w_ov), _lib.ptr(vol), _lib.ptr(d_vol), _lib.ptr(d_feats), _lib.ptr(d_w_no), _lib.ptr(d_b_no),
                   _lib.ptr(d_w_ov), _lib.ptr(d_b_ov), _lib.ptr(ws), ctypes.c_size_t(ws.numel() * 4), _stream())
-        return d_feats, d_w_no, d_b_no, d_w_ov, d_b_ov, None, None, None, None, None, None, None
+        return d_feats, d_w_no, d_b_no, d_w_ov, d_b_ov, None, None, None, None, None, None, None, None
 
 
-def voxel_fuse(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, geom):
+def voxel_fuse(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, geom):
     """feats_cl [B,cams,h,w,C] + MLP parameters -> channel-last voxel volume [B,N,Cv]."""
-    return _VoxelFuse.apply(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, geom)
+    return _VoxelFuse.apply(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, geom)
 
 
 def voxel_gather_depth(feats_cl, mask_small, K, Einv, geom, detail=False):
