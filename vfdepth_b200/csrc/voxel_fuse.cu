@@ -20,6 +20,8 @@
 //
 // Persistent grid (one CTA per SM, 16 warps); the list lengths are read from device memory (vfd_voxel_classify's
 // totals), so nothing here needs a host round trip.
+#include <stdlib.h>
+
 #include "gather_common.cuh"
 
 namespace vfd {
@@ -370,6 +372,311 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_fwd_kernel(const F
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Forward on the 5th-generation tensor cores (tcgen05.mma kind::tf32, accumulators in TMEM).  Used when C % 32 == 0 and
+// Cv % 16 == 0 (the DDAD / nuScenes configurations); the mma.sync kernel above covers the rest.
+//
+// Tile = 128 (voxel, camera-group) rows of one pass x Cv outputs; K = C runs in chunks of 32 channels (one 128-byte
+// swizzle atom row per voxel).  Roles, one CTA per SM, 13 warps:
+//   warps 0-3   epilogue: tcgen05.ld of the finished accumulator (TMEM lane = row), + relative-depth column, bias,
+//               LeakyReLU, 16-byte stores of the 256-byte voxel row
+//   warp  4     one elected lane issues the MMAs: per chunk 4 K-steps x {A_lo W_hi, A_hi W_lo, A_hi W_hi} (3xTF32);
+//               tcgen05.commit releases the A stage / publishes the accumulator through mbarriers
+//   warps 5-12  producers: bilinear gather of the chunk's 4 corner segments (128 B each) per voxel straight from the
+//               L2-resident feature maps, split into TF32 hi / lo, written in the K-major SWIZZLE_128B layout the
+//               MMA descriptors expect (2 stages of 32 KB)
+// The weight block of the pass sits in shared memory as hi / lo planes in the same layout (128 KB at C=256, Cv=64);
+// two accumulators (2 x Cv TMEM columns) let the epilogue of tile i overlap the MMAs of tile i+1.  Descriptor encoding
+// validated by tools/umma_probe.cu.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kTcRows = 128;
+constexpr int kTcEpiWarps = 4, kTcProdWarps = 8;
+constexpr int kTcProdThreads = kTcProdWarps * VFD_WARP;
+constexpr int kTcThreads = (kTcEpiWarps + 1 + kTcProdWarps) * VFD_WARP;
+constexpr int kTcStages = 2;
+constexpr int kTcStageBytes = 2 * kTcRows * 128;       // hi + lo plane of one 32-channel chunk
+
+struct TcMeta {          // per tile (double buffered)
+    long long row[kTcRows];
+    int4 off[kMaxEnt][kTcRows];
+    float4 wgt[kMaxEnt][kTcRows];
+    int cam[kMaxEnt][kTcRows];      // b*num_cams + c
+    int cnt[kTcRows];
+    float zrel[kTcRows];            // sum of the wanted entries' relative depths
+};
+
+struct TcBars {
+    uint64_t full[kTcStages], empty[kTcStages], acc_full[2], acc_empty[2], meta_free[2];
+    uint32_t tmem_base;
+};
+
+__host__ __device__ inline size_t fuse_tc_smem_bytes(int C, int Cv) {
+    return 1024 /*alignment slack*/ + (size_t)2 * (C / 32) * Cv * 128 + (size_t)kTcStages * kTcStageBytes +
+           2 * sizeof(TcMeta) + 3 * 64 * sizeof(float) + sizeof(TcBars);
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {   // arrives on `bar` when all MMAs issued so far have finished
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row atoms of 1024 bytes (tools/umma_probe.cu)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+           ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+        "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// byte offset of (row r, 16-byte chunk c16) inside a [rows][128 B] SWIZZLE_128B tile
+__device__ __forceinline__ uint32_t sw128_off(int r, int c16) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4));
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1) voxel_fuse_fwd_tc_kernel(const FuseArgs a) {
+    extern __shared__ unsigned char smem_raw[];
+    const vfd_fusion_desc& d = a.d;
+    const int C = d.C, C1 = C + 1, Cv = d.Cv, NCH = C / 32;
+    unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms: 1024-byte aligned
+    const uint32_t wplane = (uint32_t)NCH * Cv * 128;      // bytes of one weight plane: [NCH][Cv rows][128 B]
+    unsigned char* sW = base;
+    unsigned char* sA = sW + 2 * wplane;                   // [stage][hi, lo][128 rows][128 B]
+    TcMeta* meta = reinterpret_cast<TcMeta*>(sA + kTcStages * kTcStageBytes);
+    float* sWz = reinterpret_cast<float*>(meta + 2);       // [64] relative-depth column of the pass' weight block
+    float* sBias = sWz + 64;                               // [64]
+    TcBars* bars = reinterpret_cast<TcBars*>(sBias + 128);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int M1 = a.totals[0], M2 = a.totals[1];
+    const int T1 = (M1 + kTcRows - 1) / kTcRows, T2 = (M2 + kTcRows - 1) / kTcRows;
+    unsigned gmask[2] = {0u, 0u};
+    for (int c = 0; c < d.num_cams; ++c) gmask[d.group[c] ? 1 : 0] |= 1u << c;
+    const size_t rows_total = (size_t)d.B * d.X * d.Y * d.Z;
+    const CornerTable tb = carve_table(const_cast<void*>(a.table), rows_total);
+    const size_t map = (size_t)d.h * d.w * C;
+
+    if (tid == 0) {
+        for (int s = 0; s < kTcStages; ++s) { mbar_init(&bars->full[s], kTcProdThreads); mbar_init(&bars->empty[s], 1); }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&bars->acc_full[i], 1);
+            mbar_init(&bars->acc_empty[i], kTcEpiWarps * VFD_WARP);
+            mbar_init(&bars->meta_free[i], kTcEpiWarps * VFD_WARP);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kTcEpiWarps) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(smem_u32(&bars->tmem_base)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = bars->tmem_base;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(Cv >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
+
+    uint32_t stage = 0, phase = 0;      // A-stage ring position of this role (producers and the MMA warp)
+    uint32_t ntile = 0;                 // tiles this role has started (same sequence in every role)
+
+    for (int pass = 0; pass < 3; ++pass) {
+        const int M = pass ? M2 : M1, T = pass ? T2 : T1;
+        const int64_t* idx = pass ? a.idx_ov : a.idx_no;
+        const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
+        __syncthreads();                // every role has drained the previous pass: the weight planes are free
+        {
+            const float* w = pass ? a.w_ov : a.w_no;
+            const int ld = pass ? 2 * C1 : C1, koff = pass == 2 ? C1 : 0;
+            for (int i = tid; i < Cv * C; i += kTcThreads) {
+                const int n = i / C, k = i - n * C;
+                uint32_t hi, lo;
+                split_tf32(__ldg(w + (size_t)n * ld + koff + k), hi, lo);
+                const uint32_t o = (uint32_t)(k >> 5) * Cv * 128 + sw128_off(n, (k & 31) >> 2) + (k & 3) * 4;
+                *reinterpret_cast<uint32_t*>(sW + o) = hi;
+                *reinterpret_cast<uint32_t*>(sW + wplane + o) = lo;
+            }
+            if (tid < 64) {
+                sWz[tid] = tid < Cv ? __ldg(w + (size_t)tid * ld + koff + C) : 0.f;
+                sBias[tid] = tid < Cv ? __ldg((pass ? a.b_ov : a.b_no) + tid) : 0.f;
+            }
+        }
+        fence_proxy_async_smem();
+        __syncthreads();
+
+        if (warp > kTcEpiWarps) {
+            // ===================== producers =====================
+            const int ptid = tid - (kTcEpiWarps + 1) * VFD_WARP;
+            const int c16 = ptid & 7, r0 = ptid >> 3;        // item it: row r0 + 32 it, 16-byte chunk c16 of the 128-byte row
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                TcMeta& tm = meta[ntile & 1];
+                mbar_wait(&bars->meta_free[ntile & 1], ((ntile >> 1) & 1) ^ 1);
+                {   // metadata of the tile from the corner table: thread (half, r)
+                    const int r = ptid & (kTcRows - 1), half = ptid >> 7;
+                    const int li = tile * kTcRows + r;
+                    long long row = -1;
+                    int2 m0 = make_int2(-1, 0), m1 = make_int2(-1, 0);
+                    if (li < M) {
+                        row = idx[li];
+                        m0 = __ldg(tb.meta + row);
+                        m1 = __ldg(tb.meta + rows_total + row);
+                    }
+                    const bool w0 = entry_wanted(m0, want, d.num_cams), w1 = entry_wanted(m1, want, d.num_cams);
+                    if (half == 0) {
+                        if (w0) {
+                            tm.off[0][r] = __ldg(tb.off + row);
+                            tm.wgt[0][r] = __ldg(tb.wgt + row);
+                            tm.cam[0][r] = m0.x;
+                        }
+                        tm.row[r] = row;
+                        tm.cnt[r] = (w0 ? 1 : 0) + (w1 ? 1 : 0);
+                        tm.zrel[r] = (w0 ? __int_as_float(m0.y) : 0.f) + (w1 ? __int_as_float(m1.y) : 0.f);
+                    } else if (w1) {
+                        const int dst = w0 ? 1 : 0;
+                        tm.off[dst][r] = __ldg(tb.off + rows_total + row);
+                        tm.wgt[dst][r] = __ldg(tb.wgt + rows_total + row);
+                        tm.cam[dst][r] = m1.x;
+                    }
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(kTcProdThreads) : "memory");
+                int4 off[4];
+                float4 wg[4];
+                const float* src[4];
+                int cnt[4];
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int r = r0 + 32 * it;
+                    cnt[it] = tm.cnt[r];
+                    off[it] = tm.off[0][r];
+                    wg[it] = tm.wgt[0][r];
+                    src[it] = a.feats + (size_t)(cnt[it] > 0 ? tm.cam[0][r] : 0) * map + c16 * 4;
+                }
+                for (int kc = 0; kc < NCH; ++kc) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1);
+                    float4 v[4][4];
+#pragma unroll
+                    for (int it = 0; it < 4; ++it) {
+                        const float* p = src[it] + kc * 32;
+                        const bool on = cnt[it] > 0;
+                        v[it][0] = on ? ldg_f4(p + off[it].x) : f4_zero();
+                        v[it][1] = on ? ldg_f4(p + off[it].y) : f4_zero();
+                        v[it][2] = on ? ldg_f4(p + off[it].z) : f4_zero();
+                        v[it][3] = on ? ldg_f4(p + off[it].w) : f4_zero();
+                    }
+                    unsigned char* st_hi = sA + stage * kTcStageBytes;
+#pragma unroll
+                    for (int it = 0; it < 4; ++it) {
+                        const int r = r0 + 32 * it;
+                        float4 x = f4_scale(wg[it].x, v[it][0]);
+                        f4_fma(x, wg[it].y, v[it][1]);
+                        f4_fma(x, wg[it].z, v[it][2]);
+                        f4_fma(x, wg[it].w, v[it][3]);
+                        if (cnt[it] > 1) {       // a second camera of the same group sees the voxel (rare)
+                            const int4 o2 = tm.off[1][r];
+                            const float4 w2 = tm.wgt[1][r];
+                            const float* p = a.feats + (size_t)tm.cam[1][r] * map + c16 * 4 + kc * 32;
+                            float4 y = f4_scale(w2.x, ldg_f4(p + o2.x));
+                            f4_fma(y, w2.y, ldg_f4(p + o2.y));
+                            f4_fma(y, w2.z, ldg_f4(p + o2.z));
+                            f4_fma(y, w2.w, ldg_f4(p + o2.w));
+                            f4_add(x, y);
+                        }
+                        uint4 hi, lo;
+                        split_tf32(x.x, hi.x, lo.x);
+                        split_tf32(x.y, hi.y, lo.y);
+                        split_tf32(x.z, hi.z, lo.z);
+                        split_tf32(x.w, hi.w, lo.w);
+                        const uint32_t o = sw128_off(r, c16);
+                        *reinterpret_cast<uint4*>(st_hi + o) = hi;
+                        *reinterpret_cast<uint4*>(st_hi + kTcRows * 128 + o) = lo;
+                    }
+                    fence_proxy_async_smem();
+                    mbar_arrive(&bars->full[stage]);
+                    if (++stage == kTcStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        } else if (warp == kTcEpiWarps) {
+            // ===================== MMA issue (lane 0) =====================
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                const uint32_t acc = ntile & 1;
+                mbar_wait(&bars->acc_empty[acc], ((ntile >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int kc = 0; kc < NCH; ++kc) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint64_t a_hi = umma_desc(smem_u32(sA + stage * kTcStageBytes));
+                        const uint64_t a_lo = umma_desc(smem_u32(sA + stage * kTcStageBytes + kTcRows * 128));
+                        const uint64_t b_hi = umma_desc(smem_u32(sW + (uint32_t)kc * Cv * 128));
+                        const uint64_t b_lo = umma_desc(smem_u32(sW + wplane + (uint32_t)kc * Cv * 128));
+                        const uint32_t dcol = tmem + acc * 64;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {     // 8 TF32 = 32 bytes per K-step: +2 in the 16-byte address field
+                            umma_tf32(dcol, a_lo + 2 * k, b_hi + 2 * k, idesc, (kc | k) ? 1u : 0u);
+                            umma_tf32(dcol, a_hi + 2 * k, b_lo + 2 * k, idesc, 1u);
+                            umma_tf32(dcol, a_hi + 2 * k, b_hi + 2 * k, idesc, 1u);
+                        }
+                        tc_commit(&bars->empty[stage]);                    // frees the A stage when these MMAs are done
+                        if (kc == NCH - 1) tc_commit(&bars->acc_full[acc]);   // ... and publishes the accumulator
+                    }
+                    __syncwarp();
+                    if (++stage == kTcStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        } else {
+            // ===================== epilogue (TMEM lane = row of the tile) =====================
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                const uint32_t acc = ntile & 1;
+                const TcMeta& tm = meta[ntile & 1];
+                mbar_wait(&bars->acc_full[acc], (ntile >> 1) & 1);
+                tc_fence_after();
+                const long long row = tm.row[tid];
+                const float z = tm.zrel[tid];
+                mbar_arrive(&bars->meta_free[ntile & 1]);
+                float* o = a.vol + (size_t)(row >= 0 ? row : 0) * Cv;
+                for (int c0 = 0; c0 < Cv; c0 += 16) {
+                    uint32_t v[16];
+                    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + acc * 64 + (uint32_t)c0;
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                        : "r"(taddr));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (row >= 0) {
+#pragma unroll
+                        for (int q = 0; q < 16; q += 4) {
+                            float4 y = make_float4(__uint_as_float(v[q]), __uint_as_float(v[q + 1]),
+                                                   __uint_as_float(v[q + 2]), __uint_as_float(v[q + 3]));
+                            const float4 wz = *reinterpret_cast<const float4*>(sWz + c0 + q);
+                            f4_fma(y, z, wz);
+                            if (pass == 2) f4_add(y, *reinterpret_cast<const float4*>(o + c0 + q));   // parked by pass 1
+                            if (pass != 1) {
+                                f4_add(y, *reinterpret_cast<const float4*>(sBias + c0 + q));
+                                y.x = y.x > 0.f ? y.x : 0.1f * y.x;
+                                y.y = y.y > 0.f ? y.y : 0.1f * y.y;
+                                y.z = y.z > 0.f ? y.z : 0.1f * y.z;
+                                y.w = y.w > 0.f ? y.w : 0.1f * y.w;
+                            }
+                            *reinterpret_cast<float4*>(o + c0 + q) = y;
+                        }
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&bars->acc_empty[acc]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kTcEpiWarps) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(tmem));
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Backward.  Per pass (weight block) and per tile of 64 voxels:
 //   dZ  = d_vol[rows] * LeakyReLU'(vol[rows])       (y > 0 <=> pre-activation > 0), split into TF32 hi/lo planes
 //   A   = the gathered feature rows, recomputed (L2-resident feature maps)  [64 x (C+1)]
@@ -678,6 +985,18 @@ extern "C" int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, 
     if (cudaMemsetAsync(vol, 0, vol_bytes, st) != cudaSuccess) return VFD_ERR_CUDA;
     const int sms = sm_count();
     if (sms <= 0) return VFD_ERR_CUDA;
+    // tcgen05 kernel for the production shapes; VFD_FUSE_LEGACY=1 forces the mma.sync kernel (tests compare the two)
+    const char* legacy = getenv("VFD_FUSE_LEGACY");
+    if (d->C % 32 == 0 && d->Cv % 16 == 0 && !(legacy && legacy[0] == '1')) {
+        const size_t smem = fuse_tc_smem_bytes(d->C, d->Cv);
+        if (smem > 227 * 1024) return VFD_ERR_UNSUPPORTED;
+        if (cudaFuncSetAttribute(voxel_fuse_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess)
+            return VFD_ERR_CUDA;
+        voxel_fuse_fwd_tc_kernel<<<sms, kTcThreads, smem, st>>>(a);
+        VFD_CHECK_LAUNCH();
+        return VFD_OK;
+    }
     const size_t smem = fuse_fwd_smem_bytes(a.KP);
     rc = d->C > 128 ? launch_fuse(voxel_fuse_fwd_kernel<2>, a, smem, sms, st)
                     : launch_fuse(voxel_fuse_fwd_kernel<1>, a, smem, sms, st);
