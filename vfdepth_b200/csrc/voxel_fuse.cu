@@ -695,7 +695,7 @@ __host__ __device__ inline size_t fuse_bwd_smem_bytes(int KP, int NT) {
     return meta_bytes(kFuseRows) + (size_t)NT * 8 * SN * 4 + (size_t)kFuseRows * SN * 4 + (size_t)2 * kFuseRows * kZS * 4;
 }
 
-template <int NCH>
+template <int NCH, bool DATA>   // DATA = false: weight gradients only (dA and the scatter run in voxel_fuse_bwd_data_tc_kernel)
 __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const FuseArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const vfd_fusion_desc& d = a.d;
@@ -725,7 +725,7 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
         const int64_t* idx = pass ? a.idx_ov : a.idx_no;
         const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
         __syncthreads();
-        {   // natural-layout weight block [out][in], zero padded
+        if (DATA) {   // natural-layout weight block [out][in], zero padded
             const float* w = pass ? a.w_ov : a.w_no;
             const int ld = pass ? 2 * C1 : C1, koff = pass == 2 ? C1 : 0;
             for (int i = threadIdx.x; i < NT * 8 * SN; i += blockDim.x) {
@@ -820,6 +820,10 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
                 dwz += sz;
             }
 
+            if (!DATA) {
+                __syncthreads();
+                continue;
+            }
             // dA [64 x C] = dZ [64 x Cv] W [Cv x C]
             float acca[8][4];
 #pragma unroll
@@ -909,6 +913,223 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
             P[(size_t)Cv * C1 + threadIdx.x] = db;
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Backward, data half, on tcgen05: dA [128 rows x C] = dZ [128 x Cv] W [Cv x C] per tile (3xTF32, one N = C instruction
+// per K-step, accumulator = C TMEM columns, double buffered), then the bilinear scatter of the dA rows into d_feats.
+//   warps 0-3   drain: tcgen05.ld 32 columns at a time -> staging tile in shared memory -> 8 lanes per row push
+//               128-byte contiguous red.global.add.v4.f32 to the row's 4 corners (x entries)
+//   warp  4     MMA issue
+//   warps 5-12  producers: dZ = d_vol * LeakyReLU'(vol) of the tile's rows, split hi / lo, K-major SWIZZLE_128B;
+//               tile metadata (corner table) prefetched in registers and published once the previous tile is drained
+// W^T of the pass ([in][out], hi / lo planes, 128 KB at C=256, Cv=64) stays in shared memory.
+// ---------------------------------------------------------------------------------------------------------
+struct TcBwdBars {
+    uint64_t full, empty, acc_full[2], acc_empty[2], meta_free;
+    uint32_t tmem_base;
+};
+constexpr int kStageCols = 32;     // dA columns drained per round
+
+__host__ __device__ inline size_t fuse_tc_bwd_data_smem_bytes(int C, int Cv) {
+    const int nkc = (Cv + 31) / 32;
+    return 1024 + (size_t)2 * nkc * C * 128 + (size_t)2 * nkc * kTcRows * 128 + (size_t)kTcRows * kStageCols * 4 +
+           sizeof(TcMeta) + sizeof(TcBwdBars);
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1) voxel_fuse_bwd_data_tc_kernel(const FuseArgs a) {
+    extern __shared__ unsigned char smem_raw[];
+    const vfd_fusion_desc& d = a.d;
+    const int C = d.C, C1 = C + 1, Cv = d.Cv, NKC = (Cv + 31) / 32, KS = Cv / 8;
+    unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const uint32_t wplane = (uint32_t)NKC * C * 128;           // W^T plane: [NKC][C rows (in)][128 B (32 out)]
+    const uint32_t zplane = (uint32_t)NKC * kTcRows * 128;     // dZ plane:  [NKC][128 rows][128 B]
+    unsigned char* sW = base;
+    unsigned char* sZ = sW + 2 * wplane;
+    float* sStage = reinterpret_cast<float*>(sZ + 2 * zplane);                 // [128][32]
+    TcMeta* tm = reinterpret_cast<TcMeta*>(sStage + kTcRows * kStageCols);
+    TcBwdBars* bars = reinterpret_cast<TcBwdBars*>(tm + 1);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int M1 = a.totals[0], M2 = a.totals[1];
+    const int T1 = (M1 + kTcRows - 1) / kTcRows, T2 = (M2 + kTcRows - 1) / kTcRows;
+    unsigned gmask[2] = {0u, 0u};
+    for (int c = 0; c < d.num_cams; ++c) gmask[d.group[c] ? 1 : 0] |= 1u << c;
+    const size_t rows_total = (size_t)d.B * d.X * d.Y * d.Z;
+    const CornerTable tb = carve_table(const_cast<void*>(a.table), rows_total);
+    const size_t map = (size_t)d.h * d.w * C;
+
+    if (tid == 0) {
+        mbar_init(&bars->full, kTcProdThreads);
+        mbar_init(&bars->empty, 1);
+        mbar_init(&bars->meta_free, kTcEpiWarps * VFD_WARP);
+        for (int i = 0; i < 2; ++i) { mbar_init(&bars->acc_full[i], 1); mbar_init(&bars->acc_empty[i], kTcEpiWarps * VFD_WARP); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kTcEpiWarps) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&bars->tmem_base)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = bars->tmem_base;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(C >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
+    uint32_t ntile = 0;
+
+    for (int pass = 0; pass < 3; ++pass) {
+        const int M = pass ? M2 : M1, T = pass ? T2 : T1;
+        const int64_t* idx = pass ? a.idx_ov : a.idx_no;
+        const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
+        __syncthreads();
+        {   // W^T planes: element (in, out) = w[out][koff + in]
+            const float* w = pass ? a.w_ov : a.w_no;
+            const int ld = pass ? 2 * C1 : C1, koff = pass == 2 ? C1 : 0;
+            for (int i = tid; i < Cv * C; i += kTcThreads) {
+                const int o = i / C, k = i - o * C;          // coalesced read along in
+                uint32_t hi, lo;
+                split_tf32(__ldg(w + (size_t)o * ld + koff + k), hi, lo);
+                const uint32_t off = (uint32_t)(o >> 5) * C * 128 + sw128_off(k, (o & 31) >> 2) + (o & 3) * 4;
+                *reinterpret_cast<uint32_t*>(sW + off) = hi;
+                *reinterpret_cast<uint32_t*>(sW + wplane + off) = lo;
+            }
+        }
+        fence_proxy_async_smem();
+        __syncthreads();
+
+        if (warp > kTcEpiWarps) {
+            // ===================== producers =====================
+            const int ptid = tid - (kTcEpiWarps + 1) * VFD_WARP;
+            const int nq = Cv / 4;                                   // float4 per row
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                // this thread's share of the metadata, from the corner table (published below)
+                const int r = ptid & (kTcRows - 1), half = ptid >> 7;
+                const int li = tile * kTcRows + r;
+                long long row = -1;
+                int2 m0 = make_int2(-1, 0), m1 = make_int2(-1, 0);
+                if (li < M) {
+                    row = idx[li];
+                    m0 = __ldg(tb.meta + row);
+                    m1 = __ldg(tb.meta + rows_total + row);
+                }
+                const bool w0 = entry_wanted(m0, want, d.num_cams), w1 = entry_wanted(m1, want, d.num_cams);
+                int4 e_off = make_int4(0, 0, 0, 0);
+                float4 e_wgt = f4_zero();
+                if (half == 0 ? w0 : w1) {
+                    e_off = __ldg(tb.off + (half ? rows_total : 0) + row);
+                    e_wgt = __ldg(tb.wgt + (half ? rows_total : 0) + row);
+                }
+                // dZ of the tile into the (single) operand stage
+                mbar_wait(&bars->empty, (ntile & 1) ^ 1);
+                for (int item = ptid; item < kTcRows * nq; item += kTcProdThreads) {
+                    const int rr = item / nq, q4 = item - rr * nq;
+                    const int l2 = tile * kTcRows + rr;
+                    float4 z = f4_zero();
+                    if (l2 < M) {
+                        const long long rw = idx[l2];
+                        const float4 gy = ld_stream_f4(a.d_vol + (size_t)rw * Cv + q4 * 4);
+                        const float4 y = ld_stream_f4(a.vol + (size_t)rw * Cv + q4 * 4);
+                        z.x = y.x > 0.f ? gy.x : 0.1f * gy.x;
+                        z.y = y.y > 0.f ? gy.y : 0.1f * gy.y;
+                        z.z = y.z > 0.f ? gy.z : 0.1f * gy.z;
+                        z.w = y.w > 0.f ? gy.w : 0.1f * gy.w;
+                    }
+                    uint4 hi, lo;
+                    split_tf32(z.x, hi.x, lo.x);
+                    split_tf32(z.y, hi.y, lo.y);
+                    split_tf32(z.z, hi.z, lo.z);
+                    split_tf32(z.w, hi.w, lo.w);
+                    const uint32_t o = (uint32_t)(q4 >> 3) * kTcRows * 128 + sw128_off(rr, q4 & 7);
+                    *reinterpret_cast<uint4*>(sZ + o) = hi;
+                    *reinterpret_cast<uint4*>(sZ + zplane + o) = lo;
+                }
+                // publish the metadata once the previous tile has been drained
+                mbar_wait(&bars->meta_free, (ntile & 1) ^ 1);
+                if (half == 0) {
+                    if (w0) { tm->off[0][r] = e_off; tm->wgt[0][r] = e_wgt; tm->cam[0][r] = m0.x; }
+                    tm->row[r] = row;
+                    tm->cnt[r] = (w0 ? 1 : 0) + (w1 ? 1 : 0);
+                } else if (w1) {
+                    const int dst = w0 ? 1 : 0;
+                    tm->off[dst][r] = e_off; tm->wgt[dst][r] = e_wgt; tm->cam[dst][r] = m1.x;
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(&bars->full);
+            }
+        } else if (warp == kTcEpiWarps) {
+            // ===================== MMA issue =====================
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                const uint32_t acc = ntile & 1;
+                mbar_wait(&bars->acc_empty[acc], ((ntile >> 1) & 1) ^ 1);
+                mbar_wait(&bars->full, ntile & 1);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t dcol = tmem + acc * 256;
+                    for (int ks = 0; ks < KS; ++ks) {
+                        const uint32_t kc = ks >> 2, kk = 2 * (ks & 3);
+                        const uint64_t a_hi = umma_desc(smem_u32(sZ + kc * kTcRows * 128)) + kk;
+                        const uint64_t a_lo = umma_desc(smem_u32(sZ + zplane + kc * kTcRows * 128)) + kk;
+                        const uint64_t b_hi = umma_desc(smem_u32(sW + kc * C * 128)) + kk;
+                        const uint64_t b_lo = umma_desc(smem_u32(sW + wplane + kc * C * 128)) + kk;
+                        umma_tf32(dcol, a_lo, b_hi, idesc, ks ? 1u : 0u);
+                        umma_tf32(dcol, a_hi, b_lo, idesc, 1u);
+                        umma_tf32(dcol, a_hi, b_hi, idesc, 1u);
+                    }
+                    tc_commit(&bars->empty);
+                    tc_commit(&bars->acc_full[acc]);
+                }
+                __syncwarp();
+            }
+        } else {
+            // ===================== drain + scatter =====================
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                const uint32_t acc = ntile & 1;
+                mbar_wait(&bars->acc_full[acc], (ntile >> 1) & 1);
+                tc_fence_after();
+                for (int c0 = 0; c0 < C; c0 += kStageCols) {
+                    uint32_t v[32];
+                    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + acc * 256 + (uint32_t)c0;
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+                        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                        : "r"(taddr));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    // staging: row tid, 32 columns; 16-byte chunks rotated by the row so that the column reads below
+                    // and these row writes are both conflict-free
+                    float* srow = sStage + tid * kStageCols;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        *reinterpret_cast<uint4*>(srow + (((q + tid) & 7) << 2)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                    __syncwarp();      // each warp drains the 32 rows it staged itself
+                    const int sub = lane >> 3, l8 = lane & 7;         // 4 rows per instruction, 8 lanes x 16 B per row
+                    for (int rb = 0; rb < 32; rb += 4) {
+                        const int r = warp * 32 + rb + sub;
+                        const int cnt = tm->cnt[r];
+                        const float4 gv = *reinterpret_cast<const float4*>(sStage + r * kStageCols + (((l8 + r) & 7) << 2));
+                        for (int e = 0; e < cnt; ++e) {
+                            const int4 off = tm->off[e][r];
+                            const float4 wg = tm->wgt[e][r];
+                            float* fb = a.d_feats + (size_t)tm->cam[e][r] * map + c0 + l8 * 4;
+                            if (wg.x != 0.f) red_add_f4(fb + off.x, f4_scale(wg.x, gv));
+                            if (wg.y != 0.f) red_add_f4(fb + off.y, f4_scale(wg.y, gv));
+                            if (wg.z != 0.f) red_add_f4(fb + off.z, f4_scale(wg.z, gv));
+                            if (wg.w != 0.f) red_add_f4(fb + off.w, f4_scale(wg.w, gv));
+                        }
+                    }
+                    __syncwarp();
+                }
+                tc_fence_before();
+                mbar_arrive(&bars->acc_empty[acc]);
+                mbar_arrive(&bars->meta_free);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kTcEpiWarps) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
 }
 
 // sum the per-CTA partials in CTA order -> d_w_no [Cv][C1], d_b_no, d_w_ov [Cv][2 C1], d_b_ov
@@ -1038,8 +1259,20 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
     const size_t fbytes = (size_t)d->B * d->num_cams * d->h * d->w * d->C * sizeof(float);
     if (cudaMemsetAsync(d_feats, 0, fbytes, st) != cudaSuccess) return VFD_ERR_CUDA;
     const size_t smem = fuse_bwd_smem_bytes(a.KP, a.NT);
-    rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2>, a, smem, sms, st)
-                    : launch_fuse(voxel_fuse_bwd_kernel<1>, a, smem, sms, st);
+    const char* legacy = getenv("VFD_FUSE_LEGACY");
+    const size_t smem_tc = fuse_tc_bwd_data_smem_bytes(d->C, d->Cv);
+    if (d->C % 32 == 0 && d->Cv % 16 == 0 && smem_tc <= 227 * 1024 && !(legacy && legacy[0] == '1')) {
+        // production shapes: dA + scatter on tcgen05, weight gradients on the mma.sync kernel
+        if (cudaFuncSetAttribute(voxel_fuse_bwd_data_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem_tc) != cudaSuccess)
+            return VFD_ERR_CUDA;
+        voxel_fuse_bwd_data_tc_kernel<<<sms, kTcThreads, smem_tc, st>>>(a);
+        rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2, false>, a, smem, sms, st)
+                        : launch_fuse(voxel_fuse_bwd_kernel<1, false>, a, smem, sms, st);
+    } else {
+        rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2, true>, a, smem, sms, st)
+                        : launch_fuse(voxel_fuse_bwd_kernel<1, true>, a, smem, sms, st);
+    }
     if (rc) return rc;
     const int total = 3 * d->Cv * (d->C + 2);
     voxel_fuse_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(a.partial, sms, d->Cv, d->C + 1, d_w_no, d_b_no,
