@@ -77,7 +77,7 @@ struct WarpSample {
     float dvx[3], dvy[3];  // d v / d ix, d v / d iy   (ATen grid_sampler_2d_backward)
     float cam[3];          // P @ [X;1]
     float den;             // cam.z + 1e-7
-    bool nan;              // the sample was replaced by 2.0: no gradient flows
+    bool nan;              // the sample was replaced by 2.0 or lies outside the image: no gradient flows
 };
 
 template <bool GRAD>
@@ -115,7 +115,10 @@ __device__ __forceinline__ WarpSample warp_sample(const float* P, const float* _
     // bilinear, zeros padding, align_corners=True; weights as ATen forms them
     const float x0f = floorf(ix), y0f = floorf(iy);
     s.v[0] = s.v[1] = s.v[2] = 0.f;
-    if (!(x0f >= -1.f && x0f <= (float)(W - 1) && y0f >= -1.f && y0f <= (float)(H - 1))) return s;
+    if (!(x0f >= -1.f && x0f <= (float)(W - 1) && y0f >= -1.f && y0f <= (float)(H - 1))) {
+        if (GRAD) s.nan = true;    // all four corners outside the image: zeros, and no gradient either
+        return s;
+    }
     const int x0 = (int)x0f, y0 = (int)y0f;
     const float tx1 = (x0f + 1.f) - ix, tx0 = ix - x0f, ty1 = (y0f + 1.f) - iy, ty0 = iy - y0f;
     const bool vx0 = x0 >= 0, vx1 = x0 + 1 <= W - 1, vy0 = y0 >= 0, vy1 = y0 + 1 <= H - 1;

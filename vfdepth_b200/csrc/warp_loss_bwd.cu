@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     const int W = d.W, H = d.H, HW = H * W, n_src = d.n_src;
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH, ox = tx0 - 2, oy = ty0 - 2;
     warp_ctx_init(ctx, d, a.T, a.params, b, ci);
+    for (int i = threadIdx.x; i < (kTileThreads / 32) * kMaxW * 12; i += kTileThreads) (&s_dP[0][0])[i] = 0.f;
     __syncthreads();
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
@@ -173,45 +174,55 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     }
     float gdepth = 0.f;
     for (int j = 0; j < ctx.NW; ++j) {
+        if (!ctx.active[j]) continue;      // CTA-uniform
         float dP[12];
 #pragma unroll
         for (int i = 0; i < 12; ++i) dP[i] = 0.f;
-        if (live && ctx.active[j]) {
+        // Most (pixel, warp) pairs carry no gradient: the min picked the other frame in the whole 3x3 neighbourhood, or
+        // the pixel lies outside the spatial overlap.  Those skip the sampler; a warp whose 32 pixels all skip also
+        // skips the reduction (its slots of s_dP stay zero, so the sums are unchanged).
+        bool contrib = false;
+        if (live) {
             const int k = j < n_src ? j : VFD_WARP_SRC + (j - n_src) / VFD_WARP_NBR;
-            const WarpSample s = warp_sample<true>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
-            if (!s.nan) {
-                const float ng = warp_normalise_grad(ctx.prm[j], s.m);
-                float gix = 0.f, giy = 0.f;
+            const float up[3] = {pick5(dpred, k, 0), pick5(dpred, k, 1), pick5(dpred, k, 2)};
+            if (up[0] != 0.f || up[1] != 0.f || up[2] != 0.f) {
+                const WarpSample s = warp_sample<true>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
+                if (!s.nan) {
+                    contrib = true;
+                    const float ng = warp_normalise_grad(ctx.prm[j], s.m);
+                    float gix = 0.f, giy = 0.f;
 #pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    const float dw = pick5(dpred, k, c) * ng;
-                    gix = fmaf(dw, s.dvx[c], gix);
-                    giy = fmaf(dw, s.dvy[c], giy);
-                }
-                // ix == cam.x / den, iy == cam.y / den  (normalise then un-normalise cancel exactly in the derivative)
-                const float inv = 1.f / s.den;
-                const float dc0 = gix * inv, dc1 = giy * inv;
-                const float dc2 = -(gix * s.cam[0] + giy * s.cam[1]) * inv * inv;
-                const float* P = ctx.P[j];
-                // d(ix)/d(depth) = (a0 * den - cam.x * a2) / den^2 with a = P[:, :3] @ ray, cam = depth * a + P[:, 3].
-                // The depth-proportional parts cancel EXACTLY in that numerator (a pure rotation moves no pixel when
-                // depth changes); written as below the fp32 result keeps ~7 digits even when depth*|a| >> |t|, where
-                // the chain-rule form loses 2-3 of them.
-                const float a0 = P[0] * ray[0] + P[1] * ray[1] + P[2] * ray[2];
-                const float a1 = P[4] * ray[0] + P[5] * ray[1] + P[6] * ray[2];
-                const float a2 = P[8] * ray[0] + P[9] * ray[1] + P[10] * ray[2];
-                const float t2 = P[11] + 1e-7f;
-                gdepth += (gix * (a0 * t2 - P[3] * a2) + giy * (a1 * t2 - P[7] * a2)) * inv * inv;
-                const float dc[3] = {dc0, dc1, dc2};
+                    for (int c = 0; c < 3; ++c) {
+                        const float dw = up[c] * ng;
+                        gix = fmaf(dw, s.dvx[c], gix);
+                        giy = fmaf(dw, s.dvy[c], giy);
+                    }
+                    // ix == cam.x / den, iy == cam.y / den  (normalise then un-normalise cancel exactly in the derivative)
+                    const float inv = 1.f / s.den;
+                    const float dc0 = gix * inv, dc1 = giy * inv;
+                    const float dc2 = -(gix * s.cam[0] + giy * s.cam[1]) * inv * inv;
+                    const float* P = ctx.P[j];
+                    // d(ix)/d(depth) = (a0 * den - cam.x * a2) / den^2 with a = P[:, :3] @ ray, cam = depth * a + P[:, 3].
+                    // The depth-proportional parts cancel EXACTLY in that numerator (a pure rotation moves no pixel when
+                    // depth changes); written as below the fp32 result keeps ~7 digits even when depth*|a| >> |t|, where
+                    // the chain-rule form loses 2-3 of them.
+                    const float a0 = P[0] * ray[0] + P[1] * ray[1] + P[2] * ray[2];
+                    const float a1 = P[4] * ray[0] + P[5] * ray[1] + P[6] * ray[2];
+                    const float a2 = P[8] * ray[0] + P[9] * ray[1] + P[10] * ray[2];
+                    const float t2 = P[11] + 1e-7f;
+                    gdepth += (gix * (a0 * t2 - P[3] * a2) + giy * (a1 * t2 - P[7] * a2)) * inv * inv;
+                    const float dc[3] = {dc0, dc1, dc2};
 #pragma unroll
-                for (int rr = 0; rr < 3; ++rr) {
-                    dP[rr * 4 + 0] = dc[rr] * X[0];
-                    dP[rr * 4 + 1] = dc[rr] * X[1];
-                    dP[rr * 4 + 2] = dc[rr] * X[2];
-                    dP[rr * 4 + 3] = dc[rr];
+                    for (int rr = 0; rr < 3; ++rr) {
+                        dP[rr * 4 + 0] = dc[rr] * X[0];
+                        dP[rr * 4 + 1] = dc[rr] * X[1];
+                        dP[rr * 4 + 2] = dc[rr] * X[2];
+                        dP[rr * 4 + 3] = dc[rr];
+                    }
                 }
             }
         }
+        if (!__any_sync(0xffffffffu, contrib)) continue;
         {   // warp sum of the 12 values as a reduce-scatter butterfly (16 shuffles instead of 60, fixed order):
             // after the steps over lane bits 4..1 lane l holds element l >> 1 summed over half the warp
             float v[16];
