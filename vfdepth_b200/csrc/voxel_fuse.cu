@@ -695,7 +695,7 @@ __host__ __device__ inline size_t fuse_bwd_smem_bytes(int KP, int NT) {
     return meta_bytes(kFuseRows) + (size_t)NT * 8 * SN * 4 + (size_t)kFuseRows * SN * 4 + (size_t)2 * kFuseRows * kZS * 4;
 }
 
-template <int NCH, bool DATA>   // DATA = false: weight gradients only (dA and the scatter run in voxel_fuse_bwd_data_tc_kernel)
+template <int NCH>
 __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const FuseArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const vfd_fusion_desc& d = a.d;
@@ -725,7 +725,7 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
         const int64_t* idx = pass ? a.idx_ov : a.idx_no;
         const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
         __syncthreads();
-        if (DATA) {   // natural-layout weight block [out][in], zero padded
+        {   // natural-layout weight block [out][in], zero padded
             const float* w = pass ? a.w_ov : a.w_no;
             const int ld = pass ? 2 * C1 : C1, koff = pass == 2 ? C1 : 0;
             for (int i = threadIdx.x; i < NT * 8 * SN; i += blockDim.x) {
@@ -820,10 +820,6 @@ __global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_kernel(const F
                 dwz += sz;
             }
 
-            if (!DATA) {
-                __syncthreads();
-                continue;
-            }
             // dA [64 x C] = dZ [64 x Cv] W [Cv x C]
             float acca[8][4];
 #pragma unroll
@@ -1132,6 +1128,198 @@ __global__ void __launch_bounds__(kTcThreads, 1) voxel_fuse_bwd_data_tc_kernel(c
     if (warp == kTcEpiWarps) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Backward, weight half (companion of voxel_fuse_bwd_data_tc_kernel):  dW^T += A^T dZ, db += sum dZ over the rows of
+// every pass.  Warp specialised so that the L2 gather and the tensor pipe overlap instead of alternating:
+//   warps 0-7   producers: tile metadata from the corner table, dZ tile split into TF32 hi / lo planes, bilinear
+//               gather of the tile's 32 feature rows -> one of kWtStages shared-memory stages
+//   warps 8-15  consumers: each owns two 16-channel blocks of dW^T (accumulators in registers for the whole pass),
+//               3xTF32 mma.sync over the stage; the relative-depth column and db are SIMT partial sums
+// full / empty mbarriers per stage; the producers run ahead across pass boundaries.  Partials per CTA as in the
+// single-kernel backward (summed in CTA order by voxel_fuse_reduce_kernel).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kWtRows = 32, kWtStages = 3, kWtHalf = kFuseThreads / 2;
+
+__host__ __device__ inline size_t fuse_wt_stage_bytes(int KP) {
+    return meta_bytes(kWtRows) + (size_t)kWtRows * fuse_sn(KP) * 4 + (size_t)2 * kWtRows * kZS * 4;
+}
+__host__ __device__ inline size_t fuse_wt_smem_bytes(int KP) { return kWtStages * fuse_wt_stage_bytes(KP); }
+
+template <int NCH>
+__global__ void __launch_bounds__(kFuseThreads, 1) voxel_fuse_bwd_weight_kernel(const FuseArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint64_t s_full[kWtStages], s_empty[kWtStages];
+    __shared__ float s_part[2][4][64];
+    const vfd_fusion_desc& d = a.d;
+    const int KP = a.KP, SN = fuse_sn(KP), NT = a.NT, C = d.C, C1 = C + 1, Cv = d.Cv;
+    const size_t stage_bytes = fuse_wt_stage_bytes(KP);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int M1 = a.totals[0], M2 = a.totals[1];
+    const int T1 = (M1 + kWtRows - 1) / kWtRows, T2 = (M2 + kWtRows - 1) / kWtRows;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kWtStages; ++s) { mbar_init(&s_full[s], kWtHalf); mbar_init(&s_empty[s], kWtHalf); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t ntile = 0;
+
+    if (warp < kFuseWarps / 2) {
+        // ===================== producers =====================
+        const Group G = {(int)threadIdx.x, kWtHalf, 1};
+        unsigned gmask[2] = {0u, 0u};
+        for (int c = 0; c < d.num_cams; ++c) gmask[d.group[c] ? 1 : 0] |= 1u << c;
+        const size_t rows_total = (size_t)d.B * d.X * d.Y * d.Z;
+        const CornerTable tb = carve_table(const_cast<void*>(a.table), rows_total);
+        for (int pass = 0; pass < 3; ++pass) {
+            const int M = pass ? M2 : M1, T = pass ? T2 : T1;
+            const int64_t* idx = pass ? a.idx_ov : a.idx_no;
+            const unsigned want = pass ? gmask[pass - 1] : 0xffffffffu;
+            int tile = blockIdx.x;
+            TilePf pf = prefetch_tile<kWtRows>(a, tb, rows_total, G, idx, tile * kWtRows, M, want, tile < T);
+            for (; tile < T; tile += gridDim.x, ++ntile) {
+                const uint32_t s = ntile % kWtStages, ph = (ntile / kWtStages) & 1;
+                unsigned char* st = smem_raw + s * stage_bytes;
+                const TileMeta tm = carve_meta<kWtRows>(st);
+                float* sA = reinterpret_cast<float*>(st + meta_bytes(kWtRows));
+                uint32_t* Zhi = reinterpret_cast<uint32_t*>(sA + (size_t)kWtRows * SN);
+                uint32_t* Zlo = Zhi + kWtRows * kZS;
+                mbar_wait(&s_empty[s], ph ^ 1);
+                commit_tile<kWtRows>(tm, G, pf, want, d.num_cams);
+                pf = prefetch_tile<kWtRows>(a, tb, rows_total, G, idx, (tile + (int)gridDim.x) * kWtRows, M, want,
+                                            tile + (int)gridDim.x < T);
+                group_sync(G);
+                for (int i = G.tid; i < kWtRows * (kZS / 4); i += kWtHalf) {
+                    const int r = i / (kZS / 4), q = (i - r * (kZS / 4)) * 4;
+                    const long long row = tm.row[r];
+                    float4 z = f4_zero();
+                    if (row >= 0 && q < Cv) {
+                        const float4 gy = ld_stream_f4(a.d_vol + (size_t)row * Cv + q);
+                        const float4 y = ld_stream_f4(a.vol + (size_t)row * Cv + q);
+                        z.x = y.x > 0.f ? gy.x : 0.1f * gy.x;
+                        z.y = y.y > 0.f ? gy.y : 0.1f * gy.y;
+                        z.z = y.z > 0.f ? gy.z : 0.1f * gy.z;
+                        z.w = y.w > 0.f ? gy.w : 0.1f * gy.w;
+                    }
+                    uint4 hi, lo;
+                    split_tf32(z.x, hi.x, lo.x);
+                    split_tf32(z.y, hi.y, lo.y);
+                    split_tf32(z.z, hi.z, lo.z);
+                    split_tf32(z.w, hi.w, lo.w);
+                    *reinterpret_cast<uint4*>(Zhi + r * kZS + q) = hi;
+                    *reinterpret_cast<uint4*>(Zlo + r * kZS + q) = lo;
+                }
+                constexpr int kPer = kWtRows / (kFuseWarps / 2);     // rows per producer warp
+#pragma unroll
+                for (int rr = 0; rr < kPer; rr += 2)
+                    gather_rows<NCH, kWtRows, 2>(a, tm, warp * kPer + rr, lane, sA + (size_t)(warp * kPer + rr) * SN, SN);
+                mbar_arrive(&s_full[s]);
+            }
+        }
+    } else {
+        // ===================== consumers =====================
+        const int cw = warp - kFuseWarps / 2, ctid = threadIdx.x - kWtHalf, g = lane >> 2, t = lane & 3;
+        const int MT = (C + 15) / 16;
+        const int so = ctid & 63, sp = ctid >> 6;                  // SIMT sums: output so, rows sp*8 .. sp*8+7 of the tile
+        const size_t pstride = (size_t)Cv * (C1 + 1);
+        for (int pass = 0; pass < 3; ++pass) {
+            const int T = pass ? T2 : T1;
+            float accw[2][8][4];
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) accw[b][j][i] = 0.f;
+            float db = 0.f, dwz = 0.f;
+            for (int tile = blockIdx.x; tile < T; tile += gridDim.x, ++ntile) {
+                const uint32_t s = ntile % kWtStages, ph = (ntile / kWtStages) & 1;
+                unsigned char* st = smem_raw + s * stage_bytes;
+                const float* sA = reinterpret_cast<const float*>(st + meta_bytes(kWtRows));
+                const uint32_t* Zhi = reinterpret_cast<const uint32_t*>(sA + (size_t)kWtRows * SN);
+                const uint32_t* Zlo = Zhi + kWtRows * kZS;
+                mbar_wait(&s_full[s], ph);
+                if (cw * 2 < MT) {
+                    const bool two = cw * 2 + 1 < MT;
+                    const float* At = sA + t * SN + cw * 32 + g;
+                    const uint32_t* Bh = Zhi + t * kZS + g;
+                    const uint32_t* Bl = Zlo + t * kZS + g;
+#pragma unroll 1
+                    for (int ks = 0; ks < kWtRows; ks += 8) {
+                        uint32_t ah[2][4], al[2][4];
+#pragma unroll
+                        for (int b = 0; b < 2; ++b) {
+                            if (b == 0 || two) {
+                                split_tf32(At[ks * SN + b * 16], ah[b][0], al[b][0]);
+                                split_tf32(At[ks * SN + b * 16 + 8], ah[b][1], al[b][1]);
+                                split_tf32(At[(ks + 4) * SN + b * 16], ah[b][2], al[b][2]);
+                                split_tf32(At[(ks + 4) * SN + b * 16 + 8], ah[b][3], al[b][3]);
+                            }
+                        }
+#pragma unroll
+                        for (int jg = 0; jg < 8; jg += 4) {
+                            if (jg < NT) {
+                                uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    bh0[j] = Bh[ks * kZS + (jg + j) * 8];
+                                    bh1[j] = Bh[(ks + 4) * kZS + (jg + j) * 8];
+                                    bl0[j] = Bl[ks * kZS + (jg + j) * 8];
+                                    bl1[j] = Bl[(ks + 4) * kZS + (jg + j) * 8];
+                                }
+#pragma unroll
+                                for (int b = 0; b < 2; ++b) {
+                                    if (b == 0 || two) {
+#pragma unroll
+                                        for (int j = 0; j < 4; ++j) mma_tf32(accw[b][jg + j], al[b], bh0[j], bh1[j]);
+#pragma unroll
+                                        for (int j = 0; j < 4; ++j) mma_tf32(accw[b][jg + j], ah[b], bl0[j], bl1[j]);
+#pragma unroll
+                                        for (int j = 0; j < 4; ++j) mma_tf32(accw[b][jg + j], ah[b], bh0[j], bh1[j]);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                if (so < Cv) {
+#pragma unroll
+                    for (int r = sp * 8; r < sp * 8 + 8; ++r) {
+                        const float z = __uint_as_float(Zhi[r * kZS + so]) + __uint_as_float(Zlo[r * kZS + so]);
+                        db += z;
+                        dwz = fmaf(z, sA[r * SN + C], dwz);
+                    }
+                }
+                mbar_arrive(&s_empty[s]);
+            }
+            // flush this pass' partials: partial[cta][pass][out][in], then [out] bias
+            float* P = a.partial + ((size_t)blockIdx.x * 3 + pass) * pstride;
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                if (cw * 2 + b < MT) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (j < NT) {
+                            const int in0 = (cw * 2 + b) * 16 + g, o0 = j * 8 + 2 * t;
+                            if (o0 < Cv) {
+                                if (in0 < C) { P[(size_t)o0 * C1 + in0] = accw[b][j][0]; P[(size_t)(o0 + 1) * C1 + in0] = accw[b][j][1]; }
+                                if (in0 + 8 < C) { P[(size_t)o0 * C1 + in0 + 8] = accw[b][j][2]; P[(size_t)(o0 + 1) * C1 + in0 + 8] = accw[b][j][3]; }
+                            }
+                        }
+                    }
+                }
+            }
+            s_part[0][sp][so] = db;
+            s_part[1][sp][so] = dwz;
+            asm volatile("bar.sync 2, %0;" ::"n"(kWtHalf) : "memory");
+            if (sp == 0 && so < Cv) {
+                P[(size_t)so * C1 + C] = (s_part[1][0][so] + s_part[1][1][so]) + (s_part[1][2][so] + s_part[1][3][so]);
+                P[(size_t)Cv * C1 + so] = (s_part[0][0][so] + s_part[0][1][so]) + (s_part[0][2][so] + s_part[0][3][so]);
+            }
+            asm volatile("bar.sync 2, %0;" ::"n"(kWtHalf) : "memory");
+        }
+    }
+}
+
 // sum the per-CTA partials in CTA order -> d_w_no [Cv][C1], d_b_no, d_w_ov [Cv][2 C1], d_b_ov
 __global__ void voxel_fuse_reduce_kernel(const float* partial, int ctas, int Cv, int C1, float* d_w_no, float* d_b_no,
                                          float* d_w_ov, float* d_b_ov) {
@@ -1267,11 +1455,12 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
                                  (int)smem_tc) != cudaSuccess)
             return VFD_ERR_CUDA;
         voxel_fuse_bwd_data_tc_kernel<<<sms, kTcThreads, smem_tc, st>>>(a);
-        rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2, false>, a, smem, sms, st)
-                        : launch_fuse(voxel_fuse_bwd_kernel<1, false>, a, smem, sms, st);
+        const size_t smem_wt = fuse_wt_smem_bytes(a.KP);
+        rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_weight_kernel<2>, a, smem_wt, sms, st)
+                        : launch_fuse(voxel_fuse_bwd_weight_kernel<1>, a, smem_wt, sms, st);
     } else {
-        rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2, true>, a, smem, sms, st)
-                        : launch_fuse(voxel_fuse_bwd_kernel<1, true>, a, smem, sms, st);
+        rc = d->C > 128 ? launch_fuse(voxel_fuse_bwd_kernel<2>, a, smem, sms, st)
+                        : launch_fuse(voxel_fuse_bwd_kernel<1>, a, smem, sms, st);
     }
     if (rc) return rc;
     const int total = 3 * d->Cv * (d->C + 2);

@@ -22,7 +22,7 @@ struct LossFwdArgs {
 
 extern __shared__ __align__(16) float vfd_warp_smem[];
 
-__global__ void __launch_bounds__(kTileThreads) warp_loss_fwd_kernel(const LossFwdArgs a) {
+__global__ void __launch_bounds__(kTileThreads, 3) warp_loss_fwd_kernel(const LossFwdArgs a) {
     using Rg = Region<1>;
     const vfd_warp_desc& d = a.d;
     __shared__ WarpCtx ctx;
