@@ -1,5 +1,6 @@
-"""Read an .ncu-rep (ncu --set full) and write a per-kernel summary CSV + profiles/traffic.json (DRAM bytes per launch,
-keyed by the C-ABI entry point that launches the kernel; bench.py reports it as roofline.traffic)."""
+"""Read an .ncu-rep (ncu --set full) and write a per-kernel summary CSV + profiles/traffic.json (DRAM bytes per ABI call = the
+kernels that call launches, summed; bench.py reports it as roofline.traffic).
+    python tools/summarize_ncu.py gpurun_out/prof_step.ncu-rep profiles/rNN_ncu_full_summary.csv profiles/traffic.json [steps]"""
 import csv
 import io
 import json
@@ -11,15 +12,21 @@ KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'launch__registers_per_thread', 'smsp__issue_active.avg.pct_of_peak_sustained_active',
         'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active', 'l1tex__t_sector_hit_rate.pct',
         'lts__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed']
-ABI = {'voxel_fuse_fwd_kernel': 'vfd_voxel_fuse_fwd', 'voxel_fuse_bwd_kernel': 'vfd_voxel_fuse_bwd',
-       'ray_sample_fwd_vec_kernel': 'vfd_ray_sample_fwd', 'ray_sample_bwd_vec_kernel': 'vfd_ray_sample_bwd',
-       'warp_stats_kernel': 'vfd_warp_stats', 'warp_loss_fwd_kernel': 'vfd_warp_loss_fwd',
-       'warp_loss_bwd_kernel': 'vfd_warp_loss_bwd', 'voxel_count_kernel': 'vfd_voxel_classify', 'smooth_loss_kernel': 'vfd_smooth_loss_fwd',
-       'voxel_gather_fwd_kernel': 'vfd_voxel_gather_depth_fwd', 'voxel_gather_bwd_kernel': 'vfd_voxel_gather_depth_bwd'}
+# kernel-name fragment -> C-ABI entry point that launches it (first match wins)
+ABI = [('voxel_fuse_fwd', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_bwd', 'vfd_voxel_fuse_bwd'),
+       ('voxel_fuse_reduce', 'vfd_voxel_fuse_bwd'), ('ray_sample_fwd', 'vfd_ray_sample_fwd'),
+       ('ray_sample_bwd', 'vfd_ray_sample_bwd'), ('warp_stats', 'vfd_warp_stats'),
+       ('warp_loss_fwd', 'vfd_warp_loss_fwd'), ('warp_loss_bwd', 'vfd_warp_loss_bwd'),
+       ('warp_dT_reduce', 'vfd_warp_loss_bwd'), ('voxel_count', 'vfd_voxel_classify'),
+       ('voxel_scan', 'vfd_voxel_classify'), ('voxel_slot', 'vfd_voxel_classify'),
+       ('smooth_mean', 'vfd_smooth_loss_fwd'), ('smooth_loss_kernel', 'vfd_smooth_loss_fwd'),
+       ('smooth_bwd', 'vfd_smooth_loss_bwd'), ('voxel_gather_fwd', 'vfd_voxel_gather_depth_fwd'),
+       ('voxel_gather_bwd', 'vfd_voxel_gather_depth_bwd')]
 UNIT = {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}
 
 
-def main(rep, out_csv, out_json):
+def main(rep, out_csv, out_json, steps=1):
+    steps = int(steps)
     raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
@@ -32,15 +39,18 @@ def main(rep, out_csv, out_json):
         w.writerow([''] + [units[col[k]] for k in KEYS])
         for r in rows[2:]:
             w.writerow([r[name_i]] + [r[col[k]] for k in KEYS])
-            for frag, abi in ABI.items():
+            for frag, abi in ABI:
                 if frag in r[name_i]:
                     b = sum(float(r[col[k]].replace(',', '')) * UNIT[units[col[k]]]
                             for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
                     traffic.setdefault(abi, []).append(b)
+                    break
+    # the capture covers `steps` steps (default 1): DRAM bytes of all kernels one ABI call launches, per call
     with open(out_json, 'w') as f:
-        json.dump({k: sum(v) / len(v) for k, v in traffic.items()}, f, indent=1, sort_keys=True)
+        json.dump({k: sum(v) / steps for k, v in traffic.items()}, f, indent=1, sort_keys=True)
+    print({k: len(v) for k, v in traffic.items()})
     print(open(out_csv).read())
 
 
 if __name__ == '__main__':
-    main(*sys.argv[1:4])
+    main(*sys.argv[1:5])
