@@ -29,6 +29,10 @@ class WarpWorkload:
 
     def step(self, inputs, depth, disp, noise, T):
         n = self.cfg['data']['num_cams']
+        if noise is None:
+            # tie-break noise of the identity-reprojection loss: drawn on the device, inside the step (the reference
+            # draws it on the CPU and ships it, single_cam_loss.py:45-46; same distribution, no PCIe traffic)
+            noise = torch.randn((self.B, n, len(self.frames) - 1, self.H, self.W), device=self.dev)
         depths = [depth[:, c:c + 1].detach().requires_grad_(True) for c in range(n)]
         Ts = {f: t.detach().requires_grad_(True) for f, t in T.items()}
         total, _ = view.warp_and_loss(self.cfg, inputs, depths, [disp[:, c:c + 1] for c in range(n)], Ts,
@@ -44,7 +48,7 @@ class WarpWorkload:
         nb = dict(non_blocking=True)
         inputs = {k: v.to(self.dev, **nb) for k, v in self.h_inputs.items()}
         return (inputs, self.h_depth.to(self.dev, **nb), self.h_disp.to(self.dev, **nb),
-                self.h_noise.to(self.dev, **nb), {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
+                None, {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
 
     def compute(self, staged):
         return self.step(*staged)
@@ -55,7 +59,7 @@ class WarpWorkload:
         self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
 
     def h2d_bytes(self):
-        ts = list(self.h_inputs.values()) + [self.h_depth, self.h_disp, self.h_noise] + list(self.h_T.values())
+        ts = list(self.h_inputs.values()) + [self.h_depth, self.h_disp] + list(self.h_T.values())
         return sum(t.numel() * t.element_size() for t in ts)
 
     def d2h_bytes(self):

@@ -310,8 +310,9 @@ class MultiCamLoss(torch.nn.Module):
         tv = outputs[('cam', cam)]
         c = tv[_CTX]
         wi = c['wi']
-        # the reference draws the tie-break noise on the CPU and ships it (single_cam_loss.py:45-46)
-        noise = torch.randn((wi.B, wi.n_src, wi.H, wi.W)).to(wi.device).unsqueeze(1)
+        # tie-break noise: the reference draws it on the CPU and ships it (single_cam_loss.py:45-46); here it is drawn on
+        # the device (same distribution; parity tests pass their own noise through warp_and_loss)
+        noise = torch.randn((wi.B, 1, wi.n_src, wi.H, wi.W), device=wi.device)
         num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['stats'], ('reproj_loss', 'reproj_mask'))
         tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
         tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
