@@ -33,11 +33,10 @@ class WarpWorkload:
             # tie-break noise of the identity-reprojection loss: drawn on the device, inside the step (the reference
             # draws it on the CPU and ships it, single_cam_loss.py:45-46; same distribution, no PCIe traffic)
             noise = torch.randn((self.B, n, len(self.frames) - 1, self.H, self.W), device=self.dev)
-        depths = [depth[:, c:c + 1].detach().requires_grad_(True) for c in range(n)]
+        depth = depth.detach().requires_grad_(True)          # all cameras stacked: [B,6,H,W]
         Ts = {f: t.detach().requires_grad_(True) for f, t in T.items()}
-        total, _ = view.warp_and_loss(self.cfg, inputs, depths, [disp[:, c:c + 1] for c in range(n)], Ts,
-                                      [noise[:, c] for c in range(n)])
-        grads = torch.autograd.grad(total, depths + list(Ts.values()))
+        total, _ = view.warp_and_loss(self.cfg, inputs, depth, disp, Ts, noise)
+        grads = torch.autograd.grad(total, [depth] + list(Ts.values()))
         return total, grads
 
     def step_resident(self):
@@ -55,7 +54,7 @@ class WarpWorkload:
 
     def download(self, result):
         total, grads = result
-        self.h_out.copy_(torch.cat(grads[:6], 1), non_blocking=True)
+        self.h_out.copy_(grads[0], non_blocking=True)
         self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
 
     def h2d_bytes(self):

@@ -225,15 +225,16 @@ def combine_losses(cfg, num, den, smooth):
 def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises, want_views=()):
     """The view-synthesis half of a training step for a whole rig batch in three launches
     (models/vfdepth.py:290-313: loop over cameras, mean over cameras).
-    depths / disps / noises: list over cameras of [B,1,H,W] / [B,1,H,W] / [B,n_src,H,W]; cam_T_cam {f: [B,cams,4,4]}.
+    depths / disps / noises: list over cameras of [B,1,H,W] / [B,1,H,W] / [B,n_src,H,W] (the reference's per-camera
+    outputs), or the already stacked [B,cams,H,W] / [B,cams,H,W] / [B,cams,n_src,H,W]; cam_T_cam {f: [B,cams,4,4]}.
     -> (total loss, dict(terms [cams,3], cam_loss [cams], views))."""
     wi = WarpInputs(cfg, inputs)
-    depth = torch.cat(depths, 1)
-    noise = torch.stack(noises, 1)
+    depth = depths if torch.is_tensor(depths) else torch.cat(depths, 1)
+    noise = noises if torch.is_tensor(noises) else torch.stack(noises, 1)
     T = rig_transforms(wi, inputs, cam_T_cam)
     num, den, views = warp_loss_sums(wi, depth, T, noise, 0, None, want_views)
     color0 = inputs[('color', 0, 0)]
-    sm = smooth_loss(color0, torch.cat(disps, 1))
+    sm = smooth_loss(color0, disps if torch.is_tensor(disps) else torch.cat(disps, 1))
     cam_loss, terms = combine_losses(cfg, num, den, sm)
     return cam_loss.sum() / wi.num_cams, dict(terms=terms, cam_loss=cam_loss, smooth=sm, views=views, T=T)
 
@@ -310,9 +311,9 @@ class MultiCamLoss(torch.nn.Module):
         tv = outputs[('cam', cam)]
         c = tv[_CTX]
         wi = c['wi']
-        # tie-break noise: the reference draws it on the CPU and ships it (single_cam_loss.py:45-46); here it is drawn on
-        # the device (same distribution; parity tests pass their own noise through warp_and_loss)
-        noise = torch.randn((wi.B, 1, wi.n_src, wi.H, wi.W), device=wi.device)
+        # the reference draws the tie-break noise on the CPU and ships it (single_cam_loss.py:45-46); the drop-in does the
+        # same so that a seeded run replays the reference's random stream (warp_and_loss takes device noise directly)
+        noise = torch.randn((wi.B, wi.n_src, wi.H, wi.W)).to(wi.device).unsqueeze(1)
         num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['stats'], ('reproj_loss', 'reproj_mask'))
         tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
         tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
