@@ -32,7 +32,7 @@ UNIT = 'rigs/s'
 BATCH = 8                 # rigs per GPU per step (configs[1])
 WORKLOAD = ('configs[1]: VFNet fusion fwd+bwd (voxel gather + 1x1 MLPs + ray sampling, no reduce_dim)%s, %d DDAD-shaped '
             'rigs (6x384x640) per GPU per step')
-WARP_PART = ' + configs[2]: 6-cam x 3-frame view-synthesis warp + SSIM/L1 photometric loss fwd+bwd'
+WARP_PART = ' + configs[2]: to_depth + 6-cam x 3-frame view-synthesis warp + SSIM/L1 photometric + smoothness loss fwd+bwd (to disparity and poses)'
 DATASET = 'ddad'
 
 
@@ -247,10 +247,11 @@ def cpu_step_pass(steps, warmup, seed=1234, with_warp=True):
         proj = orc.project_voxel_into_image(cfg, vox, inputs[('inv_K', lvl)], inputs['extrinsics'])
         torch.autograd.backward(proj, [g_up] * len(proj))
         if with_warp:
-            depths = [d.clone().requires_grad_(True) for d in extras['depth']]
+            disps = [d.clone().requires_grad_(True) for d in extras['disp']]
+            depths = [orc.to_depth(cfg, d, inputs[('K', 0)][:, c]) for c, d in enumerate(disps)]
             Ts = {k: v.clone().requires_grad_(True) for k, v in extras['cam_T_cam'].items()}
-            total, _ = orc.warp_and_loss(cfg, inputs, depths, extras['disp'], Ts, extras['noise'])
-            torch.autograd.grad(total, depths + list(Ts.values()))
+            total, _ = orc.warp_and_loss(cfg, inputs, depths, disps, Ts, extras['noise'])
+            torch.autograd.grad(total, disps + list(Ts.values()))
         return f.grad
 
     for _ in range(warmup):

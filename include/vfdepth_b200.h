@@ -244,6 +244,18 @@ int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* color, const
 int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* color, const float* disp, const double* img_sum,
                         const float* d_smooth, double* gdot, float* d_disp, void* stream);
 
+/* --------------------------------------------------------------------------------------------------
+ * Disparity -> metric depth (models/vfdepth.py:277-288 to_depth, called per camera and scale at :266-275), all cameras
+ * of the batch at once:
+ *   d = bilinear upsample (align_corners=False) of disp [B,cams,hs,ws] to [H,W]  (identity when hs==H, ws==W)
+ *   depth [B,cams,H,W] = (1 / (1/max_depth + (1/min_depth - 1/max_depth) * d)) * K[b,c,0,0] / focal_length_scale
+ *   K [B,cams,4,4] = inputs['K', 0]. */
+int vfd_to_depth_fwd(int B, int cams, int hs, int ws, int H, int W, const float* disp, const float* K, float min_depth,
+                     float max_depth, float focal_length_scale, float* depth, void* stream);
+/* backward w.r.t. disp: d_depth [B,cams,H,W] -> d_disp [B,cams,hs,ws] (zero-filled here when it is accumulated). */
+int vfd_to_depth_bwd(int B, int cams, int hs, int ws, int H, int W, const float* disp, const float* K, float min_depth,
+                     float max_depth, float focal_length_scale, const float* d_depth, float* d_disp, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

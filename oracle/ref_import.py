@@ -83,3 +83,32 @@ def load():
     _loaded.update(VFNet=vf.VFNet, Projection=geo.Projection, ViewRendering=vr.ViewRendering, Pose=pose.Pose,
                    loss_util=lu, MultiCamLoss=mcl.MultiCamLoss)
     return types.SimpleNamespace(**_loaded)
+
+
+def load_algo():
+    """-> the reference's ``VFDepthAlgo`` class (models/vfdepth.py), for its stateless helper methods such as
+    ``to_depth`` (:277-288).  ``dataset`` (packnet-sfm stack, absent) is stubbed; the class is never constructed --
+    methods are called unbound on a ``types.SimpleNamespace`` carrying the config attributes they read."""
+    if 'VFDepthAlgo' in _loaded:
+        return _loaded['VFDepthAlgo']
+    ref = load()
+
+    def _unused(*a, **k):
+        raise NotImplementedError('stubbed third-party symbol')
+
+    if 'dataset' not in sys.modules:
+        _stub('dataset', construct_dataset=_unused)
+    cwd = os.getcwd()
+    os.chdir(REF_ROOT)
+    try:
+        importlib.import_module('network')
+        geo_pkg, loss_pkg = sys.modules['models.geometry'], sys.modules['models.losses']
+        geo_pkg.Pose, geo_pkg.ViewRendering = ref.Pose, ref.ViewRendering
+        loss_pkg.MultiCamLoss = ref.MultiCamLoss
+        loss_pkg.SingleCamLoss = importlib.import_module('models.losses.single_cam_loss').SingleCamLoss
+        loss_pkg.DepthSynLoss = importlib.import_module('models.losses.depth_synthesis_loss').DepthSynLoss
+        algo = importlib.import_module('models.vfdepth').VFDepthAlgo
+    finally:
+        os.chdir(cwd)
+    _loaded['VFDepthAlgo'] = algo
+    return algo

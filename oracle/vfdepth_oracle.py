@@ -435,3 +435,15 @@ def warp_and_loss(cfg, inputs, depths, disps, cam_T_cam, noises, decisions=None)
         details.append(det)
         total = total + loss
     return total / cfg['data']['num_cams'], details
+
+
+def to_depth(cfg, disp_in, K_in):
+    """models/vfdepth.py:277-288 (VFDepthAlgo.to_depth): disp [B,1,hs,ws] of one camera, K [B,4,4] -> depth [B,1,H,W]."""
+    t = cfg['training']
+    min_disp = 1 / t['max_depth']
+    max_disp = 1 / t['min_depth']
+    disp_range = max_disp - min_disp
+    disp_in = F.interpolate(disp_in, [t['height'], t['width']], mode='bilinear', align_corners=False)
+    disp = min_disp + disp_range * disp_in
+    depth = 1 / disp
+    return depth * K_in[:, 0:1, 0:1].unsqueeze(2) / t['focal_length_scale']

@@ -2,7 +2,8 @@
 
     python tests/golden/make_golden.py            # needs /root/reference (or $VFDEPTH_REF)
 
-Writes ``golden_fusion.npz`` and ``golden_warp.npz`` next to this file.  The
+Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz`` next to this file
+(``--only-to-depth`` regenerates just the last one).  The
 fixtures hold the seeded inputs and what the reference's own classes
 (``VFNet``, ``ViewRendering``, ``Pose``, ``MultiCamLoss``) returned for them, at
 sizes small enough to commit.  ``tests/test_oracle_golden.py`` then pins
@@ -142,7 +143,34 @@ def make_warp(ref, path):
     print('wrote', path, 'total loss', float(total))
 
 
+def make_to_depth(path):
+    """VFDepthAlgo.to_depth (models/vfdepth.py:277-288) called unbound on a namespace with the attributes it reads,
+    per camera as vfdepth.py:266-275 does, for decoder outputs of scale 0, 1 and 2; gradients for a seeded upstream."""
+    import types
+    algo = ref_import.load_algo()
+    cfg = warp_cfg()
+    t = cfg['training']
+    inputs, _ = make_rig(cfg, seed=777, with_feats=False)
+    K = inputs[('K', 0)]
+    B, H, W = t['batch_size'], t['height'], t['width']
+    ns = types.SimpleNamespace(max_depth=t['max_depth'], min_depth=t['min_depth'], height=H, width=W,
+                               focal_length_scale=t['focal_length_scale'])
+    gen = torch.Generator().manual_seed(31)
+    out = {'K': _np(K)}
+    for s in (0, 1, 2):
+        disp = torch.rand((B, 6, H >> s, W >> s), generator=gen).requires_grad_(True)
+        depth = torch.cat([algo.to_depth(ns, disp[:, c:c + 1], K[:, c]) for c in range(6)], 1)
+        g_up = torch.randn(depth.shape, generator=gen)
+        (d_disp,) = torch.autograd.grad((depth * g_up).sum(), disp)
+        out.update({'disp_%d' % s: _np(disp), 'depth_%d' % s: _np(depth), 'g_up_%d' % s: _np(g_up),
+                    'd_disp_%d' % s: _np(d_disp)})
+    np.savez_compressed(path, **out)
+    print('wrote', path)
+
+
 if __name__ == '__main__':
     ref = ref_import.load()
-    make_fusion(ref, os.path.join(HERE, 'golden_fusion.npz'))
-    make_warp(ref, os.path.join(HERE, 'golden_warp.npz'))
+    if '--only-to-depth' not in sys.argv:
+        make_fusion(ref, os.path.join(HERE, 'golden_fusion.npz'))
+        make_warp(ref, os.path.join(HERE, 'golden_warp.npz'))
+    make_to_depth(os.path.join(HERE, 'golden_to_depth.npz'))

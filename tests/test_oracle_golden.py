@@ -67,3 +67,15 @@ def test_warp_loss_bit_exact():
     assert torch.equal(torch.stack(grads[:6], 1), g['d_depth'])
     assert torch.allclose(grads[6], g['d_T_m1'], rtol=1e-6, atol=1e-9)
     assert torch.allclose(grads[7], g['d_T_p1'], rtol=1e-6, atol=1e-9)
+
+
+def test_to_depth_bit_exact():
+    """oracle.to_depth against VFDepthAlgo.to_depth itself (models/vfdepth.py:277-288) at scales 0, 1, 2."""
+    g = H.load_npz('golden_to_depth.npz')
+    cfg = H.warp_cfg()
+    for s in (0, 1, 2):
+        disp = g['disp_%d' % s].clone().requires_grad_(True)
+        depth = torch.cat([orc.to_depth(cfg, disp[:, c:c + 1], g['K'][:, c]) for c in range(6)], 1)
+        assert torch.equal(depth, g['depth_%d' % s]), s
+        d_disp, = torch.autograd.grad((depth * g['g_up_%d' % s]).sum(), disp)
+        assert torch.equal(d_disp, g['d_disp_%d' % s]), s

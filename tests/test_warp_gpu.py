@@ -328,3 +328,44 @@ def test_smooth_loss_matches_oracle(B, n, Hh, W):
     g_got, = torch.autograd.grad((got * up.to(dev)).sum(), d_got)
     assert H.rel_err(got.detach().cpu(), ref.detach()) < 1e-4
     assert H.rel_err(g_got.cpu(), g_ref) < 1e-4
+
+
+@pytest.mark.parametrize('scale', [0, 1, 2])
+def test_to_depth_matches_reference_golden(scale):
+    """vfd_to_depth_fwd / _bwd against the fixture produced by the reference's own VFDepthAlgo.to_depth
+    (models/vfdepth.py:277-288): depth within 1e-6 relative per element (the division chain is correctly rounded, the
+    bilinear weights are formed as ATen forms them), d_disp within 1e-5 of its scale (atomics change the order)."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    g = H.load_npz('golden_to_depth.npz')
+    cfg = H.warp_cfg()
+    disp = g['disp_%d' % scale].to(dev).requires_grad_(True)
+    depth = view.to_depth(cfg, disp, g['K'].to(dev))
+    ref = g['depth_%d' % scale]
+    assert depth.shape == ref.shape
+    assert float(((depth.detach().cpu() - ref).abs() / ref.abs()).max()) < 1e-6
+    if scale == 0:
+        assert torch.equal(depth.detach().cpu(), ref)
+    d_disp, = torch.autograd.grad((depth * g['g_up_%d' % scale].to(dev)).sum(), disp)
+    assert H.rel_err(d_disp.cpu(), g['d_disp_%d' % scale]) < 1e-5
+
+
+def test_to_depth_ragged_sizes_match_oracle():
+    """odd sizes / non-integer upsampling ratios / a single camera against the oracle restatement."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    cfg = vcfg.default_config('ddad', batch_size=1, training__height=37, training__width=53)
+    gen = torch.Generator().manual_seed(5)
+    for hs, ws in ((37, 53), (19, 27), (5, 53)):
+        disp = torch.rand((1, 1, hs, ws), generator=gen)
+        K = torch.eye(4).reshape(1, 1, 4, 4).clone()
+        K[..., 0, 0] = 411.7
+        up = torch.randn((1, 1, 37, 53), generator=gen)
+        d_ref = disp.clone().requires_grad_(True)
+        ref = orc.to_depth(cfg, d_ref, K[:, 0])
+        g_ref, = torch.autograd.grad((ref * up).sum(), d_ref)
+        d_got = disp.to(dev).requires_grad_(True)
+        got = view.to_depth(cfg, d_got, K.to(dev))
+        g_got, = torch.autograd.grad((got * up.to(dev)).sum(), d_got)
+        assert float(((got.detach().cpu() - ref.detach()).abs() / ref.detach().abs()).max()) < 1e-6
+        assert H.rel_err(g_got.cpu(), g_ref) < 1e-5

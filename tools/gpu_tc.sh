@@ -1,10 +1,9 @@
 mkdir -p gpurun_out
-for e in 0 1 2; do
-VFD_EXP=$e timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:voxel_fuse_bwd --csv --log-file gpurun_out/tc_launches_$e.csv python tools/kernel_bench.py --only fuse_bwd --iters 2 > gpurun_out/tc_ncu.log 2>&1
-python - <<PY
-import csv
-rows=[r for r in csv.reader(open('gpurun_out/tc_launches_$e.csv')) if len(r)>5]
-h=rows[0]; ki=h.index('Kernel Name'); vi=h.index('Metric Value')
-for r in rows[1:][-2:]: print('exp $e', r[ki][:60], r[vi])
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest_gpu rc=$?"; tail -5 gpurun_out/pytest_gpu.log
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench.log 2>&1; echo "bench rc=$?"; tail -3 gpurun_out/bench.log | cut -c1-300
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench.log').read().strip().splitlines()[-1])
+print('value',d['value'],'ms',d['ms_per_step'],'e2e',d['e2e'], 'glue', d['config'].get('torch_glue_ms_per_step'), 'launches', d['gpu_launches'])
+for k,v in d['kernels'].items(): print('%-24s %.3f ms'%(k,v['ms_per_step']))
 PY
-done

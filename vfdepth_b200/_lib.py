@@ -54,7 +54,10 @@ class WarpViews(ctypes.Structure):
 
 _lock = threading.Lock()
 _lib = None
-launches = 0   # number of kernel-launching ABI calls made by this process (bench.py reports it)
+launches = 0   # number of kernels launched through the ABI by this process (bench.py reports it)
+# kernels one call of each entry point launches (memsets not counted); anything not listed launches one
+KERNELS_PER_CALL = {'vfd_voxel_classify': 3, 'vfd_voxel_fuse_bwd': 3, 'vfd_warp_stats': 2, 'vfd_warp_loss_bwd': 2,
+                    'vfd_smooth_loss_fwd': 2, 'vfd_smooth_loss_bwd': 2}
 
 
 def load():
@@ -111,7 +114,7 @@ def stop_event_trace():
 def call(name, *args):
     global launches
     fn = getattr(load(), name)
-    launches += 1
+    launches += KERNELS_PER_CALL.get(name, 1)
     if _events is None:
         check(fn(*args), name)
         return

@@ -1,5 +1,6 @@
-"""Workload of bench.py's view-synthesis half: 6 cameras x 3 frames warp + SSIM/L1 photometric loss, forward and
-backward to the 6 depth maps and the 12 cam_T_cam (BASELINE.json configs[2]), on synthetic DDAD-shaped rigs."""
+"""Workload of bench.py's view-synthesis half: decoder disparity -> depth (to_depth), 6 cameras x 3 frames warp +
+SSIM/L1 photometric loss + edge-aware smoothness, forward and backward to the 6 disparity maps (through the depth maps)
+and the 12 cam_T_cam (BASELINE.json configs[2]), on synthetic DDAD-shaped rigs."""
 import torch
 
 from . import config as vcfg
@@ -17,37 +18,36 @@ class WarpWorkload:
         pin = lambda x: x.contiguous().pin_memory()
         keys = [('color', f, 0) for f in self.frames] + ['mask', ('K', 0), ('inv_K', 0), 'extrinsics', 'extrinsics_inv']
         self.h_inputs = {k: pin(inputs[k]) for k in keys}
-        self.h_depth = pin(torch.cat(ex['depth'], 1))                 # [B,6,H,W]
-        self.h_disp = pin(torch.cat(ex['disp'], 1))
+        self.h_disp = pin(torch.cat(ex['disp'], 1))                   # [B,6,H,W] decoder output of scale 0
         self.h_noise = pin(torch.stack(ex['noise'], 1))               # [B,6,2,H,W]
         self.h_T = {f: pin(ex['cam_T_cam'][f]) for f in self.frames[1:]}
         self.h_out = torch.empty((batch, 6, self.H, self.W)).pin_memory()
         self.h_loss = torch.zeros(1).pin_memory()
         self.inputs = {k: v.to(dev) for k, v in self.h_inputs.items()}
-        self.depth, self.disp, self.noise = self.h_depth.to(dev), self.h_disp.to(dev), self.h_noise.to(dev)
+        self.disp, self.noise = self.h_disp.to(dev), self.h_noise.to(dev)
         self.T = {f: v.to(dev) for f, v in self.h_T.items()}
 
-    def step(self, inputs, depth, disp, noise, T):
+    def step(self, inputs, disp, noise, T):
         n = self.cfg['data']['num_cams']
         if noise is None:
             # tie-break noise of the identity-reprojection loss: drawn on the device, inside the step (the reference
             # draws it on the CPU and ships it, single_cam_loss.py:45-46; same distribution, no PCIe traffic)
             noise = torch.randn((self.B, n, len(self.frames) - 1, self.H, self.W), device=self.dev)
-        depth = depth.detach().requires_grad_(True)          # all cameras stacked: [B,6,H,W]
+        disp = disp.detach().requires_grad_(True)            # all cameras stacked: [B,6,H,W]
         Ts = {f: t.detach().requires_grad_(True) for f, t in T.items()}
+        depth = view.to_depth(self.cfg, disp, inputs[('K', 0)])          # models/vfdepth.py:266-275
         total, _ = view.warp_and_loss(self.cfg, inputs, depth, disp, Ts, noise)
-        grads = torch.autograd.grad(total, [depth] + list(Ts.values()))
+        grads = torch.autograd.grad(total, [disp] + list(Ts.values()))
         return total, grads
 
     def step_resident(self):
-        return self.step(self.inputs, self.depth, self.disp, self.noise, self.T)
+        return self.step(self.inputs, self.disp, self.noise, self.T)
 
     def upload(self):
         """host (pinned) -> device copies of one step's inputs, on the current stream."""
         nb = dict(non_blocking=True)
         inputs = {k: v.to(self.dev, **nb) for k, v in self.h_inputs.items()}
-        return (inputs, self.h_depth.to(self.dev, **nb), self.h_disp.to(self.dev, **nb),
-                None, {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
+        return (inputs, self.h_disp.to(self.dev, **nb), None, {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
 
     def compute(self, staged):
         return self.step(*staged)
@@ -58,7 +58,7 @@ class WarpWorkload:
         self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
 
     def h2d_bytes(self):
-        ts = list(self.h_inputs.values()) + [self.h_depth, self.h_disp] + list(self.h_T.values())
+        ts = list(self.h_inputs.values()) + [self.h_disp] + list(self.h_T.values())
         return sum(t.numel() * t.element_size() for t in ts)
 
     def d2h_bytes(self):
@@ -70,4 +70,5 @@ class WarpWorkload:
         imgs, depth, mask, noise = 3 * 3 * px, px, px, 2 * px
         return {'vfd_warp_stats': imgs + depth + mask, 'vfd_warp_loss_fwd': imgs + depth + mask + noise,
                 'vfd_warp_loss_bwd': imgs + depth + mask + noise + px,
-                'vfd_smooth_loss_fwd': 3 * px + px}
+                'vfd_smooth_loss_fwd': 3 * px + px, 'vfd_smooth_loss_bwd': 3 * px + 2 * px,
+                'vfd_to_depth_fwd': 2 * px, 'vfd_to_depth_bwd': 3 * px}

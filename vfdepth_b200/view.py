@@ -213,6 +213,40 @@ def smooth_loss(color, disp):
     return _SmoothLoss.apply(color.contiguous(), disp.contiguous())
 
 
+class _ToDepth(torch.autograd.Function):
+    """vfd_to_depth_fwd / _bwd: decoder output -> metric depth for every camera of the batch, gradient to disp."""
+
+    @staticmethod
+    def forward(ctx, disp, K, min_depth, max_depth, focal, H, W):
+        B, n, hs, ws = disp.shape
+        _chk(disp, 'disp', (B, n, hs, ws))
+        _chk(K, 'K', (B, n, 4, 4))
+        depth = torch.empty((B, n, H, W), device=disp.device)
+        ctx.args = (B, n, hs, ws, H, W, ctypes.c_float(min_depth), ctypes.c_float(max_depth), ctypes.c_float(focal))
+        B, n, hs, ws, H, W, lo, hi, fs = ctx.args
+        _lib.call('vfd_to_depth_fwd', B, n, hs, ws, H, W, _lib.ptr(disp), _lib.ptr(K), lo, hi, fs, _lib.ptr(depth),
+                  _stream())
+        ctx.save_for_backward(disp, K)
+        return depth
+
+    @staticmethod
+    def backward(ctx, d_depth):
+        disp, K = ctx.saved_tensors
+        B, n, hs, ws, H, W, lo, hi, fs = ctx.args
+        d_disp = torch.empty_like(disp)
+        _lib.call('vfd_to_depth_bwd', B, n, hs, ws, H, W, _lib.ptr(disp), _lib.ptr(K), lo, hi, fs,
+                  _lib.ptr(d_depth.contiguous()), _lib.ptr(d_disp), _stream())
+        return d_disp, None, None, None, None, None, None
+
+
+def to_depth(cfg, disp, K):
+    """models/vfdepth.py:277-288 for all cameras at once.
+    disp [B,cams,hs,ws] (decoder output of one scale), K [B,cams,4,4] = inputs['K', 0] -> depth [B,cams,H,W]."""
+    t = cfg['training']
+    return _ToDepth.apply(disp.contiguous(), K.contiguous(), float(t['min_depth']), float(t['max_depth']),
+                          float(t['focal_length_scale']), int(t['height']), int(t['width']))
+
+
 def combine_losses(cfg, num, den, smooth):
     """per-camera total of multi_cam_loss.py:118-137 from the kernel's sums. num/den [n,3], smooth [n] -> [n]"""
     L = cfg['loss']
