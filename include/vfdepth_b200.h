@@ -231,7 +231,8 @@ int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T
 /* --------------------------------------------------------------------------------------------------
  * Edge-aware disparity smoothness (models/losses/single_cam_loss.py:57-65, loss_util.py:28-40), scale 0, all cameras
  * of the batch at once.
- *   color   [B,cams,3,H,W]  inputs['color', 0, 0]
+ *   color   [B,cams,3,H,W]  inputs['color', 0, 0]; NULL = no edge weighting (the depth_sm_loss of
+ *                           depth_synthesis_loss.py:35-41 on ('disp', 0, 'aug'))
  *   disp    [B,cams,H,W]    ('disp', 0) of every camera
  *   img_sum [B*cams] f64    out: sum of disp per image (the mean of single_cam_loss.py:63), kept for the backward
  *   sums    [cams][2] f64   out: sum over the batch of |d nd / dx| * exp(-|d rgb / dx|) and of the y term; the loss of
@@ -255,6 +256,35 @@ int vfd_to_depth_fwd(int B, int cams, int hs, int ws, int H, int W, const float*
 /* backward w.r.t. disp: d_depth [B,cams,H,W] -> d_disp [B,cams,hs,ws] (zero-filled here when it is accumulated). */
 int vfd_to_depth_bwd(int B, int cams, int hs, int ws, int H, int W, const float* disp, const float* K, float min_depth,
                      float max_depth, float focal_length_scale, const float* d_depth, float* d_disp, void* stream);
+
+/* --------------------------------------------------------------------------------------------------
+ * Depth-synthesis consistency loss of the aug_depth configuration:
+ * ViewRendering.get_virtual_depth (models/geometry/view_rendering.py:84-116) for the sources
+ * rel_cam_list[cam] + [cam] (:201-241) fused with the consistency part of DepthSynLoss.compute_aug_losses
+ * (models/losses/depth_synthesis_loss.py:15-33).
+ *   depth  [B,cams,H,W]       ('depth', 0) of every camera (sources)
+ *   aug    [B,n_call,H,W]     ('depth', 0, 'aug') of the target cameras [cam0, cam0 + n_call)
+ *   T      [B,n_call,3,4,4]   inverse(extrinsics_aug[cam]) @ extrinsics[src]  (source camera -> novel view), slot i = src[cam][i]
+ *   Tinv   [B,n_call,3,4,4]   inverse(T)  (torch.inverse, view_rendering.py:96)
+ *   sums   [n_call][2] f64    out (zero-filled here): sum loss*mask, sum mask over the sources and the batch;
+ *                             depth_con_loss = sums[c][0] / (sums[c][1] + 1e-8)  (loss_util.py:21-25)
+ *   out_depth / out_mask [B,n_call,3,H,W] or NULL: ('tform_depth', 0) / ('tform_depth_mask', 0) for the logger */
+#define VFD_SYN_SRC 3
+typedef struct vfd_syn_desc {
+    int32_t B, num_cams, H, W;
+    int32_t cam0, n_call;
+    int32_t src[VFD_MAX_CAMS][VFD_SYN_SRC]; /* source camera of slot i, -1 = skipped (:210-212) */
+    float min_depth, max_depth;             /* training.min_depth / max_depth (:109-113) */
+    const float* mask;                      /* device [B,cams,H,W]  inputs['mask'] */
+    const float* K;                         /* device [B,cams,4,4]  inputs['K', 0] */
+    const float* invK;                      /* device [B,cams,4,4]  inputs['inv_K', 0] */
+} vfd_syn_desc;
+int vfd_depth_syn_fwd(const vfd_syn_desc* d, const float* depth, const float* aug, const float* T, const float* Tinv,
+                      double* sums, float* out_depth, float* out_mask, void* stream);
+/* backward: wcam [n_call] = upstream gradient of sums[c][0]; d_aug [B,n_call,H,W] written, d_depth [B,cams,H,W]
+ * zero-filled here and accumulated (bilinear scatter). */
+int vfd_depth_syn_bwd(const vfd_syn_desc* d, const float* depth, const float* aug, const float* T, const float* Tinv,
+                      const float* wcam, float* d_aug, float* d_depth, void* stream);
 
 #ifdef __cplusplus
 }

@@ -447,3 +447,63 @@ def to_depth(cfg, disp_in, K_in):
     disp = min_disp + disp_range * disp_in
     depth = 1 / disp
     return depth * K_in[:, 0:1, 0:1].unsqueeze(2) / t['focal_length_scale']
+
+
+# --------------------------------------------------------------------------------------
+# 8f-3  depth synthesis (aug_depth)   view_rendering.py:84-116, :201-241; depth_synthesis_loss.py:15-43
+# --------------------------------------------------------------------------------------
+def virtual_depth(src_depth, src_mask, src_inv_K, src_K, tar_depth, tar_inv_K, tar_K, T, min_depth, max_depth):
+    """-> (source depth warped into the target view [B,1,H,W], its mask) -- view_rendering.py:84-116."""
+    b, _, h, w = src_depth.size()
+    homo = homo_points(b, h, w, src_depth.dtype)
+    src_points = src_depth.view(b, 1, -1) * torch.matmul(src_inv_K[:, :3, :3], homo)
+    src_points = torch.cat([src_points, homo[:, 2:3]], 1)
+    src_points_warped = torch.matmul(T[:, :3, :], src_points)
+    src_depth_warped = src_points_warped.reshape(b, 3, h, w)[:, 2:3, :, :]
+    pix_coords = reproject_grid(tar_depth, torch.inverse(T), tar_inv_K, src_K)
+    depth_warped = F.grid_sample(src_depth_warped, pix_coords, mode='bilinear', padding_mode='zeros',
+                                 align_corners=True)
+    mask_warped = F.grid_sample(src_mask, pix_coords, mode='nearest', padding_mode='zeros', align_corners=True)
+    depth_warped[torch.isnan(depth_warped)] = 2.0
+    mask_warped[torch.isnan(mask_warped)] = 0
+    g = pix_coords.permute(0, 3, 1, 2)
+    invalid = torch.logical_or(g > 1, g < -1).sum(dim=1, keepdim=True) > 0
+    valid_min = depth_warped > min_depth
+    depth_warped[~valid_min] = min_depth
+    valid_max = depth_warped < max_depth
+    depth_warped[~valid_max] = max_depth
+    return depth_warped, (~invalid).float() * mask_warped * valid_min * valid_max
+
+
+def depth_synthesis(cfg, inputs, depths, aug_depth, cam):
+    """the aug_depth branch of ViewRendering.forward (:201-241) for one camera: depths = list over cameras of
+    ('depth', 0), aug_depth = ('depth', 0, 'aug') of `cam` -> (tform_depth list, tform_mask list)."""
+    t = cfg['training']
+    n = cfg['data']['num_cams']
+    aug_ext_inv = torch.inverse(inputs['extrinsics_aug'][:, cam])
+    K, inv_K = inputs[('K', 0)], inputs[('inv_K', 0)]
+    tform_depth, tform_mask = [], []
+    for src in cfg['data']['rel_cam_list'][cam] + [cam]:
+        if src >= n:
+            continue
+        rel_pose = torch.matmul(aug_ext_inv, inputs['extrinsics'][:, src])
+        d, m = virtual_depth(depths[src], inputs['mask'][:, src], inv_K[:, src], K[:, src], aug_depth, inv_K[:, cam],
+                             K[:, cam], rel_pose, t['min_depth'], t['max_depth'])
+        tform_depth.append(d)
+        tform_mask.append(m)
+    return tform_depth, tform_mask
+
+
+def aug_losses(aug_depth, tform_depth, tform_mask, disp_aug):
+    """DepthSynLoss.compute_aug_losses (depth_synthesis_loss.py:15-43) -> (depth_con_loss, depth_sm_loss)."""
+    losses, masks = [], []
+    for d, m in zip(tform_depth, tform_mask):
+        pl = (aug_depth - d).abs() / (aug_depth + d + 1e-8)
+        losses.append(torch.clamp(pl, 0., 1.))
+        masks.append(m)
+    con = masked_loss(torch.cat(losses, 0), torch.cat(masks, 0))
+    mean_disp = disp_aug.mean(2, True).mean(3, True)
+    nd = disp_aug / (mean_disp + 1e-8)
+    gx = torch.abs(nd[:, :, :, :-1] - nd[:, :, :, 1:])
+    gy = torch.abs(nd[:, :, :-1, :] - nd[:, :, 1:, :])
+    return con, gx.mean() + gy.mean()

@@ -2,8 +2,8 @@
 
     python tests/golden/make_golden.py            # needs /root/reference (or $VFDEPTH_REF)
 
-Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz`` next to this file
-(``--only-to-depth`` regenerates just the last one).  The
+Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz``, ``golden_depth_syn.npz`` next to this file
+(``--only-new`` regenerates just the last two).  The
 fixtures hold the seeded inputs and what the reference's own classes
 (``VFNet``, ``ViewRendering``, ``Pose``, ``MultiCamLoss``) returned for them, at
 sizes small enough to commit.  ``tests/test_oracle_golden.py`` then pins
@@ -168,9 +168,76 @@ def make_to_depth(path):
     print('wrote', path)
 
 
+SYN_CFG = dict(training__aug_depth=True, loss__depth_con_coeff=0.03, loss__depth_sm_coeff=0.05)
+
+
+def syn_cfg():
+    return vcfg.default_config('ddad', batch_size=2, **dict(WARP_CFG, **SYN_CFG))
+
+
+def syn_case(cfg, seed):
+    """seeded inputs of the depth-synthesis path: a rig, augmented extrinsics (small rotations so that the novel views
+    overlap their sources), the novel-view depth / disparity predictions."""
+    from vfdepth_b200.rig import axis_angle_to_matrix
+    inputs, extras = make_rig(cfg, seed=seed, with_feats=False)
+    B = cfg['training']['batch_size']
+    gen = torch.Generator().manual_seed(seed + 1)
+    angle = (torch.rand((B, 6, 3), generator=gen) - 0.5) * torch.tensor([0.2, 0.2, 0.5])
+    tform = torch.eye(4).repeat(B, 6, 1, 1)
+    tform[:, :, :3, :3] = axis_angle_to_matrix(angle)
+    inputs['extrinsics_aug'] = tform @ inputs['extrinsics']
+    depth = torch.cat(extras['depth'], 1)
+    aug = depth * (1.0 + 0.1 * (torch.rand(depth.shape, generator=gen) - 0.5))
+    disp_aug = torch.rand(depth.shape, generator=gen) * 0.5 + 0.05
+    w = torch.rand((6, 2), generator=gen) + 0.5
+    return inputs, extras, depth, aug, disp_aug, w
+
+
+def make_depth_syn(ref, path):
+    """ViewRendering.forward with aug_depth (view_rendering.py:201-241 -> get_virtual_depth :84-116) and
+    DepthSynLoss.compute_aug_losses (depth_synthesis_loss.py:15-43), the reference's own classes."""
+    ref_import.load_algo()
+    import sys as _sys
+    DepthSynLoss = _sys.modules['models.losses'].DepthSynLoss
+    cfg = syn_cfg()
+    inputs, extras, depth, aug, disp_aug, w = syn_case(cfg, 779)
+    vr = ref.ViewRendering(cfg, 'cpu')
+    pose = ref.Pose(cfg)
+    lossm = DepthSynLoss(cfg, 'cpu')
+    depths = [depth[:, c:c + 1].clone().requires_grad_(True) for c in range(6)]
+    augs = [aug[:, c:c + 1].clone().requires_grad_(True) for c in range(6)]
+    disps = [disp_aug[:, c:c + 1].clone().requires_grad_(True) for c in range(6)]
+    outputs = {}
+    for cam in range(6):
+        outputs[('cam', cam)] = {('depth', 0): depths[cam], ('disp', 0): extras['disp'][cam],
+                                 ('depth', 0, 'aug'): augs[cam], ('disp', 0, 'aug'): disps[cam],
+                                 ('cam_T_cam', 0, -1): extras['cam_T_cam'][-1][:, cam],
+                                 ('cam_T_cam', 0, 1): extras['cam_T_cam'][1][:, cam]}
+    total, con, sm = 0, [], []
+    out = {k: _np(inputs[k]) for k in ('mask', 'extrinsics', 'extrinsics_aug')}
+    out.update(K=_np(inputs[('K', 0)]), inv_K=_np(inputs[('inv_K', 0)]), depth=_np(depth), aug=_np(aug),
+               disp_aug=_np(disp_aug), w=_np(w))
+    for cam in range(6):
+        rel = pose.compute_relative_cam_poses(inputs, outputs, cam)
+        vr(inputs, outputs, cam, rel)
+        c, s_ = lossm.compute_aug_losses(outputs[('cam', cam)], 0)
+        con.append(c)
+        sm.append(s_)
+        total = total + w[cam, 0] * c + w[cam, 1] * s_
+        if cam in (0, 3):
+            out['cam%d_tform_depth' % cam] = _np(torch.cat(outputs[('cam', cam)][('tform_depth', 0)], 1))
+            out['cam%d_tform_mask' % cam] = _np(torch.cat(outputs[('cam', cam)][('tform_depth_mask', 0)], 1))
+    grads = torch.autograd.grad(total, depths + augs + disps)
+    out.update(con=_np(torch.stack(con)), sm=_np(torch.stack(sm)), d_depth=_np(torch.cat(grads[:6], 1)),
+               d_aug=_np(torch.cat(grads[6:12], 1)), d_disp_aug=_np(torch.cat(grads[12:], 1)))
+    np.savez_compressed(path, **out)
+    print('wrote', path, 'con', [float(c) for c in con])
+
+
 if __name__ == '__main__':
     ref = ref_import.load()
-    if '--only-to-depth' not in sys.argv:
+    if '--only-new' not in sys.argv:
         make_fusion(ref, os.path.join(HERE, 'golden_fusion.npz'))
         make_warp(ref, os.path.join(HERE, 'golden_warp.npz'))
     make_to_depth(os.path.join(HERE, 'golden_to_depth.npz'))
+    make_depth_syn(ref, os.path.join(HERE, 'golden_depth_syn.npz'))

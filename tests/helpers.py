@@ -47,3 +47,15 @@ def rel_err(a, b):
     """max |a-b| / max(|b|) -- the 'relative to the tensor's scale' error used for fp32 parity."""
     a, b = a.double(), b.double()
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+SYN_CFG = dict(training__aug_depth=True, loss__depth_con_coeff=0.03, loss__depth_sm_coeff=0.05)
+
+
+def syn_cfg():
+    return vcfg.default_config('ddad', batch_size=2, **dict(WARP_CFG, **SYN_CFG))
+
+
+def syn_inputs(g):
+    return {'mask': g['mask'], ('K', 0): g['K'], ('inv_K', 0): g['inv_K'], 'extrinsics': g['extrinsics'],
+            'extrinsics_aug': g['extrinsics_aug']}

@@ -79,3 +79,27 @@ def test_to_depth_bit_exact():
         assert torch.equal(depth, g['depth_%d' % s]), s
         d_disp, = torch.autograd.grad((depth * g['g_up_%d' % s]).sum(), disp)
         assert torch.equal(d_disp, g['d_disp_%d' % s]), s
+
+
+def test_depth_synthesis_bit_exact():
+    """oracle.depth_synthesis / aug_losses against the reference's ViewRendering (aug_depth branch, :201-241 ->
+    get_virtual_depth :84-116) and DepthSynLoss.compute_aug_losses (depth_synthesis_loss.py:15-43)."""
+    g = H.load_npz('golden_depth_syn.npz')
+    cfg = H.syn_cfg()
+    inputs = H.syn_inputs(g)
+    depths = [g['depth'][:, c:c + 1].clone().requires_grad_(True) for c in range(6)]
+    augs = [g['aug'][:, c:c + 1].clone().requires_grad_(True) for c in range(6)]
+    disps = [g['disp_aug'][:, c:c + 1].clone().requires_grad_(True) for c in range(6)]
+    total = 0
+    for cam in range(6):
+        td, tm = orc.depth_synthesis(cfg, inputs, depths, augs[cam], cam)
+        if cam in (0, 3):
+            assert torch.equal(torch.cat(td, 1), g['cam%d_tform_depth' % cam])
+            assert torch.equal(torch.cat(tm, 1), g['cam%d_tform_mask' % cam])
+        con, sm = orc.aug_losses(augs[cam], td, tm, disps[cam])
+        assert torch.equal(con, g['con'][cam]) and torch.equal(sm, g['sm'][cam])
+        total = total + g['w'][cam, 0] * con + g['w'][cam, 1] * sm
+    grads = torch.autograd.grad(total, depths + augs + disps)
+    assert torch.equal(torch.cat(grads[:6], 1), g['d_depth'])
+    assert torch.equal(torch.cat(grads[6:12], 1), g['d_aug'])
+    assert torch.equal(torch.cat(grads[12:], 1), g['d_disp_aug'])

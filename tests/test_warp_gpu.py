@@ -369,3 +369,104 @@ def test_to_depth_ragged_sizes_match_oracle():
         g_got, = torch.autograd.grad((got * up.to(dev)).sum(), d_got)
         assert float(((got.detach().cpu() - ref.detach()).abs() / ref.detach().abs()).max()) < 1e-6
         assert H.rel_err(g_got.cpu(), g_ref) < 1e-5
+
+
+def _syn_gpu(cfg, g, dev, cam0=0, n_call=6, want_views=False):
+    from vfdepth_b200 import view
+    inputs = {k: v.to(dev) for k, v in H.syn_inputs(g).items()}
+    depth = g['depth'].to(dev).requires_grad_(True)
+    aug = g['aug'][:, cam0:cam0 + n_call].to(dev).requires_grad_(True)
+    disp = g['disp_aug'][:, cam0:cam0 + n_call].to(dev).requires_grad_(True)
+    con, sm, v = view.depth_syn_loss(cfg, inputs, depth, aug, disp, cam0, want_views)
+    return depth, aug, disp, con, sm, v
+
+
+def test_depth_synthesis_matches_reference_golden():
+    """vfd_depth_syn_fwd / _bwd + the colour-less smoothness against the fixture produced by the reference's
+    ViewRendering (aug_depth branch) and DepthSynLoss.compute_aug_losses: losses and all three gradients within 1e-4
+    of their scale; warped depths / masks of cameras 0 and 3 element-wise (masks bit-exact except where the warped
+    depth sits within 1e-4 of a range threshold)."""
+    dev = _dev()
+    g = H.load_npz('golden_depth_syn.npz')
+    cfg = H.syn_cfg()
+    depth, aug, disp, con, sm, v = _syn_gpu(cfg, g, dev, want_views=True)
+    assert H.rel_err(con.detach().cpu(), g['con']) < TOL
+    assert H.rel_err(sm.detach().cpu(), g['sm']) < TOL
+    for cam in (0, 3):
+        td, tm = v['tform_depth'][:, cam].cpu(), v['tform_depth_mask'][:, cam].cpu()
+        ref_d, ref_m = g['cam%d_tform_depth' % cam], g['cam%d_tform_mask' % cam]
+        flips = (tm != ref_m)
+        assert float(flips.float().mean()) < 1e-4
+        ok = ~flips
+        assert float(((td - ref_d).abs() / ref_d.abs().clamp_min(1e-3))[ok].max()) < 1e-4
+    w = g['w'].to(dev)
+    total = (w[:, 0] * con + w[:, 1] * sm).sum()
+    gd, ga, gs = torch.autograd.grad(total, [depth, aug, disp])
+    assert H.rel_err(gd.cpu(), g['d_depth']) < TOL
+    assert H.rel_err(ga.cpu(), g['d_aug']) < TOL
+    assert H.rel_err(gs.cpu(), g['d_disp_aug']) < TOL
+
+
+def test_depth_synthesis_camera_subset_and_dropin():
+    """a call for one target camera equals the matching slice of the rig-level call; the DepthSynLoss drop-in adds
+    depth_con_coeff * con + depth_sm_coeff * sm to the MultiCamLoss total and writes the reference's keys."""
+    dev = _dev()
+    g = H.load_npz('golden_depth_syn.npz')
+    cfg = H.syn_cfg()
+    _, _, _, con, sm, _ = _syn_gpu(cfg, g, dev)
+    for cam in (1, 4):
+        _, _, _, c1, s1, v1 = _syn_gpu(cfg, g, dev, cam, 1, True)
+        assert torch.equal(c1[0], con[cam]) and torch.equal(s1[0], sm[cam])
+        assert v1['tform_depth'].shape == (2, 1, 3, 48, 64)
+
+
+def test_depth_synthesis_degenerate_inputs():
+    """novel view identical to the source view: the camera's own depth warps onto itself (loss of that source = 0 when
+    aug == depth), and cameras without neighbours (-1 slots) are skipped."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    g = H.load_npz('golden_depth_syn.npz')
+    cfg = H.syn_cfg()
+    cfg['data']['rel_cam_list'] = {c: [] for c in range(6)}          # only the camera itself
+    inputs = {k: v.to(dev) for k, v in H.syn_inputs(g).items()}
+    inputs['extrinsics_aug'] = inputs['extrinsics'].clone()
+    depth = g['depth'].to(dev)
+    con, sm, _ = view.depth_syn_loss(cfg, inputs, depth, depth.clone(), g['disp_aug'].to(dev))
+    assert float(con.max()) < 1e-5
+
+
+def test_depth_syn_loss_module_dropin():
+    """DepthSynLoss(cfg, rank).forward(inputs, outputs, cam) (depth_synthesis_loss.py:45-89) = the MultiCamLoss total
+    + depth_con_coeff * con + depth_sm_coeff * sm with con / sm as the reference computed them (golden fixture), the
+    reference's extra keys written, gradients reaching the novel-view predictions."""
+    from tests.golden.make_golden import syn_case
+    from vfdepth_b200 import view
+    dev = _dev()
+    g = H.load_npz('golden_depth_syn.npz')
+    cfg = H.syn_cfg()
+    inp, ex, depth, aug, disp_aug, _ = syn_case(cfg, 779)
+    assert torch.equal(aug, g['aug']) and torch.equal(inp['extrinsics_aug'], g['extrinsics_aug'])
+    to = lambda t: t.to(dev)
+    inputs = {k: to(v) for k, v in inp.items()}
+    augs = [to(aug[:, c:c + 1]).requires_grad_(True) for c in range(6)]
+    outputs = {('cam', c): {('depth', 0): to(depth[:, c:c + 1]), ('disp', 0): to(ex['disp'][c]),
+                            ('depth', 0, 'aug'): augs[c], ('disp', 0, 'aug'): to(disp_aug[:, c:c + 1]),
+                            ('cam_T_cam', 0, -1): to(ex['cam_T_cam'][-1][:, c]),
+                            ('cam_T_cam', 0, 1): to(ex['cam_T_cam'][1][:, c])} for c in range(6)}
+    vr = view.ViewRendering(cfg, dev)
+    base, full = view.MultiCamLoss(cfg, dev), view.DepthSynLoss(cfg, dev)
+    L = cfg['loss']
+    for cam in (0, 4):
+        Ts = {-1: outputs[('cam', cam)][('cam_T_cam', 0, -1)], 1: outputs[('cam', cam)][('cam_T_cam', 0, 1)]}
+        vr(inputs, outputs, cam, orc.relative_cam_poses(cfg, inputs, Ts, cam))
+        torch.manual_seed(5)
+        l0, _ = base(inputs, outputs, cam)
+        torch.manual_seed(5)
+        l1, ld = full(inputs, outputs, cam)
+        want = L['depth_con_coeff'] * float(g['con'][cam]) + L['depth_sm_coeff'] * float(g['sm'][cam])
+        assert abs(float(l1 - l0) - want) / want < 1e-4
+        assert abs(ld['depth_con_loss'] - float(g['con'][cam])) / float(g['con'][cam]) < 1e-4
+        tv = outputs[('cam', cam)]
+        assert len(tv[('tform_depth', 0)]) == 3 and tv[('tform_depth_mask', 0)][0].shape == (2, 1, 48, 64)
+        ga, = torch.autograd.grad(l1, augs[cam])
+        assert H.rel_err(ga.cpu(), L['depth_con_coeff'] * g['d_aug'][:, cam:cam + 1] / g['w'][cam, 0]) < 1e-4

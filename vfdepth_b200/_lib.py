@@ -46,6 +46,17 @@ class WarpDesc(ctypes.Structure):
     ]
 
 
+class SynDesc(ctypes.Structure):
+    """struct vfd_syn_desc"""
+    _fields_ = [
+        ('B', ctypes.c_int32), ('num_cams', ctypes.c_int32), ('H', ctypes.c_int32), ('W', ctypes.c_int32),
+        ('cam0', ctypes.c_int32), ('n_call', ctypes.c_int32),
+        ('src', (ctypes.c_int32 * 3) * VFD_MAX_CAMS),
+        ('min_depth', ctypes.c_float), ('max_depth', ctypes.c_float),
+        ('mask', ctypes.c_void_p), ('K', ctypes.c_void_p), ('invK', ctypes.c_void_p),
+    ]
+
+
 class WarpViews(ctypes.Structure):
     """struct vfd_warp_views"""
     _fields_ = [(n, ctypes.c_void_p) for n in ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss',

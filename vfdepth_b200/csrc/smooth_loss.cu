@@ -50,6 +50,7 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_mean_kernel(const Smoot
 
 // edge weight exp(-mean_c |rgb[p] - rgb[q]|)
 __device__ __forceinline__ float edge_weight(const float* col, int HW, int p, int q) {
+    if (!col) return 1.f;      // plain smoothness (depth_synthesis_loss.py:35-41)
     const float d0 = fabsf(__ldg(col + p) - __ldg(col + q));
     const float d1 = fabsf(__ldg(col + HW + p) - __ldg(col + HW + q));
     const float d2 = fabsf(__ldg(col + 2 * HW + p) - __ldg(col + 2 * HW + q));
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_loss_kernel(const Smoot
     __shared__ double s_red[kSmoothThreads / 32];
     const int bc = blockIdx.y, cam = bc % a.cams, HW = a.H * a.W, W = a.W, H = a.H;
     const float* d = a.disp + (size_t)bc * HW;
-    const float* col = a.color + (size_t)bc * 3 * HW;
+    const float* col = a.color ? a.color + (size_t)bc * 3 * HW : nullptr;
     const float den = image_scale(a, bc);
     float sx = 0.f, sy = 0.f;
     for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads) {
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const Smooth
     __shared__ double s_red[kSmoothThreads / 32];
     const int bc = blockIdx.y, cam = bc % a.cams, HW = a.H * a.W, W = a.W, H = a.H;
     const float* d = a.disp + (size_t)bc * HW;
-    const float* col = a.color + (size_t)bc * 3 * HW;
+    const float* col = a.color ? a.color + (size_t)bc * 3 * HW : nullptr;
     float* g = a.d_disp + (size_t)bc * HW;
     const float den = image_scale(a, bc);
     const float up = __ldg(a.d_smooth + cam);
@@ -140,7 +141,7 @@ extern "C" int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* c
                                    double* img_sum, double* sums, void* stream) {
     int rc = check_smooth(B, cams, H, W);
     if (rc) return rc;
-    if (!color || !disp || !img_sum || !sums) return VFD_ERR_NULL;
+    if (!disp || !img_sum || !sums) return VFD_ERR_NULL;      // color may be NULL
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(img_sum, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
     if (cudaMemsetAsync(sums, 0, sizeof(double) * cams * 2, st) != cudaSuccess) return VFD_ERR_CUDA;
@@ -158,7 +159,7 @@ extern "C" int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* c
                                    void* stream) {
     int rc = check_smooth(B, cams, H, W);
     if (rc) return rc;
-    if (!color || !disp || !img_sum || !d_smooth || !gdot || !d_disp) return VFD_ERR_NULL;
+    if (!disp || !img_sum || !d_smooth || !gdot || !d_disp) return VFD_ERR_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(gdot, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
     SmoothArgs a = {};

@@ -184,23 +184,26 @@ class _SmoothLoss(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, color, disp):
-        B, n, _, H, W = color.shape
-        _chk(color, 'color', (B, n, 3, H, W))
+        B, n, H, W = disp.shape
+        if color is not None:
+            _chk(color, 'color', (B, n, 3, H, W))
         _chk(disp, 'disp', (B, n, H, W))
-        dev = color.device
+        dev = disp.device
         img_sum = torch.empty((B * n,), device=dev, dtype=torch.float64)
         sums = torch.empty((n, 2), device=dev, dtype=torch.float64)
         _lib.call('vfd_smooth_loss_fwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum), _lib.ptr(sums),
                   _stream())
-        ctx.save_for_backward(color, disp, img_sum)
+        ctx.color = color
+        ctx.save_for_backward(disp, img_sum)
         out = sums[:, 0] / float(B * H * (W - 1)) + sums[:, 1] / float(B * (H - 1) * W)
         return out.float()
 
     @staticmethod
     def backward(ctx, d_smooth):
-        color, disp, img_sum = ctx.saved_tensors
-        B, n, _, H, W = color.shape
-        gdot = torch.empty((B * n,), device=color.device, dtype=torch.float64)
+        disp, img_sum = ctx.saved_tensors
+        color = ctx.color
+        B, n, H, W = disp.shape
+        gdot = torch.empty((B * n,), device=disp.device, dtype=torch.float64)
         d_disp = torch.empty_like(disp)
         _lib.call('vfd_smooth_loss_bwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum),
                   _lib.ptr(d_smooth.float().contiguous()), _lib.ptr(gdot), _lib.ptr(d_disp), _stream())
@@ -209,8 +212,73 @@ class _SmoothLoss(torch.autograd.Function):
 
 def smooth_loss(color, disp):
     """single_cam_loss.py:57-65 + loss_util.py:28-40 for all cameras at once.
-    color [B,cams,3,H,W], disp [B,cams,H,W] -> per-camera loss [cams]."""
-    return _SmoothLoss.apply(color.contiguous(), disp.contiguous())
+    color [B,cams,3,H,W] (None: no edge weighting, the depth_sm_loss of depth_synthesis_loss.py:35-41),
+    disp [B,cams,H,W] -> per-camera loss [cams]."""
+    return _SmoothLoss.apply(None if color is None else color.contiguous(), disp.contiguous())
+
+
+class _DepthSyn(torch.autograd.Function):
+    """vfd_depth_syn_fwd / _bwd: masked consistency sums of the warped source depths against the novel-view depth."""
+
+    @staticmethod
+    def forward(ctx, depth, aug, T, Tinv, desc, keep, views):
+        d = desc
+        sums = torch.empty((d.n_call, 2), device=depth.device, dtype=torch.float64)
+        out_d, out_m = views if views is not None else (None, None)
+        _lib.call('vfd_depth_syn_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(aug), _lib.ptr(T), _lib.ptr(Tinv),
+                  _lib.ptr(sums), _lib.ptr(out_d), _lib.ptr(out_m), _stream())
+        ctx.desc, ctx.keep = d, keep
+        ctx.save_for_backward(depth, aug, T, Tinv)
+        num, den = sums[:, 0].float(), sums[:, 1].float()
+        ctx.mark_non_differentiable(den)
+        return num, den
+
+    @staticmethod
+    def backward(ctx, d_num, _d_den):
+        depth, aug, T, Tinv = ctx.saved_tensors
+        d_aug, d_depth = torch.empty_like(aug), torch.empty_like(depth)
+        _lib.call('vfd_depth_syn_bwd', ctypes.byref(ctx.desc), _lib.ptr(depth), _lib.ptr(aug), _lib.ptr(T),
+                  _lib.ptr(Tinv), _lib.ptr(d_num.float().contiguous()), _lib.ptr(d_aug), _lib.ptr(d_depth), _stream())
+        return d_depth, d_aug, None, None, None, None, None
+
+
+def depth_syn_loss(cfg, inputs, depth, aug_depth, disp_aug, cam0=0, want_views=False):
+    """The aug_depth losses for target cameras [cam0, cam0 + n_call) of the whole rig batch:
+    view_rendering.py:201-241 (get_virtual_depth :84-116 for rel_cam_list[cam] + [cam]) fused with
+    depth_synthesis_loss.py:15-43.
+    depth [B,cams,H,W] = ('depth', 0) of every camera; aug_depth / disp_aug [B,n_call,H,W] = ('depth', 0, 'aug') /
+    ('disp', 0, 'aug') of the targets; inputs needs 'mask', 'extrinsics', 'extrinsics_aug', ('K', 0), ('inv_K', 0).
+    -> (depth_con_loss [n_call], depth_sm_loss [n_call], views {'tform_depth', 'tform_depth_mask'} [B,n_call,3,H,W])."""
+    t = cfg['training']
+    n = cfg['data']['num_cams']
+    B, cams, H, W = depth.shape
+    n_call = aug_depth.shape[1]
+    _chk(depth, 'depth', (B, n, H, W))
+    _chk(aug_depth, 'aug_depth', (B, n_call, H, W))
+    mask = inputs['mask'].reshape(B, n, H, W).contiguous()
+    K, invK = inputs[('K', 0)].contiguous(), inputs[('inv_K', 0)].contiguous()
+    d = _lib.SynDesc()
+    d.B, d.num_cams, d.H, d.W, d.cam0, d.n_call = B, n, H, W, cam0, n_call
+    d.min_depth, d.max_depth = float(t['min_depth']), float(t['max_depth'])
+    d.mask, d.K, d.invK = mask.data_ptr(), K.data_ptr(), invK.data_ptr()
+    rel = cfg['data']['rel_cam_list']
+    idx = []
+    for c in range(n):
+        srcs = ([s if s < n else -1 for s in list(rel[c]) + [c]] + [-1] * 3)[:3]
+        for i in range(3):
+            d.src[c][i] = srcs[i]
+        idx.append([max(s, 0) for s in srcs])
+    sel = torch.tensor(idx[cam0:cam0 + n_call], device=depth.device)                 # [n_call,3]
+    aug_inv = torch.inverse(inputs['extrinsics_aug'][:, cam0:cam0 + n_call])         # :206
+    T = (aug_inv[:, :, None] @ inputs['extrinsics'][:, sel]).contiguous()            # :224  [B,n_call,3,4,4]
+    Tinv = torch.inverse(T).contiguous()                                             # :96
+    views = None
+    if want_views:
+        views = (torch.empty((B, n_call, 3, H, W), device=depth.device), torch.empty((B, n_call, 3, H, W), device=depth.device))
+    num, den = _DepthSyn.apply(depth.contiguous(), aug_depth.contiguous(), T, Tinv, d, (mask, K, invK), views)
+    con = num / (den + 1e-8)
+    sm = smooth_loss(None, disp_aug)
+    return con, sm, ({'tform_depth': views[0], 'tform_depth_mask': views[1]} if views else {})
 
 
 class _ToDepth(torch.autograd.Function):
@@ -293,8 +361,8 @@ class ViewRendering(torch.nn.Module):
         super().__init__()
         vcfg.flatten_into(self, cfg)
         self.cfg, self.rank, self.materialize = cfg, rank, materialize
-        if getattr(self, 'aug_depth', False):
-            raise NotImplementedError('aug_depth (view_rendering.py:201-241) is outside the hot path')
+        # aug_depth (view_rendering.py:201-241): the warped source depths are produced, fused with their loss, by
+        # DepthSynLoss.forward, which also writes ('tform_depth', 0) / ('tform_depth_mask', 0)
         if list(self.scales) != [0]:
             raise NotImplementedError('only scales == [0] (all reference configs)')
 
@@ -365,3 +433,27 @@ class MultiCamLoss(torch.nn.Module):
                 for i, n in enumerate(('pose/tx', 'pose/ty', 'pose/tz')):
                     loss_dict[n] = pose_t[:, i, 3].abs().mean()
         return cam_loss[0], loss_dict
+
+
+class DepthSynLoss(MultiCamLoss):
+    """Drop-in for models/losses/depth_synthesis_loss.py:8 (``DepthSynLoss(cfg, rank)``; ``forward(inputs, outputs,
+    cam)`` -> ``(cam_loss, loss_dict)``): the MultiCamLoss terms plus depth_con_coeff * consistency + depth_sm_coeff *
+    smoothness of the novel-view prediction.  Reads ('depth', 0) of every camera, ('depth', 0, 'aug') and
+    ('disp', 0, 'aug') of ``cam`` and inputs['extrinsics_aug'] (written by VFNet.forward); writes ('tform_depth', 0) /
+    ('tform_depth_mask', 0) as the reference's ViewRendering does (view_rendering.py:240-241)."""
+
+    def forward(self, inputs, outputs, cam):
+        cam_loss, loss_dict = super().forward(inputs, outputs, cam)
+        n = self.cfg['data']['num_cams']
+        tv = outputs[('cam', cam)]
+        depth = torch.cat([outputs[('cam', c)][('depth', 0)] for c in range(n)], 1)
+        con, sm, v = depth_syn_loss(self.cfg, inputs, depth, tv[('depth', 0, 'aug')], tv[('disp', 0, 'aug')], cam,
+                                    want_views=True)
+        slots = [i for i, s in enumerate((list(self.cfg['data']['rel_cam_list'][cam]) + [cam])[:3]) if s < n]
+        tv[('tform_depth', 0)] = [v['tform_depth'][:, 0, i:i + 1] for i in slots]
+        tv[('tform_depth_mask', 0)] = [v['tform_depth_mask'][:, 0, i:i + 1] for i in slots]
+        depthsyn = self.depth_con_coeff * con[0] + self.depth_sm_coeff * sm[0]
+        cam_loss = cam_loss + depthsyn / len(self.scales)
+        loss_dict.update(depth_loss=float(depthsyn.detach()), depth_sm_loss=float(sm[0].detach()),
+                         depth_con_loss=float(con[0].detach()))
+        return cam_loss, loss_dict
