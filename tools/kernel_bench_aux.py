@@ -1,0 +1,86 @@
+"""Per-kernel timing of the small full-resolution kernels either side of the warp path at the
+bench batch: to_depth, edge-aware smoothness, depth synthesis.  CUDA events on the launch stream, inputs larger than
+L2 in total (B=8: 47 MB per [B,6,H,W] map, 8 maps live).
+
+    python tools/kernel_bench_aux.py [--batch 8] [--iters 20]
+"""
+import argparse
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tools'))
+
+from kernel_bench import peak_gbs  # noqa: E402
+from vfdepth_b200 import config as vcfg  # noqa: E402
+from vfdepth_b200 import view  # noqa: E402
+from vfdepth_b200.rig import axis_angle_to_matrix, make_rig  # noqa: E402
+
+
+def timed(fn, iters, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--batch', type=int, default=8)
+    ap.add_argument('--iters', type=int, default=20)
+    args = ap.parse_args()
+    dev = torch.device('cuda:0')
+    B = args.batch
+    cfg = vcfg.default_config('ddad', batch_size=1)
+    inputs, ex = make_rig(cfg, seed=3, with_feats=False)
+    rep = lambda t: t.to(dev).repeat(B, *([1] * (t.dim() - 1))).contiguous()
+    inp = {k: rep(v) for k, v in inputs.items() if k in ('mask', 'extrinsics', ('K', 0), ('inv_K', 0), ('color', 0, 0))}
+    gen = torch.Generator().manual_seed(9)
+    angle = (torch.rand((1, 6, 3), generator=gen) - 0.5) * torch.tensor([0.2, 0.2, 0.5])
+    tform = torch.eye(4).repeat(1, 6, 1, 1)
+    tform[:, :, :3, :3] = axis_angle_to_matrix(angle)
+    inp['extrinsics_aug'] = rep(tform @ inputs['extrinsics'])
+    disp = rep(torch.cat(ex['disp'], 1))
+    H, W = disp.shape[-2:]
+    px = B * 6 * H * W * 4
+    peak, how = peak_gbs()
+
+    def report(name, ms, nbytes):
+        gbs = nbytes / ms / 1e6
+        print('%-16s B=%d  %7.3f ms  %7.1f MB alg  %7.1f GB/s  %.3f of %s HBM peak (%.0f GB/s)' %
+              (name, B, ms, nbytes / 1e6, gbs, gbs / peak, how, peak), flush=True)
+
+    # to_depth
+    d_leaf = disp.clone().requires_grad_(True)
+    depth = view.to_depth(cfg, d_leaf, inp[('K', 0)])
+    up = torch.randn_like(depth)
+    report('to_depth_fwd', timed(lambda: view.to_depth(cfg, disp, inp[('K', 0)]), args.iters), 2 * px)
+    report('to_depth_bwd', timed(lambda: torch.autograd.grad(depth, d_leaf, up, retain_graph=True), args.iters), 3 * px)
+    # smoothness
+    sm = view.smooth_loss(inp[('color', 0, 0)], d_leaf)
+    ups = torch.ones_like(sm)
+    report('smooth_fwd', timed(lambda: view.smooth_loss(inp[('color', 0, 0)], disp), args.iters), 4 * px)
+    report('smooth_bwd', timed(lambda: torch.autograd.grad(sm, d_leaf, ups, retain_graph=True), args.iters), 5 * px)
+    # depth synthesis: novel-view depth = the camera's own depth perturbed by 5 %
+    dep = depth.detach().clone().requires_grad_(True)
+    aug = (depth.detach() * (1.0 + 0.1 * (torch.rand_like(depth) - 0.5))).requires_grad_(True)
+    con, sm2, _ = view.depth_syn_loss(cfg, inp, dep, aug, disp)
+    upc = torch.ones_like(con)
+    with torch.no_grad():
+        report('depth_syn_fwd', timed(lambda: view.depth_syn_loss(cfg, inp, dep, aug, disp), args.iters), 4 * px)
+    report('depth_syn_bwd', timed(lambda: torch.autograd.grad(con, [dep, aug], upc, retain_graph=True), args.iters), 5 * px)
+    print('depth_con_loss per camera:', [round(float(c), 4) for c in con])
+    print('(depth_syn_fwd includes the colour-less smoothness of disp_aug and two batched 4x4 inversions in torch)')
+
+
+if __name__ == '__main__':
+    main()
