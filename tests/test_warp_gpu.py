@@ -470,3 +470,24 @@ def test_depth_syn_loss_module_dropin():
         assert len(tv[('tform_depth', 0)]) == 3 and tv[('tform_depth_mask', 0)][0].shape == (2, 1, 48, 64)
         ga, = torch.autograd.grad(l1, augs[cam])
         assert H.rel_err(ga.cpu(), L['depth_con_coeff'] * g['d_aug'][:, cam:cam + 1] / g['w'][cam, 0]) < 1e-4
+
+
+def test_training_mode_matches_separate_launches():
+    """vfd_warp_loss_train_fwd/_bwd (sums + unit-upstream gradients in one launch, scaled afterwards) against the
+    separate vfd_warp_loss_fwd / vfd_warp_loss_bwd launches on the same inputs: identical decisions, sums to fp32
+    rounding, gradients within 1e-5 of their scale."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    cfg, inp, ex = _rig(96, 160, 2, seed=33)
+    res = []
+    for fused in (True, False):
+        view._WarpLoss.fuse_training = fused
+        try:
+            t, det, g = _run_gpu(cfg, inp, ex, dev)
+        finally:
+            view._WarpLoss.fuse_training = True
+        res.append((float(t), det['terms'].cpu(), g))
+    assert abs(res[0][0] - res[1][0]) / abs(res[1][0]) < 1e-6
+    assert H.rel_err(res[0][1], res[1][1]) < 1e-6
+    for a, b in zip(res[0][2], res[1][2]):
+        assert H.rel_err(a, b) < 1e-5

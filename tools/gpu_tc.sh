@@ -1,2 +1,9 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_warp_gpu.py -m gpu -x -q -k "depth_syn or to_depth or smooth or dropin" > gpurun_out/pytest_new.log 2>&1; echo "pytest_new rc=$?"; tail -40 gpurun_out/pytest_new.log
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest_gpu rc=$?"; tail -5 gpurun_out/pytest_gpu.log
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench.log 2>&1; echo "bench rc=$?"; tail -3 gpurun_out/bench.log | cut -c1-200
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench.log').read().strip().splitlines()[-1])
+print('value',d['value'],'ms',d['ms_per_step'],'e2e',d['e2e']['value'], 'glue', d['config'].get('torch_glue_ms_per_step'), 'launches', d['gpu_launches'])
+for k,v in d['kernels'].items(): print('%-26s %.3f ms'%(k,v['ms_per_step']))
+PY

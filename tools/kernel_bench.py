@@ -34,6 +34,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--dataset', default='ddad')
     ap.add_argument('--only', default='')
+    ap.add_argument('--sort', default='', help="experiment: reorder the compact lists by 'rowmajor' or 'morton' pixel key")
     args = ap.parse_args()
     dev = torch.device('cuda:0')
     B = args.batch
@@ -84,6 +85,30 @@ def main():
     # compact lists + fused gather/MLP kernels
     cnt8, slot, idx_no, idx_ov, totals, table = ops.voxel_classify(mask_small, K, Einv, g, sizes=False, table=True)
     m1, m2 = totals.tolist()
+    if args.sort:
+        rows = B * N
+        t32 = torch.view_as_real(table).view(torch.int32).reshape(-1)
+        off = t32[:rows * 2 * 4].view(2, rows, 4)
+        meta = t32[rows * 2 * 8:rows * 2 * 8 + rows * 2 * 2].view(2, rows, 2)
+
+        def reorder(idx, m):
+            r = idx[:m]
+            pix = off[0, r, 0] // g.C
+            y0, x0 = (pix // g.w).long(), (pix % g.w).long()
+            if args.sort == 'morton':
+                code = torch.zeros_like(x0)
+                for bit in range(7):
+                    code |= ((x0 >> bit) & 1) << (2 * bit)
+                    code |= ((y0 >> bit) & 1) << (2 * bit + 1)
+            else:
+                code = y0 * g.w + x0
+            key = meta[0, r, 0].long() * 16384 + code
+            order = torch.sort(key, stable=True).indices
+            idx[:m] = r[order]
+
+        reorder(idx_no, m1)
+        reorder(idx_ov, m2)
+        print('lists reordered by', args.sort, flush=True)
     w_no, b_no = torch.randn(g.Cv, c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
     w_ov, b_ov = torch.randn(g.Cv, 2 * c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
     fvol = torch.empty(B, N, g.Cv, device=dev)

@@ -16,8 +16,11 @@ KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
 ABI = [('voxel_fuse_fwd', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_bwd', 'vfd_voxel_fuse_bwd'),
        ('voxel_fuse_reduce', 'vfd_voxel_fuse_bwd'), ('ray_sample_fwd', 'vfd_ray_sample_fwd'),
        ('ray_sample_bwd', 'vfd_ray_sample_bwd'), ('warp_stats', 'vfd_warp_stats'),
-       ('warp_loss_fwd', 'vfd_warp_loss_fwd'), ('warp_loss_bwd', 'vfd_warp_loss_bwd'),
-       ('warp_dT_reduce', 'vfd_warp_loss_bwd'), ('voxel_count', 'vfd_voxel_classify'),
+       ('warp_loss_fwd', 'vfd_warp_loss_fwd'), ('warp_loss_bwd_kernel<1>', 'vfd_warp_loss_train_fwd'),
+       ('warp_loss_bwd_kernel<true>', 'vfd_warp_loss_train_fwd'), ('warp_loss_bwd', 'vfd_warp_loss_bwd'),
+       ('warp_grad_combine', 'vfd_warp_loss_train_bwd'), ('warp_dT_reduce', 'vfd_warp_loss_train_bwd'),
+       ('to_depth_fwd', 'vfd_to_depth_fwd'), ('to_depth_bwd', 'vfd_to_depth_bwd'),
+       ('depth_syn_fwd', 'vfd_depth_syn_fwd'), ('depth_syn_bwd', 'vfd_depth_syn_bwd'), ('voxel_count', 'vfd_voxel_classify'),
        ('voxel_scan', 'vfd_voxel_classify'), ('voxel_slot', 'vfd_voxel_classify'),
        ('smooth_mean', 'vfd_smooth_loss_fwd'), ('smooth_loss_kernel', 'vfd_smooth_loss_fwd'),
        ('smooth_bwd', 'vfd_smooth_loss_bwd'), ('voxel_gather_fwd', 'vfd_voxel_gather_depth_fwd'),

@@ -70,5 +70,7 @@ class WarpWorkload:
         imgs, depth, mask, noise = 3 * 3 * px, px, px, 2 * px
         return {'vfd_warp_stats': imgs + depth + mask, 'vfd_warp_loss_fwd': imgs + depth + mask + noise,
                 'vfd_warp_loss_bwd': imgs + depth + mask + noise + px,
+                # training mode: sums and per-set gradients in one launch (3 gradient maps out), then the combine
+                'vfd_warp_loss_train_fwd': imgs + depth + mask + noise + 3 * px, 'vfd_warp_loss_train_bwd': 4 * px,
                 'vfd_smooth_loss_fwd': 3 * px + px, 'vfd_smooth_loss_bwd': 3 * px + 2 * px,
                 'vfd_to_depth_fwd': 2 * px, 'vfd_to_depth_bwd': 3 * px}

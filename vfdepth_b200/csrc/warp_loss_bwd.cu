@@ -22,6 +22,10 @@ struct LossBwdArgs {
     float* d_depth;
     float* d_T;
     float* partial;       // [B*n_call][tiles][kMaxW*12]
+    // fused forward + backward (training): the loss sums leave this kernel too, gradients are written per loss set and
+    // scaled by the upstream once the sums are known
+    double* sums;         // [n_call][8]
+    float* g3;            // [B,n_call,3,H,W] d loss_set / d depth with unit upstream
 };
 
 extern __shared__ __align__(16) float vfd_warp_smem[];
@@ -53,11 +57,17 @@ __device__ __forceinline__ float pick5(const float (*v)[3], int k, int c) {
     return r;
 }
 
+// FUSED: training mode.  One launch evaluates the loss sums (what warp_loss_fwd_kernel computes) AND the gradients with
+// unit upstream, per loss set (every differentiable image belongs to exactly one set: temporal warps -> reprojection,
+// overlap_0 -> spatial, overlap_+-1 -> spatio-temporal); vfd_warp_loss_train_bwd scales them by d total / d num_set once
+// autograd knows it.  The backward kernel recomputed the whole forward anyway, so the separate forward launch goes away.
+template <bool FUSED>
 __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const LossBwdArgs a) {
     using Rg = Region<2>;
     const vfd_warp_desc& d = a.d;
     __shared__ WarpCtx ctx;
     __shared__ float s_dP[kTileThreads / 32][kMaxW * 12];
+    __shared__ double sacc[8];
     float* sm = vfd_warp_smem;
     float* cf = sm + Rg::kFloats;
     const int b = blockIdx.z / d.n_call, ci = blockIdx.z % d.n_call, cam = d.cam0 + ci;
@@ -65,6 +75,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH, ox = tx0 - 2, oy = ty0 - 2;
     warp_ctx_init(ctx, d, a.T, a.params, b, ci);
     for (int i = threadIdx.x; i < (kTileThreads / 32) * kMaxW * 12; i += kTileThreads) (&s_dP[0][0])[i] = 0.f;
+    if (FUSED && threadIdx.x < 8) sacc[threadIdx.x] = 0.0;
     __syncthreads();
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
@@ -72,7 +83,11 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     __syncthreads();
 
     // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
-    const float w_set[3] = {__ldg(a.d_num + ci * 3 + 0), __ldg(a.d_num + ci * 3 + 1), __ldg(a.d_num + ci * 3 + 2)};
+    float w_set[3] = {1.f, 1.f, 1.f};
+    if (!FUSED) {
+        w_set[0] = __ldg(a.d_num + ci * 3 + 0); w_set[1] = __ldg(a.d_num + ci * 3 + 1); w_set[2] = __ldg(a.d_num + ci * 3 + 2);
+    }
+    float facc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int r = threadIdx.x; r < Coef::R; r += kTileThreads) {
         const int x = tx0 - 1 + r % Coef::RW, y = ty0 - 1 + r / Coef::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
@@ -81,6 +96,11 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         for (int k = 0; k < n_src; ++k) nz[k] = __ldg(a.noise + ((size_t)(b * d.n_call + ci) * n_src + k) * HW + p);
         SsimGrad2 g[3];
         const PixelLoss o = pixel_loss<2, true>(sm, d, x, y, ox, oy, __ldg(rmaskp + p), nz, g);
+        if (FUSED && x >= tx0 && x < tx0 + kTileW && y >= ty0 && y < ty0 + kTileH) {   // this CTA's own pixels
+            facc[0] += VFD_MUL(o.reproj, o.automask); facc[1] += o.automask;
+            facc[2] += VFD_MUL(o.spatial, o.sp_mask); facc[3] += o.sp_mask;
+            facc[4] += VFD_MUL(o.st, o.st_mask);      facc[5] += o.st_mask;
+        }
         const float wr = w_set[0] * o.automask, ws = w_set[1] * o.sp_mask, wt = w_set[2] * o.st_mask;
         const bool s1 = o.sel_reproj == 1, t1 = o.sel_st == 1;
 #pragma unroll
@@ -101,7 +121,17 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         cf[Coef::kWgt + 2 * Coef::R + r] = wt;
         reinterpret_cast<int*>(cf)[Coef::kSel + r] = (s1 ? 1 : 0) | (t1 ? 2 : 0);
     }
+    if (FUSED) {   // loss sums: fp32 inside a warp, fp64 above (as warp_loss_fwd_kernel)
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            float v = facc[q];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(&sacc[q], (double)v);
+        }
+    }
     __syncthreads();
+    if (FUSED && threadIdx.x < 6 && sacc[threadIdx.x] != 0.0) atomicAdd(a.sums + ci * 8 + threadIdx.x, sacc[threadIdx.x]);
 
     // ---- phase C: gather the coefficients at the interior pixel, then back through normalise / sampler / projection ----
     const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
@@ -172,7 +202,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         const float dep = __ldg(depth + y * W + x);
         X[0] = VFD_MUL(dep, ray[0]); X[1] = VFD_MUL(dep, ray[1]); X[2] = VFD_MUL(dep, ray[2]);
     }
-    float gdepth = 0.f;
+    float gdepth = 0.f, gset[3] = {0.f, 0.f, 0.f};
     for (int j = 0; j < ctx.NW; ++j) {
         if (!ctx.active[j]) continue;      // CTA-uniform
         float dP[12];
@@ -210,7 +240,14 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
                     const float a1 = P[4] * ray[0] + P[5] * ray[1] + P[6] * ray[2];
                     const float a2 = P[8] * ray[0] + P[9] * ray[1] + P[10] * ray[2];
                     const float t2 = P[11] + 1e-7f;
-                    gdepth += (gix * (a0 * t2 - P[3] * a2) + giy * (a1 * t2 - P[7] * a2)) * inv * inv;
+                    const float gj = (gix * (a0 * t2 - P[3] * a2) + giy * (a1 * t2 - P[7] * a2)) * inv * inv;
+                    if (FUSED) {
+                        if (k < VFD_WARP_SRC) gset[0] += gj;
+                        else if (k == VFD_WARP_SRC) gset[1] += gj;
+                        else gset[2] += gj;
+                    } else {
+                        gdepth += gj;
+                    }
                     const float dc[3] = {dc0, dc1, dc2};
 #pragma unroll
                     for (int rr = 0; rr < 3; ++rr) {
@@ -241,7 +278,14 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
             if (!(lane & 1) && (lane >> 1) < 12) s_dP[wid][j * 12 + (lane >> 1)] = v[0];
         }
     }
-    if (live) a.d_depth[(size_t)(b * d.n_call + ci) * HW + y * W + x] = gdepth;
+    if (live) {
+        if (FUSED) {
+            float* g3 = a.g3 + (size_t)(b * d.n_call + ci) * 3 * HW + y * W + x;
+            g3[0] = gset[0]; g3[HW] = gset[1]; g3[2 * HW] = gset[2];
+        } else {
+            a.d_depth[(size_t)(b * d.n_call + ci) * HW + y * W + x] = gdepth;
+        }
+    }
     __syncthreads();
     const int ntile = gridDim.x * gridDim.y, tile = blockIdx.y * gridDim.x + blockIdx.x;
     float* part = a.partial + ((size_t)blockIdx.z * ntile + tile) * (kMaxW * 12);
@@ -254,7 +298,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
 }
 
 // d_T[b,ci,j] = K_src^T[:, :3] @ (sum over tiles of dP), tiles added in index order with fp64 accumulators.
-__global__ void __launch_bounds__(128) warp_dT_reduce_kernel(const LossBwdArgs a, int ntile) {
+__global__ void __launch_bounds__(128) warp_dT_reduce_kernel(const LossBwdArgs a, int ntile, bool scale_sets) {
     const vfd_warp_desc& d = a.d;
     __shared__ double s_sum[kMaxW * 12];
     const int bc = blockIdx.x, b = bc / d.n_call, ci = bc % d.n_call, cam = d.cam0 + ci;
@@ -263,6 +307,11 @@ __global__ void __launch_bounds__(128) warp_dT_reduce_kernel(const LossBwdArgs a
     for (int i = threadIdx.x; i < NW * 12; i += blockDim.x) {
         double s = 0.0;
         for (int t = 0; t < ntile; ++t) s += (double)part[(size_t)t * (kMaxW * 12) + i];
+        if (scale_sets) {   // partials of the fused kernel carry unit upstream: apply d total / d num of the warp's set
+            const int j = i / 12;
+            const int set = j < d.n_src ? 0 : ((j - d.n_src) / VFD_WARP_NBR == 0 ? 1 : 2);
+            s *= (double)__ldg(a.d_num + ci * 3 + set);
+        }
         s_sum[i] = s;
     }
     __syncthreads();
@@ -279,6 +328,17 @@ __global__ void __launch_bounds__(128) warp_dT_reduce_kernel(const LossBwdArgs a
         }
         a.d_T[((size_t)bc * NW + j) * 16 + i % 16] = v;
     }
+}
+
+// d_depth = sum over the three loss sets of (d total / d num_set) * g3_set
+__global__ void __launch_bounds__(256) warp_grad_combine_kernel(const LossBwdArgs a) {
+    const vfd_warp_desc& d = a.d;
+    const int bc = blockIdx.y, ci = bc % d.n_call, HW = d.H * d.W;
+    const float w0 = __ldg(a.d_num + ci * 3 + 0), w1 = __ldg(a.d_num + ci * 3 + 1), w2 = __ldg(a.d_num + ci * 3 + 2);
+    const float* g = a.g3 + (size_t)bc * 3 * HW;
+    float* o = a.d_depth + (size_t)bc * HW;
+    for (int p = blockIdx.x * 256 + threadIdx.x; p < HW; p += gridDim.x * 256)
+        o[p] = w0 * __ldg(g + p) + w1 * __ldg(g + HW + p) + w2 * __ldg(g + 2 * HW + p);
 }
 
 int check_warp_desc(const vfd_warp_desc* d);   // warp_stats.cu
@@ -310,12 +370,53 @@ extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, con
     const size_t smem = bwd_smem_bytes();
     // > 48 KB of dynamic shared memory needs the opt-in; setting it is idempotent and per device, so it is simply
     // repeated on every call (no global state to keep in step with the current device)
-    if (cudaFuncSetAttribute(warp_loss_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    if (cudaFuncSetAttribute(warp_loss_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return VFD_ERR_CUDA;
     dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);
-    warp_loss_bwd_kernel<<<grid, kTileThreads, smem, st>>>(a);
+    warp_loss_bwd_kernel<false><<<grid, kTileThreads, smem, st>>>(a);
     VFD_CHECK_LAUNCH();
-    warp_dT_reduce_kernel<<<d->B * d->n_call, 128, 0, st>>>(a, (int)(grid.x * grid.y));
+    warp_dT_reduce_kernel<<<d->B * d->n_call, 128, 0, st>>>(a, (int)(grid.x * grid.y), false);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+extern "C" int vfd_warp_loss_train_fwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
+                                       const float* raw, const float* noise, double* sums, float* g3, void* ws,
+                                       size_t ws_bytes, void* stream) {
+    int rc = check_warp_desc(d);
+    if (rc) return rc;
+    if (!depth || !T || !params || !raw || !noise || !sums || !g3 || !ws) return VFD_ERR_NULL;
+    if (reinterpret_cast<uintptr_t>(raw) & 15) return VFD_ERR_ALIGN;
+    if (ws_bytes < vfd_warp_bwd_workspace_bytes(d)) return VFD_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(sums, 0, (size_t)d->n_call * 8 * sizeof(double), st) != cudaSuccess) return VFD_ERR_CUDA;
+    LossBwdArgs a = {};
+    a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise;
+    a.sums = sums; a.g3 = g3; a.partial = (float*)ws;
+    const size_t smem = bwd_smem_bytes();
+    if (cudaFuncSetAttribute(warp_loss_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return VFD_ERR_CUDA;
+    dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);
+    warp_loss_bwd_kernel<true><<<grid, kTileThreads, smem, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+extern "C" int vfd_warp_loss_train_bwd(const vfd_warp_desc* d, const float* d_num, const float* g3, const void* ws,
+                                       size_t ws_bytes, float* d_depth, float* d_T, void* stream) {
+    int rc = check_warp_desc(d);
+    if (rc) return rc;
+    if (!d_num || !g3 || !ws || !d_depth || !d_T) return VFD_ERR_NULL;
+    if (ws_bytes < vfd_warp_bwd_workspace_bytes(d)) return VFD_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    LossBwdArgs a = {};
+    a.d = *d; a.d_num = d_num; a.g3 = const_cast<float*>(g3); a.partial = (float*)const_cast<void*>(ws);
+    a.d_depth = d_depth; a.d_T = d_T;
+    int bx = (d->H * d->W + 1023) / 1024;
+    if (bx > 256) bx = 256;
+    warp_grad_combine_kernel<<<dim3(bx, d->B * d->n_call), 256, 0, st>>>(a);
+    const int tiles = ((d->W + kTileW - 1) / kTileW) * ((d->H + kTileH - 1) / kTileH);
+    warp_dT_reduce_kernel<<<d->B * d->n_call, 128, 0, st>>>(a, tiles, true);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }

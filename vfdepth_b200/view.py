@@ -99,6 +99,8 @@ def _alloc_views(wi, n_call, want):
 class _WarpLoss(torch.autograd.Function):
     """(depth, T) -> masked-loss numerators [n_call,3] (differentiable) and denominators [n_call,3]."""
 
+    fuse_training = True    # False: separate vfd_warp_loss_fwd / vfd_warp_loss_bwd launches (tests compare the two)
+
     @staticmethod
     def forward(ctx, depth, T, wi, params, raw, noise, cam0, views_struct):
         n_call = depth.shape[1]
@@ -107,11 +109,23 @@ class _WarpLoss(torch.autograd.Function):
         _chk(noise, 'noise', (wi.B, n_call, wi.n_src, wi.H, wi.W))
         sums = torch.empty((n_call, 8), device=wi.device, dtype=torch.float64)
         d = wi.desc(cam0, n_call)
-        vptr = ctypes.byref(views_struct) if views_struct is not None else None
-        _lib.call('vfd_warp_loss_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
-                  _lib.ptr(raw), _lib.ptr(noise), _lib.ptr(sums), vptr, _stream())
         ctx.wi, ctx.cam0 = wi, cam0
-        ctx.save_for_backward(depth, T, params, raw, noise)
+        # training: one launch computes the sums and the unit-upstream gradients (vfd_warp_loss_train_fwd)
+        ctx.fused = views_struct is None and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]) and _WarpLoss.fuse_training
+        if ctx.fused:
+            nbytes = _lib.load().vfd_warp_bwd_workspace_bytes(ctypes.byref(d))
+            ws = torch.empty((max(nbytes, 4) // 4,), device=wi.device, dtype=torch.float32)
+            g3 = torch.empty((wi.B, n_call, 3, wi.H, wi.W), device=wi.device)
+            _lib.call('vfd_warp_loss_train_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
+                      _lib.ptr(raw), _lib.ptr(noise), _lib.ptr(sums), _lib.ptr(g3), _lib.ptr(ws), ctypes.c_size_t(nbytes),
+                      _stream())
+            ctx.nbytes, ctx.shapes = nbytes, (depth.shape, T.shape)
+            ctx.save_for_backward(g3, ws)
+        else:
+            vptr = ctypes.byref(views_struct) if views_struct is not None else None
+            _lib.call('vfd_warp_loss_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(params),
+                      _lib.ptr(raw), _lib.ptr(noise), _lib.ptr(sums), vptr, _stream())
+            ctx.save_for_backward(depth, T, params, raw, noise)
         s = sums.float()
         num, den = s[:, 0:6:2].contiguous(), s[:, 1:6:2].contiguous()
         ctx.mark_non_differentiable(den)
@@ -119,11 +133,20 @@ class _WarpLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, d_num, _):
-        depth, T, params, raw, noise = ctx.saved_tensors
         wi = ctx.wi
+        d_num = d_num.float().contiguous()
+        if ctx.fused:
+            g3, ws = ctx.saved_tensors
+            n_call = g3.shape[1]
+            d = wi.desc(ctx.cam0, n_call)
+            d_depth = torch.empty(ctx.shapes[0], device=wi.device)
+            d_T = torch.empty(ctx.shapes[1], device=wi.device)
+            _lib.call('vfd_warp_loss_train_bwd', ctypes.byref(d), _lib.ptr(d_num), _lib.ptr(g3), _lib.ptr(ws),
+                      ctypes.c_size_t(ctx.nbytes), _lib.ptr(d_depth), _lib.ptr(d_T), _stream())
+            return d_depth, d_T, None, None, None, None, None, None
+        depth, T, params, raw, noise = ctx.saved_tensors
         n_call = depth.shape[1]
         d = wi.desc(ctx.cam0, n_call)
-        d_num = d_num.float().contiguous()
         d_depth = torch.empty_like(depth)
         d_T = torch.empty_like(T)
         nbytes = _lib.load().vfd_warp_bwd_workspace_bytes(ctypes.byref(d))
