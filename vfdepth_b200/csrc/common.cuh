@@ -52,6 +52,30 @@ __device__ __forceinline__ void red_add_f1(float* p, float a) {
 
 __device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 
+// ---- packed fp32 (fma.rn.f32x2 / mul.rn.f32x2, sm_100+): two IEEE results per instruction, bit-identical to scalar ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float a, float b) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 r, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
+__device__ __forceinline__ f32x2 mul2p(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 fma2p(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+// acc += w * v with w already splatted into both halves
+__device__ __forceinline__ void f4_fma_w2(float4& acc, f32x2 w2, const float4& v) {
+    unpack2(fma2p(w2, pack2(v.x, v.y), pack2(acc.x, acc.y)), acc.x, acc.y);
+    unpack2(fma2p(w2, pack2(v.z, v.w), pack2(acc.z, acc.w)), acc.z, acc.w);
+}
+
 __device__ __forceinline__ void f4_fma(float4& acc, float w, const float4& v) {
     acc.x = fmaf(w, v.x, acc.x);
     acc.y = fmaf(w, v.y, acc.y);

@@ -88,6 +88,16 @@ __device__ __forceinline__ void corner_weights(const RaySlot& s, float* w) {
     w[4] = a * s.fz; w[5] = b * s.fz; w[6] = c * s.fz; w[7] = d * s.fz;
 }
 
+// the same eight weights, each splatted into both halves of a packed register (products formed exactly as above)
+__device__ __forceinline__ void corner_weights2(const RaySlot& s, f32x2* w) {
+    const float ex = 1.f - s.fx, ey = 1.f - s.fy, ez = 1.f - s.fz;
+    const f32x2 ex2 = pack2(ex, ex), fx2 = pack2(s.fx, s.fx), ey2 = pack2(ey, ey), fy2 = pack2(s.fy, s.fy);
+    const f32x2 ez2 = pack2(ez, ez), fz2 = pack2(s.fz, s.fz);
+    const f32x2 a = mul2p(ex2, ey2), b = mul2p(fx2, ey2), c = mul2p(ex2, fy2), d = mul2p(fx2, fy2);
+    w[0] = mul2p(a, ez2); w[1] = mul2p(b, ez2); w[2] = mul2p(c, ez2); w[3] = mul2p(d, ez2);
+    w[4] = mul2p(a, fz2); w[5] = mul2p(b, fz2); w[6] = mul2p(c, fz2); w[7] = mul2p(d, fz2);
+}
+
 extern __shared__ __align__(16) unsigned char vfd_ray_smem[];
 
 static size_t ray_smem_bytes(int D) { return (size_t)kRayWarps * D * sizeof(RaySlot); }
@@ -281,7 +291,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
                                         ? ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC)
                                         : f4_zero();
                     }
-                    float w[8];
+                    float w[8];     // scalar here: the packed form costs 12 registers (76 vs 64) and occupancy
                     corner_weights(s, w);
 #pragma unroll
                     for (int k = 0; k < 8; ++k) f4_fma(r, w[k], vv[k]);
@@ -346,10 +356,10 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
                             cur_base = s.base;
                             cur_corners = s.corners;
                         }
-                        float w[8];
-                        corner_weights(s, w);
+                        f32x2 w[8];
+                        corner_weights2(s, w);
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) f4_fma(acc[k], w[k], g[i]);
+                        for (int k = 0; k < 8; ++k) f4_fma_w2(acc[k], w[k], g[i]);
                     }
                 }
 #pragma unroll

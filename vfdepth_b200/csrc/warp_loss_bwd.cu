@@ -297,16 +297,29 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     }
 }
 
-// d_T[b,ci,j] = K_src^T[:, :3] @ (sum over tiles of dP), tiles added in index order with fp64 accumulators.
-__global__ void __launch_bounds__(128) warp_dT_reduce_kernel(const LossBwdArgs a, int ntile, bool scale_sets) {
+// d_T[b,ci,j] = K_src^T[:, :3] @ (sum over tiles of dP): kDtParts threads per element each add a contiguous range of
+// tiles in index order (fp64), the ranges are then added in order -- a fixed summation tree, so d_T is deterministic.
+constexpr int kDtParts = 8, kDtThreads = kMaxW * 12 * kDtParts;
+__global__ void __launch_bounds__(kDtThreads) warp_dT_reduce_kernel(const LossBwdArgs a, int ntile, bool scale_sets) {
     const vfd_warp_desc& d = a.d;
+    __shared__ double s_part[kDtParts][kMaxW * 12];
     __shared__ double s_sum[kMaxW * 12];
     const int bc = blockIdx.x, b = bc / d.n_call, ci = bc % d.n_call, cam = d.cam0 + ci;
     const int NW = warp_count(d);
     const float* part = a.partial + (size_t)bc * ntile * (kMaxW * 12);
+    {
+        const int i = threadIdx.x % (kMaxW * 12), q = threadIdx.x / (kMaxW * 12);
+        const int per = (ntile + kDtParts - 1) / kDtParts, t0 = q * per, t1 = min(ntile, t0 + per);
+        double s = 0.0;
+        if (i < NW * 12)
+            for (int t = t0; t < t1; ++t) s += (double)part[(size_t)t * (kMaxW * 12) + i];
+        s_part[q][i] = s;
+    }
+    __syncthreads();
     for (int i = threadIdx.x; i < NW * 12; i += blockDim.x) {
         double s = 0.0;
-        for (int t = 0; t < ntile; ++t) s += (double)part[(size_t)t * (kMaxW * 12) + i];
+#pragma unroll
+        for (int q = 0; q < kDtParts; ++q) s += s_part[q][i];
         if (scale_sets) {   // partials of the fused kernel carry unit upstream: apply d total / d num of the warp's set
             const int j = i / 12;
             const int set = j < d.n_src ? 0 : ((j - d.n_src) / VFD_WARP_NBR == 0 ? 1 : 2);
@@ -375,7 +388,7 @@ extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, con
     dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);
     warp_loss_bwd_kernel<false><<<grid, kTileThreads, smem, st>>>(a);
     VFD_CHECK_LAUNCH();
-    warp_dT_reduce_kernel<<<d->B * d->n_call, 128, 0, st>>>(a, (int)(grid.x * grid.y), false);
+    warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, (int)(grid.x * grid.y), false);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
@@ -416,7 +429,7 @@ extern "C" int vfd_warp_loss_train_bwd(const vfd_warp_desc* d, const float* d_nu
     if (bx > 256) bx = 256;
     warp_grad_combine_kernel<<<dim3(bx, d->B * d->n_call), 256, 0, st>>>(a);
     const int tiles = ((d->W + kTileW - 1) / kTileW) * ((d->H + kTileH - 1) / kTileH);
-    warp_dT_reduce_kernel<<<d->B * d->n_call, 128, 0, st>>>(a, tiles, true);
+    warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, tiles, true);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
