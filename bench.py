@@ -45,6 +45,7 @@ def parse():
     ap.add_argument('--batch', type=int, default=BATCH)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='launch the resident step eagerly instead of replaying a CUDA graph')
     ap.add_argument('--no-warp', action='store_true', help='time the fusion half only')
     return ap.parse_args()
 
@@ -357,12 +358,32 @@ def run_ours(args):
     for _ in range(max(3, args.warmup)):
         step()
     torch.cuda.synchronize()
+    # the resident step is replayed from a CUDA graph (vfdepth_b200/graph.py): same kernels, no launch gaps
+    run_step, graphed, per_step = step, False, None
+    if not args.no_graph:
+        try:
+            from vfdepth_b200 import graph as vgraph
+            n0 = _lib.launches
+            run_step, _ = vgraph.capture(step, warmup=1)
+            per_step = (_lib.launches - n0) // 2          # one warm-up call + the captured call
+            graphed = True
+            for _ in range(2):
+                run_step()
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001 -- fall back to eager launches, and say so in the line
+            print('bench: CUDA graph capture failed (%s); eager launches' % e, file=sys.stderr, flush=True)
+            run_step, graphed = step, False
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()         # drop the aborted capture's private pool, then re-warm the eager path
+            for _ in range(3):
+                step()
+            torch.cuda.synchronize()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     n0 = _lib.launches
-    ms = timed(step, args.steps, world)
-    launches = _lib.launches - n0
+    ms = timed(run_step, args.steps, world)
+    launches = per_step * args.steps if graphed else _lib.launches - n0
     rigs = args.batch * world * args.steps
     value = rigs / (ms * 1e-3)
 
@@ -412,7 +433,7 @@ def run_ours(args):
                 'config': {'workload': WORKLOAD % (WARP_PART if warp else '', args.batch),
                            'rigs_per_step_per_gpu': args.batch, 'l2': 'inputs and outputs larger than L2 '
                            '(189 MB feature maps, 1.7 GB compact gather rows, 2.4 GB ray samples per step)',
-                           'sharding': 'whole rigs per rank, no data-path collective',
+                           'sharding': 'whole rigs per rank, no data-path collective', 'cuda_graph': graphed,
                            'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms},
                 'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof, 'kernels': kernels}
         if world == 1 and not args.no_cpu_baseline:

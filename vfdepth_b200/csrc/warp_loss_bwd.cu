@@ -93,7 +93,11 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
         float nz[VFD_WARP_SRC] = {0.f, 0.f};
-        for (int k = 0; k < n_src; ++k) nz[k] = __ldg(a.noise + ((size_t)(b * d.n_call + ci) * n_src + k) * HW + p);
+        {   // static indices: a run-time index would put nz[] in local memory
+            const float* np = a.noise + (size_t)(b * d.n_call + ci) * n_src * HW + p;
+            nz[0] = __ldg(np);
+            if (n_src > 1) nz[1] = __ldg(np + HW);
+        }
         SsimGrad2 g[3];
         const PixelLoss o = pixel_loss<2, true>(sm, d, x, y, ox, oy, __ldg(rmaskp + p), nz, g);
         if (FUSED && x >= tx0 && x < tx0 + kTileW && y >= ty0 && y < ty0 + kTileH) {   // this CTA's own pixels

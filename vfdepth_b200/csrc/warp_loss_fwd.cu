@@ -44,7 +44,11 @@ __global__ void __launch_bounds__(kTileThreads, 3) warp_loss_fwd_kernel(const Lo
         const int p = y * W + x;
         const float rmask = __ldg(d.mask + (size_t)(b * d.num_cams + cam) * HW + p);
         float nz[VFD_WARP_SRC] = {0.f, 0.f};
-        for (int k = 0; k < n_src; ++k) nz[k] = __ldg(a.noise + ((size_t)(b * d.n_call + ci) * n_src + k) * HW + p);
+        {   // static indices: a run-time index would put nz[] in local memory
+            const float* np = a.noise + (size_t)(b * d.n_call + ci) * n_src * HW + p;
+            nz[0] = __ldg(np);
+            if (n_src > 1) nz[1] = __ldg(np + HW);
+        }
         const PixelLoss o = pixel_loss<1, false>(sm, d, x, y, ox, oy, rmask, nz, nullptr);
         acc[0] = VFD_MUL(o.reproj, o.automask); acc[1] = o.automask;
         acc[2] = VFD_MUL(o.spatial, o.sp_mask); acc[3] = o.sp_mask;

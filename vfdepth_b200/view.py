@@ -173,6 +173,18 @@ def warp_loss_sums(wi, depth, T, noise, cam0=0, stats=None, want_views=()):
 # --------------------------------------------------------------------------------------------------
 # pose plumbing (models/geometry/pose.py:66-96): 4x4 products on [B,4,4] -- stays torch, differentiable
 # --------------------------------------------------------------------------------------------------
+_INDEX_CACHE = {}
+
+
+def _device_index(idx, device):
+    """a Python index list as a cached device tensor (indexing with a list costs a pageable host->device copy per
+    call, which also cannot be captured in a CUDA graph)"""
+    key = (tuple(idx), str(device))
+    if key not in _INDEX_CACHE:
+        _INDEX_CACHE[key] = torch.tensor(list(idx), dtype=torch.long, device=device)
+    return _INDEX_CACHE[key]
+
+
 def rig_transforms(wi, inputs, cam_T_cam):
     """cam_T_cam {f: [B,cams,4,4]} -> T [B,cams,NW,4,4] in the kernel's warp order (include/vfdepth_b200.h):
     temporal warps first, then for every frame the two neighbours' relative poses ext_inv[nbr] @ ext[cam] (@ T_f)."""
@@ -183,7 +195,7 @@ def rig_transforms(wi, inputs, cam_T_cam):
     rel0 = []
     for k in range(NBR):
         idx = [wi.rel[c][k] if k < len(wi.rel[c]) and wi.rel[c][k] < ncam else c for c in range(ncam)]
-        rel0.append(torch.matmul(Einv[:, idx], E))                      # pose.py:81
+        rel0.append(torch.matmul(Einv[:, _device_index(idx, E.device)], E))                      # pose.py:81
     for fi, f in enumerate(wi.frame_ids):
         for k in range(NBR):
             cols.append(rel0[k] if fi == 0 else torch.matmul(rel0[k], cam_T_cam[f]))   # pose.py:95
@@ -291,7 +303,7 @@ def depth_syn_loss(cfg, inputs, depth, aug_depth, disp_aug, cam0=0, want_views=F
         for i in range(3):
             d.src[c][i] = srcs[i]
         idx.append([max(s, 0) for s in srcs])
-    sel = torch.tensor(idx[cam0:cam0 + n_call], device=depth.device)                 # [n_call,3]
+    sel = _device_index([s_ for row in idx[cam0:cam0 + n_call] for s_ in row], depth.device).view(n_call, 3)
     aug_inv = torch.inverse(inputs['extrinsics_aug'][:, cam0:cam0 + n_call])         # :206
     T = (aug_inv[:, :, None] @ inputs['extrinsics'][:, sel]).contiguous()            # :224  [B,n_call,3,4,4]
     Tinv = torch.inverse(T).contiguous()                                             # :96
