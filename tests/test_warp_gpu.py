@@ -491,3 +491,34 @@ def test_training_mode_matches_separate_launches():
     assert H.rel_err(res[0][1], res[1][1]) < 1e-6
     for a, b in zip(res[0][2], res[1][2]):
         assert H.rel_err(a, b) < 1e-5
+
+
+def test_step_is_cuda_graph_capturable():
+    """the view-synthesis half of a step (to_depth -> warp/loss training mode -> gradients) captured with
+    vfdepth_b200.graph.capture replays to the eager result: no entry point synchronises, allocates or copies from
+    pageable host memory."""
+    from vfdepth_b200 import graph as vgraph
+    from vfdepth_b200 import view
+    dev = _dev()
+    cfg, inp, ex = _rig(64, 96, 2, seed=41)
+    to = lambda t: t.to(dev)
+    inputs = {k: to(v) for k, v in inp.items()}
+    disp = to(torch.cat(ex['disp'], 1))
+    noise = to(torch.stack(ex['noise'], 1))
+    T0 = {f: to(t) for f, t in ex['cam_T_cam'].items()}
+
+    def step():
+        d = disp.detach().requires_grad_(True)
+        Ts = {f: t.detach().requires_grad_(True) for f, t in T0.items()}
+        depth = view.to_depth(cfg, d, inputs[('K', 0)])
+        total, _ = view.warp_and_loss(cfg, inputs, depth, d, Ts, noise)
+        return (total,) + torch.autograd.grad(total, [d] + list(Ts.values()))
+
+    eager = [t.detach().clone() for t in step()]
+    replay, outs = vgraph.capture(step)
+    for _ in range(2):
+        replay()
+    torch.cuda.synchronize()
+    assert abs(float(outs[0]) - float(eager[0])) / abs(float(eager[0])) < 1e-6
+    for a, b in zip(outs[1:], eager[1:]):
+        assert H.rel_err(a.detach().cpu(), b.cpu()) < 1e-5
