@@ -256,6 +256,14 @@ int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* color, const
 int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* color, const float* disp, const double* img_sum,
                         const float* d_smooth, double* gdot, float* d_disp, void* stream);
 
+/* Training mode of the smoothness: the means, then ONE stencil pass that yields the loss sums, the gradient map
+ * g [B,cams,H,W] with unit upstream and gdot [B*cams] f64; vfd_smooth_loss_train_bwd applies d_smooth [cams]:
+ * d_disp = d_smooth[c] * (g / den - gdot / (den^2 HW)).  color may be NULL as above. */
+int vfd_smooth_loss_train_fwd(int B, int cams, int H, int W, const float* color, const float* disp, double* img_sum,
+                              double* sums, double* gdot, float* g, void* stream);
+int vfd_smooth_loss_train_bwd(int B, int cams, int H, int W, const double* img_sum, const double* gdot, const float* g,
+                              const float* d_smooth, float* d_disp, void* stream);
+
 /* --------------------------------------------------------------------------------------------------
  * Disparity -> metric depth (models/vfdepth.py:277-288 to_depth, called per camera and scale at :266-275), all cameras
  * of the batch at once:

@@ -79,6 +79,10 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.vfd_smooth_loss_fwd(1, 6, 8, 8, null, null, null, null, null) == -1      # colour may be NULL, disp not
     assert lib.vfd_smooth_loss_fwd(1, 6, 1, 8, null, null, null, null, null) == -2
     assert lib.vfd_smooth_loss_bwd(1, 6, 8, 8, null, null, null, null, null, null, null) == -1
+    assert lib.vfd_smooth_loss_train_fwd(1, 6, 8, 8, null, null, null, null, null, null, null) == -1
+    assert lib.vfd_smooth_loss_train_bwd(1, 6, 8, 8, null, null, null, null, null, null) == -1
+    assert lib.vfd_warp_loss_train_fwd(null, null, null, null, null, null, null, null, null, ctypes.c_size_t(0), null) == -1
+    assert lib.vfd_warp_loss_train_bwd(null, null, null, null, ctypes.c_size_t(0), null, null, null) == -1
     f = ctypes.c_float
     assert lib.vfd_to_depth_fwd(1, 6, 8, 8, 8, 8, null, null, f(1.5), f(200.0), f(300.0), null, null) == -1
     assert lib.vfd_to_depth_fwd(1, 6, 8, 8, 4, 8, null, null, f(1.5), f(200.0), f(300.0), null, null) == -2

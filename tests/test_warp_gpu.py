@@ -323,11 +323,16 @@ def test_smooth_loss_matches_oracle(B, n, Hh, W):
     d_ref = disp.clone().requires_grad_(True)
     ref = torch.stack([orc.edge_smooth_loss(color[:, c], d_ref[:, c:c + 1]) for c in range(n)])
     g_ref, = torch.autograd.grad((ref * up).sum(), d_ref)
-    d_got = disp.to(dev).requires_grad_(True)
-    got = view.smooth_loss(color.to(dev), d_got)
-    g_got, = torch.autograd.grad((got * up.to(dev)).sum(), d_got)
-    assert H.rel_err(got.detach().cpu(), ref.detach()) < 1e-4
-    assert H.rel_err(g_got.cpu(), g_ref) < 1e-4
+    for fused in (True, False):      # training mode (one stencil pass) and the separate forward / backward passes
+        view._SmoothLoss.fuse_training = fused
+        try:
+            d_got = disp.to(dev).requires_grad_(True)
+            got = view.smooth_loss(color.to(dev), d_got)
+            g_got, = torch.autograd.grad((got * up.to(dev)).sum(), d_got)
+        finally:
+            view._SmoothLoss.fuse_training = True
+        assert H.rel_err(got.detach().cpu(), ref.detach()) < 1e-4
+        assert H.rel_err(g_got.cpu(), g_ref) < 1e-4
 
 
 @pytest.mark.parametrize('scale', [0, 1, 2])

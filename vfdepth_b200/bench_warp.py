@@ -26,6 +26,7 @@ class WarpWorkload:
         self.inputs = {k: v.to(dev) for k, v in self.h_inputs.items()}
         self.disp, self.noise = self.h_disp.to(dev), self.h_noise.to(dev)
         self.T = {f: v.to(dev) for f, v in self.h_T.items()}
+        self._stage = {}
 
     def step(self, inputs, disp, noise, T):
         n = self.cfg['data']['num_cams']
@@ -43,11 +44,20 @@ class WarpWorkload:
     def step_resident(self):
         return self.step(self.inputs, self.disp, self.noise, self.T)
 
-    def upload(self):
-        """host (pinned) -> device copies of one step's inputs, on the current stream."""
-        nb = dict(non_blocking=True)
-        inputs = {k: v.to(self.dev, **nb) for k, v in self.h_inputs.items()}
-        return (inputs, self.h_disp.to(self.dev, **nb), None, {f: v.to(self.dev, **nb) for f, v in self.h_T.items()})
+    def upload(self, slot=0):
+        """host (pinned) -> device copies of one step's inputs into the staging buffers of `slot`, on the current
+        stream (preallocated: no allocator traffic inside the timed region)."""
+        if slot not in self._stage:
+            mk = lambda t: torch.empty(t.shape, dtype=t.dtype, device=self.dev)
+            self._stage[slot] = ({k: mk(v) for k, v in self.h_inputs.items()}, mk(self.h_disp),
+                                 {f: mk(v) for f, v in self.h_T.items()})
+        inputs, disp, T = self._stage[slot]
+        for k, v in self.h_inputs.items():
+            inputs[k].copy_(v, non_blocking=True)
+        disp.copy_(self.h_disp, non_blocking=True)
+        for f, v in self.h_T.items():
+            T[f].copy_(v, non_blocking=True)
+        return inputs, disp, None, T
 
     def compute(self, staged):
         return self.step(*staged)
@@ -73,4 +83,5 @@ class WarpWorkload:
                 # training mode: sums and per-set gradients in one launch (3 gradient maps out), then the combine
                 'vfd_warp_loss_train_fwd': imgs + depth + mask + noise + 3 * px, 'vfd_warp_loss_train_bwd': 4 * px,
                 'vfd_smooth_loss_fwd': 3 * px + px, 'vfd_smooth_loss_bwd': 3 * px + 2 * px,
+                'vfd_smooth_loss_train_fwd': 3 * px + 2 * px, 'vfd_smooth_loss_train_bwd': 2 * px,
                 'vfd_to_depth_fwd': 2 * px, 'vfd_to_depth_bwd': 3 * px}

@@ -85,7 +85,10 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_loss_kernel(const Smoot
 
 __device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
 
-// g_i = d loss / d nd_i (written to d_disp), and sum_i g_i * disp_i per image
+// g_i = d loss / d nd_i (written to d_disp), and sum_i g_i * disp_i per image.
+// TRAIN: unit upstream, and the loss sums of smooth_loss_kernel from the same taps -- the forward and the backward of a
+// training step share one pass over the images; smooth_bwd_finish_kernel applies the upstream afterwards.
+template <bool TRAIN>
 __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const SmoothArgs a) {
     __shared__ double s_red[kSmoothThreads / 32];
     const int bc = blockIdx.y, cam = bc % a.cams, HW = a.H * a.W, W = a.W, H = a.H;
@@ -93,32 +96,52 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const Smooth
     const float* col = a.color ? a.color + (size_t)bc * 3 * HW : nullptr;
     float* g = a.d_disp + (size_t)bc * HW;
     const float den = image_scale(a, bc);
-    const float up = __ldg(a.d_smooth + cam);
+    const float up = TRAIN ? 1.f : __ldg(a.d_smooth + cam);
     const float ux = up / (float)((double)a.B * H * (W - 1)), uy = up / (float)((double)a.B * (H - 1) * W);
     double acc = 0.0;
+    float sx = 0.f, sy = 0.f;
     for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads) {
         const int x = p % W, y = p / W;
         const float dp = __ldg(d + p), n0 = dp / den;
         float gi = 0.f;
-        if (x + 1 < W) gi += ux * sgn(n0 - __ldg(d + p + 1) / den) * edge_weight(col, HW, p, p + 1);
+        if (x + 1 < W) {
+            const float df = n0 - __ldg(d + p + 1) / den, w = edge_weight(col, HW, p, p + 1);
+            gi += ux * sgn(df) * w;
+            if (TRAIN) sx += fabsf(df) * w;
+        }
         if (x > 0) gi -= ux * sgn(__ldg(d + p - 1) / den - n0) * edge_weight(col, HW, p - 1, p);
-        if (y + 1 < H) gi += uy * sgn(n0 - __ldg(d + p + W) / den) * edge_weight(col, HW, p, p + W);
+        if (y + 1 < H) {
+            const float df = n0 - __ldg(d + p + W) / den, w = edge_weight(col, HW, p, p + W);
+            gi += uy * sgn(df) * w;
+            if (TRAIN) sy += fabsf(df) * w;
+        }
         if (y > 0) gi -= uy * sgn(__ldg(d + p - W) / den - n0) * edge_weight(col, HW, p - W, p);
         g[p] = gi;
         acc += (double)gi * (double)dp;
     }
     const double t = block_sum(acc, s_red);
     if (threadIdx.x == 0) atomicAdd(a.gdot + bc, t);
+    if (TRAIN) {
+        const double tx = block_sum((double)sx, s_red);
+        const double ty = block_sum((double)sy, s_red);
+        if (threadIdx.x == 0) {
+            atomicAdd(a.sums + cam * 2 + 0, tx);
+            atomicAdd(a.sums + cam * 2 + 1, ty);
+        }
+    }
 }
 
-// d_disp_j = g_j / den - (sum_i g_i disp_i) / (den^2 * HW)      (nd = disp / den, den = mean + 1e-8)
-__global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_finish_kernel(const SmoothArgs a) {
+// d_disp_j = up * (g_j / den - (sum_i g_i disp_i) / (den^2 * HW))      (nd = disp / den, den = mean + 1e-8); up = 1
+// unless the gradient map carries unit upstream (training mode: src = that map, d_smooth = the upstream)
+__global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_finish_kernel(const SmoothArgs a, const float* src) {
     const int bc = blockIdx.y, HW = a.H * a.W;
     float* g = a.d_disp + (size_t)bc * HW;
+    const float* gs = src ? src + (size_t)bc * HW : g;
     const float den = image_scale(a, bc);
+    const float up = src ? __ldg(a.d_smooth + bc % a.cams) : 1.f;
     const float shift = (float)(a.gdot[bc] / ((double)den * (double)den * (double)HW));
     for (int p = blockIdx.x * kSmoothThreads + threadIdx.x; p < HW; p += gridDim.x * kSmoothThreads)
-        g[p] = g[p] / den - shift;
+        g[p] = up * (gs[p] / den - shift);
 }
 
 static int check_smooth(int B, int cams, int H, int W) {
@@ -166,8 +189,42 @@ extern "C" int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* c
     a.B = B; a.cams = cams; a.H = H; a.W = W; a.color = color; a.disp = disp;
     a.img_sum = const_cast<double*>(img_sum); a.d_smooth = d_smooth; a.gdot = gdot; a.d_disp = d_disp;
     const dim3 grid = smooth_grid(B, cams, H, W);
-    smooth_bwd_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
-    smooth_bwd_finish_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    smooth_bwd_kernel<false><<<grid, kSmoothThreads, 0, st>>>(a);
+    smooth_bwd_finish_kernel<<<grid, kSmoothThreads, 0, st>>>(a, nullptr);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+// Training mode: loss sums + unit-upstream gradient map g [B,cams,H,W] + gdot in one stencil pass (after the means);
+// vfd_smooth_loss_train_bwd turns g into d_disp once the upstream d_smooth [cams] is known.
+extern "C" int vfd_smooth_loss_train_fwd(int B, int cams, int H, int W, const float* color, const float* disp,
+                                         double* img_sum, double* sums, double* gdot, float* g, void* stream) {
+    int rc = check_smooth(B, cams, H, W);
+    if (rc) return rc;
+    if (!disp || !img_sum || !sums || !gdot || !g) return VFD_ERR_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(img_sum, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
+    if (cudaMemsetAsync(sums, 0, sizeof(double) * cams * 2, st) != cudaSuccess) return VFD_ERR_CUDA;
+    if (cudaMemsetAsync(gdot, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
+    SmoothArgs a = {};
+    a.B = B; a.cams = cams; a.H = H; a.W = W; a.color = color; a.disp = disp; a.img_sum = img_sum; a.sums = sums;
+    a.gdot = gdot; a.d_disp = g;
+    const dim3 grid = smooth_grid(B, cams, H, W);
+    smooth_mean_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    smooth_bwd_kernel<true><<<grid, kSmoothThreads, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+extern "C" int vfd_smooth_loss_train_bwd(int B, int cams, int H, int W, const double* img_sum, const double* gdot,
+                                         const float* g, const float* d_smooth, float* d_disp, void* stream) {
+    int rc = check_smooth(B, cams, H, W);
+    if (rc) return rc;
+    if (!img_sum || !gdot || !g || !d_smooth || !d_disp) return VFD_ERR_NULL;
+    SmoothArgs a = {};
+    a.B = B; a.cams = cams; a.H = H; a.W = W; a.img_sum = const_cast<double*>(img_sum); a.gdot = const_cast<double*>(gdot);
+    a.d_smooth = d_smooth; a.d_disp = d_disp;
+    smooth_bwd_finish_kernel<<<smooth_grid(B, cams, H, W), kSmoothThreads, 0, (cudaStream_t)stream>>>(a, g);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }

@@ -217,6 +217,8 @@ def camera_transforms(wi, target_view, rel_pose_dict, cam):
 class _SmoothLoss(torch.autograd.Function):
     """vfd_smooth_loss_fwd / _bwd: edge-aware smoothness of every camera of the batch, gradient to disp."""
 
+    fuse_training = True    # False: separate forward / backward stencil passes (tests compare the two)
+
     @staticmethod
     def forward(ctx, color, disp):
         B, n, H, W = disp.shape
@@ -226,22 +228,38 @@ class _SmoothLoss(torch.autograd.Function):
         dev = disp.device
         img_sum = torch.empty((B * n,), device=dev, dtype=torch.float64)
         sums = torch.empty((n, 2), device=dev, dtype=torch.float64)
-        _lib.call('vfd_smooth_loss_fwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum), _lib.ptr(sums),
-                  _stream())
         ctx.color = color
-        ctx.save_for_backward(disp, img_sum)
+        ctx.train = bool(ctx.needs_input_grad[1]) and _SmoothLoss.fuse_training
+        if ctx.train:      # loss sums and the unit-upstream gradient map from one stencil pass
+            gdot = torch.empty((B * n,), device=dev, dtype=torch.float64)
+            g = torch.empty_like(disp)
+            _lib.call('vfd_smooth_loss_train_fwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum),
+                      _lib.ptr(sums), _lib.ptr(gdot), _lib.ptr(g), _stream())
+            ctx.save_for_backward(img_sum, gdot, g)
+        else:
+            _lib.call('vfd_smooth_loss_fwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum),
+                      _lib.ptr(sums), _stream())
+            ctx.save_for_backward(disp, img_sum)
         out = sums[:, 0] / float(B * H * (W - 1)) + sums[:, 1] / float(B * (H - 1) * W)
         return out.float()
 
     @staticmethod
     def backward(ctx, d_smooth):
+        d_smooth = d_smooth.float().contiguous()
+        if ctx.train:
+            img_sum, gdot, g = ctx.saved_tensors
+            B, n, H, W = g.shape
+            d_disp = torch.empty_like(g)
+            _lib.call('vfd_smooth_loss_train_bwd', B, n, H, W, _lib.ptr(img_sum), _lib.ptr(gdot), _lib.ptr(g),
+                      _lib.ptr(d_smooth), _lib.ptr(d_disp), _stream())
+            return None, d_disp
         disp, img_sum = ctx.saved_tensors
         color = ctx.color
         B, n, H, W = disp.shape
         gdot = torch.empty((B * n,), device=disp.device, dtype=torch.float64)
         d_disp = torch.empty_like(disp)
         _lib.call('vfd_smooth_loss_bwd', B, n, H, W, _lib.ptr(color), _lib.ptr(disp), _lib.ptr(img_sum),
-                  _lib.ptr(d_smooth.float().contiguous()), _lib.ptr(gdot), _lib.ptr(d_disp), _stream())
+                  _lib.ptr(d_smooth), _lib.ptr(gdot), _lib.ptr(d_disp), _stream())
         return None, d_disp
 
 
