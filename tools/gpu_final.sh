@@ -9,5 +9,5 @@ python tools/kernel_bench_aux.py > gpurun_out/kernel_bench_aux.log 2>&1; echo "k
 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launch.log 2>&1; echo "ncu_launch rc=$?" >> gpurun_out/rc.log
 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k 'regex:voxel_|ray_sample|warp_|smooth_|to_depth' -s 60 -c 20 -o gpurun_out/prof_step python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full.log 2>&1; echo "ncu_full rc=$?" >> gpurun_out/rc.log
+ncu --set full --clock-control none --import-source on -k 'regex:voxel_|ray_sample|warp_|smooth_|to_depth' -s 57 -c 19 -o gpurun_out/prof_step python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full.log 2>&1; echo "ncu_full rc=$?" >> gpurun_out/rc.log
 cat gpurun_out/rc.log; tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; cat gpurun_out/kernel_bench.log

@@ -22,7 +22,7 @@ ABI = [('voxel_fuse_fwd', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_bwd', 'vfd_voxel_f
        ('to_depth_fwd', 'vfd_to_depth_fwd'), ('to_depth_bwd', 'vfd_to_depth_bwd'),
        ('depth_syn_fwd', 'vfd_depth_syn_fwd'), ('depth_syn_bwd', 'vfd_depth_syn_bwd'), ('voxel_count', 'vfd_voxel_classify'),
        ('voxel_scan', 'vfd_voxel_classify'), ('voxel_slot', 'vfd_voxel_classify'),
-       ('smooth_mean', 'vfd_smooth_loss_fwd'), ('smooth_loss_kernel', 'vfd_smooth_loss_fwd'),
+       ('smooth_mean', 'vfd_smooth_loss_train_fwd'), ('smooth_loss_kernel', 'vfd_smooth_loss_fwd'),
        ('smooth_bwd_kernel<1>', 'vfd_smooth_loss_train_fwd'), ('smooth_bwd_kernel<true>', 'vfd_smooth_loss_train_fwd'),
        ('smooth_bwd_finish', 'vfd_smooth_loss_train_bwd'), ('smooth_bwd', 'vfd_smooth_loss_bwd'), ('voxel_gather_fwd', 'vfd_voxel_gather_depth_fwd'),
        ('voxel_gather_bwd', 'vfd_voxel_gather_depth_bwd')]
