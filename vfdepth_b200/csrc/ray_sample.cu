@@ -215,6 +215,15 @@ __device__ __forceinline__ RaySlot make_slot(const vfd_fusion_desc& d, const flo
     return s;
 }
 
+// slot of the column kernels: the eight trilinear weights are formed once by the lane that builds the slot instead
+// of by every one of the 16 lanes that later consume it (48 bytes = three 128-bit shared loads)
+struct __align__(16) RaySlotW {
+    int base;
+    unsigned corners;
+    float w[8];
+    float pad[2];
+};
+
 struct ColTask {
     int b, c, u, d0;
 };
@@ -232,7 +241,7 @@ __device__ __forceinline__ ColTask decode_col(long task, const vfd_fusion_desc& 
 }
 
 template <int KBINS>
-__device__ __forceinline__ void col_phase1(const RayArgs& a, const ColTask& t, int lane, RaySlot* slot) {
+__device__ __forceinline__ void col_phase1(const RayArgs& a, const ColTask& t, int lane, RaySlotW* slot) {
     const vfd_fusion_desc& d = a.d;
     const float* invK = a.invK + (size_t)(t.b * d.num_cams + t.c) * 16;
     const float* E = a.E + (size_t)(t.b * d.num_cams + t.c) * 16;
@@ -251,7 +260,12 @@ __device__ __forceinline__ void col_phase1(const RayArgs& a, const ColTask& t, i
                 go[0] = g[0]; go[1] = g[1]; go[2] = g[2];
             }
         }
-        slot[idx] = s;
+        RaySlotW sw;
+        sw.base = s.base;
+        sw.corners = s.corners;
+        corner_weights(s, sw.w);
+        sw.pad[0] = sw.pad[1] = 0.f;
+        slot[idx] = sw;
     }
 }
 
@@ -263,7 +277,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
     const int q = lane / kLanes, l = lane % kLanes;
     const int H = d.h, W = d.w, D = d.D;
     const long ntasks = (long)d.B * d.num_cams * W * ((D + kBins - 1) / kBins);
-    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * kBins * H;
+    RaySlotW* slot = reinterpret_cast<RaySlotW*>(vfd_ray_smem) + warp * kBins * H;
     const int XC = d.X * CV, YXC = d.Y * XC;
     for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
         const ColTask t = decode_col<kBins>(task, d);
@@ -279,7 +293,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
 #pragma unroll
             for (int k = 0; k < 8; ++k) vv[k] = f4_zero();
             for (int v = 0; v < H; ++v) {
-                const RaySlot s = slot[q * H + v];
+                const RaySlotW s = slot[q * H + v];
                 float4 r = f4_zero();
                 if (s.corners) {
                     if (s.base != cur_base) {
@@ -291,10 +305,8 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
                                         ? ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC)
                                         : f4_zero();
                     }
-                    float w[8];     // scalar here: the packed form costs 12 registers (76 vs 64) and occupancy
-                    corner_weights(s, w);
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) f4_fma(r, w[k], vv[k]);
+                    for (int k = 0; k < 8; ++k) f4_fma(r, s.w[k], vv[k]);
                 }
                 st_stream_f4(o + v * ostride, r);
             }
@@ -311,7 +323,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
     const int q = lane / kLanes, l = lane % kLanes;
     const int H = d.h, W = d.w, D = d.D;
     const long ntasks = (long)d.B * d.num_cams * W * ((D + kBins - 1) / kBins);
-    RaySlot* slot = reinterpret_cast<RaySlot*>(vfd_ray_smem) + warp * kBins * H;
+    RaySlotW* slot = reinterpret_cast<RaySlotW*>(vfd_ray_smem) + warp * kBins * H;
     const int XC = d.X * CV, YXC = d.Y * XC;
     for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += (long)gridDim.x * kRayWarps) {
         const ColTask t = decode_col<kBins>(task, d);
@@ -341,7 +353,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
                 for (int i = 0; i < kPf; ++i) {
                     const int v = v0 + i;
                     if (v >= H) break;
-                    const RaySlot s = slot[q * H + v];
+                    const RaySlotW s = slot[q * H + v];
                     if (s.corners) {
                         if (s.base != cur_base) {
                             if (cur_corners) {
@@ -356,10 +368,8 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
                             cur_base = s.base;
                             cur_corners = s.corners;
                         }
-                        f32x2 w[8];
-                        corner_weights2(s, w);
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) f4_fma_w2(acc[k], w[k], g[i]);
+                        for (int k = 0; k < 8; ++k) f4_fma_w2(acc[k], pack2(s.w[k], s.w[k]), g[i]);
                     }
                 }
 #pragma unroll
@@ -400,7 +410,7 @@ static int launch_ray(const RayArgs& a, bool bwd, cudaStream_t st) {
 #define VFD_RAY_VEC(CVAL)                                                                                   \
     if (d.Cv == CVAL && vec_ok) {                                                                           \
         constexpr int kb = VFD_WARP / (CVAL / 4);                                                           \
-        const size_t vsmem = (size_t)kRayWarps * kb * d.h * sizeof(RaySlot);                                \
+        const size_t vsmem = (size_t)kRayWarps * kb * d.h * sizeof(RaySlotW);                               \
         const long vtasks = (long)d.B * d.num_cams * d.w * ((d.D + kb - 1) / kb);                           \
         const long vblocks = (vtasks + kRayWarps - 1) / kRayWarps;                                          \
         const unsigned vgrid = (unsigned)(vblocks < kRayGrid ? vblocks : kRayGrid);                         \
