@@ -76,6 +76,12 @@ __device__ __forceinline__ void f4_fma_w2(float4& acc, f32x2 w2, const float4& v
     unpack2(fma2p(w2, pack2(v.z, v.w), pack2(acc.z, acc.w)), acc.z, acc.w);
 }
 
+// acc = w * v
+__device__ __forceinline__ void f4_mul_w2(float4& acc, f32x2 w2, const float4& v) {
+    unpack2(mul2p(w2, pack2(v.x, v.y)), acc.x, acc.y);
+    unpack2(mul2p(w2, pack2(v.z, v.w)), acc.z, acc.w);
+}
+
 __device__ __forceinline__ void f4_fma(float4& acc, float w, const float4& v) {
     acc.x = fmaf(w, v.x, acc.x);
     acc.y = fmaf(w, v.y, acc.y);

@@ -363,13 +363,15 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
                                     if (cur_corners & (1u << k))
                                         red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
                             }
-#pragma unroll
-                            for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
                             cur_base = s.base;
                             cur_corners = s.corners;
-                        }
+                            // new cell: the accumulators start from the product (same value as 0 + w * g)
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) f4_fma_w2(acc[k], pack2(s.w[k], s.w[k]), g[i]);
+                            for (int k = 0; k < 8; ++k) f4_mul_w2(acc[k], pack2(s.w[k], s.w[k]), g[i]);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) f4_fma_w2(acc[k], pack2(s.w[k], s.w[k]), g[i]);
+                        }
                     }
                 }
 #pragma unroll
