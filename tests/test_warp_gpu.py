@@ -37,8 +37,8 @@ def _golden():
                                        cam_T_cam={-1: g['T_m1'], 1: g['T_p1']}), g
 
 
-def _rig(height, width, batch, seed, **over):
-    cfg = vcfg.default_config('ddad', batch_size=batch, training__height=height, training__width=width,
+def _rig(height, width, batch, seed, dataset='ddad', **over):
+    cfg = vcfg.default_config(dataset, batch_size=batch, training__height=height, training__width=width,
                               training__focal_length_scale=300 * width / 640, **over)
     inp, ex = make_rig(cfg, seed=seed, with_feats=False)
     return cfg, inp, ex
@@ -180,13 +180,13 @@ def _terms(det_ref):
                          for c in range(6)], dtype=torch.float64)
 
 
-def _standard_case(dev, height, width, batch, seed):
+def _standard_case(dev, height, width, batch, seed, dataset='ddad'):
     """The reference's own configuration (3 frames, spatio + spatio-temporal, intensity alignment).
     1. against the plain fp32 oracle: images within tolerance, masks bit-exact, the three per-pixel decisions identical
        except at near-ties (few, and each with a tiny oracle margin);
     2. against the oracle PINNED to the kernel's decisions (fp32 and fp64): loss map, loss terms, total and every
        gradient (6 depth maps, 2 x [B,6,4,4] poses) within tolerance at every pixel -- no exclusions."""
-    cfg, inp, ex = _rig(height, width, batch, seed)
+    cfg, inp, ex = _rig(height, width, batch, seed, dataset)
     total, det, grads = _run_gpu(cfg, inp, ex, dev, ALL_VIEWS)
     t32, d32, g32 = _run_oracle(cfg, inp, ex)
     _check_views(cfg, det, d32, range(6))
@@ -212,6 +212,26 @@ def _standard_case(dev, height, width, batch, seed):
 
 def test_oracle_midsize_standard_config():
     _standard_case(_dev(), 96, 160, 2, seed=99)
+
+
+def test_nuscenes_shaped_rig():
+    """BASELINE configs[3] shape (nusc_surround_fusion.yaml: 352 x 640, max_depth 80, nuScenes camera ring) at a
+    quarter of the resolution against the oracle, then the training-mode kernel at full resolution against the
+    separate launches."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    _standard_case(dev, 88, 160, 2, seed=7, dataset='nuscenes')
+    cfg, inp, ex = _rig(352, 640, 1, seed=8, dataset='nuscenes')
+    res = []
+    for fused in (True, False):
+        view._WarpLoss.fuse_training = fused
+        try:
+            res.append(_run_gpu(cfg, inp, ex, dev))
+        finally:
+            view._WarpLoss.fuse_training = True
+    assert abs(float(res[0][0]) - float(res[1][0])) / abs(float(res[1][0])) < 1e-6
+    for a, b in zip(res[0][2], res[1][2]):
+        assert H.rel_err(a, b) < 5e-5       # the per-set scaling happens after the sums instead of before
 
 
 def test_full_size_standard_config():
