@@ -32,6 +32,8 @@ extern __shared__ __align__(16) float vfd_warp_smem[];
 
 // coefficient planes over the 1-halo ring (R1 pixels): 3 sets (reproj, spatial, spatio-temporal) x 3 channels x (a,b,c),
 // the set's upstream weight (for the L1 term) and the frame each min selected
+constexpr int kStrip = 8;   // tiles a CTA of the backward walks, top to bottom
+
 struct Coef {
     static constexpr int RW = kTileW + 2, RH = kTileH + 2, R = RW * RH;
     static constexpr int kAbc = 0;                 // [3 sets][3 ch][3][R]
@@ -72,23 +74,50 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     float* cf = sm + Rg::kFloats;
     const int b = blockIdx.z / d.n_call, ci = blockIdx.z % d.n_call, cam = d.cam0 + ci;
     const int W = d.W, H = d.H, HW = H * W, n_src = d.n_src;
-    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH, ox = tx0 - 2, oy = ty0 - 2;
+    // a CTA walks a vertical strip of kStrip tiles: the bottom 4 region rows / 2 ring rows of a tile are the top rows of
+    // the next one, so they are moved up inside shared memory instead of being refilled / recomputed, and the per-CTA
+    // prologue (warp context) is paid once per strip
+    const int tiles_y = (H + kTileH - 1) / kTileH;
+    const int ty_first = blockIdx.y * kStrip, ty_last = min(tiles_y, ty_first + kStrip);
+    const int strip_y0 = ty_first * kTileH, strip_y1 = ty_last * kTileH;
+    const int tx0 = blockIdx.x * kTileW, ox = tx0 - 2;
     warp_ctx_init(ctx, d, a.T, a.params, b, ci);
-    for (int i = threadIdx.x; i < (kTileThreads / 32) * kMaxW * 12; i += kTileThreads) (&s_dP[0][0])[i] = 0.f;
     if (FUSED && threadIdx.x < 8) sacc[threadIdx.x] = 0.0;
     __syncthreads();
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
-    fill_region<2>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW, sm);
-    __syncthreads();
-
-    // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
     float w_set[3] = {1.f, 1.f, 1.f};
     if (!FUSED) {
         w_set[0] = __ldg(a.d_num + ci * 3 + 0); w_set[1] = __ldg(a.d_num + ci * 3 + 1); w_set[2] = __ldg(a.d_num + ci * 3 + 2);
     }
     float facc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int r = threadIdx.x; r < Coef::R; r += kTileThreads) {
+    for (int tyi = ty_first; tyi < ty_last; ++tyi) {
+    const int ty0 = tyi * kTileH, oy = ty0 - 2;
+    const bool cont = tyi > ty_first;
+    if (cont) {
+        // rows 8..11 of the region -> rows 0..3, ring rows 8, 9 -> 0, 1 (sources and destinations are disjoint)
+        float2* img2 = reinterpret_cast<float2*>(sm + Rg::kImg);
+        for (int i = threadIdx.x; i < 3 * kPairs * 4 * Rg::RW; i += kTileThreads) {
+            const int pl = i / (4 * Rg::RW), o = i - pl * (4 * Rg::RW);
+            img2[pl * Rg::R + o] = img2[pl * Rg::R + kTileH * Rg::RW + o];
+        }
+        float* mk = sm + Rg::kOmask;     // the 1 + VFD_WARP_SRC overlap-mask planes and VFD_WARP_SRC colour-mask planes
+        for (int i = threadIdx.x; i < (1 + 2 * VFD_WARP_SRC) * 4 * Rg::RW; i += kTileThreads) {
+            const int pl = i / (4 * Rg::RW), o = i - pl * (4 * Rg::RW);
+            mk[pl * Rg::R + o] = mk[pl * Rg::R + kTileH * Rg::RW + o];
+        }
+        for (int i = threadIdx.x; i < (Coef::kFloats / Coef::R) * 2 * Coef::RW; i += kTileThreads) {
+            const int pl = i / (2 * Coef::RW), o = i - pl * (2 * Coef::RW);
+            cf[pl * Coef::R + o] = cf[pl * Coef::R + kTileH * Coef::RW + o];
+        }
+        __syncthreads();      // the fill below overwrites the rows that were just read
+    }
+    for (int i = threadIdx.x; i < (kTileThreads / 32) * kMaxW * 12; i += kTileThreads) (&s_dP[0][0])[i] = 0.f;
+    fill_region<2>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW, sm, cont ? 4 : 0);
+    __syncthreads();
+
+    // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
+    for (int r = (cont ? 2 * Coef::RW : 0) + threadIdx.x; r < Coef::R; r += kTileThreads) {
         const int x = tx0 - 1 + r % Coef::RW, y = ty0 - 1 + r / Coef::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
@@ -100,7 +129,8 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         }
         SsimGrad2 g[3];
         const PixelLoss o = pixel_loss<2, true>(sm, d, x, y, ox, oy, __ldg(rmaskp + p), nz, g);
-        if (FUSED && x >= tx0 && x < tx0 + kTileW && y >= ty0 && y < ty0 + kTileH) {   // this CTA's own pixels
+        // every ring row is evaluated once per strip: its loss counts here if the row belongs to the strip
+        if (FUSED && x >= tx0 && x < tx0 + kTileW && y >= strip_y0 && y < strip_y1) {
             facc[0] += VFD_MUL(o.reproj, o.automask); facc[1] += o.automask;
             facc[2] += VFD_MUL(o.spatial, o.sp_mask); facc[3] += o.sp_mask;
             facc[4] += VFD_MUL(o.st, o.st_mask);      facc[5] += o.st_mask;
@@ -125,17 +155,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         cf[Coef::kWgt + 2 * Coef::R + r] = wt;
         reinterpret_cast<int*>(cf)[Coef::kSel + r] = (s1 ? 1 : 0) | (t1 ? 2 : 0);
     }
-    if (FUSED) {   // loss sums: fp32 inside a warp, fp64 above (as warp_loss_fwd_kernel)
-#pragma unroll
-        for (int q = 0; q < 6; ++q) {
-            float v = facc[q];
-#pragma unroll
-            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(&sacc[q], (double)v);
-        }
-    }
     __syncthreads();
-    if (FUSED && threadIdx.x < 6 && sacc[threadIdx.x] != 0.0) atomicAdd(a.sums + ci * 8 + threadIdx.x, sacc[threadIdx.x]);
 
     // ---- phase C: gather the coefficients at the interior pixel, then back through normalise / sampler / projection ----
     const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
@@ -291,7 +311,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         }
     }
     __syncthreads();
-    const int ntile = gridDim.x * gridDim.y, tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const int ntile = gridDim.x * tiles_y, tile = tyi * gridDim.x + blockIdx.x;
     float* part = a.partial + ((size_t)blockIdx.z * ntile + tile) * (kMaxW * 12);
     for (int i = threadIdx.x; i < ctx.NW * 12; i += kTileThreads) {
         float v = 0.f;
@@ -299,6 +319,19 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         for (int w = 0; w < kTileThreads / 32; ++w) v += s_dP[w][i];
         part[i] = v;
     }
+    __syncthreads();      // s_dP, the region and the ring are rewritten by the next tile
+    }   // tiles of the strip
+    if (FUSED) {   // loss sums: fp32 inside a warp, fp64 above (as warp_loss_fwd_kernel)
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            float v = facc[q];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(&sacc[q], (double)v);
+        }
+    }
+    __syncthreads();
+    if (FUSED && threadIdx.x < 6 && sacc[threadIdx.x] != 0.0) atomicAdd(a.sums + ci * 8 + threadIdx.x, sacc[threadIdx.x]);
 }
 
 // d_T[b,ci,j] = K_src^T[:, :3] @ (sum over tiles of dP): kDtParts threads per element each add a contiguous range of
@@ -389,10 +422,11 @@ extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, con
     // repeated on every call (no global state to keep in step with the current device)
     if (cudaFuncSetAttribute(warp_loss_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return VFD_ERR_CUDA;
-    dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);
+    const int tiles_x = (d->W + kTileW - 1) / kTileW, tiles_y = (d->H + kTileH - 1) / kTileH;
+    dim3 grid(tiles_x, (tiles_y + kStrip - 1) / kStrip, d->B * d->n_call);
     warp_loss_bwd_kernel<false><<<grid, kTileThreads, smem, st>>>(a);
     VFD_CHECK_LAUNCH();
-    warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, (int)(grid.x * grid.y), false);
+    warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, tiles_x * tiles_y, false);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
@@ -413,7 +447,8 @@ extern "C" int vfd_warp_loss_train_fwd(const vfd_warp_desc* d, const float* dept
     const size_t smem = bwd_smem_bytes();
     if (cudaFuncSetAttribute(warp_loss_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return VFD_ERR_CUDA;
-    dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);
+    const int tiles_x = (d->W + kTileW - 1) / kTileW, tiles_y = (d->H + kTileH - 1) / kTileH;
+    dim3 grid(tiles_x, (tiles_y + kStrip - 1) / kStrip, d->B * d->n_call);
     warp_loss_bwd_kernel<true><<<grid, kTileThreads, smem, st>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;

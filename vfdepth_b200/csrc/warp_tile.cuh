@@ -55,7 +55,7 @@ __device__ __forceinline__ void warp_slot(int j, int n_src, int R, int omask0, i
 // in the reference's order (neighbour k = 0, then 1, view_rendering.py:193-198) and written once.
 template <int HALO, int NSRC>
 __device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
-                                              const float4* __restrict__ raw, float* sm) {
+                                              const float4* __restrict__ raw, float* sm, int row0) {
     using Rg = Region<HALO>;
     constexpr int NWc = NSRC + (1 + NSRC) * VFD_WARP_NBR;
     const int W = d.W, H = d.H, HW = H * W, cam = d.cam0 + ci;
@@ -66,7 +66,7 @@ __device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp
     bool act[NWc];
 #pragma unroll
     for (int j = 0; j < NWc; ++j) act[j] = ctx.active[j] != 0;
-    for (int r = threadIdx.x; r < Rg::R; r += kTileThreads) {
+    for (int r = row0 * Rg::RW + threadIdx.x; r < Rg::R; r += kTileThreads) {      // rows below row0 are already there
         const int x = ox + r % Rg::RW, y = oy + r / Rg::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
@@ -123,9 +123,9 @@ __device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp
 
 template <int HALO>
 __device__ __forceinline__ void fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
-                                            const float4* __restrict__ raw, float* sm) {
-    if (d.n_src == 2) fill_region_n<HALO, 2>(ctx, d, b, ci, ox, oy, raw, sm);
-    else fill_region_n<HALO, 1>(ctx, d, b, ci, ox, oy, raw, sm);
+                                            const float4* __restrict__ raw, float* sm, int row0 = 0) {
+    if (d.n_src == 2) fill_region_n<HALO, 2>(ctx, d, b, ci, ox, oy, raw, sm, row0);
+    else fill_region_n<HALO, 1>(ctx, d, b, ci, ox, oy, raw, sm, row0);
 }
 
 // Everything the loss decides at one pixel (single_cam_loss.py:17-55, multi_cam_loss.py:16-59).
