@@ -259,7 +259,8 @@ def test_compact_rows_equal_dense_rows(B):
     assert H.rel_err(d_c, d_d) < 1e-5      # atomics: summation order differs
 
 
-@pytest.mark.parametrize('dataset,B,C,Cv', [('ddad', 2, 256, 64), ('nuscenes', 1, 64, 32), ('ddad', 1, 20, 12)])
+@pytest.mark.parametrize('dataset,B,C,Cv', [('ddad', 2, 256, 64), ('nuscenes', 1, 64, 32), ('ddad', 1, 20, 12),
+                                            ('ddad', 1, 128, 32), ('nuscenes', 1, 128, 48)])
 def test_fused_mlp_matches_fp32_gemm_path(dataset, B, C, Cv):
     """SURVEY.md 8f-1 at BASELINE size: the fused gather + MLP kernels (3xTF32 tensor-core products) against the dense
     gather rows + fp32 cuBLAS GEMMs -- volume, feature gradient and the four parameter gradients within 1e-4 of each
