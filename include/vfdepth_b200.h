@@ -305,6 +305,29 @@ int vfd_depth_syn_fwd(const vfd_syn_desc* d, const float* depth, const float* au
 int vfd_depth_syn_bwd(const vfd_syn_desc* d, const float* depth, const float* aug, const float* T, const float* Tinv,
                       const float* wcam, float* d_aug, float* d_depth, void* stream);
 
+/* --------------------------------------------------------------------------------------------------
+ * Multi-level feature aggregation in front of the fusion (network/fusion_depthnet.py:57-66,
+ * network/fusion_posenet.py:62-70):  LeakyReLU(conv1x1(cat[f_lev, up(f_lev+1), ...]) + b), up = F.interpolate(bilinear,
+ * align_corners=True).  conv1x1 and the resize commute, so the caller projects each level at its own resolution
+ * (channel-last GEMMs with the column blocks of the conv1x1 weight) and this entry point resizes, adds, applies bias and
+ * LeakyReLU and writes the channel-last map the voxel kernels read:
+ *   y0  [n_img,h,w,C]            projection of the finest level (no bias)
+ *   yc  host array of n_coarse device pointers, yc[l] = [n_img,ch[l],cw[l],C]
+ *   out [n_img,h,w,C]            feats_agg, channel-last; C % 4 == 0, C <= 1024, 16-byte aligned pointers. */
+#define VFD_AGG_LEVELS 3
+typedef struct vfd_agg_desc {
+    int32_t n_img, h, w, C;
+    int32_t n_coarse;
+    int32_t ch[VFD_AGG_LEVELS], cw[VFD_AGG_LEVELS];
+    float slope;                            /* LeakyReLU negative slope (0.1, network/blocks.py:47) */
+} vfd_agg_desc;
+int vfd_feat_agg_fwd(const vfd_agg_desc* d, const float* y0, const float* const* yc, const float* bias, float* out,
+                     void* stream);
+/* backward: d_y0 [n_img,h,w,C] = d_out * (out > 0 ? 1 : slope) (its column sums are the bias gradient), d_yc[l] written
+ * (gathered from d_y0 through the transposed resize; deterministic). */
+int vfd_feat_agg_bwd(const vfd_agg_desc* d, const float* out, const float* d_out, float* d_y0, float* const* d_yc,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

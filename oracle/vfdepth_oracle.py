@@ -449,6 +449,16 @@ def to_depth(cfg, disp_in, K_in):
     return depth * K_in[:, 0:1, 0:1].unsqueeze(2) / t['focal_length_scale']
 
 
+def aggregate_features(packed_feats, lev, weight, bias, slope=0.1):
+    """network/fusion_depthnet.py:57-66 (same lines in fusion_posenet.py:62-70): resize the encoder levels above
+    ``lev`` to level ``lev`` (bilinear, align_corners=True), concatenate, 1x1 conv + LeakyReLU (blocks.py:41-61 conv2d
+    with kernel_size=1).  packed_feats: list of [B*cams,C_l,h_l,w_l]; weight [Cout,sum C_l,1,1] -> [B*cams,Cout,h,w]."""
+    _, _, up_h, up_w = packed_feats[lev].size()
+    feats = packed_feats[lev:lev + 1] + [F.interpolate(feat, [up_h, up_w], mode='bilinear', align_corners=True)
+                                         for feat in packed_feats[lev + 1:]]
+    return F.leaky_relu(F.conv2d(torch.cat(feats, dim=1), weight, bias), slope)
+
+
 # --------------------------------------------------------------------------------------
 # 8f-3  depth synthesis (aug_depth)   view_rendering.py:84-116, :201-241; depth_synthesis_loss.py:15-43
 # --------------------------------------------------------------------------------------

@@ -2,8 +2,8 @@
 
     python tests/golden/make_golden.py            # needs /root/reference (or $VFDEPTH_REF)
 
-Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz``, ``golden_depth_syn.npz`` next to this file
-(``--only-new`` regenerates just the last two).  The
+Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz``, ``golden_depth_syn.npz``,
+``golden_feat_agg.npz`` next to this file (``--only-new`` regenerates just the last three, ``--only-agg`` the last).  The
 fixtures hold the seeded inputs and what the reference's own classes
 (``VFNet``, ``ViewRendering``, ``Pose``, ``MultiCamLoss``) returned for them, at
 sizes small enough to commit.  ``tests/test_oracle_golden.py`` then pins
@@ -234,10 +234,65 @@ def make_depth_syn(ref, path):
     print('wrote', path, 'con', [float(c) for c in con])
 
 
+AGG_CFG = dict(training__height=64, training__width=96, model__fusion_feat_in_dim=64, model__voxel_size=[20, 20, 4],
+               model__voxel_str_p=[-10.0, -10.0, -2.0], model__voxel_unit_size=[1.0, 1.0, 1.0], model__proj_d_bins=8)
+
+
+def make_feat_agg(path):
+    """The reference's FusedDepthNet (network/fusion_depthnet.py:13-92, randomly initialised ResNet-18 encoder) run on
+    a seeded rig with forward hooks on its encoder and its conv1x1 block: the fixture holds the encoder levels
+    lev.. (the inputs of :57-64), conv1x1's parameters, its output (= feats_agg before unpacking) and the gradients of a
+    seeded upstream w.r.t. the levels and the parameters."""
+    import importlib
+    ref_import.load_algo()
+    fdn = importlib.import_module('network.fusion_depthnet')
+    cfg = vcfg.default_config('ddad', batch_size=1, **AGG_CFG)
+    cfg['model']['weights_init'] = False
+    torch.manual_seed(0)
+    net = fdn.FusedDepthNet(cfg)
+    with torch.no_grad():
+        net.conv1x1[0].bias.normal_(0, 0.05)
+    inputs, _ = make_rig(cfg, seed=5, with_feats=False)
+    inputs[('color_aug', 0, 0)] = inputs[('color', 0, 0)]
+    cap = {}
+    net.encoder.register_forward_hook(lambda m, i, o: cap.update(feats=list(o)))
+    net.conv1x1.register_forward_hook(lambda m, i, o: cap.update(agg=o))
+    net.conv1x1.register_forward_pre_hook(lambda m, i: cap.update(cat=i[0]))
+    net.train()
+    net(inputs)
+    lev = cfg['model']['fusion_level']
+    levels = cap['feats'][lev:]
+    gen = torch.Generator().manual_seed(77)
+    g_up = torch.randn(cap['agg'].shape, generator=gen)
+    params = [net.conv1x1[0].weight, net.conv1x1[0].bias]
+    # gradients through the reference's graph w.r.t. the concatenated maps and the parameters.  (Inside the encoder
+    # level l+1 is a function of level l, so the graph's gradient w.r.t. a level would include that path; the partial
+    # derivative of lines :57-64 alone is the slice of d_cat pulled back through the same F.interpolate call.)
+    d_cat, d_w, d_b = torch.autograd.grad((cap['agg'] * g_up).sum(), [cap['cat']] + params)
+    out = {'lev': np.int64(lev), 'agg': _np(cap['agg']), 'g_up': _np(g_up), 'weight': _np(params[0]), 'bias': _np(params[1]),
+           'd_weight': _np(d_w), 'd_bias': _np(d_b)}
+    up_h, up_w = levels[0].shape[-2:]
+    off = 0
+    for i, x in enumerate(levels):
+        c = x.shape[1]
+        leaf = x.detach().clone().requires_grad_(True)
+        y = leaf if i == 0 else torch.nn.functional.interpolate(leaf, [up_h, up_w], mode='bilinear', align_corners=True)
+        (g,) = torch.autograd.grad((y * d_cat[:, off:off + c]).sum(), leaf)
+        off += c
+        out['feat_%d' % i] = _np(x)
+        out['d_feat_%d' % i] = _np(g)
+    np.savez_compressed(path, **out)
+    print('wrote', path, [tuple(x.shape) for x in levels], tuple(cap['agg'].shape))
+
+
 if __name__ == '__main__':
+    if '--only-agg' in sys.argv:
+        make_feat_agg(os.path.join(HERE, 'golden_feat_agg.npz'))
+        sys.exit(0)
     ref = ref_import.load()
     if '--only-new' not in sys.argv:
         make_fusion(ref, os.path.join(HERE, 'golden_fusion.npz'))
         make_warp(ref, os.path.join(HERE, 'golden_warp.npz'))
     make_to_depth(os.path.join(HERE, 'golden_to_depth.npz'))
     make_depth_syn(ref, os.path.join(HERE, 'golden_depth_syn.npz'))
+    make_feat_agg(os.path.join(HERE, 'golden_feat_agg.npz'))

@@ -39,7 +39,8 @@ def test_header_is_plain_c_and_structs_match_ctypes():
 int main(void) {
   printf("%zu %zu %zu ", sizeof(vfd_fusion_desc), sizeof(vfd_warp_desc), sizeof(vfd_warp_views));
   printf("%zu %zu %zu ", offsetof(vfd_fusion_desc, group), offsetof(vfd_fusion_desc, depth_div), offsetof(vfd_fusion_desc, axis_x));
-  printf("%zu %zu %zu\n", offsetof(vfd_warp_desc, nbr), offsetof(vfd_warp_desc, color), offsetof(vfd_warp_desc, invK));
+  printf("%zu %zu %zu ", offsetof(vfd_warp_desc, nbr), offsetof(vfd_warp_desc, color), offsetof(vfd_warp_desc, invK));
+  printf("%zu %zu %zu %zu\n", sizeof(vfd_syn_desc), sizeof(vfd_agg_desc), offsetof(vfd_agg_desc, cw), offsetof(vfd_agg_desc, slope));
   return 0; }
 '''
     d = tempfile.mkdtemp(prefix='vfd_abi_')
@@ -50,7 +51,8 @@ int main(void) {
     got = [int(x) for x in subprocess.check_output([exe]).split()]
     F, W, V = _lib.FusionDesc, _lib.WarpDesc, _lib.WarpViews
     want = [ctypes.sizeof(F), ctypes.sizeof(W), ctypes.sizeof(V), F.group.offset, F.depth_div.offset, F.axis_x.offset,
-            W.nbr.offset, W.color.offset, W.invK.offset]
+            W.nbr.offset, W.color.offset, W.invK.offset,
+            ctypes.sizeof(_lib.SynDesc), ctypes.sizeof(_lib.AggDesc), _lib.AggDesc.cw.offset, _lib.AggDesc.slope.offset]
     assert got == want
 
 
@@ -93,6 +95,17 @@ def test_bad_arguments_are_rejected_before_any_launch():
     sd = _lib.SynDesc()
     assert lib.vfd_depth_syn_fwd(ctypes.byref(sd), null, null, null, null, null, null, null, null) == -2
     assert lib.vfd_warp_stats(null, null, null, null, null, null, null) == -1
+    assert lib.vfd_feat_agg_fwd(null, null, null, null, null, null) == -1
+    assert lib.vfd_feat_agg_bwd(null, null, null, null, null, null) == -1
+    ad = _lib.AggDesc()
+    assert lib.vfd_feat_agg_fwd(ctypes.byref(ad), null, null, null, null, null) == -2      # zero sizes
+    ad.n_img, ad.h, ad.w, ad.C, ad.n_coarse = 6, 8, 12, 64, 1
+    ad.ch[0], ad.cw[0] = 9, 6                                                              # coarser level larger than h
+    assert lib.vfd_feat_agg_fwd(ctypes.byref(ad), null, null, null, null, null) == -2
+    ad.ch[0] = 4
+    assert lib.vfd_feat_agg_fwd(ctypes.byref(ad), null, null, null, null, null) == -1      # valid descriptor, NULL data
+    ad.C = 66
+    assert lib.vfd_feat_agg_bwd(ctypes.byref(ad), null, null, null, null, null) == -2      # C % 4
     # descriptor out of range
     d = _lib.FusionDesc()
     assert lib.vfd_voxel_gather_depth_fwd(ctypes.byref(d), null, null, null, null, null, null, null, null, null, null) == -2

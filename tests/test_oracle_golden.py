@@ -103,3 +103,17 @@ def test_depth_synthesis_bit_exact():
     assert torch.equal(torch.cat(grads[:6], 1), g['d_depth'])
     assert torch.equal(torch.cat(grads[6:12], 1), g['d_aug'])
     assert torch.equal(torch.cat(grads[12:], 1), g['d_disp_aug'])
+
+
+def test_aggregate_features_bit_exact():
+    """oracle.aggregate_features against what the reference's FusedDepthNet computed between its encoder and its fusion
+    net (network/fusion_depthnet.py:57-66; fixture from forward hooks on the real module), forward and gradients."""
+    g = H.load_npz('golden_feat_agg.npz')
+    levels = [g['feat_%d' % i].clone().requires_grad_(True) for i in range(3)]
+    w, b = g['weight'].clone().requires_grad_(True), g['bias'].clone().requires_grad_(True)
+    agg = orc.aggregate_features(levels, 0, w, b)
+    assert torch.equal(agg, g['agg'])
+    grads = torch.autograd.grad((agg * g['g_up']).sum(), levels + [w, b])
+    for i in range(3):
+        assert torch.equal(grads[i], g['d_feat_%d' % i]), i
+    assert torch.equal(grads[3], g['d_weight']) and torch.equal(grads[4], g['d_bias'])

@@ -57,6 +57,19 @@ class SynDesc(ctypes.Structure):
     ]
 
 
+VFD_AGG_LEVELS = 3
+
+
+class AggDesc(ctypes.Structure):
+    """struct vfd_agg_desc"""
+    _fields_ = [
+        ('n_img', ctypes.c_int32), ('h', ctypes.c_int32), ('w', ctypes.c_int32), ('C', ctypes.c_int32),
+        ('n_coarse', ctypes.c_int32),
+        ('ch', ctypes.c_int32 * VFD_AGG_LEVELS), ('cw', ctypes.c_int32 * VFD_AGG_LEVELS),
+        ('slope', ctypes.c_float),
+    ]
+
+
 class WarpViews(ctypes.Structure):
     """struct vfd_warp_views"""
     _fields_ = [(n, ctypes.c_void_p) for n in ('color', 'color_mask', 'overlap', 'overlap_mask', 'reproj_loss',
@@ -68,7 +81,8 @@ _lib = None
 launches = 0   # number of kernels launched through the ABI by this process (bench.py reports it)
 # kernels one call of each entry point launches (memsets not counted); anything not listed launches one
 KERNELS_PER_CALL = {'vfd_voxel_classify': 3, 'vfd_voxel_fuse_bwd': 3, 'vfd_warp_stats': 2, 'vfd_warp_loss_bwd': 2, 'vfd_warp_loss_train_bwd': 2,
-                    'vfd_smooth_loss_fwd': 2, 'vfd_smooth_loss_bwd': 2, 'vfd_smooth_loss_train_fwd': 2}
+                    'vfd_smooth_loss_fwd': 2, 'vfd_smooth_loss_bwd': 2, 'vfd_smooth_loss_train_fwd': 2,
+                    'vfd_feat_agg_bwd': 3}     # fine + one launch per coarse level (two at the shipped configs)
 
 
 def load():
