@@ -146,6 +146,15 @@ int vfd_voxel_gather_pose_fwd(const vfd_fusion_desc* d, const float* feats, cons
 int vfd_voxel_gather_pose_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
                               const float* Einv, const float* d_avg, float* d_feats, void* stream);
 
+/* The pose gather with rows ordered (y, x, z) instead of the reference's (z, y, x): bev [B,Y,X,Z,ld_no] read as
+ * [B,Y,X,Z*ld_no] is the channels-last form of the BEV map VFNet.forward hands to reduce_dim (:339-342; channel
+ * z*ld_no + c there is channel c*Z + z of the reference, pad columns are zero), so the [B,257*Z,Y,X] reshape copy
+ * (411 MB of traffic per rig and call, again in backward) disappears.  count stays in voxel order. */
+int vfd_voxel_gather_pose_bev_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                                  const float* K, const float* Einv, float* bev, uint8_t* count, void* stream);
+int vfd_voxel_gather_pose_bev_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                                  const float* Einv, const float* d_bev, float* d_feats, void* stream);
+
 /* VFNet.project_voxel_into_image without reduce_dim (:245-262):
  *   vol   [B,Z,Y,X,Cv]       channel-last voxel volume (voxel_feat of :240)
  *   invK  [B,cams,4,4]       inputs['inv_K', fusion_level+1];   E [B,cams,4,4] camera->ego

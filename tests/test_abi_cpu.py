@@ -95,6 +95,8 @@ def test_bad_arguments_are_rejected_before_any_launch():
     sd = _lib.SynDesc()
     assert lib.vfd_depth_syn_fwd(ctypes.byref(sd), null, null, null, null, null, null, null, null) == -2
     assert lib.vfd_warp_stats(null, null, null, null, null, null, null) == -1
+    assert lib.vfd_voxel_gather_pose_bev_fwd(null, null, null, null, null, null, null, null) == -1
+    assert lib.vfd_voxel_gather_pose_bev_bwd(null, null, null, null, null, null, null) == -1
     assert lib.vfd_feat_agg_fwd(null, null, null, null, null, null) == -1
     assert lib.vfd_feat_agg_bwd(null, null, null, null, null, null) == -1
     ad = _lib.AggDesc()

@@ -359,3 +359,45 @@ def test_fused_mlp_degenerate_lists(keep):
     outside = (cnt != 1) & (cnt != 2)
     if bool(outside.any()):
         assert float(vol[outside].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('dataset,C', [('ddad', 32), ('nuscenes', 20)])
+def test_pose_bev_handoff_matches_reference_reshape(dataset, C):
+    """SURVEY.md 8f-2, pose side (:339-342): the gather writes the BEV map channels-last (rows ordered y, x, z) and
+    reduce_dim's first conv reads it with permuted input channels -- same result and gradients as the reference's
+    [B,C',N] -> [B,C'*Z,Y,X] reshape followed by reduce_dim, rows bit-identical to the reference-order gather."""
+    dev = _dev()
+    cfg = vcfg.default_config(dataset, batch_size=2, model__voxel_size=[24, 20, 6], model__voxel_str_p=[-24.0, -20.0, -3.0],
+                              model__voxel_unit_size=[2.0, 2.0, 1.5], model__fusion_feat_in_dim=C)
+    inputs, extras = make_rig(cfg, seed=55, with_images=False, with_feats=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, C, 16, 'pose', None, dev)
+    g = net.geom
+    to = lambda t: t.to(dev)
+    torch.manual_seed(9)
+    feats0 = torch.randn(2, 6, C, g.h, g.w, device=dev)
+    args = (to(inputs['mask']), to(inputs[('K', lvl)]), to(inputs['extrinsics_inv']))
+    # rows: bit-identical, only reordered
+    f = feats0.clone()
+    ref_vox = net.backproject_into_voxel(f, *args)                          # [B,C+1,N], reference order
+    rows = net.bev_rows(f, *args)                                           # [B,Y,X,Z*ld]
+    got = rows.view(2, g.Y, g.X, g.Z, g.ld_no)[..., :C + 1].permute(0, 4, 3, 1, 2).reshape(2, C + 1, -1)
+    assert torch.equal(got, ref_vox)
+    assert float(rows.view(2, g.Y, g.X, g.Z, g.ld_no)[..., C + 1:].abs().max()) == 0.0
+    # forward + gradients through reduce_dim
+    k = {'K': args[1], 'extr': args[2]}
+    inp = {'mask': args[0], ('K', lvl): k['K'], ('inv_K', lvl): to(inputs[('inv_K', lvl)]),
+           'extrinsics': to(inputs['extrinsics']), 'extrinsics_inv': k['extr']}
+    params = [net.reduce_dim[0].weight, net.reduce_dim[0].bias, net.reduce_dim[3].weight]
+    f1 = feats0.clone().requires_grad_(True)
+    out = net(inp, f1)
+    up = torch.randn_like(out)
+    g1 = torch.autograd.grad((out * up).sum(), [f1] + params)
+    f2 = feats0.clone().requires_grad_(True)
+    vox = net.backproject_into_voxel(f2, *args)
+    ref = net.reduce_dim(vox.reshape(2, (C + 1) * g.Z, g.Y, g.X))
+    g2 = torch.autograd.grad((ref * up).sum(), [f2] + params)
+    assert out.shape == ref.shape
+    assert H.rel_err(out, ref) < TOL
+    for a, b in zip(g1, g2):
+        assert H.rel_err(a, b) < TOL

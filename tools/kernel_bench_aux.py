@@ -33,6 +33,49 @@ def timed(fn, iters, warmup=3):
     return e0.elapsed_time(e1) / iters
 
 
+def bench_aggregation(B, iters, report, dev):
+    """feature aggregation (fusion_depthnet.py:57-66) at the DDAD sizes: ResNet levels 128@48x80, 256@24x40, 512@12x20
+    -> 256 channels.  Ours (per-level GEMMs + vfd_feat_agg) against the reference's formulation in torch on the same
+    GPU (interpolate, cat, conv2d, LeakyReLU, then the channel-last copy the voxel kernels need)."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from vfdepth_b200 import _lib, aggregate
+    n = B * 6
+    gen = torch.Generator().manual_seed(1)
+    lv = [torch.randn((n, c, h, w), generator=gen).to(dev).requires_grad_(True)
+          for c, h, w in ((128, 48, 80), (256, 24, 40), (512, 12, 20))]
+    blk = nn.Sequential(nn.Conv2d(896, 256, 1, bias=True), nn.Identity(), nn.LeakyReLU(0.1, inplace=True)).to(dev)
+    params = [blk[0].weight, blk[0].bias]
+    up = torch.randn((B, 6, 256, 48, 80), device=dev)
+    out_bytes = n * 48 * 80 * 256 * 4
+    in_bytes = sum(x.numel() for x in lv) * 4
+
+    def ours():
+        o = aggregate.aggregate_features(lv, 0, blk, B, 6)
+        return torch.autograd.grad(o, lv + params, up)
+
+    def ref():
+        cat = torch.cat([lv[0]] + [F.interpolate(x, [48, 80], mode='bilinear', align_corners=True) for x in lv[1:]], 1)
+        o = blk(cat).view(B, 6, 256, 48, 80)
+        cl = o.permute(0, 1, 3, 4, 2).contiguous()
+        return torch.autograd.grad(cl, lv + params, up.permute(0, 1, 3, 4, 2))
+
+    with torch.no_grad():
+        report('feat_agg ours fwd', timed(lambda: aggregate.aggregate_features(lv, 0, blk, B, 6), iters), in_bytes + out_bytes)
+        report('feat_agg ref  fwd', timed(lambda: blk(torch.cat([lv[0]] + [F.interpolate(x, [48, 80], mode='bilinear', align_corners=True) for x in lv[1:]], 1)).permute(0, 2, 3, 1).contiguous(), iters), in_bytes + out_bytes)
+    report('feat_agg ours f+b', timed(ours, iters), 3 * (in_bytes + out_bytes))
+    report('feat_agg ref  f+b', timed(ref, iters), 3 * (in_bytes + out_bytes))
+    # the kernels alone (projections resident): fwd reads y0 + coarse, writes out; bwd reads out, d_out, writes d_y*
+    _lib.start_event_trace()
+    for _ in range(iters):
+        ours()
+    tr = _lib.stop_event_trace()
+    coarse = n * 256 * 4 * (24 * 40 + 12 * 20)
+    for name, nbytes in (('vfd_feat_agg_fwd', 2 * out_bytes + coarse), ('vfd_feat_agg_bwd', 3 * out_bytes + coarse)):
+        if name in tr:
+            report(name, tr[name][1] / tr[name][0], nbytes)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--batch', type=int, default=8)
@@ -79,6 +122,7 @@ def main():
         report('depth_syn_fwd', timed(lambda: view.depth_syn_loss(cfg, inp, dep, aug, disp), args.iters), 4 * px)
     report('depth_syn_bwd', timed(lambda: torch.autograd.grad(con, [dep, aug], upc, retain_graph=True), args.iters), 5 * px)
     print('depth_con_loss per camera:', [round(float(c), 4) for c in con])
+    bench_aggregation(B, args.iters, report, dev)
     print('(depth_syn_fwd includes the colour-less smoothness of disp_aug and two batched 4x4 inversions in torch)')
 
 

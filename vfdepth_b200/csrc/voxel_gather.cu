@@ -33,7 +33,19 @@ struct GatherArgs {
     float* d_feats;
     // compact rows (only voxels with count 1 / 2 own a row); NULL = dense rows, one per voxel
     const int32_t* slot;
+    // pose: 1 = rows ordered (y, x, z) -- [B,Y,X,Z*ld] IS the channels-last BEV map reduce_dim reads (:339-342)
+    int bev_rows;
 };
+
+// dense row of voxel n = (z*Y + y)*X + x: the reference's flatten order, or z innermost for the BEV hand-off
+__device__ __forceinline__ size_t dense_row(const GatherArgs& a, int b, long n) {
+    const vfd_fusion_desc& d = a.d;
+    const size_t N = (size_t)d.X * d.Y * d.Z;
+    if (!a.bev_rows) return (size_t)b * N + n;
+    const long xy = (long)d.X * d.Y;
+    const long z = n / xy, r = n - z * xy;
+    return (size_t)b * N + (size_t)r * d.Z + z;
+}
 
 // phase 1: returns the camera bit-mask of this lane's voxel and fills slot[c][lane]
 __device__ __forceinline__ unsigned project_voxel(const GatherArgs& a, const float* s_mat, int b, long n, int lane,
@@ -126,7 +138,7 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_fwd_kerne
             }
             if (g1) z1 += s.zrel; else z0 += s.zrel;
         }
-        const size_t row = a.slot ? (size_t)sl : (size_t)b * N + n0 + j;
+        const size_t row = a.slot ? (size_t)sl : dense_row(a, b, n0 + j);
         if (MODE == 0) {
             // dense: both rows of every voxel; compact: the x_no row of a count-1 voxel, the x_ov row of a count-2 one
             const bool wr_no = !a.slot || cnt == 1, wr_ov = !a.slot || cnt == 2;
@@ -201,7 +213,7 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_gather_bwd_kerne
         if (!m) continue;
         if (MODE == 0 && a.slot && sl < 0) continue;
         const int cnt = __popc(m);
-        const size_t row = a.slot ? (size_t)sl : (size_t)b * N + n0 + j;
+        const size_t row = a.slot ? (size_t)sl : dense_row(a, b, n0 + j);
         float4 gno[ITERS];
         if (MODE == 0) {
 #pragma unroll
@@ -453,6 +465,20 @@ extern "C" int vfd_voxel_gather_pose_fwd(const vfd_fusion_desc* d, const float* 
     return launch<1>(a, false, (cudaStream_t)stream);
 }
 
+extern "C" int vfd_voxel_gather_pose_bev_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small,
+                                             const float* K, const float* Einv, float* bev, uint8_t* count,
+                                             void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, false))) return rc;
+    if (!feats || !mask_small || !K || !Einv || !bev) return VFD_ERR_NULL;
+    if (!aligned16(feats) || !aligned16(bev)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.feats = feats; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.x_no = bev; a.count = count;
+    a.bev_rows = 1;
+    return launch<1>(a, false, (cudaStream_t)stream);
+}
+
 static int bwd_common(const vfd_fusion_desc* d, GatherArgs& a, float* d_feats, cudaStream_t st) {
     const size_t bytes = (size_t)d->B * d->num_cams * d->h * d->w * d->C * sizeof(float);
     if (cudaMemsetAsync(d_feats, 0, bytes, st) != cudaSuccess) return VFD_ERR_CUDA;
@@ -483,6 +509,20 @@ extern "C" int vfd_voxel_gather_pose_bwd(const vfd_fusion_desc* d, const float* 
     if (!aligned16(d_feats) || !aligned16(d_avg)) return VFD_ERR_ALIGN;
     GatherArgs a = {};
     a.d = *d; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.d_x_no = d_avg;
+    if ((rc = bwd_common(d, a, d_feats, (cudaStream_t)stream))) return rc;
+    return launch<1>(a, true, (cudaStream_t)stream);
+}
+
+extern "C" int vfd_voxel_gather_pose_bev_bwd(const vfd_fusion_desc* d, const float* mask_small, const float* K,
+                                             const float* Einv, const float* d_bev, float* d_feats, void* stream) {
+    int rc = check_desc(d);
+    if (rc) return rc;
+    if ((rc = check_rows(d, false))) return rc;
+    if (!mask_small || !K || !Einv || !d_bev || !d_feats) return VFD_ERR_NULL;
+    if (!aligned16(d_feats) || !aligned16(d_bev)) return VFD_ERR_ALIGN;
+    GatherArgs a = {};
+    a.d = *d; a.mask_small = mask_small; a.K = K; a.Einv = Einv; a.d_x_no = d_bev;
+    a.bev_rows = 1;
     if ((rc = bwd_common(d, a, d_feats, (cudaStream_t)stream))) return rc;
     return launch<1>(a, true, (cudaStream_t)stream);
 }

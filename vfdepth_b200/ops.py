@@ -138,7 +138,7 @@ class _VoxelGatherDepth(torch.autograd.Function):
 
 class _VoxelGatherPose(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, feats, mask_small, K, Einv, geom):
+    def forward(ctx, feats, mask_small, K, Einv, geom, bev=False):
         B = feats.shape[0]
         g = geom
         _chk(feats, 'feats', (B, g.num_cams, g.h, g.w, g.C))
@@ -149,9 +149,11 @@ class _VoxelGatherPose(torch.autograd.Function):
         d = g.desc(dev, B)
         avg = torch.empty((B, g.N, g.ld_no), device=dev, dtype=torch.float32)
         count = torch.empty((B, g.N), device=dev, dtype=torch.uint8)
-        _lib.call('vfd_voxel_gather_pose_fwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
-                  _lib.ptr(Einv), _lib.ptr(avg), _lib.ptr(count), _stream())
+        _lib.call('vfd_voxel_gather_pose_bev_fwd' if bev else 'vfd_voxel_gather_pose_fwd', ctypes.byref(d),
+                  _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv), _lib.ptr(avg), _lib.ptr(count),
+                  _stream())
         ctx.geom = g
+        ctx.bev = bev
         ctx.save_for_backward(mask_small, K, Einv)
         ctx.mark_non_differentiable(count)
         return avg, count
@@ -165,9 +167,9 @@ class _VoxelGatherPose(torch.autograd.Function):
         d = g.desc(dev, B)
         d_avg = d_avg.contiguous()
         d_feats = torch.empty((B, g.num_cams, g.h, g.w, g.C), device=dev, dtype=torch.float32)
-        _lib.call('vfd_voxel_gather_pose_bwd', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv),
-                  _lib.ptr(d_avg), _lib.ptr(d_feats), _stream())
-        return d_feats, None, None, None, None
+        _lib.call('vfd_voxel_gather_pose_bev_bwd' if ctx.bev else 'vfd_voxel_gather_pose_bwd', ctypes.byref(d),
+                  _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv), _lib.ptr(d_avg), _lib.ptr(d_feats), _stream())
+        return d_feats, None, None, None, None, None
 
 
 class _RaySample(torch.autograd.Function):
@@ -338,9 +340,9 @@ def voxel_gather_depth(feats_cl, mask_small, K, Einv, geom, detail=False):
     return _VoxelGatherDepth.apply(feats_cl, mask_small, K, Einv, geom, detail)
 
 
-def voxel_gather_pose(feats_cl, mask_small, K, Einv, geom):
-    """-> avg [B,N,ld_no], count [B,N]"""
-    return _VoxelGatherPose.apply(feats_cl, mask_small, K, Einv, geom)
+def voxel_gather_pose(feats_cl, mask_small, K, Einv, geom, bev=False):
+    """-> avg [B,N,ld_no], count [B,N]; bev=True: rows ordered (y,x,z) = the channels-last BEV map [B,Y,X,Z*ld_no]"""
+    return _VoxelGatherPose.apply(feats_cl, mask_small, K, Einv, geom, bev)
 
 
 def ray_sample(vol_cl, invK, E, geom, want_grid=False):

@@ -182,6 +182,9 @@ class VFNet(nn.Module):
         mask, K, inv_K = inputs['mask'], inputs['K', lvl], inputs['inv_K', lvl]
         extrinsics, extrinsics_inv = inputs['extrinsics'], inputs['extrinsics_inv']
         fusion_dict = {('cam', cam): {} for cam in range(self.num_cams)}
+        if self.model == 'pose':
+            # no [B,C',N] -> [B,C'*Z,Y,X] reshape copy: the gather writes the BEV map channels-last
+            return self.reduce_bev(self.bev_rows(feats_agg, mask, K, extrinsics_inv))
         voxel_feat = self.backproject_into_voxel(feats_agg, mask, K, extrinsics_inv)
         if self.model == 'depth':
             feats = self.project_voxel_into_image(voxel_feat, inv_K, extrinsics)
@@ -193,8 +196,28 @@ class VFNet(nn.Module):
             if getattr(self, 'syn_visualize', False):
                 raise NotImplementedError('synthesis visualisation sweep (:320-336) is outside the hot path')
             return fusion_dict
-        if self.model == 'pose':
-            b, c, _ = voxel_feat.shape
-            bev = voxel_feat.reshape(b, c * self.z_dim, self.y_dim, self.x_dim)
-            return self.reduce_dim(bev)
         raise ValueError(self.model)
+
+    def bev_rows(self, feats_agg, input_mask, intrinsics, extrinsics_inv):
+        """pose gather with z innermost: [B,Y,X,Z*ld] = the BEV map of :339-340 in channels-last storage."""
+        g = self.geom
+        avg, count = ops.voxel_gather_pose(self._channel_last(feats_agg), self._mask_small(input_mask),
+                                           intrinsics.float().contiguous(), extrinsics_inv.float().contiguous(), g,
+                                           bev=True)
+        self.last_count = count
+        return avg.view(avg.shape[0], self.y_dim, self.x_dim, self.z_dim * g.ld_no)
+
+    def reduce_bev(self, bev_rows):
+        """reduce_dim (:341) on the channels-last BEV rows.  Channel z*ld + c here is channel c*Z + z of the reference's
+        reshape (:340); the first conv's INPUT channels are permuted / zero-padded on the fly, the parameter keeps
+        the reference's shape."""
+        g = self.geom
+        c1 = self.feat_in_dim + 1
+        conv0 = self.reduce_dim[0]
+        w0 = conv0.weight.view(conv0.out_channels, c1, self.z_dim, 3, 3).permute(0, 2, 1, 3, 4)
+        w0 = F.pad(w0, (0, 0, 0, 0, 0, g.ld_no - c1)).reshape(conv0.out_channels, self.z_dim * g.ld_no, 3, 3)
+        x = bev_rows.permute(0, 3, 1, 2)                      # NCHW view of channels_last storage
+        y = F.conv2d(F.pad(x, (1, 1, 1, 1), mode='reflect'), w0, conv0.bias, stride=conv0.stride)
+        for layer in list(self.reduce_dim)[1:]:
+            y = layer(y)
+        return y
