@@ -315,6 +315,29 @@ int vfd_depth_syn_bwd(const vfd_syn_desc* d, const float* depth, const float* au
                       const float* wcam, float* d_aug, float* d_depth, void* stream);
 
 /* --------------------------------------------------------------------------------------------------
+ * Stand-alone warp of ONE (source, target) pair per batch element: the sub-method surface of the reference that the
+ * fused rig kernels bypass.  Same bit-exact coordinates and sampler as vfd_warp_loss_*.
+ *   Projection.forward (models/geometry/geometry_util.py:79-82)      vfd_warp_image_fwd with src_img = NULL: grid only
+ *   ViewRendering.get_virtual_image (view_rendering.py:61-82)        vfd_warp_image_fwd: img (NaN -> 2.0), valid * mask
+ *   Projection.backproject / .reproject (:52-60 / :62-77)            vfd_projection_backproject / _reproject
+ *   src_img [B,3,H,W], src_mask [B,1,H,W], depth [B,1,H,W] (target), invK [B,4,4] (target), K [B,4,4] (source),
+ *   T [B,4,4] (target -> source); img [B,3,H,W], mask [B,1,H,W], grid [B,H,W,2] (optional with an image).
+ * Backward (d_img and / or d_grid given): d_depth [B,1,H,W] written; dP_part [B, vfd_warp_image_blocks(), 12] per-CTA
+ * partial sums of the gradient w.r.t. P = (K @ T)[:3,:] -- the caller adds them in order (deterministic) and forms
+ * d_T = K[:3,:]^T dP, d_K[:3,:] = dP T^T.  No gradient to src_img (an input of the training step). */
+int vfd_warp_image_blocks(void);
+int vfd_warp_image_fwd(int B, int H, int W, const float* src_img, const float* src_mask, const float* depth,
+                       const float* invK, const float* K, const float* T, float* img, float* mask, float* grid,
+                       void* stream);
+int vfd_warp_image_bwd(int B, int H, int W, const float* src_img, const float* src_mask, const float* depth,
+                       const float* invK, const float* K, const float* T, const float* d_img, const float* d_grid,
+                       float* d_depth, float* dP_part, void* stream);
+/* points [B,4,H*W] = depth * (invK[:3,:3] @ (u,v,1)), row 3 = 1;  grid [B,H,W,2] from such points (row 3 taken as 1) */
+int vfd_projection_backproject(int B, int H, int W, const float* depth, const float* invK, float* points, void* stream);
+int vfd_projection_reproject(int B, int H, int W, const float* points, const float* K, const float* T, float* grid,
+                             void* stream);
+
+/* --------------------------------------------------------------------------------------------------
  * Multi-level feature aggregation in front of the fusion (network/fusion_depthnet.py:57-66,
  * network/fusion_posenet.py:62-70):  LeakyReLU(conv1x1(cat[f_lev, up(f_lev+1), ...]) + b), up = F.interpolate(bilinear,
  * align_corners=True).  conv1x1 and the resize commute, so the caller projects each level at its own resolution

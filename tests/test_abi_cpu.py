@@ -97,6 +97,12 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.vfd_warp_stats(null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_gather_pose_bev_fwd(null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_gather_pose_bev_bwd(null, null, null, null, null, null, null) == -1
+    assert lib.vfd_warp_image_blocks() == 148
+    assert lib.vfd_warp_image_fwd(2, 8, 8, null, null, null, null, null, null, null, null, null, null) == -1
+    assert lib.vfd_warp_image_fwd(2, 1, 8, null, null, null, null, null, null, null, null, null, null) == -2
+    assert lib.vfd_warp_image_bwd(2, 8, 8, null, null, null, null, null, null, null, null, null, null, null) == -1
+    assert lib.vfd_projection_backproject(2, 8, 8, null, null, null, null) == -1
+    assert lib.vfd_projection_reproject(0, 8, 8, null, null, null, null, null) == -2
     assert lib.vfd_feat_agg_fwd(null, null, null, null, null, null) == -1
     assert lib.vfd_feat_agg_bwd(null, null, null, null, null, null) == -1
     ad = _lib.AggDesc()

@@ -1,0 +1,113 @@
+"""GPU: the sub-method surface of the view synthesis -- Projection.backproject / reproject / forward
+(models/geometry/geometry_util.py:33-82) and ViewRendering.get_virtual_image (view_rendering.py:61-82) -- through the C
+ABI against the oracle (which is pinned bit for bit to the reference, tests/test_oracle_golden.py): coordinates and
+masks bit-exact, samples and gradients within 1e-4."""
+import pytest
+import torch
+
+from oracle import vfdepth_oracle as orc
+from tests import helpers as H
+from vfdepth_b200 import config as vcfg
+from vfdepth_b200.rig import make_rig
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a GPU')
+    return torch.device('cuda:0')
+
+
+def _pair(dataset, seed, cam=0, src=None, frame=-1):
+    """one (source, target) pair of a seeded rig: temporal (src None: same camera, frame f) or spatial (neighbour)."""
+    cfg = vcfg.default_config(dataset, batch_size=2, training__height=96, training__width=160,
+                              training__focal_length_scale=75)
+    inp, ex = make_rig(cfg, seed=seed, with_feats=False)
+    if src == 'nbr':
+        src = cfg['data']['rel_cam_list'][cam][0]
+    s = cam if src is None else src
+    T = ex['cam_T_cam'][frame][:, cam]
+    if src is not None:
+        T = inp['extrinsics_inv'][:, src] @ inp['extrinsics'][:, cam]
+        frame = 0
+    return dict(src_img=inp[('color', frame, 0)][:, s].contiguous(), src_mask=inp['mask'][:, s].contiguous(),
+                depth=ex['depth'][cam].contiguous(), invK=inp[('inv_K', 0)][:, cam].contiguous(),
+                K=inp[('K', 0)][:, s].contiguous(), T=T.contiguous())
+
+
+@pytest.mark.parametrize('dataset,cam,src', [('ddad', 0, None), ('ddad', 2, 'nbr'), ('nuscenes', 1, 'nbr')])
+def test_projection_grid_bit_exact_and_gradients(dataset, cam, src):
+    from vfdepth_b200.projection import Projection
+    dev = _dev()
+    p = _pair(dataset, 11, cam, src)
+    B, _, Hh, Ww = p['depth'].shape
+    proj = Projection(B, Hh, Ww, dev)
+    d = {k: v.to(dev) for k, v in p.items()}
+    depth = d['depth'].clone().requires_grad_(True)
+    T = d['T'].clone().requires_grad_(True)
+    K = d['K'].clone().requires_grad_(True)
+    grid = proj(depth, T, d['invK'], K)
+    dr = p['depth'].clone().requires_grad_(True)
+    Tr = p['T'].clone().requires_grad_(True)
+    Kr = p['K'].clone().requires_grad_(True)
+    ref = orc.reproject_grid(dr, Tr, p['invK'], Kr)
+    assert torch.equal(grid.cpu(), ref)
+    # the two halves on their own
+    pts = proj.backproject(d['invK'], d['depth'])
+    homo = orc.homo_points(B, Hh, Ww)
+    ref_pts = torch.cat([p['depth'].view(B, 1, -1) * torch.matmul(p['invK'][:, :3, :3], homo), homo[:, 2:3]], 1)
+    assert torch.equal(pts.cpu(), ref_pts)
+    assert torch.equal(proj.reproject(d['K'], pts, d['T']).cpu(), ref)
+    gen = torch.Generator().manual_seed(1)
+    up = torch.randn(ref.shape, generator=gen)
+    got = torch.autograd.grad((grid * up.to(dev)).sum(), [depth, T, K])
+    want = torch.autograd.grad((ref * up).sum(), [dr, Tr, Kr])
+    for n, a, b in zip(('d_depth', 'd_T', 'd_K'), got, want):
+        assert H.rel_err(a.cpu(), b) < TOL, (n, H.rel_err(a.cpu(), b))
+    with pytest.raises(ValueError):
+        proj(depth[:, :, :-1], T, d['invK'], K)
+
+
+@pytest.mark.parametrize('dataset,cam,src', [('ddad', 0, None), ('ddad', 3, 'nbr'), ('nuscenes', 5, 'nbr')])
+def test_get_virtual_image_matches_oracle(dataset, cam, src):
+    from vfdepth_b200 import view
+    dev = _dev()
+    p = _pair(dataset, 23, cam, src)
+    cfg = vcfg.default_config(dataset, batch_size=2, training__height=96, training__width=160)
+    vr = view.ViewRendering(cfg, 0)
+    d = {k: v.to(dev) for k, v in p.items()}
+    depth = d['depth'].clone().requires_grad_(True)
+    T = d['T'].clone().requires_grad_(True)
+    img, mask = vr.get_virtual_image(d['src_img'], d['src_mask'], depth, d['invK'], d['K'], T)
+    dr = p['depth'].clone().requires_grad_(True)
+    Tr = p['T'].clone().requires_grad_(True)
+    ref_img, ref_mask = orc.virtual_image(p['src_img'], p['src_mask'], dr, p['invK'], p['K'], Tr)
+    assert torch.equal(mask.cpu(), ref_mask.float())
+    assert float((img.cpu() - ref_img).abs().max()) < 1e-5
+    assert 200 < float(mask.sum()) < mask.numel()   # the pair really overlaps (neighbouring cameras: a narrow strip)
+    gen = torch.Generator().manual_seed(2)
+    up = torch.randn(ref_img.shape, generator=gen)
+    got = torch.autograd.grad((img * up.to(dev)).sum(), [depth, T])
+    want = torch.autograd.grad((ref_img * up).sum(), [dr, Tr])
+    # depth gradient: per pixel, compared on the scale of the whole map
+    assert H.rel_err(got[0].cpu(), want[0]) < 1e-3
+    assert H.rel_err(got[1].cpu(), want[1]) < 1e-3
+
+
+def test_virtual_image_nan_and_behind_camera():
+    """a NaN depth gives 2.0 / mask 0 (view_rendering.py:73-76); points behind the source camera are NOT rejected (the
+    reference has no z > 0 test): whatever the projection yields is sampled."""
+    from vfdepth_b200 import projection
+    dev = _dev()
+    p = _pair('ddad', 5, 0, None)
+    depth = p['depth'].clone()
+    depth[:, :, 10:12, 20:30] = float('nan')
+    depth[:, :, 40:44, 50:60] = -3.0
+    d = {k: v.to(dev) for k, v in p.items()}
+    img, mask = projection.get_virtual_image(d['src_img'], d['src_mask'], depth.to(dev), d['invK'], d['K'], d['T'])
+    ref_img, ref_mask = orc.virtual_image(p['src_img'], p['src_mask'], depth, p['invK'], p['K'], p['T'])
+    assert torch.equal(mask.cpu(), ref_mask.float())
+    assert float((img.cpu() - ref_img).abs().max()) < 1e-5
+    assert float(img[:, :, 10:12, 20:30].min()) == 2.0 and float(mask[:, :, 10:12, 20:30].max()) == 0.0

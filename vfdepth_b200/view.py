@@ -431,6 +431,12 @@ class ViewRendering(torch.nn.Module):
         if self.materialize:
             self.render(inputs, outputs, cam)
 
+    def get_virtual_image(self, src_img, src_mask, tar_depth, tar_invK, src_K, T, scale=0):
+        """view_rendering.py:61-82 for one (source, target) pair: (warped image, valid * warped mask); differentiable
+        w.r.t. tar_depth, T and src_K (csrc/warp_image.cu)."""
+        from . import projection
+        return projection.get_virtual_image(src_img, src_mask, tar_depth, tar_invK, src_K, T, scale)
+
     @torch.no_grad()
     def render(self, inputs, outputs, cam):
         """write the reference's image keys for camera ``cam`` (on demand)."""
