@@ -337,6 +337,15 @@ int vfd_projection_backproject(int B, int H, int W, const float* depth, const fl
 int vfd_projection_reproject(int B, int H, int W, const float* points, const float* K, const float* T, float* grid,
                              void* stream);
 
+/* ViewRendering.get_norm_image_single (view_rendering.py:39-59) for one warped image per batch element: intensity
+ * alignment of warp_img to the target image over the overlap (ref_mask * warp_mask), batch-wide early exit when any
+ * element has no overlap.  stats [B,8] f64 scratch (zero-filled here, kept for the backward); out [B,3,H,W].
+ * Backward w.r.t. warp_img only (the statistics are constants, as under torch.no_grad in the reference). */
+int vfd_norm_image_fwd(int B, int H, int W, const float* ref_img, const float* ref_mask, const float* warp_img,
+                       const float* warp_mask, double* stats, float* out, void* stream);
+int vfd_norm_image_bwd(int B, int H, int W, const float* warp_mask, const double* stats, const float* d_out,
+                       float* d_warp, void* stream);
+
 /* --------------------------------------------------------------------------------------------------
  * Multi-level feature aggregation in front of the fusion (network/fusion_depthnet.py:57-66,
  * network/fusion_posenet.py:62-70):  LeakyReLU(conv1x1(cat[f_lev, up(f_lev+1), ...]) + b), up = F.interpolate(bilinear,

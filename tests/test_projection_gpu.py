@@ -111,3 +111,61 @@ def test_virtual_image_nan_and_behind_camera():
     assert torch.equal(mask.cpu(), ref_mask.float())
     assert float((img.cpu() - ref_img).abs().max()) < 1e-5
     assert float(img[:, :, 10:12, 20:30].min()) == 2.0 and float(mask[:, :, 10:12, 20:30].max()) == 0.0
+
+
+@pytest.mark.parametrize('dataset,cam', [('ddad', 0), ('nuscenes', 4)])
+def test_get_virtual_depth_matches_oracle(dataset, cam):
+    """view_rendering.py:84-116 (forward-only sub-method): a neighbour's depth map seen from a slightly rotated copy of
+    the camera, mask identical (up to 1e-4 of the pixels at the depth-range thresholds), depth within 1e-4."""
+    from vfdepth_b200 import view
+    from vfdepth_b200.rig import axis_angle_to_matrix
+    dev = _dev()
+    cfg = vcfg.default_config(dataset, batch_size=2, training__height=96, training__width=160,
+                              training__focal_length_scale=75)
+    inp, ex = make_rig(cfg, seed=31, with_feats=False)
+    src = cfg['data']['rel_cam_list'][cam][0]
+    tform = torch.eye(4).repeat(2, 1, 1)
+    tform[:, :3, :3] = axis_angle_to_matrix(torch.tensor([[0.03, -0.02, 0.05], [-0.04, 0.01, 0.02]]))
+    ext_aug = tform @ inp['extrinsics'][:, cam]
+    T = torch.inverse(ext_aug) @ inp['extrinsics'][:, src]                 # source -> (novel) target
+    t = cfg['training']
+    args = (ex['depth'][src], inp['mask'][:, src], inp[('inv_K', 0)][:, src], inp[('K', 0)][:, src], ex['depth'][cam],
+            inp[('inv_K', 0)][:, cam], inp[('K', 0)][:, cam], T)
+    ref_d, ref_m = orc.virtual_depth(*[a.clone() for a in args], t['min_depth'], t['max_depth'])
+    vr = view.ViewRendering(cfg, 0)
+    got_d, got_m = vr.get_virtual_depth(*[a.to(dev) for a in args], t['min_depth'], t['max_depth'])
+    assert got_d.shape == ref_d.shape and got_m.shape == ref_m.shape
+    flips = got_m.cpu() != ref_m                         # the depth-range tests sit on a computed value
+    assert float(flips.float().mean()) < 1e-4
+    assert 200 < float(got_m.sum())
+    assert H.rel_err(got_d.cpu(), ref_d) < TOL           # same tolerance as the fused form (tests/test_warp_gpu.py)
+
+
+@pytest.mark.parametrize('empty', [False, True])
+def test_get_norm_image_single_matches_oracle(empty):
+    """view_rendering.py:39-59: aligned image and its gradient w.r.t. the warped image; with an empty overlap in ONE batch
+    element the whole batch is returned unchanged (the reference's batch-wide early exit)."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    p = _pair('ddad', 41, 0, None)
+    cfg = vcfg.default_config('ddad', batch_size=2, training__height=96, training__width=160)
+    vr = view.ViewRendering(cfg, 0)
+    ref_img = p['src_img'].flip(-1).contiguous() * 0.8 + 0.1       # a "target" image with different statistics
+    ref_mask = p['src_mask']
+    warp_img, warp_mask = orc.virtual_image(p['src_img'], p['src_mask'], p['depth'], p['invK'], p['K'], p['T'])
+    warp_mask = warp_mask.float()
+    if empty:
+        warp_mask = warp_mask.clone()
+        warp_mask[1] = 0
+    wr = warp_img.clone().requires_grad_(True)
+    ref = orc.norm_image_single(ref_img, ref_mask, wr, warp_mask)
+    wg = warp_img.to(dev).requires_grad_(True)
+    got = vr.get_norm_image_single(ref_img.to(dev), ref_mask.to(dev), wg, warp_mask.to(dev))
+    if empty:
+        assert torch.equal(got.cpu(), warp_img)
+    assert H.rel_err(got.cpu(), ref.detach()) < TOL
+    gen = torch.Generator().manual_seed(4)
+    up = torch.randn(ref.shape, generator=gen)
+    g_ref, = torch.autograd.grad((ref * up).sum(), wr)
+    g_got, = torch.autograd.grad((got * up.to(dev)).sum(), wg)
+    assert H.rel_err(g_got.cpu(), g_ref) < TOL

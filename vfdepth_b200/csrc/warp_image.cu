@@ -238,3 +238,122 @@ extern "C" int vfd_projection_reproject(int B, int H, int W, const float* points
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// ViewRendering.get_norm_image_single (view_rendering.py:39-59) for one warped image per batch element:
+//   mask = (src_mask * warp_mask) != 0 on 3 channels; if ANY batch element has an empty mask the warp is returned as is;
+//   mean = masked mean, var = sum over ALL pixels of (x - mean)^2 / (3 H W), std = sqrt(var + 1e-16)   (get_mean_std :30-37)
+//   out = ((warp - w_mean) / (w_std + 1e-8) * s_std + s_mean) * warp_mask.
+// The statistics are constants for autograd (torch.no_grad in the reference); sums in f64.
+// ---------------------------------------------------------------------------------------------------------
+namespace vfd {
+
+struct NormArgs {
+    int B, H, W;
+    const float* ref;        // [B,3,H,W] target image (the reference's src_img argument)
+    const float* ref_mask;   // [B,1,H,W]
+    const float* warp;       // [B,3,H,W]
+    const float* warp_mask;  // [B,1,H,W]
+    double* stats;           // [B,8]: count, sum ref*m, sum warp*m, sum warp, sum warp^2, sum ref, sum ref^2, -
+    float* out;              // [B,3,H,W]
+    const float* d_out;
+    float* d_warp;
+};
+
+__global__ void __launch_bounds__(kWiThreads) norm_stats_kernel(const NormArgs a) {
+    __shared__ double s_red[kWiThreads / 32][7];
+    const int b = blockIdx.y, HW = a.H * a.W, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int p = blockIdx.x * kWiThreads + threadIdx.x; p < HW; p += gridDim.x * kWiThreads) {
+        const float m = (__ldg(a.ref_mask + (size_t)b * HW + p) * __ldg(a.warp_mask + (size_t)b * HW + p)) != 0.f ? 1.f : 0.f;
+        float sr = 0.f, sw = 0.f, sr2 = 0.f, sw2 = 0.f;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float r = __ldg(a.ref + ((size_t)b * 3 + c) * HW + p), w = __ldg(a.warp + ((size_t)b * 3 + c) * HW + p);
+            sr += r; sw += w; sr2 = fmaf(r, r, sr2); sw2 = fmaf(w, w, sw2);
+        }
+        acc[0] += 3.0 * m; acc[1] += (double)(sr * m); acc[2] += (double)(sw * m);
+        acc[3] += sw; acc[4] += sw2; acc[5] += sr; acc[6] += sr2;
+    }
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+        double v = acc[i];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_red[warp][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 7) {
+        double v = 0;
+#pragma unroll
+        for (int w = 0; w < kWiThreads / 32; ++w) v += s_red[w][threadIdx.x];
+        atomicAdd(a.stats + (size_t)b * 8 + threadIdx.x, v);
+    }
+}
+
+// {w_mean, 1 / (w_std + 1e-8), s_std, s_mean} of batch element b; apply = 0 when any element of the batch has no overlap
+__device__ __forceinline__ bool norm_params(const NormArgs& a, int b, float* prm) {
+    bool apply = true;
+    for (int i = 0; i < a.B; ++i) apply = apply && a.stats[(size_t)i * 8] > 0.0;
+    const double* s = a.stats + (size_t)b * 8;
+    const double n = 3.0 * a.H * a.W, cnt = s[0] + 1e-8;
+    const double wm = s[2] / cnt, sm = s[1] / cnt;
+    const double wv = (s[4] - 2.0 * wm * s[3] + n * wm * wm) / n, sv = (s[6] - 2.0 * sm * s[5] + n * sm * sm) / n;
+    prm[0] = (float)wm;
+    prm[1] = (float)(1.0 / (sqrt((wv > 0 ? wv : 0) + 1e-16) + 1e-8));
+    prm[2] = (float)sqrt((sv > 0 ? sv : 0) + 1e-16);
+    prm[3] = (float)sm;
+    return apply;
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(kWiThreads) norm_apply_kernel(const NormArgs a) {
+    __shared__ float s_prm[4];
+    __shared__ int s_apply;
+    const int b = blockIdx.y, HW = a.H * a.W;
+    if (threadIdx.x == 0) s_apply = norm_params(a, b, s_prm) ? 1 : 0;
+    __syncthreads();
+    const bool apply = s_apply != 0;
+    const float wm = s_prm[0], iw = s_prm[1], ss = s_prm[2], sm = s_prm[3];
+    for (int p = blockIdx.x * kWiThreads + threadIdx.x; p < HW; p += gridDim.x * kWiThreads) {
+        const float m = __ldg(a.warp_mask + (size_t)b * HW + p);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const size_t i = ((size_t)b * 3 + c) * HW + p;
+            if (BWD) a.d_warp[i] = apply ? __ldg(a.d_out + i) * (iw * ss) * m : __ldg(a.d_out + i);
+            else a.out[i] = apply ? ((__ldg(a.warp + i) - wm) * iw * ss + sm) * m : __ldg(a.warp + i);
+        }
+    }
+}
+
+}  // namespace vfd
+
+extern "C" int vfd_norm_image_fwd(int B, int H, int W, const float* ref_img, const float* ref_mask, const float* warp_img,
+                                  const float* warp_mask, double* stats, float* out, void* stream) {
+    int rc = check_wi(B, H, W);
+    if (rc) return rc;
+    if (!ref_img || !ref_mask || !warp_img || !warp_mask || !stats || !out) return VFD_ERR_NULL;
+    if (reinterpret_cast<uintptr_t>(stats) & 7) return VFD_ERR_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(stats, 0, sizeof(double) * 8 * B, st) != cudaSuccess) return VFD_ERR_CUDA;
+    NormArgs a = {};
+    a.B = B; a.H = H; a.W = W; a.ref = ref_img; a.ref_mask = ref_mask; a.warp = warp_img; a.warp_mask = warp_mask;
+    a.stats = stats; a.out = out;
+    norm_stats_kernel<<<dim3(kWiBlocks, B), kWiThreads, 0, st>>>(a);
+    norm_apply_kernel<false><<<dim3(kWiBlocks, B), kWiThreads, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+extern "C" int vfd_norm_image_bwd(int B, int H, int W, const float* warp_mask, const double* stats, const float* d_out,
+                                  float* d_warp, void* stream) {
+    int rc = check_wi(B, H, W);
+    if (rc) return rc;
+    if (!warp_mask || !stats || !d_out || !d_warp) return VFD_ERR_NULL;
+    NormArgs a = {};
+    a.B = B; a.H = H; a.W = W; a.warp_mask = warp_mask; a.stats = const_cast<double*>(stats); a.d_out = d_out;
+    a.d_warp = d_warp;
+    norm_apply_kernel<true><<<dim3(kWiBlocks, B), kWiThreads, 0, (cudaStream_t)stream>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}

@@ -140,3 +140,38 @@ class Projection(torch.nn.Module):
         self._check(B, H, W)
         c = lambda t: t.float().contiguous()
         return _ProjectionGrid.apply(c(depth), c(bp_invK), c(rp_K), c(T))
+
+
+class _NormImage(torch.autograd.Function):
+    """vfd_norm_image_fwd / _bwd: intensity alignment of one warped image per batch element."""
+
+    @staticmethod
+    def forward(ctx, ref_img, ref_mask, warp_img, warp_mask):
+        B, _, H, W = warp_img.shape
+        _chk(ref_img, 'src_img', (B, 3, H, W))
+        _chk(ref_mask, 'src_mask', (B, 1, H, W))
+        _chk(warp_img, 'warp_img', (B, 3, H, W))
+        _chk(warp_mask, 'warp_mask', (B, 1, H, W))
+        stats = torch.empty((B, 8), device=warp_img.device, dtype=torch.float64)
+        out = torch.empty_like(warp_img)
+        _lib.call('vfd_norm_image_fwd', B, H, W, _lib.ptr(ref_img), _lib.ptr(ref_mask), _lib.ptr(warp_img),
+                  _lib.ptr(warp_mask), _lib.ptr(stats), _lib.ptr(out), _stream())
+        ctx.save_for_backward(warp_mask, stats)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        warp_mask, stats = ctx.saved_tensors
+        B, _, H, W = warp_mask.shape
+        d_warp = torch.empty((B, 3, H, W), device=d_out.device)
+        _lib.call('vfd_norm_image_bwd', B, H, W, _lib.ptr(warp_mask), _lib.ptr(stats), _lib.ptr(d_out.contiguous()),
+                  _lib.ptr(d_warp), _stream())
+        return None, None, d_warp, None
+
+
+def get_norm_image_single(src_img, src_mask, warp_img, warp_mask):
+    """view_rendering.py:39-59 (``src_img`` / ``src_mask`` are the TARGET frame's image and mask there): the warped
+    image with its masked mean / standard deviation aligned to the target's over their overlap, times ``warp_mask``;
+    returned unchanged when any batch element has no overlap.  Gradient flows to ``warp_img`` only."""
+    c = lambda t: t.float().contiguous()
+    return _NormImage.apply(c(src_img), c(src_mask), c(warp_img), c(warp_mask.detach()))

@@ -437,6 +437,40 @@ class ViewRendering(torch.nn.Module):
         from . import projection
         return projection.get_virtual_image(src_img, src_mask, tar_depth, tar_invK, src_K, T, scale)
 
+    def get_norm_image_single(self, src_img, src_mask, warp_img, warp_mask):
+        """view_rendering.py:39-59 for one warped image per batch element (csrc/warp_image.cu)."""
+        from . import projection
+        return projection.get_norm_image_single(src_img, src_mask, warp_img, warp_mask)
+
+    @torch.no_grad()
+    def get_virtual_depth(self, src_depth, src_mask, src_invK, src_K, tar_depth, tar_invK, tar_K, T, min_depth,
+                          max_depth, scale=0):
+        """view_rendering.py:84-116 for one (source, target) pair: (source depth seen from the target view, clamped to
+        [min_depth, max_depth]; its mask).  Forward-only: the differentiable form is the fused consistency loss
+        (``depth_syn_loss`` / ``DepthSynLoss``), which this calls with a two-camera descriptor (camera 1 = source)."""
+        B, _, H, W = src_depth.shape
+        c = lambda t: t.float().contiguous()
+        depth = c(torch.cat([tar_depth, src_depth], 1))
+        mask = c(torch.cat([torch.zeros_like(src_mask), src_mask], 1))
+        K, invK = c(torch.stack([tar_K, src_K], 1)), c(torch.stack([tar_invK, src_invK], 1))
+        _chk(depth, 'depth', (B, 2, H, W))
+        _chk(mask, 'mask', (B, 2, H, W))
+        d = _lib.SynDesc()
+        d.B, d.num_cams, d.H, d.W, d.cam0, d.n_call = B, 2, H, W, 0, 1
+        d.min_depth, d.max_depth = float(min_depth), float(max_depth)
+        d.mask, d.K, d.invK = mask.data_ptr(), K.data_ptr(), invK.data_ptr()
+        for cam in range(2):
+            for i in range(3):
+                d.src[cam][i] = 1 if (cam == 0 and i == 0) else -1
+        T3 = c(T[:, None, None].expand(B, 1, 3, 4, 4))
+        Tinv3 = c(torch.inverse(T3))
+        out_d = torch.zeros((B, 1, 3, H, W), device=depth.device)
+        out_m = torch.zeros_like(out_d)
+        sums = torch.empty((1, 2), device=depth.device, dtype=torch.float64)
+        _lib.call('vfd_depth_syn_fwd', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(c(tar_depth)), _lib.ptr(T3),
+                  _lib.ptr(Tinv3), _lib.ptr(sums), _lib.ptr(out_d), _lib.ptr(out_m), _stream())
+        return out_d[:, 0, 0:1].contiguous(), out_m[:, 0, 0:1].contiguous()
+
     @torch.no_grad()
     def render(self, inputs, outputs, cam):
         """write the reference's image keys for camera ``cam`` (on demand)."""
