@@ -346,6 +346,15 @@ int vfd_norm_image_fwd(int B, int H, int W, const float* ref_img, const float* r
 int vfd_norm_image_bwd(int B, int H, int W, const float* warp_mask, const double* stats, const float* d_out,
                        float* d_warp, void* stream);
 
+/* loss_util.compute_ssim_loss / compute_photometric_loss (models/losses/loss_util.py:43-78) of two images:
+ *   ssim  [B,3,H,W] (optional) = clamp((1 - SSIM_3x3,reflect) / 2, 0, 1) per channel
+ *   photo [B,1,H,W] (optional) = 0.85 * mean_c ssim + 0.15 * mean_c |target - pred|
+ * backward w.r.t. pred for upstreams d_ssim and / or d_photo; d_pred [B,3,H,W] zero-filled here, accumulated. */
+int vfd_photometric_loss_fwd(int B, int H, int W, const float* pred, const float* target, float* ssim, float* photo,
+                             void* stream);
+int vfd_photometric_loss_bwd(int B, int H, int W, const float* pred, const float* target, const float* d_ssim,
+                             const float* d_photo, float* d_pred, void* stream);
+
 /* --------------------------------------------------------------------------------------------------
  * Multi-level feature aggregation in front of the fusion (network/fusion_depthnet.py:57-66,
  * network/fusion_posenet.py:62-70):  LeakyReLU(conv1x1(cat[f_lev, up(f_lev+1), ...]) + b), up = F.interpolate(bilinear,

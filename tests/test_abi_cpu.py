@@ -102,6 +102,9 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.vfd_warp_image_fwd(2, 1, 8, null, null, null, null, null, null, null, null, null, null) == -2
     assert lib.vfd_warp_image_bwd(2, 8, 8, null, null, null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_projection_backproject(2, 8, 8, null, null, null, null) == -1
+    assert lib.vfd_photometric_loss_fwd(2, 8, 8, null, null, null, null, null) == -1
+    assert lib.vfd_photometric_loss_bwd(2, 8, 8, null, null, null, null, null, null) == -1
+    assert lib.vfd_photometric_loss_fwd(2, 8, 1, null, null, null, null, null) == -2
     assert lib.vfd_norm_image_fwd(2, 8, 8, null, null, null, null, null, null, null) == -1
     assert lib.vfd_norm_image_bwd(2, 8, 1, null, null, null, null, null) == -2
     assert lib.vfd_projection_reproject(0, 8, 8, null, null, null, null, null) == -2

@@ -169,3 +169,27 @@ def test_get_norm_image_single_matches_oracle(empty):
     g_ref, = torch.autograd.grad((ref * up).sum(), wr)
     g_got, = torch.autograd.grad((got * up.to(dev)).sum(), wg)
     assert H.rel_err(g_got.cpu(), g_ref) < TOL
+
+
+def test_photometric_free_functions_match_oracle():
+    """loss_util.compute_ssim_loss / compute_photometric_loss (:43-78) on two images: values within 1e-5 absolute
+    (fp32 noise floor of E[x^2] - mu^2), gradients w.r.t. pred within 1e-3 of the map's scale (the clamp and |.| kinks
+    are decided on values that differ by an ulp)."""
+    from vfdepth_b200 import loss_util
+    dev = _dev()
+    p = _pair('ddad', 61, 0, None)
+    target = p['src_img']
+    pred, _ = orc.virtual_image(p['src_img'], p['src_mask'], p['depth'], p['invK'], p['K'], p['T'])
+    pr = pred.clone().requires_grad_(True)
+    pg = pred.to(dev).requires_grad_(True)
+    gen = torch.Generator().manual_seed(8)
+    for fn_ref, fn_got, ch in ((orc.ssim_loss, loss_util.compute_ssim_loss, 3),
+                               (orc.photometric_loss, loss_util.compute_photometric_loss, 1)):
+        ref = fn_ref(pr, target)
+        got = fn_got(pg, target.to(dev))
+        assert got.shape == ref.shape == (2, ch, 96, 160)
+        assert float((got.cpu() - ref).abs().max()) < 1e-5
+        up = torch.randn(ref.shape, generator=gen)
+        g_ref, = torch.autograd.grad((ref * up).sum(), pr)
+        g_got, = torch.autograd.grad((got * up.to(dev)).sum(), pg)
+        assert H.rel_err(g_got.cpu(), g_ref) < 1e-3
