@@ -355,6 +355,25 @@ int vfd_photometric_loss_fwd(int B, int H, int W, const float* pred, const float
 int vfd_photometric_loss_bwd(int B, int H, int W, const float* pred, const float* target, const float* d_ssim,
                              const float* d_photo, float* d_pred, void* stream);
 
+/* loss_util.compute_auto_masks (models/losses/loss_util.py:6-18): mask [B,1,HW] = 1 where the first arg-min over
+ * cat[reproj [B,F1,HW], identity [B,F2,HW]] along the channel is channel 0 (torch.argmin order: first minimum, NaN
+ * smallest), else 0.  F2 = 0 / identity = NULL compares the reprojection channels only.  No gradient. */
+int vfd_auto_masks(int B, int F1, int F2, int HW, const float* reproj, const float* identity, float* mask, void* stream);
+
+/* loss_util.compute_masked_loss (:21-25) over n elements: sums [2] f64 (zero-filled here) = sum(loss * mask), sum(mask);
+ * the value is sums[0] / (sums[1] + 1e-8).  backward: d_loss [n] = d_out[0] * mask / (sums[1] + 1e-8), d_out a device
+ * scalar. */
+int vfd_masked_loss_fwd(size_t n, const float* loss, const float* mask, double* sums, void* stream);
+int vfd_masked_loss_bwd(size_t n, const float* mask, const double* sums, const float* d_out, float* d_loss, void* stream);
+
+/* loss_util.compute_edg_smooth_loss (:28-40) WITHOUT the mean normalisation of single_cam_loss.py:57-65 (which
+ * vfd_smooth_loss_* fuses): rgb [B,C,H,W], disp [B,1,H,W]; sums [2] f64 (zero-filled here) = sum of
+ * |disp[x] - disp[x+1]| exp(-mean_c |rgb[x] - rgb[x+1]|) and of the y term; the value is
+ * sums[0] / (B*H*(W-1)) + sums[1] / (B*(H-1)*W).  backward w.r.t. disp (d_out a device scalar), one write per pixel. */
+int vfd_edg_smooth_loss_fwd(int B, int C, int H, int W, const float* rgb, const float* disp, double* sums, void* stream);
+int vfd_edg_smooth_loss_bwd(int B, int C, int H, int W, const float* rgb, const float* disp, const float* d_out,
+                            float* d_disp, void* stream);
+
 /* --------------------------------------------------------------------------------------------------
  * Multi-level feature aggregation in front of the fusion (network/fusion_depthnet.py:57-66,
  * network/fusion_posenet.py:62-70):  LeakyReLU(conv1x1(cat[f_lev, up(f_lev+1), ...]) + b), up = F.interpolate(bilinear,

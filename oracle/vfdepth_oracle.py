@@ -348,6 +348,23 @@ def photometric_loss(pred, target):
     return 0.85 * ssim_loss(pred, target).mean(1, True) + 0.15 * l1
 
 
+def auto_masks(reprojection_loss, identity_reprojection_loss):
+    """loss_util.py:6-18"""
+    if identity_reprojection_loss is None:
+        return torch.ones_like(reprojection_loss)
+    idxs = torch.argmin(torch.cat([reprojection_loss, identity_reprojection_loss], dim=1), dim=1, keepdim=True)
+    return (idxs == 0).float()
+
+
+def edg_smooth_loss_raw(rgb, disp_map):
+    """loss_util.py:28-40 as the free function is written (no mean normalisation)."""
+    grx = (rgb[:, :, :, :-1] - rgb[:, :, :, 1:]).abs().mean(1, True)
+    gry = (rgb[:, :, :-1, :] - rgb[:, :, 1:, :]).abs().mean(1, True)
+    gdx = (disp_map[:, :, :, :-1] - disp_map[:, :, :, 1:]).abs() * (-1.0 * grx).exp()
+    gdy = (disp_map[:, :, :-1, :] - disp_map[:, :, 1:, :]).abs() * (-1.0 * gry).exp()
+    return gdx.mean() + gdy.mean()
+
+
 def masked_loss(loss, mask):
     """loss_util.py:21-25 -- sums run over the whole local batch."""
     return (loss * mask).sum() / (mask.sum() + 1e-8)

@@ -3,7 +3,8 @@
     python tests/golden/make_golden.py            # needs /root/reference (or $VFDEPTH_REF)
 
 Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz``, ``golden_depth_syn.npz``,
-``golden_feat_agg.npz`` next to this file (``--only-new`` regenerates just the last three, ``--only-agg`` the last).  The
+``golden_feat_agg.npz``, ``golden_loss_free.npz`` next to this file (``--only-new`` regenerates all but the first two,
+``--only-agg`` / ``--only-loss`` just that one).  The
 fixtures hold the seeded inputs and what the reference's own classes
 (``VFNet``, ``ViewRendering``, ``Pose``, ``MultiCamLoss``) returned for them, at
 sizes small enough to commit.  ``tests/test_oracle_golden.py`` then pins
@@ -285,7 +286,39 @@ def make_feat_agg(path):
     print('wrote', path, [tuple(x.shape) for x in levels], tuple(cap['agg'].shape))
 
 
+def make_loss_free(ref, path):
+    """The reference's loss_util free functions (models/losses/loss_util.py:6-78) on seeded smooth images."""
+    gen = torch.Generator().manual_seed(515)
+    B, Hh, Ww = 2, 24, 40
+    base = torch.rand(B, 3, Hh // 4, Ww // 4, generator=gen)
+    target = torch.nn.functional.interpolate(base, size=(Hh, Ww), mode='bilinear', align_corners=True)
+    pred = (target + 0.05 * torch.randn(B, 3, Hh, Ww, generator=gen)).clamp(0, 1)
+    disp = torch.rand(B, 1, Hh, Ww, generator=gen)
+    reproj = torch.rand(B, 1, Hh, Ww, generator=gen)
+    ident = torch.rand(B, 2, Hh, Ww, generator=gen)
+    ident[:, 0, ::3] = reproj[:, 0, ::3]                      # ties: the first minimum wins
+    mask = (torch.rand(B, 1, Hh, Ww, generator=gen) > 0.4).float()
+    lu = ref.loss_util
+    pr = pred.clone().requires_grad_(True)
+    ssim = lu.compute_ssim_loss(pr, target)
+    photo = lu.compute_photometric_loss(pr, target)
+    dd = disp.clone().requires_grad_(True)
+    sm = lu.compute_edg_smooth_loss(target, dd)
+    ll = photo.detach().clone().requires_grad_(True)
+    ml = lu.compute_masked_loss(ll, mask)
+    out = {'pred': pred, 'target': target, 'disp': disp, 'reproj': reproj, 'ident': ident, 'mask': mask,
+           'ssim': ssim, 'photo': photo, 'auto_mask': lu.compute_auto_masks(reproj, ident),
+           'auto_mask_none': lu.compute_auto_masks(reproj, None), 'smooth': sm, 'masked': ml,
+           'd_disp': torch.autograd.grad(sm, dd)[0], 'd_loss': torch.autograd.grad(ml, ll)[0],
+           'd_pred': torch.autograd.grad(photo.sum(), pr)[0]}
+    np.savez_compressed(path, **{k: _np(v) for k, v in out.items()})
+    print('wrote', path)
+
+
 if __name__ == '__main__':
+    if '--only-loss' in sys.argv:
+        make_loss_free(ref_import.load(), os.path.join(HERE, 'golden_loss_free.npz'))
+        sys.exit(0)
     if '--only-agg' in sys.argv:
         make_feat_agg(os.path.join(HERE, 'golden_feat_agg.npz'))
         sys.exit(0)
@@ -296,3 +329,4 @@ if __name__ == '__main__':
     make_to_depth(os.path.join(HERE, 'golden_to_depth.npz'))
     make_depth_syn(ref, os.path.join(HERE, 'golden_depth_syn.npz'))
     make_feat_agg(os.path.join(HERE, 'golden_feat_agg.npz'))
+    make_loss_free(ref, os.path.join(HERE, 'golden_loss_free.npz'))

@@ -105,6 +105,14 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.vfd_photometric_loss_fwd(2, 8, 8, null, null, null, null, null) == -1
     assert lib.vfd_photometric_loss_bwd(2, 8, 8, null, null, null, null, null, null) == -1
     assert lib.vfd_photometric_loss_fwd(2, 8, 1, null, null, null, null, null) == -2
+    assert lib.vfd_auto_masks(2, 2, 2, 64, null, null, null, null) == -1
+    assert lib.vfd_auto_masks(2, 0, 2, 64, null, null, null, null) == -2
+    assert lib.vfd_masked_loss_fwd(ctypes.c_size_t(64), null, null, null, null) == -1
+    assert lib.vfd_masked_loss_fwd(ctypes.c_size_t(0), null, null, null, null) == -2
+    assert lib.vfd_masked_loss_bwd(ctypes.c_size_t(64), null, null, null, null, null) == -1
+    assert lib.vfd_edg_smooth_loss_fwd(2, 3, 8, 8, null, null, null, null) == -1
+    assert lib.vfd_edg_smooth_loss_fwd(2, 3, 1, 8, null, null, null, null) == -2
+    assert lib.vfd_edg_smooth_loss_bwd(2, 3, 8, 8, null, null, null, null, null) == -1
     assert lib.vfd_norm_image_fwd(2, 8, 8, null, null, null, null, null, null, null) == -1
     assert lib.vfd_norm_image_bwd(2, 8, 1, null, null, null, null, null) == -2
     assert lib.vfd_projection_reproject(0, 8, 8, null, null, null, null, null) == -2

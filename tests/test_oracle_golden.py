@@ -117,3 +117,26 @@ def test_aggregate_features_bit_exact():
     for i in range(3):
         assert torch.equal(grads[i], g['d_feat_%d' % i]), i
     assert torch.equal(grads[3], g['d_weight']) and torch.equal(grads[4], g['d_bias'])
+
+
+def test_loss_free_functions_bit_exact():
+    """oracle ssim_loss / photometric_loss / auto_masks / masked_loss / edg_smooth_loss_raw against the reference's
+    loss_util free functions (models/losses/loss_util.py:6-78; fixture: make_golden.py --only-loss), values and
+    gradients bit for bit."""
+    g = H.load_npz('golden_loss_free.npz')
+    pr = g['pred'].clone().requires_grad_(True)
+    photo = orc.photometric_loss(pr, g['target'])
+    assert torch.equal(orc.ssim_loss(pr, g['target']).detach(), g['ssim'])
+    assert torch.equal(photo.detach(), g['photo'])
+    assert torch.equal(torch.autograd.grad(photo.sum(), pr)[0], g['d_pred'])
+    assert torch.equal(orc.auto_masks(g['reproj'], g['ident']), g['auto_mask'])
+    assert torch.equal(orc.auto_masks(g['reproj'], None), g['auto_mask_none'])
+    assert 0.2 < float(g['auto_mask'].mean()) < 0.9
+    dd = g['disp'].clone().requires_grad_(True)
+    sm = orc.edg_smooth_loss_raw(g['target'], dd)
+    assert torch.equal(sm.detach(), g['smooth'])
+    assert torch.equal(torch.autograd.grad(sm, dd)[0], g['d_disp'])
+    ll = g['photo'].clone().requires_grad_(True)
+    ml = orc.masked_loss(ll, g['mask'])
+    assert torch.equal(ml.detach(), g['masked'])
+    assert torch.equal(torch.autograd.grad(ml, ll)[0], g['d_loss'])

@@ -193,3 +193,64 @@ def test_photometric_free_functions_match_oracle():
         g_ref, = torch.autograd.grad((ref * up).sum(), pr)
         g_got, = torch.autograd.grad((got * up.to(dev)).sum(), pg)
         assert H.rel_err(g_got.cpu(), g_ref) < 1e-3
+
+
+def test_loss_free_functions_match_reference_fixture():
+    """loss_util.compute_auto_masks / compute_masked_loss / compute_edg_smooth_loss (:6-40) and the photometric pair on
+    the fixture the reference itself produced (tests/golden/golden_loss_free.npz): the auto-mask bit-exact (ties and
+    all), the masked-loss gradient bit-exact, scalars within 1e-6 relative (f64 sums against torch's fp32 tree),
+    the smoothness gradient within 1e-5 of its scale (expf against the host's exp)."""
+    from vfdepth_b200 import loss_util
+    dev = _dev()
+    g = {k: v.to(dev) for k, v in H.load_npz('golden_loss_free.npz').items()}
+    assert torch.equal(loss_util.compute_auto_masks(g['reproj'], g['ident']), g['auto_mask'])
+    assert torch.equal(loss_util.compute_auto_masks(g['reproj'], None), g['auto_mask_none'])
+    # NaN is the smallest value of torch.argmin; the first one wins
+    rp, idl = g['reproj'].clone(), g['ident'].clone()
+    rp[0, 0, 0, :5] = float('nan')
+    idl[1, 1, 3, :7] = float('nan')
+    idl[0, 0, 0, 2] = float('nan')
+    assert torch.equal(loss_util.compute_auto_masks(rp, idl).cpu(), orc.auto_masks(rp.cpu(), idl.cpu()))
+
+    ll = g['photo'].clone().requires_grad_(True)
+    ml = loss_util.compute_masked_loss(ll, g['mask'])
+    assert ml.shape == g['masked'].shape
+    assert abs(float(ml) - float(g['masked'])) < 1e-6 * abs(float(g['masked']))
+    d_loss, = torch.autograd.grad(ml, ll)
+    assert H.rel_err(d_loss.cpu(), g['d_loss'].cpu()) < 1e-6
+    zero = loss_util.compute_masked_loss(g['photo'], torch.zeros_like(g['mask']))
+    assert float(zero) == 0.0                                           # empty mask: 0 / 1e-8
+
+    dd = g['disp'].clone().requires_grad_(True)
+    sm = loss_util.compute_edg_smooth_loss(g['target'], dd)
+    assert abs(float(sm) - float(g['smooth'])) < 1e-6 * abs(float(g['smooth']))
+    d_disp, = torch.autograd.grad(sm * 3.0, dd)
+    assert H.rel_err(d_disp.cpu(), 3.0 * g['d_disp'].cpu()) < 1e-5
+
+    pr = g['pred'].clone().requires_grad_(True)
+    photo = loss_util.compute_photometric_loss(pr, g['target'])
+    assert float((photo - g['photo']).abs().max()) < 1e-5
+    assert float((loss_util.compute_ssim_loss(pr, g['target']) - g['ssim']).abs().max()) < 1e-5
+    with pytest.raises(ValueError):
+        loss_util.compute_masked_loss(g['photo'].cpu(), g['mask'].cpu())
+
+
+def test_loss_free_functions_full_size():
+    """the three free functions at 8 x 384 x 640 against the oracle on the same seeded inputs."""
+    from vfdepth_b200 import loss_util
+    dev = _dev()
+    gen = torch.Generator().manual_seed(77)
+    B, Hh, Ww = 8, 384, 640
+    rgb = torch.nn.functional.interpolate(torch.rand(B, 3, 48, 80, generator=gen), size=(Hh, Ww), mode='bilinear',
+                                          align_corners=True)
+    disp = torch.rand(B, 1, Hh, Ww, generator=gen).requires_grad_(True)
+    rp, idl = torch.rand(B, 1, Hh, Ww, generator=gen), torch.rand(B, 2, Hh, Ww, generator=gen)
+    mask = orc.auto_masks(rp, idl)
+    assert torch.equal(loss_util.compute_auto_masks(rp.to(dev), idl.to(dev)).cpu(), mask)
+    ref = orc.edg_smooth_loss_raw(rgb, disp) + orc.masked_loss(disp, mask)
+    dg = disp.detach().to(dev).requires_grad_(True)
+    got = loss_util.compute_edg_smooth_loss(rgb.to(dev), dg) + loss_util.compute_masked_loss(dg, mask.to(dev))
+    assert abs(float(got) - float(ref)) < 1e-5 * abs(float(ref))
+    g_ref, = torch.autograd.grad(ref, disp)
+    g_got, = torch.autograd.grad(got, dg)
+    assert H.rel_err(g_got.cpu(), g_ref) < 1e-5
