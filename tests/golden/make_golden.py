@@ -4,7 +4,7 @@
 
 Writes ``golden_fusion.npz``, ``golden_warp.npz`` and ``golden_to_depth.npz``, ``golden_depth_syn.npz``,
 ``golden_feat_agg.npz``, ``golden_loss_free.npz`` next to this file (``--only-new`` regenerates all but the first two,
-``--only-agg`` / ``--only-loss`` just that one).  The
+``--only-agg`` / ``--only-loss`` / ``--only-sweep`` just that one).  The
 fixtures hold the seeded inputs and what the reference's own classes
 (``VFNet``, ``ViewRendering``, ``Pose``, ``MultiCamLoss``) returned for them, at
 sizes small enough to commit.  ``tests/test_oracle_golden.py`` then pins
@@ -315,7 +315,38 @@ def make_loss_free(ref, path):
     print('wrote', path)
 
 
+SWEEP_PICK = list(range(0, 767, 37)) + [151, 152, 254, 255, 355, 356, 406, 407, 766]
+
+
+def make_syn_sweep(ref, path):
+    """The synthesis-visualisation sweep of VFNet.forward (volumetric_fusionnet.py:320-336, utils/visualize.py:9-57) run
+    by the reference on the rig of golden_fusion.npz: every view's angles, and for the views of SWEEP_PICK the
+    augmented inverse intrinsics and camera 0's raw ray samples (reduce_dim replaced by the identity)."""
+    import importlib
+    cfg = fusion_cfg()
+    cfg['eval'] = dict(cfg.get('eval', {}), syn_visualize=True)
+    inputs, extras = make_rig(cfg, seed=4242, with_images=False)
+    C = cfg['model']['fusion_feat_in_dim']
+    lvl = cfg['model']['fusion_level'] + 1
+    torch.manual_seed(7)
+    net = ref.VFNet(cfg, C, 16, model='depth')
+    net.reduce_dim = torch.nn.Identity()
+    assert net.syn_visualize
+    with torch.no_grad():
+        fd = net(inputs, extras['feats_agg'])
+    params = importlib.import_module('utils.visualize').aug_depth_params(inputs[('K', lvl)])
+    assert len(params) == len(fd['syn_feat']) == 767
+    out = {'angles': np.array([[float(a) for a in p[1:]] for p in params], dtype=np.float64),
+           'pick': np.array(SWEEP_PICK), 'inv_K_aug': np.stack([_np(params[i][0]) for i in SWEEP_PICK]),
+           'syn_feat': np.stack([_np(fd['syn_feat'][i]) for i in SWEEP_PICK])}
+    np.savez_compressed(path, **out)
+    print('wrote', path, {k: v.shape for k, v in out.items()})
+
+
 if __name__ == '__main__':
+    if '--only-sweep' in sys.argv:
+        make_syn_sweep(ref_import.load(), os.path.join(HERE, 'golden_syn_sweep.npz'))
+        sys.exit(0)
     if '--only-loss' in sys.argv:
         make_loss_free(ref_import.load(), os.path.join(HERE, 'golden_loss_free.npz'))
         sys.exit(0)
@@ -330,3 +361,4 @@ if __name__ == '__main__':
     make_depth_syn(ref, os.path.join(HERE, 'golden_depth_syn.npz'))
     make_feat_agg(os.path.join(HERE, 'golden_feat_agg.npz'))
     make_loss_free(ref, os.path.join(HERE, 'golden_loss_free.npz'))
+    make_syn_sweep(ref, os.path.join(HERE, 'golden_syn_sweep.npz'))

@@ -401,3 +401,24 @@ def test_pose_bev_handoff_matches_reference_reshape(dataset, C):
     assert H.rel_err(out, ref) < TOL
     for a, b in zip(g1, g2):
         assert H.rel_err(a, b) < TOL
+
+
+def test_syn_visualize_sweep_matches_reference():
+    """VFNet.forward with eval.syn_visualize (volumetric_fusionnet.py:320-336): 767 virtual views of camera 0; the
+    picked ones equal reduce_dim applied to the ray samples the reference itself produced for those views
+    (tests/golden/golden_syn_sweep.npz), the base view equals 'proj_feat' of camera 0."""
+    dev = _dev()
+    g, s = H.load_npz('golden_fusion.npz'), H.load_npz('golden_syn_sweep.npz')
+    cfg = H.fusion_cfg()
+    cfg['eval'] = dict(cfg.get('eval', {}), syn_visualize=True)
+    net = _net(cfg, 8, 16, 'depth', _mlp(g), dev)
+    assert net.syn_visualize
+    inputs = {k: v.to(dev) for k, v in H.fusion_inputs(g, cfg).items()}
+    with torch.no_grad():
+        fd = net(inputs, g['feats_agg'].to(dev))
+        syn = fd['syn_feat']
+        assert len(syn) == 767 and syn[0].shape == (2, 16, 8, 12)
+        assert H.rel_err(syn[0].cpu(), fd['proj_feat'].view(2, 6, 16, 8, 12)[:, 0].cpu()) < 1e-6
+        for k, i in enumerate(s['pick'].tolist()):
+            ref = net.reduce_dim(s['syn_feat'][k].to(dev))
+            assert H.rel_err(syn[i].cpu(), ref.cpu()) < TOL, i

@@ -140,3 +140,21 @@ def test_loss_free_functions_bit_exact():
     ml = orc.masked_loss(ll, g['mask'])
     assert torch.equal(ml.detach(), g['masked'])
     assert torch.equal(torch.autograd.grad(ml, ll)[0], g['d_loss'])
+
+
+def test_syn_sweep_params_and_samples_bit_exact():
+    """The synthesis-visualisation sweep (volumetric_fusionnet.py:320-336): vfdepth_b200.vfnet.aug_depth_params against
+    the reference's utils/visualize.py:9-57 (all 767 angle triples, the augmented inverse intrinsics of the picked
+    views), and the oracle's ray sampling of those views against the reference's 'syn_feat' -- bit for bit."""
+    from vfdepth_b200.vfnet import VFNet, aug_depth_params
+    g, s = H.load_npz('golden_fusion.npz'), H.load_npz('golden_syn_sweep.npz')
+    cfg = H.fusion_cfg()
+    params = aug_depth_params(g['K'])
+    assert len(params) == 767
+    assert torch.equal(torch.tensor([[float(a) for a in p[1:]] for p in params], dtype=torch.float64), s['angles'])
+    for k, i in enumerate(s['pick'].tolist()):
+        inv_K_aug, *ang = params[i]
+        assert torch.equal(inv_K_aug, s['inv_K_aug'][k])
+        E = VFNet.rotate_extrinsics(g['extrinsics'], ang)
+        cam0 = orc.project_voxel_into_image(cfg, g['voxel_feat'], inv_K_aug, E)[0]
+        assert torch.equal(cam0, s['syn_feat'][k]), i

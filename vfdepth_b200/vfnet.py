@@ -40,6 +40,35 @@ def _conv3x3_layers(cin, cout, stride):
             nn.Identity(), _act()]
 
 
+_DEG = 0.0174533      # the reference's rounded pi / 180 (utils/visualize.py:6)
+
+
+def _sweep(top, step=2):
+    """0 -> top -> -top -> 0 in steps of ``step`` (both turning points visited twice, as the reference's lists do)."""
+    return list(range(0, top + 1, step)) + list(range(top, -top - 1, -step)) + list(range(-top, 1, step))
+
+
+def aug_depth_params(K, n_steps=75):
+    """Virtual-view sweep of the synthesis visualisation (reference: utils/visualize.py:9-57): a list of
+    ``[inv_K_aug [B,cams,4,4], ang_x, ang_y, ang_z]`` -- roll +-10 deg, pitch +-5 deg, two focal-length ramps (camera
+    1 / camera 0 focal ratio, divided by 1.5 and back) and a full yaw turn at the last ramp's intrinsics."""
+    inv_K = torch.inverse(K)
+    params = [[inv_K, _DEG * (a / n_steps * 10.), 0.0, 0.0] for a in _sweep(n_steps)]
+    params += [[inv_K, 0.0, _DEG * (a / 10.), 0.0] for a in _sweep(50)]
+    ratio = K[:, 1, 0, 0] / K[:, 0, 0, 0]
+    ratio_aug = ratio / 1.5
+    ramps = [(i / 100. * ratio_aug + (1 - i / 100.)) for i in range(101)]
+    ramps += [(i / 50. * ratio + (1 - i / 50.) * ratio_aug) for i in range(51)]
+    for scale in ramps:
+        K_aug = K.clone()
+        K_aug[:, :, 0, 0] *= scale[:, None]
+        K_aug[:, :, 1, 1] *= scale[:, None]
+        params.append([torch.inverse(K_aug), 0.0, 0.0, 0.0])
+    inv_last = torch.inverse(K_aug)
+    params += [[inv_last, 0.0, 0.0, _DEG * 360 * (i / 360.)] for i in range(360)]
+    return params
+
+
 class VFNet(nn.Module):
     """Surround-view volumetric fusion (reference: VFNet, volumetric_fusionnet.py:11)."""
 
@@ -176,6 +205,13 @@ class VFNet(nn.Module):
             tform[:, :, :3, :3] = axis_angle_to_matrix(angle)
             return tform.to(device=ext.device, dtype=ext.dtype) @ ext
 
+    @staticmethod
+    def rotate_extrinsics(ext, angles):
+        """(rotation by the axis-angle vector ``angles``) @ extrinsics for every camera (:321-327)."""
+        tform = torch.eye(4)
+        tform[:3, :3] = axis_angle_to_matrix(torch.tensor([list(angles)], dtype=torch.float32))[0]
+        return tform.to(device=ext.device, dtype=ext.dtype) @ ext
+
     def forward(self, inputs, feats_agg):
         """Reference :289-343."""
         lvl = self.fusion_level + 1
@@ -194,7 +230,11 @@ class VFNet(nn.Module):
                 feats = self.project_voxel_into_image(voxel_feat, inv_K, inputs['extrinsics_aug'])
                 fusion_dict['proj_feat_aug'] = torch.stack(feats, 1).flatten(0, 1)
             if getattr(self, 'syn_visualize', False):
-                raise NotImplementedError('synthesis visualisation sweep (:320-336) is outside the hot path')
+                # synthesis sweep (:320-336): camera 0's projected features for every virtual view of the sweep
+                with torch.no_grad():
+                    fusion_dict['syn_feat'] = [
+                        self.project_voxel_into_image(voxel_feat, inv_K_aug, self.rotate_extrinsics(extrinsics, ang))[0]
+                        for inv_K_aug, *ang in aug_depth_params(K)]
             return fusion_dict
         raise ValueError(self.model)
 
