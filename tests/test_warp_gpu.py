@@ -309,6 +309,13 @@ def test_dropin_modules_per_camera():
         torch.manual_seed(1000 + cam)           # the module draws the same tensor from the global CPU stream
         cam_loss, ld = lossm(inputs, outputs, cam)
         assert set(ld) >= {'reproj_loss', 'spatio_loss', 'spatio_tempo_loss', 'smooth', 'depth/mean'}
+        # SingleCamLoss (single_cam_loss.py:66-95): the same reprojection and smoothness terms, nothing else
+        torch.manual_seed(1000 + cam)
+        single, ld1 = view.SingleCamLoss(cfg, dev)(inputs, outputs, cam)
+        assert 'spatio_loss' not in ld1 and ld1['reproj_loss'] == ld['reproj_loss'] and ld1['smooth'] == ld['smooth']
+        want = ld['reproj_loss'] + cfg['loss']['disparity_smoothness'] * ld['smooth']
+        assert abs(float(single) - want) < 1e-6 * abs(want)
+        assert float(single) < float(cam_loss)
         total = total + cam_loss
     total = total / 6
     g_mod = torch.autograd.grad(total, depths + [Ts[-1], Ts[1]])

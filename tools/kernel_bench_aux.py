@@ -33,6 +33,34 @@ def timed(fn, iters, warmup=3):
     return e0.elapsed_time(e1) / iters
 
 
+def bench_loss_free(B, cfg, iters, report, dev):
+    """stand-alone loss_util free functions (csrc/loss_free.cu, photometric.cu) on [B*6,.,H,W] maps."""
+    from vfdepth_b200 import loss_util
+    H, W = cfg['training']['height'], cfg['training']['width']
+    n = B * 6
+    gen = torch.Generator().manual_seed(2)
+    rgb = torch.rand((n, 3, H, W), generator=gen).to(dev)
+    pred = torch.rand((n, 3, H, W), generator=gen).to(dev).requires_grad_(True)
+    disp = torch.rand((n, 1, H, W), generator=gen).to(dev).requires_grad_(True)
+    rp = torch.rand((n, 1, H, W), generator=gen).to(dev)
+    idl = torch.rand((n, 2, H, W), generator=gen).to(dev)
+    px = n * H * W * 4
+    one = torch.ones((), device=dev)
+    with torch.no_grad():
+        report('auto_masks', timed(lambda: loss_util.compute_auto_masks(rp, idl), iters), 4 * px)
+        mask = loss_util.compute_auto_masks(rp, idl)
+        report('masked_loss_fwd', timed(lambda: loss_util.compute_masked_loss(disp, mask), iters), 2 * px)
+        report('edg_smooth_fwd', timed(lambda: loss_util.compute_edg_smooth_loss(rgb, disp), iters), 4 * px)
+        report('photometric_fwd', timed(lambda: loss_util.compute_photometric_loss(pred, rgb), iters), 7 * px)
+    ml = loss_util.compute_masked_loss(disp, mask)
+    report('masked_loss_bwd', timed(lambda: torch.autograd.grad(ml, disp, one, retain_graph=True), iters), 2 * px)
+    sm = loss_util.compute_edg_smooth_loss(rgb, disp)
+    report('edg_smooth_bwd', timed(lambda: torch.autograd.grad(sm, disp, one, retain_graph=True), iters), 5 * px)
+    ph = loss_util.compute_photometric_loss(pred, rgb)
+    upp = torch.ones_like(ph)
+    report('photometric_bwd', timed(lambda: torch.autograd.grad(ph, pred, upp, retain_graph=True), iters), 10 * px)
+
+
 def bench_aggregation(B, iters, report, dev):
     """feature aggregation (fusion_depthnet.py:57-66) at the DDAD sizes: ResNet levels 128@48x80, 256@24x40, 512@12x20
     -> 256 channels.  Ours (per-level GEMMs + vfd_feat_agg) against the reference's formulation in torch on the same
@@ -122,6 +150,7 @@ def main():
         report('depth_syn_fwd', timed(lambda: view.depth_syn_loss(cfg, inp, dep, aug, disp), args.iters), 4 * px)
     report('depth_syn_bwd', timed(lambda: torch.autograd.grad(con, [dep, aug], upc, retain_graph=True), args.iters), 5 * px)
     print('depth_con_loss per camera:', [round(float(c), 4) for c in con])
+    bench_loss_free(B, cfg, args.iters, report, dev)
     bench_aggregation(B, args.iters, report, dev)
     print('(depth_syn_fwd includes the colour-less smoothness of disp_aug and two batched 4x4 inversions in torch)')
 

@@ -368,12 +368,14 @@ def to_depth(cfg, disp, K):
                           float(t['focal_length_scale']), int(t['height']), int(t['width']))
 
 
-def combine_losses(cfg, num, den, smooth):
-    """per-camera total of multi_cam_loss.py:118-137 from the kernel's sums. num/den [n,3], smooth [n] -> [n]"""
+def combine_losses(cfg, num, den, smooth, spatial=True):
+    """per-camera total of multi_cam_loss.py:118-137 (``spatial=False``: single_cam_loss.py:79-80) from the kernel's
+    sums. num/den [n,3], smooth [n] -> [n]"""
     L = cfg['loss']
     terms = num / (den + 1e-8)
     cam = terms[:, 0] + L['disparity_smoothness'] * smooth
-    cam = cam + (L['spatio_coeff'] * terms[:, 1] + L['spatio_tempo_coeff'] * terms[:, 2])
+    if spatial:
+        cam = cam + (L['spatio_coeff'] * terms[:, 1] + L['spatio_tempo_coeff'] * terms[:, 2])
     return cam / len(cfg['training']['scales']), terms
 
 
@@ -502,6 +504,8 @@ class MultiCamLoss(torch.nn.Module):
         if self.pose_model == 'fsm':
             raise NotImplementedError('FSM pose-consistency loss (multi_cam_loss.py:61-92) is outside the hot path')
 
+    spatial_terms = True
+
     def forward(self, inputs, outputs, cam):
         tv = outputs[('cam', cam)]
         c = tv[_CTX]
@@ -513,10 +517,11 @@ class MultiCamLoss(torch.nn.Module):
         tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
         tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
         sm = smooth_loss(inputs[('color', 0, 0)][:, cam:cam + 1], tv[('disp', 0)])[0]
-        cam_loss, terms = combine_losses(self.cfg, num, den, sm.reshape(1))
+        cam_loss, terms = combine_losses(self.cfg, num, den, sm.reshape(1), spatial=self.spatial_terms)
         t = terms[0].detach().cpu()
-        loss_dict = {'reproj_loss': float(t[0]), 'spatio_loss': float(t[1]), 'spatio_tempo_loss': float(t[2]),
-                     'smooth': float(sm.detach())}
+        loss_dict = {'reproj_loss': float(t[0]), 'smooth': float(sm.detach())}
+        if self.spatial_terms:
+            loss_dict.update(spatio_loss=float(t[1]), spatio_tempo_loss=float(t[2]))
         depth_log = tv[('depth', 0)].detach()           # base_loss.py:29-33
         loss_dict['depth/mean'], loss_dict['depth/max'], loss_dict['depth/min'] = \
             depth_log.mean(), depth_log.max(), depth_log.min()
@@ -526,6 +531,14 @@ class MultiCamLoss(torch.nn.Module):
                 for i, n in enumerate(('pose/tx', 'pose/ty', 'pose/tz')):
                     loss_dict[n] = pose_t[:, i, 3].abs().mean()
         return cam_loss[0], loss_dict
+
+
+class SingleCamLoss(MultiCamLoss):
+    """Drop-in for models/losses/single_cam_loss.py:11 (``SingleCamLoss(cfg, rank)``, the loss of the configurations
+    with ``training.spatio == False``, models/vfdepth.py:50-53): reprojection + disparity_smoothness * smoothness
+    (:66-95).  Same kernels as MultiCamLoss -- the temporal warps, the auto-mask and the masked sums do not depend on
+    the spatial warps, whose two terms are simply left out of the total and of ``loss_dict``."""
+    spatial_terms = False
 
 
 class DepthSynLoss(MultiCamLoss):
