@@ -297,7 +297,11 @@ def run_ours(args):
         raise SystemExit('bench.py needs a CUDA device: vfdepth_b200 has no CPU path')
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    numa = 'unbound (single process)'
     if world > 1:
+        # before any pinned allocation: first-touch places the staging buffers on the GPU's own NUMA node
+        from vfdepth_b200 import shard
+        numa = shard.bind_to_gpu_numa(local)
         dist.init_process_group('nccl', device_id=dev)
     torch.backends.cuda.matmul.allow_tf32 = False      # the reference's setting (train.py:25)
     from vfdepth_b200 import _lib
@@ -444,7 +448,7 @@ def run_ours(args):
                 'config': {'workload': WORKLOAD % (WARP_PART if warp else '', args.batch),
                            'rigs_per_step_per_gpu': args.batch, 'l2': 'inputs and outputs larger than L2 '
                            '(189 MB feature maps, 1.7 GB compact gather rows, 2.4 GB ray samples per step)',
-                           'sharding': 'whole rigs per rank, no data-path collective', 'cuda_graph': graphed,
+                           'sharding': 'whole rigs per rank, no data-path collective', 'host_affinity': numa, 'cuda_graph': graphed,
                            'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms},
                 'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof, 'kernels': kernels}
         if world == 1 and not args.no_cpu_baseline:
