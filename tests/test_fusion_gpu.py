@@ -418,7 +418,8 @@ def test_syn_visualize_sweep_matches_reference():
         fd = net(inputs, g['feats_agg'].to(dev))
         syn = fd['syn_feat']
         assert len(syn) == 767 and syn[0].shape == (2, 16, 8, 12)
-        assert H.rel_err(syn[0].cpu(), fd['proj_feat'].view(2, 6, 16, 8, 12)[:, 0].cpu()) < 1e-6
+        # view 0 is the unrotated camera with torch.inverse(K) in place of the data loader's pinv (ulps apart)
+        assert H.rel_err(syn[0].cpu(), fd['proj_feat'].view(2, 6, 16, 8, 12)[:, 0].cpu()) < TOL
         for k, i in enumerate(s['pick'].tolist()):
             ref = net.reduce_dim(s['syn_feat'][k].to(dev))
             assert H.rel_err(syn[i].cpu(), ref.cpu()) < TOL, i
