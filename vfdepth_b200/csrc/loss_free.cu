@@ -38,18 +38,19 @@ __device__ __forceinline__ void block_add2(double a, double b, double* out) {
 }
 
 // torch.argmin semantics: first minimum wins, a NaN is smaller than everything (first NaN wins)
-__global__ void __launch_bounds__(kLfThreads) auto_masks_kernel(int B, int F1, int F2, int HW, const float* reproj,
+__global__ void __launch_bounds__(kLfThreads) auto_masks_kernel(int F1, int F2, int HW, const float* reproj,
                                                                 const float* identity, float* mask) {
-    const size_t n = (size_t)B * HW;
-    for (size_t i = (size_t)blockIdx.x * kLfThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kLfThreads) {
-        const size_t b = i / HW, p = i % HW;
-        float best = __ldg(reproj + b * F1 * HW + p);
+    const int b = blockIdx.y;
+    const float* rp = reproj + (size_t)b * F1 * HW;
+    const float* id = identity + (size_t)b * F2 * HW;
+    for (int p = blockIdx.x * kLfThreads + threadIdx.x; p < HW; p += gridDim.x * kLfThreads) {
+        float best = __ldg(rp + p);
         int arg = 0;
         for (int f = 1; f < F1 + F2; ++f) {
-            const float v = f < F1 ? __ldg(reproj + (b * F1 + f) * HW + p) : __ldg(identity + (b * F2 + (f - F1)) * HW + p);
+            const float v = f < F1 ? __ldg(rp + (size_t)f * HW + p) : __ldg(id + (size_t)(f - F1) * HW + p);
             if (!(best != best) && (v < best || v != v)) { best = v; arg = f; }
         }
-        mask[i] = arg == 0 ? 1.f : 0.f;
+        mask[(size_t)b * HW + p] = arg == 0 ? 1.f : 0.f;
     }
 }
 
@@ -87,19 +88,19 @@ __device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f 
 __global__ void __launch_bounds__(kLfThreads) edg_smooth_kernel(int B, int C, int H, int W, const float* rgb,
                                                                 const float* disp, double* sums, const float* d_out,
                                                                 float* d_disp) {
-    const size_t HW = (size_t)H * W, n = (size_t)B * HW;
+    const int HWi = H * W, b = blockIdx.y;
+    const size_t HW = (size_t)HWi;
     float gx = 0.f, gy = 0.f;
     if (d_disp) {
         const float g = __ldg(d_out);
         gx = g / (float)((size_t)B * H * (W - 1));
         gy = g / (float)((size_t)B * (H - 1) * W);
     }
+    const float* im = rgb + (size_t)b * C * HW;
+    const float* dp = disp + (size_t)b * HW;
     double sx = 0.0, sy = 0.0;
-    for (size_t i = (size_t)blockIdx.x * kLfThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kLfThreads) {
-        const size_t b = i / HW, p = i % HW;
-        const int x = (int)(p % W), y = (int)(p / W);
-        const float* im = rgb + b * C * HW;
-        const float* dp = disp + b * HW;
+    for (int p = blockIdx.x * kLfThreads + threadIdx.x; p < HWi; p += gridDim.x * kLfThreads) {
+        const int y = p / W, x = p - y * W;
         const float d0 = __ldg(dp + p);
         float acc = 0.f;
         if (x + 1 < W) {
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(kLfThreads) edg_smooth_kernel(int B, int C, in
         if (d_disp) {
             if (x > 0) acc -= gx * sgn(__fsub_rn(__ldg(dp + p - 1), d0)) * edge_weight(im, C, HW, p - 1, p);
             if (y > 0) acc -= gy * sgn(__fsub_rn(__ldg(dp + p - W), d0)) * edge_weight(im, C, HW, p - W, p);
-            d_disp[i] = acc;
+            d_disp[(size_t)b * HW + p] = acc;
         }
     }
     if (!d_disp) block_add2(sx, sy, sums);
@@ -126,16 +127,23 @@ static int lf_blocks(size_t n) {
     return (int)(need < (size_t)kLfBlocks ? (need ? need : 1) : kLfBlocks);
 }
 
+// one image per blockIdx.y; enough CTAs in x to fill the machine (4 per SM over the whole grid) without exceeding the image
+static dim3 lf_grid(int B, int HW) {
+    const int need = (HW + kLfThreads - 1) / kLfThreads;
+    int per = (kLfBlocks + B - 1) / B;
+    if (per > need) per = need;
+    return dim3(per < 1 ? 1 : per, B);
+}
+
 }  // namespace vfd
 
 using namespace vfd;
 
 extern "C" int vfd_auto_masks(int B, int F1, int F2, int HW, const float* reproj, const float* identity, float* mask,
                               void* stream) {
-    if (B < 1 || F1 < 1 || F2 < 0 || HW < 1) return VFD_ERR_DESC;
+    if (B < 1 || B > 65535 || F1 < 1 || F2 < 0 || HW < 1 || HW >= (1 << 30)) return VFD_ERR_DESC;
     if (!reproj || !mask || (F2 > 0 && !identity)) return VFD_ERR_NULL;
-    auto_masks_kernel<<<lf_blocks((size_t)B * HW), kLfThreads, 0, (cudaStream_t)stream>>>(B, F1, F2, HW, reproj, identity,
-                                                                                       mask);
+    auto_masks_kernel<<<lf_grid(B, HW), kLfThreads, 0, (cudaStream_t)stream>>>(F1, F2, HW, reproj, identity, mask);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
@@ -161,21 +169,21 @@ extern "C" int vfd_masked_loss_bwd(size_t n, const float* mask, const double* su
 
 extern "C" int vfd_edg_smooth_loss_fwd(int B, int C, int H, int W, const float* rgb, const float* disp, double* sums,
                                        void* stream) {
-    if (B < 1 || C < 1 || H < 2 || W < 2) return VFD_ERR_DESC;
+    if (B < 1 || B > 65535 || C < 1 || H < 2 || W < 2 || (long)H * W >= (1L << 30)) return VFD_ERR_DESC;
     if (!rgb || !disp || !sums) return VFD_ERR_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(sums, 0, 2 * sizeof(double), st) != cudaSuccess) return VFD_ERR_CUDA;
-    edg_smooth_kernel<<<lf_blocks((size_t)B * H * W), kLfThreads, 0, st>>>(B, C, H, W, rgb, disp, sums, nullptr, nullptr);
+    edg_smooth_kernel<<<lf_grid(B, H * W), kLfThreads, 0, st>>>(B, C, H, W, rgb, disp, sums, nullptr, nullptr);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
 
 extern "C" int vfd_edg_smooth_loss_bwd(int B, int C, int H, int W, const float* rgb, const float* disp,
                                        const float* d_out, float* d_disp, void* stream) {
-    if (B < 1 || C < 1 || H < 2 || W < 2) return VFD_ERR_DESC;
+    if (B < 1 || B > 65535 || C < 1 || H < 2 || W < 2 || (long)H * W >= (1L << 30)) return VFD_ERR_DESC;
     if (!rgb || !disp || !d_out || !d_disp) return VFD_ERR_NULL;
-    edg_smooth_kernel<<<lf_blocks((size_t)B * H * W), kLfThreads, 0, (cudaStream_t)stream>>>(B, C, H, W, rgb, disp, nullptr,
-                                                                                          d_out, d_disp);
+    edg_smooth_kernel<<<lf_grid(B, H * W), kLfThreads, 0, (cudaStream_t)stream>>>(B, C, H, W, rgb, disp, nullptr, d_out,
+                                                                               d_disp);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
