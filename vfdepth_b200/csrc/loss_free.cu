@@ -9,7 +9,7 @@
 
 namespace vfd {
 
-constexpr int kLfThreads = 256, kLfBlocks = 148 * 8;
+constexpr int kLfThreads = 256, kLfBlocks = 148 * 4;
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -127,7 +127,7 @@ static int lf_blocks(size_t n) {
     return (int)(need < (size_t)kLfBlocks ? (need ? need : 1) : kLfBlocks);
 }
 
-// one image per blockIdx.y; enough CTAs in x to fill the machine (8 per SM over the whole grid) without exceeding the image
+// one image per blockIdx.y; enough CTAs in x to fill the machine (4 per SM over the whole grid) without exceeding the image
 static dim3 lf_grid(int B, int HW) {
     const int need = (HW + kLfThreads - 1) / kLfThreads;
     int per = (kLfBlocks + B - 1) / B;
