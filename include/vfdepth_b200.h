@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VFD_VERSION 100 /* major*100 + minor */
+#define VFD_VERSION 200 /* major*100 + minor */
 #define VFD_MAX_CAMS 8
 
 typedef enum vfd_status {
@@ -95,9 +95,10 @@ int vfd_voxel_gather_depth_bwd(const vfd_fusion_desc* d, const float* mask_small
  *   idx_ov  [>= B*N] i64  same for x_ov (first totals[1] entries)
  *   totals  [2] i32       device: number of count-1 and count-2 voxels; the caller reads it back to size the MLP GEMMs
  *   table   (optional)    vfd_voxel_table_bytes(d) bytes, 16-byte aligned: for every listed voxel the bilinear corner
- *                         offsets / weights, camera and relative depth of the one or two cameras that see it, so that
+ *                         pixel indices / weights, camera and relative depth of the one or two cameras that see it, so that
  *                         vfd_voxel_fuse_fwd / _bwd do not project again; NULL = not written
- *   ws                    scratch of vfd_voxel_classify_workspace_bytes(d) bytes, 8-byte aligned */
+ *   ws                    scratch of vfd_voxel_classify_workspace_bytes(d) bytes, 8-byte aligned
+ * slot / idx_no / idx_ov / totals may be NULL together: only count (+ table) is produced, in one launch. */
 size_t vfd_voxel_classify_workspace_bytes(const vfd_fusion_desc* d);
 size_t vfd_voxel_table_bytes(const vfd_fusion_desc* d);
 int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_small, const float* K, const float* Einv,
@@ -114,29 +115,34 @@ int vfd_voxel_gather_depth_compact_bwd(const vfd_fusion_desc* d, const float* ma
                                        const float* d_x_ov, float* d_feats, void* stream);
 
 /* Fused gather + both 1x1 MLPs: VFNet.backproject_into_voxel, model='depth', :116-159 INCLUDING
- * preprocess_non_overlap (:197-207) and preprocess_overlap (:209-230).  The GEMM rows never reach HBM.
- *   idx_no/idx_ov/totals/table  from vfd_voxel_classify (totals stay on the device: no host round trip)
+ * preprocess_non_overlap (:197-207) and preprocess_overlap (:209-230), in "project, then gather" form: the MLPs are
+ * linear up to their LeakyReLU and so is the bilinear gather, so every feature PIXEL is multiplied once with the weight
+ * blocks its camera can need (dense tcgen05 + TMA product, 3xTF32 = fp32-level accuracy; B*cams*h*w rows instead of one
+ * row per (voxel, camera)) and the voxel kernel gathers Cv-float rows of that product, adds the relative-depth column
+ * and the bias and applies LeakyReLU(0.1).  Neither the GEMM rows nor the gathered rows reach HBM.
+ *   count, table                    from vfd_voxel_classify (table is required)
  *   w_no [Cv][C+1], b_no [Cv]       conv_non_overlap.0.{weight,bias}   (Conv1d weight with the k=1 axis squeezed)
  *   w_ov [Cv][2(C+1)], b_ov [Cv]    conv_overlap.0.{weight,bias}
- *   vol  [B,N,Cv]                   channel-last voxel volume (voxel_feat of :158 transposed); zero-filled here, rows
- *                                   of count-1 / count-2 voxels = LeakyReLU_0.1(x W^T + b)
- * Cv even, <= 64.  The products run as error-compensated 3xTF32 on the tensor cores (fp32-level accuracy). */
-int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small, const float* K,
-                       const float* Einv, const int64_t* idx_no, const int64_t* idx_ov, const int32_t* totals,
-                       const void* table, const float* w_no, const float* b_no, const float* w_ov, const float* b_ov,
-                       float* vol, void* stream);
+ *   vol  [B,N,Cv]                   channel-last voxel volume (voxel_feat of :158 transposed); every row is written:
+ *                                   LeakyReLU_0.1(x W^T + b) for count-1 / count-2 voxels, zeros elsewhere
+ *   ws                              scratch of vfd_voxel_fuse_fwd_workspace_bytes(d) bytes, 256-byte aligned
+ * C multiple of 4, <= 256; Cv multiple of 4, <= 64.  Deterministic. */
+size_t vfd_voxel_fuse_fwd_workspace_bytes(const vfd_fusion_desc* d);
+int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, const uint8_t* count, const void* table,
+                       const float* w_no, const float* b_no, const float* w_ov, const float* b_ov, float* vol, void* ws,
+                       size_t ws_bytes, void* stream);
 
 /* Backward of vfd_voxel_fuse_fwd w.r.t. the feature maps and the four MLP parameters.
  *   vol    [B,N,Cv]  the forward output (the sign of the pre-activation is read from it)
  *   d_vol  [B,N,Cv]  upstream gradient
- *   d_feats [B,cams,h,w,C]  zero-filled here, then accumulated (L2 atomics)
- *   d_w_no [Cv][C+1], d_b_no [Cv], d_w_ov [Cv][2(C+1)], d_b_ov [Cv]  written; per-CTA partial sums go through `ws`
- *                    (vfd_voxel_fuse_bwd_workspace_bytes) and are reduced in a fixed order (deterministic) */
+ *   d_feats [B,cams,h,w,C]  written (every element once, by the dense product dP . Wcat)
+ *   d_w_no [Cv][C+1], d_b_no [Cv], d_w_ov [Cv][2(C+1)], d_b_ov [Cv]  written
+ *   ws     scratch of vfd_voxel_fuse_bwd_workspace_bytes(d) bytes, 256-byte aligned
+ * The per-voxel gradients are scattered into the pixel-domain buffer dP with L2 atomics (summation order varies
+ * between runs at the 1e-7 level); everything after that is reduced in a fixed order. */
 size_t vfd_voxel_fuse_bwd_workspace_bytes(const vfd_fusion_desc* d);
-int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, const float* mask_small, const float* K,
-                       const float* Einv, const int64_t* idx_no, const int64_t* idx_ov, const int32_t* totals,
-                       const void* table, const float* w_no, const float* w_ov, const float* vol, const float* d_vol,
-                       float* d_feats,
+int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, const uint8_t* count, const void* table,
+                       const float* w_no, const float* w_ov, const float* vol, const float* d_vol, float* d_feats,
                        float* d_w_no, float* d_b_no, float* d_w_ov, float* d_b_ov, void* ws, size_t ws_bytes,
                        void* stream);
 

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 12
     for n in names:
         assert hasattr(lib, n), n
-    assert lib.vfd_version() == 100
+    assert lib.vfd_version() == 200
 
 
 def test_header_is_plain_c_and_structs_match_ctypes():
@@ -74,10 +74,17 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.vfd_voxel_gather_depth_compact_fwd(null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_gather_depth_compact_bwd(null, null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_classify_workspace_bytes(null) == 0
-    assert lib.vfd_voxel_fuse_fwd(*([null] * 15)) == -1
-    assert lib.vfd_voxel_fuse_bwd(*([null] * 19), ctypes.c_size_t(0), null) == -1
+    assert lib.vfd_voxel_fuse_fwd(*([null] * 10), ctypes.c_size_t(0), null) == -1
+    assert lib.vfd_voxel_fuse_bwd(*([null] * 14), ctypes.c_size_t(0), null) == -1
     assert lib.vfd_voxel_table_bytes(null) == 0
     assert lib.vfd_voxel_fuse_bwd_workspace_bytes(null) == 0
+    assert lib.vfd_voxel_fuse_fwd_workspace_bytes(null) == 0
+    fd = _lib.FusionDesc()
+    fd.B, fd.num_cams, fd.C, fd.h, fd.w, fd.X, fd.Y, fd.Z, fd.D, fd.Cv = 1, 6, 256, 48, 80, 100, 100, 20, 50, 64
+    # P [6*3840][128] + three [2][128][256] weight planes, each block 256-byte aligned
+    assert lib.vfd_voxel_fuse_fwd_workspace_bytes(ctypes.byref(fd)) == 6 * 3840 * 128 * 4 + 3 * 2 * 128 * 256 * 4
+    fd.Cv = 66                                                                             # Cv % 4
+    assert lib.vfd_voxel_fuse_fwd(ctypes.byref(fd), *([null] * 9), ctypes.c_size_t(0), null) == -6
     assert lib.vfd_smooth_loss_fwd(1, 6, 8, 8, null, null, null, null, null) == -1      # colour may be NULL, disp not
     assert lib.vfd_smooth_loss_fwd(1, 6, 1, 8, null, null, null, null, null) == -2
     assert lib.vfd_smooth_loss_bwd(1, 6, 8, 8, null, null, null, null, null, null, null) == -1

@@ -264,7 +264,8 @@ def test_compact_rows_equal_dense_rows(B):
 def test_fused_mlp_matches_fp32_gemm_path(dataset, B, C, Cv):
     """SURVEY.md 8f-1 at BASELINE size: the fused gather + MLP kernels (3xTF32 tensor-core products) against the dense
     gather rows + fp32 cuBLAS GEMMs -- volume, feature gradient and the four parameter gradients within 1e-4 of each
-    tensor's scale; parameter gradients bit-identical between two runs.
+    tensor's scale; the forward bit-identical between two runs, the gradients to 1e-5 (the pixel-domain gradient buffer
+    is accumulated with L2 atomics).
 
     LeakyReLU has a kink: where a pre-activation is ~0 two fp32 implementations may take different slopes, which
     changes that element's gradient by a factor 10 however small the value.  As for the loss decisions
@@ -293,9 +294,9 @@ def test_fused_mlp_matches_fp32_gemm_path(dataset, B, C, Cv):
         vox = net.backproject_into_voxel(f, *args)
         grads = torch.autograd.grad((vox * up).sum(), [f] + params)
         res[name] = [vox.detach()] + [x.detach() for x in grads]
-    assert torch.equal(res['fused'][0], res['fused2'][0])
-    for a, b in zip(res['fused'][2:], res['fused2'][2:]):
-        assert torch.equal(a, b)
+    assert torch.equal(res['fused'][0], res['fused2'][0])        # the forward is deterministic
+    for a, b in zip(res['fused'][1:], res['fused2'][1:]):        # the backward scatters with L2 atomics: order varies
+        assert H.rel_err(a, b) < 1e-5
     cnt = net.last_count
     vol = res['fused'][0].permute(0, 2, 1)                      # [B,N,Cv]
     assert float(vol[(cnt != 1) & (cnt != 2)].abs().max()) == 0.0
@@ -423,3 +424,118 @@ def test_syn_visualize_sweep_matches_reference():
         for k, i in enumerate(s['pick'].tolist()):
             ref = net.reduce_dim(s['syn_feat'][k].to(dev))
             assert H.rel_err(syn[i].cpu(), ref.cpu()) < TOL, i
+
+
+def _report(name, rec):
+    """achieved errors go to gpurun_out/ (copied into profiles/ with the round's evidence) and to the test log"""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    os.makedirs(os.path.join(root, 'gpurun_out'), exist_ok=True)
+    with open(os.path.join(root, 'gpurun_out', 'parity_report.jsonl'), 'a') as f:
+        f.write(json.dumps(dict(test=name, **rec)) + '\n')
+    print(name, rec)
+
+
+@pytest.mark.parametrize('dataset,seed', [('ddad', 201), ('nuscenes', 202)])
+def test_baseline_size_oracle_parity(dataset, seed):
+    """The benchmarked configuration's own kernels (C=256, Cv=64, full 100x100x20 grid, 50 depth bins, B=1: the tcgen05 +
+    TMA projection, voxel_fuse_gather / _scatter, dense_dw, ray_sample_*_vec<64>) against the oracle =
+    /root/reference/network/volumetric_fusionnet.py:116-164, 197-230, 232-262 on the CPU: sampling grids, validity masks
+    and camera counts bit-exact; volume, ray samples, d_feats and the four parameter gradients within 1e-4 of each
+    tensor's scale (LeakyReLU slopes pinned to the kernel's pattern, which may differ only at pre-activations ~0)."""
+    dev = _dev()
+    C, Cv = 256, 64
+    cfg = vcfg.default_config(dataset, batch_size=1)
+    assert cfg['model']['fusion_feat_in_dim'] == C and cfg['model']['voxel_pre_dim'][-1] == Cv
+    inputs, extras = make_rig(cfg, seed=seed, with_images=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, C, 128, 'depth', None, dev)
+    with torch.no_grad():
+        net.conv_non_overlap[0].bias.normal_(0, 0.3)
+        net.conv_overlap[0].bias.normal_(0, 0.3)
+    assert net.fused_mlp
+    params = [net.conv_non_overlap[0].weight, net.conv_non_overlap[0].bias,
+              net.conv_overlap[0].weight, net.conv_overlap[0].bias]
+    to = lambda t: t.to(dev)
+    feats = to(extras['feats_agg']).requires_grad_(True)
+    vox = net.backproject_into_voxel(feats, to(inputs['mask']), to(inputs[('K', lvl)]), to(inputs['extrinsics_inv']))
+    rows, rgrid = net.ray_rows(vox, to(inputs[('inv_K', lvl)]), to(inputs['extrinsics']), want_grid=True)
+    got = _ray_to_ref(rows, cfg['model']['proj_d_bins'])
+    gen = torch.Generator().manual_seed(seed)
+    up = torch.randn(got.shape, generator=gen)
+    grads = torch.autograd.grad((got * to(up)).sum(), [feats] + params)
+
+    # oracle
+    mlp = {k: p.detach().cpu().clone().requires_grad_(True)
+           for k, p in zip(('w_no', 'b_no', 'w_ov', 'b_ov'), params)}
+    f_ref = extras['feats_agg'].clone().requires_grad_(True)
+    free = orc.backproject_into_voxel(cfg, f_ref, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'],
+                                      'depth', mlp).detach()
+    rec = {'dataset': dataset, 'voxel_feat_free': H.rel_err(vox.detach().cpu(), free)}
+    flip = (vox.detach().cpu() > 0) != (free > 0)
+    rec['slope_flips'] = int(flip.sum())
+    rec['slope_flip_max_preact'] = float(free[flip].abs().max()) if int(flip.sum()) else 0.0
+    assert rec['voxel_feat_free'] < TOL
+    assert rec['slope_flips'] <= max(1, int(1e-5 * flip.numel()))
+    assert rec['slope_flip_max_preact'] < 1e-4 * float(free.abs().max())
+    d = orc.backproject_into_voxel(cfg, f_ref, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'], 'depth',
+                                   mlp, detail=True, slopes_from=vox.detach().cpu())
+    proj_ref, grids_ref = orc.project_voxel_into_image(cfg, d['voxel_feat'], inputs[('inv_K', lvl)],
+                                                       inputs['extrinsics'], detail=True)
+    ref = torch.stack(proj_ref, 1)
+    g_ref = torch.autograd.grad((ref * up).sum(), [f_ref] + [mlp[k] for k in ('w_no', 'b_no', 'w_ov', 'b_ov')])
+
+    # bit-exact geometry: the dense gather kernel exposes the per-camera grids / masks, the classification its count
+    _, _, count, grid, valid = net.gather_rows(feats.detach(), to(inputs['mask']), to(inputs[('K', lvl)]),
+                                               to(inputs['extrinsics_inv']), detail=True)
+    assert torch.equal(grid.cpu(), torch.stack(d['grids'], 1).squeeze(3))
+    assert torch.equal(valid.cpu().bool(), torch.stack(d['valids'], 1).squeeze(2))
+    assert torch.equal(count.cpu().long(), d['count'].squeeze(1))
+    assert torch.equal(net.last_count.cpu(), count.cpu())
+    assert torch.equal(rgrid.cpu(), torch.stack(grids_ref, 1))
+    rec['voxel_feat'] = H.rel_err(vox.detach().cpu(), d['voxel_feat'].detach())
+    rec['ray_samples'] = H.rel_err(got.detach().cpu(), ref.detach())
+    for name, a, b in zip(('d_feats', 'd_w_no', 'd_b_no', 'd_w_ov', 'd_b_ov'), grads, g_ref):
+        rec[name] = H.rel_err(a.cpu().reshape(b.shape), b)
+    _report('baseline_size_oracle_parity', rec)
+    for k in ('voxel_feat', 'ray_samples', 'd_feats', 'd_w_no', 'd_b_no', 'd_w_ov', 'd_b_ov'):
+        assert rec[k] < TOL, (k, rec[k])
+
+
+def test_batch8_rig_slices_equal_single_rig_launches():
+    """bench.py's configuration (B=8, C=256, Cv=64, 384x640 rigs; the ray-sample tensor is 2.36 GB, past 2^31 bytes): rigs
+    are independent, so rig i of the B=8 launch must equal a B=1 launch of the same rig -- bit for bit where the kernel
+    is deterministic (volume, ray samples), to 1e-6 where gradients are accumulated with atomics."""
+    dev = _dev()
+    B = 8
+    cfg = vcfg.default_config('ddad', batch_size=B)
+    inputs, _ = make_rig(cfg, seed=88, with_images=False, with_feats=False)
+    lvl = cfg['model']['fusion_level'] + 1
+    net = _net(cfg, 256, 128, 'depth', None, dev)
+    g = net.geom
+    to = lambda t: t.to(dev)
+    torch.manual_seed(11)
+    feats0 = torch.randn(B, 6, 256, g.h, g.w, device=dev)
+    up = torch.randn(B, 6, g.h, g.w, g.D, g.Cv, device=dev)
+    assert up.numel() * 4 > 2 ** 31
+    names = ('mask', ('K', lvl), 'extrinsics_inv', ('inv_K', lvl), 'extrinsics')
+    full = [to(inputs[k]) for k in names]
+
+    def run(sl):
+        f = feats0[sl].clone().requires_grad_(True)
+        m, K, Einv, invK, E = (t[sl] for t in full)
+        vox = net.backproject_into_voxel(f, m, K, Einv)
+        rows = net.ray_rows(vox, invK, E)
+        d_f, = torch.autograd.grad((rows * up[sl]).sum(), f)
+        return vox.detach(), rows.detach(), d_f
+
+    vox8, rows8, df8 = run(slice(0, B))
+    rec = {}
+    for i in (0, B - 1):
+        vox1, rows1, df1 = run(slice(i, i + 1))
+        assert torch.equal(vox1, vox8[i:i + 1]), i
+        assert torch.equal(rows1, rows8[i:i + 1]), i
+        rec['d_feats_rig%d' % i] = H.rel_err(df1, df8[i:i + 1])
+        assert rec['d_feats_rig%d' % i] < 1e-6, (i, rec)
+    _report('batch8_rig_slices', rec)

@@ -34,7 +34,6 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--dataset', default='ddad')
     ap.add_argument('--only', default='')
-    ap.add_argument('--sort', default='', help="experiment: reorder the compact lists by 'rowmajor' or 'morton' pixel key")
     args = ap.parse_args()
     dev = torch.device('cuda:0')
     B = args.batch
@@ -83,39 +82,20 @@ def main():
                     vol.numel() * 4 + out.numel() * 4),
     }
     # compact lists + fused gather/MLP kernels
-    cnt8, slot, idx_no, idx_ov, totals, table = ops.voxel_classify(mask_small, K, Einv, g, sizes=False, table=True)
+    cnt8, slot, idx_no, idx_ov, totals = ops.voxel_classify(mask_small, K, Einv, g, sizes=False)
     m1, m2 = totals.tolist()
-    if args.sort:
-        rows = B * N
-        t32 = torch.view_as_real(table).view(torch.int32).reshape(-1)
-        off = t32[:rows * 2 * 4].view(2, rows, 4)
-        meta = t32[rows * 2 * 8:rows * 2 * 8 + rows * 2 * 2].view(2, rows, 2)
-
-        def reorder(idx, m):
-            r = idx[:m]
-            pix = off[0, r, 0] // g.C
-            y0, x0 = (pix // g.w).long(), (pix % g.w).long()
-            if args.sort == 'morton':
-                code = torch.zeros_like(x0)
-                for bit in range(7):
-                    code |= ((x0 >> bit) & 1) << (2 * bit)
-                    code |= ((y0 >> bit) & 1) << (2 * bit + 1)
-            else:
-                code = y0 * g.w + x0
-            key = meta[0, r, 0].long() * 16384 + code
-            order = torch.sort(key, stable=True).indices
-            idx[:m] = r[order]
-
-        reorder(idx_no, m1)
-        reorder(idx_ov, m2)
-        print('lists reordered by', args.sort, flush=True)
+    cnt8, table = ops.voxel_classify(mask_small, K, Einv, g, table=True)
     w_no, b_no = torch.randn(g.Cv, c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
     w_ov, b_ov = torch.randn(g.Cv, 2 * c1, device=dev) * 0.05, torch.randn(g.Cv, device=dev) * 0.1
     fvol = torch.empty(B, N, g.Cv, device=dev)
     gvol = torch.randn(B, N, g.Cv, device=dev)
     dw_no, db_no, dw_ov, db_ov = (torch.empty_like(t) for t in (w_no, b_no, w_ov, b_ov))
     nws = _lib.load().vfd_voxel_fuse_bwd_workspace_bytes(ctypes.byref(d))
-    ws = torch.empty(nws // 4, device=dev)
+    ws = torch.empty(nws, device=dev, dtype=torch.uint8)
+    nws_f = _lib.load().vfd_voxel_fuse_fwd_workspace_bytes(ctypes.byref(d))
+    ws_f = torch.empty(nws_f, device=dev, dtype=torch.uint8)
+    nws_c = _lib.load().vfd_voxel_classify_workspace_bytes(ctypes.byref(d))
+    ws_c = torch.empty(max(nws_c, 8), device=dev, dtype=torch.uint8)
     cx_no = torch.empty(max(m1, 1), g.ld_no, device=dev)
     cx_ov = torch.empty(max(m2, 1), g.ld_ov, device=dev)
     rows_b = (m1 + 2 * m2) * c1 * 4
@@ -125,12 +105,15 @@ def main():
                                           p(K), p(Einv), p(slot), p(cx_no), p(cx_ov), st), feat_b + rows_b),
         'compact_bwd': (lambda: _lib.call('vfd_voxel_gather_depth_compact_bwd', ctypes.byref(d), p(mask_small), p(K),
                                           p(Einv), p(slot), p(cx_no), p(cx_ov), p(d_feats), st), feat_b + rows_b),
-        'fuse_fwd': (lambda: _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), p(feats), p(mask_small), p(K), p(Einv),
-                                       p(idx_no), p(idx_ov), p(totals), p(table), p(w_no), p(b_no), p(w_ov), p(b_ov), p(fvol), st),
+        'classify': (lambda: _lib.call('vfd_voxel_classify', ctypes.byref(d), p(mask_small), p(K), p(Einv), p(cnt8), None,
+                                       None, None, None, p(table), p(ws_c), ctypes.c_size_t(ws_c.numel()), st),
+                     B * 6 * g.h * g.w * 4 + B * N + (m1 + 2 * m2) * 40),
+        'fuse_fwd': (lambda: _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), p(feats), p(cnt8), p(table), p(w_no), p(b_no),
+                                       p(w_ov), p(b_ov), p(fvol), p(ws_f), ctypes.c_size_t(nws_f), st),
                      feat_b + vol_b),
-        'fuse_bwd': (lambda: _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), p(feats), p(mask_small), p(K), p(Einv),
-                                       p(idx_no), p(idx_ov), p(totals), p(table), p(w_no), p(w_ov), p(fvol), p(gvol), p(d_feats),
-                                       p(dw_no), p(db_no), p(dw_ov), p(db_ov), p(ws), ctypes.c_size_t(nws), st),
+        'fuse_bwd': (lambda: _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), p(feats), p(cnt8), p(table), p(w_no), p(w_ov),
+                                       p(fvol), p(gvol), p(d_feats), p(dw_no), p(db_no), p(dw_ov), p(db_ov), p(ws),
+                                       ctypes.c_size_t(nws), st),
                      2 * feat_b + 2 * vol_b),
     })
     print('count-1 voxels %d, count-2 voxels %d of %d' % (m1, m2, B * N), flush=True)

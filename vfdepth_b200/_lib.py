@@ -80,7 +80,7 @@ _lock = threading.Lock()
 _lib = None
 launches = 0   # number of kernels launched through the ABI by this process (bench.py reports it)
 # kernels one call of each entry point launches (memsets not counted); anything not listed launches one
-KERNELS_PER_CALL = {'vfd_voxel_classify': 3, 'vfd_voxel_fuse_bwd': 3, 'vfd_warp_stats': 2, 'vfd_warp_loss_bwd': 2, 'vfd_warp_loss_train_bwd': 2,
+KERNELS_PER_CALL = {'vfd_voxel_classify': 3, 'vfd_voxel_fuse_fwd': 3, 'vfd_voxel_fuse_bwd': 5, 'vfd_warp_stats': 2, 'vfd_warp_loss_bwd': 2, 'vfd_warp_loss_train_bwd': 2,
                     'vfd_smooth_loss_fwd': 2, 'vfd_smooth_loss_bwd': 2, 'vfd_smooth_loss_train_fwd': 2,
                     'vfd_feat_agg_bwd': 3, 'vfd_norm_image_fwd': 2}     # fine + one launch per coarse level (two at the shipped configs)
 
@@ -93,8 +93,8 @@ def load():
     with _lock:
         if _lib is not None:
             return _lib
-        if not os.path.isfile(LIB_PATH):
-            from . import build as _build
+        from . import build as _build
+        if _build._stale():          # missing, or older than any source / header it is built from
             _build.build()
         lib = ctypes.CDLL(LIB_PATH)
         lib.vfd_version.restype = ctypes.c_int
@@ -103,6 +103,7 @@ def load():
         lib.vfd_warp_bwd_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_classify_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_fuse_bwd_workspace_bytes.restype = ctypes.c_size_t
+        lib.vfd_voxel_fuse_fwd_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_table_bytes.restype = ctypes.c_size_t
         _lib = lib
     return _lib
@@ -136,10 +137,10 @@ def stop_event_trace():
     return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in (ev or {}).items()}
 
 
-def call(name, *args):
+def call(name, *args, kernels=None):
     global launches
     fn = getattr(load(), name)
-    launches += KERNELS_PER_CALL.get(name, 1)
+    launches += KERNELS_PER_CALL.get(name, 1) if kernels is None else kernels
     if _events is None:
         check(fn(*args), name)
         return

@@ -21,13 +21,32 @@ def sources():
     return sorted(glob.glob(os.path.join(CSRC, '*.cu')))
 
 
-def _stale():
-    if not os.path.isfile(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = sources() + glob.glob(os.path.join(CSRC, '*.h')) + glob.glob(os.path.join(CSRC, '*.cuh')) + \
+STAMP = LIB + '.srchash'
+
+
+def _deps():
+    return sources() + sorted(glob.glob(os.path.join(CSRC, '*.h')) + glob.glob(os.path.join(CSRC, '*.cuh'))) + \
         [os.path.join(os.path.dirname(HERE), 'include', 'vfdepth_b200.h')]
-    return any(os.path.getmtime(p) > t for p in deps)
+
+
+def source_hash():
+    """sha256 over every file the library is built from + the compiler flags (file times do not survive a snapshot
+    copy to another box, contents do)"""
+    import hashlib
+    h = hashlib.sha256(' '.join(FLAGS).encode())
+    for p in _deps():
+        h.update(os.path.basename(p).encode())
+        with open(p, 'rb') as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def _stale():
+    """True when the library is missing or was built from other sources than the ones in the tree now."""
+    if not os.path.isfile(LIB) or not os.path.isfile(STAMP):
+        return True
+    with open(STAMP) as f:
+        return f.read().strip() != source_hash()
 
 
 def build(force=False, verbose=False):
@@ -48,6 +67,8 @@ def build(force=False, verbose=False):
         if p.returncode:
             raise RuntimeError('nvcc failed on %s' % src)
     subprocess.check_call([NVCC, '-shared', '-o', LIB] + objs + ['-lcudart'])
+    with open(STAMP, 'w') as f:
+        f.write(source_hash() + '\n')
     return LIB
 
 

@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(kGatherWarps* VFD_WARP) voxel_count_kernel(con
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 if (e < cnt) {
-                    const Corners q = make_corners(ent[e], d.w, d.h, d.C);
+                    const Corners q = make_corners(ent[e], d.w, d.h, 1);     // pixel indices inside the camera's map
                     t.off[e * rows + row] = make_int4(q.off[0], q.off[1], q.off[2], q.off[3]);
                     t.wgt[e * rows + row] = make_float4(q.wgt[0], q.wgt[1], q.wgt[2], q.wgt[3]);
                     t.meta[e * rows + row] = make_int2(b * d.num_cams + ecam[e], __float_as_int(ent[e].zrel));
@@ -545,7 +545,10 @@ extern "C" int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_sm
                                   void* stream) {
     int rc = check_desc(d);
     if (rc) return rc;
-    if (!mask_small || !K || !Einv || !count || !slot || !idx_no || !idx_ov || !totals || !ws) return VFD_ERR_NULL;
+    if (!mask_small || !K || !Einv || !count || !ws) return VFD_ERR_NULL;
+    // the compact lists are optional as a group: the fused path (vfd_voxel_fuse_*) needs only count + table
+    const bool lists = slot || idx_no || idx_ov || totals;
+    if (lists && (!slot || !idx_no || !idx_ov || !totals)) return VFD_ERR_NULL;
     if (ws_bytes < vfd_voxel_classify_workspace_bytes(d)) return VFD_ERR_WORKSPACE;
     if (reinterpret_cast<uintptr_t>(ws) & 7) return VFD_ERR_ALIGN;
     const long N = (long)d->X * d->Y * d->Z;
@@ -558,8 +561,10 @@ extern "C" int vfd_voxel_classify(const vfd_fusion_desc* d, const float* mask_sm
     cudaStream_t st = (cudaStream_t)stream;
     dim3 grid((unsigned)((N + kGatherWarps * VFD_WARP - 1) / (kGatherWarps * VFD_WARP)), d->B);
     voxel_count_kernel<<<grid, kGatherWarps * VFD_WARP, 0, st>>>(c);
-    voxel_scan_kernel<<<1, 1024, 0, st>>>(c.block_tot, (int)(grid.x * grid.y), totals);
-    voxel_slot_kernel<<<grid, kGatherWarps * VFD_WARP, 0, st>>>(c);
+    if (lists) {
+        voxel_scan_kernel<<<1, 1024, 0, st>>>(c.block_tot, (int)(grid.x * grid.y), totals);
+        voxel_slot_kernel<<<grid, kGatherWarps * VFD_WARP, 0, st>>>(c);
+    }
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }

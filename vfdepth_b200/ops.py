@@ -210,7 +210,8 @@ class _RaySample(torch.autograd.Function):
 def voxel_classify(mask_small, K, Einv, geom, sizes=True, table=False):
     """-> count [B,N] u8, slot [B,N] i32, idx_no [M1] i64, idx_ov [M2] i64 (only count-1 / count-2
     voxels reach an MLP).  With ``sizes`` the two totals are read back to the host (one 8-byte copy) to slice the
-    lists; without, the full-capacity lists and the device-side totals [2] are returned (no synchronisation)."""
+    lists; without, the full-capacity lists and the device-side totals [2] are returned (no synchronisation).
+    ``table=True`` (the fused path): -> (count, table) only -- one launch, no lists."""
     g = geom
     B = mask_small.shape[0]
     _chk(mask_small, 'mask_small', (B, g.num_cams, g.h, g.w))
@@ -219,21 +220,22 @@ def voxel_classify(mask_small, K, Einv, geom, sizes=True, table=False):
     dev = mask_small.device
     d = g.desc(dev, B)
     count = torch.empty((B, g.N), device=dev, dtype=torch.uint8)
+    nbytes = _lib.load().vfd_voxel_classify_workspace_bytes(ctypes.byref(d))
+    ws = torch.empty((max(nbytes, 8) // 8,), device=dev, dtype=torch.int64)
+    if table:   # per-voxel corner table for the fused kernels (80 bytes per voxel of the grid)
+        tab = torch.empty((_lib.load().vfd_voxel_table_bytes(ctypes.byref(d)) // 16,), device=dev,
+                          dtype=torch.complex128)
+        _lib.call('vfd_voxel_classify', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv),
+                  _lib.ptr(count), None, None, None, None, _lib.ptr(tab), _lib.ptr(ws),
+                  ctypes.c_size_t(ws.numel() * 8), _stream(), kernels=1)
+        return count, tab
     slot = torch.empty((B, g.N), device=dev, dtype=torch.int32)
     idx_no = torch.empty((B * g.N,), device=dev, dtype=torch.int64)
     idx_ov = torch.empty((B * g.N,), device=dev, dtype=torch.int64)
     totals = torch.empty((2,), device=dev, dtype=torch.int32)
-    nbytes = _lib.load().vfd_voxel_classify_workspace_bytes(ctypes.byref(d))
-    ws = torch.empty((max(nbytes, 8) // 8,), device=dev, dtype=torch.int64)
-    tab = None
-    if table:   # per-voxel corner table for the fused kernels (80 bytes per voxel of the grid)
-        tab = torch.empty((_lib.load().vfd_voxel_table_bytes(ctypes.byref(d)) // 16,), device=dev,
-                          dtype=torch.complex128)
     _lib.call('vfd_voxel_classify', ctypes.byref(d), _lib.ptr(mask_small), _lib.ptr(K), _lib.ptr(Einv),
-              _lib.ptr(count), _lib.ptr(slot), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(tab),
+              _lib.ptr(count), _lib.ptr(slot), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), None,
               _lib.ptr(ws), ctypes.c_size_t(ws.numel() * 8), _stream())
-    if table:
-        return count, slot, idx_no, idx_ov, totals, tab
     if not sizes:
         return count, slot, idx_no, idx_ov, totals
     m1, m2 = totals.tolist()
@@ -283,56 +285,64 @@ def voxel_gather_depth_compact(feats_cl, mask_small, K, Einv, slot, m1, m2, geom
     return _VoxelGatherDepthCompact.apply(feats_cl, mask_small, K, Einv, slot, m1, m2, geom)
 
 
+def _workspace(nbytes, dev):
+    """256-byte aligned scratch (the caching allocator hands out 512-byte aligned blocks)"""
+    return torch.empty((max(nbytes, 256),), device=dev, dtype=torch.uint8)
+
+
 class _VoxelFuse(torch.autograd.Function):
-    """gather + both 1x1 MLPs in one kernel (vfd_voxel_fuse_fwd); backward in vfd_voxel_fuse_bwd."""
+    """gather + both 1x1 MLPs (vfd_voxel_fuse_fwd: dense projection of the feature pixels, then the voxel gather);
+    backward in vfd_voxel_fuse_bwd."""
 
     @staticmethod
-    def forward(ctx, feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, geom):
+    def forward(ctx, feats, w_no, b_no, w_ov, b_ov, count, table, geom):
         B = feats.shape[0]
         g = geom
         c1 = g.C + 1
         _chk(feats, 'feats', (B, g.num_cams, g.h, g.w, g.C))
-        _chk(mask_small, 'mask_small', (B, g.num_cams, g.h, g.w))
-        _chk(K, 'K', (B, g.num_cams, 4, 4))
-        _chk(Einv, 'Einv', (B, g.num_cams, 4, 4))
         w_no, b_no, w_ov, b_ov = (t.detach().contiguous() for t in (w_no, b_no, w_ov, b_ov))
         _chk(w_no, 'w_no', (g.Cv, c1))
         _chk(b_no, 'b_no', (g.Cv,))
         _chk(w_ov, 'w_ov', (g.Cv, 2 * c1))
         _chk(b_ov, 'b_ov', (g.Cv,))
+        if count.dtype != torch.uint8 or tuple(count.shape) != (B, g.N) or not count.is_cuda or not count.is_contiguous():
+            raise ValueError('count must be a contiguous CUDA uint8 tensor [B,N]')
         dev = feats.device
         d = g.desc(dev, B)
         vol = torch.empty((B, g.N, g.Cv), device=dev, dtype=torch.float32)
-        _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
-                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(table), _lib.ptr(w_no),
-                  _lib.ptr(b_no), _lib.ptr(w_ov), _lib.ptr(b_ov), _lib.ptr(vol), _stream())
+        nbytes = _lib.load().vfd_voxel_fuse_fwd_workspace_bytes(ctypes.byref(d))
+        if nbytes == 0:
+            raise ValueError('vfd_voxel_fuse_fwd does not take C=%d, Cv=%d' % (g.C, g.Cv))
+        ws = _workspace(nbytes, dev)
+        _lib.call('vfd_voxel_fuse_fwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(count), _lib.ptr(table),
+                  _lib.ptr(w_no), _lib.ptr(b_no), _lib.ptr(w_ov), _lib.ptr(b_ov), _lib.ptr(vol), _lib.ptr(ws),
+                  ctypes.c_size_t(ws.numel()), _stream())
         ctx.geom = g
-        ctx.save_for_backward(feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, vol)
+        ctx.save_for_backward(feats, w_no, w_ov, count, table, vol)
         return vol
 
     @staticmethod
     def backward(ctx, d_vol):
-        feats, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, vol = ctx.saved_tensors
+        feats, w_no, w_ov, count, table, vol = ctx.saved_tensors
         g = ctx.geom
         B = feats.shape[0]
         dev = feats.device
         d = g.desc(dev, B)
         d_vol = d_vol.contiguous()
         d_feats = torch.empty_like(feats)
-        d_w_no, d_b_no = torch.empty_like(w_no), torch.empty_like(b_no)
-        d_w_ov, d_b_ov = torch.empty_like(w_ov), torch.empty_like(b_ov)
-        nbytes = _lib.load().vfd_voxel_fuse_bwd_workspace_bytes(ctypes.byref(d))
-        ws = torch.empty((max(nbytes, 16) // 4,), device=dev, dtype=torch.float32)
-        _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(mask_small), _lib.ptr(K),
-                  _lib.ptr(Einv), _lib.ptr(idx_no), _lib.ptr(idx_ov), _lib.ptr(totals), _lib.ptr(table), _lib.ptr(w_no),
-                  _lib.ptr(w_ov), _lib.ptr(vol), _lib.ptr(d_vol), _lib.ptr(d_feats), _lib.ptr(d_w_no), _lib.ptr(d_b_no),
-                  _lib.ptr(d_w_ov), _lib.ptr(d_b_ov), _lib.ptr(ws), ctypes.c_size_t(ws.numel() * 4), _stream())
-        return d_feats, d_w_no, d_b_no, d_w_ov, d_b_ov, None, None, None, None, None, None, None, None
+        d_w_no, d_b_no = torch.empty_like(w_no), torch.empty((g.Cv,), device=dev)
+        d_w_ov, d_b_ov = torch.empty_like(w_ov), torch.empty((g.Cv,), device=dev)
+        ws = _workspace(_lib.load().vfd_voxel_fuse_bwd_workspace_bytes(ctypes.byref(d)), dev)
+        _lib.call('vfd_voxel_fuse_bwd', ctypes.byref(d), _lib.ptr(feats), _lib.ptr(count), _lib.ptr(table),
+                  _lib.ptr(w_no), _lib.ptr(w_ov), _lib.ptr(vol), _lib.ptr(d_vol), _lib.ptr(d_feats), _lib.ptr(d_w_no),
+                  _lib.ptr(d_b_no), _lib.ptr(d_w_ov), _lib.ptr(d_b_ov), _lib.ptr(ws), ctypes.c_size_t(ws.numel()),
+                  _stream())
+        return d_feats, d_w_no, d_b_no, d_w_ov, d_b_ov, None, None, None
 
 
-def voxel_fuse(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, geom):
+def voxel_fuse(feats_cl, w_no, b_no, w_ov, b_ov, count, table, geom):
     """feats_cl [B,cams,h,w,C] + MLP parameters -> channel-last voxel volume [B,N,Cv]."""
-    return _VoxelFuse.apply(feats_cl, w_no, b_no, w_ov, b_ov, mask_small, K, Einv, idx_no, idx_ov, totals, table, geom)
+    return _VoxelFuse.apply(feats_cl, w_no, b_no, w_ov, b_ov, count, table, geom)
 
 
 def voxel_gather_depth(feats_cl, mask_small, K, Einv, geom, detail=False):

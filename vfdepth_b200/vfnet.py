@@ -146,13 +146,13 @@ class VFNet(nn.Module):
             K = intrinsics.float().contiguous()
             Einv = extrinsics_inv.float().contiguous()
             if self.fused_mlp and g.C <= 256 and g.Cv <= 64 and g.Cv % 4 == 0:
-                # gather + both MLPs in one kernel, no host round trip, rows never reach HBM
-                count, _, idx_no, idx_ov, totals, table = ops.voxel_classify(mask_small, K, Einv, g, sizes=False,
-                                                                             table=True)
+                # the MLPs commute with the bilinear gather -- project every feature pixel once (dense
+                # tcgen05 + TMA product), gather Cv-float rows per voxel; no host round trip, no GEMM row in HBM
+                count, table = ops.voxel_classify(mask_small, K, Einv, g, table=True)
                 self.last_count = count
                 vol = ops.voxel_fuse(feats_cl, self.conv_non_overlap[0].weight.squeeze(-1),
                                      self.conv_non_overlap[0].bias, self.conv_overlap[0].weight.squeeze(-1),
-                                     self.conv_overlap[0].bias, mask_small, K, Einv, idx_no, idx_ov, totals, table, g)
+                                     self.conv_overlap[0].bias, count, table, g)
                 return vol.permute(0, 2, 1)
             count, slot, idx_no, idx_ov = ops.voxel_classify(mask_small, K, Einv, g)
             self.last_count = count
