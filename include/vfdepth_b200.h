@@ -217,10 +217,15 @@ typedef struct vfd_warp_views {
  *   T      [B,n_call,NW,4,4]     target->source transforms (cam_T_cam / rel_pose_dict, pose.py:66-96)
  *   stats  [B,n_call,NW,8] f64   scratch, zero-filled here: {count, sum ref*m, sum warp*m, sum warp, sum warp^2,
  *                                sum ref, sum ref^2, -}
- *   params [B,n_call,NW,8] f32   out: {w_mean, w_std+1e-8, s_std, s_mean, apply, 1/(w_std+1e-8), -, -}; apply = 0
- *                                when intensity_align is off or the batch-wide early exit of :50-53 fires for warp j
- *   raw    [B,n_call,NW,H,W,4]   out: the un-normalised warp (r, g, b) and warp mask of every source image
- *                                (get_virtual_image, :61-82); 16-byte aligned.  The loss passes read it back. */
+ *   params [B,n_call,NW,8] f32   out: {w_mean, w_std+1e-8, s_std, s_mean, apply, 1/(w_std+1e-8), finite, -}; apply = 0
+ *                                when intensity_align is off or the batch-wide early exit of :50-53 fires for warp j;
+ *                                finite = 1 when every parameter is finite
+ *   raw    vfd_warp_raw_bytes(d) bytes, 16-byte aligned, out: [B,n_call,NW,H,W,4] floats = the un-normalised warp
+ *                                (r, g, b) and warp mask of every source image (get_virtual_image, :61-82), followed by
+ *                                [B,n_call,H,W] bytes = which of a pixel's NW warps are not all-zero.  Only those
+ *                                entries are written, and only those are read back by the loss passes (a spatial
+ *                                warp leaves the neighbour camera's image for most pixels of the target). */
+size_t vfd_warp_raw_bytes(const vfd_warp_desc* d);
 int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const float* T, double* stats, float* params,
                    float* raw, void* stream);
 

@@ -102,6 +102,7 @@ def test_bad_arguments_are_rejected_before_any_launch():
     sd = _lib.SynDesc()
     assert lib.vfd_depth_syn_fwd(ctypes.byref(sd), null, null, null, null, null, null, null, null) == -2
     assert lib.vfd_warp_stats(null, null, null, null, null, null, null) == -1
+    assert lib.vfd_warp_raw_bytes(null) == 0
     assert lib.vfd_voxel_gather_pose_bev_fwd(null, null, null, null, null, null, null, null) == -1
     assert lib.vfd_voxel_gather_pose_bev_bwd(null, null, null, null, null, null, null) == -1
     assert lib.vfd_warp_image_blocks() == 148
@@ -145,6 +146,8 @@ def test_bad_arguments_are_rejected_before_any_launch():
     # valid sizes but NULL data pointers
     w.B, w.num_cams, w.H, w.W, w.n_src, w.cam0, w.n_call = 1, 6, 8, 8, 2, 0, 6
     assert lib.vfd_warp_stats(ctypes.byref(w), null, null, null, null, null, null) == -1
+    w.color[0] = w.color[1] = w.color[2] = w.mask = w.K = w.invK = 16        # non-NULL: only the sizes are read
+    assert lib.vfd_warp_raw_bytes(ctypes.byref(w)) == 1 * 6 * 8 * 64 * 16 + 1 * 6 * 64
     with pytest.raises(RuntimeError, match='NULL'):
         _lib.check(-1, 'vfd_test')
 

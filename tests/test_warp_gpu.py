@@ -180,6 +180,17 @@ def _terms(det_ref):
                          for c in range(6)], dtype=torch.float64)
 
 
+def _report(name, rec):
+    """achieved errors go to gpurun_out/parity_report.jsonl (copied into profiles/ with the round's evidence)"""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    os.makedirs(os.path.join(root, 'gpurun_out'), exist_ok=True)
+    with open(os.path.join(root, 'gpurun_out', 'parity_report.jsonl'), 'a') as f:
+        f.write(json.dumps(dict(test=name, **rec)) + '\n')
+    print(name, rec)
+
+
 def _standard_case(dev, height, width, batch, seed, dataset='ddad'):
     """The reference's own configuration (3 frames, spatio + spatio-temporal, intensity alignment).
     1. against the plain fp32 oracle: images within tolerance, masks bit-exact, the three per-pixel decisions identical
@@ -197,16 +208,26 @@ def _standard_case(dev, height, width, batch, seed, dataset='ddad'):
     dec = _gpu_decisions(det, cfg)
     p32 = _run_oracle(cfg, inp, ex, torch.float32, dec)
     p64 = _run_oracle(cfg, inp, ex, torch.float64, dec)
-    assert abs(float(total) - float(p64[0])) / float(p64[0]) < TOL
+    rec = dict(dataset=dataset, size=[batch, height, width], pixels=npix, decision_flips=nflip,
+               worst_flip_margin=worst, total_rel_err=abs(float(total) - float(p64[0])) / float(p64[0]))
+    assert rec['total_rel_err'] < TOL
     e, bar = _arbitrated(det['terms'].cpu(), _terms(p32[1]), _terms(p64[1]))
+    rec['terms'] = dict(err=e, bar=bar)
     assert e <= bar, ('terms', e, bar)
+    rec['reproj_map'] = []
     for cam in range(6):
         e, bar = _arbitrated(det['views']['reproj_loss'][:, cam:cam + 1].cpu(), p32[1][cam]['reproj_map'].detach(),
                              p64[1][cam]['reproj_map'].detach())
+        rec['reproj_map'].append(dict(err=e, bar=2 * bar))
         assert e <= 2 * bar, ('reproj_map', cam, e, bar)     # SSIM amplifies 1 ulp of the image to ~5e-5 of the map
+    rec['gradients'] = []
+    names = ['d_depth_cam%d' % c for c in range(6)] + ['d_T_%d' % f for f in cfg['training']['frame_ids'][1:]]
     for i in range(len(grads)):
         e, bar = _arbitrated(grads[i], p32[2][i], p64[2][i])
+        # err / bar are relative to the fp64 oracle; oracle32 = the fp32 oracle's own distance to it (bar = max(1e-4, 2x))
+        rec['gradients'].append(dict(name=names[i], err=e, bar=bar))
         assert e <= bar, ('gradient', i, e, bar)
+    _report('warp_standard_case', rec)
     return nflip, npix
 
 
@@ -554,3 +575,40 @@ def test_step_is_cuda_graph_capturable():
     assert abs(float(outs[0]) - float(eager[0])) / abs(float(eager[0])) < 1e-6
     for a, b in zip(outs[1:], eager[1:]):
         assert H.rel_err(a.detach().cpu(), b.cpu()) < 1e-5
+
+
+def test_batch8_rig_slices_equal_single_rig_launches():
+    """bench.py's warp/loss configuration (B=8, 6 x 3 x 384 x 640; the raw-warp scratch is 1.5 GB): rigs only meet in
+    the masked sums (loss_util.py:21-25 sums over the local batch) and in the batch-wide early exit of the intensity
+    alignment (no rig of this batch triggers it), so the sums of the B=8 launch must equal the sum of the B=1 launches
+    of its rigs, and d num_set / d depth of rig i must equal the B=1 launch's -- the whole backward is deterministic
+    and per-pixel, so bit for bit; the sums are fp64 atomics, so to 1e-9."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    B = 8
+    cfg, inp, ex = _rig(384, 640, B, seed=321)
+    to = lambda t: t.to(dev)
+    inp_d = {k: to(v) for k, v in inp.items()}
+    depth = torch.cat([to(d) for d in ex['depth']], 1)
+    noise = torch.stack([to(n) for n in ex['noise']], 1)
+    T_all = {f: to(t) for f, t in ex['cam_T_cam'].items()}
+
+    def run(sl):
+        sub = {k: v[sl] for k, v in inp_d.items()}
+        wi = view.WarpInputs(cfg, sub)
+        d = depth[sl].clone().requires_grad_(True)
+        T = view.rig_transforms(wi, sub, {f: t[sl] for f, t in T_all.items()})
+        num, den, _ = view.warp_loss_sums(wi, d, T, noise[sl].contiguous())
+        w = torch.tensor([1.0, 0.5, 0.25], device=dev)
+        g, = torch.autograd.grad((num * w).sum(), d)
+        return num.double(), den.double(), g
+
+    num8, den8, g8 = run(slice(0, B))
+    nsum, dsum = torch.zeros_like(num8), torch.zeros_like(den8)
+    for i in range(B):
+        n1, d1, g1 = run(slice(i, i + 1))
+        nsum += n1
+        dsum += d1
+        if i in (0, B - 1):
+            assert torch.equal(g1, g8[i:i + 1]), i
+    assert H.rel_err(num8, nsum) < 1e-6 and H.rel_err(den8, dsum) < 1e-6      # the sums leave the kernel as fp32

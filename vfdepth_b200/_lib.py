@@ -101,6 +101,7 @@ def load():
         lib.vfd_last_error.restype = ctypes.c_char_p
         lib.vfd_last_error.argtypes = [ctypes.c_int]
         lib.vfd_warp_bwd_workspace_bytes.restype = ctypes.c_size_t
+        lib.vfd_warp_raw_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_classify_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_fuse_bwd_workspace_bytes.restype = ctypes.c_size_t
         lib.vfd_voxel_fuse_fwd_workspace_bytes.restype = ctypes.c_size_t

@@ -387,14 +387,213 @@ int dense_dw_slabs(int n_img) {
     return s < 1 ? 1 : s;
 }
 
-size_t dense_dw_part_floats(int n_img, int C, int N2) { return (size_t)n_img * dense_dw_slabs(n_img) * N2 * C; }
+// ---------------------------------------------------------------------------------------------------------
+// dWcat on tcgen05 (N2 == 128, C % 16 == 0):  D[n][c] += sum over pixels dP[p][n] * feats[p][c].  The contraction runs
+// over the ROWS of both tensors, so both operands are MN-major: TMA boxes {32 channels, 32 pixels} land as [pixel][128 B]
+// blocks with SWIZZLE_128B_ATOM_32B, which is the one MN-major layout kind::tf32 takes (umma_desc_mn).  One CTA per SM
+// accumulates the [128 x C] product of its share of one camera group's pixels in TMEM (C columns) and writes it once.
+//   warps 0-3  epilogue (after the last chunk): tcgen05.ld -> partial [cta][128][C]
+//   warp  4    TMA producer: per 32-pixel chunk N2/32 + C/32 boxes into a stage (2 stages x 96 KB at C = 256)
+//   warp  5    MMA issue: 4 K-steps of 8 pixels x {A_lo B_hi, A_hi B_lo, A_hi B_hi}
+//   warps 6-13 split both operand tiles into TF32 hi (in place) + lo (second half of the stage)
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kDtKP = 32;                        // pixels per chunk
+constexpr int kDtThreads = 14 * VFD_WARP, kDtConvThreads = 8 * VFD_WARP;
+constexpr int kDtBlock = kDtKP * 128;            // bytes of one {32 channels, 32 pixels} box
 
-int dense_dw(int n_img, int hw, int C, int N2, const float* dP, const float* feats, float* part, cudaStream_t st) {
+struct DwTcArgs {
+    int hw, C, N2, cams, chunks_per_img;
+    int n_group_img[2];               // images per overlap group
+    int ncam[2];                      // cameras per group
+    int camlist[2][VFD_MAX_CAMS];     // their indices
+    int cta0[3];                      // CTAs [cta0[g], cta0[g+1]) work on group g
+    float* part;                      // [ctas][N2][C]
+};
+
+struct DtBars {
+    uint64_t tma_full[2], conv_full[2], empty[2], acc_full;
+    uint32_t tmem_base;
+};
+
+static inline uint32_t dt_stage_bytes(int C, int N2) { return 2u * (uint32_t)(N2 / 32 + C / 32) * kDtBlock; }
+static inline size_t dt_smem_bytes(int C, int N2) { return 1024 + 2 * (size_t)dt_stage_bytes(C, N2) + sizeof(DtBars); }
+
+__global__ void __launch_bounds__(kDtThreads, 1)
+    dense_dw_tc_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant__ CUtensorMap mapF, const DwTcArgs a,
+                       int tmem_cols) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int C = a.C, N2 = a.N2, nbA = N2 / 32, nbB = C / 32;
+    const uint32_t half = (uint32_t)(nbA + nbB) * kDtBlock, sbytes = 2 * half;   // [A hi | B hi | A lo | B lo]
+    DtBars* bars = reinterpret_cast<DtBars*>(base + 2 * (size_t)sbytes);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = (int)blockIdx.x >= a.cta0[1] ? 1 : 0;
+    const int nc = a.cta0[g + 1] - a.cta0[g], ci = (int)blockIdx.x - a.cta0[g];
+    const long items = (long)a.n_group_img[g] * a.chunks_per_img;
+    const long it0 = items * ci / nc, it1 = items * (ci + 1) / nc;
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&bars->tma_full[s], 1);
+            mbar_init(&bars->conv_full[s], kDtConvThreads);
+            mbar_init(&bars->empty[s], 1);
+        }
+        mbar_init(&bars->acc_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        if (lane == 0) { tma_prefetch_desc(&mapP); tma_prefetch_desc(&mapF); }
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)),
+                     "r"(tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = bars->tmem_base;
+
+    uint32_t stage = 0, phase = 0;
+    if (warp == 4) {
+        if (lane == 0) {
+            for (long it = it0; it < it1; ++it) {
+                const int ki = (int)(it / a.chunks_per_img), p0 = (int)(it - (long)ki * a.chunks_per_img) * kDtKP;
+                const int img = (ki / a.ncam[g]) * a.cams + a.camlist[g][ki % a.ncam[g]];
+                mbar_wait(&bars->empty[stage], phase ^ 1);
+                unsigned char* st = base + (size_t)stage * sbytes;
+                mbar_expect_tx(&bars->tma_full[stage], half);
+                for (int k = 0; k < nbA; ++k) tma_load_3d(st + k * kDtBlock, &mapP, k * 32, p0, img, &bars->tma_full[stage]);
+                for (int k = 0; k < nbB; ++k)
+                    tma_load_3d(st + (nbA + k) * kDtBlock, &mapF, k * 32, p0, img, &bars->tma_full[stage]);
+                if (++stage == 2) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 5) {
+        const uint32_t idesc = umma_idesc_tf32_mn(N2, C);
+        for (long it = it0; it < it1; ++it) {
+            mbar_wait(&bars->conv_full[stage], phase);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t s0 = smem_u32(base + (size_t)stage * sbytes);
+#pragma unroll
+                for (int ks = 0; ks < kDtKP / 8; ++ks) {     // 8 pixels = 8 rows of 128 bytes per K-step
+                    const uint32_t o = (uint32_t)ks * 1024u;
+                    const uint64_t a_hi = umma_desc_mn(s0 + o, kDtBlock), a_lo = umma_desc_mn(s0 + half + o, kDtBlock);
+                    const uint64_t b_hi = umma_desc_mn(s0 + nbA * kDtBlock + o, kDtBlock);
+                    const uint64_t b_lo = umma_desc_mn(s0 + half + nbA * kDtBlock + o, kDtBlock);
+                    umma_tf32(tmem, a_lo, b_hi, idesc, (it > it0 || ks) ? 1u : 0u);
+                    umma_tf32(tmem, a_hi, b_lo, idesc, 1u);
+                    umma_tf32(tmem, a_hi, b_hi, idesc, 1u);
+                }
+                tc_commit(&bars->empty[stage]);
+                if (it == it1 - 1) tc_commit(&bars->acc_full);
+            }
+            __syncwarp();
+            if (++stage == 2) { stage = 0; phase ^= 1; }
+        }
+    } else if (warp >= 6) {
+        const int ctid = tid - 6 * VFD_WARP;
+        const int n16 = (int)(half / 16);
+        for (long it = it0; it < it1; ++it) {
+            mbar_wait(&bars->tma_full[stage], phase);
+            uint4* ph = reinterpret_cast<uint4*>(base + (size_t)stage * sbytes);
+            uint4* pl = reinterpret_cast<uint4*>(base + (size_t)stage * sbytes + half);
+            for (int o = ctid; o < n16; o += kDtConvThreads) {
+                const uint4 v = ph[o];
+                uint4 h, l;
+                split_tf32(__uint_as_float(v.x), h.x, l.x);
+                split_tf32(__uint_as_float(v.y), h.y, l.y);
+                split_tf32(__uint_as_float(v.z), h.z, l.z);
+                split_tf32(__uint_as_float(v.w), h.w, l.w);
+                ph[o] = h;
+                pl[o] = l;
+            }
+            fence_proxy_async_smem();
+            mbar_arrive(&bars->conv_full[stage]);
+            if (++stage == 2) { stage = 0; phase ^= 1; }
+        }
+    } else {
+        // epilogue: TMEM lane = n
+        float* o = a.part + ((size_t)blockIdx.x * N2 + tid) * C;
+        if (it1 > it0) {
+            mbar_wait(&bars->acc_full, 0);
+            tc_fence_after();
+            for (int c0 = 0; c0 < C; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+                for (int q = 0; q < 16; q += 4)
+                    *reinterpret_cast<float4*>(o + c0 + q) = make_float4(__uint_as_float(v[q]), __uint_as_float(v[q + 1]),
+                                                                       __uint_as_float(v[q + 2]), __uint_as_float(v[q + 3]));
+            }
+        } else {
+            for (int c0 = 0; c0 < C; c0 += 4) *reinterpret_cast<float4*>(o + c0) = f4_zero();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(tmem_cols));
+}
+
+bool dense_dw_tc_ok(int C, int N2) { return N2 == 128 && C % 32 == 0 && C >= 32 && C <= 256; }
+
+// number of partial [N2][C] blocks dense_dw writes, and which overlap group each belongs to
+int dense_dw_parts(int n_img, int C, int N2) {
+    if (dense_dw_tc_ok(C, N2)) {
+        const int sms = sm_count_pj();
+        return sms > 0 ? sms : 148;
+    }
+    return n_img * dense_dw_slabs(n_img);
+}
+
+size_t dense_dw_part_floats(int n_img, int C, int N2) {
+    int p = dense_dw_parts(n_img, C, N2);
+    if (p < 256) p = 256;          // sized before the SM count is known to the caller's allocator: never too small
+    return (size_t)p * N2 * C;
+}
+
+// -> *n_parts partial blocks [N2][C] in `part`.  *split >= 0 (tensor path): blocks [0, split) belong to overlap group 0,
+// the rest to group 1.  *split < 0 (fp32 FMA path): block i belongs to the group of image i / dense_dw_slabs(n_img).
+int dense_dw(int n_img, int hw, int C, int N2, int cams, const int* group, const float* dP, const float* feats, float* part,
+             int* n_parts, int* split, cudaStream_t st) {
     if (N2 > kDwN || C > kDwC || N2 % 4 || C % 4) return VFD_ERR_UNSUPPORTED;
+    if (dense_dw_tc_ok(C, N2)) {
+        DwTcArgs a = {};
+        a.hw = hw; a.C = C; a.N2 = N2; a.cams = cams; a.chunks_per_img = (hw + kDtKP - 1) / kDtKP; a.part = part;
+        for (int c = 0; c < cams; ++c) {
+            const int g = group[c] ? 1 : 0;
+            a.camlist[g][a.ncam[g]++] = c;
+        }
+        const int B = n_img / cams;
+        a.n_group_img[0] = B * a.ncam[0];
+        a.n_group_img[1] = B * a.ncam[1];
+        const int ctas = dense_dw_parts(n_img, C, N2);
+        int c0 = (int)((long)ctas * a.n_group_img[0] / n_img);
+        if (a.n_group_img[0] > 0 && c0 < 1) c0 = 1;
+        if (a.n_group_img[1] > 0 && c0 > ctas - 1) c0 = ctas - 1;
+        if (a.n_group_img[1] == 0) c0 = ctas;
+        a.cta0[0] = 0; a.cta0[1] = c0; a.cta0[2] = ctas;
+        *n_parts = ctas;
+        *split = c0;
+        CUtensorMap mp, mf;
+        if (!make_map_3d(&mp, dP, (uint64_t)N2, (uint64_t)hw, (uint64_t)n_img, kDtKP, true) ||
+            !make_map_3d(&mf, feats, (uint64_t)C, (uint64_t)hw, (uint64_t)n_img, kDtKP, true))
+            return VFD_ERR_CUDA;
+        const size_t smem = dt_smem_bytes(C, N2);
+        if (smem > 227 * 1024) return VFD_ERR_UNSUPPORTED;
+        if (cudaFuncSetAttribute(dense_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return VFD_ERR_CUDA;
+        int cols = 32;
+        while (cols < C) cols <<= 1;
+        dense_dw_tc_kernel<<<ctas, kDtThreads, smem, st>>>(mp, mf, a, cols);
+        VFD_CHECK_LAUNCH();
+        return VFD_OK;
+    }
     DwArgs a = {};
     a.hw = hw; a.C = C; a.N2 = N2; a.slabs = dense_dw_slabs(n_img);
     a.slab_len = ((hw + a.slabs - 1) / a.slabs + kDwKT - 1) / kDwKT * kDwKT;
     a.dP = dP; a.feats = feats; a.part = part;
+    *n_parts = n_img * a.slabs;
+    *split = -1;
     dense_dw_kernel<<<dim3(a.slabs, n_img), kDwThreads, 0, st>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;

@@ -31,6 +31,19 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
 __host__ __device__ inline uint32_t umma_idesc_tf32(int M, int N) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// MN-major operand (rows = K, 32 consecutive M/N elements per 128-byte row, 4-row atoms of 512 bytes with 32-byte chunks
+// XOR row & 3 = what a TMA box {32 floats, rows} with SWIZZLE_128B_ATOM_32B leaves in shared memory): layout type
+// SWIZZLE_128B_BASE32B, leading byte offset = distance between 32-element M/N blocks, stride byte offset = 512 (between
+// the two 4-row atoms one K = 8 instruction reads).  Validated by tools/umma_mn_probe.cu (profiles/r02_umma_mn_probe.txt).
+__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t saddr, uint32_t block_stride_bytes) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((block_stride_bytes >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)1 << 61);
+}
+// instruction descriptor of kind::tf32, fp32 accumulate, both operands MN-major
+__host__ __device__ inline uint32_t umma_idesc_tf32_mn(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
+}
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -79,8 +92,11 @@ inline vfd_encode_tiled_fn encode_tiled_entry() {
     return fn;
 }
 
-// fp32 tensor [d2][d1][d0] (d0 contiguous), box [1][box1][32 floats = 128 bytes], SWIZZLE_128B, zero fill
-inline bool make_map_3d(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box1) {
+// fp32 tensor [d2][d1][d0] (d0 contiguous), box [1][box1][32 floats = 128 bytes], zero fill.  swizzle32 = false:
+// SWIZZLE_128B (16-byte chunks XOR row & 7: the K-major operand layout); true: SWIZZLE_128B_ATOM_32B (32-byte chunks XOR
+// row & 3: the only MN-major layout kind::tf32 accepts -- UMMA layout type SWIZZLE_128B_BASE32B, tools/umma_mn_probe.cu)
+inline bool make_map_3d(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box1,
+                        bool swizzle32 = false) {
     vfd_encode_tiled_fn enc = encode_tiled_entry();
     if (!enc) return false;
     const cuuint64_t dims[3] = {d0, d1, d2};
@@ -88,7 +104,8 @@ inline bool make_map_3d(CUtensorMap* map, const void* base, uint64_t d0, uint64_
     const cuuint32_t box[3] = {32, box1, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), dims, strides, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+               CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 

@@ -17,7 +17,8 @@
 //
 // Backward: voxel_fuse_scatter_kernel forms dZ = d_vol * LeakyReLU'(vol) per voxel, scatters w_k dZ into dP
 // (red.global.add.v4.f32, 256 B rows) and accumulates the bias / relative-depth-column gradients; then
-//   d_feats = dP . Wcat_g  (the same tcgen05 + TMA kernel, K = 2 Cv, N = C) and dWcat_g = dP^T . feats (dense_dw_kernel)
+//   d_feats = dP . Wcat_g  (the same tcgen05 + TMA kernel, K = 2 Cv, N = C) and dWcat_g = dP^T . feats (dense_dw_tc_kernel:
+// tcgen05 with both operands MN-major, TMA-staged)
 // with a fixed-order reduction into d_w_no / d_w_ov.
 #include "gather_common.cuh"
 
@@ -29,13 +30,15 @@ int dense_proj(int n_img, int hw, int K, int N, int cams, const int* group, cons
                const float* Whi, const float* Wlo, cudaStream_t st);
 int dense_dw_slabs(int n_img);
 size_t dense_dw_part_floats(int n_img, int C, int N2);
-int dense_dw(int n_img, int hw, int C, int N2, const float* dP, const float* feats, float* part, cudaStream_t st);
+int dense_dw(int n_img, int hw, int C, int N2, int cams, const int* group, const float* dP, const float* feats, float* part,
+             int* n_parts, int* split, cudaStream_t st);
 __global__ void wcat_prep_kernel(const float* __restrict__ w_no, const float* __restrict__ w_ov, int C, int Cv,
                                  int transpose, float* full, float* hi, float* lo);
 
 constexpr int kFgWarps = 8, kFgThreads = kFgWarps * VFD_WARP;
 constexpr int kFgMaxCv = 64;
 constexpr int kFgCtasPerSm = 8;
+constexpr int kFgRun = 64;          // consecutive voxels one warp of the gather kernel walks
 
 struct FuseArgs {
     vfd_fusion_desc d;
@@ -97,8 +100,11 @@ __global__ void __launch_bounds__(kFgThreads) voxel_fuse_gather_kernel(const Fus
     const bool chan = q4 < Cv;
     const size_t rows = (size_t)d.B * d.X * d.Y * d.Z;
     const CornerTable tb = carve_table(const_cast<void*>(a.table), rows);
-    const size_t stride = (size_t)gridDim.x * kFgWarps * vpw;
-    for (size_t v = ((size_t)blockIdx.x * kFgWarps + warp) * vpw + sub; v < rows; v += stride) {
+    // neighbouring voxels (x fastest) project to neighbouring pixels and share bilinear corners: a warp walks a run of
+    // kFgRun consecutive voxels, the CTA a block of kFgWarps runs, so the shared rows of P are served by L1
+    const size_t v0 = ((size_t)blockIdx.x * kFgWarps + warp) * kFgRun;
+    const size_t v1 = v0 + kFgRun < rows ? v0 + kFgRun : rows;
+    for (size_t v = v0 + sub; v < v1; v += vpw) {
         const int cnt = __ldg(a.count + v);
         float4 acc = f4_zero();
         if ((cnt == 1 || cnt == 2) && chan) {
@@ -197,41 +203,45 @@ __global__ void __launch_bounds__(kFgThreads) voxel_fuse_scatter_kernel(const Fu
     }
 }
 
-// d_w_no [Cv][C1], d_b_no [Cv], d_w_ov [Cv][2 C1], d_b_ov [Cv] from the dense partial products (dense_dw_kernel: one
-// [2 Cv][C] block per (image, slab)) and the scatter kernel's per-CTA bias / depth-column sums, added in a fixed order.
+// d_w_no [Cv][C1], d_b_no [Cv], d_w_ov [Cv][2 C1], d_b_ov [Cv] from the dense partial products (dense_dw: n_parts blocks
+// [2 Cv][C], each belonging to one overlap group) and the scatter kernel's per-CTA bias / depth-column sums, added in
+// a fixed order.
 struct ReduceArgs {
-    const float* dw_part;   // [n_img][slabs][2 Cv][C]
+    const float* dw_part;   // [n_parts][2 Cv][C]
     const float* sc_part;   // [ctas][5][Cv]
-    int n_img, slabs, ctas, C, Cv, cams;
+    int n_parts, split, slabs, ctas, C, Cv, cams;
     int group[VFD_MAX_CAMS];
     float *d_w_no, *d_b_no, *d_w_ov, *d_b_ov;
 };
 
+__device__ __forceinline__ int part_group(const ReduceArgs& r, int i) {
+    return r.split >= 0 ? (i >= r.split ? 1 : 0) : (r.group[(i / r.slabs) % r.cams] ? 1 : 0);
+}
+
 __global__ void __launch_bounds__(256) voxel_fuse_reduce_kernel(const ReduceArgs r) {
     const int C = r.C, Cv = r.Cv, C1 = C + 1, N2 = 2 * Cv;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n_mat = 2 * N2 * C;            // (group, n, c)
+    const int n_mat = N2 * C;            // (n, c)
     if (i < n_mat) {
-        const int g = i / (N2 * C), rem = i - g * N2 * C, n = rem / C, c = rem - n * C;
-        float acc = 0.f;
-        for (int img = 0; img < r.n_img; ++img) {
-            if ((r.group[img % r.cams] ? 1 : 0) != g) continue;
-            const float* p = r.dw_part + ((size_t)img * r.slabs * N2 + n) * C + c;
-            for (int s = 0; s < r.slabs; ++s) acc += p[(size_t)s * N2 * C];
+        const int n = i / C, c = i - n * C;
+        float acc[2] = {0.f, 0.f};
+        const float* p = r.dw_part + (size_t)n * C + c;
+        if (r.split >= 0) {              // two contiguous runs of blocks: independent loads, many in flight
+#pragma unroll 8
+            for (int k = 0; k < r.split; ++k) acc[0] += p[(size_t)k * n_mat];
+#pragma unroll 8
+            for (int k = r.split; k < r.n_parts; ++k) acc[1] += p[(size_t)k * n_mat];
+        } else {
+            for (int k = 0; k < r.n_parts; ++k) {
+                const float v = p[(size_t)k * n_mat];
+                if (part_group(r, k)) acc[1] += v; else acc[0] += v;
+            }
         }
         if (n >= Cv) {
-            r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + g * C1 + c] = acc;
+            r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + c] = acc[0];
+            r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + C1 + c] = acc[1];
         } else {
-            // W_no serves both camera groups: the thread of group 0 adds group 1's block in the same fixed order
-            if (g == 0) {
-                float acc1 = 0.f;
-                for (int img = 0; img < r.n_img; ++img) {
-                    if (!r.group[img % r.cams]) continue;
-                    const float* p = r.dw_part + ((size_t)img * r.slabs * N2 + n) * C + c;
-                    for (int s = 0; s < r.slabs; ++s) acc1 += p[(size_t)s * N2 * C];
-                }
-                r.d_w_no[(size_t)n * C1 + c] = acc + acc1;
-            }
+            r.d_w_no[(size_t)n * C1 + c] = acc[0] + acc[1];     // W_no serves both camera groups
         }
         return;
     }
@@ -328,7 +338,8 @@ extern "C" int vfd_voxel_fuse_fwd(const vfd_fusion_desc* d, const float* feats, 
     a.d = *d; a.count = count; a.table = table; a.P = P;
     a.w_no = w_no; a.b_no = b_no; a.w_ov = w_ov; a.b_ov = b_ov; a.vol = vol;
     a.lpv = lanes_per_voxel(d->Cv);
-    voxel_fuse_gather_kernel<<<sms * kFgCtasPerSm, kFgThreads, 0, st>>>(a);
+    const size_t n_vox = (size_t)d->B * d->X * d->Y * d->Z;
+    voxel_fuse_gather_kernel<<<(unsigned)((n_vox + kFgWarps * kFgRun - 1) / (kFgWarps * kFgRun)), kFgThreads, 0, st>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
@@ -378,13 +389,14 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
     VFD_CHECK_LAUNCH();
     // d_feats[img, p, :] = dP[img, p, :] . Wcat_g   (K = 2 Cv, N = C; weight planes transposed: [2][C][2 Cv])
     if ((rc = dense_proj(n_img, hw, N2, d->C, d->num_cams, d->group, dP, d_feats, wf, wh, wl, st))) return rc;
-    if ((rc = dense_dw(n_img, hw, d->C, N2, dP, feats, dwp, st))) return rc;
+    int n_parts = 0, split = -1;
+    if ((rc = dense_dw(n_img, hw, d->C, N2, d->num_cams, d->group, dP, feats, dwp, &n_parts, &split, st))) return rc;
     ReduceArgs r = {};
-    r.dw_part = dwp; r.sc_part = scp; r.n_img = n_img; r.slabs = dense_dw_slabs(n_img); r.ctas = ctas;
+    r.dw_part = dwp; r.sc_part = scp; r.n_parts = n_parts; r.split = split; r.slabs = dense_dw_slabs(n_img); r.ctas = ctas;
     r.C = d->C; r.Cv = d->Cv; r.cams = d->num_cams;
     for (int c = 0; c < VFD_MAX_CAMS; ++c) r.group[c] = c < d->num_cams ? d->group[c] : 0;
     r.d_w_no = d_w_no; r.d_b_no = d_b_no; r.d_w_ov = d_w_ov; r.d_b_ov = d_b_ov;
-    const int total = 2 * N2 * d->C + 5 * d->Cv;
+    const int total = N2 * d->C + 5 * d->Cv;
     voxel_fuse_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(r);
     VFD_CHECK_LAUNCH();
     return VFD_OK;

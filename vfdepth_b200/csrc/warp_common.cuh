@@ -69,6 +69,17 @@ __device__ __forceinline__ void warp_ctx_init(WarpCtx& c, const vfd_warp_desc& d
     }
 }
 
+// Pass 1 -> pass 2 scratch ("raw"): one float4 (r, g, b, warp mask) per pixel and warp, [B,n_call,NW,H*W], followed by
+// one validity byte per pixel, [B,n_call,H*W]: bit j set <=> warp j's float4 at this pixel is not all-zero.  Only those
+// float4 are written and read back -- a spatial / spatio-temporal warp leaves the neighbour camera's image for most
+// pixels of the target (zeros padding, mask 0), so ~2/3 of the buffer is never touched.
+__host__ __device__ inline size_t warp_raw_f4(const vfd_warp_desc& d) {
+    return (size_t)d.B * d.n_call * (d.n_src + (1 + d.n_src) * VFD_WARP_NBR) * d.H * d.W;
+}
+__host__ __device__ inline size_t warp_raw_bytes(const vfd_warp_desc& d) {
+    return warp_raw_f4(d) * sizeof(float4) + (size_t)d.B * d.n_call * d.H * d.W;
+}
+
 struct WarpSample {
     float v[3];   // bilinear sample of the source image (NaN -> 2.0, view_rendering.py:73-74)
     float m;      // warped mask: in-bounds(strict) * nearest(src mask)   (:70, :77-82)

@@ -17,6 +17,7 @@ struct LossBwdArgs {
     const float* T;
     const float* params;
     const float4* raw;
+    const uint8_t* vbits;
     const float* noise;
     const float* d_num;   // [n_call,3]
     float* d_depth;
@@ -59,6 +60,41 @@ __device__ __forceinline__ float pick5(const float (*v)[3], int k, int c) {
     return r;
 }
 
+// Phase B at ring position r: loss decisions + SSIM derivative coefficients -> coefficient planes.  SP = false: the tile
+// holds no spatial / spatio-temporal warp, the planes of those two sets are zero.
+template <bool SP>
+__device__ __forceinline__ PixelLoss ring_pixel(const float* sm, float* cf, const vfd_warp_desc& d, int x, int y, int ox,
+                                                int oy, int r, float rmask, const float* nz, const float* w_set) {
+    SsimGrad2 g[3];
+    const PixelLoss o = pixel_loss<2, true, SP>(sm, d, x, y, ox, oy, rmask, nz, g);
+    const float wr = w_set[0] * o.automask, ws = SP ? w_set[1] * o.sp_mask : 0.f, wt = SP ? w_set[2] * o.st_mask : 0.f;
+    const bool s1 = o.sel_reproj == 1, t1 = o.sel_st == 1;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
+        q[0] = wr * (s1 ? g[0].a[c].y : g[0].a[c].x);
+        q[Coef::R] = wr * (s1 ? g[0].b[c].y : g[0].b[c].x);
+        q[2 * Coef::R] = wr * (s1 ? g[0].c[c].y : g[0].c[c].x);
+        q += 9 * Coef::R;
+        if (SP) {
+            q[0] = ws * g[2].a[c].x; q[Coef::R] = ws * g[2].b[c].x; q[2 * Coef::R] = ws * g[2].c[c].x;
+            q += 9 * Coef::R;
+            q[0] = wt * (t1 ? g[1].a[c].y : g[1].a[c].x);
+            q[Coef::R] = wt * (t1 ? g[1].b[c].y : g[1].b[c].x);
+            q[2 * Coef::R] = wt * (t1 ? g[1].c[c].y : g[1].c[c].x);
+        } else {      // a later tile of the strip may carry these ring rows over and read them
+            q[0] = 0.f; q[Coef::R] = 0.f; q[2 * Coef::R] = 0.f;
+            q += 9 * Coef::R;
+            q[0] = 0.f; q[Coef::R] = 0.f; q[2 * Coef::R] = 0.f;
+        }
+    }
+    cf[Coef::kWgt + r] = wr;
+    cf[Coef::kWgt + Coef::R + r] = ws;
+    cf[Coef::kWgt + 2 * Coef::R + r] = wt;
+    reinterpret_cast<int*>(cf)[Coef::kSel + r] = (s1 ? 1 : 0) | (t1 ? 2 : 0);
+    return o;
+}
+
 // FUSED: training mode.  One launch evaluates the loss sums (what warp_loss_fwd_kernel computes) AND the gradients with
 // unit upstream, per loss set (every differentiable image belongs to exactly one set: temporal warps -> reprojection,
 // overlap_0 -> spatial, overlap_+-1 -> spatio-temporal); vfd_warp_loss_train_bwd scales them by d total / d num_set once
@@ -70,6 +106,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     __shared__ WarpCtx ctx;
     __shared__ float s_dP[kTileThreads / 32][kMaxW * 12];
     __shared__ double sacc[8];
+    __shared__ unsigned s_flags[2];
     float* sm = vfd_warp_smem;
     float* cf = sm + Rg::kFloats;
     const int b = blockIdx.z / d.n_call, ci = blockIdx.z % d.n_call, cam = d.cam0 + ci;
@@ -83,7 +120,9 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     const int tx0 = blockIdx.x * kTileW, ox = tx0 - 2;
     warp_ctx_init(ctx, d, a.T, a.params, b, ci);
     if (FUSED && threadIdx.x < 8) sacc[threadIdx.x] = 0.0;
+    if (threadIdx.x < 2) s_flags[threadIdx.x] = 0u;
     __syncthreads();
+    unsigned carried = 0u;     // spatial presence in the region rows carried over from the previous tile of the strip
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
     float w_set[3] = {1.f, 1.f, 1.f};
@@ -113,8 +152,14 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         __syncthreads();      // the fill below overwrites the rows that were just read
     }
     for (int i = threadIdx.x; i < (kTileThreads / 32) * kMaxW * 12; i += kTileThreads) (&s_dP[0][0])[i] = 0.f;
-    fill_region<2>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW, sm, cont ? 4 : 0);
-    __syncthreads();
+    const unsigned fl = fill_region<2>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW,
+                                       a.vbits + (size_t)(b * d.n_call + ci) * HW, sm, cont ? 4 : 0);
+    // any spatial / spatio-temporal warp in this tile's region?  (flag words alternate between tiles; the other one is
+    // cleared for the next tile now that every thread is past the previous tile's read of it)
+    const unsigned any = cta_or(fl, &s_flags[tyi & 1]);
+    if (threadIdx.x == 0) s_flags[(tyi + 1) & 1] = 0u;
+    const bool sp = ((any & 1u) | (cont ? carried : 0u)) != 0u;
+    carried = (any >> 1) & 1u;
 
     // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
     for (int r = (cont ? 2 * Coef::RW : 0) + threadIdx.x; r < Coef::R; r += kTileThreads) {
@@ -127,33 +172,15 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
             nz[0] = __ldg(np);
             if (n_src > 1) nz[1] = __ldg(np + HW);
         }
-        SsimGrad2 g[3];
-        const PixelLoss o = pixel_loss<2, true>(sm, d, x, y, ox, oy, __ldg(rmaskp + p), nz, g);
+        const float rm = __ldg(rmaskp + p);
+        const PixelLoss o = sp ? ring_pixel<true>(sm, cf, d, x, y, ox, oy, r, rm, nz, w_set)
+                               : ring_pixel<false>(sm, cf, d, x, y, ox, oy, r, rm, nz, w_set);
         // every ring row is evaluated once per strip: its loss counts here if the row belongs to the strip
         if (FUSED && x >= tx0 && x < tx0 + kTileW && y >= strip_y0 && y < strip_y1) {
             facc[0] += VFD_MUL(o.reproj, o.automask); facc[1] += o.automask;
             facc[2] += VFD_MUL(o.spatial, o.sp_mask); facc[3] += o.sp_mask;
             facc[4] += VFD_MUL(o.st, o.st_mask);      facc[5] += o.st_mask;
         }
-        const float wr = w_set[0] * o.automask, ws = w_set[1] * o.sp_mask, wt = w_set[2] * o.st_mask;
-        const bool s1 = o.sel_reproj == 1, t1 = o.sel_st == 1;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
-            q[0] = wr * (s1 ? g[0].a[c].y : g[0].a[c].x);
-            q[Coef::R] = wr * (s1 ? g[0].b[c].y : g[0].b[c].x);
-            q[2 * Coef::R] = wr * (s1 ? g[0].c[c].y : g[0].c[c].x);
-            q += 9 * Coef::R;
-            q[0] = ws * g[2].a[c].x; q[Coef::R] = ws * g[2].b[c].x; q[2 * Coef::R] = ws * g[2].c[c].x;
-            q += 9 * Coef::R;
-            q[0] = wt * (t1 ? g[1].a[c].y : g[1].a[c].x);
-            q[Coef::R] = wt * (t1 ? g[1].b[c].y : g[1].b[c].x);
-            q[2 * Coef::R] = wt * (t1 ? g[1].c[c].y : g[1].c[c].x);
-        }
-        cf[Coef::kWgt + r] = wr;
-        cf[Coef::kWgt + Coef::R + r] = ws;
-        cf[Coef::kWgt + 2 * Coef::R + r] = wt;
-        reinterpret_cast<int*>(cf)[Coef::kSel + r] = (s1 ? 1 : 0) | (t1 ? 2 : 0);
     }
     __syncthreads();
 
@@ -186,17 +213,19 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
                 for (int c = 0; c < 3; ++c) {
                     const float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
                     const float ra = mult * q[0], rb = mult * q[Coef::R], rc = mult * q[2 * Coef::R];
-                    q += 9 * Coef::R;
-                    const float sa = mult * q[0], sb = mult * q[Coef::R], sc = mult * q[2 * Coef::R];
-                    q += 9 * Coef::R;
-                    const float ta = mult * q[0], tb = mult * q[Coef::R], tc = mult * q[2 * Coef::R];
 #pragma unroll
                     for (int k = 0; k < VFD_WARP_SRC; ++k)
                         if (kr == k) { SA[k][c] += ra; SB[k][c] += rb; SC[k][c] += rc; }
-                    SA[VFD_WARP_SRC][c] += sa; SB[VFD_WARP_SRC][c] += sb; SC[VFD_WARP_SRC][c] += sc;
+                    if (sp) {      // CTA-uniform: the spatial / spatio-temporal planes are all zero otherwise
+                        q += 9 * Coef::R;
+                        const float sa = mult * q[0], sb = mult * q[Coef::R], sc = mult * q[2 * Coef::R];
+                        q += 9 * Coef::R;
+                        const float ta = mult * q[0], tb = mult * q[Coef::R], tc = mult * q[2 * Coef::R];
+                        SA[VFD_WARP_SRC][c] += sa; SB[VFD_WARP_SRC][c] += sb; SC[VFD_WARP_SRC][c] += sc;
 #pragma unroll
-                    for (int k = VFD_WARP_SRC + 1; k < kNPred; ++k)
-                        if (kt == k) { SA[k][c] += ta; SB[k][c] += tb; SC[k][c] += tc; }
+                        for (int k = VFD_WARP_SRC + 1; k < kNPred; ++k)
+                            if (kt == k) { SA[k][c] += ta; SB[k][c] += tb; SC[k][c] += tc; }
+                    }
                 }
             }
         }
@@ -206,6 +235,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         const float wl[3] = {cf[Coef::kWgt + r0], cf[Coef::kWgt + Coef::R + r0], cf[Coef::kWgt + 2 * Coef::R + r0]};
 #pragma unroll
         for (int k = 0; k < kNPred; ++k) {
+            if (!sp && k >= VFD_WARP_SRC) continue;     // dpred stays 0
             // which set's L1 term reaches pred k at this pixel
             float w1;
             if (k < VFD_WARP_SRC) w1 = ((sel0 & 1) == k) ? wl[0] : 0.f;
@@ -228,7 +258,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     }
     float gdepth = 0.f, gset[3] = {0.f, 0.f, 0.f};
     for (int j = 0; j < ctx.NW; ++j) {
-        if (!ctx.active[j]) continue;      // CTA-uniform
+        if (!ctx.active[j] || (!sp && j >= n_src)) continue;      // CTA-uniform
         float dP[12];
 #pragma unroll
         for (int i = 0; i < 12; ++i) dP[i] = 0.f;
@@ -416,6 +446,7 @@ extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, con
     cudaStream_t st = (cudaStream_t)stream;
     LossBwdArgs a = {};
     a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise; a.d_num = d_num;
+    a.vbits = reinterpret_cast<const uint8_t*>(a.raw + warp_raw_f4(*d));
     a.d_depth = d_depth; a.d_T = d_T; a.partial = (float*)ws;
     const size_t smem = bwd_smem_bytes();
     // > 48 KB of dynamic shared memory needs the opt-in; setting it is idempotent and per device, so it is simply
@@ -443,6 +474,7 @@ extern "C" int vfd_warp_loss_train_fwd(const vfd_warp_desc* d, const float* dept
     if (cudaMemsetAsync(sums, 0, (size_t)d->n_call * 8 * sizeof(double), st) != cudaSuccess) return VFD_ERR_CUDA;
     LossBwdArgs a = {};
     a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise;
+    a.vbits = reinterpret_cast<const uint8_t*>(a.raw + warp_raw_f4(*d));
     a.sums = sums; a.g3 = g3; a.partial = (float*)ws;
     const size_t smem = bwd_smem_bytes();
     if (cudaFuncSetAttribute(warp_loss_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
@@ -467,6 +499,7 @@ extern "C" int vfd_warp_loss_train_bwd(const vfd_warp_desc* d, const float* d_nu
     int bx = (d->H * d->W + 1023) / 1024;
     if (bx > 256) bx = 256;
     warp_grad_combine_kernel<<<dim3(bx, d->B * d->n_call), 256, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
     const int tiles = ((d->W + kTileW - 1) / kTileW) * ((d->H + kTileH - 1) / kTileH);
     warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, tiles, true);
     VFD_CHECK_LAUNCH();

@@ -14,6 +14,7 @@ struct LossFwdArgs {
     const float* T;
     const float* params;
     const float4* raw;
+    const uint8_t* vbits;
     const float* noise;
     double* sums;
     vfd_warp_views views;
@@ -27,16 +28,19 @@ __global__ void __launch_bounds__(kTileThreads, 3) warp_loss_fwd_kernel(const Lo
     const vfd_warp_desc& d = a.d;
     __shared__ WarpCtx ctx;
     __shared__ double sacc[8];
+    __shared__ unsigned s_flags;
     float* sm = vfd_warp_smem;
     const int b = blockIdx.z / d.n_call, ci = blockIdx.z % d.n_call, cam = d.cam0 + ci;
     const int W = d.W, H = d.H, HW = H * W, n_src = d.n_src;
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH, ox = tx0 - 1, oy = ty0 - 1;
     warp_ctx_init(ctx, d, a.T, a.params, b, ci);
     if (threadIdx.x < 8) sacc[threadIdx.x] = 0.0;
+    if (threadIdx.x == 0) s_flags = 0u;
     __syncthreads();
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
-    fill_region<1>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW, sm);
-    __syncthreads();
+    const unsigned fl = fill_region<1>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW,
+                                       a.vbits + (size_t)(b * d.n_call + ci) * HW, sm);
+    const bool sp = (cta_or(fl, &s_flags) & 1u) != 0;     // any spatial / spatio-temporal warp in this tile's region?
 
     const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
     float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -49,7 +53,8 @@ __global__ void __launch_bounds__(kTileThreads, 3) warp_loss_fwd_kernel(const Lo
             nz[0] = __ldg(np);
             if (n_src > 1) nz[1] = __ldg(np + HW);
         }
-        const PixelLoss o = pixel_loss<1, false>(sm, d, x, y, ox, oy, rmask, nz, nullptr);
+        const PixelLoss o = sp ? pixel_loss<1, false, true>(sm, d, x, y, ox, oy, rmask, nz, nullptr)
+                               : pixel_loss<1, false, false>(sm, d, x, y, ox, oy, rmask, nz, nullptr);
         acc[0] = VFD_MUL(o.reproj, o.automask); acc[1] = o.automask;
         acc[2] = VFD_MUL(o.spatial, o.sp_mask); acc[3] = o.sp_mask;
         acc[4] = VFD_MUL(o.st, o.st_mask);      acc[5] = o.st_mask;
@@ -117,6 +122,7 @@ extern "C" int vfd_warp_loss_fwd(const vfd_warp_desc* d, const float* depth, con
     if (cudaMemsetAsync(sums, 0, (size_t)d->n_call * 8 * sizeof(double), st) != cudaSuccess) return VFD_ERR_CUDA;
     LossFwdArgs a = {};
     a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise; a.sums = sums;
+    a.vbits = reinterpret_cast<const uint8_t*>(a.raw + warp_raw_f4(*d));
     if (views) { a.views = *views; a.has_views = 1; }
     const size_t smem = Region<1>::kFloats * sizeof(float);
     dim3 grid((d->W + kTileW - 1) / kTileW, (d->H + kTileH - 1) / kTileH, d->B * d->n_call);

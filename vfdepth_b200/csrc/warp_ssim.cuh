@@ -98,7 +98,9 @@ struct SsimGrad2 {
 // Photometric loss 0.85 * mean_c clamp((1 - ssim_c) / 2, 0, 1) + 0.15 * mean_c |t_c - p_c| of the 7 images against
 // the target (loss_util.py:70-78).  img: float2 planes [3 channels][kPairs][plane].  L[q] = losses of pair q
 // (L[3].y, target against itself, is meaningless).  g (GRAD): coefficients for pairs 0..2.
-template <bool GRAD>
+// SP = false: the tile holds no spatial / spatio-temporal warp at all (their images are zero and their masks too), so
+// pair 1 is not evaluated (L[1] = 0, g[1] untouched) -- its losses would be multiplied by a zero mask anyway.
+template <bool GRAD, bool SP = true>
 __device__ __forceinline__ void photometric8(const float2* __restrict__ img, int plane, const int* idx, float2* L,
                                              SsimGrad2* g) {
     float2 ssum[kPairs], lsum[kPairs];
@@ -114,10 +116,11 @@ __device__ __forceinline__ void photometric8(const float2* __restrict__ img, int
         for (int k = 0; k < 9; ++k) {
             float2 x[kPairs];
 #pragma unroll
-            for (int q = 0; q < kPairs; ++q) x[q] = pc[q * plane + idx[k]];
+            for (int q = 0; q < kPairs; ++q) x[q] = (SP || q != 1) ? pc[q * plane + idx[k]] : splat2(0.f);
             const float2 yy = splat2(x[3].y);
 #pragma unroll
             for (int q = 0; q < kPairs; ++q) {
+                if (!SP && q == 1) continue;
                 sx[q] = add2(sx[q], x[q]);
                 sxx[q] = add2(sxx[q], mul2(x[q], x[q]));
                 sxy[q] = add2(sxy[q], mul2(x[q], yy));
@@ -129,6 +132,7 @@ __device__ __forceinline__ void photometric8(const float2* __restrict__ img, int
         const float2 yc = splat2(xc[3].y);
 #pragma unroll
         for (int q = 0; q < kPairs; ++q) {
+            if (!SP && q == 1) continue;
             const float2 mu = div_const2<9>(sx[q]);
             const float2 musq = mul2(mu, mu), mu_xy = mul2(mu, splat2(mu_y));
             const float2 sig_x = sub2(div_const2<9>(sxx[q]), musq);
@@ -163,6 +167,7 @@ __device__ __forceinline__ void photometric8(const float2* __restrict__ img, int
     }
 #pragma unroll
     for (int q = 0; q < kPairs; ++q) {
+        if (!SP && q == 1) { L[q] = splat2(0.f); continue; }
         const float2 s_mean = div_const2<3>(ssum[q]), l_mean = div_const2<3>(lsum[q]);
         L[q] = add2(mul2(splat2(0.85f), s_mean), mul2(splat2(0.15f), l_mean));
     }

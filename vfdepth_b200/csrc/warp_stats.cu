@@ -4,7 +4,8 @@
 // Per (rig, target camera, warp j):  count of pixels with ref_mask*warp_mask != 0, the masked sums of the target
 // and of the warped image, and the UNMASKED sums / sums of squares the reference's variance runs over (:36).
 // The raw warps (r, g, b, mask) are also written out, one float4 per pixel and warp, so that the loss kernels
-// normalise and compare them without projecting and sampling again.
+// normalise and compare them without projecting and sampling again -- but only where they are not all-zero (one
+// validity byte per pixel says which): most pixels of a spatial warp fall outside the neighbour camera's image.
 // Per-thread partial sums are fp32 over a handful of pixels; everything above that (warp, CTA, grid) is fp64, so the
 // one-pass variance  (S2 - 2 m S1 + n m^2) / n  is as accurate as the reference's two-pass form.
 #include "warp_common.cuh"
@@ -21,6 +22,7 @@ struct StatsArgs {
     double* stats;
     float* params;
     float4* raw;   // [B,n_call,NW,H*W] (r, g, b, warp mask) of every warp: read back by the loss kernels
+    uint8_t* vbits;  // [B,n_call,H*W] which of a pixel's warps are not all-zero (only those are stored in raw)
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -67,6 +69,7 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
             atomicAdd(&sacc[0][6], (double)s2);
         }
     }
+    unsigned long long vb = 0ull;      // validity bits of this thread's kStatPx pixels, one byte each
     for (int j = 0; j < NW; ++j) {
         if (!ctx.active[j]) continue;
         float4* raw = a.raw + ((size_t)(b * d.n_call + ci) * NW + j) * HW;
@@ -79,7 +82,10 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
             float X[3];
             vfd_backproject(ctx.invK, (float)u, (float)v, __ldg(depth + p), X);
             const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
-            raw[p] = make_float4(s.v[0], s.v[1], s.v[2], s.m);
+            if (s.v[0] != 0.f || s.v[1] != 0.f || s.v[2] != 0.f || s.m != 0.f) {
+                raw[p] = make_float4(s.v[0], s.v[1], s.v[2], s.m);
+                vb |= 1ull << (8 * k + j);
+            }
             const bool m = (__ldg(rmask + p) * s.m) != 0.f;   // (src_mask * warp_mask).bool()  (:46)
             const float w3 = s.v[0] + s.v[1] + s.v[2];
             sw1 += w3;
@@ -97,6 +103,14 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
             atomicAdd(&sacc[j][2], (double)swm);
             atomicAdd(&sacc[j][3], (double)sw1);
             atomicAdd(&sacc[j][4], (double)sw2);
+        }
+    }
+    {
+        uint8_t* vbits = a.vbits + (size_t)(b * d.n_call + ci) * HW;
+#pragma unroll
+        for (int k = 0; k < kStatPx; ++k) {
+            const int p = p0 + k * kStatThreads;
+            if (p < HW) vbits[p] = (uint8_t)(vb >> (8 * k));
         }
     }
     __syncthreads();
@@ -135,7 +149,10 @@ __global__ void warp_stats_finalize_kernel(const StatsArgs a) {
         p[3] = (float)s_mean;
         p[4] = apply ? 1.f : 0.f;
         p[5] = 1.0f / p[1];
-        p[6] = p[7] = 0.f;
+        // all parameters finite: an all-zero (skipped) raw sample normalises to exactly 0, as the reference's masked
+        // product does; otherwise the loss kernels run the arithmetic so that NaN / Inf propagate as in the reference
+        p[6] = (isfinite(p[0]) && isfinite(p[1]) && isfinite(p[2]) && isfinite(p[3]) && isfinite(p[5])) ? 1.f : 0.f;
+        p[7] = 0.f;
     }
 }
 
@@ -165,7 +182,9 @@ extern "C" int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const 
     const int NW = d->n_src + (1 + d->n_src) * VFD_WARP_NBR;
     if (cudaMemsetAsync(stats, 0, (size_t)d->B * d->n_call * NW * 8 * sizeof(double), st) != cudaSuccess)
         return VFD_ERR_CUDA;
-    StatsArgs a = {*d, depth, T, stats, params, reinterpret_cast<float4*>(raw)};
+    static_assert(kMaxW <= 8, "one validity byte per pixel");
+    StatsArgs a = {*d, depth, T, stats, params, reinterpret_cast<float4*>(raw),
+                   reinterpret_cast<uint8_t*>(reinterpret_cast<float4*>(raw) + warp_raw_f4(*d))};
     const int HW = d->H * d->W, per = kStatThreads * kStatPx;
     dim3 grid((HW + per - 1) / per, d->n_call, d->B);
     warp_stats_kernel<<<grid, kStatThreads, 0, st>>>(a);
@@ -174,4 +193,9 @@ extern "C" int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const 
     warp_stats_finalize_kernel<<<(nt + 63) / 64, 64, 0, st>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
+}
+
+extern "C" size_t vfd_warp_raw_bytes(const vfd_warp_desc* d) {
+    if (check_warp_desc(d)) return 0;
+    return warp_raw_bytes(*d);
 }

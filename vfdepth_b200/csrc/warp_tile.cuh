@@ -53,26 +53,43 @@ __device__ __forceinline__ void warp_slot(int j, int n_src, int R, int omask0, i
 // NSRC (= n_src, 1 or 2) is a template parameter so that the warp -> plane mapping is static: all raw warps and the
 // un-warped images of a pixel are loaded in one batch (8 x 16 B + 9 x 4 B in flight per thread), combined in registers
 // in the reference's order (neighbour k = 0, then 1, view_rendering.py:193-198) and written once.
+// Returns this thread's spatial-presence flags: bit 0 = some pixel it filled has a non-zero spatial / spatio-temporal
+// warp (or such a warp's parameters are not finite), bit 1 = the same restricted to region rows >= kTileH (the rows a
+// strip-walking caller carries over to the next tile).  A tile whose whole region has none skips the overlap images.
 template <int HALO, int NSRC>
-__device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
-                                              const float4* __restrict__ raw, float* sm, int row0) {
+__device__ __forceinline__ unsigned fill_region_n(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
+                                                  const float4* __restrict__ raw, const uint8_t* __restrict__ vbits,
+                                                  float* sm, int row0) {
     using Rg = Region<HALO>;
     constexpr int NWc = NSRC + (1 + NSRC) * VFD_WARP_NBR;
+    constexpr unsigned kSpatialBits = ((1u << NWc) - 1u) & ~((1u << NSRC) - 1u);
     const int W = d.W, H = d.H, HW = H * W, cam = d.cam0 + ci;
     const float* ref = d.color[0] + (size_t)(b * d.num_cams + cam) * 3 * HW;
     const float* src0 = d.color[1] + (size_t)(b * d.num_cams + cam) * 3 * HW;
     const float* src1 = d.color[NSRC] + (size_t)(b * d.num_cams + cam) * 3 * HW;   // == src0 when NSRC == 1 (unused)
     float2* img = reinterpret_cast<float2*>(sm + Rg::kImg);
-    bool act[NWc];
+    // bit j of `live`: warp j exists; bit j of `always`: its parameters are not finite, so even an all-zero sample goes
+    // through the arithmetic (NaN * 0 must stay NaN as in the reference)
+    unsigned live = 0, always = 0;
 #pragma unroll
-    for (int j = 0; j < NWc; ++j) act[j] = ctx.active[j] != 0;
+    for (int j = 0; j < NWc; ++j) {
+        if (ctx.active[j] != 0) {
+            live |= 1u << j;
+            if (ctx.prm[j][6] == 0.f) always |= 1u << j;
+        }
+    }
+    unsigned flags = (always & kSpatialBits) ? 3u : 0u;
     for (int r = row0 * Rg::RW + threadIdx.x; r < Rg::R; r += kTileThreads) {      // rows below row0 are already there
         const int x = ox + r % Rg::RW, y = oy + r / Rg::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
+        const unsigned vb = __ldg(vbits + p);
+        const unsigned use = live & (vb | always);
+        if (vb & kSpatialBits) flags |= (r >= kTileH * Rg::RW) ? 3u : 1u;
         float4 w[NWc];
 #pragma unroll
-        for (int j = 0; j < NWc; ++j) w[j] = act[j] ? __ldg(raw + (size_t)j * HW + p) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < NWc; ++j)
+            w[j] = (live & vb & (1u << j)) ? __ldg(raw + (size_t)j * HW + p) : make_float4(0.f, 0.f, 0.f, 0.f);
         float vr[3], v0[3], v1[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -84,7 +101,7 @@ __device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp
         float tw[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}, cm[2] = {0.f, 0.f};
 #pragma unroll
         for (int j = 0; j < NSRC; ++j) {
-            if (act[j]) {
+            if (use & (1u << j)) {
                 tw[j][0] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].x, w[j].w));
                 tw[j][1] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].y, w[j].w));
                 tw[j][2] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].z, w[j].w));
@@ -93,16 +110,18 @@ __device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp
         }
         // neighbour warps of frame fi, summed over the two neighbours: fi = 0 -> pair 2.x, fi = 1, 2 -> pair 1.x / .y
         float ov[3][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}, om[3] = {0.f, 0.f, 0.f};
+        if (use & kSpatialBits) {
 #pragma unroll
-        for (int fi = 0; fi <= NSRC; ++fi) {
+            for (int fi = 0; fi <= NSRC; ++fi) {
 #pragma unroll
-            for (int k = 0; k < VFD_WARP_NBR; ++k) {
-                const int j = NSRC + fi * VFD_WARP_NBR + k;
-                if (act[j]) {
-                    ov[fi][0] = VFD_ADD(ov[fi][0], warp_normalise(ctx.prm[j], w[j].x, w[j].w));
-                    ov[fi][1] = VFD_ADD(ov[fi][1], warp_normalise(ctx.prm[j], w[j].y, w[j].w));
-                    ov[fi][2] = VFD_ADD(ov[fi][2], warp_normalise(ctx.prm[j], w[j].z, w[j].w));
-                    om[fi] = VFD_ADD(om[fi], w[j].w);
+                for (int k = 0; k < VFD_WARP_NBR; ++k) {
+                    const int j = NSRC + fi * VFD_WARP_NBR + k;
+                    if (use & (1u << j)) {
+                        ov[fi][0] = VFD_ADD(ov[fi][0], warp_normalise(ctx.prm[j], w[j].x, w[j].w));
+                        ov[fi][1] = VFD_ADD(ov[fi][1], warp_normalise(ctx.prm[j], w[j].y, w[j].w));
+                        ov[fi][2] = VFD_ADD(ov[fi][2], warp_normalise(ctx.prm[j], w[j].z, w[j].w));
+                        om[fi] = VFD_ADD(om[fi], w[j].w);
+                    }
                 }
             }
         }
@@ -119,13 +138,23 @@ __device__ __forceinline__ void fill_region_n(const WarpCtx& ctx, const vfd_warp
 #pragma unroll
         for (int f = 0; f < VFD_WARP_SRC; ++f) sm[Rg::kCmask + f * Rg::R + r] = cm[f];
     }
+    return flags;
 }
 
 template <int HALO>
-__device__ __forceinline__ void fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
-                                            const float4* __restrict__ raw, float* sm, int row0 = 0) {
-    if (d.n_src == 2) fill_region_n<HALO, 2>(ctx, d, b, ci, ox, oy, raw, sm, row0);
-    else fill_region_n<HALO, 1>(ctx, d, b, ci, ox, oy, raw, sm, row0);
+__device__ __forceinline__ unsigned fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
+                                                const float4* __restrict__ raw, const uint8_t* __restrict__ vbits,
+                                                float* sm, int row0 = 0) {
+    if (d.n_src == 2) return fill_region_n<HALO, 2>(ctx, d, b, ci, ox, oy, raw, vbits, sm, row0);
+    return fill_region_n<HALO, 1>(ctx, d, b, ci, ox, oy, raw, vbits, sm, row0);
+}
+
+// CTA-wide bitwise OR of every thread's `flags` (one shared word, zeroed by the caller before the previous barrier)
+__device__ __forceinline__ unsigned cta_or(unsigned flags, unsigned* s_word) {
+    const unsigned w = __reduce_or_sync(0xffffffffu, flags);
+    if ((threadIdx.x & 31) == 0 && w) atomicOr(s_word, w);
+    __syncthreads();
+    return *s_word;
 }
 
 // Everything the loss decides at one pixel (single_cam_loss.py:17-55, multi_cam_loss.py:16-59).
@@ -136,8 +165,9 @@ struct PixelLoss {
     int sel_reproj, sel_st;          // which frame won each min (gradient routing)
 };
 
-// g (GRAD): SSIM derivative coefficients of pairs 0..2 (see warp_ssim.cuh)
-template <int HALO, bool GRAD>
+// g (GRAD): SSIM derivative coefficients of pairs 0..2 (see warp_ssim.cuh).  SP = false (no spatial / spatio-temporal
+// warp anywhere in the tile's region): the overlap images and masks are all zero, their terms are exactly zero.
+template <int HALO, bool GRAD, bool SP = true>
 __device__ __forceinline__ PixelLoss pixel_loss(const float* sm, const vfd_warp_desc& d, int x, int y, int ox, int oy,
                                                 float rmask, const float* noise /*[VFD_WARP_SRC]*/, SsimGrad2* g) {
     using Rg = Region<HALO>;
@@ -146,7 +176,7 @@ __device__ __forceinline__ PixelLoss pixel_loss(const float* sm, const vfd_warp_
     tap_indices(x, y, d.W, d.H, ox, oy, Rg::RW, idx);
     const int ctr = (y - oy) * Rg::RW + (x - ox);
     float2 L[kPairs];
-    photometric8<GRAD>(reinterpret_cast<const float2*>(sm + Rg::kImg), Rg::R, idx, L, g);
+    photometric8<GRAD, SP>(reinterpret_cast<const float2*>(sm + Rg::kImg), Rg::R, idx, L, g);
     PixelLoss o;
     // temporal reprojection: torch.min over frames keeps the first minimum on a tie
     o.sel_reproj = (two && L[0].y < L[0].x) ? 1 : 0;
@@ -156,6 +186,12 @@ __device__ __forceinline__ PixelLoss pixel_loss(const float* sm, const vfd_warp_
     if (two) ident = fminf(ident, VFD_ADD(L[3].x, VFD_MUL(0.00001f, noise[1])));
     // argmin over cat([reproj, identity]) == 0: the first minimum wins a tie (loss_util.py:15-17)
     o.automask = VFD_MUL((o.reproj <= ident) ? 1.f : 0.f, rmask);
+    if (!SP) {
+        o.sp_mask = o.st_mask = 0.f;
+        o.spatial = o.st = 0.f;
+        o.sel_st = 0;
+        return o;
+    }
     o.sp_mask = VFD_MUL(rmask, sm[Rg::kOmask + ctr]);
     o.spatial = L[2].x;
     o.sel_st = (two && L[1].y < L[1].x) ? 1 : 0;

@@ -65,16 +65,18 @@ class WarpInputs:
 
 
 def warp_stats(wi, depth, T, cam0=0):
-    """pass 1 -> (params [B,n_call,NW,8], raw [B,n_call,NW,H,W,4]): the intensity-alignment constants (autograd
-    constants: view_rendering.py:45 runs under no_grad) and the raw warps (r, g, b, mask) the loss passes read back."""
+    """pass 1 -> (params [B,n_call,NW,8], raw): the intensity-alignment constants (autograd constants:
+    view_rendering.py:45 runs under no_grad) and the scratch the loss passes read back -- the raw warps (r, g, b, mask)
+    [B,n_call,NW,H,W,4] followed by one validity byte per pixel [B,n_call,H,W] (only warps that are not all-zero at a
+    pixel are stored and re-read; vfd_warp_raw_bytes)."""
     n_call = depth.shape[1]
     NW = num_warps(wi.n_src)
     _chk(depth, 'depth', (wi.B, n_call, wi.H, wi.W))
     _chk(T, 'T', (wi.B, n_call, NW, 4, 4))
     stats = torch.empty((wi.B, n_call, NW, 8), device=wi.device, dtype=torch.float64)
     params = torch.empty((wi.B, n_call, NW, 8), device=wi.device, dtype=torch.float32)
-    raw = torch.empty((wi.B, n_call, NW, wi.H, wi.W, 4), device=wi.device, dtype=torch.float32)
     d = wi.desc(cam0, n_call)
+    raw = torch.empty((_lib.load().vfd_warp_raw_bytes(ctypes.byref(d)),), device=wi.device, dtype=torch.uint8)
     _lib.call('vfd_warp_stats', ctypes.byref(d), _lib.ptr(depth), _lib.ptr(T), _lib.ptr(stats), _lib.ptr(params),
               _lib.ptr(raw), _stream())
     return params, raw
