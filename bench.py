@@ -1,16 +1,26 @@
-"""bench.py -- rigs/second of the VFDepth fusion (+ view-synthesis) hot path on B200.
+"""bench.py -- rigs/second of the VFDepth fusion + view-synthesis hot path on B200.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 ... bench.py --gpus N ...
 
-One step = one pass of the hot path, forward AND backward, over one batch of synthetic DDAD-shaped rigs
-(BASELINE.json configs[1]: 8 rigs of 6 cameras, 384x640 images -> 48x80x256 feature maps, 100x100x20 voxels,
-50 depth bins): VFNet.backproject_into_voxel (voxel gather kernel + the two 1x1 MLPs, which stay cuBLAS) ->
-project_voxel_into_image without reduce_dim (ray-sampling kernel) -> backward of both with a resident upstream
-gradient; then, when built, the 6-camera x 3-frame view-synthesis warp + SSIM/L1 loss forward+backward.
-Every rank owns whole rigs (weak scaling, no data-path collective); value = rigs all ranks processed / max-over-
-ranks device time.  The JSON line also carries the roofline of the dominant kernel, the CPU baseline (the oracle =
-the reference's own torch ops on the host cores) and the end-to-end number with host buffers.
+Headline (`value`, BASELINE.json configs[1] + configs[2]).  One step = one pass of the hot path, forward AND backward,
+over one batch of synthetic DDAD-shaped rigs (8 rigs of 6 cameras, 384x640 images -> 48x80x256 feature maps,
+100x100x20 voxels, 50 depth bins): VFNet.backproject_into_voxel (voxel classification, the two 1x1 MLPs as a dense
+tcgen05 projection of the feature pixels, voxel gather) -> project_voxel_into_image without reduce_dim (ray sampling) ->
+backward of both with a resident upstream gradient; then to_depth + the 6-camera x 3-frame view-synthesis warp + SSIM/L1
++ smoothness loss forward+backward.  Every rank owns whole rigs (weak scaling, no data-path collective); value = rigs all
+ranks processed / max-over-ranks device time.
+
+The same JSON line also carries
+  roofline / rooflines   the two calls with the most time per step against the measured HBM peak
+  e2e                    the same step fed from pinned host buffers (uint8 images, as datasets store them)
+  full_step              + what a reference step runs around the headline: the two pose-network gathers with the BEV
+                         hand-off, and the reduce_dim convolutions (cuDNN) of the depth and pose VFNets, timed apart
+  train_step             BASELINE.json configs[3]/[4]: the chained nuScenes-shaped fusion-depth training step (two pose
+                         forwards, depth forward, to_depth, warp + losses, one backward, Adam) under
+                         DistributedDataParallel when N > 1 -- the one collective of the path, inside the timed step
+  torch_cuda_baseline    the reference's own torch ops (the oracle) on the same B200 with the reference's flags
+  cpu_baseline           the same ops on the host cores: all cores, and 1 thread (the reference launcher's setting)
 """
 import argparse
 import json
@@ -30,8 +40,8 @@ if ROOT not in sys.path:
 METRIC = 'vfnet_fusion_warp_fwd_bwd_rigs_per_sec'
 UNIT = 'rigs/s'
 BATCH = 8                 # rigs per GPU per step (configs[1])
-WORKLOAD = ('configs[1]: VFNet fusion fwd+bwd (voxel gather + 1x1 MLPs + ray sampling, no reduce_dim)%s, %d DDAD-shaped '
-            'rigs (6x384x640) per GPU per step')
+WORKLOAD = ('configs[1]: VFNet fusion fwd+bwd (voxel classification + 1x1 MLPs + voxel gather + ray sampling, no reduce_dim)%s, '
+            '%d DDAD-shaped rigs (6x384x640) per GPU per step')
 WARP_PART = ' + configs[2]: to_depth + 6-cam x 3-frame view-synthesis warp + SSIM/L1 photometric + smoothness loss fwd+bwd (to disparity and poses)'
 DATASET = 'ddad'
 
@@ -47,6 +57,7 @@ def parse():
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='launch the resident step eagerly instead of replaying a CUDA graph')
     ap.add_argument('--no-warp', action='store_true', help='time the fusion half only')
+    ap.add_argument('--no-extras', action='store_true', help='headline only: no full_step / train_step / torch_cuda_baseline')
     return ap.parse_args()
 
 
@@ -188,19 +199,17 @@ class FusionWorkload:
         msk = B * g.num_cams * g.h * g.w * 4
         vol = B * g.N * g.Cv * 4
         ray = B * g.num_cams * g.h * g.w * g.Cv * g.D * 4
-        # compact GEMM rows: one (C+1)-float row per voxel seen by exactly one camera, one 2(C+1)-float row per voxel
-        # seen by exactly two (data dependent; read from the last classification).  Backward reads the same rows.
+        # corner table: 40 bytes per (voxel, camera) entry of the voxels seen by exactly one / exactly two cameras
+        # (data dependent; read from the last classification), written once, read by the forward and the backward
         cnt = self.net.last_count
         m1 = int((cnt == 1).sum()) if cnt is not None else B * g.N
         m2 = int((cnt == 2).sum()) if cnt is not None else B * g.N
-        rows = (m1 + 2 * m2) * (g.C + 1) * 4
-        table = (m1 + 2 * m2) * 40          # corner table: 40 bytes per (voxel, camera) entry, written once, read per pass
-        classify = msk + B * g.N * (1 + 4) + (m1 + m2) * 8 + table + m1 * 8
-        return {'vfd_voxel_gather_depth_compact_fwd': feats + msk + rows,
-                'vfd_voxel_gather_depth_compact_bwd': feats + msk + rows, 'vfd_voxel_classify': classify,
-                # fused gather + MLPs: the rows never reach HBM.  fwd: features in, volume out;
-                # bwd: features + volume + its gradient in, feature gradient out
-                'vfd_voxel_fuse_fwd': feats + table + vol, 'vfd_voxel_fuse_bwd': 2 * feats + table + 2 * vol,
+        table = (m1 + 2 * m2) * 40
+        return {'vfd_voxel_classify': msk + B * g.N + table,
+                # fused gather + MLPs: neither the GEMM rows nor the projected pixels reach HBM as
+                # required traffic.  fwd: features + table + count in, volume out; bwd: features + volume + its gradient
+                # + table in, feature gradient out
+                'vfd_voxel_fuse_fwd': feats + table + B * g.N + vol, 'vfd_voxel_fuse_bwd': 2 * feats + table + B * g.N + 2 * vol,
                 'vfd_ray_sample_fwd': vol + ray, 'vfd_ray_sample_bwd': vol + ray}
 
 
@@ -226,18 +235,16 @@ def timed(fn, steps, world):
 
 
 # --------------------------------------------------------------------------------------------------
-# CPU baseline / reference arm: the reference's own torch path (the oracle) on the host cores
+# baselines: the reference's own torch path (the oracle, bit-identical to the reference on the CPU --
+# tests/test_oracle_golden.py) on the host cores or on the GPU
 # --------------------------------------------------------------------------------------------------
-def cpu_step_pass(steps, warmup, seed=1234, with_warp=True):
-    """One rig per step through the oracle (bit-identical to the reference on CPU, tests/test_oracle_golden.py):
-    fusion forward+backward (gather + 1x1 MLPs + ray sampling) and, with ``with_warp``, the 6-camera x 3-frame warp +
-    SSIM/L1 loss forward+backward.  -> (rigs/s, cores, seconds per rig)."""
+def reference_step(batch, device, seed=1234, with_warp=True):
+    """-> a closure running one step (fusion fwd+bwd + warp/loss fwd+bwd of `batch` rigs) through the oracle on
+    `device`; the rigs are drawn once, outside the timed region."""
     from oracle import vfdepth_oracle as orc
     from vfdepth_b200 import config as vcfg
     from vfdepth_b200.rig import make_rig
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    cfg = vcfg.default_config(DATASET, batch_size=1)
+    cfg = vcfg.default_config(DATASET, batch_size=batch)
     inputs, extras = make_rig(cfg, seed=seed, with_images=with_warp)
     lvl = cfg['model']['fusion_level'] + 1
     C, Cv = cfg['model']['fusion_feat_in_dim'], cfg['model']['voxel_pre_dim'][-1]
@@ -245,41 +252,95 @@ def cpu_step_pass(steps, warmup, seed=1234, with_warp=True):
     mlp = dict(w_no=torch.randn((Cv, C + 1, 1), generator=gen) * 0.05, b_no=torch.zeros(Cv),
                w_ov=torch.randn((Cv, 2 * (C + 1), 1), generator=gen) * 0.05, b_ov=torch.zeros(Cv))
     h, w = orc.feature_hw(cfg)
-    g_up = torch.randn((1, Cv * cfg['model']['proj_d_bins'], h, w), generator=gen)
+    g_up = torch.randn((batch, Cv * cfg['model']['proj_d_bins'], h, w), generator=gen)
+    to = lambda t: t.to(device)
+    inputs = {k: to(v) for k, v in inputs.items()}
+    feats = to(extras['feats_agg'])
+    mlp = {k: to(v) for k, v in mlp.items()}
+    g_up = to(g_up)
+    if with_warp:
+        disp0 = [to(d) for d in extras['disp']]
+        T0 = {k: to(v) for k, v in extras['cam_T_cam'].items()}
+        noise = [to(n) for n in extras['noise']]
 
     def one():
-        f = extras['feats_agg'].clone().requires_grad_(True)
+        f = feats.clone().requires_grad_(True)
         p = {k: v.clone().requires_grad_(True) for k, v in mlp.items()}
-        vox = orc.backproject_into_voxel(cfg, f, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'],
-                                         'depth', p)
+        vox = orc.backproject_into_voxel(cfg, f, inputs['mask'], inputs[('K', lvl)], inputs['extrinsics_inv'], 'depth', p)
         proj = orc.project_voxel_into_image(cfg, vox, inputs[('inv_K', lvl)], inputs['extrinsics'])
         torch.autograd.backward(proj, [g_up] * len(proj))
         if with_warp:
-            disps = [d.clone().requires_grad_(True) for d in extras['disp']]
+            disps = [d.clone().requires_grad_(True) for d in disp0]
             depths = [orc.to_depth(cfg, d, inputs[('K', 0)][:, c]) for c, d in enumerate(disps)]
-            Ts = {k: v.clone().requires_grad_(True) for k, v in extras['cam_T_cam'].items()}
-            total, _ = orc.warp_and_loss(cfg, inputs, depths, disps, Ts, extras['noise'])
+            Ts = {k: v.clone().requires_grad_(True) for k, v in T0.items()}
+            total, _ = orc.warp_and_loss(cfg, inputs, depths, disps, Ts, noise)
             torch.autograd.grad(total, disps + list(Ts.values()))
         return f.grad
 
-    for _ in range(warmup):
-        one()
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        one()
-    dt = time.perf_counter() - t0
-    return steps / dt, cores, dt / steps
+    return one
+
+
+def cpu_step_pass(steps, warmup, threads=None, with_warp=True):
+    """One rig per step through the oracle on the host cores.  -> (rigs/s, threads, seconds per rig)."""
+    cores = os.cpu_count() or 1
+    threads = cores if threads is None else threads
+    prev = torch.get_num_threads()
+    torch.set_num_threads(threads)
+    try:
+        one = reference_step(1, torch.device('cpu'), with_warp=with_warp)
+        for _ in range(warmup):
+            one()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            one()
+        dt = time.perf_counter() - t0
+    finally:
+        torch.set_num_threads(prev)
+    return steps / dt, threads, dt / steps
+
+
+def torch_cuda_pass(batch, dev, with_warp=True):
+    """The 'reference torch path on the same B200' of BASELINE.json configs[1]: the reference's ATen calls (the oracle) on
+    cuda with /root/reference/train.py:23-25's flags, CUDA-event timed.  -> dict (or an 'unavailable' note)."""
+    flags = (torch.backends.cudnn.deterministic, torch.backends.cudnn.benchmark, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.deterministic, torch.backends.cudnn.benchmark = True, False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        for b in (batch, 2, 1):
+            try:
+                one = reference_step(b, dev, with_warp=with_warp)
+                one()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                n = 3
+                e0.record()
+                for _ in range(n):
+                    one()
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / n
+                return {'value': b / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms, 'rigs_per_step': b,
+                        'how': 'the reference\'s torch ops (oracle/vfdepth_oracle.py = network/volumetric_fusionnet.py, '
+                               'models/geometry, models/losses) on cuda:0, cudnn.deterministic=True, benchmark=False, '
+                               'matmul.allow_tf32=False (train.py:23-25), 1 warm-up + %d timed steps, CUDA events' % n}
+            except torch.cuda.OutOfMemoryError:
+                one = None
+                torch.cuda.empty_cache()
+        return {'unavailable': 'out of memory at every batch size tried'}
+    finally:
+        torch.backends.cudnn.deterministic, torch.backends.cudnn.benchmark = flags[0], flags[1]
+        torch.backends.cuda.matmul.allow_tf32 = flags[2]
+        torch.cuda.empty_cache()
 
 
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    steps, warmup = max(1, args.steps), max(1, min(args.warmup, 2))
-    steps = min(steps, 6)               # ~5-15 s per rig on a many-core host: keep the arm within minutes
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
     rps, cores, sec = cpu_step_pass(steps, warmup, with_warp=not args.no_warp)
-    sample = ('fusion fwd+bwd (gather + 1x1 MLPs + ray sampling, no reduce_dim)%s of 1 DDAD rig per step, %d steps, '
-              'reference torch ops on %d host threads' % ('' if args.no_warp else ' + 6-cam x 3-frame warp + SSIM/L1 loss fwd+bwd', steps, cores))
+    sample = ('fusion fwd+bwd (gather + 1x1 MLPs + ray sampling, no reduce_dim)%s of 1 DDAD rig per step, %d warm-up + %d '
+              'timed steps, reference torch ops on %d host threads' % ('' if args.no_warp else ' + 6-cam x 3-frame warp + SSIM/L1 loss fwd+bwd', warmup, steps, cores))
     line = {'impl': 'reference', 'metric': METRIC, 'value': rps, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
             'warmup': warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
@@ -289,6 +350,113 @@ def run_reference(args):
             'e2e': {'value': rps, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# extras: what a reference step runs around the headline, and the chained training step
+# --------------------------------------------------------------------------------------------------
+def _event_ms(fn, iters):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def full_step_pass(wl, headline_ms, iters):
+    """SURVEY.md 8d config 2 asks for the geometry core and reduce_dim apart, and a reference step does three voxel
+    gathers (one depth + two pose, network/fusion_posenet.py:70 via models/geometry/pose.py:32-41): time the two pose
+    gathers with the BEV hand-off (fwd+bwd), the pose reduce_dim (fwd+bwd, cuDNN) and the depth reduce_dim over the ray
+    samples (fwd+bwd, cuDNN) on the same rigs."""
+    from vfdepth_b200.vfnet import VFNet
+    dev, B, g = wl.dev, wl.B, wl.g
+    torch.manual_seed(7)
+    pose = VFNet(wl.cfg, g.C, 128, 'pose').to(dev)
+    feats = [torch.randn_like(wl.feats) for _ in range(2)]                      # the two pose encoders' feature maps
+    s = wl.small
+    out = {}
+    with torch.no_grad():
+        bev0 = pose.bev_rows(feats[0].permute(0, 1, 4, 2, 3), s['mask'], s['K'], s['extrinsics_inv'])
+    g_bev = torch.randn_like(bev0)
+
+    def pose_gathers():
+        for f in feats:
+            x = f.permute(0, 1, 4, 2, 3).requires_grad_(True)
+            rows = pose.bev_rows(x, s['mask'], s['K'], s['extrinsics_inv'])
+            torch.autograd.backward(rows, g_bev)
+
+    def pose_reduce():
+        for _ in feats:
+            x = bev0.detach().requires_grad_(True)
+            y = pose.reduce_bev(x)
+            y.sum().backward()
+
+    rows0, _ = wl.step_resident()
+    rows0 = rows0.detach()
+
+    def depth_reduce():
+        x = rows0.requires_grad_(True)
+        Bc, n, h, w, D, cv = x.shape
+        xi = x.view(Bc * n, h, w, D * cv).permute(0, 3, 1, 2)
+        conv0 = wl.net.reduce_dim[0]
+        w0 = conv0.weight.view(conv0.out_channels, cv, D, 3, 3).permute(0, 2, 1, 3, 4).reshape(conv0.out_channels, D * cv, 3, 3)
+        y = torch.nn.functional.conv2d(torch.nn.functional.pad(xi, (1, 1, 1, 1), mode='reflect'), w0, conv0.bias)
+        for layer in list(wl.net.reduce_dim)[1:]:
+            y = layer(y)
+        y.sum().backward()
+        x.grad = None
+
+    for name, fn in (('pose_gathers_2x_fwd_bwd_ms', pose_gathers), ('reduce_dim_pose_2x_fwd_bwd_ms', pose_reduce),
+                     ('reduce_dim_depth_fwd_bwd_ms', depth_reduce)):
+        fn()
+        out[name] = _event_ms(fn, iters)
+    out['hot_path_ms'] = headline_ms
+    out['geometry_core_ms'] = headline_ms + out['pose_gathers_2x_fwd_bwd_ms']
+    out['rigs_per_s_geometry_core'] = B / (out['geometry_core_ms'] * 1e-3)
+    total = out['geometry_core_ms'] + out['reduce_dim_pose_2x_fwd_bwd_ms'] + out['reduce_dim_depth_fwd_bwd_ms']
+    out['ms_per_step'] = total
+    out['rigs_per_s'] = B / (total * 1e-3)
+    pose_bytes = 2 * 2 * (B * g.num_cams * g.h * g.w * g.C * 4 + B * g.N * (g.C + 1) * 4)
+    out['pose_gathers_frac_of_hbm_peak'] = pose_bytes / (out['pose_gathers_2x_fwd_bwd_ms'] * 1e-3) / 1e9 / measured_peak()[0]
+    out['what'] = ('headline hot path + the two pose-network voxel gathers with the BEV hand-off (geometry core), + reduce_dim of '
+                   'the pose VFNet (2x) and of the depth VFNet over the ray samples -- cuDNN convolutions that stay torch '
+                   '(SURVEY.md 8a A6), timed separately, per GPU, %d rigs' % B)
+    del pose, feats, bev0, g_bev, rows0
+    torch.cuda.empty_cache()
+    return out
+
+
+def train_step_pass(dev, rank, world, steps):
+    """BASELINE.json configs[3] (nuScenes-shaped full fusion-depth training step, random init, B=2 per GPU as
+    configs/nuscenes/nusc_surround_fusion.yaml:47) and configs[4] (the same under DDP: the gradient all-reduce of every
+    parameter over NCCL/NVLink inside the timed step, no per-step barrier).  Encoders / decoders are stand-ins
+    (vfdepth_b200/train_step.py) -- they are outside the hot path."""
+    from vfdepth_b200 import config as vcfg
+    from vfdepth_b200 import train_step as ts
+    from vfdepth_b200.rig import make_rig
+    B = 2
+    cfg = vcfg.default_config('nuscenes', batch_size=B)
+    inputs, _ = make_rig(cfg, seed=4321 + 1000 * rank, with_feats=False)
+    inputs = {k: v.to(dev) for k, v in inputs.items()}
+    step = ts.TrainStep(cfg, dev, ddp=world > 1, seed=11)
+    for _ in range(3):
+        step.step(inputs)
+    n = max(3, min(steps, 10))
+    ms = timed(lambda: step.step(inputs), n, world) / n
+    out = {'value': B * world / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms, 'rigs_per_step_per_gpu': B, 'steps': n,
+           'n_gpus': world, 'dataset_shape': 'nuScenes 6 x 352 x 640, 44 x 80 x 256 features, 100 x 100 x 20 voxels',
+           'param_grad_bytes': step.grad_bytes(),
+           'collective': ('DistributedDataParallel over NCCL: %d bytes of parameter gradients (encoders, 1x1 aggregation, VFNet '
+                          'MLPs + reduce_dim of both networks, decoders) all-reduced per step in 25 MB buckets overlapped with '
+                          'the backward; no per-step barrier' % step.grad_bytes()) if world > 1 else 'none (single GPU)',
+           'what': 'two pose-network forwards + depth-network forward + to_depth + rig-level warp/loss + one backward + Adam; '
+                   'stand-in encoders / decoders (out of scope), everything between them on the CUDA kernels'}
+    del step
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_ours(args):
@@ -308,11 +476,8 @@ def run_ours(args):
     wl = FusionWorkload(args.batch, dev, seed=1234 + 1000 * rank)
     warp = None
     if not args.no_warp:
-        try:
-            from vfdepth_b200.bench_warp import WarpWorkload
-            warp = WarpWorkload(args.batch, dev, seed=1234 + 1000 * rank)
-        except ImportError:
-            warp = None
+        from vfdepth_b200.bench_warp import WarpWorkload
+        warp = WarpWorkload(args.batch, dev, seed=1234 + 1000 * rank)
 
     def step():
         wl.step_resident()
@@ -416,8 +581,24 @@ def run_ours(args):
         d2h = wl.d2h_bytes() + (warp.d2h_bytes() if warp else 0)
         e2e = {'value': rigs / (ms_e2e * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                'ms_per_step': ms_e2e / args.steps,
-               'how': 'pinned host buffers; H2D of step i+1 on a copy stream while step i computes, D2H on a third stream'}
+               'how': 'pinned host buffers; H2D of step i+1 on a copy stream while step i computes, D2H on a third stream. '
+                      'Images travel as uint8 (what every dataset stores) and are converted on the device inside the timed '
+                      'region; %d of the H2D bytes are the fp32 feature maps, which stand in for an encoder that lives on '
+                      'the device in training (they never exist on the host there)' % (wl.h_feats.numel() * 4)}
     clocks = sampler.stop() if rank == 0 else None
+
+    extras = {}
+    if not args.no_extras:
+        del run_step
+        torch.cuda.empty_cache()
+        full = full_step_pass(wl, ms / args.steps, max(2, min(args.steps, 5)))
+        if rank == 0:
+            extras['full_step'] = full
+        wl.g_up = None
+        torch.cuda.empty_cache()
+        tr = train_step_pass(dev, rank, world, args.steps)
+        if rank == 0:
+            extras['train_step'] = tr
 
     if rank == 0:
         peak, how = measured_peak()
@@ -434,28 +615,47 @@ def run_ours(args):
                 k['frac_of_hbm_peak'] = k['gbs'] / peak
             kernels[name] = k
         ours_ms = sum(k['ms_per_step'] for k in kernels.values())
-        dom = max(kernels, key=lambda n: kernels[n]['ms_per_step'])
-        roof = {'bound': 'hbm', 'kernel': dom, 'achieved': kernels[dom].get('gbs'), 'peak': peak, 'unit': 'GB/s',
-                'frac': kernels[dom].get('frac_of_hbm_peak'), 'traffic': None, 'peak_source': how,
-                'algorithmic_bytes_per_launch': alg.get(dom), 'ms_per_launch': kernels[dom]['ms_per_launch']}
+        traffic = {}
         tpath = os.path.join(ROOT, 'profiles', 'traffic.json')
         if os.path.isfile(tpath):
             with open(tpath) as f:
-                roof['traffic'] = json.load(f).get(dom)
+                traffic = json.load(f)
+
+        def roof(name):
+            return {'bound': 'hbm', 'kernel': name, 'achieved': kernels[name].get('gbs'), 'peak': peak, 'unit': 'GB/s',
+                    'frac': kernels[name].get('frac_of_hbm_peak'), 'traffic': traffic.get(name), 'peak_source': how,
+                    'algorithmic_bytes_per_launch': alg.get(name), 'ms_per_launch': kernels[name]['ms_per_launch'],
+                    'share_of_step': kernels[name]['ms_per_step'] / ours_ms}
+
+        ranked = sorted(kernels, key=lambda n: -kernels[n]['ms_per_step'])
+        step_alg = sum(alg.get(n, 0) * kernels[n]['launches_per_step'] for n in kernels)
         line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
                 'warmup': max(3, args.warmup), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
                 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
                 'config': {'workload': WORKLOAD % (WARP_PART if warp else '', args.batch),
                            'rigs_per_step_per_gpu': args.batch, 'l2': 'inputs and outputs larger than L2 '
-                           '(189 MB feature maps, 1.7 GB compact gather rows, 2.4 GB ray samples per step)',
+                           '(189 MB feature maps, 410 MB voxel volume, 2.4 GB ray samples, 0.6 GB of images per step)',
                            'sharding': 'whole rigs per rank, no data-path collective', 'host_affinity': numa, 'cuda_graph': graphed,
                            'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms},
-                'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof, 'kernels': kernels}
+                'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof(ranked[0]),
+                'rooflines': [roof(n) for n in ranked[:2]],
+                'step_roofline': {'algorithmic_bytes_per_step': step_alg, 'frac_of_hbm_peak': step_alg / (ms / args.steps) / 1e6 / peak},
+                'kernels': kernels}
+        line.update(extras)
+        if world == 1 and not args.no_extras:
+            tc = torch_cuda_pass(args.batch, dev, with_warp=warp is not None)
+            line['torch_cuda_baseline'] = tc
+            if 'value' in tc:
+                line['vs_torch_cuda'] = value / tc['value']
         if world == 1 and not args.no_cpu_baseline:
             rps, cores, sec = cpu_step_pass(2, 1, with_warp=warp is not None)
             line['cpu_baseline'] = {'value': rps, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                                     'sample': 'the same step (fusion%s fwd+bwd) of 1 DDAD rig through the oracle (reference '
                                               'torch ops), 1 warm-up + 2 timed, %.1f s per rig' % (' + warp/loss' if warp is not None else '', sec)}
+            # the reference launcher pins OMP / MKL / NUMEXPR to ONE thread (train.py:17-20): that number too
+            rps1, _, sec1 = cpu_step_pass(1, 0, threads=1, with_warp=warp is not None)
+            line['cpu_baseline']['one_thread'] = {'value': rps1, 'unit': UNIT, 'cores': 1,
+                                                  'sample': 'the same step, 1 rig, 1 timed step without warm-up, %.1f s' % sec1}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -131,7 +131,7 @@ def backproject_into_voxel(cfg, feats_agg, input_mask, K, E_inv, model='depth', 
     """
     B = feats_agg.shape[0]
     ncam = cfg['data']['num_cams']
-    vox = voxel_points(cfg, B).to(feats_agg.dtype)
+    vox = voxel_points(cfg, B).to(device=feats_agg.device, dtype=feats_agg.dtype)   # the reference's type_check (:105-114)
     cams = [gather_camera(cfg, feats_agg[:, c], input_mask[:, c], K[:, c], E_inv[:, c], vox) for c in range(ncam)]
     feats = [c['feat'] for c in cams]
     count = torch.sum(torch.cat([c['valid'] for c in cams], dim=1), dim=1, keepdim=True)
@@ -171,14 +171,15 @@ def backproject_into_voxel(cfg, feats_agg, input_mask, K, E_inv, model='depth', 
 # A5  ray sampling               (:232-262, without the reduce_dim convs of :265)
 # --------------------------------------------------------------------------------------
 def ray_grid(cfg, inv_K, E, batch, dtype=torch.float32):
+    # constant grids are built on the CPU and moved, as the reference's type_check (:105-114) does
     """one camera: normalised 3-D sampling grid [B,D,h,w,3] -- :245-260."""
     m = cfg['model']
     h, w = feature_hw(cfg)
     P, D = h * w, m['proj_d_bins']
-    pix = pixel_grid(batch, h, w).to(dtype)
-    bins = depth_bins(cfg).to(dtype)
+    pix = pixel_grid(batch, h, w).to(device=inv_K.device, dtype=dtype)
+    bins = depth_bins(cfg).to(device=inv_K.device, dtype=dtype)
     dgrid = bins.view(1, 1, D, 1).expand(batch, 3, D, P)
-    ones = torch.ones(batch, 1, D, P, dtype=dtype)
+    ones = torch.ones(batch, 1, D, P, dtype=dtype, device=inv_K.device)
     cam = torch.matmul(inv_K[:, :3, :3], pix)
     cam = dgrid * cam.view(batch, 3, 1, P)
     cam = torch.cat([cam, ones], dim=1).view(batch, 4, -1)
@@ -221,7 +222,7 @@ def reproject_grid(depth, T, inv_K, K):
     """depth [B,1,H,W], T/inv_K/K [B,4,4] -> normalised grid [B,H,W,2] -- :52-82.
     Note the pre-multiplied (K @ T) of :67."""
     B, _, H, W = depth.shape
-    homo = homo_points(B, H, W, depth.dtype)
+    homo = homo_points(B, H, W, depth.dtype).to(depth.device)
     pts = depth.view(B, 1, -1) * torch.matmul(inv_K[:, :3, :3], homo)
     pts = torch.cat([pts, homo[:, 2:3]], 1)
     p2 = (K @ T)[:, :3, :] @ pts
@@ -482,7 +483,7 @@ def aggregate_features(packed_feats, lev, weight, bias, slope=0.1):
 def virtual_depth(src_depth, src_mask, src_inv_K, src_K, tar_depth, tar_inv_K, tar_K, T, min_depth, max_depth):
     """-> (source depth warped into the target view [B,1,H,W], its mask) -- view_rendering.py:84-116."""
     b, _, h, w = src_depth.size()
-    homo = homo_points(b, h, w, src_depth.dtype)
+    homo = homo_points(b, h, w, src_depth.dtype).to(src_depth.device)
     src_points = src_depth.view(b, 1, -1) * torch.matmul(src_inv_K[:, :3, :3], homo)
     src_points = torch.cat([src_points, homo[:, 2:3]], 1)
     src_points_warped = torch.matmul(T[:, :3, :], src_points)

@@ -13,8 +13,10 @@ KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active', 'l1tex__t_sector_hit_rate.pct',
         'lts__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed']
 # kernel-name fragment -> C-ABI entry point that launches it (first match wins)
-ABI = [('voxel_fuse_fwd', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_bwd', 'vfd_voxel_fuse_bwd'),
-       ('voxel_fuse_reduce', 'vfd_voxel_fuse_bwd'), ('ray_sample_fwd', 'vfd_ray_sample_fwd'),
+ABI = [('voxel_fuse_gather', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_scatter', 'vfd_voxel_fuse_bwd'),
+       ('dense_dw', 'vfd_voxel_fuse_bwd'), ('voxel_fuse_reduce', 'vfd_voxel_fuse_bwd'),
+       # launched by both directions: occurrences alternate forward, backward within a step (see ALTERNATE)
+       ('dense_proj', 'vfd_voxel_fuse_fwd'), ('wcat_prep', 'vfd_voxel_fuse_fwd'), ('ray_sample_fwd', 'vfd_ray_sample_fwd'),
        ('ray_sample_bwd', 'vfd_ray_sample_bwd'), ('warp_stats', 'vfd_warp_stats'),
        ('warp_loss_fwd', 'vfd_warp_loss_fwd'), ('warp_loss_bwd_kernel<1>', 'vfd_warp_loss_train_fwd'),
        ('warp_loss_bwd_kernel<true>', 'vfd_warp_loss_train_fwd'), ('warp_loss_bwd', 'vfd_warp_loss_bwd'),
@@ -26,6 +28,7 @@ ABI = [('voxel_fuse_fwd', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_bwd', 'vfd_voxel_f
        ('smooth_bwd_kernel<1>', 'vfd_smooth_loss_train_fwd'), ('smooth_bwd_kernel<true>', 'vfd_smooth_loss_train_fwd'),
        ('smooth_bwd_finish', 'vfd_smooth_loss_train_bwd'), ('smooth_bwd', 'vfd_smooth_loss_bwd'), ('voxel_gather_fwd', 'vfd_voxel_gather_depth_fwd'),
        ('voxel_gather_bwd', 'vfd_voxel_gather_depth_bwd')]
+ALTERNATE = {'dense_proj': ('vfd_voxel_fuse_fwd', 'vfd_voxel_fuse_bwd'), 'wcat_prep': ('vfd_voxel_fuse_fwd', 'vfd_voxel_fuse_bwd')}
 UNIT = {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}
 
 
@@ -37,6 +40,7 @@ def main(rep, out_csv, out_json, steps=1):
     col = {h: i for i, h in enumerate(hdr)}
     name_i = col['Kernel Name']
     traffic = {}
+    seen = {}
     with open(out_csv, 'w', newline='') as f:
         w = csv.writer(f)
         w.writerow(['Kernel Name'] + KEYS)
@@ -47,6 +51,9 @@ def main(rep, out_csv, out_json, steps=1):
                 if frag in r[name_i]:
                     b = sum(float(r[col[k]].replace(',', '')) * UNIT[units[col[k]]]
                             for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
+                    if frag in ALTERNATE:
+                        abi = ALTERNATE[frag][seen.get(frag, 0) % 2]
+                        seen[frag] = seen.get(frag, 0) + 1
                     traffic.setdefault(abi, []).append(b)
                     break
     # the capture covers `steps` steps (default 1): DRAM bytes of all kernels one ABI call launches, per call

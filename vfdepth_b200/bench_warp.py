@@ -18,6 +18,10 @@ class WarpWorkload:
         pin = lambda x: x.contiguous().pin_memory()
         keys = [('color', f, 0) for f in self.frames] + ['mask', ('K', 0), ('inv_K', 0), 'extrinsics', 'extrinsics_inv']
         self.h_inputs = {k: pin(inputs[k]) for k in keys}
+        # end to end the images travel as uint8 -- what every dataset stores and a loader hands over -- and become the
+        # float tensors the reference consumes on the device (the reference's loaders do ToTensor on the host)
+        self.color_keys = [('color', f, 0) for f in self.frames]
+        self.h_u8 = {k: pin((inputs[k] * 255.0).round().clamp(0, 255).to(torch.uint8)) for k in self.color_keys}
         self.h_disp = pin(torch.cat(ex['disp'], 1))                   # [B,6,H,W] decoder output of scale 0
         self.h_noise = pin(torch.stack(ex['noise'], 1))               # [B,6,2,H,W]
         self.h_T = {f: pin(ex['cam_T_cam'][f]) for f in self.frames[1:]}
@@ -50,17 +54,23 @@ class WarpWorkload:
         if slot not in self._stage:
             mk = lambda t: torch.empty(t.shape, dtype=t.dtype, device=self.dev)
             self._stage[slot] = ({k: mk(v) for k, v in self.h_inputs.items()}, mk(self.h_disp),
-                                 {f: mk(v) for f, v in self.h_T.items()})
-        inputs, disp, T = self._stage[slot]
+                                 {f: mk(v) for f, v in self.h_T.items()}, {k: mk(v) for k, v in self.h_u8.items()})
+        inputs, disp, T, u8 = self._stage[slot]
         for k, v in self.h_inputs.items():
-            inputs[k].copy_(v, non_blocking=True)
+            if k in self.h_u8:
+                u8[k].copy_(self.h_u8[k], non_blocking=True)
+            else:
+                inputs[k].copy_(v, non_blocking=True)
         disp.copy_(self.h_disp, non_blocking=True)
         for f, v in self.h_T.items():
             T[f].copy_(v, non_blocking=True)
-        return inputs, disp, None, T
+        return inputs, disp, None, T, u8
 
     def compute(self, staged):
-        return self.step(*staged)
+        inputs, disp, noise, T, u8 = staged
+        for k, v in u8.items():          # uint8 -> float in [0, 1] on the compute stream, into the preallocated tensors
+            torch.mul(v, 1.0 / 255.0, out=inputs[k])
+        return self.step(inputs, disp, noise, T)
 
     def download(self, result):
         total, grads = result
@@ -68,7 +78,7 @@ class WarpWorkload:
         self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
 
     def h2d_bytes(self):
-        ts = list(self.h_inputs.values()) + [self.h_disp] + list(self.h_T.values())
+        ts = [self.h_u8.get(k, v) for k, v in self.h_inputs.items()] + [self.h_disp] + list(self.h_T.values())
         return sum(t.numel() * t.element_size() for t in ts)
 
     def d2h_bytes(self):

@@ -62,9 +62,10 @@ VFD_HD float vfd_dot4_nofma(const float* r, float x0, float x1, float x2, float 
     return acc;
 }
 
-// ATen grid_sampler_unnormalize, align_corners=True: ((g + 1) / 2) * (size - 1)
+// ATen grid_sampler_unnormalize, align_corners=True: ((g + 1) / 2) * (size - 1).  x / 2 and x * 0.5 are the same
+// correctly rounded value for every float, so the division is written as a multiplication (one instruction instead of ~9).
 VFD_HD float vfd_unnormalize(float g, int size) {
-    return VFD_MUL(VFD_DIV(VFD_ADD(g, 1.0f), 2.0f), (float)(size - 1));
+    return VFD_MUL(VFD_MUL(VFD_ADD(g, 1.0f), 0.5f), (float)(size - 1));
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -218,37 +218,57 @@ __device__ __forceinline__ int part_group(const ReduceArgs& r, int i) {
     return r.split >= 0 ? (i >= r.split ? 1 : 0) : (r.group[(i / r.slabs) % r.cams] ? 1 : 0);
 }
 
-__global__ void __launch_bounds__(256) voxel_fuse_reduce_kernel(const ReduceArgs r) {
+// grid.x covers the (n, c) elements 64 at a time, the block's 4 thread rows split the partial blocks; every thread sums
+// its quarter in index order, the quarters are added in order: a fixed summation tree (deterministic given the partials)
+constexpr int kRedCols = 64, kRedRows = 4;
+__global__ void __launch_bounds__(kRedCols * kRedRows) voxel_fuse_reduce_kernel(const ReduceArgs r) {
+    __shared__ float s_acc[kRedRows][2][kRedCols];
     const int C = r.C, Cv = r.Cv, C1 = C + 1, N2 = 2 * Cv;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n_mat = N2 * C;            // (n, c)
-    if (i < n_mat) {
-        const int n = i / C, c = i - n * C;
+    const int col = threadIdx.x % kRedCols, row = threadIdx.x / kRedCols;
+    const int i = blockIdx.x * kRedCols + col;
+    if (blockIdx.x * kRedCols < n_mat) {           // block-uniform: matrix part
         float acc[2] = {0.f, 0.f};
-        const float* p = r.dw_part + (size_t)n * C + c;
-        if (r.split >= 0) {              // two contiguous runs of blocks: independent loads, many in flight
+        if (i < n_mat) {
+            const float* p = r.dw_part + i;
+            const int per = (r.n_parts + kRedRows - 1) / kRedRows;
+            const int k0 = row * per, k1 = min(r.n_parts, k0 + per);
+            if (r.split >= 0) {          // two contiguous runs of blocks: independent loads, many in flight
+                const int m = min(max(r.split, k0), k1);
 #pragma unroll 8
-            for (int k = 0; k < r.split; ++k) acc[0] += p[(size_t)k * n_mat];
+                for (int k = k0; k < m; ++k) acc[0] += p[(size_t)k * n_mat];
 #pragma unroll 8
-            for (int k = r.split; k < r.n_parts; ++k) acc[1] += p[(size_t)k * n_mat];
-        } else {
-            for (int k = 0; k < r.n_parts; ++k) {
-                const float v = p[(size_t)k * n_mat];
-                if (part_group(r, k)) acc[1] += v; else acc[0] += v;
+                for (int k = m; k < k1; ++k) acc[1] += p[(size_t)k * n_mat];
+            } else {
+                for (int k = k0; k < k1; ++k) {
+                    const float v = p[(size_t)k * n_mat];
+                    if (part_group(r, k)) acc[1] += v; else acc[0] += v;
+                }
             }
         }
-        if (n >= Cv) {
-            r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + c] = acc[0];
-            r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + C1 + c] = acc[1];
-        } else {
-            r.d_w_no[(size_t)n * C1 + c] = acc[0] + acc[1];     // W_no serves both camera groups
+        s_acc[row][0][col] = acc[0];
+        s_acc[row][1][col] = acc[1];
+        __syncthreads();
+        if (row == 0 && i < n_mat) {
+            float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+            for (int q = 0; q < kRedRows; ++q) { a0 += s_acc[q][0][col]; a1 += s_acc[q][1][col]; }
+            const int n = i / C, c = i - n * C;
+            if (n >= Cv) {
+                r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + c] = a0;
+                r.d_w_ov[(size_t)(n - Cv) * 2 * C1 + C1 + c] = a1;
+            } else {
+                r.d_w_no[(size_t)n * C1 + c] = a0 + a1;     // W_no serves both camera groups
+            }
         }
         return;
     }
-    const int j = i - n_mat;
+    // bias / relative-depth-column part: one thread per element
+    const int j = (blockIdx.x - (n_mat + kRedCols - 1) / kRedCols) * (kRedCols * kRedRows) + threadIdx.x;
     if (j >= 5 * Cv) return;
     const int q = j / Cv, n = j - q * Cv;
     float acc = 0.f;
+#pragma unroll 8
     for (int c = 0; c < r.ctas; ++c) acc += r.sc_part[((size_t)c * 5 + q) * Cv + n];
     if (q == 0) r.d_b_no[n] = acc;
     else if (q == 1) r.d_w_no[(size_t)n * C1 + C] = acc;
@@ -396,8 +416,8 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
     r.C = d->C; r.Cv = d->Cv; r.cams = d->num_cams;
     for (int c = 0; c < VFD_MAX_CAMS; ++c) r.group[c] = c < d->num_cams ? d->group[c] : 0;
     r.d_w_no = d_w_no; r.d_b_no = d_b_no; r.d_w_ov = d_w_ov; r.d_b_ov = d_b_ov;
-    const int total = N2 * d->C + 5 * d->Cv;
-    voxel_fuse_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(r);
+    const int blocks = (N2 * d->C + kRedCols - 1) / kRedCols + (5 * d->Cv + kRedCols * kRedRows - 1) / (kRedCols * kRedRows);
+    voxel_fuse_reduce_kernel<<<blocks, kRedCols * kRedRows, 0, st>>>(r);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }

@@ -36,7 +36,7 @@ def axis_angle_to_matrix(v):
     zero = torch.zeros_like(kx)
     Kx = torch.stack([zero, -kz, ky, kz, zero, -kx, -ky, kx, zero], -1).reshape(v.shape[:-1] + (3, 3))
     th = theta[..., None]
-    eye = torch.eye(3, dtype=v.dtype).expand(v.shape[:-1] + (3, 3))
+    eye = torch.eye(3, dtype=v.dtype, device=v.device).expand(v.shape[:-1] + (3, 3))
     return eye + torch.sin(th) * Kx + (1 - torch.cos(th)) * (Kx @ Kx)
 
 
