@@ -52,6 +52,11 @@ __device__ __forceinline__ void red_add_f1(float* p, float a) {
 
 __device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 
+// torch.min / torch.max / torch.clamp return NaN when an operand is NaN; fminf / fmaxf return the other operand
+__device__ __forceinline__ float nan_min(float a, float b) { return (a != a || b != b) ? a + b : fminf(a, b); }
+__device__ __forceinline__ float nan_max(float a, float b) { return (a != a || b != b) ? a + b : fmaxf(a, b); }
+__device__ __forceinline__ float nan_clamp01(float v) { return v != v ? v : fminf(fmaxf(v, 0.f), 1.f); }
+
 // ---- packed fp32 (fma.rn.f32x2 / mul.rn.f32x2, sm_100+): two IEEE results per instruction, bit-identical to scalar ----
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 pack2(float a, float b) {

@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kSynThreads) depth_syn_fwd_kernel(const SynArg
             const SynSample sm = syn_sample<false>(ctx, i, X, a.depth + (size_t)(b * d.num_cams + s) * HW,
                                                    d.mask + (size_t)(b * d.num_cams + s) * HW, W, H, d.min_depth, d.max_depth);
             float l = fabsf(av - sm.dw) / ((av + sm.dw) + 1e-8f);
-            l = fminf(fmaxf(l, 0.f), 1.f);
+            l = nan_clamp01(l);      // torch.clamp keeps NaN (depth_synthesis_loss.py:27)
             num += l * sm.m;
             den += sm.m;
             if (a.out_depth) a.out_depth[((size_t)bc * kSynSrc + i) * HW + p] = sm.dw;

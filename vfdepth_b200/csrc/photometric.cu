@@ -48,7 +48,7 @@ __device__ __forceinline__ SsimPix ssim_pixel(const float* x, const float* y) {
     s.inv = __frcp_rn(den);
     s.ssim = __fdiv_rn(__fmul_rn(s.n1, s.n2), den);
     s.raw = __fmul_rn(__fsub_rn(1.f, s.ssim), 0.5f);
-    s.l = fminf(fmaxf(s.raw, 0.f), 1.f);
+    s.l = nan_clamp01(s.raw);      // torch.clamp keeps NaN (loss_util.py:66)
     return s;
 }
 

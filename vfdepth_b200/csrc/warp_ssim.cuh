@@ -147,7 +147,9 @@ __device__ __forceinline__ void photometric8(const float2* __restrict__ img, int
             const float2 ssim = mul2(num, inv);
             const float2 raw = mul2(sub2(splat2(1.f), ssim), splat2(0.5f));
             const float2 l = make_float2(fminf(fmaxf(raw.x, 0.f), 1.f), fminf(fmaxf(raw.y, 0.f), 1.f));
-            ssum[q] = add2(ssum[q], l);
+            // torch.clamp keeps a NaN (loss_util.py:66) where fminf / fmaxf drop it: ssim * 0 is +-0 for every finite ssim
+            // (l + +-0 == l exactly, l >= +0) and NaN for a NaN ssim, at the price of one packed fma
+            ssum[q] = add2(ssum[q], fma2(ssim, splat2(0.f), l));
             const float2 df = sub2(yc, xc[q]);
             lsum[q] = add2(lsum[q], make_float2(fabsf(df.x), fabsf(df.y)));
             if (GRAD && q < 3) {

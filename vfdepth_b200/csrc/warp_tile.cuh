@@ -181,9 +181,10 @@ __device__ __forceinline__ PixelLoss pixel_loss(const float* sm, const vfd_warp_
     // temporal reprojection: torch.min over frames keeps the first minimum on a tie
     o.sel_reproj = (two && L[0].y < L[0].x) ? 1 : 0;
     o.reproj = o.sel_reproj ? L[0].y : L[0].x;
+    if (two && L[0].y != L[0].y) o.reproj = L[0].y;          // torch.min returns NaN if either frame's loss is NaN
     // identity reprojection + tie-break noise (single_cam_loss.py:44-47)
     float ident = VFD_ADD(L[2].y, VFD_MUL(0.00001f, noise[0]));
-    if (two) ident = fminf(ident, VFD_ADD(L[3].x, VFD_MUL(0.00001f, noise[1])));
+    if (two) ident = nan_min(ident, VFD_ADD(L[3].x, VFD_MUL(0.00001f, noise[1])));
     // argmin over cat([reproj, identity]) == 0: the first minimum wins a tie (loss_util.py:15-17)
     o.automask = VFD_MUL((o.reproj <= ident) ? 1.f : 0.f, rmask);
     if (!SP) {
@@ -196,8 +197,9 @@ __device__ __forceinline__ PixelLoss pixel_loss(const float* sm, const vfd_warp_
     o.spatial = L[2].x;
     o.sel_st = (two && L[1].y < L[1].x) ? 1 : 0;
     o.st = o.sel_st ? L[1].y : L[1].x;
+    if (two && L[1].y != L[1].y) o.st = L[1].y;
     o.st_mask = VFD_MUL(VFD_MUL(rmask, sm[Rg::kOmask + Rg::R + ctr]), o.automask);
-    if (two) o.st_mask = fmaxf(o.st_mask, VFD_MUL(VFD_MUL(rmask, sm[Rg::kOmask + 2 * Rg::R + ctr]), o.automask));
+    if (two) o.st_mask = nan_max(o.st_mask, VFD_MUL(VFD_MUL(rmask, sm[Rg::kOmask + 2 * Rg::R + ctr]), o.automask));
     return o;
 }
 

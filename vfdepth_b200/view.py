@@ -564,4 +564,5 @@ class DepthSynLoss(MultiCamLoss):
         cam_loss = cam_loss + depthsyn / len(self.scales)
         loss_dict.update(depth_loss=float(depthsyn.detach()), depth_sm_loss=float(sm[0].detach()),
                          depth_con_loss=float(con[0].detach()))
+        loss_dict['cam_loss'] = float(cam_loss.detach())          # depth_synthesis_loss.py:90
         return cam_loss, loss_dict
