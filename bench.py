@@ -429,6 +429,44 @@ def full_step_pass(wl, headline_ms, iters):
     return out
 
 
+def dropin_pass(warp, iters):
+    """the view-synthesis half through the reference's own call pattern (models/vfdepth.py:296-313: per camera
+    ViewRendering.forward then MultiCamLoss.forward on the outputs dict) instead of the rig-level view.warp_and_loss --
+    the drop-in modules share one rig-level pass, so this should cost what the rig-level call costs"""
+    from vfdepth_b200 import view
+    cfg, n = warp.cfg, warp.cfg['data']['num_cams']
+    vr, lossm = view.ViewRendering(cfg, 0), view.MultiCamLoss(cfg, 0, device_noise=True)
+    inputs = warp.inputs
+    E, Einv = inputs['extrinsics'], inputs['extrinsics_inv']
+    rel_list = cfg['data']['rel_cam_list']
+
+    def one():
+        disp = warp.disp.detach().requires_grad_(True)
+        Ts = {f: t.detach().requires_grad_(True) for f, t in warp.T.items()}
+        depth = view.to_depth(cfg, disp, inputs[('K', 0)])
+        outputs = {('cam', c): {('depth', 0): depth[:, c:c + 1], ('disp', 0): disp[:, c:c + 1],
+                                **{('cam_T_cam', 0, f): Ts[f][:, c] for f in Ts}} for c in range(n)}
+        total = 0
+        for cam in range(n):
+            rel = {}
+            for nb in rel_list[cam]:                       # Pose.compute_relative_cam_poses (pose.py:66-96)
+                rel[(0, nb)] = torch.matmul(Einv[:, nb], E[:, cam])
+                for f in Ts:
+                    rel[(f, nb)] = torch.matmul(rel[(0, nb)], outputs[('cam', cam)][('cam_T_cam', 0, f)])
+            vr(inputs, outputs, cam, rel)
+            cam_loss, _ = lossm(inputs, outputs, cam)
+            total = total + cam_loss
+        (total / n).backward()
+
+    one()
+    ms = _event_ms(one, iters)
+    rig = _event_ms(lambda: warp.step_resident(), iters)
+    return {'per_camera_modules_ms': ms, 'rig_level_call_ms': rig,
+            'what': 'to_depth + view synthesis + losses fwd+bwd of %d rigs: six ViewRendering / MultiCamLoss calls on the outputs '
+                    'dict (the reference\'s call pattern, incl. the per-camera pose products and one host read-back of the loss '
+                    'terms) against one view.warp_and_loss call; eager launches, no CUDA graph' % warp.B}
+
+
 def train_step_pass(dev, rank, world, steps):
     """BASELINE.json configs[3] (nuScenes-shaped full fusion-depth training step, random init, B=2 per GPU as
     configs/nuscenes/nusc_surround_fusion.yaml:47) and configs[4] (the same under DDP: the gradient all-reduce of every
@@ -594,6 +632,8 @@ def run_ours(args):
         full = full_step_pass(wl, ms / args.steps, max(2, min(args.steps, 5)))
         if rank == 0:
             extras['full_step'] = full
+            if warp is not None:
+                extras['dropin_modules'] = dropin_pass(warp, max(2, min(args.steps, 5)))
         wl.g_up = None
         torch.cuda.empty_cache()
         tr = train_step_pass(dev, rank, world, args.steps)

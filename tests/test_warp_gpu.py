@@ -307,6 +307,41 @@ def test_no_intensity_align_and_early_exit():
     assert abs(float(total) - float(t32)) / float(t32) < 3e-4
 
 
+def _lib_launches():
+    from vfdepth_b200 import _lib
+    return _lib.launches
+
+
+def test_dropin_single_camera_fallback_and_missing_pose():
+    """a camera rendered on its own (the other cameras' depth is not in ``outputs``): same loss terms as that camera
+    gets in the rig-level call; a neighbour pose missing from rel_pose_dict raises KeyError as the reference's
+    rel_pose_dict[(frame, neighbour)] lookup does (view_rendering.py:176)."""
+    dev = _dev()
+    from vfdepth_b200 import view
+    cfg, inp, ex = _rig(64, 96, 2, seed=22)
+    to = lambda t: t.to(dev)
+    inputs = {k: to(v) for k, v in inp.items()}
+    cam = 2
+    outputs = {('cam', c): {} for c in range(6)}
+    outputs[('cam', cam)] = {('depth', 0): to(ex['depth'][cam]), ('disp', 0): to(ex['disp'][cam]),
+                             ('cam_T_cam', 0, -1): to(ex['cam_T_cam'][-1][:, cam]), ('cam_T_cam', 0, 1): to(ex['cam_T_cam'][1][:, cam])}
+    rel = orc.relative_cam_poses(cfg, inputs, {f: outputs[('cam', cam)][('cam_T_cam', 0, f)] for f in (-1, 1)}, cam)
+    vr, lossm = view.ViewRendering(cfg, dev), view.MultiCamLoss(cfg, dev)
+    vr(inputs, outputs, cam, rel)
+    assert '_vfd_warp' not in outputs
+    torch.manual_seed(77)
+    noise = torch.randn(2, 2, 64, 96)
+    torch.manual_seed(77)
+    cam_loss, ld = lossm(inputs, outputs, cam)
+    ex2 = dict(ex, noise=[noise if c == cam else torch.zeros_like(noise) for c in range(6)])
+    _, det, _ = _run_gpu(cfg, inp, ex2, dev)
+    assert abs(float(cam_loss) - float(det['cam_loss'][cam])) < 1e-6 * abs(float(cam_loss))
+    bad = dict(rel)
+    del bad[(1, cfg['data']['rel_cam_list'][cam][0])]
+    with pytest.raises(KeyError):
+        vr(inputs, outputs, cam, bad)
+
+
 def test_dropin_modules_per_camera():
     """ViewRendering / MultiCamLoss with the reference's call pattern (models/vfdepth.py:290-313: per camera,
     outputs dict mutated in place) give the rig-level result, write the reference's keys, and back-propagate."""
@@ -320,24 +355,30 @@ def test_dropin_modules_per_camera():
     outputs = {('cam', c): {('depth', 0): depths[c], ('disp', 0): to(ex['disp'][c]),
                             ('cam_T_cam', 0, -1): Ts[-1][:, c], ('cam_T_cam', 0, 1): Ts[1][:, c]} for c in range(6)}
     vr = view.ViewRendering(cfg, dev, materialize=True)
-    lossm = view.MultiCamLoss(cfg, dev)
-    total, noises = 0, []
+    lossm = view.MultiCamLoss(cfg, dev, materialize=True)
+    # the module replays the reference's CPU stream: one torch.randn per camera, in camera order, drawn when the first
+    # camera's loss is evaluated (all six cameras run in one launch then)
+    torch.manual_seed(1000)
+    noises = [torch.randn(2, 2, 64, 96) for _ in range(6)]
+    total = 0
+    n0 = _lib_launches()
     for cam in range(6):
         rel = orc.relative_cam_poses(cfg, inputs, {-1: Ts[-1][:, cam], 1: Ts[1][:, cam]}, cam)
         vr(inputs, outputs, cam, rel)
-        torch.manual_seed(1000 + cam)
-        noises.append(torch.randn(2, 2, 64, 96))
-        torch.manual_seed(1000 + cam)           # the module draws the same tensor from the global CPU stream
+        if cam == 0:
+            torch.manual_seed(1000)
         cam_loss, ld = lossm(inputs, outputs, cam)
         assert set(ld) >= {'reproj_loss', 'spatio_loss', 'spatio_tempo_loss', 'smooth', 'depth/mean'}
         # SingleCamLoss (single_cam_loss.py:66-95): the same reprojection and smoothness terms, nothing else
-        torch.manual_seed(1000 + cam)
+        if cam == 0:
+            torch.manual_seed(1000)
         single, ld1 = view.SingleCamLoss(cfg, dev)(inputs, outputs, cam)
         assert 'spatio_loss' not in ld1 and ld1['reproj_loss'] == ld['reproj_loss'] and ld1['smooth'] == ld['smooth']
         want = ld['reproj_loss'] + cfg['loss']['disparity_smoothness'] * ld['smooth']
         assert abs(float(single) - want) < 1e-6 * abs(want)
         assert float(single) < float(cam_loss)
         total = total + cam_loss
+    assert '_vfd_warp' in outputs          # the six per-camera calls shared one rig-level pass
     total = total / 6
     g_mod = torch.autograd.grad(total, depths + [Ts[-1], Ts[1]])
     ex2 = dict(ex, noise=noises)

@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
 
     // ---- phase C: gather the coefficients at the interior pixel, then back through normalise / sampler / projection ----
     const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
-    const bool live = x < W && y < H;
+    const bool live = threadIdx.x < kTilePixels && x < W && y < H;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     float dpred[kNPred][3];
 #pragma unroll
@@ -198,14 +198,25 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         for (int k = 0; k < kNPred; ++k)
 #pragma unroll
             for (int c = 0; c < 3; ++c) SA[k][c] = SB[k][c] = SC[k][c] = 0.f;
+        // how often the window of neighbour (x + dx, y + dy) contains this pixel: 1 away from the image border (reflection
+        // padding only folds taps within two pixels of it), 0 for a neighbour outside the image
+        float mx[3] = {1.f, 1.f, 1.f}, my[3] = {1.f, 1.f, 1.f};
+        if (x < 2 || x >= W - 2) {
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) mx[dx + 1] = (x + dx < 0 || x + dx >= W) ? 0.f : (float)tap_mult(x + dx, x, W);
+        }
+        if (y < 2 || y >= H - 2) {
+#pragma unroll
+            for (int dy = -1; dy <= 1; ++dy) my[dy + 1] = (y + dy < 0 || y + dy >= H) ? 0.f : (float)tap_mult(y + dy, y, H);
+        }
+#pragma unroll
         for (int dy = -1; dy <= 1; ++dy) {
             const int py = y + dy;
-            if (py < 0 || py >= H) continue;
-            const int my = tap_mult(py, y, H);
+#pragma unroll
             for (int dx = -1; dx <= 1; ++dx) {
                 const int px = x + dx;
-                if (px < 0 || px >= W) continue;
-                const float mult = (float)(my * tap_mult(px, x, W));
+                const float mult = my[dy + 1] * mx[dx + 1];
+                if (mult == 0.f) continue;
                 const int r = (py - (ty0 - 1)) * Coef::RW + (px - (tx0 - 1));
                 const int sel = reinterpret_cast<const int*>(cf)[Coef::kSel + r];
                 const int kr = sel & 1, kt = VFD_WARP_SRC + 1 + (sel >> 1);

@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) warp_loss_fwd_kernel(const Lo
 
     const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
     float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (x < W && y < H) {
+    if (threadIdx.x < kTilePixels && x < W && y < H) {
         const int p = y * W + x;
         const float rmask = __ldg(d.mask + (size_t)(b * d.num_cams + cam) * HW + p);
         float nz[VFD_WARP_SRC] = {0.f, 0.f};

@@ -205,14 +205,30 @@ def rig_transforms(wi, inputs, cam_T_cam):
     return torch.stack(cols, 2)
 
 
+def _expected_rel_keys(wi, cam, spatio=True, spatio_temporal=True):
+    """the keys Pose.compute_relative_cam_poses (pose.py:66-96) writes for camera ``cam``"""
+    nbrs = [n for n in wi.rel[cam] if n < wi.num_cams]
+    keys = [(0, n) for n in nbrs] if spatio else []
+    if spatio_temporal:
+        keys += [(f, n) for f in wi.frame_ids[1:] for n in nbrs]
+    return keys
+
+
 def camera_transforms(wi, target_view, rel_pose_dict, cam):
-    """one camera: T [B,1,NW,4,4] from ('cam_T_cam', 0, f) and the reference's rel_pose_dict."""
+    """one camera: T [B,1,NW,4,4] from ('cam_T_cam', 0, f) and the reference's rel_pose_dict.  A neighbour pose the
+    reference would read (view_rendering.py:176, :186) but the dict lacks raises KeyError, as it does there; slots of
+    neighbours that do not exist (partial rigs, pose.py:78-79) hold the identity and are inactive in the kernels."""
     cols = [target_view[('cam_T_cam', 0, f)] for f in wi.frame_ids[1:]]
     eye = torch.eye(4, device=wi.device).expand(wi.B, 4, 4)
     for f in wi.frame_ids:
         for k in range(NBR):
             nb = wi.rel[cam][k] if k < len(wi.rel[cam]) else -1
-            cols.append(rel_pose_dict[(f, nb)] if (f, nb) in rel_pose_dict else eye)
+            if 0 <= nb < wi.num_cams:
+                if (f, nb) not in rel_pose_dict:
+                    raise KeyError((f, nb))
+                cols.append(rel_pose_dict[(f, nb)])
+            else:
+                cols.append(eye)
     return torch.stack(cols, 1).unsqueeze(1).float()
 
 
@@ -408,11 +424,15 @@ class ViewRendering(torch.nn.Module):
     """Drop-in for models/geometry/view_rendering.py:8 (``ViewRendering(cfg, rank)``;
     ``forward(inputs, outputs, cam, rel_pose_dict)`` mutating ``outputs[('cam', cam)]``).
 
-    ``forward`` runs pass 1 (statistics) for the camera and leaves the warp context for ``MultiCamLoss``; the
-    reference's image keys ``('color', f, s)``, ``('color_mask', f, s)``, ``('overlap', f, s)``,
-    ``('overlap_mask', f, s)`` are written only when ``materialize`` is true (the reference's logger reads them at
-    checkpoints only, utils/logger.py:120-170) -- they are non-differentiable copies; gradients flow through the
-    fused loss."""
+    The reference calls this once per camera (models/vfdepth.py:296-301).  When the first call of a step finds the depth
+    and the ``cam_T_cam`` of EVERY camera in ``outputs`` -- the reference's own call order guarantees it
+    (compute_depth_maps and predict_pose run before compute_losses, vfdepth.py:218-232) -- pass 1 (warps + intensity
+    statistics) runs for the whole rig in one launch and the other five calls find their camera already done; the
+    loss module then evaluates all cameras in ONE training-mode launch (the path bench.py times).  Otherwise the
+    camera is processed on its own.  The reference's image keys ``('color', f, s)``, ``('color_mask', f, s)``,
+    ``('overlap', f, s)``, ``('overlap_mask', f, s)`` are written only when ``materialize`` is true (the reference's
+    logger reads them at checkpoints only, utils/logger.py:120-170) -- they are non-differentiable copies; gradients
+    flow through the fused loss."""
 
     def __init__(self, cfg, rank, materialize=False):
         super().__init__()
@@ -423,15 +443,43 @@ class ViewRendering(torch.nn.Module):
         if list(self.scales) != [0]:
             raise NotImplementedError('only scales == [0] (all reference configs)')
 
+    @staticmethod
+    def _rig_key(wi, outputs):
+        """identity of the step's per-camera tensors, or None when some camera's depth / poses are not there yet"""
+        key = []
+        for c in range(wi.num_cams):
+            tv = outputs.get(('cam', c))
+            if tv is None or ('depth', 0) not in tv or any(('cam_T_cam', 0, f) not in tv for f in wi.frame_ids[1:]):
+                return None
+            key.append(id(tv[('depth', 0)]))
+            key += [id(tv[('cam_T_cam', 0, f)]) for f in wi.frame_ids[1:]]
+        return tuple(key)
+
     def forward(self, inputs, outputs, cam, rel_pose_dict):
         wi = inputs.get(_CTX)
         if wi is None or wi.color[0].data_ptr() != inputs[('color', 0, 0)].data_ptr():
             wi = inputs[_CTX] = WarpInputs(self.cfg, inputs)
         tv = outputs[('cam', cam)]
-        depth = tv[('depth', 0)].reshape(wi.B, 1, wi.H, wi.W)
-        T = camera_transforms(wi, tv, rel_pose_dict, cam)
-        stats = warp_stats(wi, depth.detach().contiguous(), T.detach().contiguous(), cam)
-        tv[_CTX] = dict(wi=wi, depth=depth, T=T, stats=stats)
+        for k in _expected_rel_keys(wi, cam, getattr(self, 'spatio', True), getattr(self, 'spatio_temporal', True)):
+            if k not in rel_pose_dict:
+                raise KeyError(k)          # the reference reads rel_pose_dict[(frame, neighbour)] (view_rendering.py:176)
+        key = self._rig_key(wi, outputs)
+        rig = outputs.get(_CTX)
+        if key is not None and 'extrinsics_inv' in inputs and (rig is None or rig['key'] != key):
+            n = wi.num_cams
+            depth = torch.cat([outputs[('cam', c)][('depth', 0)].reshape(wi.B, 1, wi.H, wi.W) for c in range(n)], 1)
+            cam_T_cam = {f: torch.stack([outputs[('cam', c)][('cam_T_cam', 0, f)] for c in range(n)], 1)
+                         for f in wi.frame_ids[1:]}
+            T = rig_transforms(wi, inputs, cam_T_cam)          # = pose.py:66-96 for every camera
+            stats = warp_stats(wi, depth.detach().contiguous(), T.detach().contiguous(), 0)
+            rig = outputs[_CTX] = dict(key=key, wi=wi, depth=depth, T=T, stats=stats, loss={})
+        if rig is not None and rig['key'] == key and key is not None:
+            tv[_CTX] = dict(wi=wi, rig=rig)
+        else:
+            depth = tv[('depth', 0)].reshape(wi.B, 1, wi.H, wi.W)
+            T = camera_transforms(wi, tv, rel_pose_dict, cam)
+            stats = warp_stats(wi, depth.detach().contiguous(), T.detach().contiguous(), cam)
+            tv[_CTX] = dict(wi=wi, depth=depth, T=T, stats=stats)
         if self.materialize:
             self.render(inputs, outputs, cam)
 
@@ -481,9 +529,14 @@ class ViewRendering(torch.nn.Module):
         tv = outputs[('cam', cam)]
         c = tv[_CTX]
         wi = c['wi']
+        if 'rig' in c:          # the camera's slice of the rig pass; its statistics are recomputed (logging time only)
+            depth = c['rig']['depth'][:, cam:cam + 1].detach().contiguous()
+            T = c['rig']['T'][:, cam:cam + 1].detach().contiguous()
+            stats = warp_stats(wi, depth, T, cam)
+        else:
+            depth, T, stats = c['depth'].detach(), c['T'].detach(), c['stats']
         noise = torch.zeros((wi.B, 1, wi.n_src, wi.H, wi.W), device=wi.device)
-        _, _, v = warp_loss_sums(wi, c['depth'].detach(), c['T'].detach(), noise, cam, c['stats'],
-                                 ('color', 'color_mask', 'overlap', 'overlap_mask'))
+        _, _, v = warp_loss_sums(wi, depth, T, noise, cam, stats, ('color', 'color_mask', 'overlap', 'overlap_mask'))
         for k, f in enumerate(wi.frame_ids[1:]):
             tv[('color', f, 0)] = v['color'][:, 0, k]
             tv[('color_mask', f, 0)] = v['color_mask'][:, 0, k:k + 1]
@@ -494,11 +547,22 @@ class ViewRendering(torch.nn.Module):
 
 class MultiCamLoss(torch.nn.Module):
     """Drop-in for models/losses/multi_cam_loss.py:9 (``MultiCamLoss(cfg, rank)``; ``forward(inputs, outputs, cam)``
-    -> ``(cam_loss, loss_dict)``), pose_model == 'fusion' (no pose-consistency term, multi_cam_loss.py:113)."""
+    -> ``(cam_loss, loss_dict)``), pose_model == 'fusion' (no pose-consistency term, multi_cam_loss.py:113).
 
-    def __init__(self, cfg, rank):
+    After a rig-level ``ViewRendering`` pass the first call of a step evaluates ALL cameras in one training-mode launch
+    (loss sums and gradients together) and one smoothness launch, reads the loss terms back once, and every call
+    returns its camera's entry -- six calls cost what one does, and ``loss_dict`` needs one host synchronisation per
+    step where the reference has four per camera (multi_cam_loss.py:127-130).
+
+    ``materialize`` (default False): also write ``('reproj_loss', 0)`` / ``('reproj_mask', 0)`` into ``outputs`` (the
+    reference's logger reads them at checkpoints; they cost an extra forward launch).  ``device_noise`` (default
+    False): draw the tie-break noise of single_cam_loss.py:45-46 on the device instead of replaying the reference's
+    CPU stream (``torch.randn`` per camera, in camera order) and shipping it."""
+
+    def __init__(self, cfg, rank, materialize=False, device_noise=False):
         super().__init__()
         self.cfg, self.rank = cfg, rank
+        self.materialize, self.device_noise = materialize, device_noise
         for k, v in cfg['loss'].items():
             setattr(self, k, v)
         self.scales, self.frame_ids = cfg['training']['scales'], cfg['training']['frame_ids']
@@ -508,20 +572,46 @@ class MultiCamLoss(torch.nn.Module):
 
     spatial_terms = True
 
+    def _noise(self, wi, n_call):
+        shape = (wi.B, wi.n_src, wi.H, wi.W)
+        if self.device_noise:
+            return torch.randn((wi.B, n_call) + shape[1:], device=wi.device)
+        # one CPU draw per camera in camera order = the reference's stream (its six draws follow each other directly)
+        return torch.stack([torch.randn(shape) for _ in range(n_call)], 1).to(wi.device)
+
+    def _evaluate(self, inputs, wi, depth, T, stats, disp, color0, cam0, n_call):
+        noise = self._noise(wi, n_call)
+        num, den, _ = warp_loss_sums(wi, depth, T, noise, cam0, stats)
+        sm = smooth_loss(color0, disp)
+        cam_loss, terms = combine_losses(self.cfg, num, den, sm, spatial=self.spatial_terms)
+        res = dict(cam_loss=cam_loss, host=torch.cat([terms.detach(), sm.detach()[:, None]], 1).cpu(), views=None)
+        if self.materialize:
+            with torch.no_grad():
+                _, _, res['views'] = warp_loss_sums(wi, depth.detach(), T.detach(), noise, cam0, stats,
+                                                    ('reproj_loss', 'reproj_mask'))
+        return res
+
     def forward(self, inputs, outputs, cam):
         tv = outputs[('cam', cam)]
         c = tv[_CTX]
         wi = c['wi']
-        # the reference draws the tie-break noise on the CPU and ships it (single_cam_loss.py:45-46); the drop-in does the
-        # same so that a seeded run replays the reference's random stream (warp_and_loss takes device noise directly)
-        noise = torch.randn((wi.B, wi.n_src, wi.H, wi.W)).to(wi.device).unsqueeze(1)
-        num, den, v = warp_loss_sums(wi, c['depth'], c['T'], noise, cam, c['stats'], ('reproj_loss', 'reproj_mask'))
-        tv[('reproj_loss', 0)] = v['reproj_loss'][:, 0:1]
-        tv[('reproj_mask', 0)] = v['reproj_mask'][:, 0:1]
-        sm = smooth_loss(inputs[('color', 0, 0)][:, cam:cam + 1], tv[('disp', 0)])[0]
-        cam_loss, terms = combine_losses(self.cfg, num, den, sm.reshape(1), spatial=self.spatial_terms)
-        t = terms[0].detach().cpu()
-        loss_dict = {'reproj_loss': float(t[0]), 'smooth': float(sm.detach())}
+        if 'rig' in c:
+            rig, i = c['rig'], cam
+            res = rig['loss'].get(self.spatial_terms)
+            if res is None:
+                n = wi.num_cams
+                disp = torch.cat([outputs[('cam', k)][('disp', 0)].reshape(wi.B, 1, wi.H, wi.W) for k in range(n)], 1)
+                res = rig['loss'][self.spatial_terms] = self._evaluate(inputs, wi, rig['depth'], rig['T'], rig['stats'],
+                                                                       disp, inputs[('color', 0, 0)], 0, n)
+        else:
+            i = 0
+            res = self._evaluate(inputs, wi, c['depth'], c['T'], c['stats'], tv[('disp', 0)].reshape(wi.B, 1, wi.H, wi.W),
+                                 inputs[('color', 0, 0)][:, cam:cam + 1], cam, 1)
+        if res['views'] is not None:
+            tv[('reproj_loss', 0)] = res['views']['reproj_loss'][:, i:i + 1]
+            tv[('reproj_mask', 0)] = res['views']['reproj_mask'][:, i:i + 1]
+        t = res['host'][i]
+        loss_dict = {'reproj_loss': float(t[0]), 'smooth': float(t[3])}
         if self.spatial_terms:
             loss_dict.update(spatio_loss=float(t[1]), spatio_tempo_loss=float(t[2]))
         depth_log = tv[('depth', 0)].detach()           # base_loss.py:29-33
@@ -530,9 +620,9 @@ class MultiCamLoss(torch.nn.Module):
         if cam == 0:
             pose_t = tv[('cam_T_cam', 0, -1)].detach() if ('cam_T_cam', 0, -1) in tv else None
             if pose_t is not None:
-                for i, n in enumerate(('pose/tx', 'pose/ty', 'pose/tz')):
-                    loss_dict[n] = pose_t[:, i, 3].abs().mean()
-        return cam_loss[0], loss_dict
+                for k, n in enumerate(('pose/tx', 'pose/ty', 'pose/tz')):
+                    loss_dict[n] = pose_t[:, k, 3].abs().mean()
+        return res['cam_loss'][i], loss_dict
 
 
 class SingleCamLoss(MultiCamLoss):
