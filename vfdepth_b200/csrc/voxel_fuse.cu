@@ -79,7 +79,7 @@ __device__ __forceinline__ Entry load_entry(const CornerTable& tb, size_t rows, 
 // ---------------------------------------------------------------------------------------------------------
 // forward: vol[v] = LeakyReLU(sum_e sum_k w_k P[img_e, pix_k, blk] + zrel_e * wz + bias)   blk = count - 1
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kFgThreads) voxel_fuse_gather_kernel(const FuseArgs a) {
+__global__ void __launch_bounds__(kFgThreads, 4) voxel_fuse_gather_kernel(const FuseArgs a) {
     const vfd_fusion_desc& d = a.d;
     __shared__ __align__(16) float s_c[5][kFgMaxCv];     // b_no, wz_no, b_ov, wz_ov[0], wz_ov[1]
     const int Cv = d.Cv, C1 = d.C + 1, hw = d.h * d.w, ldp = 2 * Cv;

@@ -35,12 +35,15 @@ extern __shared__ __align__(16) float vfd_warp_smem[];
 // the set's upstream weight (for the L1 term) and the frame each min selected
 constexpr int kStrip = 8;   // tiles a CTA of the backward walks, top to bottom
 
+// Stored as float4 planes -- (a, b, c, -) per (set, channel) and (w_reproj, w_spatial, w_st, selection bits) per pixel --
+// so that one 128-bit shared access moves what three 32-bit ones did (the scalar stores / loads of these planes were a
+// quarter of the kernel's stall samples).
 struct Coef {
     static constexpr int RW = kTileW + 2, RH = kTileH + 2, R = RW * RH;
-    static constexpr int kAbc = 0;                 // [3 sets][3 ch][3][R]
-    static constexpr int kWgt = kAbc + 27 * R;     // [3][R]
-    static constexpr int kSel = kWgt + 3 * R;      // [R] (int bits: sel_reproj | sel_st << 1)
-    static constexpr int kFloats = kSel + R;
+    static constexpr int kAbc = 0;                 // float4 [3 sets][3 ch][R]
+    static constexpr int kWgt = 9;                 // float4 [R]: (wr, ws, wt, int bits: sel_reproj | sel_st << 1)
+    static constexpr int kPlanes = 10;
+    static constexpr int kFloats = kPlanes * 4 * R;
 };
 
 // how many of pixel p's 3 horizontal (or vertical) window taps land on q, with reflection padding of 1
@@ -69,29 +72,21 @@ __device__ __forceinline__ PixelLoss ring_pixel(const float* sm, float* cf, cons
     const PixelLoss o = pixel_loss<2, true, SP>(sm, d, x, y, ox, oy, rmask, nz, g);
     const float wr = w_set[0] * o.automask, ws = SP ? w_set[1] * o.sp_mask : 0.f, wt = SP ? w_set[2] * o.st_mask : 0.f;
     const bool s1 = o.sel_reproj == 1, t1 = o.sel_st == 1;
+    float4* cf4 = reinterpret_cast<float4*>(cf);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
-        q[0] = wr * (s1 ? g[0].a[c].y : g[0].a[c].x);
-        q[Coef::R] = wr * (s1 ? g[0].b[c].y : g[0].b[c].x);
-        q[2 * Coef::R] = wr * (s1 ? g[0].c[c].y : g[0].c[c].x);
-        q += 9 * Coef::R;
+        cf4[(Coef::kAbc + c) * Coef::R + r] = make_float4(wr * (s1 ? g[0].a[c].y : g[0].a[c].x), wr * (s1 ? g[0].b[c].y : g[0].b[c].x),
+                                                          wr * (s1 ? g[0].c[c].y : g[0].c[c].x), 0.f);
         if (SP) {
-            q[0] = ws * g[2].a[c].x; q[Coef::R] = ws * g[2].b[c].x; q[2 * Coef::R] = ws * g[2].c[c].x;
-            q += 9 * Coef::R;
-            q[0] = wt * (t1 ? g[1].a[c].y : g[1].a[c].x);
-            q[Coef::R] = wt * (t1 ? g[1].b[c].y : g[1].b[c].x);
-            q[2 * Coef::R] = wt * (t1 ? g[1].c[c].y : g[1].c[c].x);
+            cf4[(Coef::kAbc + 3 + c) * Coef::R + r] = make_float4(ws * g[2].a[c].x, ws * g[2].b[c].x, ws * g[2].c[c].x, 0.f);
+            cf4[(Coef::kAbc + 6 + c) * Coef::R + r] = make_float4(wt * (t1 ? g[1].a[c].y : g[1].a[c].x), wt * (t1 ? g[1].b[c].y : g[1].b[c].x),
+                                                                  wt * (t1 ? g[1].c[c].y : g[1].c[c].x), 0.f);
         } else {      // a later tile of the strip may carry these ring rows over and read them
-            q[0] = 0.f; q[Coef::R] = 0.f; q[2 * Coef::R] = 0.f;
-            q += 9 * Coef::R;
-            q[0] = 0.f; q[Coef::R] = 0.f; q[2 * Coef::R] = 0.f;
+            cf4[(Coef::kAbc + 3 + c) * Coef::R + r] = f4_zero();
+            cf4[(Coef::kAbc + 6 + c) * Coef::R + r] = f4_zero();
         }
     }
-    cf[Coef::kWgt + r] = wr;
-    cf[Coef::kWgt + Coef::R + r] = ws;
-    cf[Coef::kWgt + 2 * Coef::R + r] = wt;
-    reinterpret_cast<int*>(cf)[Coef::kSel + r] = (s1 ? 1 : 0) | (t1 ? 2 : 0);
+    cf4[Coef::kWgt * Coef::R + r] = make_float4(wr, ws, wt, __int_as_float((s1 ? 1 : 0) | (t1 ? 2 : 0)));
     return o;
 }
 
@@ -145,9 +140,10 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
             const int pl = i / (4 * Rg::RW), o = i - pl * (4 * Rg::RW);
             mk[pl * Rg::R + o] = mk[pl * Rg::R + kTileH * Rg::RW + o];
         }
-        for (int i = threadIdx.x; i < (Coef::kFloats / Coef::R) * 2 * Coef::RW; i += kTileThreads) {
+        float4* cfm = reinterpret_cast<float4*>(cf);
+        for (int i = threadIdx.x; i < Coef::kPlanes * 2 * Coef::RW; i += kTileThreads) {
             const int pl = i / (2 * Coef::RW), o = i - pl * (2 * Coef::RW);
-            cf[pl * Coef::R + o] = cf[pl * Coef::R + kTileH * Coef::RW + o];
+            cfm[pl * Coef::R + o] = cfm[pl * Coef::R + kTileH * Coef::RW + o];
         }
         __syncthreads();      // the fill below overwrites the rows that were just read
     }
@@ -218,21 +214,20 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
                 const float mult = my[dy + 1] * mx[dx + 1];
                 if (mult == 0.f) continue;
                 const int r = (py - (ty0 - 1)) * Coef::RW + (px - (tx0 - 1));
-                const int sel = reinterpret_cast<const int*>(cf)[Coef::kSel + r];
+                const float4* cf4 = reinterpret_cast<const float4*>(cf);
+                const int sel = __float_as_int(cf4[Coef::kWgt * Coef::R + r].w);
                 const int kr = sel & 1, kt = VFD_WARP_SRC + 1 + (sel >> 1);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const float* q = cf + Coef::kAbc + (c * 3) * Coef::R + r;
-                    const float ra = mult * q[0], rb = mult * q[Coef::R], rc = mult * q[2 * Coef::R];
+                    const float4 q0 = cf4[(Coef::kAbc + c) * Coef::R + r];
+                    const float ra = mult * q0.x, rb = mult * q0.y, rc = mult * q0.z;
 #pragma unroll
                     for (int k = 0; k < VFD_WARP_SRC; ++k)
                         if (kr == k) { SA[k][c] += ra; SB[k][c] += rb; SC[k][c] += rc; }
                     if (sp) {      // CTA-uniform: the spatial / spatio-temporal planes are all zero otherwise
-                        q += 9 * Coef::R;
-                        const float sa = mult * q[0], sb = mult * q[Coef::R], sc = mult * q[2 * Coef::R];
-                        q += 9 * Coef::R;
-                        const float ta = mult * q[0], tb = mult * q[Coef::R], tc = mult * q[2 * Coef::R];
-                        SA[VFD_WARP_SRC][c] += sa; SB[VFD_WARP_SRC][c] += sb; SC[VFD_WARP_SRC][c] += sc;
+                        const float4 q1 = cf4[(Coef::kAbc + 3 + c) * Coef::R + r], q2 = cf4[(Coef::kAbc + 6 + c) * Coef::R + r];
+                        SA[VFD_WARP_SRC][c] += mult * q1.x; SB[VFD_WARP_SRC][c] += mult * q1.y; SC[VFD_WARP_SRC][c] += mult * q1.z;
+                        const float ta = mult * q2.x, tb = mult * q2.y, tc = mult * q2.z;
 #pragma unroll
                         for (int k = VFD_WARP_SRC + 1; k < kNPred; ++k)
                             if (kt == k) { SA[k][c] += ta; SB[k][c] += tb; SC[k][c] += tc; }
@@ -242,8 +237,9 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
         }
         const int ctr2 = (y - oy) * Rg::RW + (x - ox);
         const int r0 = (y - (ty0 - 1)) * Coef::RW + (x - (tx0 - 1));
-        const int sel0 = reinterpret_cast<const int*>(cf)[Coef::kSel + r0];
-        const float wl[3] = {cf[Coef::kWgt + r0], cf[Coef::kWgt + Coef::R + r0], cf[Coef::kWgt + 2 * Coef::R + r0]};
+        const float4 w4 = reinterpret_cast<const float4*>(cf)[Coef::kWgt * Coef::R + r0];
+        const int sel0 = __float_as_int(w4.w);
+        const float wl[3] = {w4.x, w4.y, w4.z};
 #pragma unroll
         for (int k = 0; k < kNPred; ++k) {
             if (!sp && k >= VFD_WARP_SRC) continue;     // dpred stays 0

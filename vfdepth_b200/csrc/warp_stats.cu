@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
     __syncthreads();
     const int NW = ctx.NW;
     const int lane = threadIdx.x & 31;
+    const float inv_w = 1.0f / (float)W;
     const int p0 = blockIdx.x * kStatThreads * kStatPx + threadIdx.x;
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* ref = d.color[0] + (size_t)(b * d.num_cams + cam) * 3 * HW;
@@ -78,7 +79,12 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
         for (int k = 0; k < kStatPx; ++k) {
             const int p = p0 + k * kStatThreads;
             if (p >= HW) break;
-            const int u = p % W, v = p / W;
+            // row / column without an integer division: (p + 0.5) / W is at least 0.5 / W away from an integer, far more
+            // than the fp32 error of the product for H * W < 2^22 (check_warp_desc bounds it); one fix-up step for safety
+            int v = __float2int_rz(((float)p + 0.5f) * inv_w);
+            int u = p - v * W;
+            if (u < 0) { u += W; --v; }
+            if (u >= W) { u -= W; ++v; }
             float X[3];
             vfd_backproject(ctx.invK, (float)u, (float)v, __ldg(depth + p), X);
             const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
@@ -161,7 +167,7 @@ int check_warp_desc(const vfd_warp_desc* d) {
     if (d->B < 1 || d->num_cams < 1 || d->num_cams > VFD_MAX_CAMS || d->H < 2 || d->W < 2) return VFD_ERR_DESC;
     if (d->n_src < 1 || d->n_src > VFD_WARP_SRC) return VFD_ERR_UNSUPPORTED;
     if (d->cam0 < 0 || d->n_call < 1 || d->cam0 + d->n_call > d->num_cams) return VFD_ERR_DESC;
-    if ((long)d->H * d->W >= (1L << 30)) return VFD_ERR_DESC;
+    if ((long)d->H * d->W >= (1L << 22)) return VFD_ERR_DESC;      // pixel indices are exact in fp32, see warp_stats_kernel
     for (int f = 0; f <= d->n_src; ++f)
         if (!d->color[f]) return VFD_ERR_NULL;
     if (!d->mask || !d->K || !d->invK) return VFD_ERR_NULL;
