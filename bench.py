@@ -463,8 +463,8 @@ def dropin_pass(warp, iters):
     rig = _event_ms(lambda: warp.step_resident(), iters)
     return {'per_camera_modules_ms': ms, 'rig_level_call_ms': rig,
             'what': 'to_depth + view synthesis + losses fwd+bwd of %d rigs: six ViewRendering / MultiCamLoss calls on the outputs '
-                    'dict (the reference\'s call pattern, incl. the per-camera pose products and one host read-back of the loss '
-                    'terms) against one view.warp_and_loss call; eager launches, no CUDA graph' % warp.B}
+                    'dict (the reference\'s call pattern, incl. the per-camera pose products; loss_dict entries stay on the '
+                    'device) against one view.warp_and_loss call; eager launches, no CUDA graph' % warp.B}
 
 
 def train_step_pass(dev, rank, world, steps):

@@ -377,6 +377,12 @@ def test_dropin_modules_per_camera():
         want = ld['reproj_loss'] + cfg['loss']['disparity_smoothness'] * ld['smooth']
         assert abs(float(single) - want) < 1e-6 * abs(want)
         assert float(single) < float(cam_loss)
+        if cam == 5:
+            # host_loss_dict=True: Python floats as the reference's .item() entries (multi_cam_loss.py:127-130)
+            torch.manual_seed(1000)
+            _, ldf = view.SingleCamLoss(cfg, dev, host_loss_dict=True)(inputs, outputs, cam)
+            assert isinstance(ldf['reproj_loss'], float) and ldf['reproj_loss'] == float(ld1['reproj_loss'])
+            assert torch.is_tensor(ld1['reproj_loss']) and ld1['reproj_loss'].is_cuda
         total = total + cam_loss
     assert '_vfd_warp' in outputs          # the six per-camera calls shared one rig-level pass
     total = total / 6

@@ -1,6 +1,6 @@
 """Stall samples / executed instructions of one kernel per SOURCE LINE: joins the SASS page of an .ncu-rep (--import-source
 on) with nvdisasm -g line annotations of the shipped cubin (same instruction order).
-   python tools/ncu_lines.py gpurun_out/prof_step.ncu-rep warp_loss_bwd warp_loss_bwd_kernelILb1 [top]"""
+   python tools/ncu_lines.py gpurun_out/prof_step.ncu-rep warp_loss_bwd warp_loss_bwd_kernelILb1 [top [kernel-name regex]]"""
 import csv
 import io
 import os
@@ -35,9 +35,9 @@ def sass_lines(obj, mangled_frag):
     return res
 
 
-def main(rep, obj, frag, top=40):
+def main(rep, obj, frag, top=40, kernel=None):
     lines = sass_lines(obj, frag)
-    out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-name', 'regex:' + obj.split('.')[0]],
+    out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-name', 'regex:' + (kernel or obj.split('.')[0])],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     hdr, data, nk = None, [], 0
@@ -69,4 +69,4 @@ def main(rep, obj, frag, top=40):
 
 
 if __name__ == '__main__':
-    main(*sys.argv[1:5])
+    main(*sys.argv[1:6])

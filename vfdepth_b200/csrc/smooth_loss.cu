@@ -89,22 +89,34 @@ __device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f 
 // TRAIN: unit upstream, and the loss sums of smooth_loss_kernel from the same taps -- the forward and the backward of a
 // training step share one pass over the images; smooth_bwd_finish_kernel applies the upstream afterwards.
 //
-// Mapping.  A warp owns 32 adjacent columns and walks kSmoothRun rows downwards; CTA = 8 such warps side by side.  Every
-// edge of the stencil is then evaluated ONCE: the edge below a pixel (weight, normalised neighbour, neighbour colours) is
-// carried in registers and becomes the edge above the next row's pixel, the edge to the right is handed to the lane on
-// the right as its left edge by shuffle.  Per pixel that is one division and two expf instead of five and four, and
-// 4 loads instead of 20 -- with the very same operands in the very same expressions, so d_disp is bit-identical to the
-// pixel-per-thread form.
+// Mapping.  A warp walks kSmoothRun rows downwards over 32 adjacent columns of which it OWNS the inner kSmoothOwn = 30
+// (lanes 0 and 31 are halo lanes that only feed the shuffles); CTA = 8 such warps side by side.  Every edge of the
+// stencil is then evaluated ONCE: the edge below a pixel (weight, normalised neighbour, neighbour colours) is carried
+// in registers and becomes the edge above the next row's pixel, the edge to the right is handed to the lane on the right
+// as its left edge by shuffle.  Per pixel that is one division and two expf instead of five and four, and 4 loads
+// instead of 20, with no lane-divergent loads at the warp's edges -- and with the very same operands in the very same
+// expressions, so d_disp is bit-identical to the pixel-per-thread form.  The row after next is loaded while the current
+// one is evaluated (the walk is otherwise one dependent load chain per warp), and the sums leave per warp (no barrier).
 constexpr int kSmoothRun = 16;
+constexpr int kSmoothOwn = 30;
 
 struct EdgeSide {      // what a pixel contributes to an edge: its normalised disparity and colours
     float n, c0, c1, c2;
 };
-__device__ __forceinline__ EdgeSide load_side(const float* d, const float* col, int HW, int p, float den) {
-    EdgeSide s;
-    s.n = __ldg(d + p) / den;
+struct RawSide {       // the same as loaded (disparity not yet normalised)
+    float d, c0, c1, c2;
+};
+__device__ __forceinline__ RawSide load_raw(const float* d, const float* col, int HW, int p) {
+    RawSide s;
+    s.d = __ldg(d + p);
     s.c0 = s.c1 = s.c2 = 0.f;
     if (col) { s.c0 = __ldg(col + p); s.c1 = __ldg(col + HW + p); s.c2 = __ldg(col + 2 * HW + p); }
+    return s;
+}
+__device__ __forceinline__ EdgeSide to_side(const RawSide& r, float den) {
+    EdgeSide s;
+    s.n = r.d / den;
+    s.c0 = r.c0; s.c1 = r.c1; s.c2 = r.c2;
     return s;
 }
 // exp(-mean_c |rgb[p] - rgb[q]|) with p the left / upper pixel, as edge_weight() forms it
@@ -113,10 +125,13 @@ __device__ __forceinline__ float side_weight(bool has_color, const EdgeSide& p, 
     const float d0 = fabsf(p.c0 - q.c0), d1 = fabsf(p.c1 - q.c1), d2 = fabsf(p.c2 - q.c2);
     return expf(-((d0 + d1 + d2) / 3.0f));
 }
+__device__ __forceinline__ double warp_sum(double v) {
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
 
 template <bool TRAIN>
 __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const SmoothArgs a) {
-    __shared__ double s_red[kSmoothThreads / 32];
     const int bc = blockIdx.z, cam = bc % a.cams, HW = a.H * a.W, W = a.W, H = a.H;
     const float* d = a.disp + (size_t)bc * HW;
     const float* col = a.color ? a.color + (size_t)bc * 3 * HW : nullptr;
@@ -126,48 +141,47 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const Smooth
     const float up = TRAIN ? 1.f : __ldg(a.d_smooth + cam);
     const float ux = up / (float)((double)a.B * H * (W - 1)), uy = up / (float)((double)a.B * (H - 1) * W);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x = (blockIdx.x * (kSmoothThreads / 32) + warp) * 32 + lane;
+    const int x = (blockIdx.x * (kSmoothThreads / 32) + warp) * kSmoothOwn + lane - 1;
     const int y0 = blockIdx.y * kSmoothRun, y1 = min(H, y0 + kSmoothRun);
-    const bool in = x < W;
+    const bool in = x >= 0 && x < W;
+    const bool own = in && lane >= 1 && lane <= kSmoothOwn;
+    const bool has_r = own && x + 1 < W, has_l = own && x > 0;
     double acc = 0.0;
     float sx = 0.f, sy = 0.f;
     EdgeSide cur = {0.f, 0.f, 0.f, 0.f}, above = cur;
-    float w_top = 0.f;
+    RawSide next = {0.f, 0.f, 0.f, 0.f};           // row y + 1, in flight while row y is evaluated
+    float w_top = 0.f, d_cur = 0.f;
     if (in) {
-        cur = load_side(d, col, HW, y0 * W + x, den);
+        const RawSide r0 = load_raw(d, col, HW, y0 * W + x);
+        if (y0 + 1 < H) next = load_raw(d, col, HW, (y0 + 1) * W + x);
+        d_cur = r0.d;
+        cur = to_side(r0, den);
         if (y0 > 0) {
-            above = load_side(d, col, HW, (y0 - 1) * W + x, den);
+            above = to_side(load_raw(d, col, HW, (y0 - 1) * W + x), den);
             w_top = side_weight(hc, above, cur);
         }
     }
     for (int y = y0; y < y1; ++y) {
         const int p = y * W + x;
-        // right neighbour: the lane on the right holds it, except across the warp's edge
+        const bool has_b = in && y + 1 < H;
+        const RawSide below_raw = next;
+        if (in && y + 2 < H && y + 1 < y1) next = load_raw(d, col, HW, p + 2 * W);
+        // right neighbour: the lane on the right holds it; its edge weight is the left edge of that lane
         EdgeSide right;
         right.n = __shfl_down_sync(0xffffffffu, cur.n, 1);
         right.c0 = __shfl_down_sync(0xffffffffu, cur.c0, 1);
         right.c1 = __shfl_down_sync(0xffffffffu, cur.c1, 1);
         right.c2 = __shfl_down_sync(0xffffffffu, cur.c2, 1);
-        const bool has_r = in && x + 1 < W;
-        if (lane == 31 && has_r) right = load_side(d, col, HW, p + 1, den);
-        const float w_r = has_r ? side_weight(hc, cur, right) : 0.f;
-        // left edge = the right edge of the lane on the left
-        float w_l = __shfl_up_sync(0xffffffffu, w_r, 1);
-        float n_l = __shfl_up_sync(0xffffffffu, cur.n, 1);
-        const bool has_l = in && x > 0;
-        if (lane == 0 && has_l) {
-            const EdgeSide left = load_side(d, col, HW, p - 1, den);
-            n_l = left.n;
-            w_l = side_weight(hc, left, cur);
-        }
+        const float w_r = side_weight(hc, cur, right);
+        const float w_l = __shfl_up_sync(0xffffffffu, w_r, 1);
+        const float n_l = __shfl_up_sync(0xffffffffu, cur.n, 1);
         EdgeSide below = cur;
         float w_b = 0.f;
-        const bool has_b = in && y + 1 < H;
         if (has_b) {
-            below = load_side(d, col, HW, p + W, den);
+            below = to_side(below_raw, den);
             w_b = side_weight(hc, cur, below);
         }
-        if (in) {
+        if (own) {
             float gi = 0.f;
             if (has_r) {
                 const float df = cur.n - right.n;
@@ -182,18 +196,18 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const Smooth
             }
             if (y > 0) gi -= uy * sgn(above.n - cur.n) * w_top;
             g[p] = gi;
-            acc += (double)gi * (double)__ldg(d + p);
+            acc += (double)gi * (double)d_cur;
         }
         above = cur;
         cur = below;
+        d_cur = below_raw.d;
         w_top = w_b;
     }
-    const double t = block_sum(acc, s_red);
-    if (threadIdx.x == 0) atomicAdd(a.gdot + bc, t);
+    const double t = warp_sum(acc);
+    if (lane == 0) atomicAdd(a.gdot + bc, t);
     if (TRAIN) {
-        const double tx = block_sum((double)sx, s_red);
-        const double ty = block_sum((double)sy, s_red);
-        if (threadIdx.x == 0) {
+        const double tx = warp_sum((double)sx), ty = warp_sum((double)sy);
+        if (lane == 0) {
             atomicAdd(a.sums + cam * 2 + 0, tx);
             atomicAdd(a.sums + cam * 2 + 1, ty);
         }
@@ -201,7 +215,8 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const Smooth
 }
 
 static dim3 smooth_bwd_grid(int B, int cams, int H, int W) {
-    return dim3((W + kSmoothThreads - 1) / kSmoothThreads, (H + kSmoothRun - 1) / kSmoothRun, B * cams);
+    const int per_cta = (kSmoothThreads / 32) * kSmoothOwn;
+    return dim3((W + per_cta - 1) / per_cta, (H + kSmoothRun - 1) / kSmoothRun, B * cams);
 }
 
 // d_disp_j = up * (g_j / den - (sum_i g_i disp_i) / (den^2 * HW))      (nd = disp / den, den = mean + 1e-8); up = 1

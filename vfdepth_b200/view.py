@@ -557,12 +557,15 @@ class MultiCamLoss(torch.nn.Module):
     ``materialize`` (default False): also write ``('reproj_loss', 0)`` / ``('reproj_mask', 0)`` into ``outputs`` (the
     reference's logger reads them at checkpoints; they cost an extra forward launch).  ``device_noise`` (default
     False): draw the tie-break noise of single_cam_loss.py:45-46 on the device instead of replaying the reference's
-    CPU stream (``torch.randn`` per camera, in camera order) and shipping it."""
+    CPU stream (``torch.randn`` per camera, in camera order) and shipping it.  ``host_loss_dict`` (default False): the
+    reference fills ``loss_dict`` with Python floats (``.item()``, multi_cam_loss.py:127-130), which makes the host wait
+    for the forward before it can enqueue the backward; here the entries are 0-dim device tensors (they add, divide and
+    format like floats; the wait moves to whoever prints them) unless this is set."""
 
-    def __init__(self, cfg, rank, materialize=False, device_noise=False):
+    def __init__(self, cfg, rank, materialize=False, device_noise=False, host_loss_dict=False):
         super().__init__()
         self.cfg, self.rank = cfg, rank
-        self.materialize, self.device_noise = materialize, device_noise
+        self.materialize, self.device_noise, self.host_loss_dict = materialize, device_noise, host_loss_dict
         for k, v in cfg['loss'].items():
             setattr(self, k, v)
         self.scales, self.frame_ids = cfg['training']['scales'], cfg['training']['frame_ids']
@@ -584,7 +587,8 @@ class MultiCamLoss(torch.nn.Module):
         num, den, _ = warp_loss_sums(wi, depth, T, noise, cam0, stats)
         sm = smooth_loss(color0, disp)
         cam_loss, terms = combine_losses(self.cfg, num, den, sm, spatial=self.spatial_terms)
-        res = dict(cam_loss=cam_loss, host=torch.cat([terms.detach(), sm.detach()[:, None]], 1).cpu(), views=None)
+        host = torch.cat([terms.detach(), sm.detach()[:, None]], 1)
+        res = dict(cam_loss=cam_loss, host=host.cpu() if self.host_loss_dict else host, views=None)
         if self.materialize:
             with torch.no_grad():
                 _, _, res['views'] = warp_loss_sums(wi, depth.detach(), T.detach(), noise, cam0, stats,
@@ -611,9 +615,10 @@ class MultiCamLoss(torch.nn.Module):
             tv[('reproj_loss', 0)] = res['views']['reproj_loss'][:, i:i + 1]
             tv[('reproj_mask', 0)] = res['views']['reproj_mask'][:, i:i + 1]
         t = res['host'][i]
-        loss_dict = {'reproj_loss': float(t[0]), 'smooth': float(t[3])}
+        num = float if self.host_loss_dict else (lambda v: v)
+        loss_dict = {'reproj_loss': num(t[0]), 'smooth': num(t[3])}
         if self.spatial_terms:
-            loss_dict.update(spatio_loss=float(t[1]), spatio_tempo_loss=float(t[2]))
+            loss_dict.update(spatio_loss=num(t[1]), spatio_tempo_loss=num(t[2]))
         depth_log = tv[('depth', 0)].detach()           # base_loss.py:29-33
         loss_dict['depth/mean'], loss_dict['depth/max'], loss_dict['depth/min'] = \
             depth_log.mean(), depth_log.max(), depth_log.min()
@@ -652,7 +657,8 @@ class DepthSynLoss(MultiCamLoss):
         tv[('tform_depth_mask', 0)] = [v['tform_depth_mask'][:, 0, i:i + 1] for i in slots]
         depthsyn = self.depth_con_coeff * con[0] + self.depth_sm_coeff * sm[0]
         cam_loss = cam_loss + depthsyn / len(self.scales)
-        loss_dict.update(depth_loss=float(depthsyn.detach()), depth_sm_loss=float(sm[0].detach()),
-                         depth_con_loss=float(con[0].detach()))
-        loss_dict['cam_loss'] = float(cam_loss.detach())          # depth_synthesis_loss.py:90
+        num = float if self.host_loss_dict else (lambda t: t)
+        loss_dict.update(depth_loss=num(depthsyn.detach()), depth_sm_loss=num(sm[0].detach()),
+                         depth_con_loss=num(con[0].detach()))
+        loss_dict['cam_loss'] = num(cam_loss.detach())          # depth_synthesis_loss.py:90
         return cam_loss, loss_dict
