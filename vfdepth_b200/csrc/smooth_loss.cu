@@ -48,13 +48,15 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_mean_kernel(const Smoot
     if (threadIdx.x == 0) atomicAdd(a.img_sum + bc, t);
 }
 
-// edge weight exp(-mean_c |rgb[p] - rgb[q]|)
+// edge weight exp(-mean_c |rgb[p] - rgb[q]|); the channel mean as sum * (1/3), torch's CUDA mean (a division by the
+// constant would send every warp holding one zero sum through the slow path of the division)
+constexpr float kThird = 1.0f / 3.0f;
 __device__ __forceinline__ float edge_weight(const float* col, int HW, int p, int q) {
     if (!col) return 1.f;      // plain smoothness (depth_synthesis_loss.py:35-41)
     const float d0 = fabsf(__ldg(col + p) - __ldg(col + q));
     const float d1 = fabsf(__ldg(col + HW + p) - __ldg(col + HW + q));
     const float d2 = fabsf(__ldg(col + 2 * HW + p) - __ldg(col + 2 * HW + q));
-    return expf(-((d0 + d1 + d2) / 3.0f));
+    return expf(-((d0 + d1 + d2) * kThird));
 }
 
 __device__ __forceinline__ float image_scale(const SmoothArgs& a, int bc) {
@@ -123,7 +125,7 @@ __device__ __forceinline__ EdgeSide to_side(const RawSide& r, float den) {
 __device__ __forceinline__ float side_weight(bool has_color, const EdgeSide& p, const EdgeSide& q) {
     if (!has_color) return 1.f;
     const float d0 = fabsf(p.c0 - q.c0), d1 = fabsf(p.c1 - q.c1), d2 = fabsf(p.c2 - q.c2);
-    return expf(-((d0 + d1 + d2) / 3.0f));
+    return expf(-((d0 + d1 + d2) * kThird));
 }
 __device__ __forceinline__ double warp_sum(double v) {
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -143,6 +145,7 @@ __global__ void __launch_bounds__(kSmoothThreads) smooth_bwd_kernel(const Smooth
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = (blockIdx.x * (kSmoothThreads / 32) + warp) * kSmoothOwn + lane - 1;
     const int y0 = blockIdx.y * kSmoothRun, y1 = min(H, y0 + kSmoothRun);
+    if (x - lane + 1 >= W) return;                 // the warp's first own column is outside (no CTA-wide barrier below)
     const bool in = x >= 0 && x < W;
     const bool own = in && lane >= 1 && lane <= kSmoothOwn;
     const bool has_r = own && x + 1 < W, has_l = own && x > 0;

@@ -45,6 +45,50 @@ __device__ __forceinline__ Tap make_tap(int dst, int in, int out) {
     return t;
 }
 
+// Same-size case (scale 0, every shipped config): the bilinear taps are (1, 0) on the pixel itself, so the interpolation
+// returns the input exactly for finite disparities (a sigmoid's output) and the pass is a float4 stream: 8 B per pixel
+// forward, 12 B backward.  VEC = 4 needs H*W % 4 == 0 (checked by the launcher; 16-B alignment follows from the
+// 256-B aligned tensors the host mirror passes -- the launcher checks the pointers too).
+__device__ __forceinline__ float depth_of(float d, float k00, const ToDepthArgs& a) {
+    const float disp = VFD_ADD(a.min_disp, VFD_MUL(a.range, d));
+    const float depth = __fdiv_rn(1.f, disp);
+    return __fdiv_rn(VFD_MUL(depth, k00), a.focal);
+}
+// the quotient is formed on the product -g * (k00 / focal) * range as in to_depth_bwd_kernel.  A zero numerator (pixels
+// without a gradient) would send the whole warp down the slow path of the division; 0 / x is that signed zero itself,
+// so those lanes divide a stand-in and keep the zero.
+__device__ __forceinline__ float d_disp_of(float g, float d, float kf, const ToDepthArgs& a) {
+    const float disp = a.min_disp + a.range * d;
+    const float num = -g * kf * a.range;
+    const bool zero = num == 0.f;
+    const float q = (zero ? 1.f : num) / (disp * disp);
+    return zero ? num : q;
+}
+
+__global__ void __launch_bounds__(kDepthThreads) to_depth_same_fwd_kernel(const ToDepthArgs a) {
+    const int bc = blockIdx.y, n4 = (a.H * a.W) >> 2;
+    const float4* s = reinterpret_cast<const float4*>(a.disp + (size_t)bc * a.H * a.W);
+    float4* o = reinterpret_cast<float4*>(a.depth + (size_t)bc * a.H * a.W);
+    const float k00 = __ldg(a.K + (size_t)bc * 16);
+    for (int i = blockIdx.x * kDepthThreads + threadIdx.x; i < n4; i += gridDim.x * kDepthThreads) {
+        const float4 v = __ldg(s + i);
+        o[i] = make_float4(depth_of(v.x, k00, a), depth_of(v.y, k00, a), depth_of(v.z, k00, a), depth_of(v.w, k00, a));
+    }
+}
+
+__global__ void __launch_bounds__(kDepthThreads) to_depth_same_bwd_kernel(const ToDepthArgs a) {
+    const int bc = blockIdx.y, n4 = (a.H * a.W) >> 2;
+    const float4* s = reinterpret_cast<const float4*>(a.disp + (size_t)bc * a.H * a.W);
+    const float4* g = reinterpret_cast<const float4*>(a.d_depth + (size_t)bc * a.H * a.W);
+    float4* gs = reinterpret_cast<float4*>(a.d_disp + (size_t)bc * a.H * a.W);
+    const float kf = __ldg(a.K + (size_t)bc * 16) / a.focal;
+    for (int i = blockIdx.x * kDepthThreads + threadIdx.x; i < n4; i += gridDim.x * kDepthThreads) {
+        const float4 v = __ldg(s + i), u = __ldg(g + i);
+        gs[i] = make_float4(d_disp_of(u.x, v.x, kf, a), d_disp_of(u.y, v.y, kf, a), d_disp_of(u.z, v.z, kf, a),
+                            d_disp_of(u.w, v.w, kf, a));
+    }
+}
+
 __global__ void __launch_bounds__(kDepthThreads) to_depth_fwd_kernel(const ToDepthArgs a) {
     const int bc = blockIdx.y, HW = a.H * a.W;
     const float* s = a.disp + (size_t)bc * a.hs * a.ws;
@@ -116,6 +160,12 @@ static ToDepthArgs to_depth_args(int B, int cams, int hs, int ws, int H, int W, 
     return a;
 }
 
+// the float4 same-size path: no resampling, whole float4s per image, 16-B aligned tensors
+static bool to_depth_same(const ToDepthArgs& a, const void* p0, const void* p1, const void* p2) {
+    const uintptr_t bits = (uintptr_t)p0 | (uintptr_t)p1 | (uintptr_t)p2;
+    return a.hs == a.H && a.ws == a.W && ((a.H * a.W) & 3) == 0 && (bits & 15) == 0;
+}
+
 }  // namespace vfd
 
 using namespace vfd;
@@ -127,7 +177,10 @@ extern "C" int vfd_to_depth_fwd(int B, int cams, int hs, int ws, int H, int W, c
     if (!disp || !K || !depth) return VFD_ERR_NULL;
     ToDepthArgs a = to_depth_args(B, cams, hs, ws, H, W, min_depth, max_depth, focal_length_scale);
     a.disp = disp; a.K = K; a.depth = depth;
-    to_depth_fwd_kernel<<<to_depth_grid(B, cams, H, W), kDepthThreads, 0, (cudaStream_t)stream>>>(a);
+    if (to_depth_same(a, disp, depth, nullptr))
+        to_depth_same_fwd_kernel<<<to_depth_grid(B, cams, H, W), kDepthThreads, 0, (cudaStream_t)stream>>>(a);
+    else
+        to_depth_fwd_kernel<<<to_depth_grid(B, cams, H, W), kDepthThreads, 0, (cudaStream_t)stream>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }
@@ -144,7 +197,10 @@ extern "C" int vfd_to_depth_bwd(int B, int cams, int hs, int ws, int H, int W, c
     if (hs != H || ws != W) {
         if (cudaMemsetAsync(d_disp, 0, sizeof(float) * (size_t)B * cams * hs * ws, st) != cudaSuccess) return VFD_ERR_CUDA;
     }
-    to_depth_bwd_kernel<<<to_depth_grid(B, cams, H, W), kDepthThreads, 0, st>>>(a);
+    if (to_depth_same(a, disp, d_depth, d_disp))
+        to_depth_same_bwd_kernel<<<to_depth_grid(B, cams, H, W), kDepthThreads, 0, st>>>(a);
+    else
+        to_depth_bwd_kernel<<<to_depth_grid(B, cams, H, W), kDepthThreads, 0, st>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
 }

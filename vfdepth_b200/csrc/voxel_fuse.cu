@@ -221,6 +221,7 @@ __device__ __forceinline__ int part_group(const ReduceArgs& r, int i) {
 // grid.x covers the (n, c) elements 64 at a time, the block's 4 thread rows split the partial blocks; every thread sums
 // its quarter in index order, the quarters are added in order: a fixed summation tree (deterministic given the partials)
 constexpr int kRedCols = 64, kRedRows = 4;
+constexpr int kBiasCols = 16, kBiasRows = kRedCols * kRedRows / kBiasCols;    // 16 x 16 <= the 2 x 4 x 64 floats of s_acc
 __global__ void __launch_bounds__(kRedCols * kRedRows) voxel_fuse_reduce_kernel(const ReduceArgs r) {
     __shared__ float s_acc[kRedRows][2][kRedCols];
     const int C = r.C, Cv = r.Cv, C1 = C + 1, N2 = 2 * Cv;
@@ -263,13 +264,24 @@ __global__ void __launch_bounds__(kRedCols * kRedRows) voxel_fuse_reduce_kernel(
         }
         return;
     }
-    // bias / relative-depth-column part: one thread per element
-    const int j = (blockIdx.x - (n_mat + kRedCols - 1) / kRedCols) * (kRedCols * kRedRows) + threadIdx.x;
-    if (j >= 5 * Cv) return;
-    const int q = j / Cv, n = j - q * Cv;
+    // bias / relative-depth-column part: kBiasCols elements per block, the block's kBiasRows thread rows each add every
+    // kBiasRows-th CTA partial in index order, the rows are then added in order (fixed tree; one thread per element
+    // walking all ~1200 partials was most of this kernel's time)
+    const int bcol = threadIdx.x % kBiasCols, brow = threadIdx.x / kBiasCols;
+    const int j = (blockIdx.x - (n_mat + kRedCols - 1) / kRedCols) * kBiasCols + bcol;
+    float* s_b = &s_acc[0][0][0];
     float acc = 0.f;
+    if (j < 5 * Cv) {
 #pragma unroll 8
-    for (int c = 0; c < r.ctas; ++c) acc += r.sc_part[((size_t)c * 5 + q) * Cv + n];
+        for (int c = brow; c < r.ctas; c += kBiasRows) acc += r.sc_part[(size_t)c * 5 * Cv + j];
+    }
+    s_b[brow * kBiasCols + bcol] = acc;
+    __syncthreads();
+    if (brow != 0 || j >= 5 * Cv) return;
+    acc = 0.f;
+#pragma unroll
+    for (int q = 0; q < kBiasRows; ++q) acc += s_b[q * kBiasCols + bcol];
+    const int q = j / Cv, n = j - q * Cv;
     if (q == 0) r.d_b_no[n] = acc;
     else if (q == 1) r.d_w_no[(size_t)n * C1 + C] = acc;
     else if (q == 2) r.d_b_ov[n] = acc;
@@ -416,7 +428,7 @@ extern "C" int vfd_voxel_fuse_bwd(const vfd_fusion_desc* d, const float* feats, 
     r.C = d->C; r.Cv = d->Cv; r.cams = d->num_cams;
     for (int c = 0; c < VFD_MAX_CAMS; ++c) r.group[c] = c < d->num_cams ? d->group[c] : 0;
     r.d_w_no = d_w_no; r.d_b_no = d_b_no; r.d_w_ov = d_w_ov; r.d_b_ov = d_b_ov;
-    const int blocks = (N2 * d->C + kRedCols - 1) / kRedCols + (5 * d->Cv + kRedCols * kRedRows - 1) / (kRedCols * kRedRows);
+    const int blocks = (N2 * d->C + kRedCols - 1) / kRedCols + (5 * d->Cv + kBiasCols - 1) / kBiasCols;
     voxel_fuse_reduce_kernel<<<blocks, kRedCols * kRedRows, 0, st>>>(r);
     VFD_CHECK_LAUNCH();
     return VFD_OK;

@@ -216,21 +216,28 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
                 const int r = (py - (ty0 - 1)) * Coef::RW + (px - (tx0 - 1));
                 const float4* cf4 = reinterpret_cast<const float4*>(cf);
                 const int sel = __float_as_int(cf4[Coef::kWgt * Coef::R + r].w);
-                const int kr = sel & 1, kt = VFD_WARP_SRC + 1 + (sel >> 1);
+                // the min's selection as tap weights: w[k] = mult for the selected frame, 0 for the other (mult is 0, 1, 2
+                // or 4, so w * q is exact and the fused form below rounds like the separate multiply and add it replaces;
+                // a non-finite coefficient now also reaches the unselected frame's sum, as NaN)
+                const float wr0 = (sel & 1) ? 0.f : mult, wr1 = mult - wr0;
+                const float wt0 = (sel >> 1) ? 0.f : mult, wt1 = mult - wt0;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const float4 q0 = cf4[(Coef::kAbc + c) * Coef::R + r];
-                    const float ra = mult * q0.x, rb = mult * q0.y, rc = mult * q0.z;
-#pragma unroll
-                    for (int k = 0; k < VFD_WARP_SRC; ++k)
-                        if (kr == k) { SA[k][c] += ra; SB[k][c] += rb; SC[k][c] += rc; }
+                    SA[0][c] = fmaf(q0.x, wr0, SA[0][c]); SB[0][c] = fmaf(q0.y, wr0, SB[0][c]); SC[0][c] = fmaf(q0.z, wr0, SC[0][c]);
+                    if (VFD_WARP_SRC > 1) {
+                        SA[1][c] = fmaf(q0.x, wr1, SA[1][c]); SB[1][c] = fmaf(q0.y, wr1, SB[1][c]); SC[1][c] = fmaf(q0.z, wr1, SC[1][c]);
+                    }
                     if (sp) {      // CTA-uniform: the spatial / spatio-temporal planes are all zero otherwise
                         const float4 q1 = cf4[(Coef::kAbc + 3 + c) * Coef::R + r], q2 = cf4[(Coef::kAbc + 6 + c) * Coef::R + r];
-                        SA[VFD_WARP_SRC][c] += mult * q1.x; SB[VFD_WARP_SRC][c] += mult * q1.y; SC[VFD_WARP_SRC][c] += mult * q1.z;
-                        const float ta = mult * q2.x, tb = mult * q2.y, tc = mult * q2.z;
-#pragma unroll
-                        for (int k = VFD_WARP_SRC + 1; k < kNPred; ++k)
-                            if (kt == k) { SA[k][c] += ta; SB[k][c] += tb; SC[k][c] += tc; }
+                        constexpr int S = VFD_WARP_SRC;
+                        SA[S][c] = fmaf(q1.x, mult, SA[S][c]); SB[S][c] = fmaf(q1.y, mult, SB[S][c]); SC[S][c] = fmaf(q1.z, mult, SC[S][c]);
+                        SA[S + 1][c] = fmaf(q2.x, wt0, SA[S + 1][c]); SB[S + 1][c] = fmaf(q2.y, wt0, SB[S + 1][c]);
+                        SC[S + 1][c] = fmaf(q2.z, wt0, SC[S + 1][c]);
+                        if (VFD_WARP_SRC > 1) {
+                            SA[S + 2][c] = fmaf(q2.x, wt1, SA[S + 2][c]); SB[S + 2][c] = fmaf(q2.y, wt1, SB[S + 2][c]);
+                            SC[S + 2][c] = fmaf(q2.z, wt1, SC[S + 2][c]);
+                        }
                     }
                 }
             }

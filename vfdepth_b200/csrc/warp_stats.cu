@@ -14,6 +14,10 @@ namespace vfd {
 
 constexpr int kStatThreads = 256;
 constexpr int kStatPx = 8;   // pixels per thread
+// A CTA owns a kStatTW x kStatTH pixel tile (thread = one column of a 64-wide tile, every 4th row): a compact tile lets
+// the CTA prove, from the tile's depth range, that a spatial / spatio-temporal warp leaves the neighbour camera's image
+// for ALL of its pixels and skip that warp -- the common case, the overlap with a neighbour is a band at one side.
+constexpr int kStatTW = 64, kStatTH = (kStatThreads / kStatTW) * kStatPx;
 
 struct StatsArgs {
     vfd_warp_desc d;
@@ -31,36 +35,122 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-__global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArgs a) {
+// Can warp j sample anything but zeros somewhere in the tile?  cam = P @ [d * ray(u, v); 1] is linear in (d*u, d*v, d), so
+// over the box [u0,u1] x [v0,v1] x [dmin,dmax] it stays inside the hull of the 8 corner values; when the 8 denominators
+// share a sign and are well away from 0 (relative to the terms they are summed from), the sampling coordinate
+// cam.xy / den stays inside the hull of the 8 corner coordinates.  The warp is skipped when that hull is clear of
+// [-1, W] x [-1, H] (outside of which bilinear zeros-padding sample, nearest mask and in-bounds flag are all 0,
+// warp_sample) by a margin that dwarfs the fp32 error of the per-pixel evaluation.  Anything non-finite or close
+// to the camera plane fails a comparison and keeps the warp.  Called by 8 consecutive lanes (lane & 7 = corner).
+__device__ __forceinline__ bool warp_leaves_image(const float* invK, const float* P, float u0, float u1, float v0, float v1,
+                                                  float dmin, float dmax, int W, int H, int corner) {
+    float X[3], cam[3], g[2];
+    vfd_backproject(invK, (corner & 1) ? u1 : u0, (corner & 2) ? v1 : v0, (corner & 4) ? dmax : dmin, X);
+    vfd_reproject(P, X, W, H, cam, g);
+    const float ix = vfd_unnormalize(g[0], W), iy = vfd_unnormalize(g[1], H);
+    const float den = cam[2] + 1e-7f;
+    const float mag = fabsf(P[8] * X[0]) + fabsf(P[9] * X[1]) + fabsf(P[10] * X[2]) + fabsf(P[11]);
+    // sign of den with a relative floor; 0 = too close to the camera plane (or NaN)
+    int sgn = (den > 1e-3f * mag) ? 1 : ((den < -1e-3f * mag) ? -1 : 0);
+    float xlo = ix - (4.f + 2e-3f * fabsf(ix)), xhi = ix + (4.f + 2e-3f * fabsf(ix));
+    float ylo = iy - (4.f + 2e-3f * fabsf(iy)), yhi = iy + (4.f + 2e-3f * fabsf(iy));
+    bool same = true;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        // (shuffles outside the && chains: every lane must execute them)
+        const int other_sgn = __shfl_xor_sync(0xffffffffu, sgn, o);
+        same = same && (other_sgn == sgn);
+        const int other_same = __shfl_xor_sync(0xffffffffu, (int)same, o);
+        same = same && (other_same != 0);
+        xlo = fminf(xlo, __shfl_xor_sync(0xffffffffu, xlo, o));
+        xhi = fmaxf(xhi, __shfl_xor_sync(0xffffffffu, xhi, o));
+        ylo = fminf(ylo, __shfl_xor_sync(0xffffffffu, ylo, o));
+        yhi = fmaxf(yhi, __shfl_xor_sync(0xffffffffu, yhi, o));
+    }
+    // fminf / fmaxf drop a NaN operand: a NaN coordinate must keep the warp
+    const bool finite = !(isnan(ix) || isnan(iy) || isinf(ix) || isinf(iy));
+    bool all_finite = finite;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        const int other = __shfl_xor_sync(0xffffffffu, (int)all_finite, o);
+        all_finite = all_finite && (other != 0);
+    }
+    if (!same || sgn == 0 || !all_finite) return false;
+    return xhi < -1.f || xlo > (float)W || yhi < -1.f || ylo > (float)H;
+}
+
+__global__ void __launch_bounds__(kStatThreads, 5) warp_stats_kernel(const StatsArgs a) {
     const vfd_warp_desc& d = a.d;
     __shared__ WarpCtx ctx;
     __shared__ double sacc[kMaxW][8];
+    __shared__ float s_dmin[kStatThreads / 32], s_dmax[kStatThreads / 32];
+    __shared__ int s_bad[kStatThreads / 32], s_skip[kMaxW];
+    // per pixel of the tile: the target's self-occlusion mask and channel sum -- the same for all NW warps, and read by
+    // the warp loop right after the sampler's own (dependent) loads, where one more global round trip hurt
+    __shared__ float s_rmask[kStatPx][kStatThreads], s_rsum[kStatPx][kStatThreads];
     const int b = blockIdx.z, ci = blockIdx.y, cam = d.cam0 + ci;
     const int W = d.W, H = d.H, HW = H * W;
     warp_ctx_init(ctx, d, a.T, nullptr, b, ci);
     for (int i = threadIdx.x; i < kMaxW * 8; i += kStatThreads) (&sacc[0][0])[i] = 0.0;
-    __syncthreads();
-    const int NW = ctx.NW;
-    const int lane = threadIdx.x & 31;
-    const float inv_w = 1.0f / (float)W;
-    const int p0 = blockIdx.x * kStatThreads * kStatPx + threadIdx.x;
+    const int tiles_x = (W + kStatTW - 1) / kStatTW;
+    const int tx0 = (blockIdx.x % tiles_x) * kStatTW, ty0 = (blockIdx.x / tiles_x) * kStatTH;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int u = tx0 + (threadIdx.x % kStatTW), v0 = ty0 + threadIdx.x / kStatTW;
+    constexpr int kRowStep = kStatThreads / kStatTW;
     const float* depth = a.depth + (size_t)(b * d.n_call + ci) * HW;
     const float* ref = d.color[0] + (size_t)(b * d.num_cams + cam) * 3 * HW;
     const float* rmask = d.mask + (size_t)(b * d.num_cams + cam) * HW;
+
+    // the tile's depth range (the depths are read again, from L1 / L2, by the warp loop)
+    {
+        float lo = INFINITY, hi = -INFINITY;
+        bool bad = false;
+#pragma unroll
+        for (int k = 0; k < kStatPx; ++k) {
+            const int v = v0 + k * kRowStep;
+            if (u < W && v < H) {
+                const float dep = __ldg(depth + v * W + u);
+                lo = fminf(lo, dep);
+                hi = fmaxf(hi, dep);
+                bad = bad || !isfinite(dep);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        }
+        const bool any_bad = __any_sync(0xffffffffu, bad);
+        if (lane == 0) { s_dmin[wid] = lo; s_dmax[wid] = hi; s_bad[wid] = any_bad; }
+    }
+    __syncthreads();
+    const int NW = ctx.NW;
+    if (threadIdx.x < kMaxW * 8) {     // 8 lanes per warp j, one per corner of the (u, v, depth) box
+        const int j = threadIdx.x >> 3;
+        float lo = s_dmin[0], hi = s_dmax[0];
+        int bad = s_bad[0];
+#pragma unroll
+        for (int w = 1; w < kStatThreads / 32; ++w) { lo = fminf(lo, s_dmin[w]); hi = fmaxf(hi, s_dmax[w]); bad |= s_bad[w]; }
+        const int jj = j < NW ? j : 0;
+        const bool out = warp_leaves_image(ctx.invK, ctx.P[jj], (float)tx0, (float)min(tx0 + kStatTW - 1, W - 1), (float)ty0,
+                                           (float)min(ty0 + kStatTH - 1, H - 1), lo, hi, W, H, threadIdx.x & 7);
+        if ((threadIdx.x & 7) == 0) s_skip[j] = (j < NW && out && !bad && lo <= hi) ? 1 : 0;
+    }
 
     // target image: unmasked sum and sum of squares (shared by all warps of this camera)
     {
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int k = 0; k < kStatPx; ++k) {
-            const int p = p0 + k * kStatThreads;
-            if (p < HW) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    const float r = __ldg(ref + c * HW + p);
-                    s1 += r;
-                    s2 = fmaf(r, r, s2);
-                }
+            const int v = v0 + k * kRowStep;
+            if (u < W && v < H) {
+                const int p = v * W + u;
+                const float r0 = __ldg(ref + p), r1 = __ldg(ref + HW + p), r2 = __ldg(ref + 2 * HW + p);
+                s1 += r0; s2 = fmaf(r0, r0, s2);
+                s1 += r1; s2 = fmaf(r1, r1, s2);
+                s1 += r2; s2 = fmaf(r2, r2, s2);
+                s_rsum[k][threadIdx.x] = r0 + r1 + r2;
+                s_rmask[k][threadIdx.x] = __ldg(rmask + p);
             }
         }
         s1 = warp_sum(s1);
@@ -70,21 +160,17 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
             atomicAdd(&sacc[0][6], (double)s2);
         }
     }
+    __syncthreads();
     unsigned long long vb = 0ull;      // validity bits of this thread's kStatPx pixels, one byte each
     for (int j = 0; j < NW; ++j) {
-        if (!ctx.active[j]) continue;
+        if (!ctx.active[j] || s_skip[j]) continue;
         float4* raw = a.raw + ((size_t)(b * d.n_call + ci) * NW + j) * HW;
         float cnt = 0.f, srm = 0.f, swm = 0.f, sw1 = 0.f, sw2 = 0.f;
 #pragma unroll 2
         for (int k = 0; k < kStatPx; ++k) {
-            const int p = p0 + k * kStatThreads;
-            if (p >= HW) break;
-            // row / column without an integer division: (p + 0.5) / W is at least 0.5 / W away from an integer, far more
-            // than the fp32 error of the product for H * W < 2^22 (check_warp_desc bounds it); one fix-up step for safety
-            int v = __float2int_rz(((float)p + 0.5f) * inv_w);
-            int u = p - v * W;
-            if (u < 0) { u += W; --v; }
-            if (u >= W) { u -= W; ++v; }
+            const int v = v0 + k * kRowStep;
+            if (u >= W || v >= H) continue;
+            const int p = v * W + u;
             float X[3];
             vfd_backproject(ctx.invK, (float)u, (float)v, __ldg(depth + p), X);
             const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
@@ -92,14 +178,14 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
                 raw[p] = make_float4(s.v[0], s.v[1], s.v[2], s.m);
                 vb |= 1ull << (8 * k + j);
             }
-            const bool m = (__ldg(rmask + p) * s.m) != 0.f;   // (src_mask * warp_mask).bool()  (:46)
+            const bool m = (s_rmask[k][threadIdx.x] * s.m) != 0.f;   // (src_mask * warp_mask).bool()  (:46)
             const float w3 = s.v[0] + s.v[1] + s.v[2];
             sw1 += w3;
             sw2 += s.v[0] * s.v[0] + s.v[1] * s.v[1] + s.v[2] * s.v[2];
             if (m) {
                 cnt += 1.f;
                 swm += w3;
-                srm += __ldg(ref + p) + __ldg(ref + HW + p) + __ldg(ref + 2 * HW + p);
+                srm += s_rsum[k][threadIdx.x];
             }
         }
         cnt = warp_sum(cnt); srm = warp_sum(srm); swm = warp_sum(swm); sw1 = warp_sum(sw1); sw2 = warp_sum(sw2);
@@ -115,8 +201,8 @@ __global__ void __launch_bounds__(kStatThreads) warp_stats_kernel(const StatsArg
         uint8_t* vbits = a.vbits + (size_t)(b * d.n_call + ci) * HW;
 #pragma unroll
         for (int k = 0; k < kStatPx; ++k) {
-            const int p = p0 + k * kStatThreads;
-            if (p < HW) vbits[p] = (uint8_t)(vb >> (8 * k));
+            const int v = v0 + k * kRowStep;
+            if (u < W && v < H) vbits[v * W + u] = (uint8_t)(vb >> (8 * k));
         }
     }
     __syncthreads();
@@ -167,7 +253,7 @@ int check_warp_desc(const vfd_warp_desc* d) {
     if (d->B < 1 || d->num_cams < 1 || d->num_cams > VFD_MAX_CAMS || d->H < 2 || d->W < 2) return VFD_ERR_DESC;
     if (d->n_src < 1 || d->n_src > VFD_WARP_SRC) return VFD_ERR_UNSUPPORTED;
     if (d->cam0 < 0 || d->n_call < 1 || d->cam0 + d->n_call > d->num_cams) return VFD_ERR_DESC;
-    if ((long)d->H * d->W >= (1L << 22)) return VFD_ERR_DESC;      // pixel indices are exact in fp32, see warp_stats_kernel
+    if ((long)d->H * d->W >= (1L << 22)) return VFD_ERR_DESC;      // pixel indices and coordinates stay exact in fp32
     for (int f = 0; f <= d->n_src; ++f)
         if (!d->color[f]) return VFD_ERR_NULL;
     if (!d->mask || !d->K || !d->invK) return VFD_ERR_NULL;
@@ -191,8 +277,7 @@ extern "C" int vfd_warp_stats(const vfd_warp_desc* d, const float* depth, const 
     static_assert(kMaxW <= 8, "one validity byte per pixel");
     StatsArgs a = {*d, depth, T, stats, params, reinterpret_cast<float4*>(raw),
                    reinterpret_cast<uint8_t*>(reinterpret_cast<float4*>(raw) + warp_raw_f4(*d))};
-    const int HW = d->H * d->W, per = kStatThreads * kStatPx;
-    dim3 grid((HW + per - 1) / per, d->n_call, d->B);
+    dim3 grid(((d->W + kStatTW - 1) / kStatTW) * ((d->H + kStatTH - 1) / kStatTH), d->n_call, d->B);
     warp_stats_kernel<<<grid, kStatThreads, 0, st>>>(a);
     VFD_CHECK_LAUNCH();
     const int nt = d->n_call * NW;
