@@ -55,6 +55,8 @@ def parse():
     ap.add_argument('--batch', type=int, default=BATCH)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--e2e-grads', action='store_true',
+                    help='e2e also copies the gradients (d_feats, d_disp: 236 MB per 8 rigs) to the host every step')
     ap.add_argument('--no-graph', action='store_true', help='launch the resident step eagerly instead of replaying a CUDA graph')
     ap.add_argument('--no-warp', action='store_true', help='time the fusion half only')
     ap.add_argument('--no-extras', action='store_true', help='headline only: no full_step / train_step / torch_cuda_baseline')
@@ -181,16 +183,20 @@ class FusionWorkload:
     def compute(self, staged):
         return self.step(*staged)
 
-    def download(self, result):
+    def download(self, result, grads_too=False):
+        """the step's result read back by the host: one element of the ray samples (this half has no loss of its own).
+        ``grads_too``: also d_feats, 189 MB per 8 rigs -- in training it never leaves the device (the encoder's backward
+        consumes it there)"""
         rows, d_feats = result
-        self.d_feats_host.copy_(d_feats.permute(0, 1, 3, 4, 2), non_blocking=True)
+        if grads_too:
+            self.d_feats_host.copy_(d_feats.permute(0, 1, 3, 4, 2), non_blocking=True)
         self.h_scalar.copy_(rows[0, 0, 0, 0, 0, :1], non_blocking=True)
 
     def h2d_bytes(self):
         return self.h_feats.numel() * 4 + sum(v.numel() * 4 for v in self.h_small.values())
 
-    def d2h_bytes(self):
-        return self.d_feats_host.numel() * 4 + 4
+    def d2h_bytes(self, grads_too=False):
+        return (self.d_feats_host.numel() * 4 if grads_too else 0) + 4
 
     def algorithmic_bytes(self):
         """per launch, SURVEY.md 8d: unique inputs read once + required outputs written once (fp32)."""
@@ -548,6 +554,20 @@ def run_ours(args):
             ev.record(copy_stream)
         return staged, ev
 
+    e2e_graphs, dl_ev = {}, {0: None, 1: None}
+
+    def compute_slot(slot, staged):
+        """the public-API calls of one step on the staged inputs of `slot`; replayed from a CUDA graph captured per
+        staging slot (the staging tensors are fixed per slot) unless --no-graph"""
+        if args.no_graph:
+            return [p.compute(x) for p, x in zip(parts, staged)]
+        if slot not in e2e_graphs:
+            from vfdepth_b200 import graph as vgraph
+            e2e_graphs[slot] = vgraph.capture(lambda: [p.compute(x) for p, x in zip(parts, staged)], warmup=1)
+        replay, outs = e2e_graphs[slot]
+        replay()
+        return outs
+
     def run_e2e(steps):
         """the public API fed from pinned host buffers: every step's inputs are copied host->device and its results
         device->host inside the timed region; the copy of step i+1 is issued before the compute of step i (two extra
@@ -560,16 +580,21 @@ def run_ours(args):
             if i + 1 < steps:
                 nxt = stage((i + 1) % 2)
             main.wait_event(ev)
-            results = [p.compute(x) for p, x in zip(parts, staged)]
+            if dl_ev[i % 2] is not None:       # the graph rewrites this slot's result tensors in place
+                main.wait_event(dl_ev[i % 2])
+            results = compute_slot(i % 2, staged)
             done = torch.cuda.Event()
             done.record(main)
             free_ev[i % 2] = done
             with torch.cuda.stream(out_stream):
                 out_stream.wait_event(done)
                 for p, r in zip(parts, results):
-                    p.download(r)
-            for t in _tensors(results):
-                t.record_stream(out_stream)
+                    p.download(r, args.e2e_grads)
+                dl_ev[i % 2] = torch.cuda.Event()
+                dl_ev[i % 2].record(out_stream)
+            if args.no_graph:                  # eager results come from the caching allocator: keep them alive for the D2H
+                for t in _tensors(results):
+                    t.record_stream(out_stream)
         main.wait_stream(out_stream)
         main.wait_stream(copy_stream)
 
@@ -616,13 +641,19 @@ def run_ours(args):
         run_e2e(4)          # allocator steady state for the per-step results
         ms_e2e = timed(lambda: run_e2e(args.steps), 1, world)
         h2d = wl.h2d_bytes() + (warp.h2d_bytes() if warp else 0)
-        d2h = wl.d2h_bytes() + (warp.d2h_bytes() if warp else 0)
+        d2h = wl.d2h_bytes(args.e2e_grads) + (warp.d2h_bytes(args.e2e_grads) if warp else 0)
         e2e = {'value': rigs / (ms_e2e * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                'ms_per_step': ms_e2e / args.steps,
-               'how': 'pinned host buffers; H2D of step i+1 on a copy stream while step i computes, D2H on a third stream. '
-                      'Images travel as uint8 (what every dataset stores) and are converted on the device inside the timed '
+               'cuda_graph': not args.no_graph,
+               'how': 'pinned host buffers; H2D of step i+1 on a copy stream while step i computes, D2H on a third stream; the '
+                      'public-API calls of a step are replayed from a CUDA graph captured per staging slot. D2H = the step\'s result '
+                      '(loss + one ray sample)%s. '
+                      'Images and masks travel as uint8 (what every dataset stores) and are converted on the device inside the timed '
                       'region; %d of the H2D bytes are the fp32 feature maps, which stand in for an encoder that lives on '
-                      'the device in training (they never exist on the host there)' % (wl.h_feats.numel() * 4)}
+                      'the device in training (they never exist on the host there)'
+                      % (' and the gradients d_feats / d_disp' if args.e2e_grads else '; the gradients stay on the device, where '
+                         'the encoder / decoder backward consumes them in training (--e2e-grads copies them too)',
+                         wl.h_feats.numel() * 4)}
     clocks = sampler.stop() if rank == 0 else None
 
     extras = {}

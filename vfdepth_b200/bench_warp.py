@@ -21,7 +21,8 @@ class WarpWorkload:
         # end to end the images travel as uint8 -- what every dataset stores and a loader hands over -- and become the
         # float tensors the reference consumes on the device (the reference's loaders do ToTensor on the host)
         self.color_keys = [('color', f, 0) for f in self.frames]
-        self.h_u8 = {k: pin((inputs[k] * 255.0).round().clamp(0, 255).to(torch.uint8)) for k in self.color_keys}
+        # (the self-occlusion masks too: the datasets keep them as 0 / 255 PNGs)
+        self.h_u8 = {k: pin((inputs[k] * 255.0).round().clamp(0, 255).to(torch.uint8)) for k in self.color_keys + ['mask']}
         self.h_disp = pin(torch.cat(ex['disp'], 1))                   # [B,6,H,W] decoder output of scale 0
         self.h_noise = pin(torch.stack(ex['noise'], 1))               # [B,6,2,H,W]
         self.h_T = {f: pin(ex['cam_T_cam'][f]) for f in self.frames[1:]}
@@ -68,21 +69,24 @@ class WarpWorkload:
 
     def compute(self, staged):
         inputs, disp, noise, T, u8 = staged
-        for k, v in u8.items():          # uint8 -> float in [0, 1] on the compute stream, into the preallocated tensors
-            torch.mul(v, 1.0 / 255.0, out=inputs[k])
+        for k, v in u8.items():          # uint8 -> float in [0, 1] on the compute stream (ToTensor's x / 255), preallocated
+            torch.div(v, 255.0, out=inputs[k])
         return self.step(inputs, disp, noise, T)
 
-    def download(self, result):
+    def download(self, result, grads_too=False):
+        """the step's result: the loss.  The gradients stay on the device, where the decoder's backward consumes them in
+        training (``grads_too``: also d loss / d disparity, 47 MB per 8 rigs)"""
         total, grads = result
-        self.h_out.copy_(grads[0], non_blocking=True)
+        if grads_too:
+            self.h_out.copy_(grads[0], non_blocking=True)
         self.h_loss.copy_(total.detach().reshape(1), non_blocking=True)
 
     def h2d_bytes(self):
         ts = [self.h_u8.get(k, v) for k, v in self.h_inputs.items()] + [self.h_disp] + list(self.h_T.values())
         return sum(t.numel() * t.element_size() for t in ts)
 
-    def d2h_bytes(self):
-        return self.h_out.numel() * 4 + 4
+    def d2h_bytes(self, grads_too=False):
+        return (self.h_out.numel() * 4 if grads_too else 0) + 4
 
     def algorithmic_bytes(self):
         """per launch: unique inputs read once + required outputs written once."""
