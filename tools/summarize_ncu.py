@@ -22,6 +22,7 @@ ABI = [('voxel_fuse_gather', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_scatter', 'vfd_
        ('warp_loss_bwd_kernel<true>', 'vfd_warp_loss_train_fwd'), ('warp_loss_bwd', 'vfd_warp_loss_bwd'),
        ('warp_grad_combine', 'vfd_warp_loss_train_bwd'), ('warp_dT_reduce', 'vfd_warp_loss_train_bwd'),
        ('to_depth_fwd', 'vfd_to_depth_fwd'), ('to_depth_bwd', 'vfd_to_depth_bwd'),
+       ('to_depth_same_fwd', 'vfd_to_depth_fwd'), ('to_depth_same_bwd', 'vfd_to_depth_bwd'),
        ('depth_syn_fwd', 'vfd_depth_syn_fwd'), ('depth_syn_bwd', 'vfd_depth_syn_bwd'), ('voxel_count', 'vfd_voxel_classify'),
        ('voxel_scan', 'vfd_voxel_classify'), ('voxel_slot', 'vfd_voxel_classify'),
        ('smooth_mean', 'vfd_smooth_loss_train_fwd'), ('smooth_loss_kernel', 'vfd_smooth_loss_fwd'),
