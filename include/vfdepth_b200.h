@@ -35,7 +35,8 @@ typedef enum vfd_status {
     VFD_ERR_ALIGN = -3,     /* a pointer / leading dimension violates the stated alignment */
     VFD_ERR_WORKSPACE = -4, /* workspace too small */
     VFD_ERR_CUDA = -5,      /* cudaGetLastError() after launch was not cudaSuccess */
-    VFD_ERR_UNSUPPORTED = -6
+    VFD_ERR_UNSUPPORTED = -6,
+    VFD_ERR_STATIC_LIMIT = -7 /* size exceeds the fixed capacity of a no-allocation (static scratch) entry point */
 } vfd_status;
 
 int vfd_version(void);
@@ -271,6 +272,20 @@ int vfd_warp_loss_train_bwd(const vfd_warp_desc* d, const float* d_num, const fl
  * Both buffers are zero-filled here. */
 int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* color, const float* disp, double* img_sum,
                         double* sums, void* stream);
+/* No-allocation variant of vfd_smooth_loss_fwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The per-image disparity sums -- the `img_sum` scratch the entry point above takes from the caller -- live in a
+ * file-scope `static __device__` array inside the library (csrc/smooth_loss.cu), VFD_SMOOTH_STATIC_MAX_IMAGES doubles
+ * = 32 KB that every GPU which loads the library holds until the process exits.  Same arguments and results otherwise:
+ * color [B,cams,3,H,W] (may be NULL), disp [B,cams,H,W], sums [cams][2] f64 out (zero-filled here).
+ *   - B * cams > VFD_SMOOTH_STATIC_MAX_IMAGES is rejected with VFD_ERR_STATIC_LIMIT before anything is launched.
+ *   - Calls no cudaMalloc / cudaFree / allocating library routine: the array's device address is looked up with
+ *     cudaGetSymbolAddress once per device (the device current at the call), then memset + two launches on `stream`.
+ *   - Every call on a device shares the array, which keeps the previous call's contents: the entries a call uses are
+ *     cleared on `stream` first.  Calls that overlap on the GPU (different streams, no ordering) race on it. */
+#define VFD_SMOOTH_STATIC_MAX_IMAGES 4096
+int vfd_smooth_loss_fwd_static(int B, int cams, int H, int W, const float* color, const float* disp, double* sums,
+                               void* stream);
 /* backward w.r.t. disp:  d_smooth [cams] upstream gradient of the per-camera loss, gdot [B*cams] f64 scratch
  * (zero-filled here), d_disp [B,cams,H,W] written. */
 int vfd_smooth_loss_bwd(int B, int cams, int H, int W, const float* color, const float* disp, const double* img_sum,

@@ -59,7 +59,7 @@ int main(void) {
 def test_error_strings():
     lib = _lib.load()
     assert lib.vfd_last_error(0) == b'ok'
-    for code in range(-6, 0):
+    for code in range(-7, 0):
         assert lib.vfd_last_error(code) not in (b'ok', b'unknown vfd_status')
     assert lib.vfd_last_error(-99) == b'unknown vfd_status'
 

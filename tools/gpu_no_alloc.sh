@@ -4,6 +4,4 @@ timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out
 tail -4 gpurun_out/pytest_no_alloc_alone.log
 timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_all.log 2>&1; echo "all rc=$?" >> gpurun_out/rc_no_alloc.log
 tail -4 gpurun_out/pytest_all.log
-timeout 300 compute-sanitizer --tool memcheck python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/sanitizer_no_alloc.log 2>&1; echo "memcheck rc=$?" >> gpurun_out/rc_no_alloc.log
-grep -E "ERROR SUMMARY|passed|failed" gpurun_out/sanitizer_no_alloc.log | tail -3
 cat gpurun_out/rc_no_alloc.log

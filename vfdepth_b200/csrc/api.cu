@@ -12,6 +12,8 @@ extern "C" const char* vfd_last_error(int code) {
         case VFD_ERR_WORKSPACE: return "workspace too small";
         case VFD_ERR_CUDA: return "CUDA reported an error at launch";
         case VFD_ERR_UNSUPPORTED: return "configuration not supported by this build";
+        case VFD_ERR_STATIC_LIMIT:
+            return "size exceeds the fixed capacity of this no-allocation entry point's static device scratch";
         default: return "unknown vfd_status";
     }
 }

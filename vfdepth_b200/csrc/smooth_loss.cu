@@ -7,6 +7,8 @@
 // launch and the loss one stencil launch (fp32 per thread, fp64 across threads); the backward to disp (the only
 // differentiable input) is a stencil launch that also accumulates sum_i g_i * disp_i per image for the mean's chain
 // rule, and a finishing launch.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace vfd {
@@ -247,6 +249,32 @@ static dim3 smooth_grid(int B, int cams, int H, int W) {
     return dim3(bx, B * cams);
 }
 
+// ---- no-allocation variant of the forward: the per-image disparity sums live in library-owned device memory ----
+// File-scope device array: every GPU that loads the library holds these VFD_SMOOTH_STATIC_MAX_IMAGES * 8 bytes (32 KB)
+// until the process exits.  In HOST code the name below is only a stand-in for the symbol, not a device address; the
+// address is looked up once per device with cudaGetSymbolAddress (static_scratch) and that pointer goes to the kernels.
+static __device__ __align__(256) double vfd_smooth_static_img_sum[VFD_SMOOTH_STATIC_MAX_IMAGES];
+
+constexpr int kMaxDevices = 64;
+// device address of the array on the CURRENT device, nullptr on failure.  One look-up per device and process; the
+// pointer is published with release / acquire so that concurrent host threads either see it or look it up again (the
+// look-up is idempotent).
+static double* static_scratch() {
+    static std::atomic<double*> cache[kMaxDevices];
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+    double* p = cache[dev].load(std::memory_order_acquire);
+    if (p) return p;
+    void* addr = nullptr;
+    if (cudaGetSymbolAddress(&addr, vfd_smooth_static_img_sum) != cudaSuccess || !addr) {
+        (void)cudaGetLastError();      // do not leave the failure behind for the caller's next launch check
+        return nullptr;
+    }
+    p = static_cast<double*>(addr);
+    cache[dev].store(p, std::memory_order_release);
+    return p;
+}
+
 }  // namespace vfd
 
 using namespace vfd;
@@ -256,6 +284,30 @@ extern "C" int vfd_smooth_loss_fwd(int B, int cams, int H, int W, const float* c
     int rc = check_smooth(B, cams, H, W);
     if (rc) return rc;
     if (!disp || !img_sum || !sums) return VFD_ERR_NULL;      // color may be NULL
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(img_sum, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
+    if (cudaMemsetAsync(sums, 0, sizeof(double) * cams * 2, st) != cudaSuccess) return VFD_ERR_CUDA;
+    SmoothArgs a = {};
+    a.B = B; a.cams = cams; a.H = H; a.W = W; a.color = color; a.disp = disp; a.img_sum = img_sum; a.sums = sums;
+    const dim3 grid = smooth_grid(B, cams, H, W);
+    smooth_mean_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    smooth_loss_kernel<<<grid, kSmoothThreads, 0, st>>>(a);
+    VFD_CHECK_LAUNCH();
+    return VFD_OK;
+}
+
+// Same two launches as vfd_smooth_loss_fwd with img_sum in the library's static device array: no cudaMalloc / cudaFree /
+// allocating routine on this path (cudaGetSymbolAddress on a device's first call, cudaMemsetAsync, two launches).  The
+// array is shared by every call on the device and keeps the last call's contents, so its first B*cams entries are
+// cleared here, on `stream`; two calls that overlap on the GPU (different streams) race on it.
+extern "C" int vfd_smooth_loss_fwd_static(int B, int cams, int H, int W, const float* color, const float* disp,
+                                          double* sums, void* stream) {
+    int rc = check_smooth(B, cams, H, W);
+    if (rc) return rc;
+    if ((long)B * cams > VFD_SMOOTH_STATIC_MAX_IMAGES) return VFD_ERR_STATIC_LIMIT;
+    if (!disp || !sums) return VFD_ERR_NULL;      // color may be NULL
+    double* img_sum = static_scratch();
+    if (!img_sum) return VFD_ERR_CUDA;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(img_sum, 0, sizeof(double) * B * cams, st) != cudaSuccess) return VFD_ERR_CUDA;
     if (cudaMemsetAsync(sums, 0, sizeof(double) * cams * 2, st) != cudaSuccess) return VFD_ERR_CUDA;
