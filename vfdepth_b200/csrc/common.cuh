@@ -155,24 +155,4 @@ __device__ __forceinline__ void bulk_load_g2s(void* sdst, const void* gsrc, uint
                  : "memory");
 }
 
-// L2 eviction policy for data that is streamed through once (so that it does not push resident lines out)
-__device__ __forceinline__ uint64_t l2_evict_first_policy() {
-    uint64_t p;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-    return p;
-}
-__device__ __forceinline__ void bulk_load_g2s_hint(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar,
-                                                   uint64_t policy) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
-            smem_u32(sdst)),
-        "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
-        : "memory");
-}
-__device__ __forceinline__ void st_stream_f4_hint(float* p, float4 v, uint64_t policy) {
-    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v.x),
-                 "f"(v.y), "f"(v.z), "f"(v.w), "l"(policy)
-                 : "memory");
-}
-
 }  // namespace vfd

@@ -358,7 +358,14 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
             // the gradient column is read once, straight from HBM: keep kPf rows per lane in flight (next chunk is
-            // requested before the current one is consumed)
+            // requested before the current one is consumed).
+            // Measured alternatives, all slower than this form's 0.85 ms at B=8 (that kernel is in the history: commit 51c8f75, which ran the register form at bench size because of a shared-memory cap): the column
+            // staged through a per-warp shared-memory ring by cp.async.bulk with mbarrier completion, 512-byte rows,
+            // 16 / 12 / 8 rows in flight, issue cursor running ahead across tasks -- 1.31 / 1.33 / 1.24 ms at 2 and 3
+            // CTAs per SM (one wait + warp sync + re-arm per 512-byte row costs more than the registers it frees);
+            // kPf = 2 or 1 at 3 CTAs per SM -- 0.87 / 1.04 ms; a task order that spreads the resident warps over the
+            // six cameras and distant columns -- 0.95 ms (the reductions want the L2 locality of neighbouring
+            // columns, not more parallelism).
             constexpr int kPf = 4;
             float4 g[kPf], gn[kPf];
 #pragma unroll
@@ -437,147 +444,6 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
     }
 }
 
-// The same backward with the gradient column staged through shared memory by the bulk-copy engine (cp.async.bulk,
-// completion on mbarriers): every warp owns a ring of kRayRing rows (one row = the 512 contiguous bytes its 32 lanes
-// consume per image row) that lane 0 keeps full -- across task boundaries too, so the HBM stream also runs while the
-// warp builds the next column's slots.  The register-prefetch form above keeps 4 + 4 rows per lane in flight at 126
-// registers; here 16 rows per warp are in flight and cost no registers.  (Three or four CTAs per SM -- 80 registers, an 8-row ring --
-// were measured SLOWER, 1.24 / 1.49 ms against 0.85, and so was an order that spreads the resident warps over cameras and
-// distant columns, 0.95 ms: the reductions want the locality of neighbouring columns in L2, not more parallelism.)
-// The stream is tagged L2 evict-first: it is read once, and the volume's lines should stay.
-constexpr int kRayRing = 16;
-constexpr int kRayBulkMinBlocks = 2;   // CTAs per SM the bulk kernel is compiled for
-constexpr long kRayBulkGrid = 148 * kRayBulkMinBlocks * 8;
-constexpr int kRayRowBytes = VFD_WARP * 16;
-
-template <int CV>
-__global__ void __launch_bounds__(kRayWarps* VFD_WARP, kRayBulkMinBlocks) ray_sample_bwd_bulk_kernel(const RayArgs a) {
-    constexpr int kLanes = CV / 4, kBins = VFD_WARP / kLanes;
-    const vfd_fusion_desc& d = a.d;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int q = lane / kLanes, l = lane % kLanes;
-    const int H = d.h, W = d.w, D = d.D;
-    const long ntasks = (long)d.B * d.num_cams * W * ((D + kBins - 1) / kBins);
-    const long tstride = (long)gridDim.x * kRayWarps;
-    RaySlotW* slot = reinterpret_cast<RaySlotW*>(vfd_ray_smem) + warp * kBins * H;
-    char* ring_all = reinterpret_cast<char*>(vfd_ray_smem) + (size_t)kRayWarps * kBins * H * sizeof(RaySlotW);
-    char* ring = ring_all + (size_t)warp * kRayRing * kRayRowBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(ring_all + (size_t)kRayWarps * kRayRing * kRayRowBytes) + warp * kRayRing;
-    const int XC = d.X * CV, YXC = d.Y * XC;
-    const bool carry = d.X < 1023 && d.Y < 1023 && d.Z < 1023;      // packed cell coordinates hold 10 bits per axis
-    if (lane == 0) {
-        for (int i = 0; i < kRayRing; ++i) mbar_init(&bars[i], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncwarp();
-    // issue cursor (lane 0): the next row to request, possibly of a later task than the one being consumed
-    long itask = (long)blockIdx.x * kRayWarps + warp;
-    ColTask it = decode_col<kBins>(itask < ntasks ? itask : 0, d);
-    int irow = 0;
-    unsigned issued = 0, used = 0;
-    const uint64_t policy = l2_evict_first_policy();
-    auto issue_one = [&]() {
-        if (itask >= ntasks) return;
-        const float* src = a.d_out + ((((size_t)(it.b * d.num_cams + it.c) * H + irow) * W + it.u) * D + it.d0) * CV;
-        const uint32_t bytes = (uint32_t)min(kBins, D - it.d0) * CV * sizeof(float);
-        const unsigned st = issued % kRayRing;
-        mbar_expect_tx(&bars[st], bytes);
-        bulk_load_g2s_hint(ring + st * kRayRowBytes, src, bytes, &bars[st], policy);
-        ++issued;
-        if (++irow == H) {
-            irow = 0;
-            itask += tstride;
-            if (itask < ntasks) it = decode_col<kBins>(itask, d);
-        }
-    };
-    if (lane == 0) {
-        for (int i = 0; i < kRayRing; ++i) issue_one();
-    }
-    for (long task = (long)blockIdx.x * kRayWarps + warp; task < ntasks; task += tstride) {
-        const ColTask t = decode_col<kBins>(task, d);
-        col_phase1<kBins>(a, t, lane, slot);
-        __syncwarp();
-        const int dd = t.d0 + q;
-        const bool on = dd < D;
-        float* dvol = a.d_vol + (size_t)t.b * d.X * d.Y * d.Z * CV + 4 * l;
-        int cur_base = INT_MIN, cur_pk = 0;
-        unsigned cur_corners = 0;
-        float4 acc[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = f4_zero();
-        for (int v = 0; v < H; ++v) {
-            const unsigned st = used % kRayRing;
-            mbar_wait(&bars[st], (used / kRayRing) & 1u);
-            const float4 g = on ? *reinterpret_cast<const float4*>(ring + st * kRayRowBytes + lane * 16) : f4_zero();
-            ++used;
-            __syncwarp();                       // every lane has read the row: its stage may be refilled
-            if (lane == 0) {
-                fence_proxy_async_smem();
-                issue_one();
-            }
-            if (!on) continue;
-            const RaySlotW s = slot[q * H + v];
-            if (s.corners) {
-                if (s.base != cur_base) {
-                    float* p0 = dvol + (long)cur_base * CV;
-                    bool pos;
-                    const int ax = (cur_corners && carry) ? face_step(cur_pk, s.pk, &pos) : 0;
-#define VFD_RAY_BWD_STEP(AX)                                                                                        \
-    _Pragma("unroll") for (int k = 0; k < 8; ++k) {                                                                 \
-        if (!(k & AX)) {                                                                                            \
-            const int lo = k, hi = k | AX;                                                                          \
-            const int out = pos ? lo : hi;           /* the corner that leaves */                                   \
-            if (cur_corners & (1u << out))                                                                          \
-                red_add_f4(p0 + (out & 1) * CV + ((out >> 1) & 1) * XC + (out >> 2) * YXC, pos ? acc[lo] : acc[hi]); \
-            if (pos) {                                                                                              \
-                acc[lo] = acc[hi];                                                                                  \
-                f4_fma_w2(acc[lo], pack2(s.w[lo], s.w[lo]), g);                                                     \
-                f4_mul_w2(acc[hi], pack2(s.w[hi], s.w[hi]), g);                                                     \
-            } else {                                                                                                \
-                acc[hi] = acc[lo];                                                                                  \
-                f4_fma_w2(acc[hi], pack2(s.w[hi], s.w[hi]), g);                                                     \
-                f4_mul_w2(acc[lo], pack2(s.w[lo], s.w[lo]), g);                                                     \
-            }                                                                                                       \
-        }                                                                                                           \
-    }
-                    if (ax == 1) { VFD_RAY_BWD_STEP(1) }
-                    else if (ax == 2) { VFD_RAY_BWD_STEP(2) }
-                    else if (ax == 4) { VFD_RAY_BWD_STEP(4) }
-                    else {
-                        if (cur_corners) {
-#pragma unroll
-                            for (int k = 0; k < 8; ++k)
-                                if (cur_corners & (1u << k))
-                                    red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
-                        }
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) f4_mul_w2(acc[k], pack2(s.w[k], s.w[k]), g);
-                    }
-#undef VFD_RAY_BWD_STEP
-                    cur_base = s.base;
-                    cur_pk = s.pk;
-                    cur_corners = s.corners;
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) f4_fma_w2(acc[k], pack2(s.w[k], s.w[k]), g);
-                }
-            }
-        }
-        if (on && cur_corners) {
-            float* p0 = dvol + (long)cur_base * CV;
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-                if (cur_corners & (1u << k))
-                    red_add_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC, acc[k]);
-        }
-        __syncwarp();
-    }
-}
-
-static size_t ray_bulk_smem(int kb, int h) {
-    return (size_t)kRayWarps * kb * h * sizeof(RaySlotW) + (size_t)kRayWarps * kRayRing * (kRayRowBytes + sizeof(uint64_t));
-}
-
 static int check_ray_desc(const vfd_fusion_desc* d) {
     if (!d) return VFD_ERR_NULL;
     if (d->B < 1 || d->num_cams < 1 || d->num_cams > VFD_MAX_CAMS || d->h < 1 || d->w < 1 || d->X < 1 ||
@@ -605,16 +471,6 @@ static int launch_ray(const RayArgs& a, bool bwd, cudaStream_t st) {
         const long vtasks = (long)d.B * d.num_cams * d.w * ((d.D + kb - 1) / kb);                           \
         const long vblocks = (vtasks + kRayWarps - 1) / kRayWarps;                                          \
         const unsigned vgrid = (unsigned)(vblocks < kRayGrid ? vblocks : kRayGrid);                         \
-        const size_t bsmem = ray_bulk_smem(kb, d.h);                                                        \
-        if (bwd && vsmem <= 48 * 1024 && bsmem <= 100 * 1024) {                                             \
-            static const cudaError_t attr = cudaFuncSetAttribute(                                           \
-                ray_sample_bwd_bulk_kernel<CVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); \
-            if (attr != cudaSuccess) return VFD_ERR_CUDA;                                                   \
-            const unsigned bgrid = (unsigned)(vblocks < kRayBulkGrid ? vblocks : kRayBulkGrid);             \
-            ray_sample_bwd_bulk_kernel<CVAL><<<bgrid, kRayWarps * VFD_WARP, bsmem, st>>>(a);                \
-            VFD_CHECK_LAUNCH();                                                                             \
-            return VFD_OK;                                                                                  \
-        }                                                                                                   \
         if (vsmem <= 48 * 1024) {                                                                           \
             if (bwd) ray_sample_bwd_vec_kernel<CVAL><<<vgrid, kRayWarps * VFD_WARP, vsmem, st>>>(a);        \
             else ray_sample_fwd_vec_kernel<CVAL><<<vgrid, kRayWarps * VFD_WARP, vsmem, st>>>(a);            \
