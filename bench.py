@@ -467,10 +467,24 @@ def dropin_pass(warp, iters):
     one()
     ms = _event_ms(one, iters)
     rig = _event_ms(lambda: warp.step_resident(), iters)
-    return {'per_camera_modules_ms': ms, 'rig_level_call_ms': rig,
+    # the same per-camera call pattern replayed from a CUDA graph (the modules never synchronise or read back: the
+    # ~150 small torch launches of the pose products and the dict plumbing then cost no host time)
+    graph_ms = None
+    try:
+        from vfdepth_b200 import graph as vgraph
+        replay, _ = vgraph.capture(one, warmup=1)
+        replay()
+        graph_ms = _event_ms(replay, iters)
+        del replay
+    except Exception as e:  # noqa: BLE001 -- reported, not fatal: the eager number stands
+        print('bench: CUDA graph capture of the per-camera modules failed (%s)' % e, file=sys.stderr, flush=True)
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+    return {'per_camera_modules_ms': ms, 'rig_level_call_ms': rig, 'per_camera_modules_cuda_graph_ms': graph_ms,
             'what': 'to_depth + view synthesis + losses fwd+bwd of %d rigs: six ViewRendering / MultiCamLoss calls on the outputs '
                     'dict (the reference\'s call pattern, incl. the per-camera pose products; loss_dict entries stay on the '
-                    'device) against one view.warp_and_loss call; eager launches, no CUDA graph' % warp.B}
+                    'device) against one view.warp_and_loss call, both as eager launches; and the per-camera pattern replayed from a '
+                    'CUDA graph' % warp.B}
 
 
 def train_step_pass(dev, rank, world, steps):
