@@ -80,7 +80,7 @@ _lock = threading.Lock()
 _lib = None
 launches = 0   # number of kernels launched through the ABI by this process (bench.py reports it)
 # kernels one call of each entry point launches (memsets not counted); anything not listed launches one
-KERNELS_PER_CALL = {'vfd_voxel_classify': 3, 'vfd_voxel_fuse_fwd': 3, 'vfd_voxel_fuse_bwd': 5, 'vfd_warp_stats': 2, 'vfd_warp_loss_bwd': 2, 'vfd_warp_loss_train_bwd': 2,
+KERNELS_PER_CALL = {'vfd_voxel_classify': 3, 'vfd_voxel_fuse_fwd': 3, 'vfd_voxel_fuse_bwd': 5, 'vfd_warp_stats': 2, 'vfd_warp_loss_bwd': 2, 'vfd_warp_loss_train_fwd': 2, 'vfd_warp_loss_train_bwd': 2,
                     'vfd_smooth_loss_fwd': 2, 'vfd_smooth_loss_fwd_static': 2, 'vfd_smooth_loss_bwd': 2, 'vfd_smooth_loss_train_fwd': 2,
                     'vfd_feat_agg_bwd': 3, 'vfd_norm_image_fwd': 2}     # fine + one launch per coarse level (two at the shipped configs)
 

@@ -15,6 +15,9 @@ LIB = os.path.join(HERE, 'lib', 'libvfdepth_b200.so')
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '--fmad=true',
          '-Xcompiler', '-fPIC', '-Xptxas', '-v']
+# kernel-tuning experiments (tools/gpu_*.sh): extra -D defines for one build, e.g. VFD_NVCC_DEFINES="-DVFD_LOSS_THREADS=256";
+# part of the source hash, so a library built with them is rebuilt when they change.  The shipped library uses none.
+FLAGS += os.environ.get('VFD_NVCC_DEFINES', '').split()
 
 
 def sources():

@@ -7,33 +7,26 @@
 // that a second kernel adds in a fixed order -- the whole backward is deterministic.
 //   autograd of: view_rendering.py:58-82, geometry_util.py:52-77, loss_util.py:21-25,43-78,
 //                single_cam_loss.py:17-55, multi_cam_loss.py:16-59
-#include "warp_tile.cuh"
+#include "warp_loss_bwd.cuh"
 
 namespace vfd {
-
-struct LossBwdArgs {
-    vfd_warp_desc d;
-    const float* depth;
-    const float* T;
-    const float* params;
-    const float4* raw;
-    const uint8_t* vbits;
-    const float* noise;
-    const float* d_num;   // [n_call,3]
-    float* d_depth;
-    float* d_T;
-    float* partial;       // [B*n_call][tiles][kMaxW*12]
-    // fused forward + backward (training): the loss sums leave this kernel too, gradients are written per loss set and
-    // scaled by the upstream once the sums are known
-    double* sums;         // [n_call][8]
-    float* g3;            // [B,n_call,3,H,W] d loss_set / d depth with unit upstream
-};
 
 extern __shared__ __align__(16) float vfd_warp_smem[];
 
 // coefficient planes over the 1-halo ring (R1 pixels): 3 sets (reproj, spatial, spatio-temporal) x 3 channels x (a,b,c),
 // the set's upstream weight (for the L1 term) and the frame each min selected
-constexpr int kStrip = 8;   // tiles a CTA of the backward walks, top to bottom
+// Threads per CTA.  The tile is 32 x 8 pixels (phase C: 8 warps), but a strip step fills 36 x 8 = 288 region pixels and
+// evaluates 34 x 8 = 272 ring pixels: with 8 warps each of those phases is one full pass plus a second pass of ONE warp
+// while seven wait at the barrier (a quarter of the kernel's stall samples).  Ten warps take every phase in one pass; the
+// register file then gives 96 registers per thread at two CTAs per SM (five warps per scheduler).
+#ifndef VFD_LOSS_THREADS
+#define VFD_LOSS_THREADS 320
+#endif
+constexpr int kBwdThreads = VFD_LOSS_THREADS;
+// training mode (vfd_warp_loss_train_fwd): 1 = one lean kernel per loss set (warp_loss_sets.cu), 0 = this file's kernel
+#ifndef VFD_LOSS_SPLIT
+#define VFD_LOSS_SPLIT 1
+#endif
 
 // Stored as float4 planes -- (a, b, c, -) per (set, channel) and (w_reproj, w_spatial, w_st, selection bits) per pixel --
 // so that one 128-bit shared access moves what three 32-bit ones did (the scalar stores / loads of these planes were a
@@ -45,14 +38,6 @@ struct Coef {
     static constexpr int kPlanes = 10;
     static constexpr int kFloats = kPlanes * 4 * R;
 };
-
-// how many of pixel p's 3 horizontal (or vertical) window taps land on q, with reflection padding of 1
-__device__ __forceinline__ int tap_mult(int p, int q, int n) {
-    int m = 0;
-#pragma unroll
-    for (int dlt = -1; dlt <= 1; ++dlt) m += (reflect1(p + dlt, n) == q) ? 1 : 0;
-    return m;
-}
 
 constexpr int kNPred = VFD_WARP_SRC + 1 + VFD_WARP_SRC;   // differentiable images: 2 temporal, overlap_0, 2 spatio-temporal
 
@@ -95,11 +80,11 @@ __device__ __forceinline__ PixelLoss ring_pixel(const float* sm, float* cf, cons
 // overlap_0 -> spatial, overlap_+-1 -> spatio-temporal); vfd_warp_loss_train_bwd scales them by d total / d num_set once
 // autograd knows it.  The backward kernel recomputed the whole forward anyway, so the separate forward launch goes away.
 template <bool FUSED>
-__global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const LossBwdArgs a) {
+__global__ void __launch_bounds__(kBwdThreads, 2) warp_loss_bwd_kernel(const LossBwdArgs a) {
     using Rg = Region<2>;
     const vfd_warp_desc& d = a.d;
     __shared__ WarpCtx ctx;
-    __shared__ float s_dP[kTileThreads / 32][kMaxW * 12];
+    __shared__ float s_dP[kTilePixels / 32][kMaxW * 12];     // phase C runs on the tile's 8 warps
     __shared__ double sacc[8];
     __shared__ unsigned s_flags[2];
     float* sm = vfd_warp_smem;
@@ -131,24 +116,24 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     if (cont) {
         // rows 8..11 of the region -> rows 0..3, ring rows 8, 9 -> 0, 1 (sources and destinations are disjoint)
         float2* img2 = reinterpret_cast<float2*>(sm + Rg::kImg);
-        for (int i = threadIdx.x; i < 3 * kPairs * 4 * Rg::RW; i += kTileThreads) {
+        for (int i = threadIdx.x; i < 3 * kPairs * 4 * Rg::RW; i += kBwdThreads) {
             const int pl = i / (4 * Rg::RW), o = i - pl * (4 * Rg::RW);
             img2[pl * Rg::R + o] = img2[pl * Rg::R + kTileH * Rg::RW + o];
         }
         float* mk = sm + Rg::kOmask;     // the 1 + VFD_WARP_SRC overlap-mask planes and VFD_WARP_SRC colour-mask planes
-        for (int i = threadIdx.x; i < (1 + 2 * VFD_WARP_SRC) * 4 * Rg::RW; i += kTileThreads) {
+        for (int i = threadIdx.x; i < (1 + 2 * VFD_WARP_SRC) * 4 * Rg::RW; i += kBwdThreads) {
             const int pl = i / (4 * Rg::RW), o = i - pl * (4 * Rg::RW);
             mk[pl * Rg::R + o] = mk[pl * Rg::R + kTileH * Rg::RW + o];
         }
         float4* cfm = reinterpret_cast<float4*>(cf);
-        for (int i = threadIdx.x; i < Coef::kPlanes * 2 * Coef::RW; i += kTileThreads) {
+        for (int i = threadIdx.x; i < Coef::kPlanes * 2 * Coef::RW; i += kBwdThreads) {
             const int pl = i / (2 * Coef::RW), o = i - pl * (2 * Coef::RW);
             cfm[pl * Coef::R + o] = cfm[pl * Coef::R + kTileH * Coef::RW + o];
         }
         __syncthreads();      // the fill below overwrites the rows that were just read
     }
-    for (int i = threadIdx.x; i < (kTileThreads / 32) * kMaxW * 12; i += kTileThreads) (&s_dP[0][0])[i] = 0.f;
-    const unsigned fl = fill_region<2>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW,
+    for (int i = threadIdx.x; i < (kTilePixels / 32) * kMaxW * 12; i += kBwdThreads) (&s_dP[0][0])[i] = 0.f;
+    const unsigned fl = fill_region<2, kBwdThreads>(ctx, d, b, ci, ox, oy, a.raw + (size_t)(b * d.n_call + ci) * ctx.NW * HW,
                                        a.vbits + (size_t)(b * d.n_call + ci) * HW, sm, cont ? 4 : 0);
     // any spatial / spatio-temporal warp in this tile's region?  (flag words alternate between tiles; the other one is
     // cleared for the next tile now that every thread is past the previous tile's read of it)
@@ -158,7 +143,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     carried = (any >> 1) & 1u;
 
     // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
-    for (int r = (cont ? 2 * Coef::RW : 0) + threadIdx.x; r < Coef::R; r += kTileThreads) {
+    for (int r = (cont ? 2 * Coef::RW : 0) + threadIdx.x; r < Coef::R; r += kBwdThreads) {
         const int x = tx0 - 1 + r % Coef::RW, y = ty0 - 1 + r / Coef::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
@@ -328,23 +313,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
             }
         }
         if (!__any_sync(0xffffffffu, contrib)) continue;
-        {   // warp sum of the 12 values as a reduce-scatter butterfly (16 shuffles instead of 60, fixed order):
-            // after the steps over lane bits 4..1 lane l holds element l >> 1 summed over half the warp
-            float v[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = i < 12 ? dP[i] : 0.f;
-#pragma unroll
-            for (int n = 8; n >= 1; n >>= 1) {
-                const bool up = (lane & (2 * n)) != 0;
-#pragma unroll
-                for (int i = 0; i < n; ++i) {
-                    const float keep = up ? v[i + n] : v[i], send = up ? v[i] : v[i + n];
-                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2 * n);
-                }
-            }
-            v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-            if (!(lane & 1) && (lane >> 1) < 12) s_dP[wid][j * 12 + (lane >> 1)] = v[0];
-        }
+        warp_sum12_store(dP, lane, &s_dP[wid][j * 12]);
     }
     if (live) {
         if (FUSED) {
@@ -357,10 +326,10 @@ __global__ void __launch_bounds__(kTileThreads, 2) warp_loss_bwd_kernel(const Lo
     __syncthreads();
     const int ntile = gridDim.x * tiles_y, tile = tyi * gridDim.x + blockIdx.x;
     float* part = a.partial + ((size_t)blockIdx.z * ntile + tile) * (kMaxW * 12);
-    for (int i = threadIdx.x; i < ctx.NW * 12; i += kTileThreads) {
+    for (int i = threadIdx.x; i < ctx.NW * 12; i += kBwdThreads) {
         float v = 0.f;
 #pragma unroll
-        for (int w = 0; w < kTileThreads / 32; ++w) v += s_dP[w][i];
+        for (int w = 0; w < kTilePixels / 32; ++w) v += s_dP[w][i];
         part[i] = v;
     }
     __syncthreads();      // s_dP, the region and the ring are rewritten by the next tile
@@ -443,10 +412,10 @@ static size_t bwd_smem_bytes() { return (Region<2>::kFloats + Coef::kFloats) * s
 
 using namespace vfd;
 
+// d_T partial sums, then (training mode) one flag byte per tile and one auto-mask decision byte per pixel
 extern "C" size_t vfd_warp_bwd_workspace_bytes(const vfd_warp_desc* d) {
     if (check_warp_desc(d)) return 0;
-    const size_t tiles = (size_t)((d->W + kTileW - 1) / kTileW) * ((d->H + kTileH - 1) / kTileH);
-    return (size_t)d->B * d->n_call * tiles * kMaxW * 12 * sizeof(float);
+    return warp_partial_bytes(*d) + warp_tile_flag_bytes(*d) + (size_t)d->B * d->n_call * d->H * d->W;
 }
 
 extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
@@ -469,7 +438,7 @@ extern "C" int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, con
         return VFD_ERR_CUDA;
     const int tiles_x = (d->W + kTileW - 1) / kTileW, tiles_y = (d->H + kTileH - 1) / kTileH;
     dim3 grid(tiles_x, (tiles_y + kStrip - 1) / kStrip, d->B * d->n_call);
-    warp_loss_bwd_kernel<false><<<grid, kTileThreads, smem, st>>>(a);
+    warp_loss_bwd_kernel<false><<<grid, kBwdThreads, smem, st>>>(a);
     VFD_CHECK_LAUNCH();
     warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, tiles_x * tiles_y, false);
     VFD_CHECK_LAUNCH();
@@ -490,14 +459,20 @@ extern "C" int vfd_warp_loss_train_fwd(const vfd_warp_desc* d, const float* dept
     a.d = *d; a.depth = depth; a.T = T; a.params = params; a.raw = reinterpret_cast<const float4*>(raw); a.noise = noise;
     a.vbits = reinterpret_cast<const uint8_t*>(a.raw + warp_raw_f4(*d));
     a.sums = sums; a.g3 = g3; a.partial = (float*)ws;
+#if VFD_LOSS_SPLIT
+    a.tile_flag = reinterpret_cast<uint8_t*>(ws) + warp_partial_bytes(*d);
+    a.auto_bit = a.tile_flag + warp_tile_flag_bytes(*d);
+    return launch_loss_sets(a, st);
+#else
     const size_t smem = bwd_smem_bytes();
     if (cudaFuncSetAttribute(warp_loss_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return VFD_ERR_CUDA;
     const int tiles_x = (d->W + kTileW - 1) / kTileW, tiles_y = (d->H + kTileH - 1) / kTileH;
     dim3 grid(tiles_x, (tiles_y + kStrip - 1) / kStrip, d->B * d->n_call);
-    warp_loss_bwd_kernel<true><<<grid, kTileThreads, smem, st>>>(a);
+    warp_loss_bwd_kernel<true><<<grid, kBwdThreads, smem, st>>>(a);
     VFD_CHECK_LAUNCH();
     return VFD_OK;
+#endif
 }
 
 extern "C" int vfd_warp_loss_train_bwd(const vfd_warp_desc* d, const float* d_num, const float* g3, const void* ws,

@@ -9,12 +9,17 @@
 // so one LDS.64 fetches a tap of two images and add/mul.f32x2 (sm_100 packed fp32: two IEEE round-to-nearest results
 // per instruction, bit-identical to the scalar ops) update two window sums.
 //
-// Rounding.  The 3x3 means are summed tap by tap in row-major order and divided by 9 -- the order ATen's avg_pool2d
-// uses -- with un-fused multiplies and adds, so E[x^2] - mu^2 (a difference of two nearly equal numbers) carries the
-// same rounding as the reference instead of an independent 3e-8 error on a 0.25-sized quantity.  x / 9 and x / 3 are
-// computed as q = x*r; q += fma(-9, q, x) * r, which is the correctly rounded quotient for every fp32 x (checked
-// exhaustively over all 2^23 mantissas, tools/check_div_const.py).  Only the final ssim = num / den uses a fast
-// reciprocal: it is 1-2 ulp (1e-7) on a quantity whose fp32 noise floor is 5e-5.
+// Rounding.  The 3x3 window sums run tap by tap in row-major order -- the order ATen's avg_pool2d uses -- and are divided
+// by 9 with x / 9 and x / 3 computed as q = x*r; q += fma(-9, q, x) * r, the correctly rounded quotient for every fp32 x
+// (checked exhaustively over all 2^23 mantissas, tools/check_div_const.py).  The sums of x^2 and x*y accumulate with
+// FUSED multiply-adds (one rounding per tap where the reference rounds the product tensor first): ptxas contracts a
+// mul.rn.f32x2 feeding an add.rn.f32x2 into FFMA2 whatever the rounding modifiers say (found in the SASS in round 2), so
+// the source now says fma -- every kernel that evaluates the SSIM then carries the same bits (warp_loss_fwd / _bwd /
+// _sets are compared with each other bit for bit), at 3 instead of 5 packed instructions per tap and pair.  The
+// difference to the reference's un-fused sequence is below the fp32 noise floor of the SSIM itself (E[x^2] - mu^2 is a
+// difference of nearly equal numbers: 5e-5 of the loss between ANY two fp32 evaluations, the reference on CPU and on
+// CUDA included) and is covered by the parity bars (tests/test_warp_gpu.py).  Only the final ssim = num / den uses a
+// fast reciprocal: it is 1-2 ulp (1e-7) on a quantity with that noise floor.
 #pragma once
 #include "warp_common.cuh"
 
@@ -122,8 +127,8 @@ __device__ __forceinline__ void photometric8(const float2* __restrict__ img, int
             for (int q = 0; q < kPairs; ++q) {
                 if (!SP && q == 1) continue;
                 sx[q] = add2(sx[q], x[q]);
-                sxx[q] = add2(sxx[q], mul2(x[q], x[q]));
-                sxy[q] = add2(sxy[q], mul2(x[q], yy));
+                sxx[q] = fma2(x[q], x[q], sxx[q]);
+                sxy[q] = fma2(x[q], yy, sxy[q]);
                 if (k == 4) xc[q] = x[q];
             }
         }

@@ -59,7 +59,7 @@ __device__ __forceinline__ void warp_slot(int j, int n_src, int R, int omask0, i
 // Returns this thread's spatial-presence flags: bit 0 = some pixel it filled has a non-zero spatial / spatio-temporal
 // warp (or such a warp's parameters are not finite), bit 1 = the same restricted to region rows >= kTileH (the rows a
 // strip-walking caller carries over to the next tile).  A tile whose whole region has none skips the overlap images.
-template <int HALO, int NSRC>
+template <int HALO, int NSRC, int THREADS>
 __device__ __forceinline__ unsigned fill_region_n(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
                                                   const float4* __restrict__ raw, const uint8_t* __restrict__ vbits,
                                                   float* sm, int row0) {
@@ -82,17 +82,20 @@ __device__ __forceinline__ unsigned fill_region_n(const WarpCtx& ctx, const vfd_
         }
     }
     unsigned flags = (always & kSpatialBits) ? 3u : 0u;
-    for (int r = row0 * Rg::RW + threadIdx.x; r < Rg::R; r += kTileThreads) {      // rows below row0 are already there
+    for (int r = row0 * Rg::RW + threadIdx.x; r < Rg::R; r += THREADS) {      // rows below row0 are already there
         const int x = ox + r % Rg::RW, y = oy + r / Rg::RW;
         if (x < 0 || x >= W || y < 0 || y >= H) continue;
         const int p = y * W + x;
         const unsigned vb = __ldg(vbits + p);
         const unsigned use = live & (vb | always);
         if (vb & kSpatialBits) flags |= (r >= kTileH * Rg::RW) ? 3u : 1u;
+        // The temporal warps are stored at nearly every pixel: their loads do not wait for the validity byte (an entry
+        // that was never written is read and dropped -- the buffer is allocated in full), so one L2 round trip covers
+        // them, the byte and the un-warped images; only the sparse spatial / spatio-temporal entries depend on the byte.
         float4 w[NWc];
 #pragma unroll
-        for (int j = 0; j < NWc; ++j)
-            w[j] = (live & vb & (1u << j)) ? __ldg(raw + (size_t)j * HW + p) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < NSRC; ++j)
+            w[j] = (live & (1u << j)) ? __ldg(raw + (size_t)j * HW + p) : make_float4(0.f, 0.f, 0.f, 0.f);
         float vr[3], v0[3], v1[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -100,6 +103,12 @@ __device__ __forceinline__ unsigned fill_region_n(const WarpCtx& ctx, const vfd_
             v0[c] = __ldg(src0 + c * HW + p);
             v1[c] = __ldg(src1 + c * HW + p);
         }
+#pragma unroll
+        for (int j = 0; j < NSRC; ++j)
+            if (!(vb & (1u << j))) w[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = NSRC; j < NWc; ++j)
+            w[j] = (live & vb & (1u << j)) ? __ldg(raw + (size_t)j * HW + p) : make_float4(0.f, 0.f, 0.f, 0.f);
         // temporal warps -> pair 0 (.x = frame 1, .y = frame 2); their masks -> cmask planes
         float tw[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}, cm[2] = {0.f, 0.f};
 #pragma unroll
@@ -144,12 +153,12 @@ __device__ __forceinline__ unsigned fill_region_n(const WarpCtx& ctx, const vfd_
     return flags;
 }
 
-template <int HALO>
+template <int HALO, int THREADS = kTileThreads>
 __device__ __forceinline__ unsigned fill_region(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
                                                 const float4* __restrict__ raw, const uint8_t* __restrict__ vbits,
                                                 float* sm, int row0 = 0) {
-    if (d.n_src == 2) return fill_region_n<HALO, 2>(ctx, d, b, ci, ox, oy, raw, vbits, sm, row0);
-    return fill_region_n<HALO, 1>(ctx, d, b, ci, ox, oy, raw, vbits, sm, row0);
+    if (d.n_src == 2) return fill_region_n<HALO, 2, THREADS>(ctx, d, b, ci, ox, oy, raw, vbits, sm, row0);
+    return fill_region_n<HALO, 1, THREADS>(ctx, d, b, ci, ox, oy, raw, vbits, sm, row0);
 }
 
 // CTA-wide bitwise OR of every thread's `flags` (one shared word, zeroed by the caller before the previous barrier)
