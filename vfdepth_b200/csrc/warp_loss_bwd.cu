@@ -489,7 +489,11 @@ extern "C" int vfd_warp_loss_train_bwd(const vfd_warp_desc* d, const float* d_nu
     if (bx > 256) bx = 256;
     warp_grad_combine_kernel<<<dim3(bx, d->B * d->n_call), 256, 0, st>>>(a);
     VFD_CHECK_LAUNCH();
+#if VFD_LOSS_SPLIT
+    const int tiles = warp_set_tiles(*d);
+#else
     const int tiles = ((d->W + kTileW - 1) / kTileW) * ((d->H + kTileH - 1) / kTileH);
+#endif
     warp_dT_reduce_kernel<<<d->B * d->n_call, kDtThreads, 0, st>>>(a, tiles, true);
     VFD_CHECK_LAUNCH();
     return VFD_OK;

@@ -27,15 +27,25 @@ struct LossBwdArgs {
 };
 
 constexpr int kStrip = 8;   // tiles a CTA of the backward walks, top to bottom
+// Width of a tile of the per-set training kernels (warp_loss_sets.cu).  30, not 32: the ring on which the SSIM runs is
+// then 32 x 8 = one pixel per thread and one ring row per warp -- no second pass of one warp while seven wait at the
+// barrier (17 % of the stall samples at 32), and the float2 tap loads of a warp stay inside one region row (no bank
+// conflicts: 17 % of the shared-memory wavefronts at 32).  Phase C runs 30 of 32 lanes.
+#ifndef VFD_SET_TILE_W
+#define VFD_SET_TILE_W 30
+#endif
+constexpr int kSetW = VFD_SET_TILE_W;
 
+// tiles per image of the training-mode kernels (kSetW wide; never fewer than the 32-wide tiling of warp_loss_bwd_kernel)
+__host__ __device__ inline int warp_set_tiles(const vfd_warp_desc& d) {
+    return ((d.W + kSetW - 1) / kSetW) * ((d.H + kTileH - 1) / kTileH);
+}
 // bytes of the d_T partial sums at the head of the backward workspace (16-byte multiple)
 __host__ __device__ inline size_t warp_partial_bytes(const vfd_warp_desc& d) {
-    const size_t tiles = (size_t)((d.W + kTileW - 1) / kTileW) * ((d.H + kTileH - 1) / kTileH);
-    return (size_t)d.B * d.n_call * tiles * kMaxW * 12 * sizeof(float);
+    return (size_t)d.B * d.n_call * warp_set_tiles(d) * kMaxW * 12 * sizeof(float);
 }
 __host__ __device__ inline size_t warp_tile_flag_bytes(const vfd_warp_desc& d) {
-    const size_t tiles = (size_t)((d.W + kTileW - 1) / kTileW) * ((d.H + kTileH - 1) / kTileH);
-    return ((size_t)d.B * d.n_call * tiles + 15) & ~(size_t)15;
+    return ((size_t)d.B * d.n_call * warp_set_tiles(d) + 15) & ~(size_t)15;
 }
 
 // how many of pixel p's 3 horizontal (or vertical) window taps land on q, with reflection padding of 1

@@ -13,7 +13,7 @@
 //                        the auto-mask byte.  4 images per pixel, 6 coefficient planes: 58 KB -> 3 CTAs per SM.
 // Per pixel the arithmetic (SSIM tap order, decisions, coefficient products, sampler) is the one of warp_loss_bwd_kernel
 // statement for statement, so g3 / partials / sums carry the same bits; what changes is occupancy and that tiles without
-// spatial warps never touch the overlap code.  A CTA walks a strip of kStrip tiles top to bottom; region rows and ring
+// spatial warps never touch the overlap code.  A CTA walks a strip of kStrip tiles (kSetW = 30 wide, warp_loss_bwd.cuh) top to bottom; region rows and ring
 // rows live in CIRCULAR shared-memory buffers (12 and 10 rows), so the 4 region rows / 2 ring rows the next tile shares
 // are neither moved nor recomputed.
 //   autograd of: view_rendering.py:58-82, geometry_util.py:52-77, loss_util.py:21-25,43-78,
@@ -28,7 +28,7 @@ extern __shared__ __align__(16) float vfd_warp_smem[];
 //   SET 0: pair 0 = (color_-1, color_+1) temporal warps, pair 1 = (frame -1, frame +1) identity images, aux = target
 //   SET 1: pair 0 = (overlap_-1, overlap_+1),            pair 1 = (overlap_0, target),       aux = overlap masks 0, -1, +1
 struct SetRegion {
-    static constexpr int RW = kTileW + 4, RH = kTileH + 4, R = RW * RH;
+    static constexpr int RW = kSetW + 4, RH = kTileH + 4, R = RW * RH;
     static constexpr int kAux = 2 * 3 * 2 * R;
     static constexpr int kFloats = kAux + 3 * R;
 };
@@ -38,7 +38,7 @@ struct SetRegion {
 //          of the selected spatio-temporal frame
 template <int SET>
 struct SetCoef {
-    static constexpr int RW = kTileW + 2, RH = kTileH + 2, R = RW * RH;
+    static constexpr int RW = kSetW + 2, RH = kTileH + 2, R = RW * RH;
     static constexpr int kPlanes = SET == 0 ? 3 : 6;
     static constexpr int kFloats = kPlanes * 4 * R;
 };
@@ -46,13 +46,15 @@ struct SetCoef {
 __device__ __forceinline__ int wrap_row(int v, int n) { return v >= n ? v - n : v; }
 
 // ---- phase A ------------------------------------------------------------------------------------------------------
-// Region rows [row0, RH) of the tile at (ox, oy) -> circular slots (row + base) mod RH.  Returns the spatial-presence
+// Region rows [row0, RH) of the tile at (ox, oy) -> circular slots (row + base) mod RH.  live / always: bit j = warp j
+// exists / its alignment parameters are not finite, so even an all-zero sample goes through the arithmetic (NaN * 0 must
+// stay NaN as in the reference).  Returns the spatial-presence
 // flags of fill_region_n (warp_tile.cuh): bit 0 = some pixel filled now has a spatial / spatio-temporal warp (or such a
 // warp's parameters are not finite), bit 1 = the same for rows >= kTileH (the rows the next tile of the strip shares).
 template <int SET, int NSRC>
 __device__ __forceinline__ unsigned fill_set(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
                                              const float4* __restrict__ raw, const uint8_t* __restrict__ vbits, float* sm,
-                                             int row0, int base) {
+                                             int row0, int base, unsigned live, unsigned always) {
     using Rg = SetRegion;
     constexpr int NWc = NSRC + (1 + NSRC) * VFD_WARP_NBR;
     constexpr unsigned kSpatialBits = ((1u << NWc) - 1u) & ~((1u << NSRC) - 1u);
@@ -61,14 +63,6 @@ __device__ __forceinline__ unsigned fill_set(const WarpCtx& ctx, const vfd_warp_
     const float* src0 = d.color[1] + (size_t)(b * d.num_cams + cam) * 3 * HW;
     const float* src1 = d.color[NSRC] + (size_t)(b * d.num_cams + cam) * 3 * HW;   // == src0 when NSRC == 1 (unused)
     float2* img = reinterpret_cast<float2*>(sm);
-    unsigned live = 0, always = 0;
-#pragma unroll
-    for (int j = 0; j < NWc; ++j) {
-        if (ctx.active[j] != 0) {
-            live |= 1u << j;
-            if (ctx.prm[j][6] == 0.f) always |= 1u << j;
-        }
-    }
     unsigned flags = (always & kSpatialBits) ? 3u : 0u;
     for (int r = row0 * Rg::RW + threadIdx.x; r < Rg::R; r += kTileThreads) {
         const int rr = r / Rg::RW, cx = r - rr * Rg::RW;
@@ -242,8 +236,14 @@ __device__ __forceinline__ void tap_slots(int x, int y, int W, int H, int ox, in
     }
 }
 
+#ifndef VFD_SET0_CTAS
+#define VFD_SET0_CTAS 3
+#endif
+#ifndef VFD_SET1_CTAS
+#define VFD_SET1_CTAS 3
+#endif
 template <int SET, bool FUSED>
-__global__ void __launch_bounds__(kTileThreads, SET == 0 ? 4 : 3) warp_loss_set_kernel(const LossBwdArgs a) {
+__global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_SET1_CTAS) warp_loss_set_kernel(const LossBwdArgs a) {
     using Rg = SetRegion;
     using Cf = SetCoef<SET>;
     constexpr int kSlots = SET == 0 ? VFD_WARP_SRC : (1 + VFD_WARP_SRC) * VFD_WARP_NBR;     // warps this kernel differentiates
@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? 4 : 3) warp_loss_set_
     const int tiles_y = (H + kTileH - 1) / kTileH, ntile = gridDim.x * tiles_y;
     const int ty_first = blockIdx.y * kStrip, ty_last = min(tiles_y, ty_first + kStrip);
     const int strip_y0 = ty_first * kTileH, strip_y1 = ty_last * kTileH;
-    const int tx0 = blockIdx.x * kTileW, ox = tx0 - 2;
+    const int tx0 = blockIdx.x * kSetW, ox = tx0 - 2;
     const size_t bc = (size_t)(b * d.n_call + ci);
     if (SET == 1) {     // nothing to do in this strip?  (uniform over the CTA; no barrier has been reached yet)
         bool any_tile = false;
@@ -271,6 +271,13 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? 4 : 3) warp_loss_set_
     if (threadIdx.x < 4) sacc[threadIdx.x] = 0.0;
     if (threadIdx.x < 2) s_flags[threadIdx.x] = 0u;
     __syncthreads();
+    unsigned live_w = 0, always_w = 0;      // per warp j: exists / parameters not finite (once per CTA, not per tile)
+    for (int j = 0; j < ctx.NW; ++j) {
+        if (ctx.active[j] != 0) {
+            live_w |= 1u << j;
+            if (ctx.prm[j][6] == 0.f) always_w |= 1u << j;
+        }
+    }
     const float* depth = a.depth + bc * HW;
     const float* rmaskp = d.mask + (size_t)(b * d.num_cams + cam) * HW;
     const float4* raw = a.raw + bc * ctx.NW * HW;
@@ -300,8 +307,8 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? 4 : 3) warp_loss_set_
         }
         float (*dPs)[kSlots * 12] = s_dP[nproc & 1];
         for (int i = threadIdx.x; i < (kTilePixels / 32) * kSlots * 12; i += kTileThreads) (&dPs[0][0])[i] = 0.f;
-        const unsigned fl = n_src == 2 ? fill_set<SET, 2>(ctx, d, b, ci, ox, oy, raw, vbits, sm, cont ? 4 : 0, base)
-                                       : fill_set<SET, 1>(ctx, d, b, ci, ox, oy, raw, vbits, sm, cont ? 4 : 0, base);
+        const unsigned fl = n_src == 2 ? fill_set<SET, 2>(ctx, d, b, ci, ox, oy, raw, vbits, sm, cont ? 4 : 0, base, live_w, always_w)
+                                       : fill_set<SET, 1>(ctx, d, b, ci, ox, oy, raw, vbits, sm, cont ? 4 : 0, base, live_w, always_w);
         bool sp = true;
         if (SET == 0) {
             // any spatial / spatio-temporal warp in this tile's region?  (flag words alternate between tiles; the other one
@@ -327,7 +334,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? 4 : 3) warp_loss_set_
             tap_slots(x, y, W, H, ox, oy, base, idx);
             float2 L[2];
             SsimGrad2 g0, g1;
-            const bool mine = x >= tx0 && x < tx0 + kTileW && y >= strip_y0 && y < strip_y1;   // counted / owned by this CTA
+            const bool mine = x >= tx0 && x < tx0 + kSetW && y >= strip_y0 && y < strip_y1;   // counted / owned by this CTA
             if (SET == 0) {
                 float nz0 = 0.f, nz1 = 0.f;
                 {
@@ -383,8 +390,8 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? 4 : 3) warp_loss_set_
         __syncthreads();
 
         // ---- phase C: gather the coefficients at the interior pixel, then back through normalise / sampler / projection ----
-        const int x = tx0 + (threadIdx.x % kTileW), y = ty0 + (threadIdx.x / kTileW);
-        const bool live = x < W && y < H;
+        const int x = tx0 + (threadIdx.x & 31), y = ty0 + (threadIdx.x >> 5);      // a warp per tile row
+        const bool live = (threadIdx.x & 31) < kSetW && x < W && y < H;
         const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
         constexpr int NP = SET == 0 ? VFD_WARP_SRC : 1 + VFD_WARP_SRC;      // differentiable images of this set
         float dpred[NP][3];
@@ -578,7 +585,7 @@ static size_t set_smem_bytes() { return (SetRegion::kFloats + SetCoef<SET>::kFlo
 
 int launch_loss_sets(const LossBwdArgs& a, cudaStream_t st) {
     const vfd_warp_desc& d = a.d;
-    const int tiles_x = (d.W + kTileW - 1) / kTileW, tiles_y = (d.H + kTileH - 1) / kTileH;
+    const int tiles_x = (d.W + kSetW - 1) / kSetW, tiles_y = (d.H + kTileH - 1) / kTileH;
     dim3 grid(tiles_x, (tiles_y + kStrip - 1) / kStrip, d.B * d.n_call);
     // > 48 KB of dynamic shared memory needs the opt-in; setting it is idempotent and per device, so it is simply
     // repeated on every call (no global state to keep in step with the current device)
