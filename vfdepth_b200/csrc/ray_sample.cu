@@ -322,8 +322,10 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
                                         ? ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC)
                                         : f4_zero();
                     }
+                    // packed fma.rn.f32x2: the same bits as four fmaf per corner at half the issue slots and half the
+                    // fma-pipe cycles (a three-register FFMA and an FFMA2 both take the pipe for two cycles)
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) f4_fma(r, s.w[k], vv[k]);
+                    for (int k = 0; k < 8; ++k) f4_fma_w2(r, pack2(s.w[k], s.w[k]), vv[k]);
                 }
                 st_stream_f4(o + v * ostride, r);
             }
