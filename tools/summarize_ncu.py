@@ -18,7 +18,7 @@ ABI = [('voxel_fuse_gather', 'vfd_voxel_fuse_fwd'), ('voxel_fuse_scatter', 'vfd_
        # launched by both directions: occurrences alternate forward, backward within a step (see ALTERNATE)
        ('dense_proj', 'vfd_voxel_fuse_fwd'), ('wcat_prep', 'vfd_voxel_fuse_fwd'), ('ray_sample_fwd', 'vfd_ray_sample_fwd'),
        ('ray_sample_bwd', 'vfd_ray_sample_bwd'), ('warp_stats', 'vfd_warp_stats'),
-       ('warp_loss_fwd', 'vfd_warp_loss_fwd'), ('warp_loss_bwd_kernel<1>', 'vfd_warp_loss_train_fwd'),
+       ('warp_loss_fwd', 'vfd_warp_loss_fwd'), ('warp_loss_set_kernel', 'vfd_warp_loss_train_fwd'), ('warp_loss_bwd_kernel<1>', 'vfd_warp_loss_train_fwd'),
        ('warp_loss_bwd_kernel<true>', 'vfd_warp_loss_train_fwd'), ('warp_loss_bwd', 'vfd_warp_loss_bwd'),
        ('warp_grad_combine', 'vfd_warp_loss_train_bwd'), ('warp_dT_reduce', 'vfd_warp_loss_train_bwd'),
        ('to_depth_fwd', 'vfd_to_depth_fwd'), ('to_depth_bwd', 'vfd_to_depth_bwd'),

@@ -17,10 +17,12 @@ extern __shared__ __align__(16) float vfd_warp_smem[];
 // the set's upstream weight (for the L1 term) and the frame each min selected
 // Threads per CTA.  The tile is 32 x 8 pixels (phase C: 8 warps), but a strip step fills 36 x 8 = 288 region pixels and
 // evaluates 34 x 8 = 272 ring pixels: with 8 warps each of those phases is one full pass plus a second pass of ONE warp
-// while seven wait at the barrier (a quarter of the kernel's stall samples).  Ten warps take every phase in one pass; the
-// register file then gives 96 registers per thread at two CTAs per SM (five warps per scheduler).
+// while seven wait at the barrier (a quarter of the kernel's stall samples).  -DVFD_LOSS_THREADS=320 takes every phase in
+// one pass at 96 registers (two CTAs per SM): measured 2.382 ms against 2.389 ms at 256 threads / 128 registers -- the
+// other CTA of the SM already fills the barrier wait, so the default stays 256.  What did help is occupancy: see
+// warp_loss_sets.cu, which serves the training mode.
 #ifndef VFD_LOSS_THREADS
-#define VFD_LOSS_THREADS 320
+#define VFD_LOSS_THREADS 256
 #endif
 constexpr int kBwdThreads = VFD_LOSS_THREADS;
 // training mode (vfd_warp_loss_train_fwd): 1 = one lean kernel per loss set (warp_loss_sets.cu), 0 = this file's kernel
