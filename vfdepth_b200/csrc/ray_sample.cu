@@ -369,13 +369,21 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
             // six cameras and distant columns -- 0.95 ms (the reductions want the L2 locality of neighbouring
             // columns, not more parallelism).
             constexpr int kPf = 4;
+            // Instruction count matters as much as the memory system here (ncu: 507 M warp instructions per launch, only
+            // 106 M of them FFMA2 / FMUL2; issue 58 % at 16 warps/SM): advancing the row pointer by addition instead of a
+            // 64-bit multiply per row took 0.843 -> 0.805 ms.  The loop body (three face-step variants, unrolled kPf times)
+            // is also near the instruction cache's limit: unrolling it 8 times to swap two register buffers without the
+            // copy below ran at 1.14 ms, refilling g[i] in place right after row i is consumed 1.15 / 1.94 / 2.84 ms at
+            // kPf = 4 / 6 / 8, and kPf = 2 / 3 with this form 0.92 / 0.84 ms.
             float4 g[kPf], gn[kPf];
 #pragma unroll
             for (int i = 0; i < kPf; ++i) g[i] = (i < H) ? ld_stream_f4(gp + i * gstride) : f4_zero();
+            const float* gnext = gp + kPf * gstride;
             for (int v0 = 0; v0 < H; v0 += kPf) {
 #pragma unroll
                 for (int i = 0; i < kPf; ++i)
-                    gn[i] = (v0 + kPf + i < H) ? ld_stream_f4(gp + (size_t)(v0 + kPf + i) * gstride) : f4_zero();
+                    gn[i] = (v0 + kPf + i < H) ? ld_stream_f4(gnext + i * gstride) : f4_zero();
+                gnext += kPf * gstride;
 #pragma unroll
                 for (int i = 0; i < kPf; ++i) {
                     const int v = v0 + i;
