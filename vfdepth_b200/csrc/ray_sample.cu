@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
             float4 vv[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) vv[k] = f4_zero();
-            for (int v = 0; v < H; ++v) {
+            for (int v = 0; v < H; ++v, o += ostride) {      // (output row pointer advanced by addition, as in the backward)
                 const RaySlotW s = slot[q * H + v];
                 float4 r = f4_zero();
                 if (s.corners) {
@@ -316,18 +316,23 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
                     if (s.base != cur_base) {
                         cur_base = s.base;
                         const float* p0 = vol + (long)s.base * CV;
+                        if (s.corners == 0xffu) {      // interior cell (the usual case): eight unconditional loads
 #pragma unroll
-                        for (int k = 0; k < 8; ++k)
-                            vv[k] = (s.corners & (1u << k))
-                                        ? ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC)
-                                        : f4_zero();
+                            for (int k = 0; k < 8; ++k) vv[k] = ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 8; ++k)
+                                vv[k] = (s.corners & (1u << k))
+                                            ? ldg_f4(p0 + (k & 1) * CV + ((k >> 1) & 1) * XC + (k >> 2) * YXC)
+                                            : f4_zero();
+                        }
                     }
                     // packed fma.rn.f32x2: the same bits as four fmaf per corner at half the issue slots and half the
                     // fma-pipe cycles (a three-register FFMA and an FFMA2 both take the pipe for two cycles)
 #pragma unroll
                     for (int k = 0; k < 8; ++k) f4_fma_w2(r, pack2(s.w[k], s.w[k]), vv[k]);
                 }
-                st_stream_f4(o + v * ostride, r);
+                st_stream_f4(o, r);
             }
         }
         __syncwarp();
