@@ -249,10 +249,14 @@ int vfd_warp_loss_bwd(const vfd_warp_desc* d, const float* depth, const float* T
                       const float* raw, const float* noise, const float* d_num, float* d_depth, float* d_T, void* ws,
                       size_t ws_bytes, void* stream);
 
-/* Training mode of pass 2: ONE launch evaluates the loss sums of vfd_warp_loss_fwd and the gradients of
- * vfd_warp_loss_bwd with unit upstream, per loss set (the backward kernel recomputes the forward anyway):
- *   sums [n_call][8] f64 as vfd_warp_loss_fwd;  g3 [B,n_call,3,H,W] = d loss_set / d depth;  ws = d_T partials
- *   (vfd_warp_bwd_workspace_bytes), to be kept until vfd_warp_loss_train_bwd, which applies
+/* Training mode of pass 2: ONE call evaluates the loss sums of vfd_warp_loss_fwd and the gradients of
+ * vfd_warp_loss_bwd with unit upstream, per loss set (the backward recomputes the forward anyway).  Two launches: the
+ * temporal set (reprojection + auto-mask) on every tile, then the spatial + spatio-temporal sets on the tiles a
+ * neighbour camera's warp reaches (csrc/warp_loss_sets.cu).
+ *   sums [n_call][8] f64 as vfd_warp_loss_fwd;  g3 [B,n_call,3,H,W] = d loss_set / d depth;  ws
+ *   (vfd_warp_bwd_workspace_bytes, 16-byte aligned) = the d_T partial sums -- to be kept until
+ *   vfd_warp_loss_train_bwd -- followed by what the first launch hands to the second (a flag byte per tile, the
+ *   auto-mask decision byte per pixel).  vfd_warp_loss_train_bwd applies
  *   d_num [n_call,3] = d total / d num_set:  d_depth = sum_set d_num * g3,  d_T likewise (fixed-order fp64 reduction). */
 int vfd_warp_loss_train_fwd(const vfd_warp_desc* d, const float* depth, const float* T, const float* params,
                             const float* raw, const float* noise, double* sums, float* g3, void* ws, size_t ws_bytes,
