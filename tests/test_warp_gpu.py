@@ -618,6 +618,35 @@ def test_training_mode_matches_separate_launches():
         assert H.rel_err(a, b) < 3e-5
 
 
+@pytest.mark.parametrize('height,width,batch,over', [
+    (75, 130, 2, {}),                                        # ragged in both directions: partial 30 x 8 tiles, partial strips
+    (88, 160, 1, {'training__frame_ids': [0, -1]}),          # one source frame (no min over frames)
+    (72, 200, 2, {'training__intensity_align': False}),      # raw, un-normalised warps
+    (136, 94, 1, {}),                                        # taller than wide: 17 tile rows = 2 full strips + 1 tile
+])
+def test_training_mode_set_kernels_ragged_shapes(height, width, batch, over):
+    """The per-set training kernels (csrc/warp_loss_sets.cu: 30 x 8 tiles walked in strips of 8, circular row buffers,
+    the overlap sets only on flagged tiles) against the separate forward + backward launches (32 x 8 tiles, all sets in
+    one CTA) at sizes that are multiples of neither tiling: same sums, same gradients."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    cfg, inp, ex = _rig(height, width, batch, seed=41, **over)
+    n_src = len(cfg['training']['frame_ids']) - 1
+    ex['noise'] = [n[:, :n_src].contiguous() for n in ex['noise']]
+    res = []
+    for fused in (True, False):
+        view._WarpLoss.fuse_training = fused
+        try:
+            t, det, g = _run_gpu(cfg, inp, ex, dev)
+        finally:
+            view._WarpLoss.fuse_training = True
+        res.append((float(t), det['terms'].cpu(), g))
+    assert abs(res[0][0] - res[1][0]) / abs(res[1][0]) < 1e-6
+    assert H.rel_err(res[0][1], res[1][1]) < 1e-6
+    for a, b in zip(res[0][2], res[1][2]):
+        assert H.rel_err(a, b) < 5e-5
+
+
 def test_step_is_cuda_graph_capturable():
     """the view-synthesis half of a step (to_depth -> warp/loss training mode -> gradients) captured with
     vfdepth_b200.graph.capture replays to the eager result: no entry point synchronises, allocates or copies from

@@ -362,10 +362,18 @@ __global__ void __launch_bounds__(kDtThreads) warp_dT_reduce_kernel(const LossBw
     {
         const int i = threadIdx.x % (kMaxW * 12), q = threadIdx.x / (kMaxW * 12);
         const int per = (ntile + kDtParts - 1) / kDtParts, t0 = q * per, t1 = min(ntile, t0 + per);
-        double s = 0.0;
-        if (i < NW * 12)
-            for (int t = t0; t < t1; ++t) s += (double)part[(size_t)t * (kMaxW * 12) + i];
-        s_part[q][i] = s;
+        // four independent chains per thread (combined in a fixed order): the loop was one dependent load + add per tile,
+        // i.e. pure L2 latency (0.035 ms for 48 CTAs at 8 % issue)
+        double s4[4] = {0.0, 0.0, 0.0, 0.0};
+        if (i < NW * 12) {
+            int t = t0;
+            for (; t + 4 <= t1; t += 4) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) s4[k] += (double)part[(size_t)(t + k) * (kMaxW * 12) + i];
+            }
+            for (; t < t1; ++t) s4[0] += (double)part[(size_t)t * (kMaxW * 12) + i];
+        }
+        s_part[q][i] = (s4[0] + s4[1]) + (s4[2] + s4[3]);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < NW * 12; i += blockDim.x) {
