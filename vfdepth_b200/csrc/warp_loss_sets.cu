@@ -483,15 +483,25 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
             X[0] = VFD_MUL(dep, ray[0]); X[1] = VFD_MUL(dep, ray[1]); X[2] = VFD_MUL(dep, ray[2]);
         }
         float gset[SET == 0 ? 1 : 2] = {};
-#pragma unroll
-        for (int k = 0; k < NP; ++k) {
-#pragma unroll
-            for (int nb = 0; nb < (SET == 0 ? 1 : VFD_WARP_NBR); ++nb) {
-                // SET 0: warp j = k (temporal frame k);  SET 1: warp j = n_src + k * NBR + nb (frame k of neighbour nb)
-                const int j = SET == 0 ? k : n_src + k * VFD_WARP_NBR + nb;
-                const int slot = SET == 0 ? k : k * VFD_WARP_NBR + nb;
-                if (SET == 0 ? k >= n_src : k > n_src) continue;
+        // One copy of the sampler / back-projection code, run once per warp of this set (a rolled loop: unrolled over the
+        // six overlap warps the kernel was 95 KB of code and 13 % of its stall samples were instruction-cache misses).
+        //   SET 0: warp j = slot (temporal frame k = slot);  SET 1: warp j = n_src + slot, k = slot / NBR (frame k of
+        //   neighbour slot % NBR)
+        const int n_slots = SET == 0 ? n_src : (1 + n_src) * VFD_WARP_NBR;
+#pragma unroll 1
+        for (int slot = 0; slot < n_slots; ++slot) {
+            {
+                const int k = SET == 0 ? slot : slot / VFD_WARP_NBR;
+                const int j = SET == 0 ? slot : n_src + slot;
                 if (!ctx.active[j]) continue;      // CTA-uniform
+                float up[3];      // dpred[k][:] (static indices: a run-time index would put dpred in local memory)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    float v = dpred[0][c];
+#pragma unroll
+                    for (int kk = 1; kk < NP; ++kk) v = (k == kk) ? dpred[kk][c] : v;
+                    up[c] = v;
+                }
                 float dP[12];
 #pragma unroll
                 for (int i = 0; i < 12; ++i) dP[i] = 0.f;
@@ -499,7 +509,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                 // or the pixel lies outside the spatial overlap.  Those skip the sampler; a warp whose 32 pixels all skip
                 // also skips the reduction (its slots of s_dP stay zero, so the sums are unchanged).
                 bool contrib = false;
-                if (live && (dpred[k][0] != 0.f || dpred[k][1] != 0.f || dpred[k][2] != 0.f)) {
+                if (live && (up[0] != 0.f || up[1] != 0.f || up[2] != 0.f)) {
                     const WarpSample s = warp_sample<true>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
                     if (!s.nan) {
                         contrib = true;
@@ -507,7 +517,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                         float gix = 0.f, giy = 0.f;
 #pragma unroll
                         for (int c = 0; c < 3; ++c) {
-                            const float dw = dpred[k][c] * ng;
+                            const float dw = up[c] * ng;
                             gix = fmaf(dw, s.dvx[c], gix);
                             giy = fmaf(dw, s.dvy[c], giy);
                         }
