@@ -16,6 +16,9 @@
 // spatial warps never touch the overlap code.  A CTA walks a strip of kStrip tiles (kSetW = 30 wide, warp_loss_bwd.cuh) top to bottom; region rows and ring
 // rows live in CIRCULAR shared-memory buffers (12 and 10 rows), so the 4 region rows / 2 ring rows the next tile shares
 // are neither moved nor recomputed.
+// Measured and dropped: requesting the next tile's inputs with cp.async into a per-thread staging area one tile ahead
+// (the region fill and the barrier behind it are a third of the temporal kernel's stall samples): 1.539 vs 1.550 ms --
+// the wait is for the slowest warp of the phase, not for the loads.
 //   autograd of: view_rendering.py:58-82, geometry_util.py:52-77, loss_util.py:21-25,43-78,
 //                single_cam_loss.py:17-55, multi_cam_loss.py:16-59
 #include "warp_loss_bwd.cuh"
