@@ -26,13 +26,17 @@ struct LossBwdArgs {
     uint8_t* auto_bit;    // [B*n_call][H*W]: the auto-mask decision (reprojection <= identity) of every pixel
 };
 
-constexpr int kStrip = 8;   // tiles a CTA of the backward walks, top to bottom
-// Width of a tile of the per-set training kernels (warp_loss_sets.cu).  30, not 32: the ring on which the SSIM runs is
-// then 32 x 8 = one pixel per thread and one ring row per warp -- no second pass of one warp while seven wait at the
-// barrier (17 % of the stall samples at 32), and the float2 tap loads of a warp stay inside one region row (no bank
-// conflicts: 17 % of the shared-memory wavefronts at 32).  Phase C runs 30 of 32 lanes.
+#ifndef VFD_LOSS_STRIP
+#define VFD_LOSS_STRIP 8
+#endif
+constexpr int kStrip = VFD_LOSS_STRIP;   // tiles a CTA of the backward walks, top to bottom
+// Width of a tile of the per-set training kernels (warp_loss_sets.cu).  28, not 32: the region a strip step fills is
+// then 32 x 8 = one pixel per thread (at 30 and 32 a second pass of one warp followed, with seven at the barrier), the
+// ring on which the SSIM runs is 30 x 8 = one ring row per warp, and the float2 tap loads of a warp stay inside one region
+// row (no bank conflicts: 17 % of the shared-memory wavefronts at 32).  Phase C runs 28 of 32 lanes.  Measured at B = 8:
+// 1.59 / 1.56 / 1.51 ms at 32 / 30 / 28.
 #ifndef VFD_SET_TILE_W
-#define VFD_SET_TILE_W 30
+#define VFD_SET_TILE_W 28
 #endif
 constexpr int kSetW = VFD_SET_TILE_W;
 

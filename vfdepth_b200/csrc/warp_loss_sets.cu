@@ -326,8 +326,11 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
         }
 
         // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
-        for (int r = (cont ? 2 * Cf::RW : 0) + threadIdx.x; r < Cf::R; r += kTileThreads) {
-            const int rr = r / Cf::RW, cx = r - rr * Cf::RW;
+        // a warp per ring row (lane = column; lanes past the ring's width idle when kSetW < 30)
+        static_assert(Cf::RW <= 32, "ring row = one warp");
+        for (int rr = (cont ? 2 : 0) + (threadIdx.x >> 5); rr < Cf::RH; rr += kTileThreads / 32) {
+            const int cx = threadIdx.x & 31;
+            if (cx >= Cf::RW) continue;
             const int x = tx0 - 1 + cx, y = ty0 - 1 + rr;
             if (x < 0 || x >= W || y < 0 || y >= H) continue;
             const int p = y * W + x;
