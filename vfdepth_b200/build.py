@@ -69,7 +69,8 @@ def build(force=False, verbose=False):
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError('nvcc failed on %s' % src)
-    subprocess.check_call([NVCC, '-shared', '-o', LIB] + objs + ['-lcudart'])
+    # (the arch on the link line too: without it nvcc emits an empty sm_52 image and a deprecation warning)
+    subprocess.check_call([NVCC, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', LIB] + objs + ['-lcudart'])
     with open(STAMP, 'w') as f:
         f.write(source_hash() + '\n')
     return LIB
