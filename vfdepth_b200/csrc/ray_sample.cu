@@ -375,13 +375,14 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP, 2) ray_sample_bwd_vec_ker
             // kPf = 2 or 1 at 3 CTAs per SM -- 0.87 / 1.04 ms; a task order that spreads the resident warps over the
             // six cameras and distant columns -- 0.95 ms (the reductions want the L2 locality of neighbouring
             // columns, not more parallelism).
-            constexpr int kPf = 4;
+            constexpr int kPf = 6;      // rows in flight per lane; 3 / 4 / 6 / 8: 0.775 / 0.743 / 0.722 / 0.740 ms
             // Instruction count matters as much as the memory system here (ncu: 507 M warp instructions per launch, only
             // 106 M of them FFMA2 / FMUL2; issue 58 % at 16 warps/SM): advancing the row pointer by addition instead of a
-            // 64-bit multiply per row took 0.843 -> 0.805 ms.  The loop body (three face-step variants, unrolled kPf times)
-            // is also near the instruction cache's limit: unrolling it 8 times to swap two register buffers without the
-            // copy below ran at 1.14 ms, refilling g[i] in place right after row i is consumed 1.15 / 1.94 / 2.84 ms at
-            // kPf = 4 / 6 / 8, and kPf = 2 / 3 with this form 0.92 / 0.84 ms.
+            // 64-bit multiply per row took 0.843 -> 0.805 ms, carrying the face for the one step direction that occurs
+            // (below) 0.806 -> 0.743 ms.  While the loop body still held three face-step variants it sat at the
+            // instruction cache's limit: unrolling it 8 times to swap two register buffers without the copy below ran at
+            // 1.14 ms, refilling g[i] in place right after row i is consumed 1.15 / 1.94 / 2.84 ms at kPf = 4 / 6 / 8.
+            // Three CTAs per SM (80 registers): 0.77 / 0.98 ms at kPf = 2 / 4.
             float4 g[kPf], gn[kPf];
 #pragma unroll
             for (int i = 0; i < kPf; ++i) g[i] = (i < H) ? ld_stream_f4(gp + i * gstride) : f4_zero();
