@@ -314,7 +314,9 @@ __global__ void __launch_bounds__(kRayWarps* VFD_WARP) ray_sample_fwd_vec_kernel
                     // (carrying the four corner rows a face step shares, as the backward does with its accumulators, was
                     // measured at 1.18 ms against 0.65 ms: 106 instead of 64 registers, and the reloads hit L1 anyway;
                     // requesting the next pixel's cell into L1 one row ahead with prefetch.global.L1 -- half of the stall
-                    // samples are these eight loads -- 0.69 / 0.71 ms against 0.60 ms: the extra instructions cost more)
+                    // samples are these eight loads -- 0.69 / 0.71 ms against 0.60 ms: the extra instructions cost more;
+                    // carrying only the lower face on the one step direction that occurs (z - 1, see the backward) with
+                    // four loads instead of eight -- 0.85 ms at 80 registers, 0.84 ms forced to 64)
                     if (s.base != cur_base) {
                         cur_base = s.base;
                         const float* p0 = vol + (long)s.base * CV;
