@@ -173,6 +173,20 @@ __global__ void __launch_bounds__(kStatThreads, 5) warp_stats_kernel(const Stats
             const int p = v * W + u;
             float X[3];
             vfd_backproject(ctx.invK, (float)u, (float)v, __ldg(depth + p), X);
+            if (j >= d.n_src) {
+                // Inside a kept tile most pixels of a spatial / spatio-temporal warp still land outside the neighbour's
+                // image.  A sample more than half a pixel outside [-1, W] x [-1, H] is exactly zero with mask zero
+                // (warp_sample), so it adds nothing to any sum and is not stored: decide that from cam.xy against
+                // cam.z WITHOUT the four IEEE divisions of the exact coordinate (the products carry ~1e-6 relative
+                // error against a margin of half a pixel; a NaN or a point at / behind the camera plane fails the
+                // comparisons and takes the exact path).
+                const float* P = ctx.P[j];
+                const float c0 = vfd_dot4(P + 0, X[0], X[1], X[2], 1.0f), c1 = vfd_dot4(P + 4, X[0], X[1], X[2], 1.0f);
+                const float den = VFD_ADD(vfd_dot4(P + 8, X[0], X[1], X[2], 1.0f), 1e-7f);
+                if (den > 1e-6f && (c0 < -1.5f * den || c0 > ((float)W + 0.5f) * den || c1 < -1.5f * den ||
+                                    c1 > ((float)H + 0.5f) * den))
+                    continue;
+            }
             const WarpSample s = warp_sample<false>(ctx.P[j], ctx.img[j], ctx.msk[j], X, W, H);
             if (s.v[0] != 0.f || s.v[1] != 0.f || s.v[2] != 0.f || s.m != 0.f) {
                 raw[p] = make_float4(s.v[0], s.v[1], s.v[2], s.m);
