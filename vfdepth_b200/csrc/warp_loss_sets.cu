@@ -406,11 +406,14 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
         float X[3] = {0.f, 0.f, 0.f}, ray[3] = {0.f, 0.f, 0.f};
         if (live) {
             const float dep = __ldg(depth + y * W + x);
-            float SA[NP][3], SB[NP][3], SC[NP][3];
+            // window sums of the coefficients as packed pairs: AB = (sum a, sum b), CJ = (sum c, unused lane -- the .w of a
+            // coefficient plane rides along).  One fma.rn.f32x2 where two three-register FFMA stood: the same bits, 2/3 of
+            // the instructions and of the fma-pipe cycles of this gather (math-pipe throttle was 11 % of the stall samples).
+            float2 AB[NP][3], CJ[NP][3];
 #pragma unroll
             for (int k = 0; k < NP; ++k)
 #pragma unroll
-                for (int c = 0; c < 3; ++c) SA[k][c] = SB[k][c] = SC[k][c] = 0.f;
+                for (int c = 0; c < 3; ++c) AB[k][c] = CJ[k][c] = splat2(0.f);
             // how often the window of neighbour (x + dx, y + dy) contains this pixel: 1 away from the image border (reflection
             // padding only folds taps within two pixels of it), 0 for a neighbour outside the image
             float mx[3] = {1.f, 1.f, 1.f}, my[3] = {1.f, 1.f, 1.f};
@@ -438,20 +441,25 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                     if (SET == 0) {
                         const int sel = __float_as_int(q[1].w);
                         const float w0 = sel ? 0.f : mult, w1 = mult - w0;
+                        const float2 W0 = splat2(w0), W1 = splat2(w1);
 #pragma unroll
                         for (int c = 0; c < 3; ++c) {
-                            SA[0][c] = fmaf(q[c].x, w0, SA[0][c]); SB[0][c] = fmaf(q[c].y, w0, SB[0][c]); SC[0][c] = fmaf(q[c].z, w0, SC[0][c]);
-                            SA[1][c] = fmaf(q[c].x, w1, SA[1][c]); SB[1][c] = fmaf(q[c].y, w1, SB[1][c]); SC[1][c] = fmaf(q[c].z, w1, SC[1][c]);
+                            const float2 ab = make_float2(q[c].x, q[c].y), cj = make_float2(q[c].z, q[c].w);
+                            AB[0][c] = fma2(ab, W0, AB[0][c]); CJ[0][c] = fma2(cj, W0, CJ[0][c]);
+                            AB[1][c] = fma2(ab, W1, AB[1][c]); CJ[1][c] = fma2(cj, W1, CJ[1][c]);
                         }
                     } else {
                         const int sel = __float_as_int(q[2].w);
                         const float w0 = sel ? 0.f : mult, w1 = mult - w0;
+                        const float2 WM = splat2(mult), W0 = splat2(w0), W1 = splat2(w1);
 #pragma unroll
                         for (int c = 0; c < 3; ++c) {
                             const float4 q2 = cf4[(3 + c) * Cf::R + r];
-                            SA[0][c] = fmaf(q[c].x, mult, SA[0][c]); SB[0][c] = fmaf(q[c].y, mult, SB[0][c]); SC[0][c] = fmaf(q[c].z, mult, SC[0][c]);
-                            SA[1][c] = fmaf(q2.x, w0, SA[1][c]); SB[1][c] = fmaf(q2.y, w0, SB[1][c]); SC[1][c] = fmaf(q2.z, w0, SC[1][c]);
-                            SA[2][c] = fmaf(q2.x, w1, SA[2][c]); SB[2][c] = fmaf(q2.y, w1, SB[2][c]); SC[2][c] = fmaf(q2.z, w1, SC[2][c]);
+                            const float2 ab = make_float2(q[c].x, q[c].y), cj = make_float2(q[c].z, q[c].w);
+                            const float2 ab2 = make_float2(q2.x, q2.y), cj2 = make_float2(q2.z, q2.w);
+                            AB[0][c] = fma2(ab, WM, AB[0][c]); CJ[0][c] = fma2(cj, WM, CJ[0][c]);
+                            AB[1][c] = fma2(ab2, W0, AB[1][c]); CJ[1][c] = fma2(cj2, W0, CJ[1][c]);
+                            AB[2][c] = fma2(ab2, W1, AB[2][c]); CJ[2][c] = fma2(cj2, W1, CJ[2][c]);
                         }
                     }
                 }
@@ -482,7 +490,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                     const float xv = SET == 0 ? (k == 0 ? p0.x : p0.y) : (k == 0 ? p1.x : (k == 1 ? p0.x : p0.y));
                     const float df = xv - yv;
                     const float sgn = df > 0.f ? 1.f : (df < 0.f ? -1.f : 0.f);
-                    dpred[k][c] = (SA[k][c] + 2.f * xv * SB[k][c] + yv * SC[k][c]) * (1.f / 9.f) + (0.15f / 3.f) * wl[k] * sgn;
+                    dpred[k][c] = (AB[k][c].x + 2.f * xv * AB[k][c].y + yv * CJ[k][c].x) * (1.f / 9.f) + (0.15f / 3.f) * wl[k] * sgn;
                 }
             }
             vfd_pixel_ray(ctx.invK, (float)x, (float)y, ray);
