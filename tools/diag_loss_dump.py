@@ -37,7 +37,7 @@ torch.cuda.synchronize()
 print('sums train', sums[:, :6].cpu().tolist()[0])
 print('sums fwd  ', sums2[:, :6].cpu().tolist()[0])
 print('sum diffs ', (sums - sums2)[:, :6].abs().max(0).values.cpu().tolist())
-tiles = ((Ww + 31) // 32) * ((Hh + 7) // 8)
+tiles = ((Ww + 27) // 28) * ((Hh + 7) // 8)      # kSetW = 28 (csrc/warp_loss_bwd.cuh)
 pbytes = B * n_call * tiles * 96 * 4
 fbytes = (B * n_call * tiles + 15) // 16 * 16
 abit = ws[pbytes + fbytes:pbytes + fbytes + B * n_call * Hh * Ww].view(B, n_call, Hh, Ww)

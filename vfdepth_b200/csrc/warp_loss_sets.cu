@@ -53,7 +53,8 @@ __device__ __forceinline__ int wrap_row(int v, int n) { return v >= n ? v - n : 
 // exists / its alignment parameters are not finite, so even an all-zero sample goes through the arithmetic (NaN * 0 must
 // stay NaN as in the reference).  Returns the spatial-presence
 // flags of fill_region_n (warp_tile.cuh): bit 0 = some pixel filled now has a spatial / spatio-temporal warp (or such a
-// warp's parameters are not finite), bit 1 = the same for rows >= kTileH (the rows the next tile of the strip shares).
+// warp's parameters are not finite), bit 1 = the same for rows >= kTileH (the rows the next tile of the strip shares),
+// bit 2 = some value written to the region is not finite.
 template <int SET, int NSRC>
 __device__ __forceinline__ unsigned fill_set(const WarpCtx& ctx, const vfd_warp_desc& d, int b, int ci, int ox, int oy,
                                              const float4* __restrict__ raw, const uint8_t* __restrict__ vbits, float* sm,
@@ -100,12 +101,15 @@ __device__ __forceinline__ unsigned fill_set(const WarpCtx& ctx, const vfd_warp_
                     tw[j][2] = VFD_ADD(0.f, warp_normalise(ctx.prm[j], w[j].z, w[j].w));
                 }
             }
+            float chk = 0.f;      // a non-finite value anywhere in the region switches the masked-pixel skip of phase B off
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
                 img[(c * 2 + 0) * Rg::R + s] = make_float2(tw[0][c], tw[1][c]);
                 img[(c * 2 + 1) * Rg::R + s] = make_float2(v0[c], v1[c]);
                 sm[Rg::kAux + c * Rg::R + s] = vr[c];
+                chk += (tw[0][c] + tw[1][c]) + (v0[c] + v1[c]) + vr[c];
             }
+            if (!isfinite(chk)) flags |= 4u;
         } else {
             float4 w[NWc];
 #pragma unroll
@@ -132,13 +136,16 @@ __device__ __forceinline__ unsigned fill_set(const WarpCtx& ctx, const vfd_warp_
                     }
                 }
             }
+            float chk = 0.f;
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
                 img[(c * 2 + 0) * Rg::R + s] = make_float2(ov[1][c], ov[2][c]);
                 img[(c * 2 + 1) * Rg::R + s] = make_float2(ov[0][c], vr[c]);
+                chk += (ov[1][c] + ov[2][c]) + (ov[0][c] + vr[c]);
             }
 #pragma unroll
             for (int f = 0; f < 3; ++f) sm[Rg::kAux + f * Rg::R + s] = om[f];
+            if (!isfinite(chk + (om[0] + om[1] + om[2]))) flags |= 4u;
         }
     }
     return flags;
@@ -295,6 +302,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
     bool cont = false;         // the previous tile of the strip was processed: its last 4 region / 2 ring rows are in place
     int base = 0, cbase = 0;   // circular offsets of the region (mod RH) and of the ring (mod Cf::RH)
     int nproc = 0;             // tiles processed so far: parity picks the s_dP buffer and the flag word
+    bool nonfinite = false;    // a non-finite value has entered the region since the last fresh fill
     for (int tyi = ty_first; tyi < ty_last; ++tyi) {
         const int tile = tyi * gridDim.x + blockIdx.x;
         if (SET == 1 && a.tile_flag[bc * ntile + tile] == 0) {      // CTA-uniform
@@ -313,16 +321,19 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
         const unsigned fl = n_src == 2 ? fill_set<SET, 2>(ctx, d, b, ci, ox, oy, raw, vbits, sm, cont ? 4 : 0, base, live_w, always_w)
                                        : fill_set<SET, 1>(ctx, d, b, ci, ox, oy, raw, vbits, sm, cont ? 4 : 0, base, live_w, always_w);
         bool sp = true;
-        if (SET == 0) {
-            // any spatial / spatio-temporal warp in this tile's region?  (flag words alternate between tiles; the other one
-            // is cleared for the next tile now that every thread is past the previous tile's read of it)
-            const unsigned any = cta_or(fl, &s_flags[nproc & 1]);
-            if (threadIdx.x == 0) s_flags[(nproc + 1) & 1] = 0u;
+        // CTA-wide OR of the fill's flags (flag words alternate between tiles; the other one is cleared for the next tile now
+        // that every thread is past the previous tile's read of it)
+        const unsigned any = cta_or(fl, &s_flags[nproc & 1]);
+        if (threadIdx.x == 0) s_flags[(nproc + 1) & 1] = 0u;
+        // a pixel whose self-occlusion mask is 0 has every loss mask 0: its SSIM is skipped (coefficients and sums are
+        // exactly the zeros the masked products give) -- unless something non-finite has entered the strip's region, in
+        // which case the arithmetic runs so that NaN * 0 stays NaN as in the reference
+        if (!cont) nonfinite = false;
+        nonfinite = nonfinite || (any & 4u) != 0u || (always_w != 0u);
+        if (SET == 0) {      // any spatial / spatio-temporal warp in this tile's region?
             sp = ((any & 1u) | (cont ? carried : 0u)) != 0u;
             carried = (any >> 1) & 1u;
             if (threadIdx.x == 0) a.tile_flag[bc * ntile + tile] = sp ? 1 : 0;
-        } else {
-            __syncthreads();
         }
 
         // ---- phase B: loss decisions + SSIM derivative coefficients on the ring ----
@@ -336,6 +347,12 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
             const int p = y * W + x;
             const int rs = wrap_row(rr + cbase, Cf::RH) * Cf::RW + cx;
             const float rm = __ldg(rmaskp + p);
+            if (rm == 0.f && !nonfinite) {      // masked out (see above): zero coefficients, no contribution to any sum
+#pragma unroll
+                for (int c = 0; c < Cf::kPlanes; ++c) cf4[c * Cf::R + rs] = f4_zero();
+                if (SET == 0 && x >= tx0 && x < tx0 + kSetW && y >= strip_y0 && y < strip_y1) abit[p] = 0;
+                continue;
+            }
             int idx[9];
             tap_slots(x, y, W, H, ox, oy, base, idx);
             float2 L[2];
