@@ -647,6 +647,32 @@ def test_training_mode_set_kernels_ragged_shapes(height, width, batch, over):
         assert H.rel_err(a, b) < 5e-5
 
 
+def test_training_mode_nan_under_a_zero_mask_propagates():
+    """The set kernels skip the SSIM of pixels whose self-occlusion mask is 0 -- but only while every value of the strip's
+    region is finite: the reference multiplies the loss map by the mask AFTER computing it, so a NaN in the target image
+    under a zero mask makes the camera's loss NaN (NaN * 0), and so must both kernel paths."""
+    from vfdepth_b200 import view
+    dev = _dev()
+    cfg, inp, ex = _rig(64, 96, 1, seed=21)
+    cam = 2
+    ys, xs = (inp['mask'][0, cam, 0] == 0).nonzero(as_tuple=True)
+    assert ys.numel() > 0
+    inp = dict(inp)
+    color = inp[('color', 0, 0)].clone()
+    color[0, cam, 1, ys[ys.numel() // 2], xs[xs.numel() // 2]] = float('nan')
+    inp[('color', 0, 0)] = color
+    for fused in (True, False):
+        view._WarpLoss.fuse_training = fused
+        try:
+            total, det, _ = _run_gpu(cfg, inp, ex, dev)
+        finally:
+            view._WarpLoss.fuse_training = True
+        terms = det['terms'].cpu()
+        assert torch.isnan(terms[cam, 0]), (fused, terms)                  # reprojection term of that camera
+        assert torch.isfinite(terms[[c for c in range(6) if c not in (cam, (cam + 1) % 6, (cam - 1) % 6)]]).all(), (fused, terms)
+        assert torch.isnan(total)
+
+
 def test_step_is_cuda_graph_capturable():
     """the view-synthesis half of a step (to_depth -> warp/loss training mode -> gradients) captured with
     vfdepth_b200.graph.capture replays to the eager result: no entry point synchronises, allocates or copies from
