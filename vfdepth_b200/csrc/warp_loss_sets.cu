@@ -262,6 +262,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
     __shared__ float s_dP[2][kTilePixels / 32][kSlots * 12];
     __shared__ double sacc[4];
     __shared__ unsigned s_flags[2];
+    __shared__ unsigned s_nz[SetCoef<SET>::RH];      // per ring row (circular like the coefficient planes): bit = column
     float* sm = vfd_warp_smem;
     float4* cf4 = reinterpret_cast<float4*>(sm + Rg::kFloats);
     const int b = blockIdx.z / d.n_call, ci = blockIdx.z % d.n_call, cam = d.cam0 + ci;
@@ -341,9 +342,11 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
         static_assert(Cf::RW <= 32, "ring row = one warp");
         for (int rr = (cont ? 2 : 0) + (threadIdx.x >> 5); rr < Cf::RH; rr += kTileThreads / 32) {
             const int cx = threadIdx.x & 31;
-            if (cx >= Cf::RW) continue;
+            bool nz = false;      // this ring pixel carries a non-zero upstream weight (its coefficients can be non-zero)
+            do {
+            if (cx >= Cf::RW) break;
             const int x = tx0 - 1 + cx, y = ty0 - 1 + rr;
-            if (x < 0 || x >= W || y < 0 || y >= H) continue;
+            if (x < 0 || x >= W || y < 0 || y >= H) break;
             const int p = y * W + x;
             const int rs = wrap_row(rr + cbase, Cf::RH) * Cf::RW + cx;
             const float rm = __ldg(rmaskp + p);
@@ -351,7 +354,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
 #pragma unroll
                 for (int c = 0; c < Cf::kPlanes; ++c) cf4[c * Cf::R + rs] = f4_zero();
                 if (SET == 0 && x >= tx0 && x < tx0 + kSetW && y >= strip_y0 && y < strip_y1) abit[p] = 0;
-                continue;
+                break;
             }
             int idx[9];
             tap_slots(x, y, W, H, ox, oy, base, idx);
@@ -376,6 +379,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                 const bool keep = reproj <= ident;      // argmin over cat([reproj, identity]) == 0 (loss_util.py:15-17)
                 const float automask = VFD_MUL(keep ? 1.f : 0.f, rm);
                 const float wr = w_set[0] * automask;
+                nz = wr != 0.f;      // (a NaN weight counts)
 #pragma unroll
                 for (int c = 0; c < 3; ++c)
                     cf4[c * Cf::R + rs] = make_float4(wr * (s1 ? g0.a[c].y : g0.a[c].x), wr * (s1 ? g0.b[c].y : g0.b[c].x),
@@ -397,6 +401,7 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                 float st_mask = VFD_MUL(VFD_MUL(rm, sm[Rg::kAux + Rg::R + ctr]), automask);
                 if (two) st_mask = nan_max(st_mask, VFD_MUL(VFD_MUL(rm, sm[Rg::kAux + 2 * Rg::R + ctr]), automask));
                 const float ws = w_set[1] * sp_mask, wt = w_set[2] * st_mask;
+                nz = ws != 0.f || wt != 0.f;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     cf4[c * Cf::R + rs] = make_float4(ws * g1.a[c].x, ws * g1.b[c].x, ws * g1.c[c].x,
@@ -409,6 +414,11 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
                     facc[2] += VFD_MUL(stl, st_mask);     facc[3] += st_mask;
                 }
             }
+            } while (0);
+            // which ring pixels of this row can contribute: phase C skips the 3x3 gather of a pixel whose nine taps are all
+            // zero (with the auto-mask off -- the usual case in a static scene -- or outside the overlap, most are)
+            const unsigned nzm = __ballot_sync(0xffffffffu, nz);
+            if (cx == 0) s_nz[wrap_row(rr + cbase, Cf::RH)] = nzm;
         }
         __syncthreads();
 
@@ -421,7 +431,14 @@ __global__ void __launch_bounds__(kTileThreads, SET == 0 ? VFD_SET0_CTAS : VFD_S
 #pragma unroll
         for (int k = 0; k < NP; ++k) dpred[k][0] = dpred[k][1] = dpred[k][2] = 0.f;
         float X[3] = {0.f, 0.f, 0.f}, ray[3] = {0.f, 0.f, 0.f};
+        bool taps = false;
         if (live) {
+            const int cxm = x - tx0;      // ring column of the left tap
+            const unsigned m3 = s_nz[wrap_row(y - ty0 + cbase, Cf::RH)] | s_nz[wrap_row(y - ty0 + 1 + cbase, Cf::RH)] |
+                                s_nz[wrap_row(y - ty0 + 2 + cbase, Cf::RH)];
+            taps = ((m3 >> cxm) & 7u) != 0u || nonfinite;
+        }
+        if (taps) {
             const float dep = __ldg(depth + y * W + x);
             // window sums of the coefficients as packed pairs: AB = (sum a, sum b), CJ = (sum c, unused lane -- the .w of a
             // coefficient plane rides along).  One fma.rn.f32x2 where two three-register FFMA stood: the same bits, 2/3 of
