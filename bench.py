@@ -435,6 +435,25 @@ def full_step_pass(wl, headline_ms, iters):
     return out
 
 
+def dense_mask_pass(warp, iters):
+    """the view-synthesis half with the auto-mask ON at every pixel (a huge tie-break noise makes the identity
+    reprojection lose everywhere, as tests/test_warp_gpu.py does): the loss kernels skip work where a mask is zero and the
+    synthetic rigs' auto-mask keeps under 1 % of the pixels, so this is the other end of the range -- driving data, whose
+    auto-mask typically keeps half of the pixels or more, lies in between"""
+    from vfdepth_b200 import _lib
+    noise = torch.full_like(warp.noise, 1e9)
+    fn = lambda: warp.step(warp.inputs, warp.disp, noise, warp.T)
+    fn()
+    _lib.start_event_trace()
+    ms = _event_ms(fn, iters)
+    tr = _lib.stop_event_trace()
+    per = {name: tot / max(1, n) for name, (n, tot) in tr.items()}      # ms per call
+    return {'ms_per_step': ms, 'vfd_warp_loss_train_fwd_ms': per.get('vfd_warp_loss_train_fwd'),
+            'sparse_ms_per_step': _event_ms(lambda: warp.step_resident(), iters),
+            'what': 'to_depth + warp + losses fwd+bwd of the same rigs with the auto-mask on at every pixel (eager launches), '
+                    'next to the same call on the bench rigs as they are (auto-mask sparse)'}
+
+
 def dropin_pass(warp, iters):
     """the view-synthesis half through the reference's own call pattern (models/vfdepth.py:296-313: per camera
     ViewRendering.forward then MultiCamLoss.forward on the outputs dict) instead of the rig-level view.warp_and_loss --
@@ -679,6 +698,7 @@ def run_ours(args):
             extras['full_step'] = full
             if warp is not None:
                 extras['dropin_modules'] = dropin_pass(warp, max(2, min(args.steps, 5)))
+                extras['warp_dense_auto_mask'] = dense_mask_pass(warp, max(2, min(args.steps, 5)))
         wl.g_up = None
         torch.cuda.empty_cache()
         tr = train_step_pass(dev, rank, world, args.steps)
@@ -721,7 +741,8 @@ def run_ours(args):
                            'rigs_per_step_per_gpu': args.batch, 'l2': 'inputs and outputs larger than L2 '
                            '(189 MB feature maps, 410 MB voxel volume, 2.4 GB ray samples, 0.6 GB of images per step)',
                            'sharding': 'whole rigs per rank, no data-path collective', 'host_affinity': numa, 'cuda_graph': graphed,
-                           'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms},
+                           'kernel_ms_per_step': ours_ms, 'torch_glue_ms_per_step': ms / args.steps - ours_ms,
+                           'loss_mask_density': warp.mask_density() if warp else None},
                 'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roof(ranked[0]),
                 'rooflines': [roof(n) for n in ranked[:2]],
                 'step_roofline': {'algorithmic_bytes_per_step': step_alg, 'frac_of_hbm_peak': step_alg / (ms / args.steps) / 1e6 / peak},

@@ -46,6 +46,18 @@ class WarpWorkload:
         grads = torch.autograd.grad(total, [disp] + list(Ts.values()))
         return total, grads
 
+    def mask_density(self):
+        """fractions of the pixels whose loss masks are non-zero on this workload's rigs (outside the timed region): the
+        set kernels skip work where a mask is zero, so a bench line says how sparse its synthetic data is"""
+        wi = view.WarpInputs(self.cfg, self.inputs)
+        depth = view.to_depth(self.cfg, self.disp, self.inputs[('K', 0)])
+        T = view.rig_transforms(wi, self.inputs, self.T)
+        _, den, _ = view.warp_loss_sums(wi, depth, T, self.noise)
+        px = float(self.B * self.H * self.W)
+        f = (den.double().sum(0) / (px * wi.num_cams)).tolist()
+        return {'auto_mask_kept': f[0], 'spatial_overlap': f[1], 'spatio_temporal': f[2],
+                'self_occlusion_mask_zero': float((self.inputs['mask'] == 0).double().mean())}
+
     def step_resident(self):
         return self.step(self.inputs, self.disp, self.noise, self.T)
 
