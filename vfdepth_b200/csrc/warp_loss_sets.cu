@@ -6,16 +6,18 @@
 // meet in two places: the spatio-temporal mask multiplies the auto-mask (multi_cam_loss.py:49-56) and d_depth adds them.
 // So the work is split by set:
 //   SET 0 (every tile)   temporal warps + identity images: reprojection min, auto-mask (single_cam_loss.py:17-55).
-//                        5 images per pixel, 3 coefficient planes: 42 KB -> 4 CTAs per SM.  Writes the auto-mask decision
-//                        of every pixel (one byte) and, per tile, whether its region holds a spatial / spatio-temporal
-//                        warp at all (the validity bytes of pass 1 say so).
+//                        5 images per pixel, 3 coefficient planes: 37 KB, 3 CTAs per SM at 80 registers.  Writes the
+//                        auto-mask decision of every pixel (one byte) and, per tile, whether its region holds a spatial /
+//                        spatio-temporal warp at all (the validity bytes of pass 1 say so).
 //   SET 1 (flagged tiles only, ~40 %)  overlap images: spatial + spatio-temporal losses (multi_cam_loss.py:16-59), reading
-//                        the auto-mask byte.  4 images per pixel, 6 coefficient planes: 58 KB -> 3 CTAs per SM.
+//                        the auto-mask byte.  4 images per pixel, 6 coefficient planes: 52 KB, 3 CTAs per SM.
 // Per pixel the arithmetic (SSIM tap order, decisions, coefficient products, sampler) is the one of warp_loss_bwd_kernel
 // statement for statement, so g3 / partials / sums carry the same bits; what changes is occupancy and that tiles without
-// spatial warps never touch the overlap code.  A CTA walks a strip of kStrip tiles (kSetW = 30 wide, warp_loss_bwd.cuh) top to bottom; region rows and ring
-// rows live in CIRCULAR shared-memory buffers (12 and 10 rows), so the 4 region rows / 2 ring rows the next tile shares
-// are neither moved nor recomputed.
+// spatial warps never touch the overlap code.  A CTA walks a strip of kStrip tiles (kSetW = 28 wide, warp_loss_bwd.cuh)
+// top to bottom; region rows and ring rows live in CIRCULAR shared-memory buffers (12 and 10 rows), so the 4 region rows /
+// 2 ring rows the next tile shares are neither moved nor recomputed.  Work a zero mask makes zero is skipped: the SSIM of
+// ring pixels under a zero self-occlusion mask, and the 3x3 coefficient gather of pixels whose nine taps all carry a zero
+// upstream weight (a bit per ring pixel) -- both switched off once a non-finite value enters the strip's region.
 // Measured and dropped: requesting the next tile's inputs with cp.async into a per-thread staging area one tile ahead
 // (the region fill and the barrier behind it are a third of the temporal kernel's stall samples): 1.539 vs 1.550 ms --
 // the wait is for the slowest warp of the phase, not for the loads.
