@@ -24,7 +24,13 @@ namespace vfd {
 
 constexpr int kRayWarps = 8;
 // persistent-style grid: 148 SMs x resident CTAs x a few waves of work items
-constexpr long kRayGrid = 148 * 8 * 2;
+constexpr long kRayGrid = 148 * 8 * 2;      // generic (non-vectorised) kernels
+// Column kernels: ONE resident wave of persistent CTAs, i.e. CTAs per SM = what the registers allow (forward: 64
+// registers -> 4, backward: 128 -> 2).  Measured at B = 8 -- forward 4 / 6 / 8 / 12 / 16 / 32 CTAs per SM: 0.545 / 0.668 /
+// 0.581 / 0.588 / 0.603 / 0.601 ms (6 = one and a half waves); backward 2 / 8 / 32 / 64 / 128: 0.688 / 0.725 / 0.706 /
+// 0.708 / 0.709 ms.
+constexpr long kRayGridFwd = 148 * 4;
+constexpr long kRayGridBwd = 148 * 2;
 
 struct RayArgs {
     vfd_fusion_desc d;
@@ -480,7 +486,8 @@ static int launch_ray(const RayArgs& a, bool bwd, cudaStream_t st) {
         const size_t vsmem = (size_t)kRayWarps * kb * d.h * sizeof(RaySlotW);                               \
         const long vtasks = (long)d.B * d.num_cams * d.w * ((d.D + kb - 1) / kb);                           \
         const long vblocks = (vtasks + kRayWarps - 1) / kRayWarps;                                          \
-        const unsigned vgrid = (unsigned)(vblocks < kRayGrid ? vblocks : kRayGrid);                         \
+        const long vcap = bwd ? kRayGridBwd : kRayGridFwd;                                                  \
+        const unsigned vgrid = (unsigned)(vblocks < vcap ? vblocks : vcap);                                 \
         if (vsmem <= 48 * 1024) {                                                                           \
             if (bwd) ray_sample_bwd_vec_kernel<CVAL><<<vgrid, kRayWarps * VFD_WARP, vsmem, st>>>(a);        \
             else ray_sample_fwd_vec_kernel<CVAL><<<vgrid, kRayWarps * VFD_WARP, vsmem, st>>>(a);            \
