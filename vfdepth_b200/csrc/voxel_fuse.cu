@@ -37,7 +37,7 @@ __global__ void wcat_prep_kernel(const float* __restrict__ w_no, const float* __
 
 constexpr int kFgWarps = 8, kFgThreads = kFgWarps * VFD_WARP;
 constexpr int kFgMaxCv = 64;
-constexpr int kFgCtasPerSm = 8;
+constexpr int kFgCtasPerSm = 5;    // scatter kernel: one resident wave (48 registers -> 5 CTAs per SM); 4 / 5 / 8 / 10: 0.641 / 0.637 / 0.675 / 0.640 ms for the whole backward call
 constexpr int kFgRun = 64;          // consecutive voxels one warp of the gather kernel walks
 
 struct FuseArgs {
