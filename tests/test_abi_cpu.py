@@ -179,3 +179,29 @@ def test_state_dict_keys_match_reference():
                     'reduce_dim.3.bias'}
     assert set(VFNet(cfg, 8, 8, 'pose').state_dict().keys()) == {'reduce_dim.0.weight', 'reduce_dim.0.bias',
                                                                  'reduce_dim.3.weight', 'reduce_dim.3.bias'}
+
+
+def test_warp_backward_workspace_layout():
+    """vfd_warp_bwd_workspace_bytes covers what the training-mode launches put behind each other: the d_T partial sums
+    of every 28 x 8 tile ([B*n_call][tiles][8 warps * 12] floats), one flag byte per tile (rounded up to 16 bytes) and one
+    auto-mask decision byte per pixel (csrc/warp_loss_bwd.cuh); a short workspace is refused before any launch."""
+    lib = _lib.load()
+    wd = _lib.WarpDesc()
+    wd.B, wd.num_cams, wd.H, wd.W, wd.n_src, wd.cam0, wd.n_call, wd.intensity_align = 8, 6, 384, 640, 2, 0, 6, 1
+    dummy = ctypes.c_void_p(256)          # non-NULL, never dereferenced: the checks below fail first
+    for f in range(3):
+        wd.color[f] = 256
+    wd.mask, wd.K, wd.invK = 256, 256, 256
+    tiles = ((640 + 27) // 28) * (384 // 8)
+    expect = 8 * 6 * tiles * 8 * 12 * 4 + (8 * 6 * tiles + 15) // 16 * 16 + 8 * 6 * 384 * 640
+    assert lib.vfd_warp_bwd_workspace_bytes(ctypes.byref(wd)) == expect
+    wd.H, wd.W = 75, 130                  # ragged: 5 x 10 tiles
+    tiles = 5 * 10
+    expect = 8 * 6 * tiles * 96 * 4 + (8 * 6 * tiles + 15) // 16 * 16 + 8 * 6 * 75 * 130
+    assert lib.vfd_warp_bwd_workspace_bytes(ctypes.byref(wd)) == expect
+    short = ctypes.c_size_t(expect - 1)
+    args = [ctypes.byref(wd)] + [dummy] * 8
+    assert lib.vfd_warp_loss_train_fwd(*args, short, None) == -4           # VFD_ERR_WORKSPACE
+    assert lib.vfd_warp_loss_train_bwd(ctypes.byref(wd), dummy, dummy, dummy, short, dummy, dummy, None) == -4
+    wd.n_src = 3
+    assert lib.vfd_warp_bwd_workspace_bytes(ctypes.byref(wd)) == 0         # unsupported descriptor
